@@ -1,0 +1,404 @@
+// TEST INFRASTRUCTURE — not on the product path.
+//
+// ref_harness: drives the *reference's own* classes (linked from oracle/_ref/libsu2ref.a, built by
+// oracle/build_ref.sh from /root/reference) through one solver iteration at a time, in exactly the
+// call order of CMultiGridIntegration::MultiGrid_Cycle / MultiGrid_Iteration
+// (SU2_CFD/src/integration_time.cpp:42-181) and CIntegration::Space_Integration
+// (SU2_CFD/src/integration_structure.cpp:53-193), and dumps every intermediate array of the hot path
+// as .npy files.  These dumps are the golden vectors that pin oracle/rx_oracle.cpp and the CUDA path.
+//
+// Built with -fno-access-control so that protected containers of CDriver and the private tables of
+// Framework::ReactingModelLibrary can be read without editing any reference source.
+//
+// usage: ref_harness <cfg> <nIter> <outdir> [dump_every]
+#include "../../SU2_CFD/include/driver_structure.hpp"
+#include "../../SU2_CFD/include/solver_reactive.hpp"
+#include "../../Common/include/Framework/reacting_model_library.hpp"
+#include <cstdio>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <sstream>
+#include <sys/stat.h>
+
+static std::string g_out;
+
+static void npy_write(const std::string& name, const void* data, const char* descr, size_t elsize,
+                      const std::vector<size_t>& shape) {
+  std::string path = g_out + "/" + name + ".npy";
+  FILE* f = fopen(path.c_str(), "wb");
+  if (!f) { perror(path.c_str()); exit(2); }
+  std::ostringstream hd;
+  hd << "{'descr': '" << descr << "', 'fortran_order': False, 'shape': (";
+  size_t n = 1;
+  for (size_t i = 0; i < shape.size(); ++i) { hd << shape[i] << (shape.size() == 1 || i + 1 < shape.size() ? "," : ""); n *= shape[i]; }
+  hd << "), }";
+  std::string h = hd.str();
+  size_t total = 10 + h.size() + 1;
+  size_t pad = (64 - total % 64) % 64;
+  h.append(pad, ' ');
+  h.push_back('\n');
+  unsigned char pre[10] = {0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0, (unsigned char)(h.size() & 0xff), (unsigned char)(h.size() >> 8)};
+  fwrite(pre, 1, 10, f);
+  fwrite(h.data(), 1, h.size(), f);
+  fwrite(data, elsize, n, f);
+  fclose(f);
+}
+static void dump_f64(const std::string& name, const std::vector<double>& v, std::vector<size_t> shape) {
+  npy_write(name, v.data(), "<f8", 8, shape);
+}
+static void dump_i64(const std::string& name, const std::vector<int64_t>& v, std::vector<size_t> shape) {
+  npy_write(name, v.data(), "<i8", 8, shape);
+}
+
+struct Ctx {
+  CFluidDriver* drv;
+  CGeometry* geo;
+  CConfig* cfg;
+  CSolver** sol;
+  CReactiveEulerSolver* flow;
+  CNumerics** num;
+  CIntegration* integ;
+  unsigned long nPoint, nPointDomain;
+  unsigned short nVar, nPrimVar, nPrimVarGrad, nDim, nSpecies;
+  bool rans, viscous;
+};
+
+static std::string tag(unsigned long it, int rk, const char* what) {
+  char b[128];
+  snprintf(b, sizeof b, "it%04lu_rk%d_%s", it, rk, what);
+  return b;
+}
+
+static void dump_solution(Ctx& c, const std::string& name) {
+  std::vector<double> U(c.nPoint * c.nVar);
+  for (unsigned long p = 0; p < c.nPoint; ++p)
+    for (unsigned short v = 0; v < c.nVar; ++v) U[p * c.nVar + v] = c.flow->node[p]->GetSolution(v);
+  dump_f64(name, U, {c.nPoint, c.nVar});
+}
+static void dump_residual(Ctx& c, const std::string& name) {
+  std::vector<double> R(c.nPoint * c.nVar);
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    su2double* b = c.flow->LinSysRes.GetBlock(p);
+    for (unsigned short v = 0; v < c.nVar; ++v) R[p * c.nVar + v] = b[v];
+  }
+  dump_f64(name, R, {c.nPoint, c.nVar});
+}
+static void dump_primitive(Ctx& c, const std::string& pre) {
+  std::vector<double> V(c.nPoint * c.nPrimVar), aux(c.nPoint * 6), G;
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    CVariable* n = c.flow->node[p];
+    for (unsigned short v = 0; v < c.nPrimVar; ++v) V[p * c.nPrimVar + v] = n->GetPrimitive(v);
+    aux[p * 6 + 0] = n->GetSpecificHeatCp();
+    aux[p * 6 + 1] = n->GetdPdU()[c.nDim + 1] + 1.0;  // Gamma = dPdU[rhoE] + 1
+    aux[p * 6 + 2] = c.viscous ? n->GetLaminarViscosity() : 0.0;
+    aux[p * 6 + 3] = c.viscous ? n->GetThermalConductivity() : 0.0;
+    aux[p * 6 + 4] = c.viscous ? n->GetVorticity()[2] : 0.0;
+    aux[p * 6 + 5] = c.viscous ? n->GetStrainMag() : 0.0;
+  }
+  dump_f64(pre + "V", V, {c.nPoint, c.nPrimVar});
+  dump_f64(pre + "aux", aux, {c.nPoint, 6});
+  if (c.viscous) {
+    G.resize(c.nPoint * c.nPrimVarGrad * c.nDim);
+    for (unsigned long p = 0; p < c.nPoint; ++p) {
+      su2double** g = c.flow->node[p]->GetGradient_Primitive();
+      for (unsigned short v = 0; v < c.nPrimVarGrad; ++v)
+        for (unsigned short d = 0; d < c.nDim; ++d) G[(p * c.nPrimVarGrad + v) * c.nDim + d] = g[v][d];
+    }
+    dump_f64(pre + "grad", G, {c.nPoint, c.nPrimVarGrad, c.nDim});
+  }
+}
+static void dump_turb(Ctx& c, const std::string& name) {
+  // columns: muT, k, omega, dk/dx, dk/dy, sigma_k
+  std::vector<double> T(c.nPoint * 6, 0.0);
+  if (c.rans) {
+    CSolver* ts = c.sol[TURB_SOL];
+    for (unsigned long p = 0; p < c.nPoint; ++p) {
+      T[p * 6 + 0] = ts->node[p]->GetmuT();
+      T[p * 6 + 1] = ts->node[p]->GetSolution(0);
+      T[p * 6 + 2] = ts->node[p]->GetSolution(1);
+      T[p * 6 + 3] = ts->node[p]->GetGradient()[0][0];
+      T[p * 6 + 4] = ts->node[p]->GetGradient()[0][1];
+      T[p * 6 + 5] = ts->node[p]->Get_Sigmak();
+    }
+  }
+  dump_f64(name, T, {c.nPoint, 6});
+}
+static void dump_dt(Ctx& c, const std::string& name) {
+  std::vector<double> D(c.nPoint * 3, 0.0);
+  for (unsigned long p = 0; p < c.nPointDomain; ++p) {
+    D[p * 3 + 0] = c.flow->node[p]->GetDelta_Time();
+    D[p * 3 + 1] = c.flow->node[p]->GetMax_Lambda_Inv();
+    D[p * 3 + 2] = c.viscous ? c.flow->node[p]->GetMax_Lambda_Visc() : 0.0;
+  }
+  dump_f64(name, D, {c.nPoint, 3});
+}
+
+// ---- geometry: everything the path reads from CGeometry, as flat arrays -------------------------
+static void dump_geometry(Ctx& c, std::ostringstream& js) {
+  CGeometry* g = c.geo;
+  unsigned long nEdge = g->GetnEdge();
+  std::vector<int64_t> en(nEdge * 2), gi(c.nPoint), dom(c.nPoint);
+  std::vector<double> enrm(nEdge * 2), xy(c.nPoint * 2), vol(c.nPoint);
+  for (unsigned long e = 0; e < nEdge; ++e) {
+    en[2 * e] = g->edge[e]->GetNode(0); en[2 * e + 1] = g->edge[e]->GetNode(1);
+    enrm[2 * e] = g->edge[e]->GetNormal()[0]; enrm[2 * e + 1] = g->edge[e]->GetNormal()[1];
+  }
+  std::vector<int64_t> nb_ptr(c.nPoint + 1, 0), nb_pt, nb_edge;
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    xy[2 * p] = g->node[p]->GetCoord(0); xy[2 * p + 1] = g->node[p]->GetCoord(1);
+    vol[p] = g->node[p]->GetVolume();
+    gi[p] = g->node[p]->GetGlobalIndex();
+    dom[p] = g->node[p]->GetDomain() ? 1 : 0;
+    for (unsigned short k = 0; k < g->node[p]->GetnPoint(); ++k) {
+      nb_pt.push_back(g->node[p]->GetPoint(k));
+      nb_edge.push_back(g->node[p]->GetEdge(k));
+    }
+    nb_ptr[p + 1] = nb_pt.size();
+  }
+  dump_i64("geo_edge_nodes", en, {nEdge, 2});
+  dump_f64("geo_edge_normal", enrm, {nEdge, 2});
+  dump_f64("geo_coord", xy, {c.nPoint, 2});
+  dump_f64("geo_volume", vol, {c.nPoint});
+  dump_i64("geo_global_index", gi, {c.nPoint});
+  dump_i64("geo_domain", dom, {c.nPoint});
+  dump_i64("geo_nb_ptr", nb_ptr, {c.nPoint + 1});
+  dump_i64("geo_nb_point", nb_pt, {nb_pt.size()});
+  dump_i64("geo_nb_edge", nb_edge, {nb_edge.size()});
+  js << "\"nPoint\": " << c.nPoint << ", \"nPointDomain\": " << c.nPointDomain << ", \"nEdge\": " << nEdge << ",\n";
+  js << "\"markers\": [";
+  for (unsigned short m = 0; m < g->GetnMarker(); ++m) {
+    unsigned long nv = g->nVertex[m];
+    std::vector<int64_t> vn(nv), vnn(nv);
+    std::vector<double> vnrm(nv * 2);
+    for (unsigned long v = 0; v < nv; ++v) {
+      vn[v] = g->vertex[m][v]->GetNode();
+      vnn[v] = g->vertex[m][v]->GetNormal_Neighbor();
+      vnrm[2 * v] = g->vertex[m][v]->GetNormal()[0]; vnrm[2 * v + 1] = g->vertex[m][v]->GetNormal()[1];
+    }
+    std::string ms = "geo_marker" + std::to_string(m);
+    dump_i64(ms + "_node", vn, {nv});
+    dump_i64(ms + "_normal_neighbor", vnn, {nv});
+    dump_f64(ms + "_normal", vnrm, {nv, 2});
+    std::string t = c.cfg->GetMarker_All_TagBound(m);
+    unsigned short kind = c.cfg->GetMarker_All_KindBC(m);
+    js << (m ? ",\n  " : "\n  ") << "{\"tag\": \"" << t << "\", \"kind\": " << kind << ", \"nVertex\": " << nv;
+    js.precision(17);
+    if (kind == INLET_FLOW) {
+      js << ", \"bc\": \"inlet\", \"T\": " << c.cfg->GetInlet_Ttotal(t) << ", \"Vmag\": " << c.cfg->GetInlet_Ptotal(t)
+         << ", \"dir\": [" << c.cfg->GetInlet_FlowDir(t)[0] << ", " << c.cfg->GetInlet_FlowDir(t)[1] << "], \"Ys\": [";
+      for (unsigned short s = 0; s < c.nSpecies; ++s) js << (s ? ", " : "") << c.cfg->GetInlet_MassFrac(t)[s];
+      js << "]";
+    } else if (kind == OUTLET_FLOW) {
+      js << ", \"bc\": \"outlet\", \"P\": " << c.cfg->GetOutlet_Pressure(t);
+    } else if (kind == ISOTHERMAL) {
+      js << ", \"bc\": \"isothermal\", \"Twall\": " << c.cfg->GetIsothermal_Temperature(t);
+    } else if (kind == HEAT_FLUX) {
+      js << ", \"bc\": \"heatflux\", \"q\": " << c.cfg->GetWall_HeatFlux(t);
+    } else if (kind == EULER_WALL) {
+      js << ", \"bc\": \"euler_wall\"";
+    } else {
+      js << ", \"bc\": \"other\"";
+    }
+    js << "}";
+  }
+  js << "],\n";
+}
+
+// ---- chemistry library internals (Common/src/Framework/reacting_model_library.cpp) ---------------
+static void dump_chem(Ctx& c, std::ostringstream& js) {
+  using namespace Framework;
+  ReactingModelLibrary lib(c.cfg->GetConfigLibFile(), c.cfg->GetLibraryPath());
+  lib.Setup();
+  unsigned short Ns = lib.nSpecies, Nr = lib.nReactions;
+  js.precision(17);
+  js << "\"chem\": {\"Ns\": " << Ns << ", \"Nr\": " << Nr << ", \"species\": [";
+  std::vector<std::string> names(Ns);
+  for (auto& kv : lib.Species_Names) names[kv.second] = kv.first;
+  for (unsigned short s = 0; s < Ns; ++s) js << (s ? ", " : "") << "\"" << names[s] << "\"";
+  auto vec = [&](const char* k, const std::vector<double>& v) {
+    js << "], \"" << k << "\": [";
+    for (size_t i = 0; i < v.size(); ++i) js << (i ? ", " : "") << v[i];
+  };
+  vec("mMasses", lib.mMasses); vec("Ri", lib.Ri); vec("Diff_Volumes", lib.Diff_Volumes);
+  vec("Formation_Enthalpies", lib.Formation_Enthalpies);
+  if (Nr) {
+    vec("As", lib.As); vec("Betas", lib.Betas); vec("Temps_Activation", lib.Temps_Activation);
+    std::vector<double> rev(Nr), avb(Nr, 0), Ab(Nr, 0), Bb(Nr, 0), Tb(Nr, 0);
+    for (unsigned short r = 0; r < Nr; ++r) {
+      rev[r] = lib.Reversible_Reactions[r];
+      if (lib.Available_Backward_Rate.count(r)) { avb[r] = 1; Ab[r] = lib.As_back[r]; Bb[r] = lib.Betas_back[r]; Tb[r] = lib.Temps_Activation_back[r]; }
+    }
+    vec("Reversible", rev); vec("Available_Backward", avb); vec("As_back", Ab); vec("Betas_back", Bb); vec("Temps_Activation_back", Tb);
+    // matrices, all written as [reaction][species]
+    auto mat_sr = [&](const char* k, const Eigen::MatrixXd& M, bool species_rows) {
+      js << "], \"" << k << "\": [";
+      for (unsigned short r = 0; r < Nr; ++r)
+        for (unsigned short s = 0; s < Ns; ++s) js << ((r || s) ? ", " : "") << (species_rows ? M(s, r) : M(r, s));
+    };
+    mat_sr("Stoich_Reactants", lib.Stoich_Coeffs_Reactants, true);
+    mat_sr("Stoich_Products", lib.Stoich_Coeffs_Products, true);
+    mat_sr("Stoich_Reactants_Exp", lib.Stoich_Coeffs_Reactants_Exp, false);
+    mat_sr("Stoich_Products_Exp", lib.Stoich_Coeffs_Products_Exp, false);
+  }
+  js << "]},\n";
+  // spline tables: [prop][species][knot], prop order mu, kappa, cp, h, s; x grid shared
+  typedef decltype(lib.Mu_Spline) SplTab;
+  const SplTab* tabs[5] = {&lib.Mu_Spline, &lib.Kappa_Spline, &lib.Cp_Spline, &lib.Enth_Spline, &lib.Entr_Spline};
+  size_t n = std::get<0>(lib.Mu_Spline[0]).size();
+  std::vector<double> X(std::get<0>(lib.Mu_Spline[0])), Y(5 * Ns * n), Y2(5 * Ns * n);
+  for (int t = 0; t < 5; ++t)
+    for (unsigned short s = 0; s < Ns; ++s) {
+      const auto& tp = (*tabs[t])[s];
+      if (std::get<0>(tp).size() != n) { fprintf(stderr, "spline grids differ\n"); exit(3); }
+      for (size_t k = 0; k < n; ++k) {
+        Y[(t * Ns + s) * n + k] = std::get<1>(tp)[k];
+        Y2[(t * Ns + s) * n + k] = std::get<2>(tp).data()[k];  // y2[n-1] lives past size() (spline.cpp:54); read via data()
+      }
+    }
+  dump_f64("chem_x", X, {n});
+  dump_f64("chem_y", Y, {5, (size_t)Ns, n});
+  dump_f64("chem_y2", Y2, {5, (size_t)Ns, n});
+}
+
+static void dump_config(Ctx& c, std::ostringstream& js) {
+  CConfig* f = c.cfg;
+  js.precision(17);
+  js << "\"cfg\": {\"kind_solver\": " << f->GetKind_Solver() << ", \"rans\": " << (c.rans ? 1 : 0) << ", \"viscous\": " << (c.viscous ? 1 : 0)
+     << ", \"turb_model\": " << f->GetKind_Turb_Model()
+     << ", \"mach\": " << f->GetMach() << ", \"cfl\": " << f->GetCFL(MESH_0) << ", \"max_dt\": " << f->GetMax_DeltaTime()
+     << ", \"Tmin\": " << f->GetTemperatureMin() << ", \"Tmax\": " << f->GetTemperatureMax()
+     << ", \"clip_T\": " << (f->GetClipping_Temp() ? 1 : 0)
+     << ", \"ignition\": " << (f->GetIgnition() ? 1 : 0) << ", \"ignition_iter\": " << f->GetIgnitionIter()
+     << ", \"ignition_T\": " << f->GetIgnitionTemperature() << ", \"fuel_index\": " << f->GetFuelIndex()
+     << ", \"oxidizer_index\": " << f->GetOxidizerIndex()
+     << ", \"prandtl_lam\": " << f->GetPrandtl_Lam() << ", \"prandtl_turb\": " << f->GetPrandtl_Turb()
+     << ", \"lewis_turb\": " << f->GetLewis_Turb() << ", \"c_mu\": " << f->Get_Cmu() << ", \"pasr_lb\": " << f->Get_PaSR_LB()
+     << ", \"tke_inf\": " << (c.rans ? c.flow->GetTke_Inf() : 0.0)
+     << ", \"grad_method\": " << f->GetKind_Gradient_Method() << ", \"time_scheme\": " << f->GetKind_TimeIntScheme_Flow()
+     << ", \"kind_inlet\": " << f->GetKind_Inlet()
+     << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
+     << ", \"nRK\": " << f->GetnRKStep() << ", \"rk_alpha\": [";
+  for (unsigned short k = 0; k < f->GetnRKStep(); ++k) js << (k ? ", " : "") << f->Get_Alpha_RKStep(k);
+  js << "], \"lower\": [";
+  for (unsigned short v = 0; v < c.nVar; ++v) js << (v ? ", " : "") << c.flow->Lower_Limit[v];
+  js << "], \"upper\": [";
+  for (unsigned short v = 0; v < c.nVar; ++v) js << (v ? ", " : "") << c.flow->Upper_Limit[v];
+  js << "]}\n";
+}
+
+// ---- boundary loop, same order as CIntegration::Space_Integration (integration_structure.cpp:89-190)
+static void apply_bcs(Ctx& c) {
+  CSolver* s = c.flow;
+  for (unsigned short m = 0; m < c.cfg->GetnMarker_All(); ++m) {
+    switch (c.cfg->GetMarker_All_KindBC(m)) {
+      case EULER_WALL: s->BC_Euler_Wall(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.cfg, m); break;
+      case INLET_FLOW: s->BC_Inlet(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      case OUTLET_FLOW: s->BC_Outlet(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      case SUPERSONIC_INLET: s->BC_Supersonic_Inlet(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      case SUPERSONIC_OUTLET: s->BC_Supersonic_Outlet(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      case SYMMETRY_PLANE: s->BC_Sym_Plane(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      default: break;
+    }
+  }
+  for (unsigned short m = 0; m < c.cfg->GetnMarker_All(); ++m) {
+    switch (c.cfg->GetMarker_All_KindBC(m)) {
+      case ISOTHERMAL: s->BC_Isothermal_Wall(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      case HEAT_FLUX: s->BC_HeatFlux_Wall(c.geo, c.sol, c.num[CONV_BOUND_TERM], c.num[VISC_BOUND_TERM], c.cfg, m); break;
+      default: break;
+    }
+  }
+}
+
+int main(int argc, char** argv) {
+  if (argc < 4) { fprintf(stderr, "usage: ref_harness <cfg> <nIter> <outdir> [dump_from_iter]\n"); return 1; }
+  char cfgname[MAX_STRING_SIZE];
+  strcpy(cfgname, argv[1]);
+  unsigned long nIter = atol(argv[2]);
+  g_out = argv[3];
+  unsigned long dump_from = argc > 4 ? atol(argv[4]) : 0;
+  mkdir(g_out.c_str(), 0755);
+
+  SU2_Comm comm(0);
+  CConfig* cfg0 = new CConfig(cfgname, SU2_CFD);
+  unsigned short nZone = CConfig::GetnZone(cfg0->GetMesh_FileName(), cfg0->GetMesh_FileFormat(), cfg0);
+  unsigned short nDim = CConfig::GetnDim(cfg0->GetMesh_FileName(), cfg0->GetMesh_FileFormat());
+  delete cfg0;
+  CFluidDriver* drv = new CFluidDriver(cfgname, nZone, nDim, comm);
+
+  Ctx c;
+  c.drv = drv;
+  c.geo = drv->geometry_container[ZONE_0][MESH_0];
+  c.cfg = drv->config_container[ZONE_0];
+  c.sol = drv->solver_container[ZONE_0][MESH_0];
+  c.flow = dynamic_cast<CReactiveEulerSolver*>(c.sol[FLOW_SOL]);
+  if (!c.flow) { fprintf(stderr, "not a reactive solver\n"); return 4; }
+  c.num = drv->numerics_container[ZONE_0][MESH_0][FLOW_SOL];
+  c.integ = drv->integration_container[ZONE_0][FLOW_SOL];
+  c.nPoint = c.geo->GetnPoint(); c.nPointDomain = c.geo->GetnPointDomain();
+  c.nDim = nDim; c.nSpecies = c.flow->nSpecies; c.nVar = c.flow->nVar; c.nPrimVar = c.flow->nPrimVar;
+  c.nPrimVarGrad = c.flow->nPrimVarGrad;
+  unsigned short kind = c.cfg->GetKind_Solver();
+  c.rans = (kind == REACTIVE_RANS);
+  c.viscous = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
+
+  std::ostringstream js;
+  js << "{\n\"nDim\": " << nDim << ", \"nVar\": " << c.nVar << ", \"nPrimVar\": " << c.nPrimVar << ", \"nPrimVarGrad\": " << c.nPrimVarGrad
+     << ", \"nIter\": " << nIter << ",\n";
+  dump_geometry(c, js);
+  dump_chem(c, js);
+  dump_config(c, js);
+  js << "}\n";
+  { FILE* f = fopen((g_out + "/meta.json").c_str(), "w"); fputs(js.str().c_str(), f); fclose(f); }
+
+  std::vector<double> hist;
+  for (unsigned long it = 0; it < nIter; ++it) {
+    bool dmp = it >= dump_from;
+    drv->PreprocessExtIter(it);
+    c.cfg->SetGlobalParam(kind, RUNTIME_REACTIVE_SYS, it);
+    if (dmp) {
+      dump_solution(c, tag(it, 0, "U0"));
+      dump_primitive(c, tag(it, 0, "prev_"));   // V[T] here is the secant start value (variable_direct_reactive.cpp:622)
+      dump_turb(c, tag(it, 0, "turb"));
+    }
+    unsigned short nRK = (c.cfg->GetKind_TimeIntScheme() == RUNGE_KUTTA_EXPLICIT) ? c.cfg->GetnRKStep() : 1;
+    for (unsigned short rk = 0; rk < nRK; ++rk) {
+      c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, rk, RUNTIME_REACTIVE_SYS, false);
+      if (dmp) dump_primitive(c, tag(it, rk, "pre_"));
+      if (rk == 0) {
+        c.flow->Set_OldSolution(c.geo);
+        c.flow->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, it);
+        if (dmp) dump_dt(c, tag(it, rk, "dt"));
+      }
+      c.flow->Upwind_Residual(c.geo, c.sol, c.num[CONV_TERM], c.cfg, MESH_0);
+      if (dmp) dump_residual(c, tag(it, rk, "res_conv"));
+      c.flow->Viscous_Residual(c.geo, c.sol, c.num[VISC_TERM], c.cfg, MESH_0, rk);
+      if (dmp) dump_residual(c, tag(it, rk, "res_visc"));
+      c.flow->Source_Residual(c.geo, c.sol, c.num[SOURCE_FIRST_TERM], c.num[SOURCE_SECOND_TERM], c.cfg, MESH_0);
+      if (dmp) dump_residual(c, tag(it, rk, "res_src"));
+      apply_bcs(c);
+      if (dmp) dump_residual(c, tag(it, rk, "res_bc"));
+      c.integ->Time_Integration(c.geo, c.sol, c.cfg, rk, RUNTIME_REACTIVE_SYS, it);
+      if (dmp) {
+        dump_solution(c, tag(it, rk, "U1"));
+        std::vector<double> rms(c.nVar);
+        for (unsigned short v = 0; v < c.nVar; ++v) rms[v] = c.flow->GetRes_RMS(v);
+        dump_f64(tag(it, rk, "rms"), rms, {c.nVar});
+      }
+      c.flow->Postprocessing(c.geo, c.sol, c.cfg, MESH_0);
+    }
+    c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
+    if (dmp) dump_primitive(c, tag(it, 0, "out_"));
+    if (c.rans) {
+      c.cfg->SetGlobalParam(REACTIVE_RANS, RUNTIME_TURB_SYS, it);
+      drv->integration_container[ZONE_0][TURB_SOL]->SingleGrid_Iteration(drv->geometry_container, drv->solver_container,
+                                                                         drv->numerics_container, drv->config_container,
+                                                                         RUNTIME_TURB_SYS, it, ZONE_0);
+    }
+    double r0 = log10(c.flow->GetRes_RMS(0)), r3 = log10(c.flow->GetRes_RMS(nDim + 1));
+    printf("HARNESS it %lu  Res[Rho] %.6f  Res[RhoE] %.6f\n", it, r0, r3);
+    hist.push_back(r0); hist.push_back(r3);
+  }
+  dump_f64("history", hist, {(size_t)nIter, 2});
+  return 0;
+}
