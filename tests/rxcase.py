@@ -1,0 +1,213 @@
+"""Test helpers: load a golden case (dump of the reference's own classes, see oracle/ref_harness.cpp and
+oracle/make_golden.py) and drive the CPU oracle (oracle/rx_oracle.cpp) through ctypes.
+
+TEST INFRASTRUCTURE ONLY — nothing here is on the product path.
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+ORACLE_SRC = os.path.join(ROOT, "oracle", "rx_oracle.cpp")
+ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "librx_oracle.so")
+
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL = 1, 2, 3
+_BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL}
+
+
+def build_oracle(force=False):
+    """Compile the C++ restatement (gcc only, no FMA contraction: x86-64 baseline ISA like the reference build)."""
+    if force or not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(ORACLE_SRC):
+        os.makedirs(os.path.dirname(ORACLE_SO), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-w",
+                               "-o", ORACLE_SO, ORACLE_SRC])
+    return ORACLE_SO
+
+
+class Case:
+    """A golden case: meta (json), geometry + chemistry tables, and per-iteration stage dumps."""
+
+    def __init__(self, path):
+        if os.path.isdir(path):
+            self.meta = json.load(open(os.path.join(path, "meta.json")))
+            self.arr = {f[:-4]: np.load(os.path.join(path, f)) for f in os.listdir(path) if f.endswith(".npy")}
+        else:
+            z = np.load(path, allow_pickle=False)
+            self.meta = json.loads(bytes(z["meta_json"]).decode())
+            self.arr = {k: z[k] for k in z.files if k != "meta_json"}
+        m = self.meta
+        self.nPoint, self.nPointDomain, self.nEdge = m["nPoint"], m["nPointDomain"], m["nEdge"]
+        self.Ns, self.Nr = m["chem"]["Ns"], m["chem"]["Nr"]
+        self.nVar, self.nPrim, self.nGrad = self.Ns + 4, self.Ns + 7, self.Ns + 4
+
+    def __getitem__(self, k):
+        return self.arr[k]
+
+    def has(self, k):
+        return k in self.arr
+
+    def stage(self, it, rk, what):
+        return self.arr["it%04d_rk%d_%s" % (it, rk, what)]
+
+
+def _p(a, t=C.c_double):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class _Chem(C.Structure):
+    _fields_ = [("Ns", C.c_int), ("Nr", C.c_int), ("nKnots", C.c_int)] + [
+        (n, C.POINTER(C.c_double)) for n in
+        ["mMasses", "diffVol", "x", "y", "y2", "As", "Betas", "Ta", "reversible", "availBack", "AsB", "BetasB", "TaB",
+         "nuR", "nuP", "expR", "expP"]]
+
+
+class _Marker(C.Structure):
+    _fields_ = [("kind", C.c_int), ("nVertex", C.c_int), ("node", C.POINTER(C.c_int64)),
+                ("normalNeighbor", C.POINTER(C.c_int64)), ("normal", C.POINTER(C.c_double)),
+                ("T", C.c_double), ("Vmag", C.c_double), ("dir", C.c_double * 2), ("Ys", C.POINTER(C.c_double)),
+                ("P", C.c_double), ("Twall", C.c_double)]
+
+
+class _Mesh(C.Structure):
+    _fields_ = [("nPoint", C.c_int64), ("nPointDomain", C.c_int64), ("nEdge", C.c_int64),
+                ("edgeNodes", C.POINTER(C.c_int64)), ("edgeNormal", C.POINTER(C.c_double)),
+                ("coord", C.POINTER(C.c_double)), ("volume", C.POINTER(C.c_double)),
+                ("nbPtr", C.POINTER(C.c_int64)), ("nbPoint", C.POINTER(C.c_int64)),
+                ("nMarker", C.c_int), ("markers", C.POINTER(_Marker))]
+
+
+class _Opts(C.Structure):
+    _fields_ = [("viscous", C.c_int), ("rans", C.c_int), ("leastSquares", C.c_int),
+                ("mInfty", C.c_double), ("cfl", C.c_double), ("maxDt", C.c_double), ("Tmin", C.c_double), ("Tmax", C.c_double),
+                ("clipT", C.c_int), ("ignition", C.c_int), ("ignitionIter", C.c_int64), ("ignitionT", C.c_double),
+                ("fuelIndex", C.c_int), ("oxidizerIndex", C.c_int),
+                ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
+                ("pasrLb", C.c_double), ("tkeInf", C.c_double)]
+
+
+def chem_arrays(case):
+    """Chemistry tables as contiguous float64 arrays keyed like rxo_chem / rx_chem."""
+    ch = case.meta["chem"]
+    Ns, Nr = ch["Ns"], ch["Nr"]
+    f = lambda k, n: np.ascontiguousarray(np.array(ch.get(k, [0.0] * n), dtype=np.float64).reshape(-1)) if n else np.zeros(1)
+    return dict(
+        Ns=Ns, Nr=Nr, nKnots=int(case["chem_x"].shape[0]),
+        mMasses=f("mMasses", Ns), diffVol=f("Diff_Volumes", Ns),
+        x=np.ascontiguousarray(case["chem_x"]), y=np.ascontiguousarray(case["chem_y"]), y2=np.ascontiguousarray(case["chem_y2"]),
+        As=f("As", Nr), Betas=f("Betas", Nr), Ta=f("Temps_Activation", Nr), reversible=f("Reversible", Nr),
+        availBack=f("Available_Backward", Nr), AsB=f("As_back", Nr), BetasB=f("Betas_back", Nr), TaB=f("Temps_Activation_back", Nr),
+        nuR=f("Stoich_Reactants", Nr * Ns), nuP=f("Stoich_Products", Nr * Ns),
+        expR=f("Stoich_Reactants_Exp", Nr * Ns), expP=f("Stoich_Products_Exp", Nr * Ns))
+
+
+def opts_dict(case):
+    cf = case.meta["cfg"]
+    return dict(viscous=cf["viscous"], rans=cf["rans"], leastSquares=1 if cf["grad_method"] == 2 else 0,
+                mInfty=cf["mach"], cfl=cf["cfl"], maxDt=cf["max_dt"], Tmin=cf["Tmin"], Tmax=cf["Tmax"], clipT=cf["clip_T"],
+                ignition=cf["ignition"], ignitionIter=cf["ignition_iter"], ignitionT=cf["ignition_T"],
+                fuelIndex=cf["fuel_index"], oxidizerIndex=cf["oxidizer_index"], prandtlLam=cf["prandtl_lam"],
+                prandtlTurb=cf["prandtl_turb"], lewisTurb=cf["lewis_turb"], cMu=cf["c_mu"], pasrLb=cf["pasr_lb"],
+                tkeInf=cf["tke_inf"])
+
+
+def marker_list(case):
+    out = []
+    for k, mk in enumerate(case.meta["markers"]):
+        d = dict(kind=_BC_KIND.get(mk["bc"], 0), tag=mk["tag"],
+                 node=np.ascontiguousarray(case["geo_marker%d_node" % k], dtype=np.int64),
+                 normalNeighbor=np.ascontiguousarray(case["geo_marker%d_normal_neighbor" % k], dtype=np.int64),
+                 normal=np.ascontiguousarray(case["geo_marker%d_normal" % k], dtype=np.float64),
+                 T=mk.get("T", 0.0), Vmag=mk.get("Vmag", 0.0), dir=mk.get("dir", [0.0, 0.0]),
+                 Ys=np.array(mk.get("Ys", [0.0] * case.Ns), dtype=np.float64), P=mk.get("P", 0.0), Twall=mk.get("Twall", 0.0))
+        out.append(d)
+    return out
+
+
+class Oracle:
+    """ctypes driver of oracle/rx_oracle.cpp for one case."""
+
+    def __init__(self, case, opts_override=None):
+        self.case = case
+        self.lib = C.CDLL(build_oracle())
+        L = self.lib
+        L.rxo_create.restype = C.c_void_p
+        L.rxo_preprocess.restype = C.c_int64
+        self._keep = []
+        ca = chem_arrays(case)
+        ch = _Chem(ca["Ns"], ca["Nr"], ca["nKnots"], *[_p(ca[n[0]]) for n in _Chem._fields_[3:]])
+        self._keep.append(ca)
+        self.chem_struct = ch
+        mks = marker_list(case)
+        arr = (_Marker * len(mks))()
+        for i, d in enumerate(mks):
+            arr[i] = _Marker(d["kind"], len(d["node"]), _p(d["node"], C.c_int64), _p(d["normalNeighbor"], C.c_int64),
+                             _p(d["normal"]), d["T"], d["Vmag"], (C.c_double * 2)(*d["dir"]), _p(d["Ys"]), d["P"], d["Twall"])
+        self._keep.append(mks)
+        g = {k: np.ascontiguousarray(case[k]) for k in
+             ["geo_edge_nodes", "geo_edge_normal", "geo_coord", "geo_volume", "geo_nb_ptr", "geo_nb_point"]}
+        self._keep.append(g)
+        mesh = _Mesh(case.nPoint, case.nPointDomain, case.nEdge, _p(g["geo_edge_nodes"], C.c_int64), _p(g["geo_edge_normal"]),
+                     _p(g["geo_coord"]), _p(g["geo_volume"]), _p(g["geo_nb_ptr"], C.c_int64), _p(g["geo_nb_point"], C.c_int64),
+                     len(mks), arr)
+        od = opts_dict(case)
+        if opts_override:
+            od.update(opts_override)
+        self.opts = od
+        o = _Opts(**od)
+        self.ctx = C.c_void_p(L.rxo_create(C.byref(mesh), C.byref(ch), C.byref(o)))
+        self.nP, self.nVar, self.nPrim, self.nGrad = case.nPoint, case.nVar, case.nPrim, case.nGrad
+
+    def __del__(self):
+        try:
+            self.lib.rxo_destroy(self.ctx)
+        except Exception:
+            pass
+
+    def set_solution(self, U):
+        U = np.ascontiguousarray(U, dtype=np.float64); self.lib.rxo_set_solution(self.ctx, _p(U))
+
+    def set_temperature(self, T):
+        T = np.ascontiguousarray(T, dtype=np.float64); self.lib.rxo_set_temperature(self.ctx, _p(T))
+
+    def set_turbulence(self, t):
+        t = np.ascontiguousarray(t, dtype=np.float64); self.lib.rxo_set_turbulence(self.ctx, _p(t))
+
+    def solution(self):
+        U = np.empty((self.nP, self.nVar)); self.lib.rxo_get_solution(self.ctx, _p(U)); return U
+
+    def primitive(self):
+        V = np.empty((self.nP, self.nPrim)); aux = np.empty((self.nP, 6)); g = np.empty((self.nP, self.nGrad, 2))
+        self.lib.rxo_get_primitive(self.ctx, _p(V), _p(aux), _p(g)); return V, aux, g
+
+    def dt(self):
+        d = np.empty((self.nP, 3)); self.lib.rxo_get_dt(self.ctx, _p(d)); return d
+
+    def residual(self):
+        R = np.empty((self.nP, self.nVar)); self.lib.rxo_get_residual(self.ctx, _p(R)); return R
+
+    def preprocess(self, ext_iter, output=False):
+        return self.lib.rxo_preprocess(self.ctx, C.c_int64(ext_iter), int(output))
+
+    def set_old_solution(self): self.lib.rxo_set_old_solution(self.ctx)
+    def time_step(self): self.lib.rxo_time_step(self.ctx)
+    def upwind_residual(self): self.lib.rxo_upwind_residual(self.ctx)
+    def viscous_residual(self): self.lib.rxo_viscous_residual(self.ctx)
+    def source_residual(self): self.lib.rxo_source_residual(self.ctx)
+    def boundary_conditions(self): self.lib.rxo_boundary_conditions(self.ctx)
+
+    def explicit_update(self, alpha=1.0):
+        rms = np.empty(self.nVar); self.lib.rxo_explicit_update(self.ctx, C.c_double(alpha), _p(rms)); return rms
+
+
+def vec_rel_err(a, ref):
+    """Per-variable vector-relative error  max_p|a-ref| / max_p|ref|  (columns = variables)."""
+    a = np.asarray(a, dtype=np.float64).reshape(ref.shape[0], -1)
+    r = np.asarray(ref, dtype=np.float64).reshape(ref.shape[0], -1)
+    num = np.abs(a - r).max(axis=0)
+    den = np.abs(r).max(axis=0)
+    out = np.where(den > 0, num / np.where(den > 0, den, 1.0), num)
+    return out
