@@ -1,0 +1,170 @@
+#!/usr/bin/env python
+"""TEST INFRASTRUCTURE — generates the golden fixtures under tests/golden/ by running the *reference's own classes*
+(oracle/_ref/ref_harness, built by oracle/build_ref.sh from /root/reference) and packing the stage dumps as .npz.
+
+Runs only in the build container (needs /root/reference for the case data: chemistry/thermo/transport tables and the
+shipped .cfg).  The fixtures it writes are committed; nothing at test time reads /root/reference.
+
+It also prepares oracle/_ref/cases/<name>/ (git-ignored, travels to the GPU box) so that `bench.py --impl reference`
+can run the compiled reference there.
+
+usage: python oracle/make_golden.py [case ...]      (default: all)
+"""
+import json
+import os
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.environ.get("SU2_REFERENCE", "/root/reference")
+SHIPPED = os.path.join(REF, "Test_Cases", "TURBOLENT", "TURBOLENT_COMBUSTION")
+CASES = os.path.join(HERE, "_ref", "cases")
+HARNESS = os.path.join(HERE, "_ref", "ref_harness")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def write_channel_su2(path, nx, ny, L=0.25, H=0.025, stretch=1.0):
+    """Structured nx x ny point grid on [0,L]x[0,H]; every quad split into two triangles with alternating diagonal.
+    Markers: inlet (x=0), outlet (x=L), lower_wall (y=0), upper_wall (y=H)."""
+    xs = np.linspace(0.0, L, nx)
+    t = np.linspace(0.0, 1.0, ny)
+    if stretch != 1.0:  # symmetric wall clustering
+        t = 0.5 * (1.0 + np.tanh(stretch * (2 * t - 1)) / np.tanh(stretch))
+    ys = H * t
+    idx = lambda i, j: j * nx + i
+    with open(path, "w") as f:
+        f.write("NDIME= 2\nNELEM= %d\n" % (2 * (nx - 1) * (ny - 1)))
+        e = 0
+        for j in range(ny - 1):
+            for i in range(nx - 1):
+                a, b, c, d = idx(i, j), idx(i + 1, j), idx(i + 1, j + 1), idx(i, j + 1)
+                if (i + j) % 2 == 0:
+                    tris = [(a, b, c), (a, c, d)]
+                else:
+                    tris = [(a, b, d), (b, c, d)]
+                for tr in tris:
+                    f.write("5 %d %d %d %d\n" % (tr[0], tr[1], tr[2], e)); e += 1
+        f.write("NPOIN= %d\n" % (nx * ny))
+        for j in range(ny):
+            for i in range(nx):
+                f.write("%.17g %.17g %d\n" % (xs[i], ys[j], idx(i, j)))
+        f.write("NMARK= 4\n")
+        f.write("MARKER_TAG= inlet\nMARKER_ELEMS= %d\n" % (ny - 1))
+        for j in range(ny - 1): f.write("3 %d %d\n" % (idx(0, j), idx(0, j + 1)))
+        f.write("MARKER_TAG= outlet\nMARKER_ELEMS= %d\n" % (ny - 1))
+        for j in range(ny - 1): f.write("3 %d %d\n" % (idx(nx - 1, j), idx(nx - 1, j + 1)))
+        f.write("MARKER_TAG= lower_wall\nMARKER_ELEMS= %d\n" % (nx - 1))
+        for i in range(nx - 1): f.write("3 %d %d\n" % (idx(i, 0), idx(i + 1, 0)))
+        f.write("MARKER_TAG= upper_wall\nMARKER_ELEMS= %d\n" % (nx - 1))
+        for i in range(nx - 1): f.write("3 %d %d\n" % (idx(i, ny - 1), idx(i + 1, ny - 1)))
+
+
+def derive_cfg(src, dst, repl):
+    """Copy a shipped .cfg replacing `KEY= value` lines (keys matched case-sensitively before '=')."""
+    done = set()
+    out = []
+    for line in open(src):
+        s = line.strip()
+        if s and not s.startswith("%") and "=" in s:
+            key = s.split("=")[0].strip()
+            if key in repl:
+                if repl[key] is not None:
+                    out.append("%s= %s\n" % (key, repl[key]))
+                done.add(key)
+                continue
+        out.append(line)
+    for k, v in repl.items():
+        if k not in done and v is not None:
+            out.append("%s= %s\n" % (k, v))
+    open(dst, "w").writelines(out)
+
+
+def prepare_case_dir(name, shipped_mesh=False, nx=0, ny=0, stretch=1.0):
+    d = os.path.join(CASES, name)
+    os.makedirs(d, exist_ok=True)
+    for sub in ["Chemistry", "Mixture", "Thermo", "Transp"]:
+        if not os.path.isdir(os.path.join(d, sub)):
+            shutil.copytree(os.path.join(SHIPPED, sub), os.path.join(d, sub))
+    for f in ["test_chem_first.txt", "test_chem_second.txt", "test_no_chem.txt"]:
+        shutil.copy(os.path.join(SHIPPED, f), d)
+    if shipped_mesh:
+        shutil.copy(os.path.join(SHIPPED, "mesh_stretched.su2"), d)
+    else:
+        write_channel_su2(os.path.join(d, "mesh.su2"), nx, ny, stretch=stretch)
+    return d
+
+
+CHANNEL_MARKERS = {
+    "MARKER_ISOTHERMAL": "(upper_wall, 300.0, lower_wall, 600.0)",
+    "MARKER_INLET": "( inlet, 300.0, 20.0, 1.0, 0.0, 0.0 )",
+    "INLET_MASS_FRAC": "(inlet, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0)",
+    "MARKER_OUTLET": "( outlet, 101325.0)",
+    "MESH_FILENAME": "mesh.su2",
+    "MARKER_PLOTTING": "( upper_wall )", "MARKER_MONITORING": "( upper_wall )",
+}
+
+# name -> (case-dir kwargs, cfg replacements, nIter, dump_from, perturb_seed or None, lean fixture (drop intermediate residuals))
+SPECS = {
+    # config[0]: the jet-reactor case as shipped (REACTIVE_RANS + SST + PaSR, AUSM 1st order, WLS, explicit Euler)
+    "jet_rans_shipped": (dict(shipped_mesh=True), {"RESTART_SOL": "NO", "EXT_ITER": "3"}, 3, 2, None, True),
+    # same mesh and cfg, non-uniform synthetic state: exercises S-M diffusion, SST closure, PaSR, all BC kinds
+    "jet_rans_perturbed": (dict(shipped_mesh=True), {"RESTART_SOL": "NO", "EXT_ITER": "2"}, 2, 1, 7, True),
+    # small synthetic channel, laminar reactive NS + chemistry, explicit RK4-type, WLS gradients (config[1] in miniature)
+    "channel_lam_rk": (dict(nx=41, ny=21, stretch=1.5),
+                       dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                            TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )",
+                            CFL_NUMBER="0.2"), 2, 1, 11, False),
+    # same channel, Green-Gauss gradients, explicit Euler
+    "channel_lam_gg": (dict(nx=41, ny=21, stretch=1.5),
+                       dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="1", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                            NUM_METHOD_GRAD="GREEN_GAUSS"), 1, 0, 13, False),
+    # same channel, RANS + PaSR
+    "channel_rans": (dict(nx=41, ny=21, stretch=1.5),
+                     dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO"), 2, 1, 17, False),
+}
+
+
+def run_case(name):
+    kw, repl, nit, dump_from, seed, lean = SPECS[name]
+    d = prepare_case_dir(name, **kw)
+    derive_cfg(os.path.join(SHIPPED, "my_combustion_first_chem_PaSR.cfg"), os.path.join(d, "case.cfg"), repl)
+    out = os.path.join(d, "dump")
+    shutil.rmtree(out, ignore_errors=True)
+    cmd = [HARNESS, "case.cfg", str(nit), out, str(dump_from)] + ([str(seed)] if seed is not None else [])
+    log = subprocess.run(cmd, cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    tail = "\n".join(log.stdout.splitlines()[-6:])
+    if log.returncode != 0:
+        raise RuntimeError("harness failed for %s:\n%s" % (name, tail))
+    print(tail)
+    arrs = {}
+    for f in sorted(os.listdir(out)):
+        if f.endswith(".npy"):
+            k = f[:-4]
+            # the "prev_" dumps are only needed for T (secant start value); aux/grad copies are dropped to keep fixtures small
+            if k.endswith("prev_aux") or k.endswith("prev_grad") or k.endswith("out_grad"):
+                continue
+            if lean and k.split("_", 2)[-1] in ("res_conv", "res_visc", "res_src", "out_V", "out_aux"):
+                continue
+            a = np.load(os.path.join(out, f))
+            if k.endswith("prev_V"):
+                a = np.ascontiguousarray(a[:, :1])
+            arrs[k] = a
+    meta = open(os.path.join(out, "meta.json")).read()
+    json.loads(meta)
+    arrs["meta_json"] = np.frombuffer(meta.encode(), dtype=np.uint8)
+    os.makedirs(GOLDEN, exist_ok=True)
+    path = os.path.join(GOLDEN, name + ".npz")
+    np.savez_compressed(path, **arrs)
+    print("wrote %s  (%.2f MB)" % (path, os.path.getsize(path) / 1e6))
+    shutil.rmtree(out, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    names = sys.argv[1:] or list(SPECS)
+    for n in names:
+        print("== %s" % n)
+        run_case(n)

@@ -10,7 +10,7 @@
 // Built with -fno-access-control so that protected containers of CDriver and the private tables of
 // Framework::ReactingModelLibrary can be read without editing any reference source.
 //
-// usage: ref_harness <cfg> <nIter> <outdir> [dump_every]
+// usage: ref_harness <cfg> <nIter> <outdir> [dump_from_iter] [perturb_seed]
 #include "../../SU2_CFD/include/driver_structure.hpp"
 #include "../../SU2_CFD/include/solver_reactive.hpp"
 #include "../../Common/include/Framework/reacting_model_library.hpp"
@@ -310,8 +310,59 @@ static void apply_bcs(Ctx& c) {
   }
 }
 
+
+// ---- synthetic non-uniform initial state (so that every term of the path is exercised) ----------
+// Smooth fields + seeded noise on (T, P, u, v, Y_s, k, omega); conserved variables are rebuilt with the
+// reference's own library (ComputeEnthalpy / ComputeRgas), so the state is thermodynamically consistent.
+#include <random>
+static void perturb_state(Ctx& c, unsigned long seed) {
+  using namespace Framework;
+  ReactingModelLibrary lib(c.cfg->GetConfigLibFile(), c.cfg->GetLibraryPath());
+  lib.Setup();
+  unsigned short Ns = c.nSpecies;
+  double x0 = 1e300, x1 = -1e300, y0 = 1e300, y1 = -1e300;
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    double x = c.geo->node[p]->GetCoord(0), y = c.geo->node[p]->GetCoord(1);
+    x0 = std::min(x0, x); x1 = std::max(x1, x); y0 = std::min(y0, y); y1 = std::max(y1, y);
+  }
+  std::vector<double> U(c.nVar);
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    unsigned long gi = c.geo->node[p]->GetGlobalIndex();
+    std::mt19937_64 gen(seed * 1000003ULL + gi);
+    std::uniform_real_distribution<double> un(-1.0, 1.0);
+    double xh = (c.geo->node[p]->GetCoord(0) - x0) / (x1 - x0), yh = (c.geo->node[p]->GetCoord(1) - y0) / (y1 - y0);
+    double sh = 0.5 + 0.5 * std::tanh((yh - 0.5) * 6.0);
+    double T = 500.0 + 800.0 * std::exp(-std::pow((yh - 0.5) / 0.2, 2)) * (0.6 + 0.4 * std::sin(6.283185307179586 * xh)) + 8.0 * un(gen);
+    double P = 101325.0 * (1.0 + 0.05 * std::sin(3.0 * xh + yh)) * (1.0 + 1e-3 * un(gen));
+    double u = 30.0 * 4.0 * yh * (1.0 - yh) + 3.0 * std::sin(5.0 * xh) + 0.2 * un(gen);
+    double v = 2.0 * std::sin(6.283185307179586 * xh) * std::cos(3.141592653589793 * yh) + 0.2 * un(gen);
+    std::vector<double> Y(Ns, 0.0);
+    for (unsigned short s = 0; s < Ns; ++s) Y[s] = 0.02 * (1.0 + std::sin(1.7 * s + 4.0 * xh + 2.0 * yh)) * (1.0 + 0.1 * un(gen));
+    Y[c.cfg->GetFuelIndex()] += 1.0 - sh;
+    Y[c.cfg->GetOxidizerIndex()] += sh;
+    if (yh > 0.7) Y[c.cfg->GetFuelIndex()] = 0.0;          // exact zeros: exercise the 1e-15 / 1e-10 thresholds
+    if (xh < 0.3) Y[Ns - 1] = 0.0;
+    if (xh > 0.8 && yh < 0.3) { for (unsigned short s = 0; s < Ns; ++s) Y[s] = 0.0; Y[c.cfg->GetOxidizerIndex()] = 1.0; }
+    double sum = 0.0; for (double w : Y) sum += w;
+    for (double& w : Y) w /= sum;
+    double k = 0.0;
+    if (c.rans) {
+      k = 0.05 + 5.0 * yh * (1.0 - yh) * (1.0 + 0.2 * un(gen));
+      double om = 2.0e3 * (1.0 + 0.8 * std::sin(3.0 * xh) * std::cos(2.0 * yh)) * (1.0 + 0.1 * un(gen));
+      CVariable* t = c.sol[TURB_SOL]->node[p];
+      double rho_ = P / (lib.ComputeRgas(Y) * T);
+      t->SetSolution(0, k); t->SetSolution(1, om); t->SetSolution_Old(0, k); t->SetSolution_Old(1, om);
+      t->SetmuT(rho_ * k / om);
+    }
+    double R = lib.ComputeRgas(Y), rho = P / (R * T), h = lib.ComputeEnthalpy(T, Y);
+    U[0] = rho; U[1] = rho * u; U[2] = rho * v; U[3] = rho * (h + 0.5 * (u * u + v * v) + k) - P;
+    for (unsigned short s = 0; s < Ns; ++s) U[4 + s] = rho * Y[s];
+    for (unsigned short q = 0; q < c.nVar; ++q) { c.flow->node[p]->SetSolution(q, U[q]); c.flow->node[p]->SetSolution_Old(q, U[q]); }
+  }
+}
+
 int main(int argc, char** argv) {
-  if (argc < 4) { fprintf(stderr, "usage: ref_harness <cfg> <nIter> <outdir> [dump_from_iter]\n"); return 1; }
+  if (argc < 4) { fprintf(stderr, "usage: ref_harness <cfg> <nIter> <outdir> [dump_from_iter] [perturb_seed]\n"); return 1; }
   char cfgname[MAX_STRING_SIZE];
   strcpy(cfgname, argv[1]);
   unsigned long nIter = atol(argv[2]);
@@ -350,6 +401,8 @@ int main(int argc, char** argv) {
   dump_config(c, js);
   js << "}\n";
   { FILE* f = fopen((g_out + "/meta.json").c_str(), "w"); fputs(js.str().c_str(), f); fclose(f); }
+
+  if (argc > 5) perturb_state(c, atol(argv[5]));
 
   std::vector<double> hist;
   for (unsigned long it = 0; it < nIter; ++it) {
