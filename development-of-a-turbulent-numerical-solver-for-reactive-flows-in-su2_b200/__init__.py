@@ -1,0 +1,9 @@
+"""B200-native reactive-flow residual hot path (drop-in behind SU2's CSolver/CNumerics API for the reactive solvers).
+
+The product is csrc/ (hand-written FP64 CUDA for sm_100a + the C ABI of include/rx_cuda.h, built into librx_cuda.so).
+This Python package is the host-side mirror of the reference's solver interface used by the tests and bench.py; the
+C++ mirror compiled with SU2 lives in csrc/host/.  There is no CPU fallback: without librx_cuda.so or without a CUDA
+device every entry point raises.
+"""
+from .rx_solver import CReactiveNSSolverGPU, RxError, load_library, build_library, LIB_PATH  # noqa: F401
+from .mesh import channel_mesh, partition_strips  # noqa: F401

@@ -1,0 +1,457 @@
+// rx_cuda.cu — host side of librx_cuda.so: context, mesh flattening, and the C ABI of include/rx_cuda.h.
+// Every entry point enqueues kernels on the context's stream; there is NO CPU fallback anywhere in this library.
+#include "../../include/rx_cuda.h"
+#include "rx_kernels2.cuh"
+
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace rx;
+
+static thread_local std::string g_create_error;
+
+struct rx_ctx {
+  int device = 0, Ns = 0, nVar = 0, nPrim = 0, nGrad = 0, nMarker = 0;
+  cudaStream_t stream = 0;
+  std::string err;
+  Dev d{};
+  Opts o{};
+  ChemC<9> cc9{};
+  std::vector<MarkerDev> markers;
+  std::vector<void*> allocs;
+  double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr;
+  size_t stageBytes = 0;
+  int updBlocks = 0;
+  long long launches = 0;
+};
+
+#define RX_CK(call)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess) {                                                                          \
+      c->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                    \
+      return RX_ERR_CUDA;                                                                             \
+    }                                                                                                 \
+  } while (0)
+
+namespace {
+template <class T>
+T* dalloc(rx_ctx* c, size_t n) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(T));
+  c->allocs.push_back(p);
+  return (T*)p;
+}
+template <class T>
+T* dupload(rx_ctx* c, const std::vector<T>& h) {
+  T* p = dalloc<T>(c, h.size());
+  if (p && !h.empty()) cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+  return p;
+}
+inline unsigned nblk(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+// host-side constants of the mechanism; libm calls are the ones the reference makes (reacting_model_library.cpp:634-696,751-766)
+int fill_chem(rx_ctx* c, const rx_chem* ch) {
+  if (ch->Ns != 9) return RX_ERR_UNSUPPORTED;
+  if (ch->Nr > NRMAX) return RX_ERR_UNSUPPORTED;
+  constexpr int NS = 9;
+  ChemC<NS>& cc = c->cc9;
+  cc.Nr = ch->Nr; cc.nKnots = ch->nKnots;
+  std::vector<double> x(ch->x, ch->x + ch->nKnots);
+  cc.x = dupload(c, x);
+  std::vector<Knot> tab((size_t)5 * ch->nKnots * NS);
+  for (int pr = 0; pr < 5; ++pr)
+    for (int s = 0; s < NS; ++s)
+      for (int k = 0; k < ch->nKnots; ++k) {
+        const size_t src = ((size_t)pr * NS + s) * ch->nKnots + k;
+        tab[((size_t)pr * ch->nKnots + k) * NS + s] = Knot{ch->y[src], ch->y2[src]};
+      }
+  cc.tab = dupload(c, tab);
+  if (!cc.x || !cc.tab) return RX_ERR_CUDA;
+  cc.Mtot = 0.0;
+  for (int s = 0; s < NS; ++s) { cc.M[s] = ch->mMasses[s]; cc.Ri[s] = R_UNGAS / cc.M[s]; cc.Mtot = cc.Mtot + cc.M[s]; }
+  for (int i = 0; i < NS; ++i)
+    for (int j = 0; j < NS; ++j) {
+      cc.wPow[i][j] = std::pow(cc.M[j] / cc.M[i], 0.25);
+      cc.wSq[i][j] = std::sqrt(8.0 * (1.0 + cc.M[i] / cc.M[j]));
+    }
+  for (int i = 0; i < NS; ++i) {
+    const double mi = cc.M[i], dvi = std::cbrt(ch->diffVol[i]);
+    for (int j = i; j < NS; ++j) {
+      cc.Mij[i][j] = cc.Mij[j][i] = std::sqrt((mi * cc.M[j]) / (mi + cc.M[j]));
+      cc.dvs[i][j] = cc.dvs[j][i] = dvi + std::cbrt(ch->diffVol[j]);
+    }
+  }
+  for (int r = 0; r < NRMAX; ++r) {
+    const bool on = r < ch->Nr;
+    cc.As[r] = on ? ch->As[r] : 0; cc.Betas[r] = on ? ch->Betas[r] : 0; cc.Ta[r] = on ? ch->Ta[r] : 0;
+    cc.AsB[r] = on ? ch->AsB[r] : 0; cc.BetasB[r] = on ? ch->BetasB[r] : 0; cc.TaB[r] = on ? ch->TaB[r] : 0;
+    cc.rev[r] = on ? (ch->reversible[r] != 0.0) : 0; cc.avb[r] = on ? (ch->availBack[r] != 0.0) : 0;
+    for (int s = 0; s < NS; ++s) {
+      cc.nuR[r][s] = on ? ch->nuR[r * NS + s] : 0; cc.nuP[r][s] = on ? ch->nuP[r * NS + s] : 0;
+      cc.expR[r][s] = on ? ch->expR[r * NS + s] : 0; cc.expP[r][s] = on ? ch->expP[r * NS + s] : 0;
+    }
+  }
+  return RX_OK;
+}
+
+int ensure_stage(rx_ctx* c, size_t bytes) {
+  if (bytes <= c->stageBytes) return RX_OK;
+  if (c->stage) cudaFree(c->stage);
+  c->stage = nullptr; c->stageBytes = 0;
+  RX_CK(cudaMalloc((void**)&c->stage, bytes));
+  c->stageBytes = bytes;
+  return RX_OK;
+}
+int upload_aos(rx_ctx* c, const double* h, double* soa, int nv) {
+  const long long n = c->d.nPoint;
+  int rc = ensure_stage(c, (size_t)n * nv * sizeof(double));
+  if (rc) return rc;
+  RX_CK(cudaMemcpyAsync(c->stage, h, (size_t)n * nv * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_aos_to_soa<<<nblk(n * nv, 256), 256, 0, c->stream>>>(c->stage, soa, n, nv, c->d.np);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  RX_CK(cudaStreamSynchronize(c->stream));   // the caller may reuse its host buffer on return
+  return RX_OK;
+}
+int download_aos(rx_ctx* c, const double* soa, double* h, int nv) {
+  const long long n = c->d.nPoint;
+  int rc = ensure_stage(c, (size_t)n * nv * sizeof(double));
+  if (rc) return rc;
+  k_soa_to_aos<<<nblk(n * nv, 256), 256, 0, c->stream>>>(soa, c->stage, n, nv, c->d.np);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  RX_CK(cudaMemcpyAsync(h, c->stage, (size_t)n * nv * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  return RX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int rx_supported_species(int Ns) { return Ns == 9; }
+
+const char* rx_last_error(rx_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* op) {
+  if (!out || !m || !ch || !op) { g_create_error = "rx_create: null argument"; return RX_ERR_ARG; }
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    g_create_error = "rx_create: no CUDA device (this library has no CPU path)";
+    return RX_ERR_NO_DEVICE;
+  }
+  if (!rx_supported_species(ch->Ns)) { g_create_error = "rx_create: kernels are instantiated for Ns = 9 only"; return RX_ERR_UNSUPPORTED; }
+  if (ch->Nr > NRMAX) { g_create_error = "rx_create: more reactions than NRMAX"; return RX_ERR_UNSUPPORTED; }
+  if (m->nPoint >= (1LL << 31) || m->nEdge >= (1LL << 31)) { g_create_error = "rx_create: mesh exceeds int32 indices"; return RX_ERR_UNSUPPORTED; }
+  rx_ctx* c = new rx_ctx();
+  c->device = op->device;
+  if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
+  const int Ns = ch->Ns;
+  c->Ns = Ns; c->nVar = Ns + 4; c->nPrim = Ns + 7; c->nGrad = Ns + 4;
+  Opts& o = c->o;
+  o.viscous = op->viscous; o.rans = op->rans; o.leastSquares = op->leastSquares;
+  o.mInfty = op->mInfty; o.cfl = op->cfl; o.maxDt = op->maxDt; o.Tmin = op->Tmin; o.Tmax = op->Tmax;
+  o.clipT = op->clipT; o.ignition = op->ignition; o.ignitionIter = op->ignitionIter; o.ignitionT = op->ignitionT;
+  o.fuelIndex = op->fuelIndex; o.oxidizerIndex = op->oxidizerIndex;
+  o.prandtlLam = op->prandtlLam; o.prandtlTurb = op->prandtlTurb; o.lewisTurb = op->lewisTurb; o.cMu = op->cMu;
+  o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
+  int rc = fill_chem(c, ch);
+  if (rc) { g_create_error = "rx_create: chemistry upload failed"; rx_destroy(c); return rc; }
+
+  Dev& d = c->d;
+  const long long nP = m->nPoint, nE = m->nEdge;
+  d.nPoint = nP; d.nPointDomain = m->nPointDomain; d.nEdge = nE;
+  d.np = (nP + 15) / 16 * 16; d.ne = (nE + 15) / 16 * 16;
+  std::vector<int> ei(nE), ej(nE);
+  std::vector<double> enx(nE), eny(nE), x(nP), y(nP), vol(m->volume, m->volume + nP);
+  for (long long e = 0; e < nE; ++e) {
+    ei[e] = (int)m->edgeNodes[2 * e]; ej[e] = (int)m->edgeNodes[2 * e + 1];
+    enx[e] = m->edgeNormal[2 * e]; eny[e] = m->edgeNormal[2 * e + 1];
+  }
+  for (long long p = 0; p < nP; ++p) { x[p] = m->coord[2 * p]; y[p] = m->coord[2 * p + 1]; }
+  std::vector<int> nbPtr(nP + 1), nbIdx(m->nbPtr[nP]);
+  for (long long p = 0; p <= nP; ++p) nbPtr[p] = (int)m->nbPtr[p];
+  for (size_t k = 0; k < nbIdx.size(); ++k) nbIdx[k] = (int)m->nbPoint[k];
+  // incident-edge CSR in ascending edge order (counting sort keeps the order)
+  std::vector<int> incPtr(nP + 1, 0), incEdge(2 * nE);
+  for (long long e = 0; e < nE; ++e) { incPtr[ei[e] + 1]++; incPtr[ej[e] + 1]++; }
+  for (long long p = 0; p < nP; ++p) incPtr[p + 1] += incPtr[p];
+  {
+    std::vector<int> fill(incPtr.begin(), incPtr.end() - 1);
+    for (long long e = 0; e < nE; ++e) { incEdge[fill[ei[e]]++] = (int)e; incEdge[fill[ej[e]]++] = ~(int)e; }
+  }
+  d.ei = dupload(c, ei); d.ej = dupload(c, ej); d.enx = dupload(c, enx); d.eny = dupload(c, eny);
+  d.x = dupload(c, x); d.y = dupload(c, y); d.vol = dupload(c, vol);
+  d.nbPtr = dupload(c, nbPtr); d.nbIdx = dupload(c, nbIdx); d.incPtr = dupload(c, incPtr); d.incEdge = dupload(c, incEdge);
+  const size_t np = d.np, ne = d.ne;
+  d.U = dalloc<double>(c, np * c->nVar); d.Uold = dalloc<double>(c, np * c->nVar); d.R = dalloc<double>(c, np * c->nVar);
+  d.V = dalloc<double>(c, np * c->nPrim); d.X = dalloc<double>(c, np * Ns);
+  d.Cp = dalloc<double>(c, np); d.gam = dalloc<double>(c, np); d.mu = dalloc<double>(c, np); d.kap = dalloc<double>(c, np);
+  d.T175 = dalloc<double>(c, np); d.Patm = dalloc<double>(c, np);
+  d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
+  d.turb = dalloc<double>(c, np * 6); d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
+  d.fluxC = dalloc<double>(c, ne * c->nVar);
+  d.fluxV = o.viscous ? dalloc<double>(c, ne * c->nVar) : nullptr;
+  d.nonPhys = dalloc<int>(c, np); d.counters = dalloc<unsigned long long>(c, 4);
+  c->updBlocks = (int)nblk(d.nPointDomain, 128);
+  c->partial = dalloc<double>(c, (size_t)c->updBlocks * c->nVar);
+  c->rms = dalloc<double>(c, c->nVar); c->sumsq = dalloc<double>(c, c->nVar);
+  if (!d.counters || !c->sumsq || !d.fluxC || !d.grad || (o.viscous && !d.fluxV)) {
+    g_create_error = "rx_create: device allocation failed"; rx_destroy(c); return RX_ERR_CUDA;
+  }
+  c->nMarker = m->nMarker;
+  for (int k = 0; k < m->nMarker; ++k) {
+    const rx_marker& s = m->markers[k];
+    MarkerDev md{};
+    md.kind = s.kind; md.nVertex = s.nVertex;
+    std::vector<int> node(s.nVertex), nn(s.nVertex);
+    std::vector<double> nx(s.nVertex), ny(s.nVertex);
+    for (int v = 0; v < s.nVertex; ++v) {
+      node[v] = (int)s.node[v]; nn[v] = (int)s.normalNeighbor[v]; nx[v] = s.normal[2 * v]; ny[v] = s.normal[2 * v + 1];
+    }
+    md.node = dupload(c, node); md.nn = dupload(c, nn); md.nx = dupload(c, nx); md.ny = dupload(c, ny);
+    md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall;
+    for (int q = 0; q < 16; ++q) md.Ys[q] = (s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
+    c->markers.push_back(md);
+  }
+  if (cudaDeviceSynchronize() != cudaSuccess) { g_create_error = "rx_create: upload failed"; rx_destroy(c); return RX_ERR_CUDA; }
+  *out = c;
+  return RX_OK;
+}
+
+void rx_destroy(rx_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  for (void* p : c->allocs) cudaFree(p);
+  if (c->stage) cudaFree(c->stage);
+  delete c;
+}
+
+int rx_set_stream(rx_ctx* c, void* s) { c->stream = (cudaStream_t)s; return RX_OK; }
+int rx_synchronize(rx_ctx* c) { RX_CK(cudaStreamSynchronize(c->stream)); return RX_OK; }
+int64_t rx_launch_count(rx_ctx* c) { return c->launches; }
+
+int rx_set_solution(rx_ctx* c, const double* U) { return upload_aos(c, U, c->d.U, c->nVar); }
+int rx_set_turbulence(rx_ctx* c, const double* t) { return upload_aos(c, t, c->d.turb, 6); }
+int rx_set_temperature(rx_ctx* c, const double* T) { return upload_aos(c, T, c->d.V + V_T * c->d.np, 1); }
+int rx_get_solution(rx_ctx* c, double* U) { return download_aos(c, c->d.U, U, c->nVar); }
+int rx_get_residual(rx_ctx* c, double* R) { return download_aos(c, c->d.R, R, c->nVar); }
+int rx_get_primitive(rx_ctx* c, double* V, double* aux, double* grad) {
+  int rc = RX_OK;
+  if (V) rc = download_aos(c, c->d.V, V, c->nPrim);
+  if (!rc && grad) rc = download_aos(c, c->d.grad, grad, c->nGrad * 2);
+  if (!rc && aux) {
+    const long long n = c->d.nPoint;
+    rc = ensure_stage(c, (size_t)n * 6 * sizeof(double));
+    if (rc) return rc;
+    const double* f[6] = {c->d.Cp, c->d.gam, c->d.mu, c->d.kap, c->d.vort, c->d.strain};
+    for (int k = 0; k < 6; ++k) { k_gather_field<<<nblk(n, 256), 256, 0, c->stream>>>(f[k], c->stage, n, 6, k); c->launches++; }
+    RX_CK(cudaGetLastError());
+    RX_CK(cudaMemcpyAsync(aux, c->stage, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    RX_CK(cudaStreamSynchronize(c->stream));
+  }
+  return rc;
+}
+int rx_get_dt(rx_ctx* c, double* dt3) {
+  const long long n = c->d.nPoint;
+  int rc = ensure_stage(c, (size_t)n * 3 * sizeof(double));
+  if (rc) return rc;
+  const double* f[3] = {c->d.dt, c->d.lamInv, c->d.lamVisc};
+  for (int k = 0; k < 3; ++k) { k_gather_field<<<nblk(n, 256), 256, 0, c->stream>>>(f[k], c->stage, n, 3, k); c->launches++; }
+  RX_CK(cudaGetLastError());
+  RX_CK(cudaMemcpyAsync(dt3, c->stage, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  return RX_OK;
+}
+
+int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  RX_CK(cudaMemsetAsync(d.counters, 0, sizeof(unsigned long long), s));
+  k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, (long long)extIter, output);
+  c->launches++;
+  if (c->o.viscous) {
+    if (c->o.leastSquares) {
+      k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+      c->launches++;
+    } else {
+      k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d);
+      c->launches++;
+      for (const MarkerDev& m : c->markers)
+        if (m.nVertex) { k_gradient_gg_boundary<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
+      k_gradient_gg_finish<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+      c->launches++;
+    }
+  }
+  RX_CK(cudaGetLastError());
+  if (nonPhysical) {
+    unsigned long long h = 0;
+    RX_CK(cudaMemcpyAsync(&h, d.counters, sizeof(h), cudaMemcpyDeviceToHost, s));
+    RX_CK(cudaStreamSynchronize(s));
+    *nonPhysical = (int64_t)h;
+  }
+  return RX_OK;
+}
+
+int rx_set_old_solution(rx_ctx* c) {
+  RX_CK(cudaMemcpyAsync(c->d.Uold, c->d.U, (size_t)c->d.np * c->nVar * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  return RX_OK;
+}
+
+int rx_time_step(rx_ctx* c) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  k_timestep_edges<<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->o, d);
+  c->launches++;
+  for (const MarkerDev& m : c->markers)
+    if (m.nVertex) { k_timestep_boundary<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
+  k_timestep_finish<<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->o, d);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+
+int rx_residual_conv(rx_ctx* c) {
+  const Dev& d = c->d;
+  k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, c->stream>>>(c->cc9, c->o, d);
+  k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  c->launches += 2;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_residual_visc(rx_ctx* c) {
+  if (!c->o.viscous) return RX_OK;
+  const Dev& d = c->d;
+  k_edge_flux<9, false, true><<<nblk(d.nEdge, 64), 64, 0, c->stream>>>(c->cc9, c->o, d);
+  k_accumulate<9, 2><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  c->launches += 2;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_residual_source(rx_ctx* c) {
+  const Dev& d = c->d;
+  k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_bc(rx_ctx* c) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  for (const MarkerDev& m : c->markers) {
+    if (!m.nVertex) continue;
+    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+    else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  }
+  for (const MarkerDev& m : c->markers)
+    if (m.nVertex && m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  k_update<9><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial);
+  k_rms_finish<<<1, 32, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
+  c->launches += 2;
+  RX_CK(cudaGetLastError());
+  if (resRms) {
+    RX_CK(cudaMemcpyAsync(resRms, c->rms, c->nVar * sizeof(double), cudaMemcpyDeviceToHost, s));
+    RX_CK(cudaStreamSynchronize(s));
+  }
+  return RX_OK;
+}
+
+int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, double* resRms) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  int rc;
+  for (int rk = 0; rk < nRK; ++rk) {
+    if ((rc = rx_preprocess(c, extIter, 0, nullptr))) return rc;
+    if (rk == 0) {
+      if ((rc = rx_set_old_solution(c))) return rc;
+      if ((rc = rx_time_step(c))) return rc;
+    }
+    if (c->o.viscous) {
+      k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+      k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+      c->launches += 2;
+    } else {
+      k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+      k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+      k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
+      c->launches += 3;
+    }
+    RX_CK(cudaGetLastError());
+    if ((rc = rx_bc(c))) return rc;
+    if ((rc = rx_update_explicit(c, rkAlpha ? rkAlpha[rk] : 1.0, (rk == nRK - 1) ? resRms : nullptr))) return rc;
+  }
+  return rx_preprocess(c, extIter, 1, nullptr);
+}
+
+int rx_source_points_dev(rx_ctx* c, int64_t n, const double* T, const double* rho, const double* Y, const double* omT, const double* vol, double* res) {
+  k_source_points<9><<<nblk(n, 128), 128, 0, c->stream>>>(c->cc9, c->o.rans, c->o.cMu, c->o.pasrLb, (long long)n, T, rho, Y, omT, vol, res);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+
+
+// host-pointer form: builds a throw-away context-free parameter block, stages the inputs (AoS Y[n][Ns] -> SoA on the host side
+// of the copy), runs k_source_points and copies the result back (res[n][Ns]).
+int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int64_t n, const double* T, const double* rho,
+                     const double* Y, const double* omT, const double* vol, double* res, int device) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_error = "rx_source_points: no CUDA device (no CPU path)"; return RX_ERR_NO_DEVICE; }
+  if (!rx_supported_species(ch->Ns) || ch->Nr > NRMAX) { g_create_error = "rx_source_points: unsupported mechanism size"; return RX_ERR_UNSUPPORTED; }
+  rx_ctx tmp; rx_ctx* c = &tmp;
+  c->device = device;
+  RX_CK(cudaSetDevice(device));
+  int rc = fill_chem(c, ch);
+  const int Ns = ch->Ns;
+  double *dT = dalloc<double>(c, n), *dr = dalloc<double>(c, n), *dY = dalloc<double>(c, n * Ns), *dO = dalloc<double>(c, n),
+         *dV = dalloc<double>(c, n), *dR = dalloc<double>(c, n * Ns), *dA = dalloc<double>(c, n * Ns);
+  if (rc == RX_OK && !(dT && dr && dY && dO && dV && dR && dA)) rc = RX_ERR_CUDA;
+  if (rc == RX_OK) {
+    cudaMemcpy(dT, T, n * sizeof(double), cudaMemcpyHostToDevice);
+    cudaMemcpy(dr, rho, n * sizeof(double), cudaMemcpyHostToDevice);
+    cudaMemcpy(dV, vol, n * sizeof(double), cudaMemcpyHostToDevice);
+    if (omT) cudaMemcpy(dO, omT, n * sizeof(double), cudaMemcpyHostToDevice);
+    cudaMemcpy(dA, Y, n * Ns * sizeof(double), cudaMemcpyHostToDevice);
+    k_aos_to_soa<<<nblk(n * Ns, 256), 256>>>(dA, dY, n, Ns, n);
+    k_source_points<9><<<nblk(n, 128), 128>>>(c->cc9, rans, cMu, pasrLb, (long long)n, dT, dr, dY, omT ? dO : nullptr, dV, dR);
+    k_soa_to_aos<<<nblk(n * Ns, 256), 256>>>(dR, dA, n, Ns, n);
+    if (cudaMemcpy(res, dA, n * Ns * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+      g_create_error = "rx_source_points: kernel or copy failed"; rc = RX_ERR_CUDA;
+    }
+  }
+  for (void* p : c->allocs) cudaFree(p);
+  return rc;
+}
+
+int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : c->nGrad * 2; }
+int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {
+  if (n <= 0) return RX_OK;
+  const int nv = rx_halo_width(c, what);
+  k_pack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(what == 0 ? c->d.U : c->d.grad, c->d.np, nv, n, (const long long*)pts, buf);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_halo_unpack(rx_ctx* c, int what, int64_t n, const int64_t* pts, const double* buf) {
+  if (n <= 0) return RX_OK;
+  const int nv = rx_halo_width(c, what);
+  k_unpack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(what == 0 ? c->d.U : c->d.grad, c->d.np, nv, n, (const long long*)pts, buf);
+  c->launches++;
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+
+}  // extern "C"

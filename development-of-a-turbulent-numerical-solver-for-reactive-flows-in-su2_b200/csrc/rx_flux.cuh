@@ -1,0 +1,477 @@
+// rx_flux.cuh — per-edge viscous flux (Stefan–Maxwell diffusion + SST closure) and per-point Arrhenius/PaSR source.
+// See rx_device.cuh for conventions.  Reference citations are relative to /root/reference.
+#pragma once
+#include "rx_device.cuh"
+
+namespace rx {
+
+// ---- Eigen 3.3.7 reductions re-enacted (externals/Eigen/src/Core/Redux.h, SSE2 packets of 2 doubles) ----------
+// sum/product of n coefficients: two packet accumulators over groups of four, combined, horizontal op, scalar tail.
+template <int N, bool MUL>
+RX_HD double eig_redux(const double* a) {
+  constexpr int A2 = (N / 4) * 4, A1 = (N / 2) * 2;
+  auto op = [](double x, double y) { return MUL ? x * y : x + y; };
+  double res;
+  if (A1 > 0) {
+    double p00 = a[0], p01 = a[1];
+    if (A1 > 2) {
+      double p10 = a[2], p11 = a[3];
+#pragma unroll
+      for (int i = 4; i < A2; i += 4) {
+        p00 = op(p00, a[i]); p01 = op(p01, a[i + 1]);
+        p10 = op(p10, a[i + 2]); p11 = op(p11, a[i + 3]);
+      }
+      p00 = op(p00, p10); p01 = op(p01, p11);
+      if (A1 > A2) { p00 = op(p00, a[A2]); p01 = op(p01, a[A2 + 1]); }
+    }
+    res = op(p00, p01);
+#pragma unroll
+    for (int i = A1; i < N; ++i) res = op(res, a[i]);
+  } else {
+    res = a[0];
+  }
+  return res;
+}
+template <int N>
+RX_HD double eig_dot(const double* a, const double* b) {
+  double t[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) t[i] = a[i] * b[i];
+  return eig_redux<N, false>(t);
+}
+// res = A v for a column-major N x N matrix, in the order of Eigen's column-major GEMV kernel
+// (externals/Eigen/src/Core/products/GeneralMatrixVector.h:88-327; SSE2, no FMA): columns four at a time with
+// res + ((a0 v0 + a1 v1) + (a2 v2 + a3 v3)) for rows < (N & ~1), sequential products for the odd last row and for the
+// N % 4 leftover columns.  A(i,j) is supplied by the functor so the matrix may live in registers, shared or local memory.
+template <int N, class MatF>
+RX_HD void eig_gemv(MatF A, const double* v, double* res) {
+  constexpr int AS = N & ~1, CB = (N / 4) * 4;
+#pragma unroll
+  for (int j = 0; j < N; ++j) res[j] = 0.0;
+#pragma unroll
+  for (int i = 0; i < CB; i += 4) {
+#pragma unroll
+    for (int j = 0; j < AS; ++j)
+      res[j] = res[j] + ((A(j, i) * v[i] + A(j, i + 1) * v[i + 1]) + (A(j, i + 2) * v[i + 2] + A(j, i + 3) * v[i + 3]));
+#pragma unroll
+    for (int j = AS; j < N; ++j) {
+      res[j] = A(j, i) * v[i] + res[j];
+      res[j] = A(j, i + 1) * v[i + 1] + res[j];
+      res[j] = A(j, i + 2) * v[i + 2] + res[j];
+      res[j] = A(j, i + 3) * v[i + 3] + res[j];
+    }
+  }
+#pragma unroll
+  for (int k = CB; k < N; ++k) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) res[j] = A(j, k) * v[k] + res[j];
+  }
+}
+
+// Eigen::BiCGSTAB<MatrixXd>, DiagonalPreconditioner, tol 1e-11, zero initial guess, maxIters = 2N
+// (externals/Eigen/src/IterativeLinearSolvers/BiCGSTAB.h:28-108; call site numerics_direct_reactive.cpp:451-470).
+template <int N, class MatF>
+RX_HD int bicgstab(MatF A, const double* rhs, double* x) {
+  const double tol = 1.0e-11;
+  double invd[N], r[N], r0[N], v[N], p[N], y[N], z[N], s[N], t[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) { const double d = A(i, i); invd[i] = d != 0.0 ? 1.0 / d : 1.0; x[i] = 0.0; }
+#pragma unroll
+  for (int i = 0; i < N; ++i) { r[i] = rhs[i] - 0.0; r0[i] = r[i]; }   // r = rhs - A*0
+  double r0_sqnorm = eig_dot<N>(r0, r0);
+  const double rhs_sqnorm = eig_dot<N>(rhs, rhs);
+  if (rhs_sqnorm == 0) return 0;
+  double rho = 1, alpha = 1, w = 1;
+#pragma unroll
+  for (int i = 0; i < N; ++i) { v[i] = 0.0; p[i] = 0.0; }
+  const double tol2 = tol * tol * rhs_sqnorm;
+  const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
+  int it = 0, restarts = 0;
+  while (eig_dot<N>(r, r) > tol2 && it < 2 * N) {
+    const double rho_old = rho;
+    rho = eig_dot<N>(r0, r);
+    if (fabs(rho) < eps2 * r0_sqnorm) {
+      eig_gemv<N>(A, x, t);
+#pragma unroll
+      for (int k = 0; k < N; ++k) { r[k] = rhs[k] - t[k]; r0[k] = r[k]; }
+      rho = r0_sqnorm = eig_dot<N>(r, r);
+      if (restarts++ == 0) it = 0;
+    }
+    const double beta = (rho / rho_old) * (alpha / w);
+#pragma unroll
+    for (int k = 0; k < N; ++k) { p[k] = r[k] + beta * (p[k] - w * v[k]); y[k] = invd[k] * p[k]; }
+    eig_gemv<N>(A, y, v);
+    alpha = rho / eig_dot<N>(r0, v);
+#pragma unroll
+    for (int k = 0; k < N; ++k) { s[k] = r[k] - alpha * v[k]; z[k] = invd[k] * s[k]; }
+    eig_gemv<N>(A, z, t);
+    const double tt = eig_dot<N>(t, t);
+    if (tt > 0.0) w = eig_dot<N>(t, s) / tt; else w = 0.0;
+#pragma unroll
+    for (int k = 0; k < N; ++k) { x[k] = x[k] + (alpha * y[k] + w * z[k]); r[k] = s[k] - w * t[k]; }
+    ++it;
+  }
+  return it;
+}
+
+// Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) for `nrhs` right-hand sides (externals/Eigen/src/QR/ColPivHouseholderQR.h,
+// Householder/Householder.h).  Same pivot rule, rank threshold and norm down-dating; natural summation order.
+// A is N x N column-major in caller-provided scratch (destroyed); b/x are [nrhs][N].
+template <int N, int NRHS>
+RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
+  double hC[N], nU[N], nD[N];
+  int trans[N];
+  auto col = [&](int j) { return A + j * N; };
+  for (int k = 0; k < N; ++k) {
+    double s = 0.0;
+    for (int i = 0; i < N; ++i) s += col(k)[i] * col(k)[i];
+    nD[k] = nU[k] = sqrt(s);
+  }
+  const double eps = 2.220446049250313e-16;
+  double mx = nU[0];
+  for (int k = 1; k < N; ++k) mx = fmax(mx, nU[k]);
+  const double threshold_helper = (mx * eps) * (mx * eps) / (double)N;
+  const double downdate = sqrt(eps);
+  int nonzero = N;
+  for (int k = 0; k < N; ++k) {
+    int big = k;
+    for (int j = k + 1; j < N; ++j) if (nU[j] > nU[big]) big = j;
+    const double bigsq = nU[big] * nU[big];
+    if (nonzero == N && bigsq < threshold_helper * (double)(N - k)) nonzero = k;
+    trans[k] = big;
+    if (k != big) {
+      for (int i = 0; i < N; ++i) { const double tmp = col(k)[i]; col(k)[i] = col(big)[i]; col(big)[i] = tmp; }
+      double tmp = nU[k]; nU[k] = nU[big]; nU[big] = tmp;
+      tmp = nD[k]; nD[k] = nD[big]; nD[big] = tmp;
+    }
+    double* v = col(k) + k;
+    const int m = N - k;
+    double tailSq = 0.0;
+    for (int i = 1; i < m; ++i) tailSq += v[i] * v[i];
+    const double c0 = v[0];
+    double beta, tau;
+    if (tailSq <= 2.2250738585072014e-308) {
+      tau = 0.0; beta = c0;
+      for (int i = 1; i < m; ++i) v[i] = 0.0;
+    } else {
+      beta = sqrt(c0 * c0 + tailSq);
+      if (c0 >= 0.0) beta = -beta;
+      for (int i = 1; i < m; ++i) v[i] = v[i] / (c0 - beta);
+      tau = (beta - c0) / beta;
+    }
+    hC[k] = tau;
+    v[0] = beta;
+    if (m == 1) {
+      for (int j = k + 1; j < N; ++j) col(j)[k] *= (1.0 - tau);
+    } else if (tau != 0.0) {
+      for (int j = k + 1; j < N; ++j) {
+        double* w = col(j) + k;
+        double t = 0.0;
+        for (int i = 1; i < m; ++i) t += v[i] * w[i];
+        t += w[0];
+        w[0] -= tau * t;
+        for (int i = 1; i < m; ++i) w[i] -= tau * v[i] * t;
+      }
+    }
+    for (int j = k + 1; j < N; ++j) {
+      if (nU[j] != 0.0) {
+        double temp = fabs(col(j)[k]) / nU[j];
+        temp = (1.0 + temp) * (1.0 - temp);
+        temp = temp < 0.0 ? 0.0 : temp;
+        const double q = nU[j] / nD[j];
+        const double temp2 = temp * (q * q);
+        if (temp2 <= downdate) {
+          double s = 0.0;
+          for (int i = k + 1; i < N; ++i) s += col(j)[i] * col(j)[i];
+          nD[j] = sqrt(s); nU[j] = nD[j];
+        } else nU[j] *= sqrt(temp);
+      }
+    }
+  }
+  int perm[N];
+  for (int i = 0; i < N; ++i) perm[i] = i;
+  for (int k = 0; k < N; ++k) { const int t = perm[k]; perm[k] = perm[trans[k]]; perm[trans[k]] = t; }
+  for (int q = 0; q < NRHS; ++q) {
+    double c[N];
+    if (nonzero == 0) { for (int i = 0; i < N; ++i) xout[q][i] = 0.0; continue; }
+    for (int i = 0; i < N; ++i) c[i] = b[q][i];
+    for (int k = 0; k < nonzero; ++k) {
+      const int m = N - k;
+      const double* v = col(k) + k;
+      const double tau = hC[k];
+      double* w = c + k;
+      if (m == 1) w[0] *= (1.0 - tau);
+      else if (tau != 0.0) {
+        double t = 0.0;
+        for (int i = 1; i < m; ++i) t += v[i] * w[i];
+        t += w[0];
+        w[0] -= tau * t;
+        for (int i = 1; i < m; ++i) w[i] -= tau * v[i] * t;
+      }
+    }
+    for (int i = nonzero - 1; i >= 0; --i) {
+      c[i] = c[i] / col(i)[i];
+      for (int r = 0; r < i; ++r) c[r] -= c[i] * col(i)[r];
+    }
+    for (int i = 0; i < nonzero; ++i) xout[q][perm[i]] = c[i];
+    for (int i = nonzero; i < N; ++i) xout[q][perm[i]] = 0.0;
+  }
+}
+
+// ---- viscous flux ------------------------------------------------------------------------------------------
+// End state of an edge (or of a boundary vertex and its ghost): primitives, gradient, transport and SST inputs.
+template <int NS>
+struct ViscEnd {
+  double V[7 + NS];
+  double g[(4 + NS) * 2];   // rows [T,u,v,P,X_s] x 2 — filled only where needed
+  double X[NS];             // mole fractions of the end state (GetMolarFromMass of V[Y])
+  double mu, kap, T175, Patm;  // T175 = 1e-3*pow(T,1.75) and P/101325 of the point that owns the D_ij (GetDij_SM :751-766)
+  double muT, ke, gk[2], x[2];
+};
+
+// CAvgGradReactive_Flow::ComputeResidual (numerics_direct_reactive.cpp:1425-1573) / _Boundary::ComputeResidual (:478-553),
+// SetLaminarTensorFlux (:1099-1190), Solve_SM (:451-470) with GetGamma (reacting_model_library.cpp:771-798),
+// SST_Reactive_ResidualClosure (:656-852), Get_Molar2MassGrad_Operator (:861-880).
+// `scratch` must hold NS*NS doubles (the S–M matrix, then the molar->mass operator); it may be local or shared memory.
+template <int NS, bool EDGE>
+RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I, const ViscEnd<NS>& J, double nx, double ny,
+                        double sigma_k, double* scratch, double* res) {
+  constexpr int NA = 3 + NS;
+  const double mu = 2.0 / (1.0 / I.mu + 1.0 / J.mu);
+  const double ktr = 2.0 / (1.0 / I.kap + 1.0 / J.kap);
+  double Vm[7 + NS], G[NA][2];
+#pragma unroll
+  for (int v = 0; v < 7 + NS; ++v) Vm[v] = 0.5 * (I.V[v] + J.V[v]);
+#pragma unroll
+  for (int d = 0; d < 2; ++d) {
+    G[0][d] = 0.5 * (I.g[G_T * 2 + d] + J.g[G_T * 2 + d]);
+    G[1][d] = 0.5 * (I.g[(G_VX)*2 + d] + J.g[(G_VX)*2 + d]);
+    G[2][d] = 0.5 * (I.g[(G_VX + 1) * 2 + d] + J.g[(G_VX + 1) * 2 + d]);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) G[3 + s][d] = 0.5 * (I.g[(G_X + s) * 2 + d] + J.g[(G_X + s) * 2 + d]);
+  }
+  if (EDGE) {
+    const double e0 = J.x[0] - I.x[0], e1 = J.x[1] - I.x[1];
+    const double dist2 = 0.0 + e0 * e0 + e1 * e1;
+#pragma unroll
+    for (int r = 0; r < NA; ++r) {
+      const double proj = (0.0 + G[r][0] * e0) + G[r][1] * e1;
+      double diff;
+      if (r == 0) diff = J.V[V_T] - I.V[V_T];
+      else if (r < 3) diff = J.V[V_VX + r - 1] - I.V[V_VX + r - 1];
+      else diff = J.X[r - 3] - I.X[r - 3];
+      G[r][0] -= ((proj - diff) * e0) / dist2;
+      G[r][1] -= ((proj - diff) * e1) / dist2;
+    }
+  }
+  const double nrm[2] = {nx, ny};
+  double Proj[4 + NS], FT[3][2], tau[2][2], hs[NS], Ys[NS], Xs[NS], gxn[NS], Jd[NS];   // FT rows: mom-x, mom-y, energy
+  const double rho = Vm[V_RHO], T = Vm[V_T];
+  const SplPos sp = spl_pos(cc, T);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { hs[s] = spl_eval(cc, P_H, s, sp) / cc.M[s]; Ys[s] = Vm[V_Y + s]; }
+  molar_from_mass(cc, Ys, Xs);
+  double div_vel = 0.0;
+  div_vel += G[1][0]; div_vel += G[2][1];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    tau[i][0] = 0.0; tau[i][1] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) tau[i][j] += mu * (G[1 + j][i] + G[1 + i][j]);
+    tau[i][i] -= TWO3 * (mu * div_vel);
+  }
+#pragma unroll
+  for (int v = 0; v < 4 + NS; ++v) Proj[v] = 0.0;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) gxn[s] = 0.0;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    FT[2][i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) { FT[j][i] = tau[i][j]; FT[2][i] += tau[i][j] * Vm[V_VX + j]; }
+    FT[2][i] += ktr * G[0][i];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) gxn[s] += G[3 + s][i] * nrm[i];
+  }
+  // ---- Stefan–Maxwell system: mean D_ij (harmonic, element-wise :1447), Gamma (:771-798), Gamma_tilde (:463-465)
+  {
+    double* Gam = scratch;   // column-major like Eigen::MatrixXd
+    double sigma = 0.0, massTot = 0.0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) massTot += Ys[s] / cc.M[s];
+    massTot = 1.0 / massTot;
+    double maxD = 0.0;
+    // D_i(s,t) = 1e-3*T_i^1.75/(Patm_i*Mij*(dv)*(dv)) / 1e4  (GetDij_SM; variable_direct_reactive.cpp:1212)
+    for (int i = 0; i < NS; ++i) {
+      double tmp = 0.0;   // diagonal accumulation sum_{k != i} X_k / D_ik, in k order
+      for (int j = 0; j < NS; ++j) {
+        const double di = (I.T175 / (I.Patm * cc.Mij[i][j] * cc.dvs[i][j] * cc.dvs[i][j])) / (1.0 * 1.0 * 1.0e4);
+        const double dj = (J.T175 / (J.Patm * cc.Mij[i][j] * cc.dvs[i][j] * cc.dvs[i][j])) / (1.0 * 1.0 * 1.0e4);
+        const double dm = 2.0 / (1.0 / di + 1.0 / dj);
+        maxD = fmax(maxD, dm);
+        if (j != i) {
+          Gam[j * NS + i] = -sigma * massTot * Xs[i] / (rho * cc.M[j] * dm);
+          tmp += Xs[j] / dm;
+        }
+      }
+      Gam[i * NS + i] = sigma * massTot * tmp / (rho * cc.M[i]);
+    }
+    const double alpha = 1.0 / (rho * maxD);
+    for (int i = 0; i < NS; ++i)
+      for (int j = 0; j < NS; ++j) Gam[j * NS + i] = Gam[j * NS + i] + alpha * Ys[i];
+    double rhs[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) rhs[s] = -gxn[s];
+    bicgstab<NS>([&](int r, int c) { return Gam[c * NS + r]; }, rhs, Jd);
+  }
+  Proj[U_RHO] = -eig_redux<NS, false>(Jd);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { Proj[U_E] += -hs[s] * Jd[s]; Proj[U_S + s] = -Jd[s]; }
+  // ---- SST closure
+  if (o.rans) {
+    const double muT = 2.0 / (1.0 / I.muT + 1.0 / J.muT);
+    const double ke = 0.5 * (I.ke + J.ke);
+    const double gk[2] = {0.5 * (I.gk[0] + J.gk[0]), 0.5 * (I.gk[1] + J.gk[1])};
+    const double PrT = o.prandtlTurb, LeT = o.lewisTurb;
+    double Cps[NS], tt[2][2], rhsq[2][NS], MG[2][NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) Cps[s] = spl_eval(cc, P_CP, s, sp) / cc.M[s];
+    double dv = 0.0;
+    dv += G[1][0]; dv += G[2][1];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      tt[i][0] = 0.0; tt[i][1] = 0.0;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) tt[i][j] += muT * (G[1 + j][i] + G[1 + i][j]);
+      tt[i][i] -= TWO3 * (muT * dv + ke * rho);
+    }
+    double sig = 0.0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sig = sig + Xs[s];
+    double* Mt = scratch;
+    for (int i = 0; i < NS; ++i)
+      for (int j = 0; j < NS; ++j)
+        Mt[j * NS + i] = (i == j) ? cc.Mtot / cc.M[i] * (Ys[i] - Xs[i] + sig) * 1.0 + cc.Mtot * (Ys[i] / cc.M[i] - Xs[i] / cc.M[j]) * 0.0
+                                  : cc.Mtot / cc.M[i] * (Ys[i] - Xs[i] + sig) * 0.0 + cc.Mtot * (Ys[i] / cc.M[i] - Xs[i] / cc.M[j]) * 1.0;
+#pragma unroll
+    for (int d = 0; d < 2; ++d)
+#pragma unroll
+      for (int s = 0; s < NS; ++s) rhsq[d][s] = G[3 + s][d];
+    colpiv_qr_solve<NS, 2>(Mt, rhsq, MG);
+#pragma unroll
+    for (int d = 0; d < 2; ++d)
+#pragma unroll
+      for (int s = 0; s < NS; ++s) if (fabs(G[3 + s][d]) < 1e-8) MG[d][s] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) { FT[j][i] += tt[i][j]; FT[2][i] += tt[i][j] * Vm[V_VX + j]; }
+#pragma unroll
+      for (int s = 0; s < NS; ++s) Proj[U_S + s] += muT / (PrT * LeT) * MG[i][s] * nrm[i];
+#pragma unroll
+      for (int s = 0; s < NS; ++s) FT[2][i] += muT / (PrT * LeT) * hs[s] * Ys[s] * MG[i][s];
+#pragma unroll
+      for (int s = 0; s < NS; ++s) FT[2][i] += muT / PrT * Cps[s] * Ys[s] * G[0][i];
+      FT[2][i] += (mu + muT / sigma_k) * gk[i];
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 2; ++d) {
+    Proj[U_MX] += FT[0][d] * nrm[d];
+    Proj[U_MX + 1] += FT[1][d] * nrm[d];
+    Proj[U_E] += FT[2][d] * nrm[d];
+  }
+#pragma unroll
+  for (int v = 0; v < 4 + NS; ++v) res[v] = Proj[v];
+}
+
+// ---- Arrhenius + PaSR source (reacting_model_library.cpp:99-227, 803-920; numerics_direct_reactive.cpp:1728-1825) ----
+// pow(c, e) for the exponents that occur in mechanisms is short-circuited where the result is exact in both libms.
+RX_HD double pow_exp(double c, double e) {
+  if (e == 0.0) return 1.0;
+  if (e == 1.0) return c;
+  if (e == 2.0) return c * c;
+  if (e == 0.5) return sqrt(c);   // glibc pow(x,0.5) is correctly rounded == sqrt(x) for finite positive x
+  return pow(c, e);
+}
+template <int NS>
+RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pasrLb, double T, double rho, const double* Yin,
+                           double omegaTurb, double* omega) {
+  const int Nr = cc.Nr;
+  double Ys[NS], Cs[NS], tmp[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) omega[s] = 0.0;
+  if (Nr == 0) return;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { Ys[s] = clipy<NS>(Yin[s]); Cs[s] = 1.0e3 * rho * Ys[s] / cc.M[s]; }   // SetConcentration :701-705
+  double wir[NRMAX][NS], kp[NRMAX];
+  for (int r = 0; r < Nr; ++r) {
+    // ComputeRateConstants :835-867 (K_eq from Gibbs only decides kb when no backward data are available)
+    const double kf = cc.As[r] * pow_exp(T, cc.Betas[r]) * exp(-cc.Ta[r] / T);
+    double kb;
+    if (!cc.avb[r]) {
+      if (!cc.rev[r]) kb = 0.0;
+      else {
+        const SplPos sp = spl_pos(cc, T);
+        double dG = 0.0, dnu = 0.0;
+        for (int s = 0; s < NS; ++s) {
+          const double dc = cc.nuP[r][s] - cc.nuR[r][s];
+          if (dc != 0.0) { dG += dc * (spl_eval(cc, P_H, s, sp) - T * spl_eval(cc, P_S, s, sp)); dnu += dc; }
+        }
+        const double lnKp = -dG / (R_UNGAS * T);
+        const double lnKc = lnKp - dnu * log(R_UNGAS_ATM * T);
+        kb = (exp(lnKp) > 1.0e10) ? 0.0 : kf / exp(lnKc);
+      }
+    } else kb = cc.AsB[r] * pow_exp(T, cc.BetasB[r]) * exp(-cc.TaB[r] / T);
+    // SetReactionRates :872-920
+    double fr = 0.0, br = 0.0;
+    bool zero = false;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) zero = zero || (cc.expR[r][s] < 0.0 && Ys[s] < 1.0e-15);
+    if (!zero) {
+#pragma unroll
+      for (int s = 0; s < NS; ++s) tmp[s] = pow_exp(Cs[s], cc.expR[r][s]);
+      fr = eig_redux<NS, true>(tmp);
+      fr *= kf;
+    }
+    zero = false;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) zero = zero || (cc.expP[r][s] < 0.0 && Ys[s] < 1.0e-15);
+    if (!zero) {
+#pragma unroll
+      for (int s = 0; s < NS; ++s) tmp[s] = pow_exp(Cs[s], cc.expP[r][s]);
+      br = eig_redux<NS, true>(tmp);
+      br *= kb;
+    }
+#pragma unroll
+    for (int s = 0; s < NS; ++s) wir[r][s] = 1.0e-3 * cc.M[s] * (cc.nuP[r][s] - cc.nuR[r][s]) * (fr - br);   // SetSourceTerm :99-114
+    kp[r] = 1.0;
+    if (pasr) {   // Set_DfrDrhos :122-136, GetTimeCombustion_r :208-227, AssemblePaSRConstant :161-190
+      double hi = 0.0;
+      bool first = true;
+#pragma unroll
+      for (int s = 0; s < NS; ++s)
+        if (cc.nuP[r][s] != 0.0 || cc.nuR[r][s] != 0.0) {
+          const double d = (Ys[s] > 1.0e-10) ? (fr * cc.expR[r][s] - br * cc.expP[r][s]) / (rho * Ys[s]) : 0.0;
+          const double v = fabs(d * cc.M[s]);
+          if (first || v > hi) { hi = v; first = false; }
+        }
+      const double tauMix = 1 / (cMu * omegaTurb);
+      const double tauC = 1 / hi;
+      if (isinf(tauC)) kp[r] = 1.0;
+      else if ((tauC / (tauC + tauMix)) < pasrLb) kp[r] = pasrLb;
+      else kp[r] = tauC / (tauC + tauMix);
+    }
+  }
+  if (pasr) {   // GetMassProductionTerm(i) :143-154
+#pragma unroll
+    for (int s = 0; s < NS; ++s) { double w = 0.0; for (int r = 0; r < Nr; ++r) w += kp[r] * wir[r][s]; omega[s] = w; }
+  } else {      // GetMassProductionTerm() :196-202 (rowwise sum)
+#pragma unroll
+    for (int s = 0; s < NS; ++s) { double w = wir[0][s]; for (int r = 1; r < Nr; ++r) w = w + wir[r][s]; omega[s] = w; }
+  }
+}
+
+}  // namespace rx

@@ -1,0 +1,308 @@
+// rx_kernels.cuh — CUDA kernels of the reactive residual path (sm_100a, FP64, no tensor cores: nothing here is a dense
+// contraction).  State is structure-of-arrays: field f of point p lives at base[f*np + p] (np = padded point count), so
+// a warp's loads of one field are one or two contiguous 128-byte lines.  Scatter is owner-computes: every point sums the
+// fluxes of its incident edges in ascending edge order — the summation order of the reference's edge loops
+// (LinSysRes.AddBlock/SubtractBlock, solver_direct_reactive.cpp:2760-2761,5374-5375) — so accumulation is deterministic
+// and needs no atomics.
+#pragma once
+#include "rx_flux.cuh"
+
+namespace rx {
+
+struct Dev {   // device pointers + sizes, passed by value to kernels
+  long long nPoint, nPointDomain, nEdge, np, ne;   // np / ne: padded strides
+  // mesh
+  const int *ei, *ej; const double *enx, *eny;
+  const double *x, *y, *vol;
+  const int *nbPtr, *nbIdx;        // neighbour CSR (WLS gradient), reference order
+  const int *incPtr, *incEdge;     // incident-edge CSR in ascending edge order; entry = e (point is node 0) or ~e (node 1)
+  // state
+  double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *T175, *Patm, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R;
+  double *fluxC, *fluxV;
+  int* nonPhys; unsigned long long* counters;   // counters[0] = non-physical points of the last preprocess
+};
+
+struct MarkerDev { int kind, nVertex; const int *node, *nn; const double *nx, *ny; double T, Vmag, dir0, dir1, P, Twall; double Ys[16]; };
+
+__global__ void k_aos_to_soa(const double* __restrict__ aos, double* __restrict__ soa, long long n, int nv, long long stride) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n * nv) return;
+  long long p = t / nv; int v = (int)(t - p * nv);
+  soa[v * stride + p] = aos[t];
+}
+__global__ void k_soa_to_aos(const double* __restrict__ soa, double* __restrict__ aos, long long n, int nv, long long stride) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n * nv) return;
+  long long p = t / nv; int v = (int)(t - p * nv);
+  aos[t] = soa[v * stride + p];
+}
+__global__ void k_gather_field(const double* __restrict__ soa, double* __restrict__ aos, long long n, int nvOut, int col) {
+  long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p < n) aos[p * nvOut + col] = soa[p];
+}
+__global__ void k_scatter_field(const double* __restrict__ aos, double* __restrict__ soa, long long n, int nvIn, int col) {
+  long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p < n) soa[p] = aos[p * nvIn + col];
+}
+
+// ---- SetPrimitive_Variables (solver_direct_reactive.cpp:985-1038) + CReactiveNSVariable::SetPrimVar (variable_direct_reactive.cpp:1188-1228)
+template <int NS>
+__global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d,
+                                                   long long extIter, int output) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  constexpr int NV = 4 + NS, NP = 7 + NS;
+  double U[NV], V[NP];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) U[v] = d.U[v * d.np + p];
+  V[V_T] = d.V[V_T * d.np + p];
+  const double ke = o.rans ? d.turb[1 * d.np + p] : 0.0;
+  bool np = cons2prim(cc, o, extIter, U, V, ke);
+  if (np && extIter > 0) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) U[v] = d.Uold[v * d.np + p];
+    cons2prim(cc, o, extIter, U, V, ke);
+  }
+  const double* Y = V + V_Y;
+  const double Rg = rgas(cc, Y);
+  const double a = V[V_A], T = V[V_T];
+  const double Cp = (a * a * Rg) / (a * a - Rg * T);   // ComputeCP_FromSoundSpeed, reacting_model_library.hpp:408-411
+  d.Cp[p] = Cp;
+  d.gam[p] = (Cp / (Cp - Rg) - 1.0) + 1.0;             // dPdU[rhoE] = Gamma - 1 (:843-849); readers add the 1 back
+  double X[NS];
+  molar_from_mass(cc, Y, X);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) d.X[s * d.np + p] = X[s];
+  if (o.viscous) {
+    double mu, ka;
+    transport(cc, T, Y, mu, ka);
+    d.mu[p] = mu; d.kap[p] = ka;
+    d.T175[p] = 1.0e-3 * pow(T, 1.75);                 // numerator of GetDij_SM (:751-766)
+    d.Patm[p] = V[V_P] * 1.0 / 101325.0;
+  }
+  if (o.ignition && extIter < o.ignitionIter) {        // ignition hack: overwrite T only (:1013-1024)
+    if (Y[o.fuelIndex] > 0.4 && Y[o.oxidizerIndex] > 0.2 && V[V_T] < o.ignitionT) V[V_T] = o.ignitionT;
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) d.U[v * d.np + p] = U[v];
+#pragma unroll
+  for (int v = 0; v < NP; ++v) d.V[v * d.np + p] = V[v];
+  d.nonPhys[p] = np ? 1 : 0;
+  if (np) atomicAdd(d.counters, 1ULL);
+  if (!output) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) d.R[v * d.np + p] = 0.0;
+  }
+}
+
+template <int NS>
+__device__ __forceinline__ void load_gradvars(const Dev& d, long long p, double* pv) {
+  pv[G_T] = d.V[V_T * d.np + p]; pv[G_VX] = d.V[V_VX * d.np + p]; pv[G_VX + 1] = d.V[(V_VX + 1) * d.np + p]; pv[G_P] = d.V[V_P * d.np + p];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) pv[G_X + s] = d.X[s * d.np + p];
+}
+template <int NS>
+__device__ __forceinline__ void store_vort_strain(const Dev& d, long long p, const double* g /* [nG][2] */) {
+  // CReactiveNSVariable::SetVorticity / SetStrainMag, variable_direct_reactive.cpp:1038-1097
+  d.vort[p] = g[2 * 2 + 0] - g[1 * 2 + 1];
+  double div = 0.0;
+  div += g[1 * 2 + 0]; div += g[2 * 2 + 1];
+  double sm = 0.0;
+  double t = g[1 * 2 + 0] - 1.0 / 3.0 * div; sm += t * t;
+  t = g[2 * 2 + 1] - 1.0 / 3.0 * div; sm += t * t;
+  t = 0.5 * (g[1 * 2 + 1] + g[2 * 2 + 0]); sm += 2.0 * (t * t);
+  d.strain[p] = sqrt(2.0 * sm);
+}
+
+// ---- SetPrimitive_Gradient_LS (solver_direct_reactive.cpp:4887-5050), one thread per owned point
+template <int NS>
+__global__ void __launch_bounds__(128) k_gradient_ls(const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  constexpr int NG = 4 + NS;
+  double g[NG * 2];
+  if (p < d.nPointDomain) {
+    double pi[NG], pj[NG], C[NG * 2];
+    load_gradvars<NS>(d, p, pi);
+#pragma unroll
+    for (int k = 0; k < NG * 2; ++k) C[k] = 0.0;
+    const double xi = d.x[p], yi = d.y[p];
+    double r11 = 0.0, r12 = 0.0, r22 = 0.0;
+    for (int k = d.nbPtr[p]; k < d.nbPtr[p + 1]; ++k) {
+      const int q = d.nbIdx[k];
+      load_gradvars<NS>(d, q, pj);
+      const double d0 = d.x[q] - xi, d1 = d.y[q] - yi;
+      const double weight = 0.0 + d0 * d0 + d1 * d1;
+      if (weight > EPS) {
+        r11 += d0 * d0 / weight;
+        r12 += d0 * d1 / weight;
+        r22 += d1 * d1 / weight;
+#pragma unroll
+        for (int v = 0; v < NG; ++v) {
+          C[v * 2 + 0] += d0 * (pj[v] - pi[v]) / weight;
+          C[v * 2 + 1] += d1 * (pj[v] - pi[v]) / weight;
+        }
+      }
+    }
+    if (r11 > EPS) r11 = sqrt(r11); else r11 = 0.0;
+    if (fabs(r11) > EPS) r12 = r12 / r11; else r12 = 0.0;
+    if (r22 - r12 * r12 > EPS) r22 = sqrt(r22 - r12 * r12); else r22 = 0.0;
+    double detR2 = (r11 * r22) * (r11 * r22);
+    bool singular = false;
+    if (fabs(detR2) < EPS) { detR2 = 1.0; singular = true; }
+    double S00 = 0.0, S01 = 0.0, S11 = 0.0;
+    if (!singular) {
+      S00 = (r12 * r12 + r22 * r22) / detR2;
+      S01 = -r11 * r12 / detR2;
+      S11 = r11 * r11 / detR2;
+    }
+#pragma unroll
+    for (int v = 0; v < NG; ++v) {
+      g[v * 2 + 0] = (0.0 + C[v * 2 + 0] * S00) + C[v * 2 + 1] * S01;
+      g[v * 2 + 1] = (0.0 + C[v * 2 + 0] * S01) + C[v * 2 + 1] * S11;
+    }
+#pragma unroll
+    for (int k = 0; k < NG * 2; ++k) d.grad[k * d.np + p] = g[k];
+  } else {
+#pragma unroll
+    for (int k = 0; k < NG * 2; ++k) g[k] = d.grad[k * d.np + p];   // halo gradients arrive by exchange
+  }
+  store_vort_strain<NS>(d, p, g);
+}
+
+// ---- SetPrimitive_Gradient_GG (solver_direct_reactive.cpp:4784-4880): interior-edge part, owner-computes.
+// The species rows use the mole fractions of the edge's FIRST node for both ends (:4811-4814) — reproduced.
+template <int NS>
+__global__ void __launch_bounds__(128) k_gradient_gg_edges(const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  constexpr int NG = 4 + NS;
+  double g[NG * 2], pi[NG], pj[NG];
+#pragma unroll
+  for (int k = 0; k < NG * 2; ++k) g[k] = 0.0;
+  for (int k = d.incPtr[p]; k < d.incPtr[p + 1]; ++k) {
+    const int code = d.incEdge[k];
+    const bool first = code >= 0;
+    const int e = first ? code : ~code;
+    const int i = d.ei[e], j = d.ej[e];
+    load_gradvars<NS>(d, i, pi);
+    load_gradvars<NS>(d, j, pj);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) pj[G_X + s] = pi[G_X + s];
+    const double nx = d.enx[e], ny = d.eny[e];
+#pragma unroll
+    for (int v = 0; v < NG; ++v) {
+      const double avg = 0.5 * (pi[v] + pj[v]);
+      if (first) { g[v * 2 + 0] += avg * nx; g[v * 2 + 1] += avg * ny; }
+      else { g[v * 2 + 0] -= avg * nx; g[v * 2 + 1] -= avg * ny; }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NG * 2; ++k) d.grad[k * d.np + p] = g[k];
+}
+template <int NS>
+__global__ void k_gradient_gg_boundary(const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int p = m.node[k];
+  if (p >= d.nPointDomain) return;
+  constexpr int NG = 4 + NS;
+  double pi[NG];
+  load_gradvars<NS>(d, p, pi);
+#pragma unroll
+  for (int v = 0; v < NG; ++v) {
+    d.grad[(v * 2 + 0) * d.np + p] -= pi[v] * m.nx[k];
+    d.grad[(v * 2 + 1) * d.np + p] -= pi[v] * m.ny[k];
+  }
+}
+template <int NS>
+__global__ void __launch_bounds__(128) k_gradient_gg_finish(const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  constexpr int NG = 4 + NS;
+  double g[NG * 2];
+  const double vol = d.vol[p];
+#pragma unroll
+  for (int k = 0; k < NG * 2; ++k) {
+    g[k] = d.grad[k * d.np + p];
+    if (p < d.nPointDomain) { g[k] = g[k] / vol; d.grad[k * d.np + p] = g[k]; }
+  }
+  store_vort_strain<NS>(d, p, g);
+}
+
+// ---- SetTime_Step (solver_direct_reactive.cpp:5057-5298)
+__device__ __forceinline__ void edge_lambda(const Dev& d, const Opts& o, int i, int j, double nx, double ny, double& lamI, double& lamV) {
+  const double Area = sqrt(nx * nx + ny * ny);
+  const double pvi = 0.0 + d.V[V_VX * d.np + i] * nx + d.V[(V_VX + 1) * d.np + i] * ny;
+  const double pvj = 0.0 + d.V[V_VX * d.np + j] * nx + d.V[(V_VX + 1) * d.np + j] * ny;
+  const double Mean_ProjVel = 0.5 * (pvi + pvj);
+  const double Mean_SoundSpeed = 0.5 * (d.V[V_A * d.np + i] + d.V[V_A * d.np + j]);
+  const double Mean_Density = 0.5 * (d.V[V_RHO * d.np + i] + d.V[V_RHO * d.np + j]);
+  lamI = (fabs(Mean_ProjVel) + Mean_SoundSpeed) * Area;
+  lamV = 0.0;
+  if (!o.viscous) return;
+  const double Mean_ThermalCond = 0.5 * (d.kap[i] + d.kap[j]);
+  const double Mean_LaminarVisc = 0.5 * (d.mu[i] + d.mu[j]);
+  const double Mean_CV = 0.5 * (d.Cp[i] / d.gam[i] + d.Cp[j] / d.gam[j]);
+  double L1, L2;
+  if (o.rans) {
+    const double Mean_EddyVisc = 0.5 * (d.turb[i] + d.turb[j]);
+    const double Gamma = d.gam[i];   // gamma of the edge's first node only (:5141)
+    L1 = 4.0 / 3.0 * (Mean_LaminarVisc + Mean_EddyVisc);
+    L2 = (1.0 + (o.prandtlLam / o.prandtlTurb) * (Mean_EddyVisc / Mean_LaminarVisc)) * (Gamma * Mean_LaminarVisc / o.prandtlLam);
+  } else {
+    L1 = 4.0 / 3.0 * Mean_LaminarVisc;
+    L2 = Mean_ThermalCond / Mean_CV;
+  }
+  lamV = (L1 + L2) * Area * Area / Mean_Density;
+}
+__global__ void __launch_bounds__(128) k_timestep_edges(const __grid_constant__ Opts o, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  double li = 0.0, lv = 0.0;
+  for (int k = d.incPtr[p]; k < d.incPtr[p + 1]; ++k) {
+    const int code = d.incEdge[k];
+    const int e = code >= 0 ? code : ~code;
+    double a, b;
+    edge_lambda(d, o, d.ei[e], d.ej[e], d.enx[e], d.eny[e], a, b);
+    li += a; lv += b;
+  }
+  d.lamInv[p] = li; d.lamVisc[p] = lv;
+}
+__global__ void k_timestep_boundary(const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = m.nx[k], ny = m.ny[k];
+  const double Area = sqrt(nx * nx + ny * ny);
+  const double pv = 0.0 + d.V[V_VX * d.np + i] * nx + d.V[(V_VX + 1) * d.np + i] * ny;
+  d.lamInv[i] += (fabs(pv) + d.V[V_A * d.np + i]) * Area;
+  if (!o.viscous) return;
+  const double mu = d.mu[i];
+  double L1, L2;
+  if (o.rans) {
+    const double ev = d.turb[i];
+    const double Gamma = d.gam[i];
+    L1 = (4.0 / 3.0) * (mu + ev);
+    L2 = (1.0 + (o.prandtlLam / o.prandtlTurb) * (ev / mu)) * (Gamma * mu / o.prandtlLam);
+  } else {
+    L1 = 4.0 / 3.0 * mu;
+    L2 = d.kap[i] / (d.Cp[i] / d.gam[i]);
+  }
+  d.lamVisc[i] += (L1 + L2) * Area * Area / d.V[V_RHO * d.np + i];
+}
+__global__ void __launch_bounds__(128) k_timestep_finish(const __grid_constant__ Opts o, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  const double Vol = d.vol[p];
+  double dt = 0.0;
+  if (Vol > EPS) {
+    dt = o.cfl * Vol / d.lamInv[p];
+    if (o.viscous) dt = fmin(dt, o.cfl * 0.25 * Vol * Vol / d.lamVisc[p]);
+    if (dt > o.maxDt) dt = o.maxDt;
+  }
+  d.dt[p] = dt;
+}
+
+}  // namespace rx

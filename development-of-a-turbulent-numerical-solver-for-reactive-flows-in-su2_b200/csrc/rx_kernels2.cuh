@@ -1,0 +1,325 @@
+// rx_kernels2.cuh — edge-flux, owner-computes accumulation, source, boundary and update kernels.  See rx_kernels.cuh.
+#pragma once
+#include "rx_kernels.cuh"
+
+namespace rx {
+
+template <int NS>
+__device__ __forceinline__ void load_V(const Dev& d, long long p, double* V) {
+#pragma unroll
+  for (int v = 0; v < 7 + NS; ++v) V[v] = d.V[v * d.np + p];
+}
+template <int NS>
+__device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long long p, ViscEnd<NS>& E, bool withGrad) {
+  load_V<NS>(d, p, E.V);
+  if (withGrad) {
+#pragma unroll
+    for (int k = 0; k < (4 + NS) * 2; ++k) E.g[k] = d.grad[k * d.np + p];
+  }
+#pragma unroll
+  for (int s = 0; s < NS; ++s) E.X[s] = d.X[s * d.np + p];
+  E.mu = d.mu[p]; E.kap = d.kap[p]; E.T175 = d.T175[p]; E.Patm = d.Patm[p];
+  E.x[0] = d.x[p]; E.x[1] = d.y[p];
+  if (o.rans) { E.muT = d.turb[p]; E.ke = d.turb[d.np + p]; E.gk[0] = d.turb[3 * d.np + p]; E.gk[1] = d.turb[4 * d.np + p]; }
+  else { E.muT = 1.0; E.ke = 0.0; E.gk[0] = E.gk[1] = 0.0; }
+}
+
+// ---- Upwind_Residual (:2535-2785, 1st order) and Viscous_Residual (:5305-5386): one thread per edge, flux to edge arrays
+template <int NS, bool CONV, bool VISC>
+__global__ void __launch_bounds__(64) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= d.nEdge) return;
+  constexpr int NV = 4 + NS;
+  const int i = d.ei[e], j = d.ej[e];
+  const double nx = d.enx[e], ny = d.eny[e];
+  double res[NV];
+  if (VISC) {
+    ViscEnd<NS> I, J;
+    load_visc_end<NS>(d, o, i, I, true);
+    load_visc_end<NS>(d, o, j, J, true);
+    if (CONV) {
+      ausm<NS>(o.mInfty, I.V, J.V, nx, ny, res);
+#pragma unroll
+      for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
+    }
+    double scratch[NS * NS];
+    const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
+    viscous_flux<NS, true>(cc, o, I, J, nx, ny, sigma_k, scratch, res);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) d.fluxV[v * d.ne + e] = res[v];
+  } else {
+    double Vi[7 + NS], Vj[7 + NS];
+    load_V<NS>(d, i, Vi); load_V<NS>(d, j, Vj);
+    ausm<NS>(o.mInfty, Vi, Vj, nx, ny, res);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
+  }
+}
+
+// ---- Source_Residual (:2792-2874) + CSourceReactive::ComputeChemistry (numerics_direct_reactive.cpp:1728-1825), per owned point
+template <int NS>
+__device__ __forceinline__ void point_source(const ChemC<NS>& cc, const Opts& o, const Dev& d, long long p, double* src) {
+  double Y[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Y[s] = d.V[(V_Y + s) * d.np + p];
+  const double omT = o.rans ? d.turb[2 * d.np + p] : 0.0;
+  mass_production<NS>(cc, o.rans != 0, o.cMu, o.pasrLb, d.V[V_T * d.np + p], d.V[V_RHO * d.np + p], Y, omT, src);
+  const double Volume = d.vol[p];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) src[s] = src[s] * (-Volume / (1.0 / 1.0));
+}
+template <int NS>
+__global__ void __launch_bounds__(128) k_source(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  double src[NS];
+  point_source<NS>(cc, o, d, p, src);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) d.R[(U_S + s) * d.np + p] += src[s];
+}
+// stand-alone form over independent points, SoA inputs Y[s*n+p], res[s*n+p]
+template <int NS>
+__global__ void __launch_bounds__(128) k_source_points(const __grid_constant__ ChemC<NS> cc, int rans, double cMu, double pasrLb, long long n,
+                                                       const double* __restrict__ T, const double* __restrict__ rho, const double* __restrict__ Y,
+                                                       const double* __restrict__ omT, const double* __restrict__ vol, double* __restrict__ res) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  double y[NS], om[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) y[s] = Y[s * n + p];
+  mass_production<NS>(cc, rans != 0, cMu, pasrLb, T[p], rho[p], y, omT ? omT[p] : 0.0, om);
+  const double Volume = vol[p];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) res[s * n + p] = om[s] * (-Volume / (1.0 / 1.0));
+}
+
+// ---- owner-computes accumulation of edge fluxes into LinSysRes.  MODE: 1 conv (+i, -j), 2 visc (-i, +j), 3 conv, visc, then source
+template <int NS, int MODE>
+__global__ void __launch_bounds__(128) k_accumulate(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  constexpr int NV = 4 + NS;
+  double r[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) r[v] = d.R[v * d.np + p];
+  const int k0 = d.incPtr[p], k1 = d.incPtr[p + 1];
+  if (MODE & 1) {
+    for (int k = k0; k < k1; ++k) {
+      const int code = d.incEdge[k];
+      const bool first = code >= 0;
+      const long long e = first ? code : ~code;
+#pragma unroll
+      for (int v = 0; v < NV; ++v) { const double f = d.fluxC[v * d.ne + e]; r[v] = first ? r[v] + f : r[v] - f; }
+    }
+  }
+  if (MODE & 2) {
+    for (int k = k0; k < k1; ++k) {
+      const int code = d.incEdge[k];
+      const bool first = code >= 0;
+      const long long e = first ? code : ~code;
+#pragma unroll
+      for (int v = 0; v < NV; ++v) { const double f = d.fluxV[v * d.ne + e]; r[v] = first ? r[v] - f : r[v] + f; }
+    }
+  }
+  if (MODE == 3 && p < d.nPointDomain) {
+    double src[NS];
+    point_source<NS>(cc, o, d, p, src);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) r[U_S + s] += src[s];
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) d.R[v * d.np + p] = r[v];
+}
+
+// ---- boundary conditions: one thread per vertex of one marker (markers are issued in marker order on the stream)
+template <int NS>
+__device__ __forceinline__ void boundary_fluxes(const ChemC<NS>& cc, const Opts& o, const Dev& d, int i, const double* Vg, double nx, double ny) {
+  constexpr int NV = 4 + NS;
+  ViscEnd<NS> I, J;
+  load_visc_end<NS>(d, o, i, I, o.viscous != 0);
+  double res[NV];
+  ausm<NS>(o.mInfty, I.V, Vg, nx, ny, res);
+  double r[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) r[v] = d.R[v * d.np + i] + res[v];
+  if (o.viscous) {
+    J = I;   // gradient, transport, D_ij and turbulence of iPoint on both sides (:3583-3665, :4001-4110)
+#pragma unroll
+    for (int v = 0; v < 7 + NS; ++v) J.V[v] = Vg[v];
+    double scratch[NS * NS];
+    const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;
+    viscous_flux<NS, false>(cc, o, I, J, nx, ny, sigma_k, scratch, res);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) r[v] = r[v] - res[v];
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) d.R[v * d.np + i] = r[v];
+}
+// BC_Inlet, case TEMPERATURE_IMPOSE (solver_direct_reactive.cpp:3226-3674, :3467-3500)
+template <int NS>
+__global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = -m.nx[k], ny = -m.ny[k];
+  double Vg[7 + NS], Ys[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Ys[s] = m.Ys[s];
+  Vg[V_T] = m.T;
+  Vg[V_VX] = m.Vmag * m.dir0; Vg[V_VX + 1] = m.Vmag * m.dir1;
+  Vg[V_P] = d.V[V_P * d.np + i];
+  const double Rg = rgas(cc, Ys);
+  Vg[V_RHO] = Vg[V_P] / (Vg[V_T] * Rg) * 1.0;
+  bool ok = true;
+  Vg[V_H] = enthalpy(cc, m.T, Ys, ok) / 1.0 + (o.rans ? 1 : 0) * o.tkeInf;
+  Vg[V_H] += 0.5 * m.Vmag * m.Vmag;
+  const double g = frozen_gamma(cc, m.T, Ys);
+  Vg[V_A] = sqrt(g * Rg * m.T);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Vg[V_Y + s] = Ys[s];
+  boundary_fluxes<NS>(cc, o, d, i, Vg, nx, ny);
+}
+// BC_Outlet (solver_direct_reactive.cpp:3808-4123)
+template <int NS>
+__global__ void __launch_bounds__(64) k_bc_outlet(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  double Nx = m.nx[k], Ny = m.ny[k];
+  const double Area = sqrt(Nx * Nx + Ny * Ny);
+  Nx = -Nx; Ny = -Ny;
+  const double un0 = Nx / Area, un1 = Ny / Area;
+  double Vd[7 + NS], Vo[7 + NS];
+  load_V<NS>(d, i, Vd);
+  const double Density = Vd[V_RHO];
+  double Vel0 = Vd[V_VX], Vel1 = Vd[V_VX + 1];
+  double Velocity2 = 0.0;
+  Velocity2 += Vel0 * Vel0; Velocity2 += Vel1 * Vel1;
+  const double Pressure = Vd[V_P];
+  const double Gamma = d.gam[i];
+  double SoundSpeed = sqrt(Gamma * Pressure / Density);
+  const double Mach_Exit = sqrt(Velocity2) / SoundSpeed;
+  if (Mach_Exit >= 1.0) {
+#pragma unroll
+    for (int v = 0; v < 7 + NS; ++v) Vo[v] = Vd[v];
+  } else {
+    const double Entropy = Pressure * pow(1.0 / Density, Gamma);
+    const double Vn = 0.0 + Vel0 * un0 + Vel1 * un1;
+    const double Gamma_Minus_One = Gamma - 1.0;
+    const double Riemann = Vn + 2.0 * SoundSpeed / Gamma_Minus_One;
+    const double P_Exit = m.P / 1.0;
+    Vo[V_P] = P_Exit;
+    Vo[V_RHO] = pow(P_Exit / Entropy, 1.0 / Gamma);
+    SoundSpeed = sqrt(Gamma * P_Exit / Vo[V_RHO]);
+    const double Vn_Exit = Riemann - 2.0 * SoundSpeed / Gamma_Minus_One;
+    Velocity2 = 0.0;
+    Vel0 += (Vn_Exit - Vn) * un0; Velocity2 += Vel0 * Vel0; Vo[V_VX] = Vel0;
+    Vel1 += (Vn_Exit - Vn) * un1; Velocity2 += Vel1 * Vel1; Vo[V_VX + 1] = Vel1;
+    const double* Ys = Vd + V_Y;
+    Vo[V_T] = P_Exit / (Vo[V_RHO] * rgas(cc, Ys)) * 1.0;
+    bool ok = true;
+    Vo[V_H] = enthalpy(cc, Vo[V_T], Ys, ok) / 1.0 + (o.rans ? 1 : 0) * o.tkeInf;
+    Vo[V_H] += 0.5 * Velocity2;
+    Vo[V_A] = SoundSpeed;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) Vo[V_Y + s] = Ys[s];
+  }
+  boundary_fluxes<NS>(cc, o, d, i, Vo, Nx, Ny);
+}
+// BC_Isothermal_Wall (solver_direct_reactive.cpp:5393-5711), explicit, static wall
+template <int NS>
+__global__ void __launch_bounds__(64) k_bc_isothermal(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = m.nx[k], ny = m.ny[k];
+  const double Area = sqrt(nx * nx + ny * ny);
+  const int pn = m.nn[k];
+  double dij = 0.0;
+  dij += (d.x[pn] - d.x[i]) * (d.x[pn] - d.x[i]);
+  dij += (d.y[pn] - d.y[i]) * (d.y[pn] - d.y[i]);
+  dij = sqrt(dij);
+  const double rho = d.V[V_RHO * d.np + i];
+  d.Uold[U_MX * d.np + i] = 0.0 * rho;          // SetVelocity_Old (variable_direct_reactive.cpp:950-957)
+  d.Uold[(U_MX + 1) * d.np + i] = 0.0 * rho;
+  d.R[U_MX * d.np + i] = 0.0;                   // LinSysRes.SetBlock_Zero(iPoint, RHOVX+iDim)
+  d.R[(U_MX + 1) * d.np + i] = 0.0;
+  const double Twall = m.Twall;
+  const double Tj = d.V[V_T * d.np + pn];
+  const double ktr = d.kap[i];
+  double turb_closure = 0.0;
+  if (o.rans) {
+    const double eddy_v = d.turb[i];
+    const SplPos sp = spl_pos(cc, Twall);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      const double cp = spl_eval(cc, P_CP, s, sp) / cc.M[s];
+      const double aux_ys = d.U[(U_S + s) * d.np + i];   // partial density, not mass fraction (:5514-5517)
+      turb_closure += eddy_v / o.prandtlTurb * cp * aux_ys * (Twall - Tj) / dij;
+    }
+  }
+  const double dTdn = +(Twall - Tj) / dij;
+  d.R[U_E * d.np + i] -= ktr * dTdn * Area + turb_closure * Area;
+}
+
+// ---- ExplicitEuler/RK_Iteration (:2414-2493): update + per-block partial sums of Res^2 (deterministic two-stage reduction)
+template <int NS>
+__global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, double* __restrict__ partial) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  constexpr int NV = 4 + NS;
+  __shared__ double sh[4][NV];
+  double sq[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) sq[v] = 0.0;
+  if (p < d.nPointDomain) {
+    const double Vol = d.vol[p];
+    const double Delta = Vol > EPS ? d.dt[p] / Vol : 0.0;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const double Res = d.R[v * d.np + p] + 0.0;
+      const double lo = (v == U_MX || v == U_MX + 1 || v == U_E) ? -1.0 / EPS : 0.0, hi = 1.0 / EPS;
+      d.U[v * d.np + p] = fmin(fmax(d.Uold[v * d.np + p] + (-Res * Delta * alpha), lo), hi);
+      sq[v] = Res * Res;
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    double s = sq[v];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5][v] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < NV) {
+    const int v = threadIdx.x;
+    partial[(size_t)blockIdx.x * NV + v] = ((sh[0][v] + sh[1][v]) + (sh[2][v] + sh[3][v]));
+  }
+}
+__global__ void k_rms_finish(const double* __restrict__ partial, int nBlocks, int nv, long long nPointGlobal, double* __restrict__ rms, double* __restrict__ sumsq) {
+  // one block, thread v sums its column in block order: fixed order => bit-reproducible run to run
+  const int v = threadIdx.x;
+  if (v >= nv) return;
+  double s = 0.0;
+  for (int b = 0; b < nBlocks; ++b) s += partial[(size_t)b * nv + v];
+  sumsq[v] = s;
+  rms[v] = fmax(EPS * EPS, sqrt(s / (double)nPointGlobal));   // CSolver::SetResidual_RMS, solver_structure.cpp:172-187
+}
+
+// ---- halo plumbing: gather/scatter listed points of U (what=0) or of [grad, X, V, transport] (what=1)
+__global__ void k_pack(const double* __restrict__ soa, long long stride, int nv, long long n, const long long* __restrict__ pts, double* __restrict__ buf) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n * nv) return;
+  const int v = (int)(t / n); const long long k = t - (long long)v * n;
+  buf[t] = soa[v * stride + pts[k]];
+}
+__global__ void k_unpack(double* __restrict__ soa, long long stride, int nv, long long n, const long long* __restrict__ pts, const double* __restrict__ buf) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n * nv) return;
+  const int v = (int)(t / n); const long long k = t - (long long)v * n;
+  soa[v * stride + pts[k]] = buf[t];
+}
+
+}  // namespace rx

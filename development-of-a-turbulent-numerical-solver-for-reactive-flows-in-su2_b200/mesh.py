@@ -1,0 +1,181 @@
+"""Flat-array builder of the vertex-centred median-dual mesh for synthetic triangulated 2-D channels.
+
+Produces exactly the arrays the hot path reads from CGeometry (edge list + dual-face normals, control volumes,
+neighbour lists, boundary vertex normals and normal neighbours) without SU2's object-per-point preprocessing, so the
+4M / 32M / 256M-cell benchmark meshes of BASELINE.json can be built in seconds.  The formulas are SU2's:
+  CPhysicalGeometry::SetControlVolume      Common/src/geometry_structure.cpp:10457   (CEdge::SetNodes_Coord / GetVolume,
+                                            Common/src/dual_grid_structure.cpp:455-525)
+  CPhysicalGeometry::SetBoundControlVolume geometry_structure.cpp:9595               (CVertex::SetNodes_Coord :618-636)
+  CPhysicalGeometry::FindNormal_Neighbor   geometry_structure.cpp:12610
+Numbering is our own (points row-major, edges sorted by (lower node, higher node)); tests/test_mesh.py checks the values
+against the reference's geometry dump of the same .su2 mesh.
+"""
+import numpy as np
+
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL = 1, 2, 3
+
+
+def channel_points(nx, ny, L=0.25, H=0.025, stretch=1.0):
+    xs = np.linspace(0.0, L, nx)
+    t = np.linspace(0.0, 1.0, ny)
+    if stretch != 1.0:
+        t = 0.5 * (1.0 + np.tanh(stretch * (2 * t - 1)) / np.tanh(stretch))
+    ys = H * t
+    X, Y = np.meshgrid(xs, ys)          # [ny, nx], point id = j*nx + i
+    return np.stack([X.ravel(), Y.ravel()], axis=1)
+
+
+def channel_triangles(nx, ny):
+    """Every quad split in two with alternating diagonal (same as oracle/make_golden.py:write_channel_su2)."""
+    i, j = np.meshgrid(np.arange(nx - 1), np.arange(ny - 1))
+    i = i.ravel(); j = j.ravel()
+    a = j * nx + i; b = a + 1; c = b + nx; d = a + nx
+    even = ((i + j) % 2) == 0
+    t0 = np.where(even[:, None], np.stack([a, b, c], 1), np.stack([a, b, d], 1))
+    t1 = np.where(even[:, None], np.stack([a, c, d], 1), np.stack([b, c, d], 1))
+    tri = np.empty((2 * len(a), 3), dtype=np.int64)
+    tri[0::2] = t0; tri[1::2] = t1
+    return tri
+
+
+def dual_mesh(coord, tri, boundaries, nPointDomain=None):
+    """coord [nP,2], tri [nT,3], boundaries = list of (tag, line elements [nL,2]) -> flat mesh dict (see rx_cuda.h: rx_mesh)."""
+    nP = coord.shape[0]
+    x = coord[:, 0]; y = coord[:, 1]
+    # element CG: ((x0 + x1) + x2)/3  (CPrimalGrid::SetCG sums the nodes in order and divides by nNodes)
+    ecx = ((x[tri[:, 0]] + x[tri[:, 1]]) + x[tri[:, 2]]) / 3.0
+    ecy = ((y[tri[:, 0]] + y[tri[:, 1]]) + y[tri[:, 2]]) / 3.0
+    fa = np.concatenate([tri[:, 0], tri[:, 1], tri[:, 2]])
+    fb = np.concatenate([tri[:, 1], tri[:, 2], tri[:, 0]])
+    ex = np.concatenate([ecx, ecx, ecx]); ey = np.concatenate([ecy, ecy, ecy])
+    lo = np.minimum(fa, fb); hi = np.maximum(fa, fb)
+    key = lo * nP + hi
+    ukey, inv = np.unique(key, return_inverse=True)
+    nE = ukey.shape[0]
+    ei = ukey // nP; ej = ukey % nP
+    mx = 0.5 * (x[fa] + x[fb]); my = 0.5 * (y[fa] + y[fb])     # edge CG
+    flip = fa > fb
+    nxc = np.where(flip, my - ey, ey - my)
+    nyc = np.where(flip, -(mx - ex), -(ex - mx))
+    enx = np.bincount(inv, weights=nxc, minlength=nE)
+    eny = np.bincount(inv, weights=nyc, minlength=nE)
+    # control volumes: 0.5*|(E - P) x (M - P)| for both end points of every element face
+    def area(p):
+        ax = ex - x[p]; ay = ey - y[p]; bx = mx - x[p]; by = my - y[p]
+        return 0.5 * np.abs(ax * by - ay * bx)
+    vol = np.bincount(fa, weights=area(fa), minlength=nP) + np.bincount(fb, weights=area(fb), minlength=nP)
+    # neighbour CSR (sorted by neighbour index)
+    src = np.concatenate([ei, ej]); dst = np.concatenate([ej, ei])
+    order = np.lexsort((dst, src))
+    nbPoint = dst[order]
+    nbPtr = np.zeros(nP + 1, dtype=np.int64)
+    np.cumsum(np.bincount(src, minlength=nP), out=nbPtr[1:])
+    markers = []
+    for tag, lines in boundaries:
+        lines = np.asarray(lines, dtype=np.int64)
+        seq = lines.ravel()                                   # vertex order = first appearance in the element loop
+        _, first = np.unique(seq, return_index=True)
+        node = seq[np.sort(first)]
+        vid = np.full(nP, -1, dtype=np.int64); vid[node] = np.arange(len(node))
+        cx = 0.5 * (x[lines[:, 0]] + x[lines[:, 1]]); cy = 0.5 * (y[lines[:, 0]] + y[lines[:, 1]])
+        n0, n1 = lines[:, 0], lines[:, 1]
+        vnx = np.zeros(len(node)); vny = np.zeros(len(node))
+        # node 0: SetNodes_Coord(Elem_CG, Vertex) -> (Vy - Cy, -(Vx - Cx)); node 1: SetNodes_Coord(Vertex, Elem_CG) -> (Cy - Vy, -(Cx - Vx))
+        np.add.at(vnx, vid[n0], y[n0] - cy); np.add.at(vny, vid[n0], -(x[n0] - cx))
+        np.add.at(vnx, vid[n1], cy - y[n1]); np.add.at(vny, vid[n1], -(cx - x[n1]))
+        # FindNormal_Neighbor: neighbour with the largest cosine to the vertex normal (last one on ties, `>=`)
+        nn = np.empty(len(node), dtype=np.int64)
+        for k, p in enumerate(node):
+            nb = nbPoint[nbPtr[p]:nbPtr[p + 1]]
+            dx = x[nb] - x[p]; dy = y[nb] - y[p]
+            cos = (dx * vnx[k] + dy * vny[k]) / (np.sqrt(dx * dx + dy * dy) * np.sqrt(vnx[k] ** 2 + vny[k] ** 2))
+            best = -1.0; arg = 0
+            for q in range(len(nb)):
+                if cos[q] >= best:
+                    best = cos[q]; arg = q
+            nn[k] = nb[arg]
+        markers.append(dict(tag=tag, kind=0, node=node, normalNeighbor=nn, normal=np.stack([vnx, vny], 1)))
+    return dict(nPoint=nP, nPointDomain=nP if nPointDomain is None else nPointDomain, nEdge=nE,
+                edgeNodes=np.stack([ei, ej], 1), edgeNormal=np.stack([enx, eny], 1), coord=np.ascontiguousarray(coord),
+                volume=vol, nbPtr=nbPtr, nbPoint=nbPoint, markers=markers)
+
+
+def channel_boundaries(nx, ny):
+    j = np.arange(ny - 1); i = np.arange(nx - 1)
+    # line elements are oriented so that the vertex normal points out of the domain (SU2 re-orients boundary elements
+    # the same way: CPhysicalGeometry::Check_BoundElem_Orientation)
+    return [("inlet", np.stack([(j + 1) * nx, j * nx], 1)),
+            ("outlet", np.stack([j * nx + nx - 1, (j + 1) * nx + nx - 1], 1)),
+            ("lower_wall", np.stack([i, i + 1], 1)),
+            ("upper_wall", np.stack([(ny - 1) * nx + i + 1, (ny - 1) * nx + i], 1))]
+
+
+def channel_mesh(nx, ny, L=0.25, H=0.025, stretch=1.0, Ns=9, oxidizer=2):
+    """The synthetic channel of SURVEY.md §8(d): inlet (TEMPERATURE_IMPOSE, pure oxidiser, 300 K, 20 m/s), outlet 101325 Pa,
+    isothermal walls (300 K upper, 600 K lower) — the boundary set of tests/golden/channel_*.npz."""
+    coord = channel_points(nx, ny, L, H, stretch)
+    m = dual_mesh(coord, channel_triangles(nx, ny), channel_boundaries(nx, ny))
+    ys = np.zeros(Ns); ys[oxidizer] = 1.0
+    m["markers"][0].update(kind=KIND_INLET, T=300.0, Vmag=20.0, dir=[1.0, 0.0], Ys=ys)
+    m["markers"][1].update(kind=KIND_OUTLET, P=101325.0)
+    m["markers"][2].update(kind=KIND_ISOTHERMAL, Twall=600.0)
+    m["markers"][3].update(kind=KIND_ISOTHERMAL, Twall=300.0)
+    return m
+
+
+def partition_strips(mesh, nParts):
+    """Strip partition in x of a flat mesh into nParts ranks with one halo layer, SU2's scheme:
+    owned points first, then halo points grouped by owner rank; every edge with at least one owned end is kept (halo-owned
+    edges are duplicated on both sides).  Returns a list of dict(mesh=local flat mesh, glob=local->global point ids,
+    send={rank: local owned ids}, recv={rank: local halo ids}) with matching send/recv orders."""
+    nP = mesh["nPoint"]
+    xs = mesh["coord"][:, 0]
+    order = np.argsort(xs, kind="stable")
+    owner = np.empty(nP, dtype=np.int64)
+    bounds = [(nP * r) // nParts for r in range(nParts + 1)]
+    for r in range(nParts):
+        owner[order[bounds[r]:bounds[r + 1]]] = r
+    ei, ej = mesh["edgeNodes"][:, 0], mesh["edgeNodes"][:, 1]
+    parts = []
+    for r in range(nParts):
+        own = np.flatnonzero(owner == r)
+        keep = (owner[ei] == r) | (owner[ej] == r)
+        e_i, e_j = ei[keep], ej[keep]
+        touched = np.unique(np.concatenate([e_i, e_j]))
+        halo = touched[owner[touched] != r]
+        halo = halo[np.lexsort((halo, owner[halo]))]           # grouped by owner rank, ascending global id inside
+        glob = np.concatenate([own, halo])
+        g2l = np.full(nP, -1, dtype=np.int64); g2l[glob] = np.arange(len(glob))
+        loc = dict(nPoint=len(glob), nPointDomain=len(own), nEdge=int(keep.sum()),
+                   edgeNodes=np.stack([g2l[e_i], g2l[e_j]], 1), edgeNormal=mesh["edgeNormal"][keep],
+                   coord=mesh["coord"][glob], volume=mesh["volume"][glob])
+        # neighbour CSR restricted to local points (owned points keep all their neighbours by construction)
+        ptr = [0]; idx = []
+        for g in glob:
+            nb = g2l[mesh["nbPoint"][mesh["nbPtr"][g]:mesh["nbPtr"][g + 1]]]
+            nb = nb[nb >= 0]
+            idx.append(nb); ptr.append(ptr[-1] + len(nb))
+        loc["nbPtr"] = np.array(ptr, dtype=np.int64)
+        loc["nbPoint"] = np.concatenate(idx) if idx else np.zeros(0, dtype=np.int64)
+        mk = []
+        for m in mesh["markers"]:
+            sel = g2l[m["node"]] >= 0
+            sel &= owner[m["node"]] == r
+            d = dict(m)
+            d.update(node=g2l[m["node"][sel]], normalNeighbor=g2l[m["normalNeighbor"][sel]], normal=m["normal"][sel])
+            mk.append(d)
+        loc["markers"] = mk
+        recv = {int(q): g2l[halo[owner[halo] == q]] for q in np.unique(owner[halo])}
+        parts.append(dict(mesh=loc, glob=glob, recv=recv, halo_glob=halo, owner=owner))
+    for r in range(nParts):
+        send = {}
+        for q in range(nParts):
+            if q != r and r in parts[q]["recv"]:
+                hg = parts[q]["halo_glob"]
+                want = hg[parts[q]["owner"][hg] == r]           # global ids rank q expects from r, in q's halo order
+                g2l = np.full(nP, -1, dtype=np.int64); g2l[parts[r]["glob"]] = np.arange(len(parts[r]["glob"]))
+                send[q] = g2l[want]
+        parts[r]["send"] = send
+    for p in parts:
+        p.pop("halo_glob"); p.pop("owner")
+    return parts

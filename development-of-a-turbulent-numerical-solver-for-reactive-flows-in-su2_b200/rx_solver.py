@@ -1,0 +1,218 @@
+"""Host-side mirror of the reference's solver interface for the reactive residual path, over the C ABI (ctypes).
+
+Class and method names follow SU2_CFD/include/solver_reactive.hpp (CReactiveNSSolver: Preprocessing, SetTime_Step,
+Upwind_Residual, Viscous_Residual, Source_Residual, BC_*, ExplicitEuler_Iteration, ExplicitRK_Iteration, Set_OldSolution);
+each method forwards to exactly one entry point of include/rx_cuda.h.  Arrays are numpy, array-of-structures, in SU2's
+point numbering — the layout of CVariable::Solution / CSysVector.
+
+No CPU fallback: if librx_cuda.so is missing, cannot be loaded, or there is no CUDA device, RxError is raised.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librx_cuda.so")
+CSRC = os.path.join(HERE, "csrc")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+class RxError(RuntimeError):
+    pass
+
+
+def build_library(force=False, verbose=False):
+    """nvcc cross-compiles the CUDA extension for sm_100a (works without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
+    srcs.append(os.path.join(os.path.dirname(HERE), "include", "rx_cuda.h"))
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "rx_cuda.cu")]
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+_P = C.POINTER(C.c_double)
+_PI = C.POINTER(C.c_int64)
+
+
+class _Chem(C.Structure):
+    _fields_ = [("Ns", C.c_int), ("Nr", C.c_int), ("nKnots", C.c_int)] + [
+        (n, _P) for n in ["mMasses", "diffVol", "x", "y", "y2", "As", "Betas", "Ta", "reversible", "availBack", "AsB",
+                          "BetasB", "TaB", "nuR", "nuP", "expR", "expP"]]
+
+
+class _Marker(C.Structure):
+    _fields_ = [("kind", C.c_int), ("nVertex", C.c_int), ("node", _PI), ("normalNeighbor", _PI), ("normal", _P),
+                ("T", C.c_double), ("Vmag", C.c_double), ("dir", C.c_double * 2), ("Ys", _P), ("P", C.c_double),
+                ("Twall", C.c_double)]
+
+
+class _Mesh(C.Structure):
+    _fields_ = [("nPoint", C.c_int64), ("nPointDomain", C.c_int64), ("nEdge", C.c_int64), ("edgeNodes", _PI),
+                ("edgeNormal", _P), ("coord", _P), ("volume", _P), ("nbPtr", _PI), ("nbPoint", _PI),
+                ("nMarker", C.c_int), ("markers", C.POINTER(_Marker))]
+
+
+class _Opts(C.Structure):
+    _fields_ = [("viscous", C.c_int), ("rans", C.c_int), ("leastSquares", C.c_int),
+                ("mInfty", C.c_double), ("cfl", C.c_double), ("maxDt", C.c_double), ("Tmin", C.c_double), ("Tmax", C.c_double),
+                ("clipT", C.c_int), ("ignition", C.c_int), ("ignitionIter", C.c_int64), ("ignitionT", C.c_double),
+                ("fuelIndex", C.c_int), ("oxidizerIndex", C.c_int),
+                ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
+                ("pasrLb", C.c_double), ("tkeInf", C.c_double), ("device", C.c_int)]
+
+
+EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "rx_set_stream", "rx_synchronize",
+           "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
+           "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
+           "rx_residual_source", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
+           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count"]
+
+_lib = None
+
+
+def load_library():
+    """dlopen librx_cuda.so (built in-tree by build_library / __graft_entry__.build); raises RxError if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RxError("librx_cuda.so not built (run __graft_entry__.build()); there is no CPU fallback")
+        try:
+            _lib = C.CDLL(LIB_PATH)
+        except OSError as e:
+            raise RxError("cannot load %s: %s (no CPU fallback)" % (LIB_PATH, e))
+        _lib.rx_last_error.restype = C.c_char_p
+        _lib.rx_last_error.argtypes = [C.c_void_p]
+        _lib.rx_launch_count.restype = C.c_int64
+        _lib.rx_launch_count.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_P)
+
+
+def _i(a):
+    return a.ctypes.data_as(_PI)
+
+
+def _c(a, dt=np.float64):
+    return np.ascontiguousarray(a, dtype=dt)
+
+
+class CReactiveNSSolverGPU:
+    """Mirror of CReactiveNSSolver (SU2_CFD/include/solver_reactive.hpp:398) whose hot virtuals run on the GPU.
+
+    mesh  : dict(nPoint, nPointDomain, edgeNodes[nE,2], edgeNormal[nE,2], coord[nP,2], volume[nP], nbPtr, nbPoint,
+                 markers=[dict(kind, node, normalNeighbor, normal, T, Vmag, dir, Ys, P, Twall)])   (flat CGeometry export)
+    chem  : dict of ReactingModelLibrary tables (see include/rx_cuda.h: rx_chem)
+    opts  : dict of CConfig-derived constants (rx_opts)
+    """
+
+    def __init__(self, mesh, chem, opts, device=0):
+        L = self.lib = load_library()
+        self._keep = []
+        k = lambda a, dt=np.float64: (self._keep.append(_c(a, dt)), self._keep[-1])[1]
+        Ns, Nr = int(chem["Ns"]), int(chem["Nr"])
+        pad = lambda a, n: k(np.asarray(a, dtype=np.float64).reshape(-1) if n else np.zeros(1))
+        ch = _Chem(Ns, Nr, int(chem["nKnots"]), _d(k(chem["mMasses"])), _d(k(chem["diffVol"])), _d(k(chem["x"])),
+                   _d(k(chem["y"])), _d(k(chem["y2"])),
+                   *[_d(pad(chem[n], Nr)) for n in ["As", "Betas", "Ta", "reversible", "availBack", "AsB", "BetasB", "TaB"]],
+                   *[_d(pad(chem[n], Nr * Ns)) for n in ["nuR", "nuP", "expR", "expP"]])
+        mks = mesh.get("markers", [])
+        arr = (_Marker * max(len(mks), 1))()
+        for q, m in enumerate(mks):
+            node = k(m["node"], np.int64)
+            arr[q] = _Marker(int(m["kind"]), len(node), _i(node), _i(k(m["normalNeighbor"], np.int64)), _d(k(m["normal"])),
+                             float(m.get("T", 0.0)), float(m.get("Vmag", 0.0)), (C.c_double * 2)(*m.get("dir", [0.0, 0.0])),
+                             _d(k(m.get("Ys", np.zeros(Ns)))), float(m.get("P", 0.0)), float(m.get("Twall", 0.0)))
+        en = k(mesh["edgeNodes"], np.int64)
+        self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
+        ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),
+                   _d(k(mesh["volume"])), _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
+        od = dict(opts)
+        od["device"] = device
+        self.opts = od
+        o = _Opts(**{f[0]: od[f[0]] for f in _Opts._fields_})
+        self.Ns, self.nVar, self.nPrim, self.nGrad = Ns, Ns + 4, Ns + 7, Ns + 4
+        ctx = C.c_void_p()
+        rc = L.rx_create(C.byref(ctx), C.byref(ms), C.byref(ch), C.byref(o))
+        if rc != 0:
+            raise RxError("rx_create failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
+        self.ctx = ctx
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RxError("rx call failed (%d): %s" % (rc, self.lib.rx_last_error(self.ctx).decode()))
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.rx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- mirrors of node[]->Solution / Primitive / LinSysRes
+    def SetSolution(self, U): self._ck(self.lib.rx_set_solution(self.ctx, _d(_c(U))))
+    def SetTemperature(self, T): self._ck(self.lib.rx_set_temperature(self.ctx, _d(_c(T))))
+    def SetTurbulence(self, t6): self._ck(self.lib.rx_set_turbulence(self.ctx, _d(_c(t6))))
+
+    def GetSolution(self):
+        U = np.empty((self.nPoint, self.nVar)); self._ck(self.lib.rx_get_solution(self.ctx, _d(U))); return U
+
+    def GetPrimitive(self):
+        V = np.empty((self.nPoint, self.nPrim)); aux = np.empty((self.nPoint, 6)); g = np.empty((self.nPoint, self.nGrad, 2))
+        self._ck(self.lib.rx_get_primitive(self.ctx, _d(V), _d(aux), _d(g))); return V, aux, g
+
+    def GetDelta_Time(self):
+        d = np.empty((self.nPoint, 3)); self._ck(self.lib.rx_get_dt(self.ctx, _d(d))); return d
+
+    def GetLinSysRes(self):
+        R = np.empty((self.nPoint, self.nVar)); self._ck(self.lib.rx_get_residual(self.ctx, _d(R))); return R
+
+    # ---- CSolver virtuals (solver_reactive.hpp:127-363,441-554)
+    def Preprocessing(self, ExtIter, Output=False, count_nonphysical=True):
+        n = C.c_int64(0)
+        self._ck(self.lib.rx_preprocess(self.ctx, C.c_int64(ExtIter), int(Output), C.byref(n) if count_nonphysical else None))
+        return n.value
+
+    def Set_OldSolution(self): self._ck(self.lib.rx_set_old_solution(self.ctx))
+    def SetTime_Step(self): self._ck(self.lib.rx_time_step(self.ctx))
+    def Upwind_Residual(self): self._ck(self.lib.rx_residual_conv(self.ctx))
+    def Viscous_Residual(self): self._ck(self.lib.rx_residual_visc(self.ctx))
+    def Source_Residual(self): self._ck(self.lib.rx_residual_source(self.ctx))
+    def BC_All(self): self._ck(self.lib.rx_bc(self.ctx))
+
+    def ExplicitRK_Iteration(self, alpha, want_rms=True):
+        rms = np.empty(self.nVar)
+        self._ck(self.lib.rx_update_explicit(self.ctx, C.c_double(alpha), _d(rms) if want_rms else None))
+        return rms if want_rms else None
+
+    def ExplicitEuler_Iteration(self, want_rms=True):
+        return self.ExplicitRK_Iteration(1.0, want_rms)
+
+    def Iterate(self, ExtIter, rk_alpha=(1.0,), want_rms=True):
+        """One MultiGrid_Cycle + the Output preprocessing pass, all on the device (integration_time.cpp:42-181)."""
+        a = _c(rk_alpha); rms = np.empty(self.nVar)
+        self._ck(self.lib.rx_iterate(self.ctx, C.c_int64(ExtIter), len(a), _d(a), _d(rms) if want_rms else None))
+        return rms if want_rms else None
+
+    def Synchronize(self): self._ck(self.lib.rx_synchronize(self.ctx))
+    def LaunchCount(self): return int(self.lib.rx_launch_count(self.ctx))
+
+    # ---- the stage API used by the parity tests (same names as tests/rxcase.Oracle)
+    set_solution = SetSolution; set_temperature = SetTemperature; set_turbulence = SetTurbulence
+    solution = GetSolution; primitive = GetPrimitive; dt = GetDelta_Time; residual = GetLinSysRes
+    def preprocess(self, it, output=False): return self.Preprocessing(it, output)
+    set_old_solution = Set_OldSolution; time_step = SetTime_Step; upwind_residual = Upwind_Residual
+    viscous_residual = Viscous_Residual; source_residual = Source_Residual; boundary_conditions = BC_All
+    def explicit_update(self, alpha=1.0): return self.ExplicitRK_Iteration(alpha)

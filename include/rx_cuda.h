@@ -1,0 +1,137 @@
+/* rx_cuda.h — C ABI of librx_cuda.so: the B200-native (sm_100a, FP64 CUDA) implementation of the reactive-flow
+ * residual hot path of the SU2 fork LorenzoVallisa/Development-of-a-turbulent-numerical-solver-for-reactive-flows-in-SU2.
+ *
+ * This is the drop-in boundary: a host-side CSolver subclass (csrc/host/CReactiveNSSolverGPU.*, or the
+ * Python mirror rx_solver.py) overrides the CSolver virtuals declared in SU2_CFD/include/solver_reactive.hpp:127-363,441-554
+ * and forwards each to one entry point below.  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Conventions
+ *  - every `const double*` / `double*` argument is a HOST pointer unless the name ends in `_dev`; the library copies at
+ *    the call and never retains host pointers.  Arrays are array-of-structures in SU2's point numbering, exactly the
+ *    layout of CVariable::Solution / CSysVector (Common/src/vector_structure.cpp:352-395):
+ *        U[p][nVar]   = [rho, rho u, rho v, rho E, rho_1..rho_Ns]        (variable_direct_reactive.cpp:4-17)
+ *        V[p][nPrim]  = [T, u, v, P, rho, h, a, Y_1..Y_Ns]
+ *        grad[p][nGrad][2], rows [T, u, v, P, X_1..X_Ns]
+ *  - every call returns 0 or a negative rx_status; rx_last_error() gives the text.  No exception crosses the ABI.
+ *  - one host thread per rx_ctx; contexts are independent.  All work of a context is issued on one CUDA stream
+ *    (rx_set_stream; default = the legacy default stream) and the stage calls do NOT synchronise the host.
+ *  - two space dimensions (all configurations of BASELINE.json are 2-D); Ns must be one of the compiled instantiations
+ *    (rx_supported_species).  There is no CPU fallback: without a CUDA device rx_create fails with RX_ERR_NO_DEVICE.
+ */
+#ifndef RX_CUDA_H
+#define RX_CUDA_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rx_ctx rx_ctx;
+
+enum rx_status { RX_OK = 0, RX_ERR_ARG = -1, RX_ERR_NO_DEVICE = -2, RX_ERR_CUDA = -3, RX_ERR_UNSUPPORTED = -4, RX_ERR_NAN = -5 };
+enum rx_bc_kind { RX_BC_NONE = 0, RX_BC_INLET_TEMPERATURE_IMPOSE = 1, RX_BC_OUTLET = 2, RX_BC_ISOTHERMAL = 3 };
+
+/* Tables held by Framework::ReactingModelLibrary after Setup() (Common/src/Framework/reacting_model_library.cpp:1520-1586,
+ * members reacting_model_library.hpp:655-766).  Matrices are [reaction][species]. */
+typedef struct {
+  int Ns, Nr, nKnots;
+  const double* mMasses;   /* [Ns] g/mol                     (mMasses)            */
+  const double* diffVol;   /* [Ns] Fuller diffusion volumes  (Diff_Volumes)       */
+  const double* x;         /* [nKnots] equispaced temperature grid of the splines */
+  const double* y;         /* [5][Ns][nKnots]: Mu, Kappa, Cp, Enth, Entr _Spline values   */
+  const double* y2;        /* [5][Ns][nKnots]: their second derivatives (Tools/spline.cpp:10-58) */
+  const double *As, *Betas, *Ta;                 /* [Nr] forward Arrhenius (SI)                 */
+  const double *reversible, *availBack;          /* [Nr] 0/1: Reversible_Reactions, Available_Backward_Rate */
+  const double *AsB, *BetasB, *TaB;              /* [Nr] backward Arrhenius where available     */
+  const double *nuR, *nuP, *expR, *expP;         /* [Nr][Ns] Stoich_Coeffs_{Reactants,Products}[_Exp] */
+} rx_chem;
+
+/* One boundary marker: geometry->vertex[m][v]->{GetNode, GetNormal, GetNormal_Neighbor} and the marker's cfg values
+ * (MARKER_INLET + INLET_MASS_FRAC / MARKER_OUTLET / MARKER_ISOTHERMAL). */
+typedef struct {
+  int kind;                 /* rx_bc_kind */
+  int nVertex;
+  const int64_t* node;            /* [nVertex] */
+  const int64_t* normalNeighbor;  /* [nVertex] */
+  const double* normal;           /* [nVertex][2] */
+  double T, Vmag, dir[2];   /* inlet: GetInlet_Ttotal, GetInlet_Ptotal (velocity magnitude), GetInlet_FlowDir */
+  const double* Ys;         /* inlet: [Ns] GetInlet_MassFrac */
+  double P;                 /* outlet: GetOutlet_Pressure */
+  double Twall;             /* isothermal: GetIsothermal_Temperature */
+} rx_marker;
+
+/* Flat export of CGeometry (Common/include/dual_grid_structure.hpp:140,747,884). Points [0,nPointDomain) are owned,
+ * [nPointDomain,nPoint) are halos (geometry->node[p]->GetDomain()). */
+typedef struct {
+  int64_t nPoint, nPointDomain, nEdge;
+  const int64_t* edgeNodes;   /* [nEdge][2]  edge[e]->GetNode(0/1) */
+  const double* edgeNormal;   /* [nEdge][2]  edge[e]->GetNormal()  */
+  const double* coord;        /* [nPoint][2] */
+  const double* volume;       /* [nPoint]    */
+  const int64_t* nbPtr;       /* [nPoint+1]  neighbour CSR, node[p]->GetPoint(k) order (WLS gradient) */
+  const int64_t* nbPoint;
+  int nMarker;
+  const rx_marker* markers;
+} rx_mesh;
+
+/* Constants the reference reads from CConfig in the solver / numerics constructors
+ * (numerics_direct_reactive.cpp:17-19,395-399,1417,1690-1694; solver_direct_reactive.cpp:4131-4383). */
+typedef struct {
+  int viscous, rans, leastSquares;
+  double mInfty, cfl, maxDt, Tmin, Tmax;
+  int clipT, ignition; int64_t ignitionIter; double ignitionT; int fuelIndex, oxidizerIndex;
+  double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
+  int device;               /* CUDA device ordinal */
+} rx_opts;
+
+int rx_supported_species(int Ns);            /* 1 if kernels for this species count are compiled in */
+int rx_create(rx_ctx** out, const rx_mesh*, const rx_chem*, const rx_opts*);   /* replaces the CReactiveNSSolver ctor, solver_direct_reactive.cpp:4131 */
+void rx_destroy(rx_ctx*);
+const char* rx_last_error(rx_ctx*);          /* ctx may be NULL: error of the last failed rx_create */
+int rx_set_stream(rx_ctx*, void* cudaStream);
+int rx_synchronize(rx_ctx*);
+
+/* mirrors of node[]->Solution / Primitive / LinSysRes (host <-> device, AoS, SU2 numbering) */
+int rx_set_solution(rx_ctx*, const double* U);
+int rx_set_temperature(rx_ctx*, const double* T);         /* V[T] = start value of the secant solve (variable_direct_reactive.cpp:622) */
+int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k, omega, dk/dx, dk/dy, sigma_k from CTurbSSTSolver */
+int rx_get_solution(rx_ctx*, double* U);
+int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */
+int rx_get_dt(rx_ctx*, double* dt3);                      /* [nPoint][3]: Delta_Time, Max_Lambda_Inv, Max_Lambda_Visc */
+int rx_get_residual(rx_ctx*, double* R);                  /* LinSysRes */
+
+/* stages; each replaces the CSolver virtual named on the right (solver_direct_reactive.cpp) */
+int rx_preprocess(rx_ctx*, int64_t extIter, int output, int64_t* nonPhysical /* may be NULL: no host sync */);  /* Preprocessing :4693 */
+int rx_set_old_solution(rx_ctx*);                         /* CSolver::Set_OldSolution, solver_structure.inl:898 */
+int rx_time_step(rx_ctx*);                                /* SetTime_Step :5057 */
+int rx_residual_conv(rx_ctx*);                            /* Upwind_Residual :2535 */
+int rx_residual_visc(rx_ctx*);                            /* Viscous_Residual :5305 */
+int rx_residual_source(rx_ctx*);                          /* Source_Residual :2792 */
+int rx_bc(rx_ctx*);                                       /* BC_Inlet :3226, BC_Outlet :3808, then BC_Isothermal_Wall :5393 (integration_structure.cpp:89-190) */
+int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */
+
+/* one full MultiGrid_Cycle (integration_time.cpp:143-181) with everything resident: for each RK stage
+ * preprocess -> (stage 0: set_old, time_step) -> fused conv+visc+source residual -> bc -> update; then the Output
+ * preprocess pass (integration_time.cpp:110-112).  resRms may be NULL. */
+int rx_iterate(rx_ctx*, int64_t extIter, int nRK, const double* rkAlpha, double* resRms);
+
+/* stand-alone Arrhenius(+PaSR) source over independent points (CSourceReactive::ComputeChemistry,
+ * numerics_direct_reactive.cpp:1728-1825).  Host-pointer and device-pointer forms. */
+int rx_source_points(const rx_chem*, int rans, double cMu, double pasrLb, int64_t n, const double* T, const double* rho,
+                     const double* Y, const double* omegaTurb, const double* vol, double* res, int device);
+int rx_source_points_dev(rx_ctx*, int64_t n, const double* T_dev, const double* rho_dev, const double* Y_dev /* [Ns][n] SoA */,
+                         const double* omegaTurb_dev, const double* vol_dev, double* res_dev /* [Ns][n] SoA */);
+
+/* halo exchange plumbing for one-process-per-GPU runs (replaces Set_MPI_Solution :1530, Set_MPI_Primitive_Gradient :1877):
+ * pack `what` (0 = conserved U, 1 = gradients+turbulence-free primitives) of the listed points into buf_dev[nVarOfWhat][n],
+ * or unpack into them; the transport in between (NCCL send/recv) belongs to the caller. */
+int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double* buf_dev);
+int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);
+int rx_halo_width(rx_ctx*, int what);
+
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+int64_t rx_launch_count(rx_ctx*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

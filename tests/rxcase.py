@@ -211,3 +211,30 @@ def vec_rel_err(a, ref):
     den = np.abs(r).max(axis=0)
     out = np.where(den > 0, num / np.where(den > 0, den, 1.0), num)
     return out
+
+
+def mesh_dict(case):
+    """Flat mesh dict (rx_mesh layout) of a golden case, for CReactiveNSSolverGPU."""
+    mk = []
+    for d in marker_list(case):
+        mk.append(dict(kind=d["kind"], node=d["node"], normalNeighbor=d["normalNeighbor"], normal=d["normal"], T=d["T"],
+                       Vmag=d["Vmag"], dir=d["dir"], Ys=d["Ys"], P=d["P"], Twall=d["Twall"]))
+    return dict(nPoint=case.nPoint, nPointDomain=case.nPointDomain, edgeNodes=case["geo_edge_nodes"],
+                edgeNormal=case["geo_edge_normal"], coord=case["geo_coord"], volume=case["geo_volume"],
+                nbPtr=case["geo_nb_ptr"], nbPoint=case["geo_nb_point"], markers=mk)
+
+
+def load_package():
+    import importlib
+    import sys
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    return importlib.import_module("development-of-a-turbulent-numerical-solver-for-reactive-flows-in-su2_b200")
+
+
+def gpu_solver(case, opts_override=None):
+    pk = load_package()
+    od = opts_dict(case)
+    if opts_override:
+        od.update(opts_override)
+    return pk.CReactiveNSSolverGPU(mesh_dict(case), chem_arrays(case), od)
