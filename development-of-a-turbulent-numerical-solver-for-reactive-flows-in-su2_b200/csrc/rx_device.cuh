@@ -157,6 +157,24 @@ RX_HD void transport(const ChemC<NS>& cc, double T, const double* Y, double& muM
   }
 }
 
+// a^1.75 = a*sqrt(a)*sqrt(sqrt(a)) evaluated in double-double and rounded once: the correctly rounded value, which is what
+// glibc's pow(T, 1.75) returns (GetDij_SM, reacting_model_library.cpp:751-766).  CUDA's pow() is only accurate to 2 ulp,
+// and a 1-ulp change of the diffusion coefficients is amplified by the BiCGSTAB iteration of the Stefan–Maxwell solve to
+// ~1e-11 of the diffusion flux — above the 1e-12 residual parity target.  fma() here is an explicit, exact residual.
+RX_HD double pow175(double a) {
+  const double s0 = sqrt(a);
+  const double s1 = fma(-s0, s0, a) / (2.0 * s0);          // sqrt(a) = s0 + s1
+  const double q0 = sqrt(s0);
+  const double q1 = (fma(-q0, q0, s0) + s1) / (2.0 * q0);  // sqrt(sqrt(a)) = q0 + q1
+  const double p0 = a * s0;
+  const double p1 = fma(a, s0, -p0) + a * s1;              // a*sqrt(a) = p0 + p1
+  const double ph = p0 + p1;
+  const double pl = p1 - (ph - p0);
+  const double r0 = ph * q0;
+  const double r1 = fma(ph, q0, -r0) + (ph * q1 + pl * q0);
+  return r0 + r1;
+}
+
 // ---- cons -> prim (CReactiveEulerVariable::Cons2PrimVar, SU2_CFD/src/variable_direct_reactive.cpp:550-778) ----
 // U is modified in place where the reference modifies Solution (:571-583). V[V_T] holds the secant start value on entry.
 template <int NS>

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC
     double mu, ka;
     transport(cc, T, Y, mu, ka);
     d.mu[p] = mu; d.kap[p] = ka;
-    d.T175[p] = 1.0e-3 * pow(T, 1.75);                 // numerator of GetDij_SM (:751-766)
+    d.T175[p] = 1.0e-3 * pow175(T);                 // numerator of GetDij_SM (:751-766)
     d.Patm[p] = V[V_P] * 1.0 / 101325.0;
   }
   if (o.ignition && extIter < o.ignitionIter) {        // ignition hack: overwrite T only (:1013-1024)

@@ -203,6 +203,34 @@ class Oracle:
         rms = np.empty(self.nVar); self.lib.rxo_explicit_update(self.ctx, C.c_double(alpha), _p(rms)); return rms
 
 
+def group_rel_err(a, ref, groups):
+    """Vector-relative error per group of columns:  max_{p, v in group}|a-ref| / max_{p, v in group}|ref|.
+    Used for residual / conserved-variable arrays, where columns of one group share units (mass: rho and rho_s;
+    momentum; energy) and a single species column can be numerically zero everywhere."""
+    a = np.asarray(a, dtype=np.float64).reshape(ref.shape[0], -1)
+    r = np.asarray(ref, dtype=np.float64).reshape(ref.shape[0], -1)
+    out = []
+    for g in groups:
+        num = np.abs(a[:, g] - r[:, g]).max()
+        den = np.abs(r[:, g]).max()
+        out.append(num / den if den > 0 else num)
+    return np.array(out)
+
+
+def stage_rel_err(key, a, ref, Ns):
+    """Error measure used by the parity tests for the stage array named `key` (see group_rel_err / vec_rel_err)."""
+    what = key.split("_", 2)[-1]
+    sp = list(range(4, 4 + Ns))
+    if what in ("U0", "U1", "res_conv", "res_visc", "res_src", "res_bc", "rms"):
+        return group_rel_err(a, ref, [[0] + sp, [1, 2], [3]])
+    if what.endswith("grad"):
+        g = lambda rows: [2 * r + d for r in rows for d in (0, 1)]
+        return group_rel_err(a, ref, [g([0]), g([1, 2]), g([3]), g(sp)])
+    if what.endswith("V"):
+        return group_rel_err(a, ref, [[0], [1, 2], [3], [4], [5], [6], list(range(7, 7 + Ns))])
+    return vec_rel_err(a, ref)
+
+
 def vec_rel_err(a, ref):
     """Per-variable vector-relative error  max_p|a-ref| / max_p|ref|  (columns = variables)."""
     a = np.asarray(a, dtype=np.float64).reshape(ref.shape[0], -1)
