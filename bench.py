@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""bench.py — edge-flux + source updates/s of the reactive residual hot path on B200 (BASELINE.json metric).
+
+Own arm (default):   python bench.py --gpus N --steps K --warmup W      (N>1 under torchrun, one rank per GPU)
+  workload = BASELINE.json configs[1]: laminar multispecies reactive NS, shipped 9-species mechanism, synthetic
+  triangulated 2-D channel of 1415x1415 points per GPU (4.0M cells, 2.0M points, 6.0M edges), explicit 3-stage RK,
+  AUSM 1st order + Stefan-Maxwell viscous flux + Arrhenius source, WLS gradients.  One step = one solver iteration
+  (MultiGrid_Cycle: 3 RK stages of preprocess/gradients/time step/residual/BCs/update + the Output preprocessing pass).
+  Units of work per step = nRK * (interior edges + owned points)   [edge-flux updates + source-point updates].
+Reference arm:       python bench.py --impl reference --steps K --warmup W
+  the reference's own CPU classes (oracle/_ref/ref_harness, compiled from the reference sources) on the same workload
+  shape at a bounded size, one serial process per host core (no MPI runtime on the box), aggregate throughput.
+"""
+import argparse
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "development-of-a-turbulent-numerical-solver-for-reactive-flows-in-su2_b200"
+RK_ALPHA = [0.66667, 0.66667, 1.0]
+METRIC = "edge-flux+source updates/s"
+REF_CASE = os.path.join(ROOT, "oracle", "_ref", "cases", "bench_ref")
+HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu):
+        self.gpu = gpu; self.p = None; self.lines = []
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.p.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+                for n, v in zip(names, f[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def run_reference(steps, warmup, procs=None):
+    """Times oracle/_ref/ref_harness (the reference's CReactiveNSSolver & co.) on the bounded bench case."""
+    if not (os.path.exists(HARNESS) and os.path.isdir(REF_CASE)):
+        return None
+    procs = procs or min(os.cpu_count() or 1, 64)
+    nit = warmup + steps
+    tmp = tempfile.mkdtemp(prefix="rxref_")
+    ps = []
+    for k in range(procs):
+        d = os.path.join(tmp, "p%d" % k)
+        shutil.copytree(REF_CASE, d)
+        ps.append(subprocess.Popen([HARNESS, "case.cfg", str(nit), "dump", str(10 ** 9), "11"], cwd=d, stdout=subprocess.PIPE,
+                                   stderr=subprocess.STDOUT, text=True))
+    times, counts = [], None
+    for p in ps:
+        out = p.communicate()[0]
+        t = [float(m.group(1)) for m in re.finditer(r"HARNESS_TIME it \d+ flow_seconds ([0-9.eE+-]+)", out)]
+        if p.returncode != 0 or len(t) < nit:
+            shutil.rmtree(tmp, ignore_errors=True)
+            raise RuntimeError("reference harness failed:\n" + out[-2000:])
+        times.append(t[warmup:])
+    meta = json.load(open(os.path.join(tmp, "p0", "dump", "meta.json")))
+    shutil.rmtree(tmp, ignore_errors=True)
+    nE, nP = meta["nEdge"], meta["nPointDomain"]
+    units = len(RK_ALPHA) * (nE + nP)
+    per_proc = [units * steps / sum(t) for t in times]
+    ms = 1e3 * max(sum(t) for t in times) / steps
+    return dict(value=float(sum(per_proc)), cores=procs, ms_per_step=ms, nEdge=nE, nPoint=nP,
+                sample="%d independent serial reference processes (no MPI runtime on the box), each the 3-stage-RK laminar reactive NS "
+                       "iteration on a %d-point / %d-edge triangulated channel, %d timed iterations; aggregate updates/s" % (procs, nP, nE, steps))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--nx", type=int, default=1415)
+    ap.add_argument("--ny", type=int, default=1415)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    W = max(a.warmup, 0); K = max(a.steps, 1)
+    workload = "laminar reactive NS (9 species, 2 reactions), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + Arrhenius source, WLS gradients"
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        r = run_reference(K, W)
+        if r is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_harness or its case directory is missing (run oracle/build_ref.sh and oracle/make_golden.py in the build container)"}))
+            return
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "updates/s", "n_gpus": a.gpus, "steps": K, "warmup": W,
+            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload, "points": r["nPoint"], "edges": r["nEdge"], "rk_stages": len(RK_ALPHA)},
+            "cpu_baseline": {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import importlib
+    import torch
+    pk = importlib.import_module(PKG)
+    par = importlib.import_module(PKG + ".parallel")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    chem = pk.load_mechanism()
+    opts = pk.default_opts(rans=False, cfl=0.1)
+    nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
+    if world > 1:
+        mesh, plan = pk.channel_strip_mesh(nxg, a.ny, rank, world)
+    else:
+        mesh = pk.channel_mesh(a.nx, a.ny); plan = dict(send={}, recv={}, bbox=None)
+    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=False, glob_xy=plan.get("bbox"))
+    solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
+    ex = par.HaloExchanger(par.GpuHaloState(solver), plan, dev)
+    nOwn, nE = solver.nPointDomain, solver.nEdge
+    own = np.zeros(solver.nPoint, dtype=bool); own[:nOwn] = True
+    en = mesh["edgeNodes"]
+    # an edge shared with a neighbour partition is counted once (by the owner of its first node)
+    nE_counted = int(own[en[:, 0]].sum())
+    units_local = len(RK_ALPHA) * (nE_counted + nOwn)
+    Uh = torch.empty((solver.nPoint, solver.nVar), dtype=torch.float64).pin_memory()
+    Uh.numpy()[:] = U0
+    solver.SetSolutionPtr(Uh.data_ptr()); solver.SetTemperature(T0); solver.SetTurbulence(turb)
+
+    def step(it, want_rms=False):
+        if world > 1:
+            return par.distributed_iterate(solver, ex, it, RK_ALPHA, last_rms=want_rms)
+        return solver.Iterate(it, RK_ALPHA, want_rms=want_rms)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    it = 1
+    for _ in range(max(W, 3)):
+        step(it); it += 1
+    l0 = solver.LaunchCount()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step(it); it += 1
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1) / K
+    clocks = sampler.stop()
+    launches = solver.LaunchCount() - l0
+    rms = step(it, want_rms=True); it += 1
+    if not np.all(np.isfinite(rms)):
+        raise SystemExit("bench.py: non-finite residual after the timed region")
+
+    # end to end through the public call with HOST buffers: H2D of the conserved state from pinned memory (rx_set_solution),
+    # the iteration, D2H of the residual norms (the step's result)
+    solver.SetTemperature(T0)
+    for _ in range(2):
+        solver.SetSolutionPtr(Uh.data_ptr()); ex.exchange(par.WHAT_SOLUTION); step(it, want_rms=True)
+    barrier()
+    t0 = time.perf_counter()
+    Ke = max(3, min(K, 10))
+    for _ in range(Ke):
+        solver.SetSolutionPtr(Uh.data_ptr())
+        if world > 1:
+            ex.exchange(par.WHAT_SOLUTION)
+        r = step(it, want_rms=True)
+    barrier()
+    ms_e2e = 1e3 * (time.perf_counter() - t0) / Ke
+
+    # dominant kernel: fused AUSM + viscous (Stefan-Maxwell) edge flux, timed alone with CUDA events on the launching stream
+    kt = {n: solver.KernelTime(w, 5) for n, w in [("edge_flux_fused", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("gradient", 4), ("update", 6)]}
+    tt = torch.tensor([ms_dev, ms_e2e, float(units_local)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_dev, ms_e2e, units = float(mx[0]), float(mx[1]), float(sm[2])
+    else:
+        units = float(units_local)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    # algorithmic bytes of the fused edge kernel: SURVEY.md §8(d) "fused conv+visc" = 24 B/edge + (400 + 104) B/point / (E/P)
+    bytes_per_edge = 24.0 + (400.0 + 104.0) / (nE / float(nOwn))
+    ach = bytes_per_edge * nE / (kt["edge_flux_fused"] * 1e-3) / 1e9
+    bytes_conv = 24.0 + (128.0 + 104.0) / (nE / float(nOwn))
+    line = {
+        "metric": METRIC, "value": units / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload, "points_per_gpu": nOwn, "edges_per_gpu": nE, "cells_per_gpu": 2 * (a.nx - 1) * (a.ny - 1), "rk_stages": len(RK_ALPHA),
+                   "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (solver.nPoint * 8 * 160 / 1e9),
+                   "partition": "strips in x, one halo layer, NCCL send/recv of U and gradients" if world > 1 else "single partition"},
+        "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": int(solver.nPoint * solver.nVar * 8), "d2h_bytes_per_step": int(solver.nVar * 8)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"kernel": "k_edge_flux<9,conv,visc> (AUSM + Stefan-Maxwell/BiCGSTAB viscous flux, one thread per edge)",
+                     "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
+                     "note": "FP64-pipe bound, not HBM bound (about 1e4 FP64 operations and ~200 divisions per edge): see DESIGN.md; the convective-only edge kernel is the HBM-bound one",
+                     "conv_only": {"achieved": bytes_conv * nE / (kt["edge_flux_conv"] * 1e-3) / 1e9, "frac": bytes_conv * nE / (kt["edge_flux_conv"] * 1e-3) / 1e9 / hbm}},
+        "kernel_ms": kt,
+    }
+    if world == 1 and not a.no_cpu_baseline:
+        try:
+            r = run_reference(2, 1)
+            if r:
+                line["cpu_baseline"] = {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"]}
+        except Exception as e:   # the baseline is a reported number, never a reason to lose the GPU line
+            line["cpu_baseline"] = {"value": None, "unit": "updates/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % str(e)[:200]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

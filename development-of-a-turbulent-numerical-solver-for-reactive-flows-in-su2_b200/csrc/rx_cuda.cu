@@ -369,9 +369,62 @@ int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   return RX_OK;
 }
 
-int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, double* resRms) {
+int rx_residual_all(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
+  if (c->o.viscous) {
+    k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    c->launches += 2;
+  } else {
+    k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    c->launches += 3;
+  }
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+
+// average device time (ms, CUDA events on the context's stream) of `reps` launches of one kernel of the path, on the
+// context's current state.  which: 0 fused edge flux (AUSM + viscous), 1 convective edge flux only, 2 owner-computes
+// accumulation + source, 3 cons->prim + transport, 4 gradient, 5 source only, 6 explicit update.
+int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  cudaEvent_t e0, e1;
+  RX_CK(cudaEventCreate(&e0)); RX_CK(cudaEventCreate(&e1));
+  for (int pass = 0; pass < 2; ++pass) {   // pass 0 = warm-up
+    const int n = pass == 0 ? 1 : reps;
+    RX_CK(cudaEventRecord(e0, s));
+    for (int r = 0; r < n; ++r) {
+      switch (which) {
+        case 0: if (c->o.viscous) k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+                else k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
+        case 1: k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
+        case 2: if (c->o.viscous) k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+                else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
+        case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;
+        case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+                else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
+        case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
+        case 6: k_update<9><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial); break;
+        default: cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: unknown kernel id"; return RX_ERR_ARG;
+      }
+      c->launches++;
+    }
+    RX_CK(cudaEventRecord(e1, s));
+    RX_CK(cudaEventSynchronize(e1));
+    RX_CK(cudaGetLastError());
+    float ms = 0.f;
+    RX_CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (pass == 1 && msAvg) *msAvg = (double)ms / n;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return RX_OK;
+}
+
+int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, double* resRms) {
   int rc;
   for (int rk = 0; rk < nRK; ++rk) {
     if ((rc = rx_preprocess(c, extIter, 0, nullptr))) return rc;
@@ -379,17 +432,7 @@ int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, doubl
       if ((rc = rx_set_old_solution(c))) return rc;
       if ((rc = rx_time_step(c))) return rc;
     }
-    if (c->o.viscous) {
-      k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
-      k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-      c->launches += 2;
-    } else {
-      k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
-      k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-      k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
-      c->launches += 3;
-    }
-    RX_CK(cudaGetLastError());
+    if ((rc = rx_residual_all(c))) return rc;
     if ((rc = rx_bc(c))) return rc;
     if ((rc = rx_update_explicit(c, rkAlpha ? rkAlpha[rk] : 1.0, (rk == nRK - 1) ? resRms : nullptr))) return rc;
   }

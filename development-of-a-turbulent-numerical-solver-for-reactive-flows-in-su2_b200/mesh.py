@@ -179,3 +179,70 @@ def partition_strips(mesh, nParts):
     for p in parts:
         p.pop("halo_glob"); p.pop("owner")
     return parts
+
+
+def channel_strip_mesh(nxg, ny, rank, nranks, L=0.25, H=0.025, stretch=1.0, Ns=9, oxidizer=2):
+    """Local mesh of rank `rank` for a strip partition in x of the global nxg x ny channel, built WITHOUT the global mesh
+    (weak scaling: every rank builds only its own strip).  SU2's scheme: owned points first, then one
+    halo layer (left neighbour's column, then right neighbour's); every edge with at least one owned end is kept; boundary
+    vertices only on owned points.  Returns (mesh, plan) with plan = dict(send={rank: local ids}, recv={rank: local ids},
+    glob=(global i, j) of the local points, bbox=global bounding box); send/recv orders match (ascending j)."""
+    c0 = (nxg * rank) // nranks; c1 = (nxg * (rank + 1)) // nranks
+    hl = 1 if rank > 0 else 0; hr = 1 if rank < nranks - 1 else 0
+    a0, a1 = c0 - hl, c1 + hr                      # local column range incl. halos
+    nxl = a1 - a0
+    xs = np.linspace(0.0, L, nxg)[a0:a1]
+    t = np.linspace(0.0, 1.0, ny)
+    if stretch != 1.0:
+        t = 0.5 * (1.0 + np.tanh(stretch * (2 * t - 1)) / np.tanh(stretch))
+    X, Y = np.meshgrid(xs, H * t)
+    coord = np.stack([X.ravel(), Y.ravel()], axis=1)            # local id = j*nxl + il
+    i, j = np.meshgrid(np.arange(nxl - 1), np.arange(ny - 1)); i = i.ravel(); j = j.ravel()
+    a = j * nxl + i; b = a + 1; c = b + nxl; d = a + nxl
+    even = (((i + a0) + j) % 2) == 0                            # diagonal parity of the GLOBAL grid
+    tri = np.empty((2 * len(a), 3), dtype=np.int64)
+    tri[0::2] = np.where(even[:, None], np.stack([a, b, c], 1), np.stack([a, b, d], 1))
+    tri[1::2] = np.where(even[:, None], np.stack([a, c, d], 1), np.stack([b, c, d], 1))
+    jj = np.arange(ny - 1); ii = np.arange(nxl - 1)
+    bnd = []
+    bnd.append(("inlet", np.stack([(jj + 1) * nxl, jj * nxl], 1) if rank == 0 else np.zeros((0, 2), dtype=np.int64)))
+    bnd.append(("outlet", np.stack([jj * nxl + nxl - 1, (jj + 1) * nxl + nxl - 1], 1) if rank == nranks - 1 else np.zeros((0, 2), dtype=np.int64)))
+    bnd.append(("lower_wall", np.stack([ii, ii + 1], 1)))
+    bnd.append(("upper_wall", np.stack([(ny - 1) * nxl + ii + 1, (ny - 1) * nxl + ii], 1)))
+    m = dual_mesh(coord, tri, bnd)
+    il = np.tile(np.arange(nxl), ny); jl = np.repeat(np.arange(ny), nxl)
+    owned = (il >= hl) & (il < nxl - hr)
+    left = il < hl; right = il >= nxl - hr
+    order = np.concatenate([np.flatnonzero(owned), np.flatnonzero(left), np.flatnonzero(right)])   # new -> old
+    o2n = np.empty(nxl * ny, dtype=np.int64); o2n[order] = np.arange(nxl * ny)
+    nOwn = int(owned.sum())
+    ei, ej = m["edgeNodes"][:, 0], m["edgeNodes"][:, 1]
+    keep = owned[ei] | owned[ej]
+    # keep the edge orientation (normal points from first to second node); only the numbering changes
+    mesh = dict(nPoint=nxl * ny, nPointDomain=nOwn, nEdge=int(keep.sum()),
+                edgeNodes=np.stack([o2n[ei[keep]], o2n[ej[keep]]], 1), edgeNormal=m["edgeNormal"][keep],
+                coord=m["coord"][order], volume=m["volume"][order])
+    cnt = (m["nbPtr"][1:] - m["nbPtr"][:-1])[order]
+    nbPtr = np.zeros(nxl * ny + 1, dtype=np.int64); np.cumsum(cnt, out=nbPtr[1:])
+    starts = m["nbPtr"][:-1][order]
+    idx = np.repeat(starts - nbPtr[:-1], cnt) + np.arange(nbPtr[-1])
+    mesh["nbPtr"] = nbPtr; mesh["nbPoint"] = o2n[m["nbPoint"][idx]]
+    mk = []
+    for q in m["markers"]:
+        sel = owned[q["node"]] if len(q["node"]) else np.zeros(0, dtype=bool)
+        mk.append(dict(tag=q["tag"], kind=0, node=o2n[q["node"][sel]], normalNeighbor=o2n[q["normalNeighbor"][sel]], normal=q["normal"][sel]))
+    ys = np.zeros(Ns); ys[oxidizer] = 1.0
+    mk[0].update(kind=KIND_INLET, T=300.0, Vmag=20.0, dir=[1.0, 0.0], Ys=ys)
+    mk[1].update(kind=KIND_OUTLET, P=101325.0)
+    mk[2].update(kind=KIND_ISOTHERMAL, Twall=600.0)
+    mk[3].update(kind=KIND_ISOTHERMAL, Twall=300.0)
+    mesh["markers"] = mk
+    send, recv = {}, {}
+    if hl:
+        send[rank - 1] = o2n[np.flatnonzero(il == hl)]          # my first owned column, ascending j
+        recv[rank - 1] = o2n[np.flatnonzero(left)]
+    if hr:
+        send[rank + 1] = o2n[np.flatnonzero(il == nxl - hr - 1)]
+        recv[rank + 1] = o2n[np.flatnonzero(right)]
+    plan = dict(send=send, recv=recv, glob=(il[order] + a0, jl[order]), bbox=(0.0, L, 0.0, H))
+    return mesh, plan

@@ -70,7 +70,7 @@ class _Opts(C.Structure):
 EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "rx_set_stream", "rx_synchronize",
            "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
-           "rx_residual_source", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
+           "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count"]
 
 _lib = None
@@ -163,6 +163,10 @@ class CReactiveNSSolverGPU:
 
     # ---- mirrors of node[]->Solution / Primitive / LinSysRes
     def SetSolution(self, U): self._ck(self.lib.rx_set_solution(self.ctx, _d(_c(U))))
+
+    def SetSolutionPtr(self, host_ptr):
+        """Same, from a raw host address (e.g. a pinned torch tensor's data_ptr())."""
+        self._ck(self.lib.rx_set_solution(self.ctx, C.c_void_p(host_ptr)))
     def SetTemperature(self, T): self._ck(self.lib.rx_set_temperature(self.ctx, _d(_c(T))))
     def SetTurbulence(self, t6): self._ck(self.lib.rx_set_turbulence(self.ctx, _d(_c(t6))))
 
@@ -190,7 +194,13 @@ class CReactiveNSSolverGPU:
     def Upwind_Residual(self): self._ck(self.lib.rx_residual_conv(self.ctx))
     def Viscous_Residual(self): self._ck(self.lib.rx_residual_visc(self.ctx))
     def Source_Residual(self): self._ck(self.lib.rx_residual_source(self.ctx))
+    def Residual_All(self): self._ck(self.lib.rx_residual_all(self.ctx))
     def BC_All(self): self._ck(self.lib.rx_bc(self.ctx))
+
+    def KernelTime(self, which, reps=5):
+        ms = C.c_double(0.0)
+        self._ck(self.lib.rx_kernel_time(self.ctx, int(which), int(reps), C.byref(ms)))
+        return ms.value
 
     def ExplicitRK_Iteration(self, alpha, want_rms=True):
         rms = np.empty(self.nVar)
@@ -205,6 +215,14 @@ class CReactiveNSSolverGPU:
         a = _c(rk_alpha); rms = np.empty(self.nVar)
         self._ck(self.lib.rx_iterate(self.ctx, C.c_int64(ExtIter), len(a), _d(a), _d(rms) if want_rms else None))
         return rms if want_rms else None
+
+    def HaloWidth(self, what): return int(self.lib.rx_halo_width(self.ctx, int(what)))
+
+    def HaloPack(self, what, n, ids_dev_ptr, buf_dev_ptr):
+        self._ck(self.lib.rx_halo_pack(self.ctx, int(what), C.c_int64(n), C.c_void_p(ids_dev_ptr), C.c_void_p(buf_dev_ptr)))
+
+    def HaloUnpack(self, what, n, ids_dev_ptr, buf_dev_ptr):
+        self._ck(self.lib.rx_halo_unpack(self.ctx, int(what), C.c_int64(n), C.c_void_p(ids_dev_ptr), C.c_void_p(buf_dev_ptr)))
 
     def Synchronize(self): self._ck(self.lib.rx_synchronize(self.ctx))
     def LaunchCount(self): return int(self.lib.rx_launch_count(self.ctx))

@@ -109,6 +109,8 @@ int rx_residual_source(rx_ctx*);                          /* Source_Residual :27
 int rx_bc(rx_ctx*);                                       /* BC_Inlet :3226, BC_Outlet :3808, then BC_Isothermal_Wall :5393 (integration_structure.cpp:89-190) */
 int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */
 
+int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + Source residual in one pass (same sums, same order) */
+
 /* one full MultiGrid_Cycle (integration_time.cpp:143-181) with everything resident: for each RK stage
  * preprocess -> (stage 0: set_old, time_step) -> fused conv+visc+source residual -> bc -> update; then the Output
  * preprocess pass (integration_time.cpp:110-112).  resRms may be NULL. */
@@ -127,6 +129,11 @@ int rx_source_points_dev(rx_ctx*, int64_t n, const double* T_dev, const double* 
 int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double* buf_dev);
 int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);
 int rx_halo_width(rx_ctx*, int what);
+
+/* measurement hook: average device time in ms (CUDA events on the context's stream) of `reps` launches of one kernel on the
+ * current state; which = 0 fused edge flux, 1 convective edge flux, 2 accumulation+source, 3 cons->prim+transport,
+ * 4 gradient, 5 source, 6 explicit update */
+int rx_kernel_time(rx_ctx*, int which, int reps, double* msAvg);
 
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t rx_launch_count(rx_ctx*);

@@ -163,8 +163,22 @@ def run_case(name):
     shutil.rmtree(out, ignore_errors=True)
 
 
+def prepare_bench_case(nx=101, ny=101):
+    """Case directory for `bench.py --impl reference` / cpu_baseline: the bench workload (laminar reactive NS, 3-stage RK,
+    WLS gradients, AUSM 1st order) at a size the serial CPU reference finishes in seconds per iteration."""
+    d = prepare_case_dir("bench_ref", nx=nx, ny=ny, stretch=1.0)
+    derive_cfg(os.path.join(SHIPPED, "my_combustion_first_chem_PaSR.cfg"), os.path.join(d, "case.cfg"),
+               dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="100000", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                    TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.1"))
+    print("prepared %s" % d)
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["bench_ref"]:
+        prepare_bench_case()
+        sys.exit(0)
     names = sys.argv[1:] or list(SPECS)
     for n in names:
         print("== %s" % n)
         run_case(n)
+    prepare_bench_case()

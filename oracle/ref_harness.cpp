@@ -20,6 +20,7 @@
 #include <vector>
 #include <sstream>
 #include <sys/stat.h>
+#include <time.h>
 
 static std::string g_out;
 
@@ -407,6 +408,7 @@ int main(int argc, char** argv) {
   std::vector<double> hist;
   for (unsigned long it = 0; it < nIter; ++it) {
     bool dmp = it >= dump_from;
+    struct timespec ts0, ts1; clock_gettime(CLOCK_MONOTONIC, &ts0);
     drv->PreprocessExtIter(it);
     c.cfg->SetGlobalParam(kind, RUNTIME_REACTIVE_SYS, it);
     if (dmp) {
@@ -442,6 +444,8 @@ int main(int argc, char** argv) {
     }
     c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
     if (dmp) dump_primitive(c, tag(it, 0, "out_"));
+    clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
+    printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {
       c.cfg->SetGlobalParam(REACTIVE_RANS, RUNTIME_TURB_SYS, it);
       drv->integration_container[ZONE_0][TURB_SOL]->SingleGrid_Iteration(drv->geometry_container, drv->solver_container,
