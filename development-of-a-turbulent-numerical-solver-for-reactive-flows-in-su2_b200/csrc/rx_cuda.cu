@@ -13,6 +13,8 @@
 
 using namespace rx;
 
+static constexpr size_t SM_VISC = (size_t)9 * 9 * EDGE_BS * sizeof(double);   // thread-private 9x9 matrices in shared memory
+
 static thread_local std::string g_create_error;
 
 struct rx_ctx {
@@ -194,7 +196,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.U = dalloc<double>(c, np * c->nVar); d.Uold = dalloc<double>(c, np * c->nVar); d.R = dalloc<double>(c, np * c->nVar);
   d.V = dalloc<double>(c, np * c->nPrim); d.X = dalloc<double>(c, np * Ns);
   d.Cp = dalloc<double>(c, np); d.gam = dalloc<double>(c, np); d.mu = dalloc<double>(c, np); d.kap = dalloc<double>(c, np);
-  d.T175 = dalloc<double>(c, np); d.Patm = dalloc<double>(c, np);
+  d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
   d.turb = dalloc<double>(c, np * 6); d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
@@ -329,7 +331,7 @@ int rx_residual_conv(rx_ctx* c) {
 int rx_residual_visc(rx_ctx* c) {
   if (!c->o.viscous) return RX_OK;
   const Dev& d = c->d;
-  k_edge_flux<9, false, true><<<nblk(d.nEdge, 64), 64, 0, c->stream>>>(c->cc9, c->o, d);
+  k_edge_flux<9, false, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, c->stream>>>(c->cc9, c->o, d);
   k_accumulate<9, 2><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
   c->launches += 2;
   RX_CK(cudaGetLastError());
@@ -347,8 +349,8 @@ int rx_bc(rx_ctx* c) {
   cudaStream_t s = c->stream;
   for (const MarkerDev& m : c->markers) {
     if (!m.nVertex) continue;
-    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
-    else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
+    else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
   }
   for (const MarkerDev& m : c->markers)
     if (m.nVertex && m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
@@ -359,7 +361,7 @@ int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
   k_update<9><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial);
-  k_rms_finish<<<1, 32, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
+  k_rms_finish<<<c->nVar, 256, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
   c->launches += 2;
   RX_CK(cudaGetLastError());
   if (resRms) {
@@ -373,7 +375,7 @@ int rx_residual_all(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
   if (c->o.viscous) {
-    k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    k_edge_flux<9, true, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d);
     k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
     c->launches += 2;
   } else {
@@ -399,7 +401,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
     RX_CK(cudaEventRecord(e0, s));
     for (int r = 0; r < n; ++r) {
       switch (which) {
-        case 0: if (c->o.viscous) k_edge_flux<9, true, true><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+        case 0: if (c->o.viscous) k_edge_flux<9, true, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d);
                 else k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
         case 1: k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
         case 2: if (c->o.viscous) k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);

@@ -117,11 +117,19 @@ RX_HD int bicgstab(MatF A, const double* rhs, double* x) {
 // Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) for `nrhs` right-hand sides (externals/Eigen/src/QR/ColPivHouseholderQR.h,
 // Householder/Householder.h).  Same pivot rule, rank threshold and norm down-dating; natural summation order.
 // A is N x N column-major in caller-provided scratch (destroyed); b/x are [nrhs][N].
-template <int N, int NRHS>
+// Strided view of one column of a thread-private matrix: element i lives at base[i*S] (S = 1 for local memory,
+// S = block size for the shared-memory layout in which consecutive threads own consecutive 8-byte words).
+template <int S>
+struct ColView {
+  double* p;
+  RX_HD double& operator[](int i) const { return p[i * S]; }
+  RX_HD ColView operator+(int k) const { return ColView{p + k * S}; }
+};
+template <int N, int NRHS, int S>
 RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
   double hC[N], nU[N], nD[N];
   int trans[N];
-  auto col = [&](int j) { return A + j * N; };
+  auto col = [&](int j) { return ColView<S>{A + j * N * S}; };
   for (int k = 0; k < N; ++k) {
     double s = 0.0;
     for (int i = 0; i < N; ++i) s += col(k)[i] * col(k)[i];
@@ -144,7 +152,7 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
       double tmp = nU[k]; nU[k] = nU[big]; nU[big] = tmp;
       tmp = nD[k]; nD[k] = nD[big]; nD[big] = tmp;
     }
-    double* v = col(k) + k;
+    const ColView<S> v = col(k) + k;
     const int m = N - k;
     double tailSq = 0.0;
     for (int i = 1; i < m; ++i) tailSq += v[i] * v[i];
@@ -165,7 +173,7 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
       for (int j = k + 1; j < N; ++j) col(j)[k] *= (1.0 - tau);
     } else if (tau != 0.0) {
       for (int j = k + 1; j < N; ++j) {
-        double* w = col(j) + k;
+        const ColView<S> w = col(j) + k;
         double t = 0.0;
         for (int i = 1; i < m; ++i) t += v[i] * w[i];
         t += w[0];
@@ -197,7 +205,7 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
     for (int i = 0; i < N; ++i) c[i] = b[q][i];
     for (int k = 0; k < nonzero; ++k) {
       const int m = N - k;
-      const double* v = col(k) + k;
+      const ColView<S> v = col(k) + k;
       const double tau = hC[k];
       double* w = c + k;
       if (m == 1) w[0] *= (1.0 - tau);
@@ -225,15 +233,18 @@ struct ViscEnd {
   double V[7 + NS];
   double g[(4 + NS) * 2];   // rows [T,u,v,P,X_s] x 2 — filled only where needed
   double X[NS];             // mole fractions of the end state (GetMolarFromMass of V[Y])
-  double mu, kap, T175, Patm;  // T175 = 1e-3*pow(T,1.75) and P/101325 of the point that owns the D_ij (GetDij_SM :751-766)
+  double mu, kap;
+  double rD[NS * (NS + 1) / 2];   // 1/D_st of the point that owns the binary diffusion coefficients, upper triangle s <= t
   double muT, ke, gk[2], x[2];
 };
 
 // CAvgGradReactive_Flow::ComputeResidual (numerics_direct_reactive.cpp:1425-1573) / _Boundary::ComputeResidual (:478-553),
 // SetLaminarTensorFlux (:1099-1190), Solve_SM (:451-470) with GetGamma (reacting_model_library.cpp:771-798),
 // SST_Reactive_ResidualClosure (:656-852), Get_Molar2MassGrad_Operator (:861-880).
-// `scratch` must hold NS*NS doubles (the S–M matrix, then the molar->mass operator); it may be local or shared memory.
-template <int NS, bool EDGE>
+// `scratch` holds NS*NS doubles with element k at scratch[k*S] (the S–M matrix, then the molar->mass operator): S = 1 for a
+// thread-local array, S = block size for the shared-memory layout.
+RX_HD constexpr int tri_idx(int NS, int s, int t) { return s * NS - s * (s - 1) / 2 + (t - s); }   // s <= t
+template <int NS, bool EDGE, int S>
 RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I, const ViscEnd<NS>& J, double nx, double ny,
                         double sigma_k, double* scratch, double* res) {
   constexpr int NA = 3 + NS;
@@ -293,38 +304,46 @@ RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I
 #pragma unroll
     for (int s = 0; s < NS; ++s) gxn[s] += G[3 + s][i] * nrm[i];
   }
-  // ---- Stefan–Maxwell system: mean D_ij (harmonic, element-wise :1447), Gamma (:771-798), Gamma_tilde (:463-465)
+  // ---- Stefan–Maxwell system: mean D_ij (harmonic, element-wise :1447), Gamma (:771-798), Gamma_tilde (:463-465).
+  // D and Gamma's D-dependent terms are symmetric bit for bit, so each unordered pair is evaluated once; the diagonal sums
+  // tmp_i = sum_{k != i} X_k/D_ik still accumulate in ascending k (pairs (k,i), k < i, are met before pairs (i,j), j > i).
   {
-    double* Gam = scratch;   // column-major like Eigen::MatrixXd
+    double* Gam = scratch;   // column-major like Eigen::MatrixXd: Gam(r,c) at scratch[(c*NS + r)*S]
     double sigma = 0.0, massTot = 0.0;
 #pragma unroll
     for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
 #pragma unroll
     for (int s = 0; s < NS; ++s) massTot += Ys[s] / cc.M[s];
     massTot = 1.0 / massTot;
-    double maxD = 0.0;
-    // D_i(s,t) = 1e-3*T_i^1.75/(Patm_i*Mij*(dv)*(dv)) / 1e4  (GetDij_SM; variable_direct_reactive.cpp:1212)
+    double maxD = 0.0, tmp[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) tmp[s] = 0.0;
+    const double sm = -sigma * massTot;
+#pragma unroll
     for (int i = 0; i < NS; ++i) {
-      double tmp = 0.0;   // diagonal accumulation sum_{k != i} X_k / D_ik, in k order
-      for (int j = 0; j < NS; ++j) {
-        const double di = (I.T175 / (I.Patm * cc.Mij[i][j] * cc.dvs[i][j] * cc.dvs[i][j])) / (1.0 * 1.0 * 1.0e4);
-        const double dj = (J.T175 / (J.Patm * cc.Mij[i][j] * cc.dvs[i][j] * cc.dvs[i][j])) / (1.0 * 1.0 * 1.0e4);
-        const double dm = 2.0 / (1.0 / di + 1.0 / dj);
+#pragma unroll
+      for (int j = i; j < NS; ++j) {
+        const double dm = 2.0 / (I.rD[tri_idx(NS, i, j)] + J.rD[tri_idx(NS, i, j)]);   // 2/(1/D_i + 1/D_j)
         maxD = fmax(maxD, dm);
         if (j != i) {
-          Gam[j * NS + i] = -sigma * massTot * Xs[i] / (rho * cc.M[j] * dm);
-          tmp += Xs[j] / dm;
+          Gam[(j * NS + i) * S] = sm * Xs[i] / (rho * cc.M[j] * dm);
+          Gam[(i * NS + j) * S] = sm * Xs[j] / (rho * cc.M[i] * dm);
+          tmp[i] += Xs[j] / dm;
+          tmp[j] += Xs[i] / dm;
         }
       }
-      Gam[i * NS + i] = sigma * massTot * tmp / (rho * cc.M[i]);
     }
     const double alpha = 1.0 / (rho * maxD);
-    for (int i = 0; i < NS; ++i)
-      for (int j = 0; j < NS; ++j) Gam[j * NS + i] = Gam[j * NS + i] + alpha * Ys[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) Gam[(i * NS + i) * S] = sigma * massTot * tmp[i] / (rho * cc.M[i]);
+    for (int i = 0; i < NS; ++i) {
+      const double ay = alpha * Ys[i];
+      for (int j = 0; j < NS; ++j) Gam[(j * NS + i) * S] = Gam[(j * NS + i) * S] + ay;
+    }
     double rhs[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) rhs[s] = -gxn[s];
-    bicgstab<NS>([&](int r, int c) { return Gam[c * NS + r]; }, rhs, Jd);
+    bicgstab<NS>([&](int r, int c) { return Gam[(c * NS + r) * S]; }, rhs, Jd);
   }
   Proj[U_RHO] = -eig_redux<NS, false>(Jd);
 #pragma unroll
@@ -353,13 +372,13 @@ RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I
     double* Mt = scratch;
     for (int i = 0; i < NS; ++i)
       for (int j = 0; j < NS; ++j)
-        Mt[j * NS + i] = (i == j) ? cc.Mtot / cc.M[i] * (Ys[i] - Xs[i] + sig) * 1.0 + cc.Mtot * (Ys[i] / cc.M[i] - Xs[i] / cc.M[j]) * 0.0
+        Mt[(j * NS + i) * S] = (i == j) ? cc.Mtot / cc.M[i] * (Ys[i] - Xs[i] + sig) * 1.0 + cc.Mtot * (Ys[i] / cc.M[i] - Xs[i] / cc.M[j]) * 0.0
                                   : cc.Mtot / cc.M[i] * (Ys[i] - Xs[i] + sig) * 0.0 + cc.Mtot * (Ys[i] / cc.M[i] - Xs[i] / cc.M[j]) * 1.0;
 #pragma unroll
     for (int d = 0; d < 2; ++d)
 #pragma unroll
       for (int s = 0; s < NS; ++s) rhsq[d][s] = G[3 + s][d];
-    colpiv_qr_solve<NS, 2>(Mt, rhsq, MG);
+    colpiv_qr_solve<NS, 2, S>(Mt, rhsq, MG);
 #pragma unroll
     for (int d = 0; d < 2; ++d)
 #pragma unroll

@@ -17,7 +17,7 @@ struct Dev {   // device pointers + sizes, passed by value to kernels
   const int *nbPtr, *nbIdx;        // neighbour CSR (WLS gradient), reference order
   const int *incPtr, *incEdge;     // incident-edge CSR in ascending edge order; entry = e (point is node 0) or ~e (node 1)
   // state
-  double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *T175, *Patm, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R;
+  double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *rD, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R;
   double *fluxC, *fluxV;
   int* nonPhys; unsigned long long* counters;   // counters[0] = non-physical points of the last preprocess
 };
@@ -77,8 +77,19 @@ __global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC
     double mu, ka;
     transport(cc, T, Y, mu, ka);
     d.mu[p] = mu; d.kap[p] = ka;
-    d.T175[p] = 1.0e-3 * pow175(T);                 // numerator of GetDij_SM (:751-766)
-    d.Patm[p] = V[V_P] * 1.0 / 101325.0;
+    // 1/D_st of this point, upper triangle (GetDij_SM :751-766; /(V_ref*L_ref*1e4) variable_direct_reactive.cpp:1212;
+    // cwiseInverse numerics_direct_reactive.cpp:1447).  Stored per point so that an edge needs one division per pair.
+    const double T175 = 1.0e-3 * pow175(T);
+    const double Patm = V[V_P] * 1.0 / 101325.0;
+    int q = 0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+#pragma unroll
+      for (int t = s; t < NS; ++t) {
+        const double D = (T175 / (Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t])) / (1.0 * 1.0 * 1.0e4);
+        d.rD[(size_t)q * d.np + p] = 1.0 / D;
+        ++q;
+      }
   }
   if (o.ignition && extIter < o.ignitionIter) {        // ignition hack: overwrite T only (:1013-1024)
     if (Y[o.fuelIndex] > 0.4 && Y[o.oxidizerIndex] > 0.2 && V[V_T] < o.ignitionT) V[V_T] = o.ignitionT;

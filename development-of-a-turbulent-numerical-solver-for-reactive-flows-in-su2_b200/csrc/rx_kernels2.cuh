@@ -18,15 +18,18 @@ __device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long 
   }
 #pragma unroll
   for (int s = 0; s < NS; ++s) E.X[s] = d.X[s * d.np + p];
-  E.mu = d.mu[p]; E.kap = d.kap[p]; E.T175 = d.T175[p]; E.Patm = d.Patm[p];
+  E.mu = d.mu[p]; E.kap = d.kap[p];
+#pragma unroll
+  for (int q = 0; q < NS * (NS + 1) / 2; ++q) E.rD[q] = d.rD[(size_t)q * d.np + p];
   E.x[0] = d.x[p]; E.x[1] = d.y[p];
   if (o.rans) { E.muT = d.turb[p]; E.ke = d.turb[d.np + p]; E.gk[0] = d.turb[3 * d.np + p]; E.gk[1] = d.turb[4 * d.np + p]; }
   else { E.muT = 1.0; E.ke = 0.0; E.gk[0] = E.gk[1] = 0.0; }
 }
 
 // ---- Upwind_Residual (:2535-2785, 1st order) and Viscous_Residual (:5305-5386): one thread per edge, flux to edge arrays
+constexpr int EDGE_BS = 64;   // threads per block of the edge / boundary flux kernels
 template <int NS, bool CONV, bool VISC>
-__global__ void __launch_bounds__(64) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+__global__ void __launch_bounds__(EDGE_BS) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= d.nEdge) return;
   constexpr int NV = 4 + NS;
@@ -42,9 +45,9 @@ __global__ void __launch_bounds__(64) k_edge_flux(const __grid_constant__ ChemC<
 #pragma unroll
       for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
     }
-    double scratch[NS * NS];
+    extern __shared__ double smat[];   // NS*NS doubles per thread, word k of thread t at smat[k*EDGE_BS + t]: conflict-free
     const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
-    viscous_flux<NS, true>(cc, o, I, J, nx, ny, sigma_k, scratch, res);
+    viscous_flux<NS, true, EDGE_BS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
 #pragma unroll
     for (int v = 0; v < NV; ++v) d.fluxV[v * d.ne + e] = res[v];
   } else {
@@ -146,9 +149,9 @@ __device__ __forceinline__ void boundary_fluxes(const ChemC<NS>& cc, const Opts&
     J = I;   // gradient, transport, D_ij and turbulence of iPoint on both sides (:3583-3665, :4001-4110)
 #pragma unroll
     for (int v = 0; v < 7 + NS; ++v) J.V[v] = Vg[v];
-    double scratch[NS * NS];
+    extern __shared__ double smat[];
     const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;
-    viscous_flux<NS, false>(cc, o, I, J, nx, ny, sigma_k, scratch, res);
+    viscous_flux<NS, false, EDGE_BS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
 #pragma unroll
     for (int v = 0; v < NV; ++v) r[v] = r[v] - res[v];
   }
@@ -298,14 +301,22 @@ __global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, doubl
     partial[(size_t)blockIdx.x * NV + v] = ((sh[0][v] + sh[1][v]) + (sh[2][v] + sh[3][v]));
   }
 }
-__global__ void k_rms_finish(const double* __restrict__ partial, int nBlocks, int nv, long long nPointGlobal, double* __restrict__ rms, double* __restrict__ sumsq) {
-  // one block, thread v sums its column in block order: fixed order => bit-reproducible run to run
-  const int v = threadIdx.x;
-  if (v >= nv) return;
+__global__ void __launch_bounds__(256) k_rms_finish(const double* __restrict__ partial, int nBlocks, int nv, long long nPointGlobal, double* __restrict__ rms, double* __restrict__ sumsq) {
+  // one block per variable; fixed strided partial sums + fixed tree => bit-reproducible run to run
+  const int v = blockIdx.x;
+  __shared__ double sh[256];
   double s = 0.0;
-  for (int b = 0; b < nBlocks; ++b) s += partial[(size_t)b * nv + v];
-  sumsq[v] = s;
-  rms[v] = fmax(EPS * EPS, sqrt(s / (double)nPointGlobal));   // CSolver::SetResidual_RMS, solver_structure.cpp:172-187
+  for (int b = threadIdx.x; b < nBlocks; b += 256) s += partial[(size_t)b * nv + v];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    sumsq[v] = sh[0];
+    rms[v] = fmax(EPS * EPS, sqrt(sh[0] / (double)nPointGlobal));   // CSolver::SetResidual_RMS, solver_structure.cpp:172-187
+  }
 }
 
 // ---- halo plumbing: gather/scatter listed points of U (what=0) or of [grad, X, V, transport] (what=1)
