@@ -2,6 +2,7 @@
 // Every entry point enqueues kernels on the context's stream; there is NO CPU fallback anywhere in this library.
 #include "../../include/rx_cuda.h"
 #include "rx_kernels2.cuh"
+#include "rx_visc_pair.cuh"
 
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -13,7 +14,8 @@
 
 using namespace rx;
 
-static constexpr size_t SM_VISC = (size_t)9 * 9 * EDGE_BS * sizeof(double);   // thread-private 9x9 matrices in shared memory
+static constexpr size_t SM_PAIR = (size_t)VP_SMW * VP_BS * sizeof(double);
+static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
 static thread_local std::string g_create_error;
 
@@ -135,6 +137,18 @@ int download_aos(rx_ctx* c, const double* soa, double* h, int nv) {
 }
 }  // namespace
 
+// launch of the edge-flux kernels.  Laminar viscous flux: the two-lanes-per-edge kernel (rx_visc_pair.cuh), with the AUSM
+// flux from its own bandwidth-bound kernel; RANS keeps the thread-per-edge kernel that also carries the SST closure.
+template <bool CONV, bool VISC>
+static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
+  const Dev& d = c->d;
+  if (!VISC) { k_edge_flux<9, CONV, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; return; }
+  if (c->o.rans) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
+  if (CONV) { k_edge_flux<9, true, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; }
+  k_edge_visc_pair<9><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
+  c->launches++;
+}
+
 extern "C" {
 
 int rx_supported_species(int Ns) { return Ns == 9; }
@@ -155,6 +169,15 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   rx_ctx* c = new rx_ctx();
   c->device = op->device;
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
+  {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
+    const int smv = (int)SM_VISC;
+    const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    cudaError_t e = cudaFuncSetAttribute(k_edge_flux<9, true, true, true>, at, smv);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_flux<9, false, true, true>, at, smv);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
+    if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }
+  }
   const int Ns = ch->Ns;
   c->Ns = Ns; c->nVar = Ns + 4; c->nPrim = Ns + 7; c->nGrad = Ns + 4;
   Opts& o = c->o;
@@ -322,18 +345,18 @@ int rx_time_step(rx_ctx* c) {
 
 int rx_residual_conv(rx_ctx* c) {
   const Dev& d = c->d;
-  k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, c->stream>>>(c->cc9, c->o, d);
+  launch_edge_flux<true, false>(c, c->stream);
   k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
-  c->launches += 2;
+  c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
 int rx_residual_visc(rx_ctx* c) {
   if (!c->o.viscous) return RX_OK;
   const Dev& d = c->d;
-  k_edge_flux<9, false, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, c->stream>>>(c->cc9, c->o, d);
+  launch_edge_flux<false, true>(c, c->stream);
   k_accumulate<9, 2><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
-  c->launches += 2;
+  c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
@@ -375,21 +398,21 @@ int rx_residual_all(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
   if (c->o.viscous) {
-    k_edge_flux<9, true, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d);
+    launch_edge_flux<true, true>(c, s);
     k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    c->launches += 2;
+    c->launches++;
   } else {
-    k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    launch_edge_flux<true, false>(c, s);
     k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
     k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    c->launches += 3;
+    c->launches += 2;
   }
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
 
 // average device time (ms, CUDA events on the context's stream) of `reps` launches of one kernel of the path, on the
-// context's current state.  which: 0 fused edge flux (AUSM + viscous), 1 convective edge flux only, 2 owner-computes
+// context's current state.  which: 0 viscous edge flux (convective if inviscid), 1 convective edge flux, 2 owner-computes
 // accumulation + source, 3 cons->prim + transport, 4 gradient, 5 source only, 6 explicit update.
 int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
   const Dev& d = c->d;
@@ -401,9 +424,10 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
     RX_CK(cudaEventRecord(e0, s));
     for (int r = 0; r < n; ++r) {
       switch (which) {
-        case 0: if (c->o.viscous) k_edge_flux<9, true, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d);
-                else k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
-        case 1: k_edge_flux<9, true, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); break;
+        case 0: if (c->o.viscous) launch_edge_flux<false, true>(c, s);
+                else launch_edge_flux<true, false>(c, s);
+                c->launches--; break;   // the helper counts its own launch
+        case 1: launch_edge_flux<true, false>(c, s); c->launches--; break;
         case 2: if (c->o.viscous) k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
                 else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
         case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;

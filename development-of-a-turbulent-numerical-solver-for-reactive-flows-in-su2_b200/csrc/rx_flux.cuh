@@ -70,16 +70,20 @@ RX_HD void eig_gemv(MatF A, const double* v, double* res) {
 
 // Eigen::BiCGSTAB<MatrixXd>, DiagonalPreconditioner, tol 1e-11, zero initial guess, maxIters = 2N
 // (externals/Eigen/src/IterativeLinearSolvers/BiCGSTAB.h:28-108; call site numerics_direct_reactive.cpp:451-470).
-template <int N, class MatF>
-RX_HD int bicgstab(MatF A, const double* rhs, double* x) {
+// rhs, r0 and x live in caller-provided strided scratch (element k at ptr[k*S]; shared memory on the GPU) — they are touched
+// a few times per iteration only — while r, p, v, t stay in registers.
+template <int N, int S, class MatF>
+RX_HD int bicgstab(MatF A, const double* rhs, double* r0, double* x) {
+  // y = K^-1 p and z = K^-1 s are re-formed where they are used (same bits each time), and s shares the storage of r
+  // (r is dead once s exists; the new r overwrites s).
   const double tol = 1.0e-11;
-  double invd[N], r[N], r0[N], v[N], p[N], y[N], z[N], s[N], t[N];
+  double invd[N], r[N], v[N], p[N], t[N], w1[N];
 #pragma unroll
-  for (int i = 0; i < N; ++i) { const double d = A(i, i); invd[i] = d != 0.0 ? 1.0 / d : 1.0; x[i] = 0.0; }
+  for (int i = 0; i < N; ++i) { const double d = A(i, i); invd[i] = d != 0.0 ? 1.0 / d : 1.0; x[i * S] = 0.0; }
 #pragma unroll
-  for (int i = 0; i < N; ++i) { r[i] = rhs[i] - 0.0; r0[i] = r[i]; }   // r = rhs - A*0
-  double r0_sqnorm = eig_dot<N>(r0, r0);
-  const double rhs_sqnorm = eig_dot<N>(rhs, rhs);
+  for (int i = 0; i < N; ++i) { r[i] = rhs[i * S] - 0.0; r0[i * S] = r[i]; }   // r = rhs - A*0
+  double r0_sqnorm = eig_dot<N>(r, r);
+  const double rhs_sqnorm = r0_sqnorm;   // same products, same order
   if (rhs_sqnorm == 0) return 0;
   double rho = 1, alpha = 1, w = 1;
 #pragma unroll
@@ -87,28 +91,35 @@ RX_HD int bicgstab(MatF A, const double* rhs, double* x) {
   const double tol2 = tol * tol * rhs_sqnorm;
   const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
   int it = 0, restarts = 0;
+#pragma unroll 1
   while (eig_dot<N>(r, r) > tol2 && it < 2 * N) {
     const double rho_old = rho;
-    rho = eig_dot<N>(r0, r);
-    if (fabs(rho) < eps2 * r0_sqnorm) {
-      eig_gemv<N>(A, x, t);
 #pragma unroll
-      for (int k = 0; k < N; ++k) { r[k] = rhs[k] - t[k]; r0[k] = r[k]; }
+    for (int k = 0; k < N; ++k) w1[k] = r0[k * S];
+    rho = eig_dot<N>(w1, r);
+    if (fabs(rho) < eps2 * r0_sqnorm) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) w1[k] = x[k * S];
+      eig_gemv<N>(A, w1, t);
+#pragma unroll
+      for (int k = 0; k < N; ++k) { r[k] = rhs[k * S] - t[k]; r0[k * S] = r[k]; }
       rho = r0_sqnorm = eig_dot<N>(r, r);
       if (restarts++ == 0) it = 0;
     }
     const double beta = (rho / rho_old) * (alpha / w);
 #pragma unroll
-    for (int k = 0; k < N; ++k) { p[k] = r[k] + beta * (p[k] - w * v[k]); y[k] = invd[k] * p[k]; }
-    eig_gemv<N>(A, y, v);
-    alpha = rho / eig_dot<N>(r0, v);
+    for (int k = 0; k < N; ++k) { p[k] = r[k] + beta * (p[k] - w * v[k]); w1[k] = invd[k] * p[k]; }
+    eig_gemv<N>(A, w1, v);
 #pragma unroll
-    for (int k = 0; k < N; ++k) { s[k] = r[k] - alpha * v[k]; z[k] = invd[k] * s[k]; }
-    eig_gemv<N>(A, z, t);
+    for (int k = 0; k < N; ++k) w1[k] = r0[k * S];
+    alpha = rho / eig_dot<N>(w1, v);
+#pragma unroll
+    for (int k = 0; k < N; ++k) { r[k] = r[k] - alpha * v[k]; w1[k] = invd[k] * r[k]; }   // r now holds s, w1 holds z
+    eig_gemv<N>(A, w1, t);
     const double tt = eig_dot<N>(t, t);
-    if (tt > 0.0) w = eig_dot<N>(t, s) / tt; else w = 0.0;
+    if (tt > 0.0) w = eig_dot<N>(t, r) / tt; else w = 0.0;
 #pragma unroll
-    for (int k = 0; k < N; ++k) { x[k] = x[k] + (alpha * y[k] + w * z[k]); r[k] = s[k] - w * t[k]; }
+    for (int k = 0; k < N; ++k) { x[k * S] = x[k * S] + (alpha * (invd[k] * p[k]) + w * w1[k]); r[k] = r[k] - w * t[k]; }
     ++it;
   }
   return it;
@@ -234,17 +245,18 @@ struct ViscEnd {
   double g[(4 + NS) * 2];   // rows [T,u,v,P,X_s] x 2 — filled only where needed
   double X[NS];             // mole fractions of the end state (GetMolarFromMass of V[Y])
   double mu, kap;
-  double rD[NS * (NS + 1) / 2];   // 1/D_st of the point that owns the binary diffusion coefficients, upper triangle s <= t
+  const double* rD;         // 1/D_st of the point that owns the binary diffusion coefficients: upper triangle s <= t,
+  long long rDs;            // entry q = tri_idx(s,t) at rD[q * rDs] (read where it is used; 45 values per end are too many to hold)
   double muT, ke, gk[2], x[2];
 };
 
 // CAvgGradReactive_Flow::ComputeResidual (numerics_direct_reactive.cpp:1425-1573) / _Boundary::ComputeResidual (:478-553),
 // SetLaminarTensorFlux (:1099-1190), Solve_SM (:451-470) with GetGamma (reacting_model_library.cpp:771-798),
 // SST_Reactive_ResidualClosure (:656-852), Get_Molar2MassGrad_Operator (:861-880).
-// `scratch` holds NS*NS doubles with element k at scratch[k*S] (the S–M matrix, then the molar->mass operator): S = 1 for a
+// `scratch` holds NS*NS + 3*NS doubles with element k at scratch[k*S] (the S–M matrix, then the molar->mass operator): S = 1 for a
 // thread-local array, S = block size for the shared-memory layout.
 RX_HD constexpr int tri_idx(int NS, int s, int t) { return s * NS - s * (s - 1) / 2 + (t - s); }   // s <= t
-template <int NS, bool EDGE, int S>
+template <int NS, bool EDGE, int S, bool RANS>
 RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I, const ViscEnd<NS>& J, double nx, double ny,
                         double sigma_k, double* scratch, double* res) {
   constexpr int NA = 3 + NS;
@@ -280,7 +292,7 @@ RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I
   const double rho = Vm[V_RHO], T = Vm[V_T];
   const SplPos sp = spl_pos(cc, T);
 #pragma unroll
-  for (int s = 0; s < NS; ++s) { hs[s] = spl_eval(cc, P_H, s, sp) / cc.M[s]; Ys[s] = Vm[V_Y + s]; }
+  for (int s = 0; s < NS; ++s) Ys[s] = Vm[V_Y + s];
   molar_from_mass(cc, Ys, Xs);
   double div_vel = 0.0;
   div_vel += G[1][0]; div_vel += G[2][1];
@@ -308,48 +320,64 @@ RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I
   // D and Gamma's D-dependent terms are symmetric bit for bit, so each unordered pair is evaluated once; the diagonal sums
   // tmp_i = sum_{k != i} X_k/D_ik still accumulate in ascending k (pairs (k,i), k < i, are met before pairs (i,j), j > i).
   {
-    double* Gam = scratch;   // column-major like Eigen::MatrixXd: Gam(r,c) at scratch[(c*NS + r)*S]
+    double* Gam = scratch;            // column-major like Eigen::MatrixXd: Gam(r,c) at scratch[(c*NS + r)*S]
+    double* Xsm = scratch + NS * NS * S;   // copy of Xs for the rolled pair loop (dynamic index)
     double sigma = 0.0, massTot = 0.0;
 #pragma unroll
     for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
 #pragma unroll
     for (int s = 0; s < NS; ++s) massTot += Ys[s] / cc.M[s];
     massTot = 1.0 / massTot;
-    double maxD = 0.0, tmp[NS];
 #pragma unroll
-    for (int s = 0; s < NS; ++s) tmp[s] = 0.0;
+    for (int s = 0; s < NS; ++s) { Xsm[s * S] = Xs[s]; Gam[(s * NS + s) * S] = 0.0; }   // diagonal slot holds tmp_s meanwhile
+    double maxD = 0.0;
     const double sm = -sigma * massTot;
-#pragma unroll
+    const double* rdi = I.rD;
+    const double* rdj = J.rD;
+    // the pair loops stay rolled: 36 pairs x 5 IEEE divisions unrolled would be most of the kernel's code
+#pragma unroll 1
     for (int i = 0; i < NS; ++i) {
-#pragma unroll
-      for (int j = i; j < NS; ++j) {
-        const double dm = 2.0 / (I.rD[tri_idx(NS, i, j)] + J.rD[tri_idx(NS, i, j)]);   // 2/(1/D_i + 1/D_j)
+      const double Xi = Xsm[i * S], Mi = cc.M[i];
+      double ti = Gam[(i * NS + i) * S];
+      maxD = fmax(maxD, 2.0 / (*rdi + *rdj));   // D_ii takes part in the maximum only
+      rdi += I.rDs; rdj += J.rDs;
+#pragma unroll 1
+      for (int j = i + 1; j < NS; ++j) {
+        const double dm = 2.0 / (*rdi + *rdj);   // 2/(1/D_i + 1/D_j)
+        rdi += I.rDs; rdj += J.rDs;
         maxD = fmax(maxD, dm);
-        if (j != i) {
-          Gam[(j * NS + i) * S] = sm * Xs[i] / (rho * cc.M[j] * dm);
-          Gam[(i * NS + j) * S] = sm * Xs[j] / (rho * cc.M[i] * dm);
-          tmp[i] += Xs[j] / dm;
-          tmp[j] += Xs[i] / dm;
-        }
+        const double Xj = Xsm[j * S];
+        Gam[(j * NS + i) * S] = sm * Xi / (rho * cc.M[j] * dm);
+        Gam[(i * NS + j) * S] = sm * Xj / (rho * Mi * dm);
+        ti += Xj / dm;
+        Gam[(j * NS + j) * S] += Xi / dm;
       }
+      Gam[(i * NS + i) * S] = ti;
     }
     const double alpha = 1.0 / (rho * maxD);
+#pragma unroll 1
+    for (int i = 0; i < NS; ++i) Gam[(i * NS + i) * S] = sigma * massTot * Gam[(i * NS + i) * S] / (rho * cc.M[i]);
+#pragma unroll 1
+    for (int j = 0; j < NS; ++j) {
 #pragma unroll
-    for (int i = 0; i < NS; ++i) Gam[(i * NS + i) * S] = sigma * massTot * tmp[i] / (rho * cc.M[i]);
-    for (int i = 0; i < NS; ++i) {
-      const double ay = alpha * Ys[i];
-      for (int j = 0; j < NS; ++j) Gam[(j * NS + i) * S] = Gam[(j * NS + i) * S] + ay;
+      for (int i = 0; i < NS; ++i) Gam[(j * NS + i) * S] = Gam[(j * NS + i) * S] + alpha * Ys[i];
     }
-    double rhs[NS];
+    double* rhs = Xsm;                        // Xs is no longer needed in scratch
+    double* r0s = scratch + (NS * NS + NS) * S;
+    double* xs = scratch + (NS * NS + 2 * NS) * S;
 #pragma unroll
-    for (int s = 0; s < NS; ++s) rhs[s] = -gxn[s];
-    bicgstab<NS>([&](int r, int c) { return Gam[(c * NS + r) * S]; }, rhs, Jd);
+    for (int s = 0; s < NS; ++s) rhs[s * S] = -gxn[s];
+    bicgstab<NS, S>([&](int r, int c) { return Gam[(c * NS + r) * S]; }, rhs, r0s, xs);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) Jd[s] = xs[s * S];
   }
   Proj[U_RHO] = -eig_redux<NS, false>(Jd);
 #pragma unroll
+  for (int s = 0; s < NS; ++s) hs[s] = spl_eval(cc, P_H, s, sp) / cc.M[s];   // needed from here on only
+#pragma unroll
   for (int s = 0; s < NS; ++s) { Proj[U_E] += -hs[s] * Jd[s]; Proj[U_S + s] = -Jd[s]; }
   // ---- SST closure
-  if (o.rans) {
+  if (RANS) {
     const double muT = 2.0 / (1.0 / I.muT + 1.0 / J.muT);
     const double ke = 0.5 * (I.ke + J.ke);
     const double gk[2] = {0.5 * (I.gk[0] + J.gk[0]), 0.5 * (I.gk[1] + J.gk[1])};

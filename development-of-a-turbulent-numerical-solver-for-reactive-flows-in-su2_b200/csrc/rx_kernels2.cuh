@@ -19,8 +19,7 @@ __device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long 
 #pragma unroll
   for (int s = 0; s < NS; ++s) E.X[s] = d.X[s * d.np + p];
   E.mu = d.mu[p]; E.kap = d.kap[p];
-#pragma unroll
-  for (int q = 0; q < NS * (NS + 1) / 2; ++q) E.rD[q] = d.rD[(size_t)q * d.np + p];
+  E.rD = d.rD + p; E.rDs = d.np;
   E.x[0] = d.x[p]; E.x[1] = d.y[p];
   if (o.rans) { E.muT = d.turb[p]; E.ke = d.turb[d.np + p]; E.gk[0] = d.turb[3 * d.np + p]; E.gk[1] = d.turb[4 * d.np + p]; }
   else { E.muT = 1.0; E.ke = 0.0; E.gk[0] = E.gk[1] = 0.0; }
@@ -28,7 +27,7 @@ __device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long 
 
 // ---- Upwind_Residual (:2535-2785, 1st order) and Viscous_Residual (:5305-5386): one thread per edge, flux to edge arrays
 constexpr int EDGE_BS = 64;   // threads per block of the edge / boundary flux kernels
-template <int NS, bool CONV, bool VISC>
+template <int NS, bool CONV, bool VISC, bool RANS>
 __global__ void __launch_bounds__(EDGE_BS) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= d.nEdge) return;
@@ -46,8 +45,8 @@ __global__ void __launch_bounds__(EDGE_BS) k_edge_flux(const __grid_constant__ C
       for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
     }
     extern __shared__ double smat[];   // NS*NS doubles per thread, word k of thread t at smat[k*EDGE_BS + t]: conflict-free
-    const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
-    viscous_flux<NS, true, EDGE_BS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
+    const double sigma_k = RANS ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
+    viscous_flux<NS, true, EDGE_BS, RANS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
 #pragma unroll
     for (int v = 0; v < NV; ++v) d.fluxV[v * d.ne + e] = res[v];
   } else {
@@ -151,7 +150,8 @@ __device__ __forceinline__ void boundary_fluxes(const ChemC<NS>& cc, const Opts&
     for (int v = 0; v < 7 + NS; ++v) J.V[v] = Vg[v];
     extern __shared__ double smat[];
     const double sigma_k = o.rans ? d.turb[5 * d.np + i] : 1.0;
-    viscous_flux<NS, false, EDGE_BS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
+    if (o.rans) viscous_flux<NS, false, EDGE_BS, true>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
+    else viscous_flux<NS, false, EDGE_BS, false>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
 #pragma unroll
     for (int v = 0; v < NV; ++v) r[v] = r[v] - res[v];
   }

@@ -1,0 +1,348 @@
+// rx_visc_pair.cuh — laminar viscous edge flux with TWO LANES PER EDGE (sixteen edges per warp).
+//
+// Same arithmetic, bit for bit, as viscous_flux<NS, EDGE=true> in rx_flux.cuh (CAvgGradReactive_Flow::ComputeResidual,
+// numerics_direct_reactive.cpp:1425-1573; Solve_SM :451-470; GetGamma reacting_model_library.cpp:771-798), arranged for the
+// SM: the thread-per-edge form needs ~180 live doubles per thread for the 9x9 Stefan–Maxwell solve, which pins the kernel at
+// 8 warps/SM with spills.  Here the two lanes of a pair split the nine species rows as
+//     lane 0: rows 0,2,4,6        lane 1: rows 1,3,5,7 and 8          (row of slot k: 2k + lane, slot 4 = row 8)
+// which is exactly how Eigen's packet reduction (Redux.h) splits a 9-sum: ((a0+a4)+(a2+a6)) + ((a1+a5)+(a3+a7)), then + a8.
+// Each lane forms its half with the same expression, the halves meet through one shuffle (IEEE addition commutes), row 8 is
+// the scalar tail on both.  The GEMV keeps Eigen's per-row order: rows < 8 use the four-column tree, row 8 — always slot 4 —
+// the sequential form, so the choice is static.  Slot 4 of lane 0 mirrors row 8 and is never read by anything that is kept.
+// Matrix rows live in registers (slots < MREG) or in thread-private shared memory words (slot >= MREG).
+#pragma once
+#include "rx_kernels.cuh"
+
+namespace rx {
+
+constexpr int VP_BS = 128;     // threads per block = 64 edges
+constexpr int VP_MINB = 3;     // resident blocks per SM the register budget is set for
+constexpr int VP_MREG = 3;     // matrix slots held in registers; the other two go to shared memory
+constexpr int VP_SMW = 5 * 9;   // shared-memory words per thread: the lane's five matrix rows
+constexpr unsigned VP_FULL = 0xffffffffu;
+
+struct PairLane {
+  int l;          // 0 / 1
+  int odd;        // lane id of the odd lane of this pair within the warp
+  __device__ __forceinline__ double other(double v) const { return __shfl_xor_sync(VP_FULL, v, 1); }
+  __device__ __forceinline__ double fromOdd(double v) const { return __shfl_sync(VP_FULL, v, odd); }
+  __device__ __forceinline__ double sel(double even, double oddv) const { return l ? oddv : even; }
+};
+
+// sum of nine values spread over the pair (a[k] = value of the lane's slot k) in Eigen redux order
+__device__ __forceinline__ double pair_redux(const PairLane& L, const double* a) {
+  const double s = (a[0] + a[2]) + (a[1] + a[3]);
+  const double tot = s + L.other(s);
+  return tot + L.fromOdd(a[4]);
+}
+__device__ __forceinline__ double pair_dot(const PairLane& L, const double* a, const double* b) {
+  double t[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) t[k] = a[k] * b[k];
+  return pair_redux(L, t);
+}
+// all nine entries of a vector spread over the pair
+__device__ __forceinline__ void pair_gather(const PairLane& L, const double* a, double* f) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const double o = L.other(a[k]);
+    f[2 * k] = L.l ? o : a[k];
+    f[2 * k + 1] = L.l ? a[k] : o;
+  }
+  f[8] = L.fromOdd(a[4]);
+}
+// rows of the lane of A*f, Eigen GEMV order per row (see eig_gemv)
+template <class MatF>
+__device__ __forceinline__ void pair_gemv(MatF A, const double* f, double* res) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    double r = 0.0;
+    r = r + ((A(k, 0) * f[0] + A(k, 1) * f[1]) + (A(k, 2) * f[2] + A(k, 3) * f[3]));
+    r = r + ((A(k, 4) * f[4] + A(k, 5) * f[5]) + (A(k, 6) * f[6] + A(k, 7) * f[7]));
+    res[k] = A(k, 8) * f[8] + r;
+  }
+  {
+    double r = 0.0;
+#pragma unroll
+    for (int c = 0; c < 9; ++c) r = A(4, c) * f[c] + r;
+    res[4] = r;
+  }
+}
+
+template <int NS>
+__global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  static_assert(NS == 9, "the row split {0,2,4,6 | 1,3,5,7,8} is laid out for nine species");
+  extern __shared__ double vp_sm[];   // word w of thread t at vp_sm[w * VP_BS + t]
+  double* const sm = vp_sm + threadIdx.x;
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  PairLane L;
+  L.l = (int)(threadIdx.x & 1);
+  L.odd = (int)(threadIdx.x & 31) | 1;
+  long long e = t >> 1;
+  const bool keep = e < d.nEdge;
+  if (!keep) e = d.nEdge - 1;   // the lane stays in the warp's shuffles and votes; nothing it computes is stored
+  const int l = L.l;
+  const long long np = d.np;
+  const int pi = d.ei[e], pj = d.ej[e];
+  const double nx = d.enx[e], ny = d.eny[e];
+  int row[5];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) row[k] = 2 * k + l;
+  row[4] = 8;
+
+  // ---- mean state, both lanes
+  const double rho = 0.5 * (d.V[V_RHO * np + pi] + d.V[V_RHO * np + pj]);
+  const double T = 0.5 * (d.V[V_T * np + pi] + d.V[V_T * np + pj]);
+  const double um = 0.5 * (d.V[V_VX * np + pi] + d.V[V_VX * np + pj]);
+  const double vm = 0.5 * (d.V[(V_VX + 1) * np + pi] + d.V[(V_VX + 1) * np + pj]);
+  const double mu = 2.0 / (1.0 / d.mu[pi] + 1.0 / d.mu[pj]);
+  const double ktr = 2.0 / (1.0 / d.kap[pi] + 1.0 / d.kap[pj]);
+  double Ys[NS], Xs[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Ys[s] = 0.5 * (d.V[(V_Y + s) * np + pi] + d.V[(V_Y + s) * np + pj]);
+  molar_from_mass(cc, Ys, Xs);
+
+  // ---- mean gradients with the edge correction (:1480-1500), six rows per lane:
+  // slot 0: T | v,  slot 1: u | X_8,  slot 2+k: X_{2k+lane}
+  double G[6][2];
+  {
+    const double e0 = d.x[pj] - d.x[pi], e1 = d.y[pj] - d.y[pi];
+    const double dist2 = 0.0 + e0 * e0 + e1 * e1;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+      int gr;                 // gradient row
+      const double* val;      // field the row differentiates
+      if (q == 0) { gr = l ? G_VX + 1 : G_T; val = d.V + (size_t)(l ? V_VX + 1 : V_T) * np; }
+      else if (q == 1) { gr = l ? G_X + 8 : G_VX; val = l ? d.X + (size_t)8 * np : d.V + (size_t)V_VX * np; }
+      else { gr = G_X + 2 * (q - 2) + l; val = d.X + (size_t)(2 * (q - 2) + l) * np; }
+      const double* g = d.grad + (size_t)(gr * 2) * np;
+      double g0 = 0.5 * (g[pi] + g[pj]);
+      double g1 = 0.5 * (g[np + pi] + g[np + pj]);
+      const double proj = (0.0 + g0 * e0) + g1 * e1;
+      const double diff = val[pj] - val[pi];
+      g0 -= ((proj - diff) * e0) / dist2;
+      g1 -= ((proj - diff) * e1) / dist2;
+      G[q][0] = g0; G[q][1] = g1;
+    }
+  }
+  // rows T, u, v on both lanes
+  double GT[2], GU[2], GV[2];
+#pragma unroll
+  for (int dd = 0; dd < 2; ++dd) {
+    const double a = L.other(G[0][dd]);   // lane 0 receives v, lane 1 receives T
+    const double b = L.other(G[1][dd]);   // lane 1 receives u
+    GT[dd] = l ? a : G[0][dd];
+    GV[dd] = l ? G[0][dd] : a;
+    GU[dd] = l ? b : G[1][dd];
+  }
+  // viscous stresses and heat flux (SetLaminarTensorFlux :1099-1190)
+  double FT[3][2];
+  {
+    const double Gv[2][2] = {{GU[0], GU[1]}, {GV[0], GV[1]}};   // Gv[c][dim]
+    const double vel[2] = {um, vm};
+    double tau[2][2];
+    double div_vel = 0.0;
+    div_vel += Gv[0][0]; div_vel += Gv[1][1];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      tau[a][0] = 0.0; tau[a][1] = 0.0;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) tau[a][b] += mu * (Gv[b][a] + Gv[a][b]);
+      tau[a][a] -= TWO3 * (mu * div_vel);
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      FT[2][a] = 0.0;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) { FT[b][a] = tau[a][b]; FT[2][a] += tau[a][b] * vel[b]; }
+      FT[2][a] += ktr * GT[a];
+    }
+  }
+  // right-hand side of the lane's rows: -(grad X . n)
+  double rhs[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const int q = k < 4 ? k + 2 : 1;
+    double gxn = 0.0;
+    gxn += G[q][0] * nx;
+    gxn += G[q][1] * ny;
+    rhs[k] = -gxn;
+  }
+  if (l == 0) rhs[4] = 0.0;   // slot 4 of the even lane is a mirror; keep it finite
+
+  // ---- Stefan–Maxwell matrix, the lane's rows (GetGamma :771-798, Gamma_tilde :463-465).  For row r and column c != r:
+  //   D = 2/(1/D_rc(i) + 1/D_rc(j)),  Gamma(r,c) = -sigma*massTot*X_r/(rho*M_c*D),  tmp_r += X_c/D  (ascending c),
+  //   Gamma(r,r) = sigma*massTot*tmp_r/(rho*M_r);  every entry of row r then gets alpha*Y_r, alpha = 1/(rho*max D).
+  // Columns 2k and 2k+1 of slot k < 4 hold the diagonal on one lane and an ordinary entry on the other.
+  // The matrix is assembled in thread-private shared-memory words (slot k, column c at word k*NS + c) by loops that stay
+  // rolled over the slots — 135 IEEE divisions unrolled would be most of the kernel's code — with the per-slot operands
+  // rotated through registers so that no register array is indexed dynamically.
+  auto smA = [&](int k, int c) -> double& { return sm[(k * NS + c) * VP_BS]; };
+  double invd[5];
+  {
+    double sigma = 0.0, massTot = 0.0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) massTot += Ys[s] / cc.M[s];
+    massTot = 1.0 / massTot;
+    const double smm = -sigma * massTot;
+    const double* rdi = d.rD + pi;
+    const double* rdj = d.rD + pj;
+    double maxD = 0.0;
+    double Xrow[5], Yrow[5];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { Xrow[k] = L.sel(Xs[2 * k], Xs[2 * k + 1]); Yrow[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]); }
+    Xrow[4] = Xs[8]; Yrow[4] = Ys[8];
+#pragma unroll 1
+    for (int k = 0; k < 5; ++k) {
+      const int r = k < 4 ? 2 * k + l : 8;
+      const double Xr = Xrow[0];
+      double tk = 0.0;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        const int a = r < c ? r : c, b = r < c ? c : r;
+        const size_t q = (size_t)(a * NS - a * (a - 1) / 2 + (b - a)) * np;
+        const double dm = 2.0 / (rdi[q] + rdj[q]);   // D_rr takes part in the maximum only
+        maxD = fmax(maxD, dm);
+        smA(k, c) = smm * Xr / (rho * cc.M[c] * dm);
+        const double qd = Xs[c] / dm;
+        tk = (c != r) ? tk + qd : tk;
+      }
+      smA(k, r) = tk;   // the diagonal word carries tmp_r until the second pass
+#pragma unroll
+      for (int m = 0; m < 4; ++m) Xrow[m] = Xrow[m + 1];
+    }
+    maxD = fmax(maxD, L.other(maxD));
+    const double alpha = 1.0 / (rho * maxD);
+#pragma unroll 1
+    for (int k = 0; k < 5; ++k) {
+      const int r = k < 4 ? 2 * k + l : 8;
+      const double ay = alpha * Yrow[0];
+      const double dg = sigma * massTot * smA(k, r) / (rho * cc.M[r]);
+      smA(k, r) = dg;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) smA(k, c) = smA(k, c) + ay;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) Yrow[m] = Yrow[m + 1];
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { const double dg = smA(k, row[k]); invd[k] = dg != 0.0 ? 1.0 / dg : 1.0; }
+  }
+  // rows of the first VP_MREG slots move to registers; their shared-memory words then hold rhs, r0 and x of the solve
+  double A[VP_MREG > 0 ? VP_MREG : 1][NS];
+#pragma unroll
+  for (int k = 0; k < VP_MREG; ++k)
+#pragma unroll
+    for (int c = 0; c < NS; ++c) A[k][c] = smA(k, c);
+  auto getA = [&](int k, int c) -> double { return k < VP_MREG ? A[k][c] : sm[(k * NS + c) * VP_BS]; };
+  static_assert(VP_MREG * NS >= 15, "rhs, r0 and x reuse the words of the register-held rows");
+  auto s_rhs = [&](int k) -> double& { return sm[k * VP_BS]; };
+  auto s_r0 = [&](int k) -> double& { return sm[(5 + k) * VP_BS]; };
+  auto s_x = [&](int k) -> double& { return sm[(10 + k) * VP_BS]; };
+
+  // ---- Eigen::BiCGSTAB with diagonal preconditioner, tol 1e-11, zero guess, at most 2N iterations (see bicgstab<> in
+  // rx_flux.cuh for the serial form and its citations).  All scalars are identical on the two lanes of a pair.  Pairs of
+  // one warp run the loop together until the last one has converged; a pair that is done keeps its state (`live`).
+  double r[5], v[5], p[5], tv[5], w1[5], f[NS];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) { s_rhs(k) = rhs[k]; s_x(k) = 0.0; r[k] = rhs[k] - 0.0; s_r0(k) = r[k]; v[k] = 0.0; p[k] = 0.0; }
+  double r0_sqnorm = pair_dot(L, r, r);
+  const double rhs_sqnorm = r0_sqnorm;
+  double rho_b = 1, alpha_b = 1, w_b = 1;
+  const double tol2 = 1.0e-11 * 1.0e-11 * rhs_sqnorm;
+  const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
+  int it = 0, restarts = 0;
+  bool live = (rhs_sqnorm != 0) && (r0_sqnorm > tol2);   // first loop test: r == r0
+#pragma unroll 1
+  while (__any_sync(VP_FULL, live)) {
+    const double rho_old = rho_b;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) w1[k] = s_r0(k);
+    double rho_n = pair_dot(L, w1, r);
+    const bool restart = live && (fabs(rho_n) < eps2 * r0_sqnorm);
+    if (__any_sync(VP_FULL, restart)) {   // r = rhs - A x, r0 = r (rare)
+#pragma unroll
+      for (int k = 0; k < 5; ++k) w1[k] = s_x(k);
+      pair_gather(L, w1, f);
+      pair_gemv(getA, f, tv);
+      double rn[5];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) rn[k] = s_rhs(k) - tv[k];
+      const double nn = pair_dot(L, rn, rn);
+      if (restart) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) { r[k] = rn[k]; s_r0(k) = rn[k]; }
+        rho_n = r0_sqnorm = nn;
+        if (restarts++ == 0) it = 0;
+      }
+    }
+    const double beta = (rho_n / rho_old) * (alpha_b / w_b);
+    double pn[5], vn[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { pn[k] = r[k] + beta * (p[k] - w_b * v[k]); w1[k] = invd[k] * pn[k]; }
+    pair_gather(L, w1, f);
+    pair_gemv(getA, f, vn);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) w1[k] = s_r0(k);
+    const double alpha_n = rho_n / pair_dot(L, w1, vn);
+    double s[5], z[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { s[k] = r[k] - alpha_n * vn[k]; z[k] = invd[k] * s[k]; }
+    pair_gather(L, z, f);
+    pair_gemv(getA, f, tv);
+    const double tt = pair_dot(L, tv, tv);
+    const double ts = pair_dot(L, tv, s);
+    const double w_n = tt > 0.0 ? ts / tt : 0.0;
+    double rn[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) rn[k] = s[k] - w_n * tv[k];
+    const double rrn = pair_dot(L, rn, rn);
+    if (live) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        s_x(k) = s_x(k) + (alpha_n * (invd[k] * pn[k]) + w_n * z[k]);
+        r[k] = rn[k]; p[k] = pn[k]; v[k] = vn[k];
+      }
+      rho_b = rho_n; alpha_b = alpha_n; w_b = w_n;
+      ++it;
+      live = (rrn > tol2) && (it < 2 * NS);
+    }
+  }
+  double x[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) x[k] = s_x(k);
+
+  // ---- assemble the projected flux (:1530-1573).  Proj[rho] = -sum Jd (Eigen sum), Proj[E] = sum_s -h_s Jd_s in species
+  // order, then the stress/heat part; species rows go out from the lane that owns them.
+  const double sumJ = pair_redux(L, x);
+  const SplPos sp = spl_pos(cc, T);
+  double hj[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) hj[k] = -(spl_eval(cc, P_H, row[k], sp) / cc.M[row[k]]) * x[k];
+  pair_gather(L, hj, f);
+  double pE = 0.0;
+#pragma unroll
+  for (int s2 = 0; s2 < NS; ++s2) pE += f[s2];
+  double pMx = 0.0, pMy = 0.0;
+  const double nrm[2] = {nx, ny};
+#pragma unroll
+  for (int dd = 0; dd < 2; ++dd) {
+    pMx += FT[0][dd] * nrm[dd];
+    pMy += FT[1][dd] * nrm[dd];
+    pE += FT[2][dd] * nrm[dd];
+  }
+  if (!keep) return;
+  const long long ne = d.ne;
+  if (l == 0) {
+    d.fluxV[U_RHO * ne + e] = -sumJ;
+    d.fluxV[U_MX * ne + e] = pMx;
+    d.fluxV[(U_MX + 1) * ne + e] = pMy;
+    d.fluxV[U_E * ne + e] = pE;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) d.fluxV[(U_S + row[k]) * ne + e] = -x[k];
+  if (l == 1) d.fluxV[(U_S + 8) * ne + e] = -x[4];
+}
+
+}  // namespace rx
