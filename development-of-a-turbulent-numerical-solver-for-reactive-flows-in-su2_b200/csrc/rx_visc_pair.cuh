@@ -12,6 +12,7 @@
 // Matrix rows live in registers (slots < MREG) or in thread-private shared memory words (slot >= MREG).
 #pragma once
 #include "rx_kernels.cuh"
+#include <math_constants.h>
 
 namespace rx {
 
@@ -28,6 +29,15 @@ struct PairLane {
   __device__ __forceinline__ double fromOdd(double v) const { return __shfl_sync(VP_FULL, v, odd); }
   __device__ __forceinline__ double sel(double even, double oddv) const { return l ? oddv : even; }
 };
+
+// a / b.  CUDA's inline IEEE division leaves its fast path for a zero quotient, and zero numerators are common here (edge
+// components of axis-aligned edges, absent species); the quotient is then the signed zero, formed directly.
+__device__ __forceinline__ double div0(double a, double b) {
+  const bool z = (a == 0.0) && (fabs(b) > 0.0) && (fabs(b) < CUDART_INF);
+  const double q = (z ? 1.0 : a) / b;
+  const double sz = __hiloint2double((__double2hiint(a) ^ __double2hiint(b)) & 0x80000000, 0);
+  return z ? sz : q;
+}
 
 // sum of nine values spread over the pair (a[k] = value of the lane's slot k) in Eigen redux order
 __device__ __forceinline__ double pair_redux(const PairLane& L, const double* a) {
@@ -108,6 +118,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   {
     const double e0 = d.x[pj] - d.x[pi], e1 = d.y[pj] - d.y[pi];
     const double dist2 = 0.0 + e0 * e0 + e1 * e1;
+    double gi0[6], gj0[6], gi1[6], gj1[6], vi[6], vj[6];   // all loads first: the divisions below end basic blocks
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       int gr;                 // gradient row
@@ -116,12 +127,17 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       else if (q == 1) { gr = l ? G_X + 8 : G_VX; val = l ? d.X + (size_t)8 * np : d.V + (size_t)V_VX * np; }
       else { gr = G_X + 2 * (q - 2) + l; val = d.X + (size_t)(2 * (q - 2) + l) * np; }
       const double* g = d.grad + (size_t)(gr * 2) * np;
-      double g0 = 0.5 * (g[pi] + g[pj]);
-      double g1 = 0.5 * (g[np + pi] + g[np + pj]);
+      gi0[q] = g[pi]; gj0[q] = g[pj]; gi1[q] = g[np + pi]; gj1[q] = g[np + pj];
+      vi[q] = val[pi]; vj[q] = val[pj];
+    }
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+      double g0 = 0.5 * (gi0[q] + gj0[q]);
+      double g1 = 0.5 * (gi1[q] + gj1[q]);
       const double proj = (0.0 + g0 * e0) + g1 * e1;
-      const double diff = val[pj] - val[pi];
-      g0 -= ((proj - diff) * e0) / dist2;
-      g1 -= ((proj - diff) * e1) / dist2;
+      const double diff = vj[q] - vi[q];
+      g0 -= div0((proj - diff) * e0, dist2);
+      g1 -= div0((proj - diff) * e1, dist2);
       G[q][0] = g0; G[q][1] = g1;
     }
   }
@@ -194,19 +210,32 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
     for (int k = 0; k < 4; ++k) { Xrow[k] = L.sel(Xs[2 * k], Xs[2 * k + 1]); Yrow[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]); }
     Xrow[4] = Xs[8]; Yrow[4] = Ys[8];
-#pragma unroll 1
-    for (int k = 0; k < 5; ++k) {
+    double ra[NS], rb[NS];   // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead
+    auto fetchD = [&](int k) {
       const int r = k < 4 ? 2 * k + l : 8;
-      const double Xr = Xrow[0];
-      double tk = 0.0;
 #pragma unroll
       for (int c = 0; c < NS; ++c) {
         const int a = r < c ? r : c, b = r < c ? c : r;
         const size_t q = (size_t)(a * NS - a * (a - 1) / 2 + (b - a)) * np;
-        const double dm = 2.0 / (rdi[q] + rdj[q]);   // D_rr takes part in the maximum only
+        ra[c] = rdi[q]; rb[c] = rdj[q];
+      }
+    };
+    fetchD(0);
+#pragma unroll 1
+    for (int k = 0; k < 5; ++k) {
+      const int r = k < 4 ? 2 * k + l : 8;
+      const double Xr = Xrow[0];
+      double sD[NS];
+#pragma unroll
+      for (int c = 0; c < NS; ++c) sD[c] = ra[c] + rb[c];
+      if (k < 4) fetchD(k + 1);
+      double tk = 0.0;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        const double dm = 2.0 / sD[c];   // D_rr takes part in the maximum only
         maxD = fmax(maxD, dm);
-        smA(k, c) = smm * Xr / (rho * cc.M[c] * dm);
-        const double qd = Xs[c] / dm;
+        smA(k, c) = div0(smm * Xr, rho * cc.M[c] * dm);
+        const double qd = div0(Xs[c], dm);
         tk = (c != r) ? tk + qd : tk;
       }
       smA(k, r) = tk;   // the diagonal word carries tmp_r until the second pass
