@@ -16,9 +16,18 @@
 
 namespace rx {
 
-constexpr int VP_BS = 128;     // threads per block = 64 edges
-constexpr int VP_MINB = 3;     // resident blocks per SM the register budget is set for
-constexpr int VP_MREG = 3;     // matrix slots held in registers; the other two go to shared memory
+#ifndef RX_VP_BS
+#define RX_VP_BS 128
+#endif
+#ifndef RX_VP_MINB
+#define RX_VP_MINB 3
+#endif
+#ifndef RX_VP_MREG
+#define RX_VP_MREG 2
+#endif
+constexpr int VP_BS = RX_VP_BS;       // threads per block (two per edge)
+constexpr int VP_MINB = RX_VP_MINB;   // resident blocks per SM the register budget is set for
+constexpr int VP_MREG = RX_VP_MREG;   // matrix slots held in registers; the others are read from shared memory
 constexpr int VP_SMW = 5 * 9;   // shared-memory words per thread: the lane's five matrix rows
 constexpr unsigned VP_FULL = 0xffffffffu;
 
@@ -34,7 +43,9 @@ struct PairLane {
 // components of axis-aligned edges, absent species); the quotient is then the signed zero, formed directly.
 __device__ __forceinline__ double div0(double a, double b) {
   const bool z = (a == 0.0) && (fabs(b) > 0.0) && (fabs(b) < CUDART_INF);
-  const double q = (z ? 1.0 : a) / b;
+  double n = z ? 1.0 : a;
+  asm("" : "+d"(n));   // keeps the substitution: the compiler would otherwise divide the original numerator and select afterwards
+  const double q = n / b;
   const double sz = __hiloint2double((__double2hiint(a) ^ __double2hiint(b)) & 0x80000000, 0);
   return z ? sz : q;
 }
@@ -173,6 +184,15 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       for (int b = 0; b < 2; ++b) { FT[b][a] = tau[a][b]; FT[2][a] += tau[a][b] * vel[b]; }
       FT[2][a] += ktr * GT[a];
     }
+  }
+  // momentum rows are complete; of the energy row only the two stress/heat products have to outlive the solve
+  const double fE0 = FT[2][0] * nx, fE1 = FT[2][1] * ny;
+  if (keep && l == 0) {
+    double pMx = 0.0, pMy = 0.0;
+    pMx += FT[0][0] * nx; pMx += FT[0][1] * ny;
+    pMy += FT[1][0] * nx; pMy += FT[1][1] * ny;
+    d.fluxV[U_MX * d.ne + e] = pMx;
+    d.fluxV[(U_MX + 1) * d.ne + e] = pMy;
   }
   // right-hand side of the lane's rows: -(grad X . n)
   double rhs[5];
@@ -353,20 +373,12 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   double pE = 0.0;
 #pragma unroll
   for (int s2 = 0; s2 < NS; ++s2) pE += f[s2];
-  double pMx = 0.0, pMy = 0.0;
-  const double nrm[2] = {nx, ny};
-#pragma unroll
-  for (int dd = 0; dd < 2; ++dd) {
-    pMx += FT[0][dd] * nrm[dd];
-    pMy += FT[1][dd] * nrm[dd];
-    pE += FT[2][dd] * nrm[dd];
-  }
+  pE += fE0;
+  pE += fE1;
   if (!keep) return;
   const long long ne = d.ne;
   if (l == 0) {
     d.fluxV[U_RHO * ne + e] = -sumJ;
-    d.fluxV[U_MX * ne + e] = pMx;
-    d.fluxV[(U_MX + 1) * ne + e] = pMy;
     d.fluxV[U_E * ne + e] = pE;
   }
 #pragma unroll
