@@ -208,8 +208,8 @@ def main():
     barrier()
     ms_e2e = 1e3 * (time.perf_counter() - t0) / Ke
 
-    # dominant kernel: fused AUSM + viscous (Stefan-Maxwell) edge flux, timed alone with CUDA events on the launching stream
-    kt = {n: solver.KernelTime(w, 5) for n, w in [("edge_flux_fused", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("gradient", 4), ("update", 6)]}
+    # dominant kernel: viscous (Stefan-Maxwell) edge flux, timed alone with CUDA events on the launching stream
+    kt = {n: solver.KernelTime(w, 5) for n, w in [("edge_flux_visc", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("transport", 7), ("gradient", 4), ("update", 6)]}
     tt = torch.tensor([ms_dev, ms_e2e, float(units_local)], dtype=torch.float64, device=dev)
     if world > 1:
         mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -229,7 +229,7 @@ def main():
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     # algorithmic bytes of the fused edge kernel: SURVEY.md §8(d) "fused conv+visc" = 24 B/edge + (400 + 104) B/point / (E/P)
     bytes_per_edge = 24.0 + (400.0 + 104.0) / (nE / float(nOwn))
-    ach = bytes_per_edge * nE / (kt["edge_flux_fused"] * 1e-3) / 1e9
+    ach = bytes_per_edge * nE / (kt["edge_flux_visc"] * 1e-3) / 1e9
     bytes_conv = 24.0 + (128.0 + 104.0) / (nE / float(nOwn))
     line = {
         "metric": METRIC, "value": units / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
@@ -241,7 +241,7 @@ def main():
                 "h2d_bytes_per_step": int(solver.nPoint * solver.nVar * 8), "d2h_bytes_per_step": int(solver.nVar * 8)},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"kernel": "k_edge_flux<9,conv,visc> (AUSM + Stefan-Maxwell/BiCGSTAB viscous flux, one thread per edge)",
+        "roofline": {"kernel": "k_edge_visc_pair<9> (Stefan-Maxwell/BiCGSTAB viscous edge flux, two lanes per edge)",
                      "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
                      "note": "FP64-pipe bound, not HBM bound (about 1e4 FP64 operations and ~200 divisions per edge): see DESIGN.md; the convective-only edge kernel is the HBM-bound one",

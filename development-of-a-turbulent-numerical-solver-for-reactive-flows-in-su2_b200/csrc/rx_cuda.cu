@@ -301,6 +301,7 @@ int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) 
   cudaStream_t s = c->stream;
   RX_CK(cudaMemsetAsync(d.counters, 0, sizeof(unsigned long long), s));
   k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, (long long)extIter, output);
+  if (c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }
   c->launches++;
   if (c->o.viscous) {
     if (c->o.leastSquares) {
@@ -413,7 +414,7 @@ int rx_residual_all(rx_ctx* c) {
 
 // average device time (ms, CUDA events on the context's stream) of `reps` launches of one kernel of the path, on the
 // context's current state.  which: 0 viscous edge flux (convective if inviscid), 1 convective edge flux, 2 owner-computes
-// accumulation + source, 3 cons->prim + transport, 4 gradient, 5 source only, 6 explicit update.
+// accumulation + source, 3 cons->prim, 4 gradient, 5 source only, 6 explicit update, 7 laminar transport.
 int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
@@ -431,6 +432,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
         case 2: if (c->o.viscous) k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
                 else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
         case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;
+        case 7: k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); break;
         case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
                 else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
         case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
@@ -446,6 +448,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
     RX_CK(cudaEventElapsedTime(&ms, e0, e1));
     if (pass == 1 && msAvg) *msAvg = (double)ms / n;
   }
+  if (which == 3 && c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }   // mu[p] held T
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   return RX_OK;
 }

@@ -130,30 +130,37 @@ RX_HD void molar_from_mass(const ChemC<NS>& cc, const double* Y, double* X) {   
 
 // Wilke viscosity and conductivity mixing rules in one pass (ComputeEta :634-656, ComputeLambda :671-696).
 // The reference evaluates the same pair factor t_ij twice (once per rule); it is computed once here — same bits.
+// The outer species loop stays rolled (81 pair factors with a division, a square root and two more divisions each would
+// otherwise be ~5k instructions); the i-indexed operands are rotated through registers so that no array is indexed dynamically.
 template <int NS>
 RX_HD void transport(const ChemC<NS>& cc, double T, const double* Y, double& muMix, double& kMix) {
   SplPos sp = spl_pos(cc, T);
-  double mu[NS], ka[NS], yomC[NS], yomR[NS];
+  double mu[NS], yomC[NS], yomR[NS], muR[NS], kaR[NS], ycR[NS], yrR[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) {
     mu[s] = spl_eval(cc, P_MU, s, sp);
-    ka[s] = spl_eval(cc, P_KAPPA, s, sp);
+    kaR[s] = spl_eval(cc, P_KAPPA, s, sp);
     yomC[s] = clipy<NS>(Y[s]) / cc.M[s];   // ComputeEta uses the clipped Ys
     yomR[s] = Y[s] / cc.M[s];              // ComputeLambda uses the raw ys (:679)
+    muR[s] = mu[s]; ycR[s] = yomC[s]; yrR[s] = yomR[s];
   }
   muMix = 0.0; kMix = 0.0;
-#pragma unroll
+#pragma unroll 1
   for (int i = 0; i < NS; ++i) {
+    const double mui = muR[0], kai = kaR[0], yci = ycR[0], yri = yrR[0];
     double phiE = 0.0, phiL = 0.0;
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
-      const double t = 1.0 + sqrt(mu[i] / mu[j]) * cc.wPow[i][j];
+      const double t = 1.0 + sqrt(mui / mu[j]) * cc.wPow[i][j];
       phiE += yomC[j] / cc.wSq[i][j] * t * t;
-      if (j != i) phiL += 1.065 * yomR[j] / cc.wSq[i][j] * t * t;
+      const double add = 1.065 * yomR[j] / cc.wSq[i][j] * t * t;
+      phiL = (j != i) ? phiL + add : phiL;
     }
-    phiL += yomR[i];
-    muMix += mu[i] * yomC[i] / phiE;
-    kMix += ka[i] * yomR[i] / phiL;
+    phiL += yri;
+    muMix += mui * yci / phiE;
+    kMix += kai * yri / phiL;
+#pragma unroll
+    for (int m = 0; m + 1 < NS; ++m) { muR[m] = muR[m + 1]; kaR[m] = kaR[m + 1]; ycR[m] = ycR[m + 1]; yrR[m] = yrR[m + 1]; }
   }
 }
 

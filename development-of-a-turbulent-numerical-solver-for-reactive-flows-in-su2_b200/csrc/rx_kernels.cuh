@@ -45,6 +45,34 @@ __global__ void k_scatter_field(const double* __restrict__ aos, double* __restri
   if (p < n) soa[p] = aos[p * nvIn + col];
 }
 
+// ---- laminar transport of a point: Wilke mixture viscosity / conductivity and the inverse binary diffusion coefficients
+// (CReactiveNSVariable::SetPrimVar, variable_direct_reactive.cpp:1188-1228).  Its own kernel: together with the
+// temperature solve the code no longer fits the instruction cache.  Reads P, Y of the point as k_primitive left them, and
+// the temperature from mu[p]: the ignition overwrite of V[T] comes after SetPrimVar in the reference (:1013-1024).
+template <int NS>
+__global__ void __launch_bounds__(128) k_transport(const __grid_constant__ ChemC<NS> cc, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  double Y[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Y[s] = d.V[(V_Y + s) * d.np + p];
+  const double T = d.mu[p], P = d.V[V_P * d.np + p];   // k_primitive parks the temperature SetPrimVar saw in mu[p]
+  double mu, ka;
+  transport(cc, T, Y, mu, ka);
+  d.mu[p] = mu; d.kap[p] = ka;
+  // 1/D_st of this point, upper triangle (GetDij_SM :751-766; /(V_ref*L_ref*1e4) variable_direct_reactive.cpp:1212;
+  // cwiseInverse numerics_direct_reactive.cpp:1447).  Stored per point so that an edge needs one division per pair.
+  const double T175 = 1.0e-3 * pow175(T);
+  const double Patm = P * 1.0 / 101325.0;
+  int s = 0, t = 0;
+#pragma unroll 3
+  for (int q = 0; q < NS * (NS + 1) / 2; ++q) {
+    const double D = (T175 / (Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t])) / (1.0 * 1.0 * 1.0e4);
+    d.rD[(size_t)q * d.np + p] = 1.0 / D;
+    if (++t == NS) { ++s; t = s; }
+  }
+}
+
 // ---- SetPrimitive_Variables (solver_direct_reactive.cpp:985-1038) + CReactiveNSVariable::SetPrimVar (variable_direct_reactive.cpp:1188-1228)
 template <int NS>
 __global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d,
@@ -57,11 +85,14 @@ __global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC
   for (int v = 0; v < NV; ++v) U[v] = d.U[v * d.np + p];
   V[V_T] = d.V[V_T * d.np + p];
   const double ke = o.rans ? d.turb[1 * d.np + p] : 0.0;
-  bool np = cons2prim(cc, o, extIter, U, V, ke);
-  if (np && extIter > 0) {
+  bool np = false;
+#pragma unroll 1
+  for (int attempt = 0; attempt < 2; ++attempt) {   // one copy of the temperature solve in the code; second pass = :1001-1008
+    const bool bad = cons2prim(cc, o, extIter, U, V, ke);
+    if (attempt == 0) np = bad;
+    if (!(bad && extIter > 0) || attempt == 1) break;
 #pragma unroll
     for (int v = 0; v < NV; ++v) U[v] = d.Uold[v * d.np + p];
-    cons2prim(cc, o, extIter, U, V, ke);
   }
   const double* Y = V + V_Y;
   const double Rg = rgas(cc, Y);
@@ -73,24 +104,7 @@ __global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC
   molar_from_mass(cc, Y, X);
 #pragma unroll
   for (int s = 0; s < NS; ++s) d.X[s * d.np + p] = X[s];
-  if (o.viscous) {
-    double mu, ka;
-    transport(cc, T, Y, mu, ka);
-    d.mu[p] = mu; d.kap[p] = ka;
-    // 1/D_st of this point, upper triangle (GetDij_SM :751-766; /(V_ref*L_ref*1e4) variable_direct_reactive.cpp:1212;
-    // cwiseInverse numerics_direct_reactive.cpp:1447).  Stored per point so that an edge needs one division per pair.
-    const double T175 = 1.0e-3 * pow175(T);
-    const double Patm = V[V_P] * 1.0 / 101325.0;
-    int q = 0;
-#pragma unroll
-    for (int s = 0; s < NS; ++s)
-#pragma unroll
-      for (int t = s; t < NS; ++t) {
-        const double D = (T175 / (Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t])) / (1.0 * 1.0 * 1.0e4);
-        d.rD[(size_t)q * d.np + p] = 1.0 / D;
-        ++q;
-      }
-  }
+  if (o.viscous) d.mu[p] = T;                          // for k_transport, which follows on the stream
   if (o.ignition && extIter < o.ignitionIter) {        // ignition hack: overwrite T only (:1013-1024)
     if (Y[o.fuelIndex] > 0.4 && Y[o.oxidizerIndex] > 0.2 && V[V_T] < o.ignitionT) V[V_T] = o.ignitionT;
   }
