@@ -6,6 +6,10 @@
 // and needs no atomics.
 #pragma once
 #include "rx_flux.cuh"
+#include "rx_fdiv.cuh"
+#ifndef RX_TR_MINB
+#define RX_TR_MINB 3
+#endif
 
 namespace rx {
 
@@ -45,12 +49,67 @@ __global__ void k_scatter_field(const double* __restrict__ aos, double* __restri
   if (p < n) soa[p] = aos[p * nvIn + col];
 }
 
+// Wilke mixing rules as transport<> in rx_device.cuh (ComputeEta :634-656, ComputeLambda :671-696), with the 27 quotients and
+// 9 square roots of one species row issued as independent batches (rx_fdiv.cuh); same values bit for bit.
+template <int NS>
+__device__ __forceinline__ void transport_dev(const ChemC<NS>& cc, double T, const double* Y, double& muMix, double& kMix) {
+  SplPos sp = spl_pos(cc, T);
+  double mu[NS], yomC[NS], yomR[NS], muR[NS], kaR[NS], ycR[NS], yrR[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) {
+    mu[s] = spl_eval(cc, P_MU, s, sp);
+    kaR[s] = spl_eval(cc, P_KAPPA, s, sp);
+    yomC[s] = clipy<NS>(Y[s]) / cc.M[s];
+    yomR[s] = Y[s] / cc.M[s];
+    muR[s] = mu[s]; ycR[s] = yomC[s]; yrR[s] = yomR[s];
+  }
+  Recip rmu[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) rmu[s] = frecip(mu[s]);
+  muMix = 0.0; kMix = 0.0;
+#pragma unroll 1
+  for (int i = 0; i < NS; ++i) {
+    const double mui = muR[0], kai = kaR[0], yci = ycR[0], yri = yrR[0];
+    double phiE = 0.0, phiL = 0.0, tj[NS], qe[NS], ql[NS];
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < NS; ++j) tj[j] = fdiv(mui, rmu[j], bad);
+#pragma unroll
+    for (int j = 0; j < NS; ++j) tj[j] = 1.0 + fsqrt(tj[j], bad) * cc.wPow[i][j];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const Recip rw = frecip(cc.wSq[i][j]);
+      qe[j] = fdiv(yomC[j], rw, bad);
+      ql[j] = fdiv(1.065 * yomR[j], rw, bad);
+    }
+    if (bad) {   // out-of-range operands only
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        tj[j] = 1.0 + sqrt(mui / mu[j]) * cc.wPow[i][j];
+        qe[j] = yomC[j] / cc.wSq[i][j];
+        ql[j] = 1.065 * yomR[j] / cc.wSq[i][j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      phiE += qe[j] * tj[j] * tj[j];
+      const double add = ql[j] * tj[j] * tj[j];
+      phiL = (j != i) ? phiL + add : phiL;
+    }
+    phiL += yri;
+    muMix += mui * yci / phiE;
+    kMix += kai * yri / phiL;
+#pragma unroll
+    for (int m = 0; m + 1 < NS; ++m) { muR[m] = muR[m + 1]; kaR[m] = kaR[m + 1]; ycR[m] = ycR[m + 1]; yrR[m] = yrR[m + 1]; }
+  }
+}
+
 // ---- laminar transport of a point: Wilke mixture viscosity / conductivity and the inverse binary diffusion coefficients
 // (CReactiveNSVariable::SetPrimVar, variable_direct_reactive.cpp:1188-1228).  Its own kernel: together with the
 // temperature solve the code no longer fits the instruction cache.  Reads P, Y of the point as k_primitive left them, and
 // the temperature from mu[p]: the ignition overwrite of V[T] comes after SetPrimVar in the reference (:1013-1024).
 template <int NS>
-__global__ void __launch_bounds__(128) k_transport(const __grid_constant__ ChemC<NS> cc, const Dev d) {
+__global__ void __launch_bounds__(128, RX_TR_MINB) k_transport(const __grid_constant__ ChemC<NS> cc, const Dev d) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (p >= d.nPoint) return;
   double Y[NS];
@@ -58,18 +117,35 @@ __global__ void __launch_bounds__(128) k_transport(const __grid_constant__ ChemC
   for (int s = 0; s < NS; ++s) Y[s] = d.V[(V_Y + s) * d.np + p];
   const double T = d.mu[p], P = d.V[V_P * d.np + p];   // k_primitive parks the temperature SetPrimVar saw in mu[p]
   double mu, ka;
-  transport(cc, T, Y, mu, ka);
+  transport_dev(cc, T, Y, mu, ka);
   d.mu[p] = mu; d.kap[p] = ka;
   // 1/D_st of this point, upper triangle (GetDij_SM :751-766; /(V_ref*L_ref*1e4) variable_direct_reactive.cpp:1212;
   // cwiseInverse numerics_direct_reactive.cpp:1447).  Stored per point so that an edge needs one division per pair.
   const double T175 = 1.0e-3 * pow175(T);
   const double Patm = P * 1.0 / 101325.0;
+  const Recip r1e4 = frecip(1.0 * 1.0 * 1.0e4);
+  constexpr int NQ = NS * (NS + 1) / 2, QB = 5;   // 45 pairs in batches of five
+  static_assert(NQ % QB == 0, "pair batches");
   int s = 0, t = 0;
-#pragma unroll 3
-  for (int q = 0; q < NS * (NS + 1) / 2; ++q) {
-    const double D = (T175 / (Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t])) / (1.0 * 1.0 * 1.0e4);
-    d.rD[(size_t)q * d.np + p] = 1.0 / D;
-    if (++t == NS) { ++s; t = s; }
+#pragma unroll 1
+  for (int q0 = 0; q0 < NQ; q0 += QB) {
+    double den[QB], D[QB], rDv[QB];
+    bool bad = false;
+#pragma unroll
+    for (int b = 0; b < QB; ++b) {
+      den[b] = Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t];
+      if (++t == NS) { ++s; t = s; }
+    }
+#pragma unroll
+    for (int b = 0; b < QB; ++b) D[b] = fdiv(fdiv(T175, den[b], bad), r1e4, bad);
+#pragma unroll
+    for (int b = 0; b < QB; ++b) rDv[b] = fdiv(1.0, D[b], bad);
+    if (bad) {
+#pragma unroll
+      for (int b = 0; b < QB; ++b) rDv[b] = 1.0 / ((T175 / den[b]) / (1.0 * 1.0 * 1.0e4));
+    }
+#pragma unroll
+    for (int b = 0; b < QB; ++b) d.rD[(size_t)(q0 + b) * d.np + p] = rDv[b];
   }
 }
 

@@ -12,7 +12,6 @@
 // Matrix rows live in registers (slots < MREG) or in thread-private shared memory words (slot >= MREG).
 #pragma once
 #include "rx_kernels.cuh"
-#include <math_constants.h>
 
 namespace rx {
 
@@ -38,17 +37,6 @@ struct PairLane {
   __device__ __forceinline__ double fromOdd(double v) const { return __shfl_sync(VP_FULL, v, odd); }
   __device__ __forceinline__ double sel(double even, double oddv) const { return l ? oddv : even; }
 };
-
-// a / b.  CUDA's inline IEEE division leaves its fast path for a zero quotient, and zero numerators are common here (edge
-// components of axis-aligned edges, absent species); the quotient is then the signed zero, formed directly.
-__device__ __forceinline__ double div0(double a, double b) {
-  const bool z = (a == 0.0) && (fabs(b) > 0.0) && (fabs(b) < CUDART_INF);
-  double n = z ? 1.0 : a;
-  asm("" : "+d"(n));   // keeps the substitution: the compiler would otherwise divide the original numerator and select afterwards
-  const double q = n / b;
-  const double sz = __hiloint2double((__double2hiint(a) ^ __double2hiint(b)) & 0x80000000, 0);
-  return z ? sz : q;
-}
 
 // sum of nine values spread over the pair (a[k] = value of the lane's slot k) in Eigen redux order
 __device__ __forceinline__ double pair_redux(const PairLane& L, const double* a) {
@@ -141,15 +129,25 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       gi0[q] = g[pi]; gj0[q] = g[pj]; gi1[q] = g[np + pi]; gj1[q] = g[np + pj];
       vi[q] = val[pi]; vj[q] = val[pj];
     }
+    const Recip rd2 = frecip(dist2);   // one refined reciprocal serves the twelve quotients
+    bool bad = false;
+    double c0[6], c1[6];
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
-      double g0 = 0.5 * (gi0[q] + gj0[q]);
-      double g1 = 0.5 * (gi1[q] + gj1[q]);
+      const double g0 = 0.5 * (gi0[q] + gj0[q]);
+      const double g1 = 0.5 * (gi1[q] + gj1[q]);
       const double proj = (0.0 + g0 * e0) + g1 * e1;
       const double diff = vj[q] - vi[q];
-      g0 -= div0((proj - diff) * e0, dist2);
-      g1 -= div0((proj - diff) * e1, dist2);
-      G[q][0] = g0; G[q][1] = g1;
+      c0[q] = (proj - diff) * e0; c1[q] = (proj - diff) * e1;
+      G[q][0] = g0 - fdiv(c0[q], rd2, bad);
+      G[q][1] = g1 - fdiv(c1[q], rd2, bad);
+    }
+    if (bad) {
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+        G[q][0] = 0.5 * (gi0[q] + gj0[q]) - c0[q] / dist2;
+        G[q][1] = 0.5 * (gi1[q] + gj1[q]) - c1[q] / dist2;
+      }
     }
   }
   // rows T, u, v on both lanes
@@ -249,14 +247,29 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
       for (int c = 0; c < NS; ++c) sD[c] = ra[c] + rb[c];
       if (k < 4) fetchD(k + 1);
-      double tk = 0.0;
+      double tk = 0.0, dm[NS], gq[NS], tq[NS];
+      bool bad = false;
+      const double sx = smm * Xr;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) dm[c] = fdiv(2.0, sD[c], bad);   // D_rr takes part in the maximum only
 #pragma unroll
       for (int c = 0; c < NS; ++c) {
-        const double dm = 2.0 / sD[c];   // D_rr takes part in the maximum only
-        maxD = fmax(maxD, dm);
-        smA(k, c) = div0(smm * Xr, rho * cc.M[c] * dm);
-        const double qd = div0(Xs[c], dm);
-        tk = (c != r) ? tk + qd : tk;
+        gq[c] = fdiv(sx, rho * cc.M[c] * dm[c], bad);
+        tq[c] = fdiv(Xs[c], dm[c], bad);
+      }
+      if (bad) {
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {   // out-of-range values only
+          dm[c] = 2.0 / sD[c];
+          gq[c] = sx / (rho * cc.M[c] * dm[c]);
+          tq[c] = Xs[c] / dm[c];
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        maxD = fmax(maxD, dm[c]);
+        smA(k, c) = gq[c];
+        tk = (c != r) ? tk + tq[c] : tk;
       }
       smA(k, r) = tk;   // the diagonal word carries tmp_r until the second pass
 #pragma unroll
@@ -326,7 +339,12 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
         if (restarts++ == 0) it = 0;
       }
     }
-    const double beta = (rho_n / rho_old) * (alpha_b / w_b);
+    double beta;
+    {
+      bool bad = false;
+      const double q1 = fdiv(rho_n, rho_old, bad), q2 = fdiv(alpha_b, w_b, bad);
+      beta = bad ? (rho_n / rho_old) * (alpha_b / w_b) : q1 * q2;
+    }
     double pn[5], vn[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) { pn[k] = r[k] + beta * (p[k] - w_b * v[k]); w1[k] = invd[k] * pn[k]; }
