@@ -81,6 +81,21 @@ class TensorHaloState:
         self.fields[what][:, ids] = buf.view(self.fields[what].shape[0], -1)
 
 
+def global_rms(rms_local, n_local, n_owned, device):
+    """Residual norms of the whole job from the per-partition ones (SetResidual_RMS, solver_structure.cpp:172-187: sqrt of
+    the squares summed over all owned points / global owned point count): one all-reduce of nVar + 1 doubles.
+    A context normalises its own norms by its local point count `n_local` (the serial rule), which is undone here."""
+    import numpy as np
+    t = torch.empty(len(rms_local) + 1, dtype=torch.float64)
+    t[:-1] = torch.from_numpy(np.asarray(rms_local, dtype=np.float64) ** 2 * float(n_local))
+    t[-1] = float(n_owned)
+    t = t.to(device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t)
+    t = t.cpu()
+    return torch.sqrt(t[:-1] / t[-1]).numpy()
+
+
 def distributed_iterate(solver, ex, ext_iter, rk_alpha, last_rms=False):
     """One MultiGrid_Cycle on a partition, with the reference's exchange points: gradients after every Preprocessing
     (Set_MPI_Primitive_Gradient), conserved variables after every update (Set_MPI_Solution)."""
@@ -97,4 +112,6 @@ def distributed_iterate(solver, ex, ext_iter, rk_alpha, last_rms=False):
         ex.exchange(WHAT_SOLUTION)
     solver.Preprocessing(ext_iter, True, count_nonphysical=False)
     ex.exchange(WHAT_GRADIENT)
+    if last_rms and rms is not None:
+        rms = global_rms(rms, solver.nPoint, solver.nPointDomain, ex.device)
     return rms

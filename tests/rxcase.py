@@ -132,34 +132,54 @@ class Oracle:
 
     def __init__(self, case, opts_override=None):
         self.case = case
+        od = opts_dict(case)
+        if opts_override:
+            od.update(opts_override)
+        self._create(mesh_dict(case), chem_arrays(case), od)
+
+    @classmethod
+    def from_mesh(cls, mesh, chem, opts):
+        """Oracle on a flat mesh dict (the package's mesh builders) instead of a golden case."""
+        self = cls.__new__(cls)
+        self.case = None
+        self._create(mesh, chem, dict(opts))
+        return self
+
+    def _create(self, mesh, ca, od):
         self.lib = C.CDLL(build_oracle())
         L = self.lib
         L.rxo_create.restype = C.c_void_p
         L.rxo_preprocess.restype = C.c_int64
         self._keep = []
-        ca = chem_arrays(case)
+        ca = {k: (np.ascontiguousarray(v, dtype=np.float64) if isinstance(v, np.ndarray) else v) for k, v in ca.items()}
         ch = _Chem(ca["Ns"], ca["Nr"], ca["nKnots"], *[_p(ca[n[0]]) for n in _Chem._fields_[3:]])
         self._keep.append(ca)
         self.chem_struct = ch
-        mks = marker_list(case)
-        arr = (_Marker * len(mks))()
+        Ns = ca["Ns"]
+        mks = []
+        for m in mesh["markers"]:
+            mks.append(dict(kind=int(m["kind"]), node=np.ascontiguousarray(m["node"], dtype=np.int64),
+                            normalNeighbor=np.ascontiguousarray(m["normalNeighbor"], dtype=np.int64),
+                            normal=np.ascontiguousarray(m["normal"], dtype=np.float64).reshape(-1, 2),
+                            T=float(m.get("T", 0.0)), Vmag=float(m.get("Vmag", 0.0)), dir=list(m.get("dir", [0.0, 0.0])),
+                            Ys=np.ascontiguousarray(m.get("Ys", np.zeros(Ns)), dtype=np.float64), P=float(m.get("P", 0.0)),
+                            Twall=float(m.get("Twall", 0.0))))
+        arr = (_Marker * max(len(mks), 1))()
         for i, d in enumerate(mks):
             arr[i] = _Marker(d["kind"], len(d["node"]), _p(d["node"], C.c_int64), _p(d["normalNeighbor"], C.c_int64),
                              _p(d["normal"]), d["T"], d["Vmag"], (C.c_double * 2)(*d["dir"]), _p(d["Ys"]), d["P"], d["Twall"])
         self._keep.append(mks)
-        g = {k: np.ascontiguousarray(case[k]) for k in
-             ["geo_edge_nodes", "geo_edge_normal", "geo_coord", "geo_volume", "geo_nb_ptr", "geo_nb_point"]}
+        g = dict(en=np.ascontiguousarray(mesh["edgeNodes"], dtype=np.int64), nrm=np.ascontiguousarray(mesh["edgeNormal"], dtype=np.float64),
+                 xy=np.ascontiguousarray(mesh["coord"], dtype=np.float64), vol=np.ascontiguousarray(mesh["volume"], dtype=np.float64),
+                 ptr=np.ascontiguousarray(mesh["nbPtr"], dtype=np.int64), nb=np.ascontiguousarray(mesh["nbPoint"], dtype=np.int64))
         self._keep.append(g)
-        mesh = _Mesh(case.nPoint, case.nPointDomain, case.nEdge, _p(g["geo_edge_nodes"], C.c_int64), _p(g["geo_edge_normal"]),
-                     _p(g["geo_coord"]), _p(g["geo_volume"]), _p(g["geo_nb_ptr"], C.c_int64), _p(g["geo_nb_point"], C.c_int64),
-                     len(mks), arr)
-        od = opts_dict(case)
-        if opts_override:
-            od.update(opts_override)
+        nP, nE = int(mesh["nPoint"]), int(g["en"].shape[0])
+        ms = _Mesh(nP, int(mesh["nPointDomain"]), nE, _p(g["en"], C.c_int64), _p(g["nrm"]), _p(g["xy"]), _p(g["vol"]),
+                   _p(g["ptr"], C.c_int64), _p(g["nb"], C.c_int64), len(mks), arr)
         self.opts = od
         o = _Opts(**od)
-        self.ctx = C.c_void_p(L.rxo_create(C.byref(mesh), C.byref(ch), C.byref(o)))
-        self.nP, self.nVar, self.nPrim, self.nGrad = case.nPoint, case.nVar, case.nPrim, case.nGrad
+        self.ctx = C.c_void_p(L.rxo_create(C.byref(ms), C.byref(ch), C.byref(o)))
+        self.nP, self.nVar, self.nPrim, self.nGrad = nP, Ns + 4, Ns + 7, Ns + 4
 
     def __del__(self):
         try:
