@@ -263,6 +263,30 @@ int rx_set_stream(rx_ctx* c, void* s) { c->stream = (cudaStream_t)s; return RX_O
 int rx_synchronize(rx_ctx* c) { RX_CK(cudaStreamSynchronize(c->stream)); return RX_OK; }
 int64_t rx_launch_count(rx_ctx* c) { return c->launches; }
 
+int rx_fp64_peak(rx_ctx* c, double* tflops) {
+  int nsm = 0;
+  RX_CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device));
+  double* sink = nullptr;
+  RX_CK(cudaMalloc(&sink, sizeof(double)));
+  const int iters = 1 << 15, blocks = nsm * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  RX_CK(cudaEventCreate(&e0)); RX_CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {   // rep 0 warms up
+    RX_CK(cudaEventRecord(e0, c->stream));
+    k_fp64_peak<<<blocks, threads, 0, c->stream>>>(iters, 1.0000001, sink);
+    RX_CK(cudaEventRecord(e1, c->stream));
+    RX_CK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    RX_CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+    c->launches++;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+  if (tflops) *tflops = 2.0 * 8.0 * (double)iters * (double)blocks * threads / (best * 1e-3) / 1e12;
+  return RX_OK;
+}
+
 int rx_set_solution(rx_ctx* c, const double* U) { return upload_aos(c, U, c->d.U, c->nVar); }
 int rx_set_turbulence(rx_ctx* c, const double* t) { return upload_aos(c, t, c->d.turb, 6); }
 int rx_set_temperature(rx_ctx* c, const double* T) { return upload_aos(c, T, c->d.V + V_T * c->d.np, 1); }

@@ -319,6 +319,19 @@ __global__ void __launch_bounds__(256) k_rms_finish(const double* __restrict__ p
   }
 }
 
+// ---- FP64 roof: eight independent DFMA chains per thread, nothing else in the loop
+__global__ void __launch_bounds__(256) k_fp64_peak(int iters, double a, double* sink) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  const double b = 1.0e-9;
+#pragma unroll 4
+  for (int i = 0; i < iters; ++i) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == 12345.678) *sink = s;   // keeps the chains alive
+}
+
 // ---- halo plumbing: gather/scatter listed points of U (what=0) or of [grad, X, V, transport] (what=1)
 __global__ void k_pack(const double* __restrict__ soa, long long stride, int nv, long long n, const long long* __restrict__ pts, double* __restrict__ buf) {
   long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;

@@ -71,7 +71,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
-           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count"]
+           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak"]
 
 _lib = None
 
@@ -226,6 +226,12 @@ class CReactiveNSSolverGPU:
 
     def Synchronize(self): self._ck(self.lib.rx_synchronize(self.ctx))
     def LaunchCount(self): return int(self.lib.rx_launch_count(self.ctx))
+
+    def Fp64Peak(self):
+        """Measured FP64 TFLOP/s of the device (DFMA loop), the compute roof of the viscous / source kernels."""
+        v = C.c_double(0.0)
+        self._ck(self.lib.rx_fp64_peak(self.ctx, C.byref(v)))
+        return float(v.value)
 
     # ---- the stage API used by the parity tests (same names as tests/rxcase.Oracle)
     set_solution = SetSolution; set_temperature = SetTemperature; set_turbulence = SetTurbulence

@@ -131,9 +131,14 @@ int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, cons
 int rx_halo_width(rx_ctx*, int what);
 
 /* measurement hook: average device time in ms (CUDA events on the context's stream) of `reps` launches of one kernel on the
- * current state; which = 0 fused edge flux, 1 convective edge flux, 2 accumulation+source, 3 cons->prim+transport,
- * 4 gradient, 5 source, 6 explicit update */
+ * current state; which = 0 viscous edge flux (convective if inviscid), 1 convective edge flux, 2 accumulation+source,
+ * 3 cons->prim, 4 gradient, 5 source, 6 explicit update, 7 laminar transport */
 int rx_kernel_time(rx_ctx*, int which, int reps, double* msAvg);
+
+/* measurement hook: FP64 throughput of the device the context lives on, from a register-resident DFMA loop (8 independent
+ * chains per thread, every SM filled), in TFLOP/s with one fused multiply-add counted as two operations.  The compute
+ * roof of the viscous and source kernels (MEASURED_PEAKS.json carries no FP64 entry). */
+int rx_fp64_peak(rx_ctx*, double* tflops);
 
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t rx_launch_count(rx_ctx*);

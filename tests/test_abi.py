@@ -12,7 +12,7 @@ from rxcase import ROOT, load_package
 def declared_symbols():
     txt = open(os.path.join(ROOT, "include", "rx_cuda.h")).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    return sorted(set(re.findall(r"\b(rx_[a-z_]+)\s*\(", txt)))
+    return sorted(set(re.findall(r"\b(rx_[a-z0-9_]+)\s*\(", txt)))
 
 
 def test_library_exports_every_declared_symbol():
