@@ -1,0 +1,271 @@
+// CReactiveNSSolverGPU — see the header.  Compiled with the reference's include paths (oracle/build_ref.sh does so, with
+// -fno-access-control for the private tables of Framework::ReactingModelLibrary; upstream would add one `friend` line).
+#include "CReactiveNSSolverGPU.hpp"
+
+#include "reacting_model_library.hpp"
+
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+
+namespace {
+int env_int(const char* name, int dflt) {
+  const char* s = std::getenv(name);
+  return s ? std::atoi(s) : dflt;
+}
+}  // namespace
+
+void CReactiveNSSolverGPU::Check(int rc, const char* where) {
+  if (rc == RX_OK) return;
+  // the reference reports trouble on this path by throwing (solver_direct_reactive.cpp:2772,2861,5384)
+  throw std::runtime_error(std::string(where) + ": " + rx_last_error(ctx) + " (librx_cuda, status " + std::to_string(rc) + ")");
+}
+
+CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh)
+    : CReactiveNSSolver(geometry, config, iMesh) {
+  using namespace Framework;
+  mirror = env_int("SU2_RX_MIRROR", 1);
+  const unsigned short kind = config->GetKind_Solver();
+  ransMode = (kind == REACTIVE_RANS);
+  viscousMode = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
+  if (implicit) throw std::runtime_error("CReactiveNSSolverGPU: EULER_IMPLICIT is not on the CUDA path (explicit Euler / RK only)");
+  if (second_order || limiter) throw std::runtime_error("CReactiveNSSolverGPU: 2nd-order reconstruction / limiters are not on the CUDA path yet");
+  if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
+
+  // ---- geometry -> rx_mesh (flat arrays; dual_grid_structure.hpp:140,747,884)
+  const unsigned long nEdge = geometry->GetnEdge();
+  std::vector<int64_t> en(2 * nEdge), nbPtr(nPoint + 1, 0), nbPt;
+  std::vector<double> enrm(2 * nEdge), xy(2 * nPoint), vol(nPoint);
+  for (unsigned long e = 0; e < nEdge; ++e) {
+    en[2 * e] = geometry->edge[e]->GetNode(0); en[2 * e + 1] = geometry->edge[e]->GetNode(1);
+    enrm[2 * e] = geometry->edge[e]->GetNormal()[0]; enrm[2 * e + 1] = geometry->edge[e]->GetNormal()[1];
+  }
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    xy[2 * p] = geometry->node[p]->GetCoord(0); xy[2 * p + 1] = geometry->node[p]->GetCoord(1);
+    vol[p] = geometry->node[p]->GetVolume();
+    for (unsigned short k = 0; k < geometry->node[p]->GetnPoint(); ++k) nbPt.push_back(geometry->node[p]->GetPoint(k));
+    nbPtr[p + 1] = (int64_t)nbPt.size();
+  }
+  const unsigned short nMk = config->GetnMarker_All();
+  std::vector<rx_marker> mk(nMk);
+  std::vector<std::vector<int64_t>> vn(nMk), vnn(nMk);
+  std::vector<std::vector<double>> vnrm(nMk), vys(nMk);
+  for (unsigned short m = 0; m < nMk; ++m) {
+    const unsigned long nv = geometry->nVertex[m];
+    vn[m].resize(nv); vnn[m].resize(nv); vnrm[m].resize(2 * nv); vys[m].assign(nSpecies, 0.0);
+    for (unsigned long v = 0; v < nv; ++v) {
+      vn[m][v] = geometry->vertex[m][v]->GetNode();
+      vnn[m][v] = geometry->vertex[m][v]->GetNormal_Neighbor();
+      vnrm[m][2 * v] = geometry->vertex[m][v]->GetNormal()[0]; vnrm[m][2 * v + 1] = geometry->vertex[m][v]->GetNormal()[1];
+    }
+    rx_marker& r = mk[m];
+    r = rx_marker{};
+    r.nVertex = (int)nv; r.node = vn[m].data(); r.normalNeighbor = vnn[m].data(); r.normal = vnrm[m].data(); r.Ys = vys[m].data();
+    const std::string tag = config->GetMarker_All_TagBound(m);
+    switch (config->GetMarker_All_KindBC(m)) {
+      case INLET_FLOW:
+        if (config->GetKind_Inlet() != TEMPERATURE_IMPOSE) throw std::runtime_error("CReactiveNSSolverGPU: inlet type other than TEMPERATURE_IMPOSE");
+        r.kind = RX_BC_INLET_TEMPERATURE_IMPOSE;
+        r.T = config->GetInlet_Ttotal(tag); r.Vmag = config->GetInlet_Ptotal(tag);
+        r.dir[0] = config->GetInlet_FlowDir(tag)[0]; r.dir[1] = config->GetInlet_FlowDir(tag)[1];
+        for (unsigned short s = 0; s < nSpecies; ++s) vys[m][s] = config->GetInlet_MassFrac(tag)[s];
+        break;
+      case OUTLET_FLOW: r.kind = RX_BC_OUTLET; r.P = config->GetOutlet_Pressure(tag); break;
+      case ISOTHERMAL: r.kind = RX_BC_ISOTHERMAL; r.Twall = config->GetIsothermal_Temperature(tag); break;
+      case SEND_RECEIVE: case INTERNAL_BOUNDARY: r.kind = RX_BC_NONE; break;
+      default: throw std::runtime_error("CReactiveNSSolverGPU: boundary condition of marker " + tag + " is not on the CUDA path");
+    }
+  }
+  rx_mesh mesh{};
+  mesh.nPoint = (int64_t)nPoint; mesh.nPointDomain = (int64_t)nPointDomain; mesh.nEdge = (int64_t)nEdge;
+  mesh.edgeNodes = en.data(); mesh.edgeNormal = enrm.data(); mesh.coord = xy.data(); mesh.volume = vol.data();
+  mesh.nbPtr = nbPtr.data(); mesh.nbPoint = nbPt.data(); mesh.nMarker = nMk; mesh.markers = mk.data();
+
+  // ---- chemistry tables of the library object the reference solver already set up (reacting_model_library.hpp:655-766)
+  ReactingModelLibrary& lib = *std::dynamic_pointer_cast<ReactingModelLibrary>(library);
+  const int Ns = lib.nSpecies, Nr = lib.nReactions;
+  typedef decltype(lib.Mu_Spline) SplTab;
+  const SplTab* tabs[5] = {&lib.Mu_Spline, &lib.Kappa_Spline, &lib.Cp_Spline, &lib.Enth_Spline, &lib.Entr_Spline};
+  const size_t nK = std::get<0>(lib.Mu_Spline[0]).size();
+  std::vector<double> X(std::get<0>(lib.Mu_Spline[0])), Y(5 * Ns * nK), Y2(5 * Ns * nK);
+  for (int t = 0; t < 5; ++t)
+    for (int s = 0; s < Ns; ++s) {
+      const auto& tp = (*tabs[t])[s];
+      for (size_t k = 0; k < nK; ++k) {
+        Y[(t * Ns + s) * nK + k] = std::get<1>(tp)[k];
+        Y2[(t * Ns + s) * nK + k] = std::get<2>(tp).data()[k];   // the last second derivative lives past size() (spline.cpp:54)
+      }
+    }
+  std::vector<double> rev(Nr ? Nr : 1, 0.0), avb(rev), Ab(rev), Bb(rev), Tb(rev);
+  std::vector<double> nuR(Nr * Ns + 1), nuP(nuR), eR(nuR), eP(nuR);
+  for (int r = 0; r < Nr; ++r) {
+    rev[r] = lib.Reversible_Reactions[r];
+    if (lib.Available_Backward_Rate.count(r)) { avb[r] = 1; Ab[r] = lib.As_back[r]; Bb[r] = lib.Betas_back[r]; Tb[r] = lib.Temps_Activation_back[r]; }
+    for (int s = 0; s < Ns; ++s) {
+      nuR[r * Ns + s] = lib.Stoich_Coeffs_Reactants(s, r); nuP[r * Ns + s] = lib.Stoich_Coeffs_Products(s, r);
+      eR[r * Ns + s] = lib.Stoich_Coeffs_Reactants_Exp(r, s); eP[r * Ns + s] = lib.Stoich_Coeffs_Products_Exp(r, s);
+    }
+  }
+  rx_chem chem{};
+  chem.Ns = Ns; chem.Nr = Nr; chem.nKnots = (int)nK;
+  chem.mMasses = lib.mMasses.data(); chem.diffVol = lib.Diff_Volumes.data(); chem.x = X.data(); chem.y = Y.data(); chem.y2 = Y2.data();
+  chem.As = lib.As.data(); chem.Betas = lib.Betas.data(); chem.Ta = lib.Temps_Activation.data();
+  chem.reversible = rev.data(); chem.availBack = avb.data(); chem.AsB = Ab.data(); chem.BetasB = Bb.data(); chem.TaB = Tb.data();
+  chem.nuR = nuR.data(); chem.nuP = nuP.data(); chem.expR = eR.data(); chem.expP = eP.data();
+
+  // ---- constants the solver / numerics constructors read from CConfig (numerics_direct_reactive.cpp:17-19,395-399,1417,1690-1694)
+  rx_opts o{};
+  o.viscous = viscousMode; o.rans = ransMode; o.leastSquares = least_squares ? 1 : 0;
+  o.mInfty = config->GetMach(); o.cfl = config->GetCFL(iMesh); o.maxDt = config->GetMax_DeltaTime();
+  o.Tmin = config->GetTemperatureMin(); o.Tmax = config->GetTemperatureMax(); o.clipT = config->GetClipping_Temp() ? 1 : 0;
+  o.ignition = config->GetIgnition() ? 1 : 0; o.ignitionIter = (int64_t)config->GetIgnitionIter(); o.ignitionT = config->GetIgnitionTemperature();
+  o.fuelIndex = config->GetFuelIndex(); o.oxidizerIndex = config->GetOxidizerIndex();
+  o.prandtlLam = config->GetPrandtl_Lam(); o.prandtlTurb = config->GetPrandtl_Turb(); o.lewisTurb = config->GetLewis_Turb();
+  o.cMu = config->Get_Cmu(); o.pasrLb = config->Get_PaSR_LB(); o.tkeInf = ransMode ? GetTke_Inf() : 0.0;
+  o.device = env_int("SU2_RX_DEVICE", 0);
+
+  const int rc = rx_create(&ctx, &mesh, &chem, &o);
+  if (rc != RX_OK) throw std::runtime_error(std::string("CReactiveNSSolverGPU: ") + rx_last_error(nullptr));
+  bufU.resize((size_t)nPoint * nVar); bufR.resize((size_t)nPoint * nVar);
+  bufV.resize((size_t)nPoint * nPrimVar); bufAux.resize((size_t)nPoint * 6);
+  bufGrad.resize((size_t)nPoint * nPrimVarGrad * nDim); bufT.resize((size_t)nPoint * 6);
+}
+
+CReactiveNSSolverGPU::~CReactiveNSSolverGPU() { rx_destroy(ctx); }
+
+// node[] -> device: conserved variables and the previous temperature (start value of the secant solve)
+void CReactiveNSSolverGPU::UploadState() {
+  std::vector<double> T(nPoint);
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    for (unsigned short v = 0; v < nVar; ++v) bufU[p * nVar + v] = node[p]->GetSolution(v);
+    T[p] = node[p]->GetPrimitive(T_INDEX_PRIM);
+  }
+  Check(rx_set_solution(ctx, bufU.data()), "rx_set_solution");
+  Check(rx_set_temperature(ctx, T.data()), "rx_set_temperature");
+  hostDirty = false;
+}
+
+// what the viscous closure, the time step and the PaSR source read from CTurbSSTSolver (solver_direct_reactive.cpp:5333-5353, :2829)
+void CReactiveNSSolverGPU::UploadTurbulence(CSolver** solver_container) {
+  CSolver* ts = solver_container[TURB_SOL];
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    double* t = &bufT[p * 6];
+    t[0] = ts->node[p]->GetmuT(); t[1] = ts->node[p]->GetSolution(0); t[2] = ts->node[p]->GetSolution(1);
+    t[3] = ts->node[p]->GetGradient()[0][0]; t[4] = ts->node[p]->GetGradient()[0][1]; t[5] = ts->node[p]->Get_Sigmak();
+  }
+  Check(rx_set_turbulence(ctx, bufT.data()), "rx_set_turbulence");
+}
+
+void CReactiveNSSolverGPU::MirrorPrimitives() {
+  Check(rx_get_primitive(ctx, bufV.data(), bufAux.data(), viscousMode ? bufGrad.data() : nullptr), "rx_get_primitive");
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    CReactiveNSVariable* n = static_cast<CReactiveNSVariable*>(node[p]);
+    su2double* V = n->GetPrimitive();
+    for (unsigned short v = 0; v < nPrimVar; ++v) V[v] = bufV[p * nPrimVar + v];
+    const double* a = &bufAux[p * 6];
+    n->Cp = a[0];
+    n->GetdPdU()[nDim + 1] = a[1] - 1.0;
+    if (ransMode) n->SetEddyViscosity(bufT[p * 6]);   // SetPrimVar(eddy_visc, ...) stores it in the flow variable (:1193)
+    if (viscousMode) {
+      n->SetLaminarViscosity(a[2]); n->SetThermalConductivity(a[3]);
+      n->GetVorticity()[0] = 0.0; n->GetVorticity()[1] = 0.0; n->GetVorticity()[2] = a[4];
+      n->StrainMag = a[5];
+      su2double** g = n->GetGradient_Primitive();
+      for (unsigned short v = 0; v < nPrimVarGrad; ++v)
+        for (unsigned short d = 0; d < nDim; ++d) g[v][d] = bufGrad[(p * nPrimVarGrad + v) * nDim + d];
+    }
+  }
+}
+
+void CReactiveNSSolverGPU::MirrorResidual() {
+  Check(rx_get_residual(ctx, bufR.data()), "rx_get_residual");
+  for (unsigned long p = 0; p < nPoint; ++p) LinSysRes.SetBlock(p, &bufR[p * nVar]);
+}
+
+void CReactiveNSSolverGPU::MirrorTimeStep() {
+  std::vector<double> dt((size_t)nPoint * 3);
+  Check(rx_get_dt(ctx, dt.data()), "rx_get_dt");
+  for (unsigned long p = 0; p < nPointDomain; ++p) {
+    node[p]->SetDelta_Time(dt[p * 3]);
+    node[p]->SetMax_Lambda_Inv(dt[p * 3 + 1]);
+    if (viscousMode) node[p]->SetMax_Lambda_Visc(dt[p * 3 + 2]);
+  }
+}
+
+void CReactiveNSSolverGPU::Preprocessing(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh,
+                                         unsigned short iRKStep, unsigned short RunTime_EqSystem, bool Output) {
+  extIter = config->GetExtIter();
+  if (hostDirty) UploadState();
+  if (ransMode) UploadTurbulence(solver_container);
+  int64_t bad = 0;
+  const bool count = (config->GetConsole_Output_Verb() == VERB_HIGH);
+  Check(rx_preprocess(ctx, (int64_t)extIter, Output ? 1 : 0, count ? &bad : nullptr), "rx_preprocess");
+  if (count && iMesh == MESH_0) config->SetNonphysical_Points((unsigned long)bad);
+  if (mirror >= 1) MirrorPrimitives();
+  if (mirror >= 2 && !Output) MirrorResidual();
+}
+
+void CReactiveNSSolverGPU::SetTime_Step(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh,
+                                        unsigned long Iteration) {
+  // MultiGrid_Cycle calls the (non-virtual) CSolver::Set_OldSolution immediately before SetTime_Step at RK stage 0
+  // (integration_time.cpp:158-163); the device copy of U_old is taken here, at the same point of the sequence.
+  Check(rx_set_old_solution(ctx), "rx_set_old_solution");
+  Check(rx_time_step(ctx), "rx_time_step");
+  if (mirror >= 2 || (mirror >= 1 && ransMode)) MirrorTimeStep();   // the SST implicit step uses the flow time step
+}
+
+void CReactiveNSSolverGPU::Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) {
+  Check(rx_residual_conv(ctx), "rx_residual_conv");
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::Viscous_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short, unsigned short) {
+  Check(rx_residual_visc(ctx), "rx_residual_visc");
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::Source_Residual(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) {
+  Check(rx_residual_source(ctx), "rx_residual_source");
+  if (mirror >= 2) MirrorResidual();
+}
+// the state imposed at the boundary is what CTurbSSTSolver::BC_Inlet / BC_Outlet read as GetCharacPrimVar
+void CReactiveNSSolverGPU::MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker) {
+  const unsigned long nv = geometry->nVertex[val_marker];
+  std::vector<double> V((size_t)nv * nPrimVar);
+  Check(rx_get_bc_state(ctx, val_marker, V.data()), "rx_get_bc_state");
+  for (unsigned long k = 0; k < nv; ++k) {
+    if (!geometry->node[geometry->vertex[val_marker][k]->GetNode()]->GetDomain()) continue;
+    for (unsigned short v = 0; v < nPrimVar; ++v) CharacPrimVar[val_marker][k][v] = V[k * nPrimVar + v];
+  }
+}
+void CReactiveNSSolverGPU::BC_Inlet(CGeometry* geometry, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
+  if (mirror >= 1 && ransMode) MirrorBoundaryState(geometry, val_marker);
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_Outlet(CGeometry* geometry, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
+  if (mirror >= 1 && ransMode) MirrorBoundaryState(geometry, val_marker);
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
+  if (mirror >= 2) MirrorResidual();
+}
+
+// U = clip(U_old - alpha * Res * dt / Vol), residual norms; mirrors what output, restart and the host-side
+// CSolver::Set_OldSolution read (solver_direct_reactive.cpp:2414-2493, solver_structure.cpp:172-260)
+void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha) {
+  std::vector<double> rms(nVar);
+  Check(rx_update_explicit(ctx, alpha, rms.data()), "rx_update_explicit");
+  for (unsigned short v = 0; v < nVar; ++v) {
+    if (rms[v] != rms[v]) throw std::runtime_error("SU2 has diverged (NaN detected in the residual norms)");
+    SetRes_RMS(v, rms[v]);
+    SetRes_Max(v, 0.0, 0);
+  }
+  Check(rx_get_solution(ctx, bufU.data()), "rx_get_solution");
+  for (unsigned long p = 0; p < nPoint; ++p)
+    for (unsigned short v = 0; v < nVar; ++v) node[p]->SetSolution(v, bufU[p * nVar + v]);
+}
+void CReactiveNSSolverGPU::ExplicitEuler_Iteration(CGeometry* geometry, CSolver**, CConfig*) { Update(geometry, 1.0); }
+void CReactiveNSSolverGPU::ExplicitRK_Iteration(CGeometry* geometry, CSolver**, CConfig* config, unsigned short iRKStep) {
+  Update(geometry, config->Get_Alpha_RKStep(iRKStep));
+}

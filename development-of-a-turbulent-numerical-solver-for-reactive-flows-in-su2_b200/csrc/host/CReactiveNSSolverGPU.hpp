@@ -1,0 +1,66 @@
+// CReactiveNSSolverGPU — host side of the drop-in: a CSolver the reference's driver, integration and output code use
+// unchanged, whose residual path runs in librx_cuda.so (include/rx_cuda.h).
+//
+// It derives from the reference's CReactiveNSSolver (SU2_CFD/include/solver_reactive.hpp:398-560), so construction
+// (free-stream state, node[] allocation, limits, restart load) is the reference's own; the overrides below replace the
+// virtuals that MultiGrid_Cycle / Space_Integration / Time_Integration call (integration_time.cpp:143-181,
+// integration_structure.cpp:66-190, :307-330), with the signatures of solver_reactive.hpp.  The CNumerics* arguments are
+// accepted and ignored: the numerics' constants were read from CConfig at construction, as the numerics constructors do.
+//
+// This translation unit is compiled WITH the reference's headers and linked into its SU2_CFD; nothing of
+// the reference is copied here.
+#pragma once
+#include "solver_reactive.hpp"
+#include "rx_cuda.h"
+
+#include <vector>
+
+class CReactiveNSSolverGPU : public CReactiveNSSolver {
+ public:
+  // mirror levels (env SU2_RX_MIRROR, default 1):
+  //   0  conserved variables and residual norms after each update (what output and restart read)
+  //   1  + primitives, gradients, transport, vorticity/strain after each Preprocessing (what CTurbSSTSolver reads)
+  //   2  + LinSysRes after each residual / boundary stage and the time steps (stage-by-stage parity dumps)
+  CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh);
+  ~CReactiveNSSolverGPU() override;
+
+  void Preprocessing(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh,
+                     unsigned short iRKStep, unsigned short RunTime_EqSystem, bool Output) override;
+  void SetTime_Step(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh,
+                    unsigned long Iteration) override;
+  void Upwind_Residual(CGeometry* geometry, CSolver** solver_container, CNumerics* numerics, CConfig* config,
+                       unsigned short iMesh) override;
+  void Viscous_Residual(CGeometry* geometry, CSolver** solver_container, CNumerics* numerics, CConfig* config,
+                        unsigned short iMesh, unsigned short iRKStep) override;
+  void Source_Residual(CGeometry* geometry, CSolver** solver_container, CNumerics* numerics, CNumerics* second_numerics,
+                       CConfig* config, unsigned short iMesh) override;
+  void BC_Inlet(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics, CNumerics* visc_numerics,
+                CConfig* config, unsigned short val_marker) override;
+  void BC_Outlet(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics, CNumerics* visc_numerics,
+                 CConfig* config, unsigned short val_marker) override;
+  void BC_Isothermal_Wall(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics,
+                          CNumerics* visc_numerics, CConfig* config, unsigned short val_marker) override;
+  void ExplicitEuler_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config) override;
+  void ExplicitRK_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config,
+                            unsigned short iRKStep) override;
+
+  // node[]->Solution was changed on the host (restart, initial condition): upload before the next stage
+  void MarkHostSolutionDirty() { hostDirty = true; }
+  rx_ctx* Context() { return ctx; }
+
+ private:
+  void Check(int rc, const char* where);
+  void UploadState();
+  void UploadTurbulence(CSolver** solver_container);
+  void MirrorPrimitives();
+  void MirrorResidual();
+  void MirrorTimeStep();
+  void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
+  void Update(CGeometry* geometry, double alpha);
+
+  rx_ctx* ctx = nullptr;
+  bool hostDirty = true, ransMode = false, viscousMode = true;
+  int mirror = 1;
+  unsigned long extIter = 0;
+  std::vector<double> bufU, bufV, bufAux, bufGrad, bufR, bufT;
+};

@@ -242,6 +242,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
       node[v] = (int)s.node[v]; nn[v] = (int)s.normalNeighbor[v]; nx[v] = s.normal[2 * v]; ny[v] = s.normal[2 * v + 1];
     }
     md.node = dupload(c, node); md.nn = dupload(c, nn); md.nx = dupload(c, nx); md.ny = dupload(c, ny);
+    md.ghost = dalloc<double>(c, (size_t)std::max(s.nVertex, 1) * (7 + Ns));
     md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall;
     for (int q = 0; q < 16; ++q) md.Ys[q] = (s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
     c->markers.push_back(md);
@@ -392,17 +393,38 @@ int rx_residual_source(rx_ctx* c) {
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
-int rx_bc(rx_ctx* c) {
+static void launch_bc(rx_ctx* c, const MarkerDev& m) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
-  for (const MarkerDev& m : c->markers) {
-    if (!m.nVertex) continue;
-    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
-    else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
-  }
+  if (!m.nVertex) return;
+  if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  else if (m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+}
+int rx_bc(rx_ctx* c) {
   for (const MarkerDev& m : c->markers)
-    if (m.nVertex && m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET) launch_bc(c, m);
+  for (const MarkerDev& m : c->markers)
+    if (m.kind == RX_BC_ISOTHERMAL) launch_bc(c, m);
   RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_bc_marker(rx_ctx* c, int marker) {
+  if (marker < 0 || marker >= (int)c->markers.size()) { c->err = "rx_bc_marker: marker index out of range"; return RX_ERR_ARG; }
+  launch_bc(c, c->markers[marker]);
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_get_bc_state(rx_ctx* c, int marker, double* V) {
+  if (marker < 0 || marker >= (int)c->markers.size()) { c->err = "rx_get_bc_state: marker index out of range"; return RX_ERR_ARG; }
+  const MarkerDev& m = c->markers[marker];
+  if (!m.nVertex) return RX_OK;
+  const int np_ = c->nPrim;
+  std::vector<double> soa((size_t)m.nVertex * np_);
+  RX_CK(cudaMemcpyAsync(soa.data(), m.ghost, soa.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < m.nVertex; ++k)
+    for (int v = 0; v < np_; ++v) V[(size_t)k * np_ + v] = soa[(size_t)v * m.nVertex + k];
   return RX_OK;
 }
 int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {

@@ -181,6 +181,8 @@ __global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<N
   Vg[V_A] = sqrt(g * Rg * m.T);
 #pragma unroll
   for (int s = 0; s < NS; ++s) Vg[V_Y + s] = Ys[s];
+#pragma unroll
+  for (int v = 0; v < 7 + NS; ++v) m.ghost[(size_t)v * m.nVertex + k] = Vg[v];   // CharacPrimVar (:3274), read by the turbulence BCs
   boundary_fluxes<NS>(cc, o, d, i, Vg, nx, ny);
 }
 // BC_Outlet (solver_direct_reactive.cpp:3808-4123)
@@ -229,6 +231,8 @@ __global__ void __launch_bounds__(64) k_bc_outlet(const __grid_constant__ ChemC<
 #pragma unroll
     for (int s = 0; s < NS; ++s) Vo[V_Y + s] = Ys[s];
   }
+#pragma unroll
+  for (int v = 0; v < 7 + NS; ++v) m.ghost[(size_t)v * m.nVertex + k] = Vo[v];   // CharacPrimVar (:3844)
   boundary_fluxes<NS>(cc, o, d, i, Vo, Nx, Ny);
 }
 // BC_Isothermal_Wall (solver_direct_reactive.cpp:5393-5711), explicit, static wall

@@ -71,7 +71,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
-           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak"]
+           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state"]
 
 _lib = None
 
@@ -196,6 +196,7 @@ class CReactiveNSSolverGPU:
     def Source_Residual(self): self._ck(self.lib.rx_residual_source(self.ctx))
     def Residual_All(self): self._ck(self.lib.rx_residual_all(self.ctx))
     def BC_All(self): self._ck(self.lib.rx_bc(self.ctx))
+    def BC_Marker(self, marker): self._ck(self.lib.rx_bc_marker(self.ctx, int(marker)))
 
     def KernelTime(self, which, reps=5):
         ms = C.c_double(0.0)

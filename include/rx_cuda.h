@@ -107,6 +107,8 @@ int rx_residual_conv(rx_ctx*);                            /* Upwind_Residual :25
 int rx_residual_visc(rx_ctx*);                            /* Viscous_Residual :5305 */
 int rx_residual_source(rx_ctx*);                          /* Source_Residual :2792 */
 int rx_bc(rx_ctx*);                                       /* BC_Inlet :3226, BC_Outlet :3808, then BC_Isothermal_Wall :5393 (integration_structure.cpp:89-190) */
+int rx_bc_marker(rx_ctx*, int marker);                    /* one BC_* call of the reference: the boundary condition of marker `marker` (order is the caller's) */
+int rx_get_bc_state(rx_ctx*, int marker, double* V /* [nVertex][nPrim] */);   /* state imposed by the last inlet/outlet BC of the marker = CharacPrimVar (:3274, :3844), read by the turbulence BCs */
 int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */
 
 int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + Source residual in one pass (same sums, same order) */

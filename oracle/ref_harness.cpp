@@ -14,6 +14,12 @@
 #include "../../SU2_CFD/include/driver_structure.hpp"
 #include "../../SU2_CFD/include/solver_reactive.hpp"
 #include "../../Common/include/Framework/reacting_model_library.hpp"
+#ifdef RX_WITH_GPU
+// ref_harness_gpu: the same driver loop and dumps, with the flow solver object replaced by the CUDA-backed subclass
+// (package csrc/host/CReactiveNSSolverGPU) when SU2_RX_BACKEND=cuda — the drop-in demonstration of INTEGRATION.md.
+#include "CReactiveNSSolverGPU.hpp"
+#include <cstring>
+#endif
 #include <cstdio>
 #include <cstdint>
 #include <string>
@@ -383,6 +389,13 @@ int main(int argc, char** argv) {
   c.geo = drv->geometry_container[ZONE_0][MESH_0];
   c.cfg = drv->config_container[ZONE_0];
   c.sol = drv->solver_container[ZONE_0][MESH_0];
+#ifdef RX_WITH_GPU
+  if (getenv("SU2_RX_BACKEND") && !strcmp(getenv("SU2_RX_BACKEND"), "cuda")) {
+    // the factory switch of driver_structure.cpp:795-801, applied after the driver built its containers
+    c.sol[FLOW_SOL] = new CReactiveNSSolverGPU(c.geo, c.cfg, MESH_0);
+    printf("HARNESS flow solver: CReactiveNSSolverGPU (librx_cuda)\n");
+  }
+#endif
   c.flow = dynamic_cast<CReactiveEulerSolver*>(c.sol[FLOW_SOL]);
   if (!c.flow) { fprintf(stderr, "not a reactive solver\n"); return 4; }
   c.num = drv->numerics_container[ZONE_0][MESH_0][FLOW_SOL];
