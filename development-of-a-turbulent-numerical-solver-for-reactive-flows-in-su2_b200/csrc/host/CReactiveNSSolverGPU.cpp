@@ -30,6 +30,7 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   viscousMode = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
   if (implicit) throw std::runtime_error("CReactiveNSSolverGPU: EULER_IMPLICIT is not on the CUDA path (explicit Euler / RK only)");
   if (second_order || limiter) throw std::runtime_error("CReactiveNSSolverGPU: 2nd-order reconstruction / limiters are not on the CUDA path yet");
+  if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
 
   // ---- geometry -> rx_mesh (flat arrays; dual_grid_structure.hpp:140,747,884)
@@ -72,6 +73,8 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
         break;
       case OUTLET_FLOW: r.kind = RX_BC_OUTLET; r.P = config->GetOutlet_Pressure(tag); break;
       case ISOTHERMAL: r.kind = RX_BC_ISOTHERMAL; r.Twall = config->GetIsothermal_Temperature(tag); break;
+      case HEAT_FLUX: r.kind = RX_BC_HEATFLUX; r.heatFlux = config->GetWall_HeatFlux(tag); break;
+      case EULER_WALL: r.kind = RX_BC_EULER_WALL; break;
       case SEND_RECEIVE: case INTERNAL_BOUNDARY: r.kind = RX_BC_NONE; break;
       default: throw std::runtime_error("CReactiveNSSolverGPU: boundary condition of marker " + tag + " is not on the CUDA path");
     }
@@ -244,6 +247,14 @@ void CReactiveNSSolverGPU::BC_Inlet(CGeometry* geometry, CSolver**, CNumerics*, 
 void CReactiveNSSolverGPU::BC_Outlet(CGeometry* geometry, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
   Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
   if (mirror >= 1 && ransMode) MirrorBoundaryState(geometry, val_marker);
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_HeatFlux_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_Euler_Wall(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
   if (mirror >= 2) MirrorResidual();
 }
 void CReactiveNSSolverGPU::BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {

@@ -40,6 +40,10 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
                  CConfig* config, unsigned short val_marker) override;
   void BC_Isothermal_Wall(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics,
                           CNumerics* visc_numerics, CConfig* config, unsigned short val_marker) override;
+  void BC_HeatFlux_Wall(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics,
+                        CNumerics* visc_numerics, CConfig* config, unsigned short val_marker) override;
+  void BC_Euler_Wall(CGeometry* geometry, CSolver** solver_container, CNumerics* numerics, CConfig* config,
+                     unsigned short val_marker) override;
   void ExplicitEuler_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config) override;
   void ExplicitRK_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config,
                             unsigned short iRKStep) override;

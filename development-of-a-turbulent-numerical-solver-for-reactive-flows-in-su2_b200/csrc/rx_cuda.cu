@@ -243,7 +243,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     }
     md.node = dupload(c, node); md.nn = dupload(c, nn); md.nx = dupload(c, nx); md.ny = dupload(c, ny);
     md.ghost = dalloc<double>(c, (size_t)std::max(s.nVertex, 1) * (7 + Ns));
-    md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall;
+    md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall; md.heatFlux = s.heatFlux;
     for (int q = 0; q < 16; ++q) md.Ys[q] = (s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
     c->markers.push_back(md);
   }
@@ -400,12 +400,14 @@ static void launch_bc(rx_ctx* c, const MarkerDev& m) {
   if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
   else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
   else if (m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  else if (m.kind == RX_BC_HEATFLUX) { k_bc_heatflux<<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
+  else if (m.kind == RX_BC_EULER_WALL) { k_bc_euler_wall<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
 }
 int rx_bc(rx_ctx* c) {
   for (const MarkerDev& m : c->markers)
-    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET) launch_bc(c, m);
+    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) launch_bc(c, m);
   for (const MarkerDev& m : c->markers)
-    if (m.kind == RX_BC_ISOTHERMAL) launch_bc(c, m);
+    if (m.kind == RX_BC_ISOTHERMAL || m.kind == RX_BC_HEATFLUX) launch_bc(c, m);
   RX_CK(cudaGetLastError());
   return RX_OK;
 }

@@ -26,7 +26,7 @@ struct Dev {   // device pointers + sizes, passed by value to kernels
   int* nonPhys; unsigned long long* counters;   // counters[0] = non-physical points of the last preprocess
 };
 
-struct MarkerDev { int kind, nVertex; const int *node, *nn; const double *nx, *ny; double T, Vmag, dir0, dir1, P, Twall; double Ys[16];
+struct MarkerDev { int kind, nVertex; const int *node, *nn; const double *nx, *ny; double T, Vmag, dir0, dir1, P, Twall, heatFlux; double Ys[16];
                    double* ghost; };   // ghost[v * nVertex + k]: primitive state imposed at vertex k (CharacPrimVar of the reference)
 
 __global__ void k_aos_to_soa(const double* __restrict__ aos, double* __restrict__ soa, long long n, int nv, long long stride) {

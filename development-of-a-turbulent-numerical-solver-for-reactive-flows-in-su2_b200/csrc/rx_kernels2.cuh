@@ -272,6 +272,36 @@ __global__ void __launch_bounds__(64) k_bc_isothermal(const __grid_constant__ Ch
   d.R[U_E * d.np + i] -= ktr * dTdn * Area + turb_closure * Area;
 }
 
+// BC_HeatFlux_Wall (solver_direct_reactive.cpp:5717-5918), explicit, static wall: no-slip + imposed heat flux
+__global__ void __launch_bounds__(64) k_bc_heatflux(const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = m.nx[k], ny = m.ny[k];
+  const double Area = sqrt(0.0 + nx * nx + ny * ny);
+  const double rho = d.V[V_RHO * d.np + i];
+  d.Uold[U_MX * d.np + i] = 0.0 * rho;          // SetVelocity_Old(0)
+  d.Uold[(U_MX + 1) * d.np + i] = 0.0 * rho;
+  d.R[U_MX * d.np + i] = 0.0;                   // LinSysRes.SetBlock_Zero(iPoint, RHOVX+iDim)
+  d.R[(U_MX + 1) * d.np + i] = 0.0;
+  d.R[U_E * d.np + i] -= m.heatFlux * Area;     // Res_Visc[rhoE] = Wall_HeatFlux*Area (:5775), SubtractBlock
+}
+// BC_Euler_Wall (solver_direct_reactive.cpp:2881-2997), explicit, static wall: pressure (+ 2/3 rho k) on the momentum rows
+__global__ void __launch_bounds__(64) k_bc_euler_wall(const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = m.nx[k], ny = m.ny[k];
+  const double Area = sqrt(0.0 + nx * nx + ny * ny);
+  const double un0 = -nx / Area, un1 = -ny / Area;
+  const double P = d.V[V_P * d.np + i], rho = d.V[V_RHO * d.np + i];
+  const double ke = o.rans ? d.turb[1 * d.np + i] : 0.0;
+  d.R[U_MX * d.np + i] += P * un0 * Area + 2.0 / 3.0 * rho * ke * un0 * Area;
+  d.R[(U_MX + 1) * d.np + i] += P * un1 * Area + 2.0 / 3.0 * rho * ke * un1 * Area;
+}
+
 // ---- ExplicitEuler/RK_Iteration (:2414-2493): update + per-block partial sums of Res^2 (deterministic two-stage reduction)
 template <int NS>
 __global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, double* __restrict__ partial) {

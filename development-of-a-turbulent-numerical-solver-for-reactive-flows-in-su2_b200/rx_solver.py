@@ -49,7 +49,7 @@ class _Chem(C.Structure):
 class _Marker(C.Structure):
     _fields_ = [("kind", C.c_int), ("nVertex", C.c_int), ("node", _PI), ("normalNeighbor", _PI), ("normal", _P),
                 ("T", C.c_double), ("Vmag", C.c_double), ("dir", C.c_double * 2), ("Ys", _P), ("P", C.c_double),
-                ("Twall", C.c_double)]
+                ("Twall", C.c_double), ("heatFlux", C.c_double)]
 
 
 class _Mesh(C.Structure):
@@ -130,7 +130,7 @@ class CReactiveNSSolverGPU:
             node = k(m["node"], np.int64)
             arr[q] = _Marker(int(m["kind"]), len(node), _i(node), _i(k(m["normalNeighbor"], np.int64)), _d(k(m["normal"])),
                              float(m.get("T", 0.0)), float(m.get("Vmag", 0.0)), (C.c_double * 2)(*m.get("dir", [0.0, 0.0])),
-                             _d(k(m.get("Ys", np.zeros(Ns)))), float(m.get("P", 0.0)), float(m.get("Twall", 0.0)))
+                             _d(k(m.get("Ys", np.zeros(Ns)))), float(m.get("P", 0.0)), float(m.get("Twall", 0.0)), float(m.get("heatFlux", 0.0)))
         en = k(mesh["edgeNodes"], np.int64)
         self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
         ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),

@@ -28,7 +28,7 @@ extern "C" {
 typedef struct rx_ctx rx_ctx;
 
 enum rx_status { RX_OK = 0, RX_ERR_ARG = -1, RX_ERR_NO_DEVICE = -2, RX_ERR_CUDA = -3, RX_ERR_UNSUPPORTED = -4, RX_ERR_NAN = -5 };
-enum rx_bc_kind { RX_BC_NONE = 0, RX_BC_INLET_TEMPERATURE_IMPOSE = 1, RX_BC_OUTLET = 2, RX_BC_ISOTHERMAL = 3 };
+enum rx_bc_kind { RX_BC_NONE = 0, RX_BC_INLET_TEMPERATURE_IMPOSE = 1, RX_BC_OUTLET = 2, RX_BC_ISOTHERMAL = 3, RX_BC_HEATFLUX = 4, RX_BC_EULER_WALL = 5 };
 
 /* Tables held by Framework::ReactingModelLibrary after Setup() (Common/src/Framework/reacting_model_library.cpp:1520-1586,
  * members reacting_model_library.hpp:655-766).  Matrices are [reaction][species]. */
@@ -46,7 +46,7 @@ typedef struct {
 } rx_chem;
 
 /* One boundary marker: geometry->vertex[m][v]->{GetNode, GetNormal, GetNormal_Neighbor} and the marker's cfg values
- * (MARKER_INLET + INLET_MASS_FRAC / MARKER_OUTLET / MARKER_ISOTHERMAL). */
+ * (MARKER_INLET + INLET_MASS_FRAC / MARKER_OUTLET / MARKER_ISOTHERMAL / MARKER_HEATFLUX / MARKER_EULER). */
 typedef struct {
   int kind;                 /* rx_bc_kind */
   int nVertex;
@@ -57,6 +57,7 @@ typedef struct {
   const double* Ys;         /* inlet: [Ns] GetInlet_MassFrac */
   double P;                 /* outlet: GetOutlet_Pressure */
   double Twall;             /* isothermal: GetIsothermal_Temperature */
+  double heatFlux;          /* heat-flux wall: GetWall_HeatFlux */
 } rx_marker;
 
 /* Flat export of CGeometry (Common/include/dual_grid_structure.hpp:140,747,884). Points [0,nPointDomain) are owned,
@@ -106,7 +107,7 @@ int rx_time_step(rx_ctx*);                                /* SetTime_Step :5057 
 int rx_residual_conv(rx_ctx*);                            /* Upwind_Residual :2535 */
 int rx_residual_visc(rx_ctx*);                            /* Viscous_Residual :5305 */
 int rx_residual_source(rx_ctx*);                          /* Source_Residual :2792 */
-int rx_bc(rx_ctx*);                                       /* BC_Inlet :3226, BC_Outlet :3808, then BC_Isothermal_Wall :5393 (integration_structure.cpp:89-190) */
+int rx_bc(rx_ctx*);                                       /* BC_Inlet :3226, BC_Outlet :3808, BC_Euler_Wall :2881, then BC_Isothermal_Wall :5393, BC_HeatFlux_Wall :5717 (integration_structure.cpp:89-190) */
 int rx_bc_marker(rx_ctx*, int marker);                    /* one BC_* call of the reference: the boundary condition of marker `marker` (order is the caller's) */
 int rx_get_bc_state(rx_ctx*, int marker, double* V /* [nVertex][nPrim] */);   /* state imposed by the last inlet/outlet BC of the marker = CharacPrimVar (:3274, :3844), read by the turbulence BCs */
 int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */

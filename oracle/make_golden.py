@@ -125,6 +125,11 @@ SPECS = {
     # same channel, RANS + PaSR
     "channel_rans": (dict(nx=41, ny=21, stretch=1.5),
                      dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO"), 2, 1, 17, False),
+    # same channel, laminar, the other two wall kinds of SURVEY.md 8(a10): heat-flux lower wall, Euler (slip) upper wall
+    "channel_lam_walls": (dict(nx=41, ny=21, stretch=1.5),
+                          dict(CHANNEL_MARKERS, MARKER_ISOTHERMAL="( NONE )", MARKER_HEATFLUX="( lower_wall, 5000.0 )",
+                               MARKER_EULER="( upper_wall )", RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE",
+                               IGNITION="NO"), 2, 1, 19, False),
 }
 
 

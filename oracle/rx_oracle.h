@@ -38,12 +38,13 @@ typedef struct {
 } rxo_chem;
 
 typedef struct {
-  int kind;            /* 1 inlet (TEMPERATURE_IMPOSE), 2 outlet, 3 isothermal wall, 0 ignored */
+  int kind;            /* 1 inlet (TEMPERATURE_IMPOSE), 2 outlet, 3 isothermal wall, 4 heat-flux wall, 5 Euler wall, 0 ignored */
   int nVertex;
   const int64_t* node; const int64_t* normalNeighbor; const double* normal; /* [nVertex], [nVertex], [nVertex][2] */
   double T, Vmag, dir[2]; const double* Ys;   /* inlet */
   double P;                                   /* outlet */
   double Twall;                               /* isothermal */
+  double heatFlux;                            /* heat-flux wall */
 } rxo_marker;
 
 typedef struct {

@@ -15,8 +15,8 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 ORACLE_SRC = os.path.join(ROOT, "oracle", "rx_oracle.cpp")
 ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "librx_oracle.so")
 
-KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL = 1, 2, 3
-_BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL}
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL = 1, 2, 3, 4, 5
+_BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL, "heatflux": KIND_HEATFLUX, "euler_wall": KIND_EULER_WALL}
 
 
 def build_oracle(force=False):
@@ -69,7 +69,7 @@ class _Marker(C.Structure):
     _fields_ = [("kind", C.c_int), ("nVertex", C.c_int), ("node", C.POINTER(C.c_int64)),
                 ("normalNeighbor", C.POINTER(C.c_int64)), ("normal", C.POINTER(C.c_double)),
                 ("T", C.c_double), ("Vmag", C.c_double), ("dir", C.c_double * 2), ("Ys", C.POINTER(C.c_double)),
-                ("P", C.c_double), ("Twall", C.c_double)]
+                ("P", C.c_double), ("Twall", C.c_double), ("heatFlux", C.c_double)]
 
 
 class _Mesh(C.Structure):
@@ -122,7 +122,7 @@ def marker_list(case):
                  normalNeighbor=np.ascontiguousarray(case["geo_marker%d_normal_neighbor" % k], dtype=np.int64),
                  normal=np.ascontiguousarray(case["geo_marker%d_normal" % k], dtype=np.float64),
                  T=mk.get("T", 0.0), Vmag=mk.get("Vmag", 0.0), dir=mk.get("dir", [0.0, 0.0]),
-                 Ys=np.array(mk.get("Ys", [0.0] * case.Ns), dtype=np.float64), P=mk.get("P", 0.0), Twall=mk.get("Twall", 0.0))
+                 Ys=np.array(mk.get("Ys", [0.0] * case.Ns), dtype=np.float64), P=mk.get("P", 0.0), Twall=mk.get("Twall", 0.0), heatFlux=mk.get("q", 0.0))
         out.append(d)
     return out
 
@@ -163,11 +163,11 @@ class Oracle:
                             normal=np.ascontiguousarray(m["normal"], dtype=np.float64).reshape(-1, 2),
                             T=float(m.get("T", 0.0)), Vmag=float(m.get("Vmag", 0.0)), dir=list(m.get("dir", [0.0, 0.0])),
                             Ys=np.ascontiguousarray(m.get("Ys", np.zeros(Ns)), dtype=np.float64), P=float(m.get("P", 0.0)),
-                            Twall=float(m.get("Twall", 0.0))))
+                            Twall=float(m.get("Twall", 0.0)), heatFlux=float(m.get("heatFlux", 0.0))))
         arr = (_Marker * max(len(mks), 1))()
         for i, d in enumerate(mks):
             arr[i] = _Marker(d["kind"], len(d["node"]), _p(d["node"], C.c_int64), _p(d["normalNeighbor"], C.c_int64),
-                             _p(d["normal"]), d["T"], d["Vmag"], (C.c_double * 2)(*d["dir"]), _p(d["Ys"]), d["P"], d["Twall"])
+                             _p(d["normal"]), d["T"], d["Vmag"], (C.c_double * 2)(*d["dir"]), _p(d["Ys"]), d["P"], d["Twall"], d["heatFlux"])
         self._keep.append(mks)
         g = dict(en=np.ascontiguousarray(mesh["edgeNodes"], dtype=np.int64), nrm=np.ascontiguousarray(mesh["edgeNormal"], dtype=np.float64),
                  xy=np.ascontiguousarray(mesh["coord"], dtype=np.float64), vol=np.ascontiguousarray(mesh["volume"], dtype=np.float64),
@@ -266,7 +266,7 @@ def mesh_dict(case):
     mk = []
     for d in marker_list(case):
         mk.append(dict(kind=d["kind"], node=d["node"], normalNeighbor=d["normalNeighbor"], normal=d["normal"], T=d["T"],
-                       Vmag=d["Vmag"], dir=d["dir"], Ys=d["Ys"], P=d["P"], Twall=d["Twall"]))
+                       Vmag=d["Vmag"], dir=d["dir"], Ys=d["Ys"], P=d["P"], Twall=d["Twall"], heatFlux=d["heatFlux"]))
     return dict(nPoint=case.nPoint, nPointDomain=case.nPointDomain, edgeNodes=case["geo_edge_nodes"],
                 edgeNormal=case["geo_edge_normal"], coord=case["geo_coord"], volume=case["geo_volume"],
                 nbPtr=case["geo_nb_ptr"], nbPoint=case["geo_nb_point"], markers=mk)
