@@ -29,7 +29,7 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   ransMode = (kind == REACTIVE_RANS);
   viscousMode = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
   if (implicit) throw std::runtime_error("CReactiveNSSolverGPU: EULER_IMPLICIT is not on the CUDA path (explicit Euler / RK only)");
-  if (second_order || limiter) throw std::runtime_error("CReactiveNSSolverGPU: 2nd-order reconstruction / limiters are not on the CUDA path yet");
+  if (limiter && config->GetKind_SlopeLimit_Flow() != VENKATAKRISHNAN) throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN limiter is on the CUDA path");
   if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
 
@@ -125,6 +125,8 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   o.fuelIndex = config->GetFuelIndex(); o.oxidizerIndex = config->GetOxidizerIndex();
   o.prandtlLam = config->GetPrandtl_Lam(); o.prandtlTurb = config->GetPrandtl_Turb(); o.lewisTurb = config->GetLewis_Turb();
   o.cMu = config->Get_Cmu(); o.pasrLb = config->Get_PaSR_LB(); o.tkeInf = ransMode ? GetTke_Inf() : 0.0;
+  o.secondOrder = second_order ? 1 : 0; o.limiter = limiter ? 1 : 0;
+  o.limCoeff = config->GetLimiterCoeff(); o.refElemLength = config->GetRefElemLength();
   o.device = env_int("SU2_RX_DEVICE", 0);
 
   const int rc = rx_create(&ctx, &mesh, &chem, &o);
@@ -180,6 +182,13 @@ void CReactiveNSSolverGPU::MirrorPrimitives() {
   }
 }
 
+void CReactiveNSSolverGPU::MirrorLimiter() {
+  std::vector<double> L((size_t)nPoint * 4);
+  Check(rx_get_limiter(ctx, L.data()), "rx_get_limiter");
+  for (unsigned long p = 0; p < nPoint; ++p)
+    for (unsigned short v = 0; v < 4; ++v) node[p]->SetLimiter_Primitive(v, L[p * 4 + v]);
+}
+
 void CReactiveNSSolverGPU::MirrorResidual() {
   Check(rx_get_residual(ctx, bufR.data()), "rx_get_residual");
   for (unsigned long p = 0; p < nPoint; ++p) LinSysRes.SetBlock(p, &bufR[p * nVar]);
@@ -205,6 +214,7 @@ void CReactiveNSSolverGPU::Preprocessing(CGeometry* geometry, CSolver** solver_c
   Check(rx_preprocess(ctx, (int64_t)extIter, Output ? 1 : 0, count ? &bad : nullptr), "rx_preprocess");
   if (count && iMesh == MESH_0) config->SetNonphysical_Points((unsigned long)bad);
   if (mirror >= 1) MirrorPrimitives();
+  if (mirror >= 2 && limiter && !Output) MirrorLimiter();
   if (mirror >= 2 && !Output) MirrorResidual();
 }
 

@@ -58,6 +58,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void UploadTurbulence(CSolver** solver_container);
   void MirrorPrimitives();
   void MirrorResidual();
+  void MirrorLimiter();
   void MirrorTimeStep();
   void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
   void Update(CGeometry* geometry, double alpha);

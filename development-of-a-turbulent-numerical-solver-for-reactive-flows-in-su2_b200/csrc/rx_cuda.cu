@@ -142,6 +142,11 @@ int download_aos(rx_ctx* c, const double* soa, double* h, int nv) {
 template <bool CONV, bool VISC>
 static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   const Dev& d = c->d;
+  if (CONV && c->o.secondOrder) {   // MUSCL reconstruction: its own kernel, the viscous part (if any) follows unfused
+    k_edge_conv2<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++;
+    if (VISC) launch_edge_flux<false, true>(c, s);
+    return;
+  }
   if (!VISC) { k_edge_flux<9, CONV, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; return; }
   if (c->o.rans) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
   if (CONV) { k_edge_flux<9, true, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; }
@@ -187,6 +192,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   o.fuelIndex = op->fuelIndex; o.oxidizerIndex = op->oxidizerIndex;
   o.prandtlLam = op->prandtlLam; o.prandtlTurb = op->prandtlTurb; o.lewisTurb = op->lewisTurb; o.cMu = op->cMu;
   o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
+  o.secondOrder = op->secondOrder; o.limiter = op->secondOrder ? op->limiter : 0; o.limCoeff = op->limCoeff; o.refElemLength = op->refElemLength;
   int rc = fill_chem(c, ch);
   if (rc) { g_create_error = "rx_create: chemistry upload failed"; rx_destroy(c); return rc; }
 
@@ -219,6 +225,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.U = dalloc<double>(c, np * c->nVar); d.Uold = dalloc<double>(c, np * c->nVar); d.R = dalloc<double>(c, np * c->nVar);
   d.V = dalloc<double>(c, np * c->nPrim); d.X = dalloc<double>(c, np * Ns);
   d.Cp = dalloc<double>(c, np); d.gam = dalloc<double>(c, np); d.mu = dalloc<double>(c, np); d.kap = dalloc<double>(c, np);
+  d.lim = dalloc<double>(c, np * 4);
   d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
   d.turb = dalloc<double>(c, np * 6); d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
@@ -293,6 +300,7 @@ int rx_set_turbulence(rx_ctx* c, const double* t) { return upload_aos(c, t, c->d
 int rx_set_temperature(rx_ctx* c, const double* T) { return upload_aos(c, T, c->d.V + V_T * c->d.np, 1); }
 int rx_get_solution(rx_ctx* c, double* U) { return download_aos(c, c->d.U, U, c->nVar); }
 int rx_get_residual(rx_ctx* c, double* R) { return download_aos(c, c->d.R, R, c->nVar); }
+int rx_get_limiter(rx_ctx* c, double* lim4) { return download_aos(c, c->d.lim, lim4, 4); }
 int rx_get_primitive(rx_ctx* c, double* V, double* aux, double* grad) {
   int rc = RX_OK;
   if (V) rc = download_aos(c, c->d.V, V, c->nPrim);
@@ -328,7 +336,7 @@ int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) 
   k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, (long long)extIter, output);
   if (c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }
   c->launches++;
-  if (c->o.viscous) {
+  if (c->o.viscous || c->o.secondOrder) {
     if (c->o.leastSquares) {
       k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
       c->launches++;
@@ -341,6 +349,7 @@ int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) 
       c->launches++;
     }
   }
+  if (c->o.secondOrder && c->o.limiter && !output) { k_limiter<<<nblk(d.nPoint, 128), 128, 0, s>>>(c->o, d); c->launches++; }   // :4739-4742
   RX_CK(cudaGetLastError());
   if (nonPhysical) {
     unsigned long long h = 0;
@@ -556,11 +565,12 @@ int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int
   return rc;
 }
 
-int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : c->nGrad * 2; }
+int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : 4; }
+static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : c->d.lim; }
 int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {
   if (n <= 0) return RX_OK;
   const int nv = rx_halo_width(c, what);
-  k_pack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(what == 0 ? c->d.U : c->d.grad, c->d.np, nv, n, (const long long*)pts, buf);
+  k_pack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(halo_field(c, what), c->d.np, nv, n, (const long long*)pts, buf);
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -568,7 +578,7 @@ int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf
 int rx_halo_unpack(rx_ctx* c, int what, int64_t n, const int64_t* pts, const double* buf) {
   if (n <= 0) return RX_OK;
   const int nv = rx_halo_width(c, what);
-  k_unpack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(what == 0 ? c->d.U : c->d.grad, c->d.np, nv, n, (const long long*)pts, buf);
+  k_unpack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(halo_field(c, what), c->d.np, nv, n, (const long long*)pts, buf);
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;

@@ -58,6 +58,8 @@ struct Opts {
   double mInfty, cfl, maxDt, Tmin, Tmax;
   int clipT, ignition; long long ignitionIter; double ignitionT; int fuelIndex, oxidizerIndex;
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
+  int secondOrder, limiter;
+  double limCoeff, refElemLength;
 };
 
 // ---- spline (MathTools::GetSpline, Common/src/Tools/spline.cpp:61-77) ---------------------------

@@ -21,7 +21,7 @@ struct Dev {   // device pointers + sizes, passed by value to kernels
   const int *nbPtr, *nbIdx;        // neighbour CSR (WLS gradient), reference order
   const int *incPtr, *incEdge;     // incident-edge CSR in ascending edge order; entry = e (point is node 0) or ~e (node 1)
   // state
-  double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *rD, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R;
+  double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *rD, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R, *lim;
   double *fluxC, *fluxV;
   int* nonPhys; unsigned long long* counters;   // counters[0] = non-physical points of the last preprocess
 };

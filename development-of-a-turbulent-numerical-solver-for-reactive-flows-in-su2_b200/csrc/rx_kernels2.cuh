@@ -58,6 +58,100 @@ __global__ void __launch_bounds__(EDGE_BS) k_edge_flux(const __grid_constant__ C
   }
 }
 
+// ---- SetPrimitive_Limiter (:1328-1523), Venkatakrishnan, owner-computes: one thread per point over its neighbours.
+// The reference builds min/max of the neighbour differences and the minimum of the edge limiters in two edge loops;
+// min and max do not depend on the order, so the per-point form gives the same bits.  Points whose neighbour list is
+// incomplete (halos) receive their values through the limiter halo exchange, as in Set_MPI_Primitive_Limiter (:1756).
+__global__ void __launch_bounds__(128) k_limiter(const __grid_constant__ Opts o, const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  const int fld[4] = {V_T, V_VX, V_VX + 1, V_P};
+  double vp[4], smax[4], smin[4], lim[4], g[4][2];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    vp[v] = d.V[fld[v] * d.np + p]; smax[v] = -EPS; smin[v] = EPS; lim[v] = 2.0;
+    g[v][0] = d.grad[(2 * v) * d.np + p]; g[v][1] = d.grad[(2 * v + 1) * d.np + p];
+  }
+  const int k0 = d.nbPtr[p], k1 = d.nbPtr[p + 1];
+  for (int k = k0; k < k1; ++k) {
+    const int q = d.nbIdx[k];
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      const double du = d.V[fld[v] * d.np + q] - vp[v];
+      smin[v] = fmin(smin[v], du); smax[v] = fmax(smax[v], du);
+    }
+  }
+  const double eps1 = o.limCoeff * o.refElemLength, eps2 = eps1 * eps1 * eps1;
+  const double xp = d.x[p], yp = d.y[p];
+  for (int k = k0; k < k1; ++k) {
+    const int q = d.nbIdx[k];
+    const double hx = 0.5 * (d.x[q] - xp), hy = 0.5 * (d.y[q] - yp);
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      double dm = 0.0;
+      dm += hx * g[v][0]; dm += hy * g[v][1];
+      const double dp = dm > 0.0 ? smax[v] : smin[v];
+      const double lv = (dp * dp + 2.0 * dp * dm + eps2) / (dp * dp + dp * dm + 2.0 * dm * dm + eps2);
+      if (lv < lim[v]) lim[v] = lv;
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < 4; ++v) d.lim[v * d.np + p] = lim[v];
+}
+
+// ---- 2nd-order Upwind_Residual (:2554-2681): MUSCL reconstruction of [T,u,v,P] at the edge mid point, rebuild of rho, h, a
+template <int NS>
+__device__ __forceinline__ void reconstruct_state(const ChemC<NS>& cc, const Opts& o, const Dev& d, long long p, double hx, double hy,
+                                                  bool useOtherP, double otherP, double* Vr, double& Precon) {
+  double V[7 + NS];
+  load_V<NS>(d, p, V);
+  const int fld[4] = {V_T, V_VX, V_VX + 1, V_P};
+  double rec[4];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    double proj = 0.0;
+    proj += hx * d.grad[(2 * v) * d.np + p]; proj += hy * d.grad[(2 * v + 1) * d.np + p];
+    rec[v] = V[fld[v]];
+    if (o.limiter) rec[v] += d.lim[v * d.np + p] * proj; else rec[v] += proj;
+  }
+  Precon = rec[3];
+  bool nonPhys = !(rec[0] > EPS);
+  if (!nonPhys) nonPhys = !((useOtherP ? otherP : rec[3]) > EPS);   // the j side tests the pressure of the i side (:2612)
+  if (nonPhys) {
+#pragma unroll
+    for (int v = 0; v < 7 + NS; ++v) Vr[v] = V[v];
+    return;
+  }
+  const double* Ys = V + V_Y;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) Vr[V_Y + s] = Ys[s];
+  Vr[V_T] = rec[0]; Vr[V_VX] = rec[1]; Vr[V_VX + 1] = rec[2]; Vr[V_P] = rec[3];
+  double rho = rec[3] / (rec[0] * rgas(cc, Ys));
+  rho *= 1.0;
+  Vr[V_RHO] = rho;
+  bool ok = true;
+  Vr[V_H] = enthalpy(cc, rec[0], Ys, ok) / 1.0;
+  double sq = 0.0;
+  sq += rec[1] * rec[1]; sq += rec[2] * rec[2];
+  Vr[V_H] += 0.5 * sq;
+  const double g = frozen_gamma(cc, rec[0], Ys);
+  Vr[V_A] = sqrt(g * rec[3] / rho);
+}
+template <int NS>
+__global__ void __launch_bounds__(64) k_edge_conv2(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= d.nEdge) return;
+  constexpr int NV = 4 + NS;
+  const int i = d.ei[e], j = d.ej[e];
+  const double hx = 0.5 * (d.x[j] - d.x[i]), hy = 0.5 * (d.y[j] - d.y[i]);
+  double Vi[7 + NS], Vj[7 + NS], res[NV], Pi, Pj;
+  reconstruct_state<NS>(cc, o, d, i, hx, hy, false, 0.0, Vi, Pi);
+  reconstruct_state<NS>(cc, o, d, j, -hx, -hy, true, Pi, Vj, Pj);
+  ausm<NS>(o.mInfty, Vi, Vj, d.enx[e], d.eny[e], res);
+#pragma unroll
+  for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
+}
+
 // ---- Source_Residual (:2792-2874) + CSourceReactive::ComputeChemistry (numerics_direct_reactive.cpp:1728-1825), per owned point
 template <int NS>
 __device__ __forceinline__ void point_source(const ChemC<NS>& cc, const Opts& o, const Dev& d, long long p, double* src) {

@@ -9,7 +9,7 @@ The path has no other collective: residual norms are reduced once per iteration 
 import torch
 import torch.distributed as dist
 
-WHAT_SOLUTION, WHAT_GRADIENT = 0, 1
+WHAT_SOLUTION, WHAT_GRADIENT, WHAT_LIMITER = 0, 1, 2
 
 
 class HaloExchanger:
@@ -103,6 +103,8 @@ def distributed_iterate(solver, ex, ext_iter, rk_alpha, last_rms=False):
     for rk, a in enumerate(rk_alpha):
         solver.Preprocessing(ext_iter, False, count_nonphysical=False)
         ex.exchange(WHAT_GRADIENT)
+        if solver.opts.get("secondOrder") and solver.opts.get("limiter"):
+            ex.exchange(WHAT_LIMITER)   # Set_MPI_Primitive_Limiter (:1756-1870)
         if rk == 0:
             solver.Set_OldSolution()
             solver.SetTime_Step()

@@ -64,14 +64,16 @@ class _Opts(C.Structure):
                 ("clipT", C.c_int), ("ignition", C.c_int), ("ignitionIter", C.c_int64), ("ignitionT", C.c_double),
                 ("fuelIndex", C.c_int), ("oxidizerIndex", C.c_int),
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
-                ("pasrLb", C.c_double), ("tkeInf", C.c_double), ("device", C.c_int)]
+                ("pasrLb", C.c_double), ("tkeInf", C.c_double),
+                ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
+                ("device", C.c_int)]
 
 
 EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "rx_set_stream", "rx_synchronize",
            "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
-           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state"]
+           "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter"]
 
 _lib = None
 
@@ -135,7 +137,8 @@ class CReactiveNSSolverGPU:
         self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
         ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),
                    _d(k(mesh["volume"])), _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
-        od = dict(opts)
+        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1)
+        od.update(opts)
         od["device"] = device
         self.opts = od
         o = _Opts(**{f[0]: od[f[0]] for f in _Opts._fields_})
@@ -176,6 +179,9 @@ class CReactiveNSSolverGPU:
     def GetPrimitive(self):
         V = np.empty((self.nPoint, self.nPrim)); aux = np.empty((self.nPoint, 6)); g = np.empty((self.nPoint, self.nGrad, 2))
         self._ck(self.lib.rx_get_primitive(self.ctx, _d(V), _d(aux), _d(g))); return V, aux, g
+
+    def GetLimiter(self):
+        L = np.empty((self.nPoint, 4)); self._ck(self.lib.rx_get_limiter(self.ctx, _d(L))); return L
 
     def GetDelta_Time(self):
         d = np.empty((self.nPoint, 3)); self._ck(self.lib.rx_get_dt(self.ctx, _d(d))); return d
@@ -236,7 +242,7 @@ class CReactiveNSSolverGPU:
 
     # ---- the stage API used by the parity tests (same names as tests/rxcase.Oracle)
     set_solution = SetSolution; set_temperature = SetTemperature; set_turbulence = SetTurbulence
-    solution = GetSolution; primitive = GetPrimitive; dt = GetDelta_Time; residual = GetLinSysRes
+    solution = GetSolution; primitive = GetPrimitive; dt = GetDelta_Time; residual = GetLinSysRes; limiter = GetLimiter
     def preprocess(self, it, output=False): return self.Preprocessing(it, output)
     set_old_solution = Set_OldSolution; time_step = SetTime_Step; upwind_residual = Upwind_Residual
     viscous_residual = Viscous_Residual; source_residual = Source_Residual; boundary_conditions = BC_All

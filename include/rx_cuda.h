@@ -81,6 +81,8 @@ typedef struct {
   double mInfty, cfl, maxDt, Tmin, Tmax;
   int clipT, ignition; int64_t ignitionIter; double ignitionT; int fuelIndex, oxidizerIndex;
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
+  int secondOrder, limiter;   /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER] (MUSCL on T,u,v,P :2554-2681); limiter: 1 = VENKATAKRISHNAN (:1328-1523) */
+  double limCoeff, refElemLength;   /* LIMITER_COEFF, REF_ELEM_LENGTH */
   int device;               /* CUDA device ordinal */
 } rx_opts;
 
@@ -99,6 +101,7 @@ int rx_get_solution(rx_ctx*, double* U);
 int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */
 int rx_get_dt(rx_ctx*, double* dt3);                      /* [nPoint][3]: Delta_Time, Max_Lambda_Inv, Max_Lambda_Visc */
 int rx_get_residual(rx_ctx*, double* R);                  /* LinSysRes */
+int rx_get_limiter(rx_ctx*, double* lim4);                /* [nPoint][4]: Limiter_Primitive of T, u, v, P */
 
 /* stages; each replaces the CSolver virtual named on the right (solver_direct_reactive.cpp) */
 int rx_preprocess(rx_ctx*, int64_t extIter, int output, int64_t* nonPhysical /* may be NULL: no host sync */);  /* Preprocessing :4693 */
@@ -127,7 +130,7 @@ int rx_source_points_dev(rx_ctx*, int64_t n, const double* T_dev, const double* 
                          const double* omegaTurb_dev, const double* vol_dev, double* res_dev /* [Ns][n] SoA */);
 
 /* halo exchange plumbing for one-process-per-GPU runs (replaces Set_MPI_Solution :1530, Set_MPI_Primitive_Gradient :1877):
- * pack `what` (0 = conserved U, 1 = gradients+turbulence-free primitives) of the listed points into buf_dev[nVarOfWhat][n],
+ * pack `what` (0 = conserved U, 1 = primitive gradients, 2 = limiters of T,u,v,P: Set_MPI_Primitive_Limiter :1756) of the listed points into buf_dev[nVarOfWhat][n],
  * or unpack into them; the transport in between (NCCL send/recv) belongs to the caller. */
 int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double* buf_dev);
 int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);

@@ -130,6 +130,11 @@ SPECS = {
                           dict(CHANNEL_MARKERS, MARKER_ISOTHERMAL="( NONE )", MARKER_HEATFLUX="( lower_wall, 5000.0 )",
                                MARKER_EULER="( upper_wall )", RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE",
                                IGNITION="NO"), 2, 1, 19, False),
+    # same channel, laminar, 2nd-order MUSCL reconstruction of [T,u,v,P] with the Venkatakrishnan limiter
+    "channel_lam_muscl": (dict(nx=41, ny=21, stretch=1.5),
+                          dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                               SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="VENKATAKRISHNAN", CFL_NUMBER="0.2"),
+                          2, 1, 23, False),
 }
 
 

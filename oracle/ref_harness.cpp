@@ -104,6 +104,12 @@ static void dump_primitive(Ctx& c, const std::string& pre) {
     aux[p * 6 + 5] = c.viscous ? n->GetStrainMag() : 0.0;
   }
   dump_f64(pre + "V", V, {c.nPoint, c.nPrimVar});
+  if (c.flow->limiter) {
+    std::vector<double> L(c.nPoint * 4);
+    for (unsigned long p = 0; p < c.nPoint; ++p)
+      for (unsigned short v = 0; v < 4; ++v) L[p * 4 + v] = c.flow->node[p]->GetLimiter_Primitive()[v];
+    dump_f64(pre + "lim", L, {c.nPoint, 4});
+  }
   dump_f64(pre + "aux", aux, {c.nPoint, 6});
   if (c.viscous) {
     G.resize(c.nPoint * c.nPrimVarGrad * c.nDim);
@@ -285,6 +291,8 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"grad_method\": " << f->GetKind_Gradient_Method() << ", \"time_scheme\": " << f->GetKind_TimeIntScheme_Flow()
      << ", \"kind_inlet\": " << f->GetKind_Inlet()
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
+     << ", \"limiter_kind\": " << f->GetKind_SlopeLimit_Flow() << ", \"limiter_coeff\": " << f->GetLimiterCoeff()
+     << ", \"ref_elem_length\": " << f->GetRefElemLength() << ", \"limiter_iter\": " << f->GetLimiterIter()
      << ", \"nRK\": " << f->GetnRKStep() << ", \"rk_alpha\": [";
   for (unsigned short k = 0; k < f->GetnRKStep(); ++k) js << (k ? ", " : "") << f->Get_Alpha_RKStep(k);
   js << "], \"lower\": [";

@@ -62,6 +62,8 @@ typedef struct {
   double mInfty, cfl, maxDt, Tmin, Tmax;
   int clipT, ignition; int64_t ignitionIter; double ignitionT; int fuelIndex, oxidizerIndex;
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
+  int secondOrder, limiter;            /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER]; limiter: 1 = VENKATAKRISHNAN */
+  double limCoeff, refElemLength;      /* LIMITER_COEFF, REF_ELEM_LENGTH */
 } rxo_opts;
 
 rxo_ctx* rxo_create(const rxo_mesh*, const rxo_chem*, const rxo_opts*);
@@ -75,6 +77,7 @@ void rxo_get_solution(rxo_ctx*, double* U);
 void rxo_get_primitive(rxo_ctx*, double* V, double* aux6, double* grad);  /* aux = Cp,gamma,mu,kappa,vort,strain */
 void rxo_get_dt(rxo_ctx*, double* dt3);                   /* dt, lambda_inv, lambda_visc */
 void rxo_get_residual(rxo_ctx*, double* R);
+void rxo_get_limiter(rxo_ctx*, double* lim4);            /* [nPoint][4]: limiter of T, u, v, P */
 
 /* stages, same order as CMultiGridIntegration::MultiGrid_Cycle (integration_time.cpp:143-181) */
 int64_t rxo_preprocess(rxo_ctx*, int64_t extIter, int output);

@@ -86,7 +86,8 @@ class _Opts(C.Structure):
                 ("clipT", C.c_int), ("ignition", C.c_int), ("ignitionIter", C.c_int64), ("ignitionT", C.c_double),
                 ("fuelIndex", C.c_int), ("oxidizerIndex", C.c_int),
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
-                ("pasrLb", C.c_double), ("tkeInf", C.c_double)]
+                ("pasrLb", C.c_double), ("tkeInf", C.c_double),
+                ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double)]
 
 
 def chem_arrays(case):
@@ -111,7 +112,8 @@ def opts_dict(case):
                 ignition=cf["ignition"], ignitionIter=cf["ignition_iter"], ignitionT=cf["ignition_T"],
                 fuelIndex=cf["fuel_index"], oxidizerIndex=cf["oxidizer_index"], prandtlLam=cf["prandtl_lam"],
                 prandtlTurb=cf["prandtl_turb"], lewisTurb=cf["lewis_turb"], cMu=cf["c_mu"], pasrLb=cf["pasr_lb"],
-                tkeInf=cf["tke_inf"])
+                tkeInf=cf["tke_inf"], secondOrder=cf.get("second_order", 0), limiter=cf.get("limiter", 0),
+                limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1))
 
 
 def marker_list(case):
@@ -208,6 +210,9 @@ class Oracle:
 
     def residual(self):
         R = np.empty((self.nP, self.nVar)); self.lib.rxo_get_residual(self.ctx, _p(R)); return R
+
+    def limiter(self):
+        L = np.empty((self.nP, 4)); self.lib.rxo_get_limiter(self.ctx, _p(L)); return L
 
     def preprocess(self, ext_iter, output=False):
         return self.lib.rxo_preprocess(self.ctx, C.c_int64(ext_iter), int(output))

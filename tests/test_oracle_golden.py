@@ -13,7 +13,7 @@ import pytest
 
 from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 
-CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls"]
+CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl"]
 TOL = 1e-13
 
 
@@ -33,6 +33,8 @@ def drive(case, solver, check):
             check(key("pre_V"), V); check(key("pre_aux"), aux)
             if cf["viscous"]:
                 check(key("pre_grad"), g)
+            if cf.get("limiter", 0) and hasattr(solver, "limiter"):
+                check(key("pre_lim"), solver.limiter())
             if rk == 0:
                 solver.set_old_solution(); solver.time_step(); check(key("dt"), solver.dt())
             solver.upwind_residual(); check(key("res_conv"), solver.residual())
