@@ -82,12 +82,13 @@ def load_library():
     """dlopen librx_cuda.so (built in-tree by build_library / __graft_entry__.build); raises RxError if absent."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("RX_CUDA_LIB", LIB_PATH)   # tuning hook: a build variant of the same library (tools/ktime.py)
+        if not os.path.exists(path):
             raise RxError("librx_cuda.so not built (run __graft_entry__.build()); there is no CPU fallback")
         try:
-            _lib = C.CDLL(LIB_PATH)
+            _lib = C.CDLL(path)
         except OSError as e:
-            raise RxError("cannot load %s: %s (no CPU fallback)" % (LIB_PATH, e))
+            raise RxError("cannot load %s: %s (no CPU fallback)" % (path, e))
         _lib.rx_last_error.restype = C.c_char_p
         _lib.rx_last_error.argtypes = [C.c_void_p]
         _lib.rx_launch_count.restype = C.c_int64

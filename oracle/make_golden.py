@@ -9,6 +9,7 @@ It also prepares oracle/_ref/cases/<name>/ (git-ignored, travels to the GPU box)
 can run the compiled reference there.
 
 usage: python oracle/make_golden.py [case ...]      (default: all)
+       python oracle/make_golden.py prepare         (case directories only, fixtures untouched)
 """
 import json
 import os
@@ -138,10 +139,17 @@ SPECS = {
 }
 
 
-def run_case(name):
-    kw, repl, nit, dump_from, seed, lean = SPECS[name]
+def prepare_case(name):
+    """Case directory + derived cfg only (what tests/test_gpu_dropin.py and bench.py need on the GPU box)."""
+    kw, repl = SPECS[name][0], SPECS[name][1]
     d = prepare_case_dir(name, **kw)
     derive_cfg(os.path.join(SHIPPED, "my_combustion_first_chem_PaSR.cfg"), os.path.join(d, "case.cfg"), repl)
+    return d
+
+
+def run_case(name):
+    kw, repl, nit, dump_from, seed, lean = SPECS[name]
+    d = prepare_case(name)
     out = os.path.join(d, "dump")
     shutil.rmtree(out, ignore_errors=True)
     cmd = [HARNESS, "case.cfg", str(nit), out, str(dump_from)] + ([str(seed)] if seed is not None else [])
@@ -185,6 +193,11 @@ def prepare_bench_case(nx=101, ny=101):
 
 if __name__ == "__main__":
     if sys.argv[1:] == ["bench_ref"]:
+        prepare_bench_case()
+        sys.exit(0)
+    if sys.argv[1:] == ["prepare"]:   # case directories only; the committed fixtures are left alone
+        for n in SPECS:
+            prepare_case(n)
         prepare_bench_case()
         sys.exit(0)
     names = sys.argv[1:] or list(SPECS)
