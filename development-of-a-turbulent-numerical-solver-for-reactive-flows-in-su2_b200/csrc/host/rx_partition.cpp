@@ -1,0 +1,179 @@
+// rx_partition.cpp — host-side graph tools of the multi-GPU path (include/rx_cuda.h, "partitioning"):
+//   rx_partition_kway  k-way partition of the point adjacency graph.  It stands where the reference calls
+//                      ParMETIS_V3_PartKway on the same graph (Common/src/geometry_structure.cpp:11524, reached from
+//                      SetColorGrid_Parallel, driver_structure.cpp:126); METIS itself is not linked.  Method: recursive
+//                      inertial bisection (principal axis of the point cloud, split at the size-proportional quantile)
+//                      followed by boundary refinement of the edge cut under a balance constraint — first per bisection,
+//                      then k-way over the final parts.  Deterministic (ties are broken by point index).
+//   rx_rcm_order       reverse Cuthill–McKee numbering of the owned points of one partition, halo points kept last — the
+//                      role of CPhysicalGeometry::SetRCM_Ordering (geometry_structure.cpp:9200-9290; lowest-degree start,
+//                      neighbours appended by increasing degree, result reversed).  Used to keep the edge kernels' point
+//                      gathers local on unstructured partitions.
+// Plain C ABI, no device code; the arrays are the caller's.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <numeric>
+#include <utility>
+#include <vector>
+
+#include "../../../include/rx_cuda.h"
+
+namespace {
+
+struct Graph {
+  int64_t n;
+  const int64_t* ptr;
+  const int64_t* adj;
+};
+
+// moves boundary points between side 0 and side 1 of subset `sub` while the cut shrinks (or balance improves at equal cut)
+void refine_bisection(const Graph& g, const std::vector<int64_t>& ids, std::vector<int32_t>& label, int32_t sub,
+                      std::vector<int8_t>& side, int64_t target0, int64_t slack, int passes) {
+  int64_t n0 = 0;
+  for (int64_t v : ids) n0 += side[v] == 0;
+  const int64_t n = (int64_t)ids.size();
+  for (int pass = 0; pass < passes; ++pass) {
+    int64_t moved = 0;
+    for (int64_t v : ids) {
+      int64_t same = 0, other = 0;
+      for (int64_t q = g.ptr[v]; q < g.ptr[v + 1]; ++q) {
+        const int64_t w = g.adj[q];
+        if (w >= g.n || label[w] != sub) continue;
+        (side[w] == side[v] ? same : other)++;
+      }
+      if (other == 0) continue;
+      const int64_t gain = other - same;
+      const int64_t n0_after = n0 + (side[v] == 0 ? -1 : 1);
+      const int64_t dev_now = std::llabs(n0 - target0), dev_after = std::llabs(n0_after - target0);
+      const bool balanced = dev_after <= slack && n0_after > 0 && n0_after < n;
+      if ((gain > 0 && (balanced || dev_after < dev_now)) || (gain == 0 && dev_after < dev_now && dev_now > slack)) {
+        side[v] ^= 1; n0 = n0_after; ++moved;
+      }
+    }
+    if (!moved) break;
+  }
+}
+
+void bisect(const Graph& g, const double* xy, std::vector<int64_t>& ids, int32_t k0, int32_t k1, std::vector<int32_t>& label,
+            std::vector<int8_t>& side, int32_t& nextSub, int passes, double tol, int64_t* owner) {
+  if (k1 - k0 == 1) {
+    for (int64_t v : ids) owner[v] = k0;
+    return;
+  }
+  const int64_t n = (int64_t)ids.size();
+  const int32_t kl = (k1 - k0) / 2;
+  const int64_t target0 = (n * kl) / (k1 - k0);
+  // principal axis of the subset
+  double cx = 0, cy = 0;
+  for (int64_t v : ids) { cx += xy[2 * v]; cy += xy[2 * v + 1]; }
+  cx /= (double)std::max<int64_t>(n, 1); cy /= (double)std::max<int64_t>(n, 1);
+  double sxx = 0, sxy = 0, syy = 0;
+  for (int64_t v : ids) {
+    const double dx = xy[2 * v] - cx, dy = xy[2 * v + 1] - cy;
+    sxx += dx * dx; sxy += dx * dy; syy += dy * dy;
+  }
+  const double th = 0.5 * std::atan2(2.0 * sxy, sxx - syy);   // direction of the largest eigenvalue
+  const double ax = std::cos(th), ay = std::sin(th);
+  std::vector<std::pair<double, int64_t>> key(n);
+  for (int64_t q = 0; q < n; ++q) key[q] = {ax * (xy[2 * ids[q]] - cx) + ay * (xy[2 * ids[q] + 1] - cy), ids[q]};
+  if (target0 > 0 && target0 < n) std::nth_element(key.begin(), key.begin() + target0, key.end());
+  const int32_t sub = nextSub++;
+  for (int64_t q = 0; q < n; ++q) { label[key[q].second] = sub; side[key[q].second] = q < target0 ? 0 : 1; }
+  const int64_t slack = std::max<int64_t>(1, (int64_t)(tol * (double)n / (double)(k1 - k0)));
+  refine_bisection(g, ids, label, sub, side, target0, slack, passes);
+  std::vector<int64_t> a, b;
+  a.reserve(target0 + slack); b.reserve(n - target0 + slack);
+  for (int64_t v : ids) (side[v] == 0 ? a : b).push_back(v);   // ids stay in ascending order
+  std::vector<int64_t>().swap(ids);
+  bisect(g, xy, a, k0, k0 + kl, label, side, nextSub, passes, tol, owner);
+  bisect(g, xy, b, k0 + kl, k1, label, side, nextSub, passes, tol, owner);
+}
+
+// k-way boundary refinement: a point moves to the neighbouring part that holds most of its neighbours if that lowers the cut
+void refine_kway(const Graph& g, int nParts, int64_t* owner, int passes, double tol) {
+  std::vector<int64_t> size(nParts, 0);
+  for (int64_t v = 0; v < g.n; ++v) size[owner[v]]++;
+  const int64_t avg = (g.n + nParts - 1) / nParts;
+  const int64_t hi = avg + std::max<int64_t>(1, (int64_t)(tol * (double)avg));
+  const int64_t lo = std::max<int64_t>(1, avg - std::max<int64_t>(1, (int64_t)(tol * (double)avg)) - 1);
+  std::vector<int64_t> cnt(nParts, 0);
+  std::vector<int32_t> touched;
+  for (int pass = 0; pass < passes; ++pass) {
+    int64_t moved = 0;
+    for (int64_t v = 0; v < g.n; ++v) {
+      const int64_t me = owner[v];
+      touched.clear();
+      for (int64_t q = g.ptr[v]; q < g.ptr[v + 1]; ++q) {
+        const int64_t w = g.adj[q];
+        if (w >= g.n) continue;
+        const int64_t p = owner[w];
+        if (cnt[p]++ == 0) touched.push_back((int32_t)p);
+      }
+      int64_t best = me, bestCnt = cnt[me];
+      std::sort(touched.begin(), touched.end());
+      for (int32_t p : touched)
+        if (p != me && cnt[p] > bestCnt && size[p] + 1 <= hi && size[me] - 1 >= lo) { best = p; bestCnt = cnt[p]; }
+      for (int32_t p : touched) cnt[p] = 0;
+      if (best != me) { owner[v] = best; size[me]--; size[best]++; ++moved; }
+    }
+    if (!moved) break;
+  }
+}
+
+}  // namespace
+
+extern "C" int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const double* coord, int nParts,
+                                 int refinePasses, int64_t* owner, int64_t* edgeCut) {
+  if (nPoint < 0 || nParts < 1 || !nbPtr || !nbPoint || !coord || !owner || (int64_t)nParts > std::max<int64_t>(nPoint, 1)) return RX_ERR_ARG;
+  const Graph g{nPoint, nbPtr, nbPoint};
+  const double tol = 0.02;
+  {
+    std::vector<int64_t> ids(nPoint);
+    std::iota(ids.begin(), ids.end(), (int64_t)0);
+    std::vector<int32_t> label(nPoint, -1);
+    std::vector<int8_t> side(nPoint, 0);
+    int32_t nextSub = 0;
+    bisect(g, coord, ids, 0, nParts, label, side, nextSub, std::max(refinePasses, 0), tol, owner);
+  }
+  if (nParts > 2 && refinePasses > 0) refine_kway(g, nParts, owner, refinePasses, tol);
+  if (edgeCut) {
+    int64_t cut = 0;
+    for (int64_t v = 0; v < nPoint; ++v)
+      for (int64_t q = nbPtr[v]; q < nbPtr[v + 1]; ++q)
+        if (nbPoint[q] > v && nbPoint[q] < nPoint && owner[nbPoint[q]] != owner[v]) ++cut;
+    *edgeCut = cut;
+  }
+  return RX_OK;
+}
+
+extern "C" int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld) {
+  if (nPoint < 0 || nPointDomain < 0 || nPointDomain > nPoint || !nbPtr || !nbPoint || !newToOld) return RX_ERR_ARG;
+  const int64_t n = nPointDomain;
+  auto degree = [&](int64_t v) { return nbPtr[v + 1] - nbPtr[v]; };
+  std::vector<char> seen(n, 0);
+  std::vector<int64_t> order;
+  order.reserve(n);
+  std::vector<int64_t> byDegree(n);
+  std::iota(byDegree.begin(), byDegree.end(), (int64_t)0);
+  std::stable_sort(byDegree.begin(), byDegree.end(), [&](int64_t a, int64_t b) { return degree(a) < degree(b); });
+  std::vector<int64_t> nb;
+  size_t head = 0;
+  for (int64_t s : byDegree) {   // one breadth-first sweep per connected component, lowest-degree start
+    if (seen[s]) continue;
+    seen[s] = 1; order.push_back(s);
+    while (head < order.size()) {
+      const int64_t v = order[head++];
+      nb.clear();
+      for (int64_t q = nbPtr[v]; q < nbPtr[v + 1]; ++q) {
+        const int64_t w = nbPoint[q];
+        if (w < n && !seen[w]) { seen[w] = 1; nb.push_back(w); }
+      }
+      std::stable_sort(nb.begin(), nb.end(), [&](int64_t a, int64_t b) { return degree(a) < degree(b); });
+      order.insert(order.end(), nb.begin(), nb.end());
+    }
+  }
+  for (int64_t q = 0; q < n; ++q) newToOld[q] = order[n - 1 - q];
+  for (int64_t q = n; q < nPoint; ++q) newToOld[q] = q;
+  return RX_OK;
+}

@@ -216,26 +216,36 @@ __device__ __forceinline__ void store_vort_strain(const Dev& d, long long p, con
   d.strain[p] = sqrt(2.0 * sm);
 }
 
-// ---- SetPrimitive_Gradient_LS (solver_direct_reactive.cpp:4887-5050), one thread per owned point
-template <int NS>
-__global__ void __launch_bounds__(128) k_gradient_ls(const Dev d) {
-  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (p >= d.nPoint) return;
+// ---- SetPrimitive_Gradient_LS (solver_direct_reactive.cpp:4887-5050), one thread per owned point.
+// The reference divides 3 + 2*nPrimVarGrad products by the same squared distance per neighbour.  FAST: one refined
+// reciprocal per neighbour serves all 29 quotients (rx_fdiv.cuh: correctly rounded where its range test passes, which is
+// ORed into one flag for the whole point); if the flag came up the point is redone with plain divisions.
+template <int NS, bool FAST>
+__device__ __forceinline__ bool ls_sums(const Dev& d, long long p, const double* pi, double* C, double& r11, double& r12, double& r22) {
   constexpr int NG = 4 + NS;
-  double g[NG * 2];
-  if (p < d.nPointDomain) {
-    double pi[NG], pj[NG], C[NG * 2];
-    load_gradvars<NS>(d, p, pi);
+  double pj[NG];
+  bool bad = false;
 #pragma unroll
-    for (int k = 0; k < NG * 2; ++k) C[k] = 0.0;
-    const double xi = d.x[p], yi = d.y[p];
-    double r11 = 0.0, r12 = 0.0, r22 = 0.0;
-    for (int k = d.nbPtr[p]; k < d.nbPtr[p + 1]; ++k) {
-      const int q = d.nbIdx[k];
-      load_gradvars<NS>(d, q, pj);
-      const double d0 = d.x[q] - xi, d1 = d.y[q] - yi;
-      const double weight = 0.0 + d0 * d0 + d1 * d1;
-      if (weight > EPS) {
+  for (int k = 0; k < NG * 2; ++k) C[k] = 0.0;
+  r11 = 0.0; r12 = 0.0; r22 = 0.0;
+  const double xi = d.x[p], yi = d.y[p];
+  for (int k = d.nbPtr[p]; k < d.nbPtr[p + 1]; ++k) {
+    const int q = d.nbIdx[k];
+    load_gradvars<NS>(d, q, pj);
+    const double d0 = d.x[q] - xi, d1 = d.y[q] - yi;
+    const double weight = 0.0 + d0 * d0 + d1 * d1;
+    if (weight > EPS) {
+      if (FAST) {
+        const Recip rw = frecip(weight);
+        r11 += fdiv(d0 * d0, rw, bad);
+        r12 += fdiv(d0 * d1, rw, bad);
+        r22 += fdiv(d1 * d1, rw, bad);
+#pragma unroll
+        for (int v = 0; v < NG; ++v) {
+          C[v * 2 + 0] += fdiv(d0 * (pj[v] - pi[v]), rw, bad);
+          C[v * 2 + 1] += fdiv(d1 * (pj[v] - pi[v]), rw, bad);
+        }
+      } else {
         r11 += d0 * d0 / weight;
         r12 += d0 * d1 / weight;
         r22 += d1 * d1 / weight;
@@ -246,6 +256,21 @@ __global__ void __launch_bounds__(128) k_gradient_ls(const Dev d) {
         }
       }
     }
+  }
+  return bad;
+}
+
+template <int NS>
+__global__ void __launch_bounds__(128) k_gradient_ls(const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  constexpr int NG = 4 + NS;
+  double g[NG * 2];
+  if (p < d.nPointDomain) {
+    double pi[NG], C[NG * 2];
+    load_gradvars<NS>(d, p, pi);
+    double r11, r12, r22;
+    if (ls_sums<NS, true>(d, p, pi, C, r11, r12, r22)) ls_sums<NS, false>(d, p, pi, C, r11, r12, r22);
     if (r11 > EPS) r11 = sqrt(r11); else r11 = 0.0;
     if (fabs(r11) > EPS) r12 = r12 / r11; else r12 = 0.0;
     if (r22 - r12 * r12 > EPS) r22 = sqrt(r22 - r12 * r12); else r22 = 0.0;

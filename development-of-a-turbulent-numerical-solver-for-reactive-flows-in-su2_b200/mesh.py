@@ -123,19 +123,92 @@ def channel_mesh(nx, ny, L=0.25, H=0.025, stretch=1.0, Ns=9, oxidizer=2):
     return m
 
 
-def partition_strips(mesh, nParts):
-    """Strip partition in x of a flat mesh into nParts ranks with one halo layer, SU2's scheme:
-    owned points first, then halo points grouped by owner rank; every edge with at least one owned end is kept (halo-owned
-    edges are duplicated on both sides).  Returns a list of dict(mesh=local flat mesh, glob=local->global point ids,
-    send={rank: local owned ids}, recv={rank: local halo ids}) with matching send/recv orders."""
+def strip_owner(mesh, nParts):
+    """Owner rank of every point for a strip partition in x (equal point counts)."""
     nP = mesh["nPoint"]
-    xs = mesh["coord"][:, 0]
-    order = np.argsort(xs, kind="stable")
+    order = np.argsort(mesh["coord"][:, 0], kind="stable")
     owner = np.empty(nP, dtype=np.int64)
     bounds = [(nP * r) // nParts for r in range(nParts + 1)]
     for r in range(nParts):
         owner[order[bounds[r]:bounds[r + 1]]] = r
+    return owner
+
+
+def graph_owner(mesh, nParts, refine_passes=8):
+    """Owner rank of every point from the k-way graph partitioner of the library (rx_partition_kway: recursive inertial
+    bisection + edge-cut refinement), the stand-in for the reference's ParMETIS_V3_PartKway call
+    (Common/src/geometry_structure.cpp:11524).  Returns (owner, edge_cut)."""
+    import ctypes as C
+    from .rx_solver import load_library, RxError
+    L = load_library()
+    nP = int(mesh["nPoint"])
+    ptr = np.ascontiguousarray(mesh["nbPtr"], dtype=np.int64); adj = np.ascontiguousarray(mesh["nbPoint"], dtype=np.int64)
+    xy = np.ascontiguousarray(mesh["coord"], dtype=np.float64)
+    owner = np.empty(nP, dtype=np.int64); cut = C.c_int64(0)
+    I = C.POINTER(C.c_int64); D = C.POINTER(C.c_double)
+    rc = L.rx_partition_kway(C.c_int64(nP), ptr.ctypes.data_as(I), adj.ctypes.data_as(I), xy.ctypes.data_as(D), int(nParts),
+                             int(refine_passes), owner.ctypes.data_as(I), C.byref(cut))
+    if rc != 0:
+        raise RxError("rx_partition_kway failed (%d)" % rc)
+    return owner, int(cut.value)
+
+
+def rcm_order(mesh):
+    """new -> old point permutation: reverse Cuthill-McKee over the owned points, halo points kept last (rx_rcm_order;
+    role of CPhysicalGeometry::SetRCM_Ordering, geometry_structure.cpp:9200)."""
+    import ctypes as C
+    from .rx_solver import load_library, RxError
+    L = load_library()
+    ptr = np.ascontiguousarray(mesh["nbPtr"], dtype=np.int64); adj = np.ascontiguousarray(mesh["nbPoint"], dtype=np.int64)
+    n2o = np.empty(int(mesh["nPoint"]), dtype=np.int64)
+    I = C.POINTER(C.c_int64)
+    rc = L.rx_rcm_order(C.c_int64(int(mesh["nPoint"])), C.c_int64(int(mesh["nPointDomain"])), ptr.ctypes.data_as(I), adj.ctypes.data_as(I),
+                        n2o.ctypes.data_as(I))
+    if rc != 0:
+        raise RxError("rx_rcm_order failed (%d)" % rc)
+    return n2o
+
+
+def renumber_points(mesh, n2o, sort_edges=True):
+    """The same flat mesh with points renumbered (new point q = old point n2o[q]).  Edges keep their orientation (the
+    normal points from the first to the second node); with sort_edges they are re-sorted by (lower, higher) new index so
+    that the edge kernels walk the point arrays front to back."""
+    n2o = np.asarray(n2o, dtype=np.int64)
+    nP = int(mesh["nPoint"])
+    o2n = np.empty(nP, dtype=np.int64); o2n[n2o] = np.arange(nP)
+    en = o2n[mesh["edgeNodes"]]
+    normal = mesh["edgeNormal"]
+    if sort_edges:
+        eo = np.lexsort((en.max(axis=1), en.min(axis=1)))
+        en = en[eo]; normal = normal[eo]
+    cnt = (mesh["nbPtr"][1:] - mesh["nbPtr"][:-1])[n2o]
+    nbPtr = np.zeros(nP + 1, dtype=np.int64); np.cumsum(cnt, out=nbPtr[1:])
+    idx = np.repeat(mesh["nbPtr"][:-1][n2o] - nbPtr[:-1], cnt) + np.arange(nbPtr[-1])
+    nb = o2n[mesh["nbPoint"][idx]]
+    # neighbour lists stay sorted by neighbour index (the order the WLS sums run in is part of the numbering)
+    seg = np.repeat(np.arange(nP), cnt)
+    nb = nb[np.lexsort((nb, seg))]
+    out = dict(mesh)
+    out.update(edgeNodes=np.ascontiguousarray(en), edgeNormal=np.ascontiguousarray(normal), coord=mesh["coord"][n2o], volume=mesh["volume"][n2o],
+               nbPtr=nbPtr, nbPoint=nb)
+    mk = []
+    for m in mesh["markers"]:
+        d = dict(m); d.update(node=o2n[m["node"]], normalNeighbor=o2n[m["normalNeighbor"]]); mk.append(d)
+    out["markers"] = mk
+    return out, o2n
+
+
+def partition_mesh(mesh, owner, rcm=False):
+    """Splits a flat mesh by an owner array into ranks with one halo layer, SU2's scheme:
+    owned points first, then halo points grouped by owner rank; every edge with at least one owned end is kept (halo-owned
+    edges are duplicated on both sides); boundary vertices only on owned points.  Returns a list of dict(mesh=local flat
+    mesh, glob=local->global point ids, send={rank: local owned ids}, recv={rank: local halo ids}) with matching send/recv
+    orders.  rcm=True renumbers the owned points of every part by reverse Cuthill-McKee and re-sorts its edges."""
+    owner = np.asarray(owner, dtype=np.int64)
+    nParts = int(owner.max()) + 1
+    nP = mesh["nPoint"]
     ei, ej = mesh["edgeNodes"][:, 0], mesh["edgeNodes"][:, 1]
+    nbPtr, nbPoint = mesh["nbPtr"], mesh["nbPoint"]
     parts = []
     for r in range(nParts):
         own = np.flatnonzero(owner == r)
@@ -150,35 +223,52 @@ def partition_strips(mesh, nParts):
                    edgeNodes=np.stack([g2l[e_i], g2l[e_j]], 1), edgeNormal=mesh["edgeNormal"][keep],
                    coord=mesh["coord"][glob], volume=mesh["volume"][glob])
         # neighbour CSR restricted to local points (owned points keep all their neighbours by construction)
-        ptr = [0]; idx = []
-        for g in glob:
-            nb = g2l[mesh["nbPoint"][mesh["nbPtr"][g]:mesh["nbPtr"][g + 1]]]
-            nb = nb[nb >= 0]
-            idx.append(nb); ptr.append(ptr[-1] + len(nb))
-        loc["nbPtr"] = np.array(ptr, dtype=np.int64)
-        loc["nbPoint"] = np.concatenate(idx) if idx else np.zeros(0, dtype=np.int64)
+        cnt = nbPtr[glob + 1] - nbPtr[glob]
+        off = np.zeros(len(glob) + 1, dtype=np.int64); np.cumsum(cnt, out=off[1:])
+        idx = np.repeat(nbPtr[glob] - off[:-1], cnt) + np.arange(off[-1])
+        nb = g2l[nbPoint[idx]]
+        ok = nb >= 0
+        seg = np.repeat(np.arange(len(glob)), cnt)[ok]
+        loc["nbPtr"] = np.zeros(len(glob) + 1, dtype=np.int64)
+        np.cumsum(np.bincount(seg, minlength=len(glob)), out=loc["nbPtr"][1:])
+        loc["nbPoint"] = nb[ok]
         mk = []
         for m in mesh["markers"]:
-            sel = g2l[m["node"]] >= 0
-            sel &= owner[m["node"]] == r
+            sel = owner[m["node"]] == r
             d = dict(m)
             d.update(node=g2l[m["node"][sel]], normalNeighbor=g2l[m["normalNeighbor"][sel]], normal=m["normal"][sel])
             mk.append(d)
         loc["markers"] = mk
+        if rcm:
+            loc, o2n = renumber_points(loc, rcm_order(loc))
+            n2o = np.empty_like(o2n); n2o[o2n] = np.arange(len(o2n))
+            glob = glob[n2o]
+            g2l = np.full(nP, -1, dtype=np.int64); g2l[glob] = np.arange(len(glob))
         recv = {int(q): g2l[halo[owner[halo] == q]] for q in np.unique(owner[halo])}
-        parts.append(dict(mesh=loc, glob=glob, recv=recv, halo_glob=halo, owner=owner))
+        parts.append(dict(mesh=loc, glob=glob, recv=recv, halo_glob=halo))
     for r in range(nParts):
         send = {}
+        g2l = np.full(nP, -1, dtype=np.int64); g2l[parts[r]["glob"]] = np.arange(len(parts[r]["glob"]))
         for q in range(nParts):
             if q != r and r in parts[q]["recv"]:
                 hg = parts[q]["halo_glob"]
-                want = hg[parts[q]["owner"][hg] == r]           # global ids rank q expects from r, in q's halo order
-                g2l = np.full(nP, -1, dtype=np.int64); g2l[parts[r]["glob"]] = np.arange(len(parts[r]["glob"]))
+                want = hg[owner[hg] == r]                       # global ids rank q expects from r, in q's halo order
                 send[q] = g2l[want]
         parts[r]["send"] = send
     for p in parts:
-        p.pop("halo_glob"); p.pop("owner")
+        p.pop("halo_glob")
     return parts
+
+
+def partition_strips(mesh, nParts):
+    """Strip partition in x (deterministic, no graph partitioner): partition_mesh over strip_owner."""
+    return partition_mesh(mesh, strip_owner(mesh, nParts))
+
+
+def partition_graph(mesh, nParts, rcm=True, refine_passes=8):
+    """k-way graph partition of any flat mesh (unstructured included) + RCM numbering inside every part."""
+    owner, _ = graph_owner(mesh, nParts, refine_passes)
+    return partition_mesh(mesh, owner, rcm=rcm)
 
 
 def channel_strip_mesh(nxg, ny, rank, nranks, L=0.25, H=0.025, stretch=1.0, Ns=9, oxidizer=2):

@@ -146,6 +146,18 @@ int rx_kernel_time(rx_ctx*, int which, int reps, double* msAvg);
  * roof of the viscous and source kernels (MEASURED_PEAKS.json carries no FP64 entry). */
 int rx_fp64_peak(rx_ctx*, double* tflops);
 
+/* partitioning (host-side graph tools, no device work; csrc/host/rx_partition.cpp).
+ * rx_partition_kway: k-way partition of the point adjacency graph (CSR nbPtr/nbPoint, the same arrays rx_mesh carries) into
+ * nParts parts of equal size (2 % tolerance) with a small edge cut: recursive inertial bisection on coord[nPoint][2] +
+ * boundary refinement (refinePasses sweeps; 0 = geometric split only).  owner[nPoint] receives the part of every point,
+ * *edgeCut (may be NULL) the number of cut edges.  Stands where the reference calls ParMETIS_V3_PartKway
+ * (Common/src/geometry_structure.cpp:11524 via SetColorGrid_Parallel, driver_structure.cpp:126).
+ * rx_rcm_order: reverse Cuthill-McKee numbering of the first nPointDomain (owned) points, halo points stay last;
+ * newToOld[nPoint].  Role of CPhysicalGeometry::SetRCM_Ordering (geometry_structure.cpp:9200, called driver_structure.cpp:560). */
+int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const double* coord, int nParts,
+                      int refinePasses, int64_t* owner, int64_t* edgeCut);
+int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld);
+
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t rx_launch_count(rx_ctx*);
 

@@ -1,0 +1,184 @@
+"""k-way graph partitioner and RCM numbering of the library (rx_partition_kway / rx_rcm_order, csrc/host/rx_partition.cpp) —
+the stand-ins for the reference's ParMETIS_V3_PartKway (geometry_structure.cpp:11524) and SetRCM_Ordering (:9200) —
+on the SHIPPED unstructured jet-reactor mesh (9000 points, quads, from tests/golden) and on a triangulated channel:
+balance, edge cut, SU2's halo scheme (owned first, one halo layer, edges with an owned end), matching send/recv lists,
+and a world-size-3 gloo exchange over a graph partition."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+from rxcase import GOLDEN, Case, load_package, mesh_dict
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def pk():
+    p = load_package()
+    p.build_library()
+    return p
+
+
+@pytest.fixture(scope="module")
+def jet():
+    return mesh_dict(Case(os.path.join(GOLDEN, "jet_rans_perturbed.npz")))
+
+
+def _cut(mesh, owner):
+    en = np.asarray(mesh["edgeNodes"])
+    return int((owner[en[:, 0]] != owner[en[:, 1]]).sum())
+
+
+@pytest.mark.parametrize("k", [2, 3, 4, 8])
+def test_kway_balance_and_cut_on_shipped_mesh(pk, jet, k):
+    owner, cut = pk.graph_owner(jet, k)
+    n = jet["nPoint"]
+    sizes = np.bincount(owner, minlength=k)
+    assert sizes.sum() == n and sizes.min() > 0
+    assert sizes.max() <= np.ceil(n / k) * 1.03 + 1           # 2 % tolerance of the partitioner (+ rounding)
+    assert cut == _cut(jet, owner)
+    # the refined cut is no worse than the purely geometric split, and well below what strips in x give on this
+    # 10:1 aspect-ratio mesh partitioned along its long axis would give if cut across it
+    owner0, cut0 = pk.graph_owner(jet, k, refine_passes=0)
+    assert cut <= cut0
+    # determinism
+    owner2, _ = pk.graph_owner(jet, k)
+    assert np.array_equal(owner, owner2)
+    # every part is connected enough to be useful: the cut is a small fraction of the edges
+    assert cut < 0.06 * len(jet["edgeNodes"]) * np.log2(k) + 1
+
+
+def test_kway_on_square_channel_beats_strips(pk):
+    g = pk.channel_mesh(64, 64, L=1.0, H=1.0)
+    owner, cut = pk.graph_owner(g, 8)
+    strips = _cut(g, pk.strip_owner(g, 8))
+    assert cut < strips                                          # blocks cut fewer edges than 8 strips of a square
+    sizes = np.bincount(owner, minlength=8)
+    assert sizes.max() <= 64 * 64 / 8 * 1.03 + 1
+
+
+def _check_parts(mesh, parts, owner):
+    nP = mesh["nPoint"]
+    en_g = np.asarray(mesh["edgeNodes"]); nrm_g = np.asarray(mesh["edgeNormal"]).reshape(-1, 2)
+    gmap = {(int(a), int(b)): n for (a, b), n in zip(en_g, nrm_g)}
+    seen = np.zeros(nP, dtype=int)
+    counted = 0
+    for r, p in enumerate(parts):
+        m, glob = p["mesh"], p["glob"]
+        nOwn = m["nPointDomain"]
+        assert np.all(owner[glob[:nOwn]] == r) and np.all(owner[glob[nOwn:]] != r)
+        seen[glob[:nOwn]] += 1
+        np.testing.assert_array_equal(m["coord"], mesh["coord"][glob])
+        np.testing.assert_array_equal(m["volume"], mesh["volume"][glob])
+        en = np.asarray(m["edgeNodes"]); nrm = np.asarray(m["edgeNormal"]).reshape(-1, 2)
+        assert np.all((en[:, 0] < nOwn) | (en[:, 1] < nOwn))
+        for (a, b), n in zip(en, nrm):                           # orientation and normal are the global edge's
+            assert np.array_equal(gmap[(int(glob[a]), int(glob[b]))], n)
+        counted += int((en[:, 0] < nOwn).sum())
+        for q in range(0, nOwn, 11):                             # owned points keep all their neighbours
+            nb = m["nbPoint"][m["nbPtr"][q]:m["nbPtr"][q + 1]]
+            gq = glob[q]
+            assert set(glob[nb].tolist()) == set(mesh["nbPoint"][mesh["nbPtr"][gq]:mesh["nbPtr"][gq + 1]].tolist())
+        for mk in m["markers"]:
+            assert np.all(np.asarray(mk["node"]) < nOwn)
+        for q, ids in p["recv"].items():
+            assert np.all(np.asarray(ids) >= nOwn)
+            snd = parts[q]["send"][r]
+            assert np.all(np.asarray(snd) < parts[q]["mesh"]["nPointDomain"])
+            assert np.array_equal(glob[ids], parts[q]["glob"][snd])
+        # halo points are grouped by neighbour: contiguous blocks
+        halo_owner = owner[glob[nOwn:]]
+        assert np.all(np.diff(halo_owner) >= 0)
+    assert np.all(seen == 1)
+    assert counted == len(en_g)
+    for k in range(len(mesh["markers"])):
+        assert sum(len(p["mesh"]["markers"][k]["node"]) for p in parts) == len(mesh["markers"][k]["node"])
+
+
+@pytest.mark.parametrize("k,rcm", [(2, False), (3, True), (5, True)])
+def test_graph_partition_follows_su2_halo_scheme(pk, jet, k, rcm):
+    owner, _ = pk.graph_owner(jet, k)
+    parts = pk.partition_mesh(jet, owner, rcm=rcm)
+    _check_parts(jet, parts, owner)
+
+
+def _bandwidth(mesh, n):
+    en = np.asarray(mesh["edgeNodes"])
+    both = (en[:, 0] < n) & (en[:, 1] < n)
+    return int(np.abs(en[both, 0] - en[both, 1]).max())
+
+
+def test_rcm_is_a_permutation_and_reduces_bandwidth(pk, jet):
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(jet["nPoint"])
+    shuffled, _ = pk.renumber_points(jet, perm)
+    n2o = pk.rcm_order(shuffled)
+    assert np.array_equal(np.sort(n2o), np.arange(jet["nPoint"]))
+    ordered, o2n = pk.renumber_points(shuffled, n2o)
+    bw_shuffled, bw_rcm = _bandwidth(shuffled, jet["nPoint"]), _bandwidth(ordered, jet["nPoint"])
+    assert bw_rcm < 0.1 * bw_shuffled
+    assert bw_rcm <= 2 * _bandwidth(jet, jet["nPoint"])           # as good as the reference's own (RCM) numbering
+    en = np.asarray(ordered["edgeNodes"])
+    lo = en.min(axis=1)
+    assert np.all(np.diff(lo) >= 0)                               # edges re-sorted by lower node
+    # halo points stay last
+    owner, _ = pk.graph_owner(jet, 3)
+    part = pk.partition_mesh(jet, owner, rcm=False)[1]
+    n2o = pk.rcm_order(part["mesh"])
+    nOwn = part["mesh"]["nPointDomain"]
+    assert np.array_equal(np.sort(n2o[:nOwn]), np.arange(nOwn)) and np.array_equal(n2o[nOwn:], np.arange(nOwn, part["mesh"]["nPoint"]))
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, HERE)
+    from rxcase import GOLDEN, Case, load_package, mesh_dict
+    pk = load_package()
+    par = __import__(pk.__name__ + ".parallel", fromlist=["x"])
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = mesh_dict(Case(os.path.join(GOLDEN, "jet_rans_perturbed.npz")))
+        part = pk.partition_graph(g, world)[rank]             # deterministic: every rank computes the same partition
+        m, glob = part["mesh"], part["glob"]
+        nP, nOwn = m["nPoint"], m["nPointDomain"]
+        fields = {}
+        for what, nv in ((par.WHAT_SOLUTION, 13), (par.WHAT_GRADIENT, 26), (par.WHAT_LIMITER, 4)):
+            f = torch.full((nv, nP), float("nan"), dtype=torch.float64)
+            for v in range(nv):
+                f[v, :nOwn] = torch.from_numpy(glob[:nOwn] + 1e-3 * (v + 100 * what))
+            fields[what] = f
+        ex = par.HaloExchanger(par.TensorHaloState(fields), part, torch.device("cpu"))
+        ok = True
+        for what, f in fields.items():
+            ex.exchange(what)
+            want = np.stack([glob + 1e-3 * (v + 100 * what) for v in range(f.shape[0])])
+            ok = ok and bool(np.array_equal(f.numpy(), want))
+        out[rank] = 1 if ok else 0
+    finally:
+        dist.destroy_process_group()
+
+
+def test_halo_exchange_over_graph_partition_gloo():
+    import torch.multiprocessing as mp
+    load_package().build_library()
+    world = 3
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    out = ctx.Array("i", [-1] * world)
+    procs = [ctx.Process(target=_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+        assert p.exitcode == 0
+    assert list(out) == [1] * world
