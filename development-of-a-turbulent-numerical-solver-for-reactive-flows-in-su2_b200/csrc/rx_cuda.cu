@@ -9,12 +9,14 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
 using namespace rx;
 
 static constexpr size_t SM_PAIR = (size_t)VP_SMW * VP_BS * sizeof(double);
+static constexpr size_t SM_PAIR_RANS = (size_t)VP_SMW_RANS * VP_BS * sizeof(double);
 static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
 static thread_local std::string g_create_error;
@@ -32,6 +34,7 @@ struct rx_ctx {
   size_t stageBytes = 0;
   int updBlocks = 0;
   long long launches = 0;
+  bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
 
 #define RX_CK(call)                                                                                   \
@@ -148,9 +151,10 @@ static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
     return;
   }
   if (!VISC) { k_edge_flux<9, CONV, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; return; }
-  if (c->o.rans) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
+  if (c->o.rans && c->ransThreadPerEdge) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
   if (CONV) { k_edge_flux<9, true, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; }
-  k_edge_visc_pair<9><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
+  if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(c->cc9, c->o, d);
+  else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
   c->launches++;
 }
 
@@ -173,12 +177,14 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   if (m->nPoint >= (1LL << 31) || m->nEdge >= (1LL << 31)) { g_create_error = "rx_create: mesh exceeds int32 indices"; return RX_ERR_UNSUPPORTED; }
   rx_ctx* c = new rx_ctx();
   c->device = op->device;
+  { const char* ev = getenv("RX_RANS_THREAD_PER_EDGE"); c->ransThreadPerEdge = ev && ev[0] == '1'; }
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
   {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
     const int smv = (int)SM_VISC;
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_edge_flux<9, true, true, true>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_flux<9, false, true, true>, at, smv);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
     if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }

@@ -28,6 +28,7 @@ constexpr int VP_BS = RX_VP_BS;       // threads per block (two per edge)
 constexpr int VP_MINB = RX_VP_MINB;   // resident blocks per SM the register budget is set for
 constexpr int VP_MREG = RX_VP_MREG;   // matrix slots held in registers; the others are read from shared memory
 constexpr int VP_SMW = 5 * 9;   // shared-memory words per thread: the lane's five matrix rows
+constexpr int VP_SMW_RANS = 5 * 9 + 2 * 9;   // SST closure: + the column norms of the pivoted QR (updated, direct)
 constexpr unsigned VP_FULL = 0xffffffffu;
 
 struct PairLane {
@@ -78,7 +79,177 @@ __device__ __forceinline__ void pair_gemv(MatF A, const double* f, double* res) 
   }
 }
 
+
+// ---- Eigen::ColPivHouseholderQR(Mt).solve(b) for two right-hand sides with the ROWS of Mt split over the pair
+// (colpiv_qr_solve<> in rx_flux.cuh is the serial form and carries the citations: same pivot rule, rank threshold, norm
+// down-dating and reflector formulas; sums over rows are formed as lane partials that meet through one shuffle).
+// Layout: slot q of the lane is row qrow[q] (2q + lane; slot 4: row 8 on the odd lane, a zero row on the even lane), entry
+// (q, column j) at sm[(q*NS + j)*VP_BS]; the column norms (updated / direct) are replicated in words 45.. and 54.. of each
+// lane.  The reflectors are applied to the right-hand sides c[d][q] as they are formed (the same operations
+// householderSequence().transpose() performs afterwards).  On return c[d][q] = solution entry of row qrow[q].
 template <int NS>
+__device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* sm, double (*c)[5]) {
+  static_assert(NS == 9, "row split of nine species");
+  const int l = L.l;
+  const int lane = (int)(threadIdx.x & 31);
+  auto A = [&](int q, int j) -> double& { return sm[(q * NS + j) * VP_BS]; };
+  auto nU = [&](int j) -> double& { return sm[(5 * NS + j) * VP_BS]; };
+  auto nD = [&](int j) -> double& { return sm[(6 * NS + j) * VP_BS]; };
+  int qrow[5];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) qrow[q] = 2 * q + l;
+  qrow[4] = l ? 8 : 1000;
+  double mx = 0.0;
+#pragma unroll 1
+  for (int j = 0; j < NS; ++j) {
+    double s = 0.0;
+#pragma unroll
+    for (int q = 0; q < 5; ++q) { const double a = A(q, j); s += a * a; }
+    s = s + L.other(s);
+    const double n = sqrt(s);
+    nU(j) = n; nD(j) = n;
+    mx = fmax(mx, n);
+  }
+  const double eps = 2.220446049250313e-16;
+  const double threshold_helper = (mx * eps) * (mx * eps) / (double)NS;
+  const double downdate = sqrt(eps);
+  int nonzero = NS;
+  unsigned long long perm = 0x876543210ULL;   // nibble i = original column now at position i
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+    int big = k;
+    double nb = nU(k);
+#pragma unroll
+    for (int j = k + 1; j < NS; ++j) { const double nj = nU(j); if (nj > nb) { nb = nj; big = j; } }
+    if (nonzero == NS && nb * nb < threshold_helper * (double)(NS - k)) nonzero = k;
+    if (big != k) {
+#pragma unroll
+      for (int q = 0; q < 5; ++q) { const double t = A(q, k); A(q, k) = A(q, big); A(q, big) = t; }
+      nU(big) = nU(k); nU(k) = nb;
+      const double t = nD(k); nD(k) = nD(big); nD(big) = t;
+      const unsigned long long pk = (perm >> (4 * k)) & 15ULL, pb = (perm >> (4 * big)) & 15ULL;
+      perm = (perm & ~((15ULL << (4 * k)) | (15ULL << (4 * big)))) | (pb << (4 * k)) | (pk << (4 * big));
+    }
+    const int ks = k < 8 ? (k >> 1) : 4;                    // slot of row k on its owner
+    const int owner = (lane & ~1) | (k < 8 ? (k & 1) : 1);  // lane that owns row k
+    double v[5];
+    bool act[5], own[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) { v[q] = A(q, k); act[q] = qrow[q] > k; own[q] = qrow[q] == k; }
+    const double c0 = __shfl_sync(VP_FULL, v[ks], owner);
+    double tailSq = 0.0;
+#pragma unroll
+    for (int q = 0; q < 5; ++q) tailSq += act[q] ? v[q] * v[q] : 0.0;
+    tailSq = tailSq + L.other(tailSq);
+    double beta, tau;
+    if (tailSq <= 2.2250738585072014e-308) {
+      tau = 0.0; beta = c0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) if (act[q]) v[q] = 0.0;
+    } else {
+      beta = sqrt(c0 * c0 + tailSq);
+      if (c0 >= 0.0) beta = -beta;
+      const double den = c0 - beta;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) if (act[q]) v[q] = v[q] / den;
+      tau = (beta - c0) / beta;
+    }
+#pragma unroll
+    for (int q = 0; q < 5; ++q) { if (act[q]) A(q, k) = v[q]; if (own[q]) A(q, k) = beta; }
+    const bool apply = tau != 0.0;
+    // remaining columns: t = v.w + w_k,  w_k -= tau t,  w_i -= tau v_i t;  then the norm down-date of the column
+#pragma unroll 1
+    for (int j = k + 1; j < NS; ++j) {
+      double w[5];
+#pragma unroll
+      for (int q = 0; q < 5; ++q) w[q] = A(q, j);
+      double p = 0.0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) p += act[q] ? v[q] * w[q] : 0.0;
+      const double w0 = __shfl_sync(VP_FULL, w[ks], owner);
+      double t = p + L.other(p);
+      t += w0;
+      const double wk = apply ? w0 - tau * t : w0;
+      double s2 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        if (act[q]) { if (apply) w[q] = w[q] - tau * v[q] * t; A(q, j) = w[q]; s2 += w[q] * w[q]; }
+        if (own[q]) A(q, j) = wk;
+      }
+      const double nu = nU(j);
+      bool recompute = false;
+      double scaled = nu;
+      if (nu != 0.0) {
+        double temp = fabs(wk) / nu;
+        temp = (1.0 + temp) * (1.0 - temp);
+        temp = temp < 0.0 ? 0.0 : temp;
+        const double qq = nu / nD(j);
+        const double temp2 = temp * (qq * qq);
+        if (temp2 <= downdate) recompute = true; else scaled = nu * sqrt(temp);
+      }
+      if (__any_sync(VP_FULL, recompute)) {
+        s2 = s2 + L.other(s2);
+        if (recompute) { scaled = sqrt(s2); nD(j) = scaled; }
+      }
+      nU(j) = scaled;
+    }
+    // the two right-hand sides, while the factorisation has full rank so far (solve() applies the first `nonzero` reflectors)
+    const bool applyR = apply && nonzero == NS;
+#pragma unroll
+    for (int dd = 0; dd < 2; ++dd) {
+      double p = 0.0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) p += act[q] ? v[q] * c[dd][q] : 0.0;
+      const double w0 = __shfl_sync(VP_FULL, c[dd][ks], owner);
+      double t = p + L.other(p);
+      t += w0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        if (applyR && act[q]) c[dd][q] = c[dd][q] - tau * v[q] * t;
+        if (applyR && own[q]) c[dd][q] = w0 - tau * t;
+      }
+    }
+  }
+  // back substitution with R (upper triangle, column i holds R(0..i, i)), rows >= nonzero give zero
+#pragma unroll
+  for (int i = NS - 1; i >= 0; --i) {
+    const int is = i < 8 ? (i >> 1) : 4;
+    const int owner = (lane & ~1) | (i < 8 ? (i & 1) : 1);
+    const bool mine = qrow[is] == i;
+    const bool on = i < nonzero;
+    double col[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) col[q] = A(q, i);
+#pragma unroll
+    for (int dd = 0; dd < 2; ++dd) {
+      const double num = mine ? c[dd][is] : 1.0, den = mine ? col[is] : 1.0;
+      const double ci = __shfl_sync(VP_FULL, num / den, owner);
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        if (on && qrow[q] < i) c[dd][q] = c[dd][q] - ci * col[q];
+        if (qrow[q] == i) c[dd][q] = on ? ci : 0.0;
+      }
+    }
+  }
+  // undo the column permutation: entry i of the triangular solution belongs to original row perm[i].  The matrix words are
+  // dead; each lane drops its entries into the words of the lane that owns the target row (word dd*5 + slot).
+  __syncwarp();
+  double* const smPair = sm - l;
+#pragma unroll
+  for (int q = 0; q < 5; ++q) {
+    if (qrow[q] < NS) {
+      const int tr = (int)((perm >> (4 * qrow[q])) & 15ULL);
+      const int tl = tr < 8 ? (tr & 1) : 1, tq = tr < 8 ? (tr >> 1) : 4;
+      smPair[tl + (0 * 5 + tq) * VP_BS] = c[0][q];
+      smPair[tl + (1 * 5 + tq) * VP_BS] = c[1][q];
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < 5; ++q) { c[0][q] = sm[(0 * 5 + q) * VP_BS]; c[1][q] = sm[(1 * 5 + q) * VP_BS]; }
+}
+
+template <int NS, bool RANS>
 __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   static_assert(NS == 9, "the row split {0,2,4,6 | 1,3,5,7,8} is laid out for nine species");
   extern __shared__ double vp_sm[];   // word w of thread t at vp_sm[w * VP_BS + t]
@@ -183,8 +354,28 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       FT[2][a] += ktr * GT[a];
     }
   }
+  // SST closure, part 1 (SST_Reactive_ResidualClosure :656-852): Boussinesq stresses join the tensor before the projection
+  double muT = 0.0;
+  if (RANS) {
+    muT = 2.0 / (1.0 / d.turb[pi] + 1.0 / d.turb[pj]);
+    const double ke = 0.5 * (d.turb[np + pi] + d.turb[np + pj]);
+    const double Gv[2][2] = {{GU[0], GU[1]}, {GV[0], GV[1]}};
+    const double vel[2] = {um, vm};
+    double dv = 0.0;
+    dv += Gv[0][0]; dv += Gv[1][1];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      double tt[2] = {0.0, 0.0};
+#pragma unroll
+      for (int b = 0; b < 2; ++b) tt[b] += muT * (Gv[b][a] + Gv[a][b]);
+      tt[a] -= TWO3 * (muT * dv + ke * rho);
+#pragma unroll
+      for (int b = 0; b < 2; ++b) { FT[b][a] += tt[b]; FT[2][a] += tt[b] * vel[b]; }
+    }
+  }
   // momentum rows are complete; of the energy row only the two stress/heat products have to outlive the solve
-  const double fE0 = FT[2][0] * nx, fE1 = FT[2][1] * ny;
+  // (RANS: the raw tensor entries, which still receive the species and k terms of the closure)
+  const double fE0 = RANS ? FT[2][0] : FT[2][0] * nx, fE1 = RANS ? FT[2][1] : FT[2][1] * ny;
   if (keep && l == 0) {
     double pMx = 0.0, pMy = 0.0;
     pMx += FT[0][0] * nx; pMx += FT[0][1] * ny;
@@ -384,15 +575,90 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   // order, then the stress/heat part; species rows go out from the lane that owns them.
   const double sumJ = pair_redux(L, x);
   const SplPos sp = spl_pos(cc, T);
-  double hj[5];
+  double hsr[5], hj[5];
 #pragma unroll
-  for (int k = 0; k < 5; ++k) hj[k] = -(spl_eval(cc, P_H, row[k], sp) / cc.M[row[k]]) * x[k];
+  for (int k = 0; k < 5; ++k) { hsr[k] = spl_eval(cc, P_H, row[k], sp) / cc.M[row[k]]; hj[k] = -hsr[k] * x[k]; }
   pair_gather(L, hj, f);
   double pE = 0.0;
 #pragma unroll
   for (int s2 = 0; s2 < NS; ++s2) pE += f[s2];
-  pE += fE0;
-  pE += fE1;
+  double pS[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) pS[k] = -x[k];
+  if (RANS) {
+    // ---- SST closure, part 2: mass-fraction gradients from the mole-fraction ones through the molar->mass operator
+    // (Get_Molar2MassGrad_Operator :861-880, solved with Eigen's ColPivHouseholderQR :743), then the turbulent species,
+    // enthalpy and k fluxes in the reference's order of additions (:800-830; viscous_flux<> in rx_flux.cuh).
+    double sig = 0.0;
+#pragma unroll
+    for (int s2 = 0; s2 < NS; ++s2) sig = sig + Xs[s2];
+    double Yr[5], Xr[5];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { Yr[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]); Xr[k] = L.sel(Xs[2 * k], Xs[2 * k + 1]); }
+    Yr[4] = Ys[8]; Xr[4] = Xs[8];
+#pragma unroll 1
+    for (int k = 0; k < 5; ++k) {
+      const int r = k < 4 ? 2 * k + l : 8;
+      const bool zero = k == 4 && l == 0;   // the even lane has four rows; its fifth slot is a zero row of the QR
+      const double a = cc.Mtot / cc.M[r] * (Yr[0] - Xr[0] + sig);
+      const double yom = Yr[0] / cc.M[r];
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        const double b = cc.Mtot * (yom - Xr[0] / cc.M[c]);
+        const double val = (c == r) ? a * 1.0 + b * 0.0 : a * 0.0 + b * 1.0;
+        smA(k, c) = zero ? 0.0 : val;
+      }
+#pragma unroll
+      for (int m = 0; m < 4; ++m) { Yr[m] = Yr[m + 1]; Xr[m] = Xr[m + 1]; }
+    }
+    double MG[2][5];
+#pragma unroll
+    for (int dd = 0; dd < 2; ++dd) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) MG[dd][k] = G[2 + k][dd];
+      MG[dd][4] = l ? G[1][dd] : 0.0;
+    }
+    pair_colpiv_qr_solve<NS>(L, sm, MG);
+#pragma unroll
+    for (int dd = 0; dd < 2; ++dd) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) if (fabs(G[2 + k][dd]) < 1e-8) MG[dd][k] = 0.0;
+      if (fabs(G[1][dd]) < 1e-8) MG[dd][4] = 0.0;
+    }
+    const double c1 = muT / (o.prandtlTurb * o.lewisTurb), c2 = muT / o.prandtlTurb;
+    const double sigma_k = d.turb[5 * np + pi];   // sigma_k of the first node (:5345)
+    const double nrm[2] = {nx, ny};
+    double FE[2] = {fE0, fE1};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) Yr[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]);
+    Yr[4] = Ys[8];
+    double cps[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) cps[k] = spl_eval(cc, P_CP, row[k], sp) / cc.M[row[k]];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      double t1[5], t2[5];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        pS[k] += c1 * MG[a][k] * nrm[a];
+        t1[k] = c1 * hsr[k] * Yr[k] * MG[a][k];
+        t2[k] = c2 * cps[k] * Yr[k] * GT[a];
+      }
+      pair_gather(L, t1, f);
+#pragma unroll
+      for (int s2 = 0; s2 < NS; ++s2) FE[a] += f[s2];
+      pair_gather(L, t2, f);
+#pragma unroll
+      for (int s2 = 0; s2 < NS; ++s2) FE[a] += f[s2];
+      const double gk = 0.5 * (d.turb[(3 + a) * np + pi] + d.turb[(3 + a) * np + pj]);
+      FE[a] += (mu + muT / sigma_k) * gk;
+    }
+    pE += FE[0] * nx;
+    pE += FE[1] * ny;
+  } else {
+    pE += fE0;
+    pE += fE1;
+  }
   if (!keep) return;
   const long long ne = d.ne;
   if (l == 0) {
@@ -400,8 +666,8 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
     d.fluxV[U_E * ne + e] = pE;
   }
 #pragma unroll
-  for (int k = 0; k < 4; ++k) d.fluxV[(U_S + row[k]) * ne + e] = -x[k];
-  if (l == 1) d.fluxV[(U_S + 8) * ne + e] = -x[4];
+  for (int k = 0; k < 4; ++k) d.fluxV[(U_S + row[k]) * ne + e] = pS[k];
+  if (l == 1) d.fluxV[(U_S + 8) * ne + e] = pS[4];
 }
 
 }  // namespace rx
