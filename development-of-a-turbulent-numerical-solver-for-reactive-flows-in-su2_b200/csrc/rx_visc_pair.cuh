@@ -28,7 +28,7 @@ constexpr int VP_BS = RX_VP_BS;       // threads per block (two per edge)
 constexpr int VP_MINB = RX_VP_MINB;   // resident blocks per SM the register budget is set for
 constexpr int VP_MREG = RX_VP_MREG;   // matrix slots held in registers; the others are read from shared memory
 constexpr int VP_SMW = 5 * 9;   // shared-memory words per thread: the lane's five matrix rows
-constexpr int VP_SMW_RANS = 5 * 9 + 2 * 9;   // SST closure: + the column norms of the pivoted QR (updated, direct)
+constexpr int VP_SMW_RANS = 13 * 5;   // SST closure: the pair shares a 9 x 13 array (operator, two right-hand sides, norms)
 constexpr unsigned VP_FULL = 0xffffffffu;
 
 struct PairLane {
@@ -80,173 +80,182 @@ __device__ __forceinline__ void pair_gemv(MatF A, const double* f, double* res) 
 }
 
 
-// ---- Eigen::ColPivHouseholderQR(Mt).solve(b) for two right-hand sides with the ROWS of Mt split over the pair
-// (colpiv_qr_solve<> in rx_flux.cuh is the serial form and carries the citations: same pivot rule, rank threshold, norm
-// down-dating and reflector formulas; sums over rows are formed as lane partials that meet through one shuffle).
-// Layout: slot q of the lane is row qrow[q] (2q + lane; slot 4: row 8 on the odd lane, a zero row on the even lane), entry
-// (q, column j) at sm[(q*NS + j)*VP_BS]; the column norms (updated / direct) are replicated in words 45.. and 54.. of each
-// lane.  The reflectors are applied to the right-hand sides c[d][q] as they are formed (the same operations
-// householderSequence().transpose() performs afterwards).  On return c[d][q] = solution entry of row qrow[q].
+// ---- Eigen::ColPivHouseholderQR(Mt).solve(b) for two right-hand sides, worked by the two lanes of a pair on ONE copy of
+// the matrix in shared memory (colpiv_qr_solve<> in rx_flux.cuh is the serial form and carries the citations; this is the
+// same sequence of operations in the same order — pivot rule, rank threshold, norm down-dating, reflectors, natural-order
+// sums — so the result equals the serial routine's bit for bit).  The work is split by COLUMNS: after the reflector of
+// step k is formed, lane l applies it to columns k+1+l, k+3+l, ... (the two right-hand sides are columns 9 and 10) and
+// down-dates their norms; each lane back-substitutes one right-hand side.  No sum crosses lanes.
+// Storage (pair-shared: the words of both lanes): entry (i, j) at smPair[(i & 1) + (j*5 + (i >> 1)) * VP_BS], j = 0..10;
+// updated / direct column norms at column slots 11 and 12 (i = column index).
 template <int NS>
-__device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* sm, double (*c)[5]) {
-  static_assert(NS == 9, "row split of nine species");
+struct PairMat {
+  double* base;   // smPair
+  __device__ __forceinline__ double& operator()(int i, int j) const { return base[(i & 1) + (j * 5 + (i >> 1)) * VP_BS]; }
+  __device__ __forceinline__ double* col(int j) const { return base + (j * 5) * VP_BS; }
+  __device__ __forceinline__ static int off(int i) { return (i & 1) + (i >> 1) * VP_BS; }   // entry i of a column
+};
+constexpr int VP_QR_COLS = 13;   // 9 matrix columns, 2 right-hand sides, 2 norm vectors
+
+template <int NS>
+__device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* smPair, double (*mg)[5]) {
+  static_assert(NS == 9, "storage laid out for nine species");
+  using PM = PairMat<NS>;
+  const PM M{smPair};
   const int l = L.l;
-  const int lane = (int)(threadIdx.x & 31);
-  auto A = [&](int q, int j) -> double& { return sm[(q * NS + j) * VP_BS]; };
-  auto nU = [&](int j) -> double& { return sm[(5 * NS + j) * VP_BS]; };
-  auto nD = [&](int j) -> double& { return sm[(6 * NS + j) * VP_BS]; };
-  int qrow[5];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) qrow[q] = 2 * q + l;
-  qrow[4] = l ? 8 : 1000;
-  double mx = 0.0;
-#pragma unroll 1
-  for (int j = 0; j < NS; ++j) {
+  double* const nU = M.col(NS + 2);
+  double* const nD = M.col(NS + 3);
+  __syncwarp();   // the operator rows and right-hand sides were written by both lanes
+  for (int j = l; j < NS; j += 2) {
+    const double* cj = M.col(j);
     double s = 0.0;
 #pragma unroll
-    for (int q = 0; q < 5; ++q) { const double a = A(q, j); s += a * a; }
-    s = s + L.other(s);
+    for (int i = 0; i < NS; ++i) s += cj[PM::off(i)] * cj[PM::off(i)];
     const double n = sqrt(s);
-    nU(j) = n; nD(j) = n;
-    mx = fmax(mx, n);
+    nU[PM::off(j)] = n; nD[PM::off(j)] = n;
   }
+  __syncwarp();
   const double eps = 2.220446049250313e-16;
+  double mx = nU[PM::off(0)];
+#pragma unroll
+  for (int j = 1; j < NS; ++j) mx = fmax(mx, nU[PM::off(j)]);
   const double threshold_helper = (mx * eps) * (mx * eps) / (double)NS;
   const double downdate = sqrt(eps);
   int nonzero = NS;
   unsigned long long perm = 0x876543210ULL;   // nibble i = original column now at position i
-#pragma unroll
+#pragma unroll 1
   for (int k = 0; k < NS; ++k) {
+    // pivot: first column of largest updated norm (both lanes, same result)
     int big = k;
-    double nb = nU(k);
-#pragma unroll
-    for (int j = k + 1; j < NS; ++j) { const double nj = nU(j); if (nj > nb) { nb = nj; big = j; } }
+    double nb = nU[PM::off(k)];
+    for (int j = k + 1; j < NS; ++j) { const double nj = nU[PM::off(j)]; if (nj > nb) { nb = nj; big = j; } }
     if (nonzero == NS && nb * nb < threshold_helper * (double)(NS - k)) nonzero = k;
     if (big != k) {
+      double* ck = M.col(k); double* cb = M.col(big);
 #pragma unroll
-      for (int q = 0; q < 5; ++q) { const double t = A(q, k); A(q, k) = A(q, big); A(q, big) = t; }
-      nU(big) = nU(k); nU(k) = nb;
-      const double t = nD(k); nD(k) = nD(big); nD(big) = t;
+      for (int h = 0; h < 5; ++h) {   // lane l swaps the rows of its parity
+        const int i = 2 * h + l;
+        if (i < NS) { const double t = ck[PM::off(i)]; ck[PM::off(i)] = cb[PM::off(i)]; cb[PM::off(i)] = t; }
+      }
+      if (l == 0) {
+        nU[PM::off(big)] = nU[PM::off(k)]; nU[PM::off(k)] = nb;
+        const double t = nD[PM::off(k)]; nD[PM::off(k)] = nD[PM::off(big)]; nD[PM::off(big)] = t;
+      }
       const unsigned long long pk = (perm >> (4 * k)) & 15ULL, pb = (perm >> (4 * big)) & 15ULL;
       perm = (perm & ~((15ULL << (4 * k)) | (15ULL << (4 * big)))) | (pb << (4 * k)) | (pk << (4 * big));
     }
-    const int ks = k < 8 ? (k >> 1) : 4;                    // slot of row k on its owner
-    const int owner = (lane & ~1) | (k < 8 ? (k & 1) : 1);  // lane that owns row k
-    double v[5];
-    bool act[5], own[5];
+    __syncwarp();
+    // reflector of column k: both lanes form the scalars, each normalises the entries of its parity
+    double* const ck = M.col(k);
+    double vv[NS];   // entries below the diagonal, zero elsewhere (a zero entry adds nothing to the sums below)
 #pragma unroll
-    for (int q = 0; q < 5; ++q) { v[q] = A(q, k); act[q] = qrow[q] > k; own[q] = qrow[q] == k; }
-    const double c0 = __shfl_sync(VP_FULL, v[ks], owner);
+    for (int i = 1; i < NS; ++i) vv[i] = i > k ? ck[PM::off(i)] : 0.0;
+    const double c0 = M(k, k);
+    __syncwarp();   // both lanes hold the raw column before either overwrites its half
     double tailSq = 0.0;
 #pragma unroll
-    for (int q = 0; q < 5; ++q) tailSq += act[q] ? v[q] * v[q] : 0.0;
-    tailSq = tailSq + L.other(tailSq);
+    for (int i = 1; i < NS; ++i) tailSq += vv[i] * vv[i];
     double beta, tau;
     if (tailSq <= 2.2250738585072014e-308) {
       tau = 0.0; beta = c0;
 #pragma unroll
-      for (int q = 0; q < 5; ++q) if (act[q]) v[q] = 0.0;
+      for (int i = 1; i < NS; ++i) vv[i] = 0.0;
     } else {
       beta = sqrt(c0 * c0 + tailSq);
       if (c0 >= 0.0) beta = -beta;
       const double den = c0 - beta;
+      bool bad = false;
+      const Recip rden = frecip(den);
+      double vq[NS];
 #pragma unroll
-      for (int q = 0; q < 5; ++q) if (act[q]) v[q] = v[q] / den;
+      for (int i = 1; i < NS; ++i) vq[i] = fdiv(vv[i], rden, bad);
+      if (bad) {
+#pragma unroll
+        for (int i = 1; i < NS; ++i) vq[i] = vv[i] / den;
+      }
+#pragma unroll
+      for (int i = 1; i < NS; ++i) vv[i] = vq[i];
       tau = (beta - c0) / beta;
     }
 #pragma unroll
-    for (int q = 0; q < 5; ++q) { if (act[q]) A(q, k) = v[q]; if (own[q]) A(q, k) = beta; }
-    const bool apply = tau != 0.0;
-    // remaining columns: t = v.w + w_k,  w_k -= tau t,  w_i -= tau v_i t;  then the norm down-date of the column
-#pragma unroll 1
-    for (int j = k + 1; j < NS; ++j) {
-      double w[5];
+    for (int i = 1; i < NS; ++i) if (i > k && (i & 1) == l) ck[PM::off(i)] = vv[i];
+    if (l == (k & 1)) M(k, k) = beta;
+    // columns of this lane: t = v.w + w_k,  w_k -= tau t,  w_i -= tau v_i t;  then the norm down-date
+    if (tau != 0.0) {
+      double tvv[NS];
 #pragma unroll
-      for (int q = 0; q < 5; ++q) w[q] = A(q, j);
-      double p = 0.0;
+      for (int i = 1; i < NS; ++i) tvv[i] = tau * vv[i];
+      for (int j = k + 1 + l; j < NS + 2; j += 2) {
+        if (j >= NS && nonzero != NS) continue;   // solve() applies the first `nonzero` reflectors to the right-hand sides
+        double* const cj = M.col(j);
+        double w[NS];
 #pragma unroll
-      for (int q = 0; q < 5; ++q) p += act[q] ? v[q] * w[q] : 0.0;
-      const double w0 = __shfl_sync(VP_FULL, w[ks], owner);
-      double t = p + L.other(p);
-      t += w0;
-      const double wk = apply ? w0 - tau * t : w0;
-      double s2 = 0.0;
+        for (int i = 1; i < NS; ++i) w[i] = cj[PM::off(i)];
+        double t = 0.0;
 #pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        if (act[q]) { if (apply) w[q] = w[q] - tau * v[q] * t; A(q, j) = w[q]; s2 += w[q] * w[q]; }
-        if (own[q]) A(q, j) = wk;
+        for (int i = 1; i < NS; ++i) t += vv[i] * w[i];
+        const double wk = cj[PM::off(k)];
+        t += wk;
+        cj[PM::off(k)] = wk - tau * t;
+#pragma unroll
+        for (int i = 1; i < NS; ++i) if (i > k) cj[PM::off(i)] = w[i] - tvv[i] * t;
       }
-      const double nu = nU(j);
-      bool recompute = false;
-      double scaled = nu;
+    }
+    for (int j = k + 1 + l; j < NS; j += 2) {
+      const double nu = nU[PM::off(j)];
       if (nu != 0.0) {
-        double temp = fabs(wk) / nu;
+        const double* cj = M.col(j);
+        const double ndj = nD[PM::off(j)];
+        const double akj = fabs(cj[PM::off(k)]);
+        bool bad = false;
+        double temp = fdiv(akj, nu, bad);
+        double qq = fdiv(nu, ndj, bad);
+        if (bad) { temp = akj / nu; qq = nu / ndj; }
         temp = (1.0 + temp) * (1.0 - temp);
         temp = temp < 0.0 ? 0.0 : temp;
-        const double qq = nu / nD(j);
         const double temp2 = temp * (qq * qq);
-        if (temp2 <= downdate) recompute = true; else scaled = nu * sqrt(temp);
-      }
-      if (__any_sync(VP_FULL, recompute)) {
-        s2 = s2 + L.other(s2);
-        if (recompute) { scaled = sqrt(s2); nD(j) = scaled; }
-      }
-      nU(j) = scaled;
-    }
-    // the two right-hand sides, while the factorisation has full rank so far (solve() applies the first `nonzero` reflectors)
-    const bool applyR = apply && nonzero == NS;
+        if (temp2 <= downdate) {
+          double s2 = 0.0;
 #pragma unroll
-    for (int dd = 0; dd < 2; ++dd) {
-      double p = 0.0;
-#pragma unroll
-      for (int q = 0; q < 5; ++q) p += act[q] ? v[q] * c[dd][q] : 0.0;
-      const double w0 = __shfl_sync(VP_FULL, c[dd][ks], owner);
-      double t = p + L.other(p);
-      t += w0;
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        if (applyR && act[q]) c[dd][q] = c[dd][q] - tau * v[q] * t;
-        if (applyR && own[q]) c[dd][q] = w0 - tau * t;
+          for (int i = 1; i < NS; ++i) { const double a = i > k ? cj[PM::off(i)] : 0.0; s2 += a * a; }
+          const double n = sqrt(s2);
+          nD[PM::off(j)] = n; nU[PM::off(j)] = n;
+        } else {
+          bool bad2 = false;
+          double rt = fsqrt(temp, bad2);
+          if (bad2) rt = sqrt(temp);
+          nU[PM::off(j)] = nu * rt;
+        }
       }
     }
+    __syncwarp();
   }
-  // back substitution with R (upper triangle, column i holds R(0..i, i)), rows >= nonzero give zero
+  // back substitution with R (upper triangle): lane l owns right-hand side l (column 9 + l); entries >= nonzero are zero
+  {
+    double* const cr = M.col(NS + l);
+    for (int i = nonzero - 1; i >= 0; --i) {
+      const double* ci = M.col(i);
+      const double x = cr[PM::off(i)] / ci[PM::off(i)];
+      cr[PM::off(i)] = x;
 #pragma unroll
-  for (int i = NS - 1; i >= 0; --i) {
-    const int is = i < 8 ? (i >> 1) : 4;
-    const int owner = (lane & ~1) | (i < 8 ? (i & 1) : 1);
-    const bool mine = qrow[is] == i;
-    const bool on = i < nonzero;
-    double col[5];
-#pragma unroll
-    for (int q = 0; q < 5; ++q) col[q] = A(q, i);
-#pragma unroll
-    for (int dd = 0; dd < 2; ++dd) {
-      const double num = mine ? c[dd][is] : 1.0, den = mine ? col[is] : 1.0;
-      const double ci = __shfl_sync(VP_FULL, num / den, owner);
-#pragma unroll
-      for (int q = 0; q < 5; ++q) {
-        if (on && qrow[q] < i) c[dd][q] = c[dd][q] - ci * col[q];
-        if (qrow[q] == i) c[dd][q] = on ? ci : 0.0;
-      }
+      for (int r = 0; r < NS - 1; ++r) if (r < i) cr[PM::off(r)] = cr[PM::off(r)] - x * ci[PM::off(r)];
     }
-  }
-  // undo the column permutation: entry i of the triangular solution belongs to original row perm[i].  The matrix words are
-  // dead; each lane drops its entries into the words of the lane that owns the target row (word dd*5 + slot).
-  __syncwarp();
-  double* const smPair = sm - l;
-#pragma unroll
-  for (int q = 0; q < 5; ++q) {
-    if (qrow[q] < NS) {
-      const int tr = (int)((perm >> (4 * qrow[q])) & 15ULL);
-      const int tl = tr < 8 ? (tr & 1) : 1, tq = tr < 8 ? (tr >> 1) : 4;
-      smPair[tl + (0 * 5 + tq) * VP_BS] = c[0][q];
-      smPair[tl + (1 * 5 + tq) * VP_BS] = c[1][q];
+    // undo the column permutation into the (dead) norm slots: X(dd = l, perm[i]) = c[i]
+    double* const xo = M.col(NS + 2 + l);
+    __syncwarp();
+    for (int i = 0; i < NS; ++i) {
+      const int tr = (int)((perm >> (4 * i)) & 15ULL);
+      xo[PM::off(tr)] = i < nonzero ? cr[PM::off(i)] : 0.0;
     }
+    __syncwarp();
   }
-  __syncwarp();
 #pragma unroll
-  for (int q = 0; q < 5; ++q) { c[0][q] = sm[(0 * 5 + q) * VP_BS]; c[1][q] = sm[(1 * 5 + q) * VP_BS]; }
+  for (int dd = 0; dd < 2; ++dd) {
+    const double* xo = M.col(NS + 2 + dd);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) mg[dd][q] = xo[PM::off(2 * q + l)];
+    mg[dd][4] = xo[PM::off(8)];
+  }
 }
 
 template <int NS, bool RANS>
@@ -596,34 +605,50 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
     for (int k = 0; k < 4; ++k) { Yr[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]); Xr[k] = L.sel(Xs[2 * k], Xs[2 * k + 1]); }
     Yr[4] = Ys[8]; Xr[4] = Xs[8];
+    double* const smPair = sm - l;
+    const PairMat<NS> Mt{smPair};
+    __syncwarp();   // the pair's words are about to be shared: both lanes are done with the solve's private words
+    Recip rM[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) rM[c] = frecip(cc.M[c]);
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
       const int r = k < 4 ? 2 * k + l : 8;
-      const bool zero = k == 4 && l == 0;   // the even lane has four rows; its fifth slot is a zero row of the QR
       const double a = cc.Mtot / cc.M[r] * (Yr[0] - Xr[0] + sig);
       const double yom = Yr[0] / cc.M[r];
+      double xom[NS];
+      bool bad = false;
 #pragma unroll
-      for (int c = 0; c < NS; ++c) {
-        const double b = cc.Mtot * (yom - Xr[0] / cc.M[c]);
-        const double val = (c == r) ? a * 1.0 + b * 0.0 : a * 0.0 + b * 1.0;
-        smA(k, c) = zero ? 0.0 : val;
+      for (int c = 0; c < NS; ++c) xom[c] = fdiv(Xr[0], rM[c], bad);
+      if (bad) {
+#pragma unroll
+        for (int c = 0; c < NS; ++c) xom[c] = Xr[0] / cc.M[c];
+      }
+      if (k < 4 || l == 1) {   // row 8 is written by the odd lane
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {
+          const double b = cc.Mtot * (yom - xom[c]);
+          Mt(r, c) = (c == r) ? a * 1.0 + b * 0.0 : a * 0.0 + b * 1.0;
+        }
       }
 #pragma unroll
       for (int m = 0; m < 4; ++m) { Yr[m] = Yr[m + 1]; Xr[m] = Xr[m + 1]; }
     }
     double MG[2][5];
+    bool need = false;   // entries below the threshold are zeroed after the solve; if all are, the solve is moot
 #pragma unroll
     for (int dd = 0; dd < 2; ++dd) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) MG[dd][k] = G[2 + k][dd];
-      MG[dd][4] = l ? G[1][dd] : 0.0;
+      for (int k = 0; k < 4; ++k) { Mt(2 * k + l, NS + dd) = G[2 + k][dd]; MG[dd][k] = 0.0; need = need || !(fabs(G[2 + k][dd]) < 1e-8); }
+      MG[dd][4] = 0.0;
+      if (l) { Mt(8, NS + dd) = G[1][dd]; need = need || !(fabs(G[1][dd]) < 1e-8); }   // X_8 lives on the odd lane
     }
-    pair_colpiv_qr_solve<NS>(L, sm, MG);
+    if (__any_sync(VP_FULL, need)) pair_colpiv_qr_solve<NS>(L, smPair, MG);
 #pragma unroll
     for (int dd = 0; dd < 2; ++dd) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) if (fabs(G[2 + k][dd]) < 1e-8) MG[dd][k] = 0.0;
-      if (fabs(G[1][dd]) < 1e-8) MG[dd][4] = 0.0;
+      if (l == 0 || fabs(G[1][dd]) < 1e-8) MG[dd][4] = 0.0;
     }
     const double c1 = muT / (o.prandtlTurb * o.lewisTurb), c2 = muT / o.prandtlTurb;
     const double sigma_k = d.turb[5 * np + pi];   // sigma_k of the first node (:5345)
