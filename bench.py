@@ -112,13 +112,21 @@ def main():
     ap.add_argument("--nx", type=int, default=1415)
     ap.add_argument("--ny", type=int, default=1415)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans"],
+                    help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 0); K = max(a.steps, 1)
+    rans = a.workload == "rans"
     workload = "laminar reactive NS (9 species, 2 reactions), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + Arrhenius source, WLS gradients"
+    if rans:
+        workload = "reactive RANS (9 species, 2 reactions, SST fields as inputs), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + SST closure + Arrhenius/PaSR source, WLS gradients"
 
     if a.impl == "reference":
         if rank != 0:
+            return
+        if rans:
+            print(json.dumps({"impl": "reference", "unavailable": "the reference arm is prepared for the laminar bench workload (configs[1]) only"}))
             return
         r = run_reference(K, W)
         if r is None:
@@ -145,13 +153,13 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     chem = pk.load_mechanism()
-    opts = pk.default_opts(rans=False, cfl=0.1)
+    opts = pk.default_opts(rans=rans, cfl=0.1)
     nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
     if world > 1:
         mesh, plan = pk.channel_strip_mesh(nxg, a.ny, rank, world)
     else:
         mesh = pk.channel_mesh(a.nx, a.ny); plan = dict(send={}, recv={}, bbox=None)
-    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=False, glob_xy=plan.get("bbox"))
+    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=rans, glob_xy=plan.get("bbox"))
     solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
     ex = par.HaloExchanger(par.GpuHaloState(solver), plan, dev)
     nOwn, nE = solver.nPointDomain, solver.nEdge
@@ -236,7 +244,7 @@ def main():
     # here, on this device, by a DFMA loop (rx_fp64_peak).  The HBM view of the same kernel and the convective AUSM kernel
     # (HBM-bound: 24 + (128 + 104)/(E/P) bytes per edge) are carried next to it.
     fp64_peak = solver_fp64_peak
-    flops_per_edge = 1.5e4
+    flops_per_edge = 1.7e4 if rans else 1.5e4   # RANS: + the 9x9 pivoted Householder QR with two right-hand sides of the SST closure
     bytes_visc = 24.0 + (400.0 + 208.0) / (nE / float(nOwn))
     bytes_conv = 24.0 + (128.0 + 104.0) / (nE / float(nOwn))
     t_visc, t_conv = kt["edge_flux_visc"] * 1e-3, kt["edge_flux_conv"] * 1e-3
@@ -247,7 +255,7 @@ def main():
     try:   # dram__bytes_read+write of one launch from the committed ncu capture of this kernel at this workload size
         pr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
         if pr.get("edges") == nE:
-            traffic = pr.get("k_edge_visc_pair")
+            traffic = pr.get("k_edge_visc_pair_rans" if rans else "k_edge_visc_pair")
     except Exception:
         pass
     line = {
@@ -260,7 +268,7 @@ def main():
                 "h2d_bytes_per_step": int(solver.nPoint * solver.nVar * 8), "d2h_bytes_per_step": int(solver.nVar * 8)},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"kernel": "k_edge_visc_pair<9> (Stefan-Maxwell/BiCGSTAB viscous edge flux, two lanes per edge)",
+        "roofline": {"kernel": "k_edge_visc_pair<9,%s> (Stefan-Maxwell/BiCGSTAB viscous edge flux%s, two lanes per edge)" % ("true" if rans else "false", " + SST closure (pivoted QR)" if rans else ""),
                      "bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak if fp64_peak else None,
                      "traffic": traffic,
                      "peak_source": "DFMA loop measured in this run (rx_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
@@ -270,7 +278,7 @@ def main():
                                      "unit": "GB/s", "frac": ach_hbm_conv / hbm, "bytes_per_edge": bytes_conv, "peak_source": hbm_src}},
         "kernel_ms": kt,
     }
-    if world == 1 and not a.no_cpu_baseline:
+    if world == 1 and not a.no_cpu_baseline and not rans:
         try:
             r = run_reference(2, 1)
             if r:

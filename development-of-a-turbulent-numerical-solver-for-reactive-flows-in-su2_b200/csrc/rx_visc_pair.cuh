@@ -614,21 +614,25 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
       const int r = k < 4 ? 2 * k + l : 8;
-      const double a = cc.Mtot / cc.M[r] * (Yr[0] - Xr[0] + sig);
-      const double yom = Yr[0] / cc.M[r];
+      const double Mr = cc.M[r];
+      const Recip rMr = frecip(Mr);
       double xom[NS];
       bool bad = false;
+      double mom = fdiv(cc.Mtot, rMr, bad), yom = fdiv(Yr[0], rMr, bad);
 #pragma unroll
       for (int c = 0; c < NS; ++c) xom[c] = fdiv(Xr[0], rM[c], bad);
       if (bad) {
+        mom = cc.Mtot / Mr; yom = Yr[0] / Mr;
 #pragma unroll
         for (int c = 0; c < NS; ++c) xom[c] = Xr[0] / cc.M[c];
       }
+      const double a = mom * (Yr[0] - Xr[0] + sig);
       if (k < 4 || l == 1) {   // row 8 is written by the odd lane
+        // m_tilde(i,j) = a*(i==j) + b*(i!=j) (:872-873): a*1.0 + b*0.0 on the diagonal, a*0.0 + b*1.0 off it
 #pragma unroll
         for (int c = 0; c < NS; ++c) {
           const double b = cc.Mtot * (yom - xom[c]);
-          Mt(r, c) = (c == r) ? a * 1.0 + b * 0.0 : a * 0.0 + b * 1.0;
+          Mt(r, c) = (c == r) ? a + b * 0.0 : a * 0.0 + b;
         }
       }
 #pragma unroll
