@@ -428,13 +428,19 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
     for (int k = 0; k < 4; ++k) { Xrow[k] = L.sel(Xs[2 * k], Xs[2 * k + 1]); Yrow[k] = L.sel(Ys[2 * k], Ys[2 * k + 1]); }
     Xrow[4] = Xs[8]; Yrow[4] = Ys[8];
+    bool inOk = mid_range(rho);   // rho and the mole fractions enter every quotient of the assembly
+#pragma unroll
+    for (int s = 0; s < NS; ++s) inOk = inOk && num_range(Xs[s]);
     double ra[NS], rb[NS];   // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead
     auto fetchD = [&](int k) {
       const int r = k < 4 ? 2 * k + l : 8;
+      // upper-triangle index of (min, max): row r from its diagonal on is contiguous (base_r + c); above it, column r of
+      // row c (a compile-time offset per c, plus r)
+      const int base_r = r * NS - r * (r - 1) / 2 - r;
 #pragma unroll
       for (int c = 0; c < NS; ++c) {
-        const int a = r < c ? r : c, b = r < c ? c : r;
-        const size_t q = (size_t)(a * NS - a * (a - 1) / 2 + (b - a)) * np;
+        const int up = c * NS - c * (c - 1) / 2 - c + r;
+        const size_t q = (size_t)(c >= r ? base_r + c : up) * np;
         ra[c] = rdi[q]; rb[c] = rdj[q];
       }
     };
@@ -448,16 +454,18 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       for (int c = 0; c < NS; ++c) sD[c] = ra[c] + rb[c];
       if (k < 4) fetchD(k + 1);
       double tk = 0.0, dm[NS], gq[NS], tq[NS];
-      bool bad = false;
       const double sx = smm * Xr;
+      bool ok = inOk && num_range(sx);   // operand ranges of the 27 quotients (rx_fdiv.cuh: fdivu)
 #pragma unroll
-      for (int c = 0; c < NS; ++c) dm[c] = fdiv(2.0, sD[c], bad);   // D_rr takes part in the maximum only
+      for (int c = 0; c < NS; ++c) ok = ok && mid_range(sD[c]);
+#pragma unroll
+      for (int c = 0; c < NS; ++c) dm[c] = fdivu(2.0, frecip(sD[c]));   // D_rr takes part in the maximum only
 #pragma unroll
       for (int c = 0; c < NS; ++c) {
-        gq[c] = fdiv(sx, rho * cc.M[c] * dm[c], bad);
-        tq[c] = fdiv(Xs[c], dm[c], bad);
+        gq[c] = fdivu(sx, frecip(rho * cc.M[c] * dm[c]));
+        tq[c] = fdivu(Xs[c], frecip(dm[c]));
       }
-      if (bad) {
+      if (!ok) {
 #pragma unroll
         for (int c = 0; c < NS; ++c) {   // out-of-range values only
           dm[c] = 2.0 / sD[c];
