@@ -88,6 +88,12 @@ int fill_chem(rx_ctx* c, const rx_chem* ch) {
       cc.wPow[i][j] = std::pow(cc.M[j] / cc.M[i], 0.25);
       cc.wSq[i][j] = std::sqrt(8.0 * (1.0 + cc.M[i] / cc.M[j]));
     }
+  {   // reciprocals of the Wilke denominators exactly as the kernels would refine them
+    double* dv = dupload(c, std::vector<double>(&cc.wSq[0][0], &cc.wSq[0][0] + NS * NS));
+    if (!dv) return RX_ERR_CUDA;
+    k_fill_recip<<<1, NS * NS>>>(dv, NS * NS);
+    if (cudaMemcpy(&cc.rwSq[0][0], dv, sizeof(double) * NS * NS, cudaMemcpyDeviceToHost) != cudaSuccess) return RX_ERR_CUDA;
+  }
   for (int i = 0; i < NS; ++i) {
     const double mi = cc.M[i], dvi = std::cbrt(ch->diffVol[i]);
     for (int j = i; j < NS; ++j) {

@@ -45,6 +45,7 @@ struct ChemC {
   double M[NS], Ri[NS];
   double wPow[NS][NS];   // pow(M[j]/M[i], 0.25)
   double wSq[NS][NS];    // sqrt(8*(1 + M[i]/M[j]))
+  double rwSq[NS][NS];   // refined reciprocal of wSq as frecip() forms it (filled on the device at create, rx_fdiv.cuh)
   double Mij[NS][NS];    // sqrt(M_i M_j/(M_i+M_j))
   double dvs[NS][NS];    // cbrt(dv_i) + cbrt(dv_j)
   double Mtot;           // sum of molar masses (numerics_direct_reactive.cpp:665)

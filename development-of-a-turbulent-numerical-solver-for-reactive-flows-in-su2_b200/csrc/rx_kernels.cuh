@@ -50,6 +50,11 @@ __global__ void k_scatter_field(const double* __restrict__ aos, double* __restri
   if (p < n) soa[p] = aos[p * nvIn + col];
 }
 
+__global__ void k_fill_recip(double* v, int n) {   // v[i] <- the refined reciprocal frecip() forms for v[i]
+  const int i = threadIdx.x;
+  if (i < n) v[i] = frecip(v[i]).r;
+}
+
 // Wilke mixing rules as transport<> in rx_device.cuh (ComputeEta :634-656, ComputeLambda :671-696), with the 27 quotients and
 // 9 square roots of one species row issued as independent batches (rx_fdiv.cuh); same values bit for bit.
 template <int NS>
@@ -67,21 +72,25 @@ __device__ __forceinline__ void transport_dev(const ChemC<NS>& cc, double T, con
   Recip rmu[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) rmu[s] = frecip(mu[s]);
+  // operand ranges of the quotients below, tested once per point instead of once per quotient (rx_fdiv.cuh: fdivu)
+  bool inOk = true;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) inOk = inOk && mid_range(mu[s]) && num_range(yomC[s]) && num_range(1.065 * yomR[s]);
   muMix = 0.0; kMix = 0.0;
 #pragma unroll 1
   for (int i = 0; i < NS; ++i) {
     const double mui = muR[0], kai = kaR[0], yci = ycR[0], yri = yrR[0];
     double phiE = 0.0, phiL = 0.0, tj[NS], qe[NS], ql[NS];
-    bool bad = false;
+    bool bad = !inOk;
 #pragma unroll
-    for (int j = 0; j < NS; ++j) tj[j] = fdiv(mui, rmu[j], bad);
+    for (int j = 0; j < NS; ++j) tj[j] = fdivu(mui, rmu[j]);
 #pragma unroll
     for (int j = 0; j < NS; ++j) tj[j] = 1.0 + fsqrt(tj[j], bad) * cc.wPow[i][j];
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
-      const Recip rw = frecip(cc.wSq[i][j]);
-      qe[j] = fdiv(yomC[j], rw, bad);
-      ql[j] = fdiv(1.065 * yomR[j], rw, bad);
+      const Recip rw{cc.wSq[i][j], cc.rwSq[i][j]};
+      qe[j] = fdivu(yomC[j], rw);
+      ql[j] = fdivu(1.065 * yomR[j], rw);
     }
     if (bad) {   // out-of-range operands only
 #pragma unroll
@@ -125,22 +134,23 @@ __global__ void __launch_bounds__(128, RX_TR_MINB) k_transport(const __grid_cons
   const double T175 = 1.0e-3 * pow175(T);
   const double Patm = P * 1.0 / 101325.0;
   const Recip r1e4 = frecip(1.0 * 1.0 * 1.0e4);
+  const bool dOk = mid_range(T175) && mid_range(Patm);   // then every quotient below has mid-range operands (pair constants are O(1..100))
   constexpr int NQ = NS * (NS + 1) / 2, QB = 5;   // 45 pairs in batches of five
   static_assert(NQ % QB == 0, "pair batches");
   int s = 0, t = 0;
 #pragma unroll 1
   for (int q0 = 0; q0 < NQ; q0 += QB) {
     double den[QB], D[QB], rDv[QB];
-    bool bad = false;
+    const bool bad = !dOk;
 #pragma unroll
     for (int b = 0; b < QB; ++b) {
       den[b] = Patm * cc.Mij[s][t] * cc.dvs[s][t] * cc.dvs[s][t];
       if (++t == NS) { ++s; t = s; }
     }
 #pragma unroll
-    for (int b = 0; b < QB; ++b) D[b] = fdiv(fdiv(T175, den[b], bad), r1e4, bad);
+    for (int b = 0; b < QB; ++b) D[b] = fdivu(fdivu(T175, frecip(den[b])), r1e4);
 #pragma unroll
-    for (int b = 0; b < QB; ++b) rDv[b] = fdiv(1.0, D[b], bad);
+    for (int b = 0; b < QB; ++b) rDv[b] = fdivu(1.0, frecip(D[b]));
     if (bad) {
 #pragma unroll
       for (int b = 0; b < QB; ++b) rDv[b] = 1.0 / ((T175 / den[b]) / (1.0 * 1.0 * 1.0e4));
@@ -236,15 +246,21 @@ __device__ __forceinline__ bool ls_sums(const Dev& d, long long p, const double*
     const double weight = 0.0 + d0 * d0 + d1 * d1;
     if (weight > EPS) {
       if (FAST) {
+        // operand ranges instead of one test per quotient: offsets zero or in [2^-100, 2^101), differences zero or in
+        // [2^-500, 2^201)  =>  weight in [2^-200, 2^203), numerators zero or in [2^-600, 2^302): fdivu is exact rounding
         const Recip rw = frecip(weight);
-        r11 += fdiv(d0 * d0, rw, bad);
-        r12 += fdiv(d0 * d1, rw, bad);
-        r22 += fdiv(d1 * d1, rw, bad);
+        bool ok = (exp_in<-100, 100>(d0) || d0 == 0.0) && (exp_in<-100, 100>(d1) || d1 == 0.0);
+        r11 += fdivu(d0 * d0, rw);
+        r12 += fdivu(d0 * d1, rw);
+        r22 += fdivu(d1 * d1, rw);
 #pragma unroll
         for (int v = 0; v < NG; ++v) {
-          C[v * 2 + 0] += fdiv(d0 * (pj[v] - pi[v]), rw, bad);
-          C[v * 2 + 1] += fdiv(d1 * (pj[v] - pi[v]), rw, bad);
+          const double df = pj[v] - pi[v];
+          ok = ok && (exp_in<-500, 200>(df) || df == 0.0);
+          C[v * 2 + 0] += fdivu(d0 * df, rw);
+          C[v * 2 + 1] += fdivu(d1 * df, rw);
         }
+        bad = bad || !ok;
       } else {
         r11 += d0 * d0 / weight;
         r12 += d0 * d1 / weight;
