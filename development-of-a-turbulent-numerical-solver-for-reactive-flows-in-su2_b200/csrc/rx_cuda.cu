@@ -93,6 +93,10 @@ int fill_chem(rx_ctx* c, const rx_chem* ch) {
     if (!dv) return RX_ERR_CUDA;
     k_fill_recip<<<1, NS * NS>>>(dv, NS * NS);
     if (cudaMemcpy(&cc.rwSq[0][0], dv, sizeof(double) * NS * NS, cudaMemcpyDeviceToHost) != cudaSuccess) return RX_ERR_CUDA;
+    double* dm = dupload(c, std::vector<double>(&cc.M[0], &cc.M[0] + NS));
+    if (!dm) return RX_ERR_CUDA;
+    k_fill_recip<<<1, NS>>>(dm, NS);
+    if (cudaMemcpy(&cc.rM[0], dm, sizeof(double) * NS, cudaMemcpyDeviceToHost) != cudaSuccess) return RX_ERR_CUDA;
   }
   for (int i = 0; i < NS; ++i) {
     const double mi = cc.M[i], dvi = std::cbrt(ch->diffVol[i]);

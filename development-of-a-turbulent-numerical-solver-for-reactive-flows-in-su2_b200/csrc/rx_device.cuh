@@ -9,6 +9,9 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#ifdef __CUDACC__
+#include "rx_fdiv.cuh"
+#endif
 
 #if defined(__CUDACC__)
 #define RX_HD __host__ __device__ __forceinline__
@@ -43,6 +46,7 @@ struct ChemC {
   const double* x;     // [nKnots] temperature grid (device)
   const Knot* tab;     // [5][nKnots][NS] interleaved {y, y2} (device; ~0.8 MB, L2 resident)
   double M[NS], Ri[NS];
+  double rM[NS];         // refined reciprocal of M as frecip() forms it (filled on the device at create, rx_fdiv.cuh)
   double wPow[NS][NS];   // pow(M[j]/M[i], 0.25)
   double wSq[NS][NS];    // sqrt(8*(1 + M[i]/M[j]))
   double rwSq[NS][NS];   // refined reciprocal of wSq as frecip() forms it (filled on the device at create, rx_fdiv.cuh)
@@ -98,21 +102,45 @@ RX_HD double rgas(const ChemC<NS>& cc, const double* Y) {   // ComputeRgas :27-4
   for (int s = 0; s < NS; ++s) r = r + clipy<NS>(Y[s]) * cc.Ri[s];
   return r;
 }
+// a[s] <- a[s] / M[s] for every species.  The reference divides per-kmol table values and mass fractions by the molar mass
+// all over the path; on the device the quotients use the molar masses' reciprocals formed once at create (rx_fdiv.cuh:
+// fdivu is the correctly rounded quotient for numerators that are zero or in [2^-600, 2^201); anything else divides plainly).
+template <int NS>
+RX_HD void div_by_M(const ChemC<NS>& cc, double* a) {
+#ifdef __CUDA_ARCH__
+  bool ok = true;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) ok = ok && num_range(a[s]);
+  if (ok) {
+#pragma unroll
+    for (int s = 0; s < NS; ++s) a[s] = fdivu(a[s], Recip{cc.M[s], cc.rM[s]});
+    return;
+  }
+#endif
+#pragma unroll
+  for (int s = 0; s < NS; ++s) a[s] = a[s] / cc.M[s];
+}
 template <int NS>
 RX_HD double enthalpy(const ChemC<NS>& cc, double T, const double* Y, bool& ok) {   // ComputeEnthalpy :519-523
   SplPos sp = spl_pos(cc, T);
   ok = ok && sp.ok;
-  double h = 0.0;
+  double h = 0.0, hs[NS];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) h = h + clipy<NS>(Y[s]) * (spl_eval(cc, P_H, s, sp) / cc.M[s]);
+  for (int s = 0; s < NS; ++s) hs[s] = spl_eval(cc, P_H, s, sp);
+  div_by_M(cc, hs);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) h = h + clipy<NS>(Y[s]) * hs[s];
   return h;
 }
 template <int NS>
 RX_HD double frozen_gamma(const ChemC<NS>& cc, double T, const double* Y) {   // ComputeFrozenGamma :399-404, ComputeCP :612-619
   SplPos sp = spl_pos(cc, T);
-  double cp = 0.0;
+  double cp = 0.0, cps[NS];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) cp = cp + clipy<NS>(Y[s]) * (spl_eval(cc, P_CP, s, sp) / cc.M[s]);
+  for (int s = 0; s < NS; ++s) cps[s] = spl_eval(cc, P_CP, s, sp);
+  div_by_M(cc, cps);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) cp = cp + clipy<NS>(Y[s]) * cps[s];
   double R = rgas(cc, Y);
   double cv = cp - R;
   return cp / cv;
@@ -121,7 +149,8 @@ template <int NS>
 RX_HD void molar_from_mass(const ChemC<NS>& cc, const double* Y, double* X) {   // SetMolarFromMass :84-93
   double sy = 0.0, sx = 0.0;
 #pragma unroll
-  for (int s = 0; s < NS; ++s) X[s] = clipy<NS>(Y[s]) / cc.M[s];
+  for (int s = 0; s < NS; ++s) X[s] = clipy<NS>(Y[s]);
+  div_by_M(cc, X);
 #pragma unroll
   for (int s = 0; s < NS; ++s) sy = sy + clipy<NS>(Y[s]);
 #pragma unroll

@@ -452,7 +452,8 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
   for (int s = 0; s < NS; ++s) omega[s] = 0.0;
   if (Nr == 0) return;
 #pragma unroll
-  for (int s = 0; s < NS; ++s) { Ys[s] = clipy<NS>(Yin[s]); Cs[s] = 1.0e3 * rho * Ys[s] / cc.M[s]; }   // SetConcentration :701-705
+  for (int s = 0; s < NS; ++s) { Ys[s] = clipy<NS>(Yin[s]); Cs[s] = 1.0e3 * rho * Ys[s]; }   // SetConcentration :701-705
+  div_by_M(cc, Cs);
   double wir[NRMAX][NS], kp[NRMAX];
   for (int r = 0; r < Nr; ++r) {
     // ComputeRateConstants :835-867 (K_eq from Gibbs only decides kb when no backward data are available)

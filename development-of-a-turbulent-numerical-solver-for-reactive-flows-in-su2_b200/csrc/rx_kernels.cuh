@@ -6,7 +6,6 @@
 // and needs no atomics.
 #pragma once
 #include "rx_flux.cuh"
-#include "rx_fdiv.cuh"
 #ifndef RX_TR_MINB
 #define RX_TR_MINB 3
 #endif
@@ -65,10 +64,13 @@ __device__ __forceinline__ void transport_dev(const ChemC<NS>& cc, double T, con
   for (int s = 0; s < NS; ++s) {
     mu[s] = spl_eval(cc, P_MU, s, sp);
     kaR[s] = spl_eval(cc, P_KAPPA, s, sp);
-    yomC[s] = clipy<NS>(Y[s]) / cc.M[s];
-    yomR[s] = Y[s] / cc.M[s];
-    muR[s] = mu[s]; ycR[s] = yomC[s]; yrR[s] = yomR[s];
+    yomC[s] = clipy<NS>(Y[s]);
+    yomR[s] = Y[s];
   }
+  div_by_M(cc, yomC);
+  div_by_M(cc, yomR);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { muR[s] = mu[s]; ycR[s] = yomC[s]; yrR[s] = yomR[s]; }
   Recip rmu[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) rmu[s] = frecip(mu[s]);

@@ -39,6 +39,21 @@ struct PairLane {
   __device__ __forceinline__ double sel(double even, double oddv) const { return l ? oddv : even; }
 };
 
+// a[k] <- a[k] / M[row[k]] for the five slots of a lane (see div_by_M in rx_device.cuh)
+template <int NS>
+__device__ __forceinline__ void div_by_M_rows(const ChemC<NS>& cc, const int* row, double* a) {
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) ok = ok && num_range(a[k]);
+  if (ok) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) a[k] = fdivu(a[k], Recip{cc.M[row[k]], cc.rM[row[k]]});
+  } else {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) a[k] = a[k] / cc.M[row[k]];
+  }
+}
+
 // sum of nine values spread over the pair (a[k] = value of the lane's slot k) in Eigen redux order
 __device__ __forceinline__ double pair_redux(const PairLane& L, const double* a) {
   const double s = (a[0] + a[2]) + (a[1] + a[3]);
@@ -414,11 +429,14 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   auto smA = [&](int k, int c) -> double& { return sm[(k * NS + c) * VP_BS]; };
   double invd[5];
   {
-    double sigma = 0.0, massTot = 0.0;
+    double sigma = 0.0, massTot = 0.0, yom9[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
 #pragma unroll
-    for (int s = 0; s < NS; ++s) massTot += Ys[s] / cc.M[s];
+    for (int s = 0; s < NS; ++s) yom9[s] = Ys[s];
+    div_by_M(cc, yom9);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) massTot += yom9[s];
     massTot = 1.0 / massTot;
     const double smm = -sigma * massTot;
     const double* rdi = d.rD + pi;
@@ -594,7 +612,10 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   const SplPos sp = spl_pos(cc, T);
   double hsr[5], hj[5];
 #pragma unroll
-  for (int k = 0; k < 5; ++k) { hsr[k] = spl_eval(cc, P_H, row[k], sp) / cc.M[row[k]]; hj[k] = -hsr[k] * x[k]; }
+  for (int k = 0; k < 5; ++k) hsr[k] = spl_eval(cc, P_H, row[k], sp);
+  div_by_M_rows(cc, row, hsr);
+#pragma unroll
+  for (int k = 0; k < 5; ++k) hj[k] = -hsr[k] * x[k];
   pair_gather(L, hj, f);
   double pE = 0.0;
 #pragma unroll
@@ -671,7 +692,8 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
     Yr[4] = Ys[8];
     double cps[5];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) cps[k] = spl_eval(cc, P_CP, row[k], sp) / cc.M[row[k]];
+    for (int k = 0; k < 5; ++k) cps[k] = spl_eval(cc, P_CP, row[k], sp);
+    div_by_M_rows(cc, row, cps);
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
       double t1[5], t2[5];
