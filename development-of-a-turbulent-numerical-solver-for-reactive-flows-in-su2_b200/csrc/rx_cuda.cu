@@ -34,6 +34,7 @@ struct rx_ctx {
   size_t stageBytes = 0;
   int updBlocks = 0;
   long long launches = 0;
+  bool splitSource = false;         // A/B hook (env RX_SPLIT_SOURCE=1): accumulation and source term as two kernels
   bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
 
@@ -168,6 +169,20 @@ static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   c->launches++;
 }
 
+// conv + visc accumulation and the source term: one fused kernel, or (splitSource) the sums at high occupancy followed by
+// the Arrhenius/PaSR kernel — the same additions in the same order either way
+static void launch_accumulate_visc(rx_ctx* c, cudaStream_t s) {
+  const Dev& d = c->d;
+  if (c->splitSource) {
+    k_accumulate<9, 7><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    c->launches += 2;
+  } else {
+    k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    c->launches++;
+  }
+}
+
 extern "C" {
 
 int rx_supported_species(int Ns) { return Ns == 9; }
@@ -188,6 +203,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   rx_ctx* c = new rx_ctx();
   c->device = op->device;
   { const char* ev = getenv("RX_RANS_THREAD_PER_EDGE"); c->ransThreadPerEdge = ev && ev[0] == '1'; }
+  { const char* ev = getenv("RX_SPLIT_SOURCE"); c->splitSource = ev && ev[0] == '1'; }
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
   {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
     const int smv = (int)SM_VISC;
@@ -473,8 +489,7 @@ int rx_residual_all(rx_ctx* c) {
   cudaStream_t s = c->stream;
   if (c->o.viscous) {
     launch_edge_flux<true, true>(c, s);
-    k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    c->launches++;
+    launch_accumulate_visc(c, s);
   } else {
     launch_edge_flux<true, false>(c, s);
     k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
@@ -502,7 +517,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
                 else launch_edge_flux<true, false>(c, s);
                 c->launches--; break;   // the helper counts its own launch
         case 1: launch_edge_flux<true, false>(c, s); c->launches--; break;
-        case 2: if (c->o.viscous) k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+        case 2: if (c->o.viscous) { launch_accumulate_visc(c, s); c->launches -= c->splitSource ? 2 : 1; }
                 else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
         case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;
         case 7: k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); break;
