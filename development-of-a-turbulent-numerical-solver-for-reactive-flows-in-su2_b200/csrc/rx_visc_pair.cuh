@@ -493,7 +493,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       }
 #pragma unroll
       for (int c = 0; c < NS; ++c) {
-        maxD = fmax(maxD, dm[c]);
+        maxD = dm[c] > maxD ? dm[c] : maxD;   // finite positive values: the maximum without fmax's NaN handling
         smA(k, c) = gq[c];
         tk = (c != r) ? tk + tq[c] : tk;
       }
@@ -565,42 +565,42 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
         if (restarts++ == 0) it = 0;
       }
     }
+    // A pair that has converged keeps running with the warp; nothing of it is stored any more.  Instead of guarding its
+    // vectors (twenty selects and as many moves per iteration) its SCALARS are made benign — beta = alpha = omega = 0 —
+    // which freezes r, p = r, v = A M^-1 r at finite values.  Live pairs see exactly the arithmetic of before.
     double beta;
     {
       bool bad = false;
-      const double q1 = fdiv(rho_n, rho_old, bad), q2 = fdiv(alpha_b, w_b, bad);
-      beta = bad ? (rho_n / rho_old) * (alpha_b / w_b) : q1 * q2;
+      const double bn1 = live ? rho_n : 0.0, bd1 = live ? rho_old : 1.0, bn2 = live ? alpha_b : 0.0, bd2 = live ? w_b : 1.0;
+      const double q1 = fdiv(bn1, bd1, bad), q2 = fdiv(bn2, bd2, bad);
+      beta = bad ? (bn1 / bd1) * (bn2 / bd2) : q1 * q2;
     }
-    double pn[5], vn[5];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) { pn[k] = r[k] + beta * (p[k] - w_b * v[k]); w1[k] = invd[k] * pn[k]; }
+    for (int k = 0; k < 5; ++k) { p[k] = r[k] + beta * (p[k] - w_b * v[k]); w1[k] = invd[k] * p[k]; }
     pair_gather(L, w1, f);
-    pair_gemv(getA, f, vn);
+    pair_gemv(getA, f, v);
 #pragma unroll
     for (int k = 0; k < 5; ++k) w1[k] = s_r0(k);
-    const double alpha_n = rho_n / pair_dot(L, w1, vn);
+    const double r0v = pair_dot(L, w1, v);
+    const double alpha_n = (live ? rho_n : 0.0) / (live ? r0v : 1.0);
     double s[5], z[5];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) { s[k] = r[k] - alpha_n * vn[k]; z[k] = invd[k] * s[k]; }
+    for (int k = 0; k < 5; ++k) { s[k] = r[k] - alpha_n * v[k]; z[k] = invd[k] * s[k]; }
     pair_gather(L, z, f);
     pair_gemv(getA, f, tv);
     const double tt = pair_dot(L, tv, tv);
     const double ts = pair_dot(L, tv, s);
-    const double w_n = tt > 0.0 ? ts / tt : 0.0;
-    double rn[5];
+    const double w_n = (live && tt > 0.0) ? ts / tt : 0.0;
 #pragma unroll
-    for (int k = 0; k < 5; ++k) rn[k] = s[k] - w_n * tv[k];
-    const double rrn = pair_dot(L, rn, rn);
+    for (int k = 0; k < 5; ++k) r[k] = s[k] - w_n * tv[k];
+    const double rrn = pair_dot(L, r, r);
     if (live) {
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        s_x(k) = s_x(k) + (alpha_n * (invd[k] * pn[k]) + w_n * z[k]);
-        r[k] = rn[k]; p[k] = pn[k]; v[k] = vn[k];
-      }
-      rho_b = rho_n; alpha_b = alpha_n; w_b = w_n;
+      for (int k = 0; k < 5; ++k) s_x(k) = s_x(k) + (alpha_n * (invd[k] * p[k]) + w_n * z[k]);
       ++it;
       live = (rrn > tol2) && (it < 2 * NS);
     }
+    rho_b = rho_n; alpha_b = alpha_n; w_b = w_n;
   }
   double x[5];
 #pragma unroll
