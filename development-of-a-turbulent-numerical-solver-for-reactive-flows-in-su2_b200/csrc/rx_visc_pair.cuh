@@ -537,17 +537,20 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   for (int k = 0; k < 5; ++k) { s_rhs(k) = rhs[k]; s_x(k) = 0.0; r[k] = rhs[k] - 0.0; s_r0(k) = r[k]; v[k] = 0.0; p[k] = 0.0; }
   double r0_sqnorm = pair_dot(L, r, r);
   const double rhs_sqnorm = r0_sqnorm;
-  double rho_b = 1, alpha_b = 1, w_b = 1;
+  double w_b = 1;
   const double tol2 = 1.0e-11 * 1.0e-11 * rhs_sqnorm;
   const double eps2 = 2.220446049250313e-16 * 2.220446049250313e-16;
   int it = 0, restarts = 0;
   bool live = (rhs_sqnorm != 0) && (r0_sqnorm > tol2);   // first loop test: r == r0
+  // Software-pipelined scalars: rho = r0.r of the coming iteration is formed next to |r|^2 at the end of the previous one, and
+  // the factors of beta = (rho/rho_old)(alpha/omega) that do not need the new rho — 1/rho_old and alpha/omega — as soon as
+  // their operands exist.  Same operations on the same values; two reductions and a division leave the critical path.
+  double rho_n = pair_dot(L, r, r);   // r0 == r
+  double rhoOldS = 1.0, abS = 1.0, wbS = 1.0, q2 = 1.0;   // sanitised copies (a converged pair: 1, 0, 1) for the fallback
+  Recip Rold = frecip(1.0);
+  bool badq2 = false;
 #pragma unroll 1
   while (__any_sync(VP_FULL, live)) {
-    const double rho_old = rho_b;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) w1[k] = s_r0(k);
-    double rho_n = pair_dot(L, w1, r);
     const bool restart = live && (fabs(rho_n) < eps2 * r0_sqnorm);
     if (__any_sync(VP_FULL, restart)) {   // r = rhs - A x, r0 = r (rare)
 #pragma unroll
@@ -570,10 +573,10 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
     // which freezes r, p = r, v = A M^-1 r at finite values.  Live pairs see exactly the arithmetic of before.
     double beta;
     {
-      bool bad = false;
-      const double bn1 = live ? rho_n : 0.0, bd1 = live ? rho_old : 1.0, bn2 = live ? alpha_b : 0.0, bd2 = live ? w_b : 1.0;
-      const double q1 = fdiv(bn1, bd1, bad), q2 = fdiv(bn2, bd2, bad);
-      beta = bad ? (bn1 / bd1) * (bn2 / bd2) : q1 * q2;
+      bool bad = badq2;
+      const double bn1 = live ? rho_n : 0.0;
+      const double q1 = fdiv(bn1, Rold, bad);
+      beta = bad ? (bn1 / rhoOldS) * (abS / wbS) : q1 * q2;
     }
 #pragma unroll
     for (int k = 0; k < 5; ++k) { p[k] = r[k] + beta * (p[k] - w_b * v[k]); w1[k] = invd[k] * p[k]; }
@@ -594,13 +597,21 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
     for (int k = 0; k < 5; ++k) r[k] = s[k] - w_n * tv[k];
     const double rrn = pair_dot(L, r, r);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) w1[k] = s_r0(k);
+    const double rho_next = pair_dot(L, w1, r);
     if (live) {
 #pragma unroll
       for (int k = 0; k < 5; ++k) s_x(k) = s_x(k) + (alpha_n * (invd[k] * p[k]) + w_n * z[k]);
       ++it;
       live = (rrn > tol2) && (it < 2 * NS);
     }
-    rho_b = rho_n; alpha_b = alpha_n; w_b = w_n;
+    rhoOldS = live ? rho_n : 1.0; abS = live ? alpha_n : 0.0; wbS = live ? w_n : 1.0;
+    Rold = frecip(rhoOldS);
+    badq2 = false;
+    q2 = fdiv(abS, wbS, badq2);
+    w_b = w_n;
+    rho_n = rho_next;
   }
   double x[5];
 #pragma unroll
