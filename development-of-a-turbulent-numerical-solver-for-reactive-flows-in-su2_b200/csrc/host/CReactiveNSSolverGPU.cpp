@@ -29,7 +29,8 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   ransMode = (kind == REACTIVE_RANS);
   viscousMode = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
   if (implicit) throw std::runtime_error("CReactiveNSSolverGPU: EULER_IMPLICIT is not on the CUDA path (explicit Euler / RK only)");
-  if (limiter && config->GetKind_SlopeLimit_Flow() != VENKATAKRISHNAN) throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN limiter is on the CUDA path");
+  if (limiter && config->GetKind_SlopeLimit_Flow() != VENKATAKRISHNAN && config->GetKind_SlopeLimit_Flow() != BARTH_JESPERSEN)
+    throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN and BARTH_JESPERSEN limiters are on the CUDA path");
   if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
 
@@ -125,7 +126,7 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   o.fuelIndex = config->GetFuelIndex(); o.oxidizerIndex = config->GetOxidizerIndex();
   o.prandtlLam = config->GetPrandtl_Lam(); o.prandtlTurb = config->GetPrandtl_Turb(); o.lewisTurb = config->GetLewis_Turb();
   o.cMu = config->Get_Cmu(); o.pasrLb = config->Get_PaSR_LB(); o.tkeInf = ransMode ? GetTke_Inf() : 0.0;
-  o.secondOrder = second_order ? 1 : 0; o.limiter = limiter ? 1 : 0;
+  o.secondOrder = second_order ? 1 : 0; o.limiter = limiter ? (config->GetKind_SlopeLimit_Flow() == BARTH_JESPERSEN ? 2 : 1) : 0;
   o.limCoeff = config->GetLimiterCoeff(); o.refElemLength = config->GetRefElemLength();
   o.device = env_int("SU2_RX_DEVICE", 0);
 

@@ -381,7 +381,11 @@ int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) 
       c->launches++;
     }
   }
-  if (c->o.secondOrder && c->o.limiter && !output) { k_limiter<<<nblk(d.nPoint, 128), 128, 0, s>>>(c->o, d); c->launches++; }   // :4739-4742
+  if (c->o.secondOrder && c->o.limiter && !output) {   // :4739-4742
+    if (c->o.limiter == 2) k_limiter_bj<<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+    else k_limiter<<<nblk(d.nPoint, 128), 128, 0, s>>>(c->o, d);
+    c->launches++;
+  }
   RX_CK(cudaGetLastError());
   if (nonPhysical) {
     unsigned long long h = 0;

@@ -99,6 +99,52 @@ __global__ void __launch_bounds__(128) k_limiter(const __grid_constant__ Opts o,
   for (int v = 0; v < 4; ++v) d.lim[v * d.np + p] = lim[v];
 }
 
+// ---- SetPrimitive_Limiter, BARTH_JESPERSEN branch (:1380-1439) as coded.  The node-0 side of an edge takes the minimum; the
+// node-1 side compares the solver's bool `limiter` (1.0) with the running value and ASSIGNS (:1425), so the value of a point
+// depends on the order in which its edges are met.  Owner-computes over the incident-edge list in ascending edge order —
+// the order of the reference's edge loop as one point sees it — gives the same sequence of updates, hence the same bits.
+__global__ void __launch_bounds__(128) k_limiter_bj(const Dev d) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  const int fld[4] = {V_T, V_VX, V_VX + 1, V_P};
+  double vp[4], smax[4], smin[4], lim[4], g[4][2];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    vp[v] = d.V[fld[v] * d.np + p]; smax[v] = -EPS; smin[v] = EPS; lim[v] = 2.0;
+    g[v][0] = d.grad[(2 * v) * d.np + p]; g[v][1] = d.grad[(2 * v + 1) * d.np + p];
+  }
+  const int k0 = d.incPtr[p], k1 = d.incPtr[p + 1];
+  for (int k = k0; k < k1; ++k) {
+    const int code = d.incEdge[k];
+    const int q = code >= 0 ? d.ej[code] : d.ei[~code];
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      const double other = d.V[fld[v] * d.np + q];
+      const double du = code >= 0 ? other - vp[v] : -(vp[v] - other);   // node 0 sees du, node 1 sees -du with du = V_j - V_i
+      smin[v] = fmin(smin[v], du); smax[v] = fmax(smax[v], du);
+    }
+  }
+  const double xp = d.x[p], yp = d.y[p];
+  for (int k = k0; k < k1; ++k) {
+    const int code = d.incEdge[k];
+    const bool first = code >= 0;
+    const int q = first ? d.ej[code] : d.ei[~code];
+    const double hx = 0.5 * (d.x[q] - xp), hy = 0.5 * (d.y[q] - yp);
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      double dm = 0.0;
+      dm += hx * g[v][0]; dm += hy * g[v][1];
+      double lv;
+      if (dm < EPS) lv = 2.0;
+      else lv = (dm > EPS ? smax[v] : smin[v]) / dm;
+      if (first) { if (lv < lim[v]) lim[v] = lv; }
+      else if (1.0 < lim[v]) lim[v] = lv;
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < 4; ++v) { const double y = lim[v]; d.lim[v * d.np + p] = (y * y + 2.0 * y) / (y * y + y + 2.0); }
+}
+
 // ---- 2nd-order Upwind_Residual (:2554-2681): MUSCL reconstruction of [T,u,v,P] at the edge mid point, rebuild of rho, h, a
 template <int NS>
 __device__ __forceinline__ void reconstruct_state(const ChemC<NS>& cc, const Opts& o, const Dev& d, long long p, double hx, double hy,

@@ -81,7 +81,7 @@ typedef struct {
   double mInfty, cfl, maxDt, Tmin, Tmax;
   int clipT, ignition; int64_t ignitionIter; double ignitionT; int fuelIndex, oxidizerIndex;
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
-  int secondOrder, limiter;   /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER] (MUSCL on T,u,v,P :2554-2681); limiter: 1 = VENKATAKRISHNAN (:1328-1523) */
+  int secondOrder, limiter;   /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER] (MUSCL on T,u,v,P :2554-2681); limiter: 1 = VENKATAKRISHNAN (:1443-1523), 2 = BARTH_JESPERSEN as coded (:1380-1439) */
   double limCoeff, refElemLength;   /* LIMITER_COEFF, REF_ELEM_LENGTH */
   int device;               /* CUDA device ordinal */
 } rx_opts;

@@ -136,6 +136,11 @@ SPECS = {
                           dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
                                SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="VENKATAKRISHNAN", CFL_NUMBER="0.2"),
                           2, 1, 23, False),
+    # same, BARTH_JESPERSEN branch of SetPrimitive_Limiter (as coded, order dependent)
+    "channel_lam_bj": (dict(nx=41, ny=21, stretch=1.5),
+                       dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                            SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="BARTH_JESPERSEN", CFL_NUMBER="0.2"),
+                       2, 1, 29, False),
 }
 
 

@@ -112,7 +112,8 @@ def opts_dict(case):
                 ignition=cf["ignition"], ignitionIter=cf["ignition_iter"], ignitionT=cf["ignition_T"],
                 fuelIndex=cf["fuel_index"], oxidizerIndex=cf["oxidizer_index"], prandtlLam=cf["prandtl_lam"],
                 prandtlTurb=cf["prandtl_turb"], lewisTurb=cf["lewis_turb"], cMu=cf["c_mu"], pasrLb=cf["pasr_lb"],
-                tkeInf=cf["tke_inf"], secondOrder=cf.get("second_order", 0), limiter=cf.get("limiter", 0),
+                tkeInf=cf["tke_inf"], secondOrder=cf.get("second_order", 0),
+                limiter=(2 if cf.get("limiter_kind", 0) == 1 else 1) if cf.get("limiter", 0) else 0,   # 1 VENKATAKRISHNAN, 2 BARTH_JESPERSEN
                 limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1))
 
 

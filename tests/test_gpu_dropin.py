@@ -17,7 +17,7 @@ HARNESS_CPU = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 # name -> (iterations, seed)   (oracle/make_golden.py SPECS)
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
-        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23)}
+        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29)}
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-11   # later iterations start from states that already differ by rounding (gradients amplify by 1/dx)
 # jet_rans_perturbed reaches 1.04e-12 in the mass group at iteration 0.  Traced: glibc's pow() is
