@@ -278,10 +278,15 @@ void CReactiveNSSolverGPU::BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*,
 void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha) {
   std::vector<double> rms(nVar);
   Check(rx_update_explicit(ctx, alpha, rms.data()), "rx_update_explicit");
+  std::vector<double> rmax(nVar);
+  std::vector<int64_t> pmax(nVar);
+  Check(rx_get_residual_max(ctx, rmax.data(), pmax.data()), "rx_get_residual_max");
   for (unsigned short v = 0; v < nVar; ++v) {
     if (rms[v] != rms[v]) throw std::runtime_error("SU2 has diverged (NaN detected in the residual norms)");
     SetRes_RMS(v, rms[v]);
-    SetRes_Max(v, 0.0, 0);
+    SetRes_Max(v, 0.0, 0);   // then what the reference's point loop leaves behind (AddRes_Max :2436)
+    if (rmax[v] > 0.0)
+      AddRes_Max(v, rmax[v], geometry->node[pmax[v]]->GetGlobalIndex(), geometry->node[pmax[v]]->GetCoord());
   }
   Check(rx_get_solution(ctx, bufU.data()), "rx_get_solution");
   for (unsigned long p = 0; p < nPoint; ++p)

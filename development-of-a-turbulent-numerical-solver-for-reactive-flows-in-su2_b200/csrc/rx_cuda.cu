@@ -30,7 +30,9 @@ struct rx_ctx {
   ChemC<9> cc9{};
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
-  double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr;
+  double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr, *pmax = nullptr, *resMax = nullptr;
+  int *pidx = nullptr, *resMaxPoint = nullptr;
+  bool haveResMax = false;
   size_t stageBytes = 0;
   int updBlocks = 0;
   long long launches = 0;
@@ -267,6 +269,8 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   c->updBlocks = (int)nblk(d.nPointDomain, 128);
   c->partial = dalloc<double>(c, (size_t)c->updBlocks * c->nVar);
   c->rms = dalloc<double>(c, c->nVar); c->sumsq = dalloc<double>(c, c->nVar);
+  c->pmax = dalloc<double>(c, (size_t)c->updBlocks * c->nVar); c->pidx = dalloc<int>(c, (size_t)c->updBlocks * c->nVar);
+  c->resMax = dalloc<double>(c, c->nVar); c->resMaxPoint = dalloc<int>(c, c->nVar);
   if (!d.counters || !c->sumsq || !d.fluxC || !d.grad || (o.viscous && !d.fluxV)) {
     g_create_error = "rx_create: device allocation failed"; rx_destroy(c); return RX_ERR_CUDA;
   }
@@ -477,7 +481,14 @@ int rx_get_bc_state(rx_ctx* c, int marker, double* V) {
 int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
-  k_update<9><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial);
+  if (resRms) {   // norms wanted on the host: the location of the largest residual comes with them (rx_get_residual_max)
+    k_update<9, true><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, c->pmax, c->pidx);
+    k_resmax_finish<<<c->nVar, 256, 0, s>>>(c->pmax, c->pidx, c->updBlocks, c->nVar, c->resMax, c->resMaxPoint);
+    c->launches++;
+    c->haveResMax = true;
+  } else {
+    k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, nullptr, nullptr);
+  }
   k_rms_finish<<<c->nVar, 256, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
   c->launches += 2;
   RX_CK(cudaGetLastError());
@@ -485,6 +496,16 @@ int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
     RX_CK(cudaMemcpyAsync(resRms, c->rms, c->nVar * sizeof(double), cudaMemcpyDeviceToHost, s));
     RX_CK(cudaStreamSynchronize(s));
   }
+  return RX_OK;
+}
+
+int rx_get_residual_max(rx_ctx* c, double* resMax, int64_t* point) {
+  if (!c->haveResMax) { c->err = "rx_get_residual_max: no update with residual norms has run yet"; return RX_ERR_ARG; }
+  std::vector<double> m(c->nVar); std::vector<int> ip(c->nVar);
+  RX_CK(cudaMemcpyAsync(m.data(), c->resMax, c->nVar * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaMemcpyAsync(ip.data(), c->resMaxPoint, c->nVar * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  for (int v = 0; v < c->nVar; ++v) { if (resMax) resMax[v] = m[v]; if (point) point[v] = ip[v]; }
   return RX_OK;
 }
 
@@ -528,7 +549,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
         case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
                 else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
         case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
-        case 6: k_update<9><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial); break;
+        case 6: k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial, nullptr, nullptr); break;
         default: cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: unknown kernel id"; return RX_ERR_ARG;
       }
       c->launches++;

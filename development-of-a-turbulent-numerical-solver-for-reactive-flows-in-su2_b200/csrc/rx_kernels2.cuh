@@ -443,14 +443,18 @@ __global__ void __launch_bounds__(64) k_bc_euler_wall(const __grid_constant__ Op
 }
 
 // ---- ExplicitEuler/RK_Iteration (:2414-2493): update + per-block partial sums of Res^2 (deterministic two-stage reduction)
-template <int NS>
-__global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, double* __restrict__ partial) {
+// MAXR: also the largest |Res| of every variable and the point that holds it (CSolver::AddRes_Max, solver_structure.inl: the
+// FIRST point in point order that attains the maximum) as per-block partials for k_resmax_finish.
+template <int NS, bool MAXR>
+__global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, double* __restrict__ partial, double* __restrict__ pmax, int* __restrict__ pidx) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   constexpr int NV = 4 + NS;
   __shared__ double sh[4][NV];
-  double sq[NV];
+  __shared__ double shm[MAXR ? 4 : 1][NV];
+  __shared__ int shi[MAXR ? 4 : 1][NV];
+  double sq[NV], ab[NV];
 #pragma unroll
-  for (int v = 0; v < NV; ++v) sq[v] = 0.0;
+  for (int v = 0; v < NV; ++v) { sq[v] = 0.0; ab[v] = 0.0; }
   if (p < d.nPointDomain) {
     const double Vol = d.vol[p];
     const double Delta = Vol > EPS ? d.dt[p] / Vol : 0.0;
@@ -460,6 +464,21 @@ __global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, doubl
       const double lo = (v == U_MX || v == U_MX + 1 || v == U_E) ? -1.0 / EPS : 0.0, hi = 1.0 / EPS;
       d.U[v * d.np + p] = fmin(fmax(d.Uold[v * d.np + p] + (-Res * Delta * alpha), lo), hi);
       sq[v] = Res * Res;
+      ab[v] = fabs(Res);
+    }
+  }
+  if (MAXR) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      double m = ab[v];
+      int ip = (int)(p < d.nPointDomain ? p : 0x7fffffff);
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {   // a higher lane is a later point: it wins only if strictly larger
+        const double mo = __shfl_down_sync(0xffffffffu, m, off);
+        const int io = __shfl_down_sync(0xffffffffu, ip, off);
+        if (mo > m) { m = mo; ip = io; }
+      }
+      if ((threadIdx.x & 31) == 0) { shm[threadIdx.x >> 5][v] = m; shi[threadIdx.x >> 5][v] = ip; }
     }
   }
 #pragma unroll
@@ -473,7 +492,35 @@ __global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, doubl
   if (threadIdx.x < NV) {
     const int v = threadIdx.x;
     partial[(size_t)blockIdx.x * NV + v] = ((sh[0][v] + sh[1][v]) + (sh[2][v] + sh[3][v]));
+    if (MAXR) {
+      double m = shm[0][v]; int ip = shi[0][v];
+#pragma unroll
+      for (int w = 1; w < 4; ++w) if (shm[w][v] > m) { m = shm[w][v]; ip = shi[w][v]; }
+      pmax[(size_t)blockIdx.x * NV + v] = m; pidx[(size_t)blockIdx.x * NV + v] = ip;
+    }
   }
+}
+// largest residual per variable over the block partials: larger value wins, equal values go to the lower point index
+__global__ void __launch_bounds__(256) k_resmax_finish(const double* __restrict__ pmax, const int* __restrict__ pidx, int nBlocks, int nv,
+                                                       double* __restrict__ resMax, int* __restrict__ resMaxPoint) {
+  const int v = blockIdx.x;
+  __shared__ double sm[256];
+  __shared__ int si[256];
+  double m = 0.0; int ip = 0;   // SetRes_Max(iVar, 0.0, 0) before the loop (:2427)
+  for (int b = threadIdx.x; b < nBlocks; b += 256) {
+    const double mo = pmax[(size_t)b * nv + v]; const int io = pidx[(size_t)b * nv + v];
+    if (mo > m || (mo == m && mo > 0.0 && io < ip)) { m = mo; ip = io; }
+  }
+  sm[threadIdx.x] = m; si[threadIdx.x] = ip;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) {
+      const double mo = sm[threadIdx.x + w]; const int io = si[threadIdx.x + w];
+      if (mo > sm[threadIdx.x] || (mo == sm[threadIdx.x] && mo > 0.0 && io < si[threadIdx.x])) { sm[threadIdx.x] = mo; si[threadIdx.x] = io; }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { resMax[v] = sm[0]; resMaxPoint[v] = si[0]; }
 }
 __global__ void __launch_bounds__(256) k_rms_finish(const double* __restrict__ partial, int nBlocks, int nv, long long nPointGlobal, double* __restrict__ rms, double* __restrict__ sumsq) {
   // one block per variable; fixed strided partial sums + fixed tree => bit-reproducible run to run

@@ -75,7 +75,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
-           "rx_partition_kway", "rx_rcm_order"]
+           "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max"]
 
 _lib = None
 
@@ -216,6 +216,13 @@ class CReactiveNSSolverGPU:
         rms = np.empty(self.nVar)
         self._ck(self.lib.rx_update_explicit(self.ctx, C.c_double(alpha), _d(rms) if want_rms else None))
         return rms if want_rms else None
+
+    def GetRes_Max(self):
+        """(max |LinSysRes| per variable, local index of the first point attaining it) of the last update with norms —
+        CSolver::GetRes_Max / GetPoint_Max."""
+        m = np.empty(self.nVar); ip = np.empty(self.nVar, dtype=np.int64)
+        self._ck(self.lib.rx_get_residual_max(self.ctx, _d(m), _i(ip)))
+        return m, ip
 
     def ExplicitEuler_Iteration(self, want_rms=True):
         return self.ExplicitRK_Iteration(1.0, want_rms)

@@ -115,6 +115,7 @@ int rx_bc_marker(rx_ctx*, int marker);                    /* one BC_* call of th
 int rx_get_bc_state(rx_ctx*, int marker, double* V /* [nVertex][nPrim] */);   /* state imposed by the last inlet/outlet BC of the marker = CharacPrimVar (:3274, :3844), read by the turbulence BCs */
 int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */
 
+int rx_get_residual_max(rx_ctx*, double* resMax /* [nVar] */, int64_t* point /* [nVar], local point index */);   /* CSolver::AddRes_Max of the last update that returned norms: largest |LinSysRes| per variable and the first point attaining it (:2436) */
 int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + Source residual in one pass (same sums, same order) */
 
 /* one full MultiGrid_Cycle (integration_time.cpp:143-181) with everything resident: for each RK stage

@@ -65,3 +65,21 @@ def test_fused_iteration_matches_staged(name):
     assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1]) and np.array_equal(out[0][2], out[1][2])
     last = "it%04d_rk%d_U1" % (it, len(alphas) - 1)
     assert stage_rel_err(last, out[1][0], case[last], case.Ns).max() <= TOL
+
+
+def test_residual_max_and_location():
+    """CSolver::AddRes_Max (solver_direct_reactive.cpp:2436): largest |LinSysRes| per variable and the FIRST point attaining it,
+    reduced on the device with the residual norms."""
+    case = Case("%s/%s.npz" % (GOLDEN, "channel_lam_rk"))
+    s = gpu_solver(case)
+    it = 1
+    s.set_solution(case.stage(it, 0, "U0")); s.set_temperature(case.stage(it, 0, "prev_V")[:, 0]); s.set_turbulence(case.stage(it, 0, "turb"))
+    s.preprocess(it, False); s.set_old_solution(); s.time_step()
+    s.Residual_All(); s.BC_All()
+    R = np.abs(s.residual()[:s.nPointDomain])
+    rms = s.ExplicitRK_Iteration(0.66667)
+    m, ip = s.GetRes_Max()
+    np.testing.assert_array_equal(m, R.max(axis=0))
+    np.testing.assert_array_equal(ip, R.argmax(axis=0))            # argmax returns the first maximum, as AddRes_Max keeps it
+    np.testing.assert_allclose(rms, np.maximum(1e-32, np.sqrt((R ** 2).sum(axis=0) / s.nPoint)), rtol=1e-12)
+    s.close()
