@@ -103,6 +103,120 @@ def run_reference(steps, warmup, procs=None):
                        "iteration on a %d-point / %d-edge triangulated channel, %d timed iterations; aggregate updates/s" % (procs, nP, nE, steps))
 
 
+def bench_source(a, pk, chem, rank, world, local, dev, K, W):
+    """configs[3]: the Arrhenius + PaSR source term alone over independent points (rx_source_points_dev; every rank its own
+    points, no exchange).  value: device-timed passes over HBM-resident SoA inputs; e2e: the host-buffer entry point
+    rx_source_points (allocation, H2D, kernel, D2H) on a bounded number of points."""
+    import torch
+    import torch.distributed as dist
+    n = int(a.points)
+    base = min(n, 4_000_000)                     # seeded states, tiled on the device up to n
+    T, rho, Y, omT, vol = pk.synthetic_points(chem, base, seed=12345 + rank)
+    reps = (n + base - 1) // base
+    t = lambda x: torch.as_tensor(np.ascontiguousarray(x), device=dev)
+    tile = lambda x: t(x).repeat(reps)[:n].contiguous()
+    dT, dr, dO, dV = tile(T), tile(rho), tile(omT), tile(vol)
+    dY = t(Y.T).repeat(1, reps)[:, :n].contiguous()
+    dR = torch.empty((chem["Ns"], n), dtype=torch.float64, device=dev)
+    opts = pk.default_opts(rans=True)
+    solver = pk.CReactiveNSSolverGPU(pk.channel_mesh(5, 4), chem, opts, device=local)
+
+    def step():
+        solver.SourcePointsDev(n, dT.data_ptr(), dr.data_ptr(), dY.data_ptr(), dO.data_ptr(), dV.data_ptr(), dR.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(W, 3)):
+        step()
+    l0 = solver.LaunchCount()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1) / K
+    clocks = sampler.stop()
+    launches = solver.LaunchCount() - l0
+    if not bool(torch.isfinite(dR).all()):
+        raise SystemExit("bench.py: non-finite source term")
+    ne = min(n, 8_000_000)
+    hT, hr, hY, hO, hV = T, rho, Y, omT, vol
+    if ne > base:
+        r2 = (ne + base - 1) // base
+        hT, hr, hO, hV = [np.tile(x, r2)[:ne] for x in (T, rho, omT, vol)]; hY = np.tile(Y, (r2, 1))[:ne]
+    else:
+        hT, hr, hO, hV, hY = T[:ne], rho[:ne], omT[:ne], vol[:ne], Y[:ne]
+    pk.source_points(chem, hT, hr, hY, hV, omegaTurb=hO, rans=True, device=local)
+    barrier()
+    t0 = time.perf_counter()
+    Ke = 3
+    for _ in range(Ke):
+        pk.source_points(chem, hT, hr, hY, hV, omegaTurb=hO, rans=True, device=local)
+    barrier()
+    ms_e2e = 1e3 * (time.perf_counter() - t0) / Ke
+    fp64_peak = solver.Fp64Peak()
+    tt = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_dev, ms_e2e = float(tt[0]), float(tt[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    flops_per_point = 3.5e3      # SURVEY.md 8(d): FP64-equivalent operations of Arrhenius + PaSR for 2 reactions, 9 species
+    bytes_per_point = 8.0 * (4 + 2 * chem["Ns"])
+    ach = flops_per_point * n / (ms_dev * 1e-3) / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    line = {"metric": "source-point updates/s", "value": world * n / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+            "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "isolated Arrhenius + PaSR source term (9 species, 2 reactions) over independent points, SoA inputs resident in HBM",
+                       "points_per_gpu": n, "cache": "inputs %.1f GB per GPU, larger than L2" % (n * bytes_per_point / 1e9)},
+            "e2e": {"value": world * ne / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e, "points_per_call": ne,
+                    "h2d_bytes_per_step": int(ne * 8 * (4 + chem["Ns"])), "d2h_bytes_per_step": int(ne * 8 * chem["Ns"])},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"kernel": "k_source_points<9>", "bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": ach / fp64_peak if fp64_peak else None, "traffic": None, "flops_per_point": flops_per_point,
+                         "peak_source": "DFMA loop measured in this run (rx_fp64_peak)",
+                         "hbm_view": {"achieved": bytes_per_point * n / (ms_dev * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                                      "frac": bytes_per_point * n / (ms_dev * 1e-3) / 1e9 / hbm, "bytes_per_point": bytes_per_point}}}
+    if world == 1 and not a.no_cpu_baseline:
+        try:   # the CPU restatement (oracle, one core) on a bounded sample of the same states
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import ctypes as C
+            import rxcase
+            lib = C.CDLL(rxcase.build_oracle()) if os.path.exists(os.path.join(ROOT, "oracle", "rx_oracle.cpp")) else None
+            ns = 200_000
+            keep = []
+            k = lambda x: (keep.append(np.ascontiguousarray(x, dtype=np.float64)), keep[-1])[1]
+            ch = rxcase._Chem(chem["Ns"], chem["Nr"], chem["nKnots"], *[rxcase._p(k(np.asarray(chem[q]).reshape(-1))) for q in
+                              ["mMasses", "diffVol", "x", "y", "y2", "As", "Betas", "Ta", "reversible", "availBack", "AsB", "BetasB", "TaB", "nuR", "nuP", "expR", "expP"]])
+            res = np.empty((ns, chem["Ns"]))
+            lib.rxo_source_points.restype = None
+            t0 = time.perf_counter(); nrep = 0
+            while time.perf_counter() - t0 < 10.0:
+                lib.rxo_source_points(C.byref(ch), 1, C.c_double(0.09), C.c_double(0.2), C.c_int64(ns), rxcase._p(k(T[:ns])), rxcase._p(k(rho[:ns])),
+                                      rxcase._p(k(Y[:ns])), rxcase._p(k(omT[:ns])), rxcase._p(k(vol[:ns])), rxcase._p(res))
+                nrep += 1
+            line["cpu_baseline"] = {"value": nrep * ns / (time.perf_counter() - t0), "unit": "updates/s", "cores": 1, "kind": "port",
+                                    "sample": "%d passes of the CPU restatement (oracle/rx_oracle.cpp: rxo_source_points) over the first %d points, one core" % (nrep, ns)}
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": "updates/s", "cores": 0, "kind": "port", "sample": "failed: %s" % str(e)[:200]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -112,8 +226,10 @@ def main():
     ap.add_argument("--nx", type=int, default=1415)
     ap.add_argument("--ny", type=int, default=1415)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans"],
-                    help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share)")
+    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source"],
+                    help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share); "
+                         "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3])")
+    ap.add_argument("--points", type=int, default=64_000_000)
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 0); K = max(a.steps, 1)
@@ -125,7 +241,7 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        if rans:
+        if rans or a.workload == "source":
             print(json.dumps({"impl": "reference", "unavailable": "the reference arm is prepared for the laminar bench workload (configs[1]) only"}))
             return
         r = run_reference(K, W)
@@ -153,6 +269,8 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     chem = pk.load_mechanism()
+    if a.workload == "source":
+        return bench_source(a, pk, chem, rank, world, local, dev, K, W)
     opts = pk.default_opts(rans=rans, cfl=0.1)
     nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
     if world > 1:

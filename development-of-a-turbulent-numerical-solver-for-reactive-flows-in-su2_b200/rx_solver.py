@@ -110,6 +110,34 @@ def _c(a, dt=np.float64):
     return np.ascontiguousarray(a, dtype=dt)
 
 
+def _chem_struct(chem, keep):
+    """rx_chem over numpy arrays (kept alive in `keep`)."""
+    k = lambda a, dt=np.float64: (keep.append(_c(a, dt)), keep[-1])[1]
+    Ns, Nr = int(chem["Ns"]), int(chem["Nr"])
+    pad = lambda a, n: k(np.asarray(a, dtype=np.float64).reshape(-1) if n else np.zeros(1))
+    return _Chem(Ns, Nr, int(chem["nKnots"]), _d(k(chem["mMasses"])), _d(k(chem["diffVol"])), _d(k(chem["x"])),
+                 _d(k(chem["y"])), _d(k(chem["y2"])),
+                 *[_d(pad(chem[n], Nr)) for n in ["As", "Betas", "Ta", "reversible", "availBack", "AsB", "BetasB", "TaB"]],
+                 *[_d(pad(chem[n], Nr * Ns)) for n in ["nuR", "nuP", "expR", "expP"]])
+
+
+def source_points(chem, T, rho, Y, vol, omegaTurb=None, rans=False, cMu=0.09, pasrLb=0.2, device=0):
+    """Stand-alone Arrhenius (+ PaSR when rans) source over independent points, host arrays in and out
+    (CSourceReactive::ComputeChemistry, numerics_direct_reactive.cpp:1728-1825): returns res[n][Ns] = -omega_s * vol."""
+    L = load_library()
+    keep = []
+    ch = _chem_struct(chem, keep)
+    T = _c(T); rho = _c(rho); Y = _c(Y); vol = _c(vol)
+    n = T.shape[0]
+    res = np.empty((n, int(chem["Ns"])))
+    om = _c(omegaTurb) if omegaTurb is not None else None
+    rc = L.rx_source_points(C.byref(ch), int(bool(rans)), C.c_double(cMu), C.c_double(pasrLb), C.c_int64(n), _d(T), _d(rho), _d(Y),
+                            _d(om) if om is not None else None, _d(vol), _d(res), int(device))
+    if rc != 0:
+        raise RxError("rx_source_points failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
+    return res
+
+
 class CReactiveNSSolverGPU:
     """Mirror of CReactiveNSSolver (SU2_CFD/include/solver_reactive.hpp:398) whose hot virtuals run on the GPU.
 
@@ -240,6 +268,11 @@ class CReactiveNSSolverGPU:
 
     def HaloUnpack(self, what, n, ids_dev_ptr, buf_dev_ptr):
         self._ck(self.lib.rx_halo_unpack(self.ctx, int(what), C.c_int64(n), C.c_void_p(ids_dev_ptr), C.c_void_p(buf_dev_ptr)))
+
+    def SourcePointsDev(self, n, T_ptr, rho_ptr, Y_ptr, omegaTurb_ptr, vol_ptr, res_ptr):
+        """Device-pointer form of source_points (SoA Y[Ns][n], res[Ns][n]); constants (rans, C_mu, PaSR bound) are the context's."""
+        v = lambda p: C.c_void_p(p) if p else None
+        self._ck(self.lib.rx_source_points_dev(self.ctx, C.c_int64(n), v(T_ptr), v(rho_ptr), v(Y_ptr), v(omegaTurb_ptr), v(vol_ptr), v(res_ptr)))
 
     def Synchronize(self): self._ck(self.lib.rx_synchronize(self.ctx))
     def LaunchCount(self): return int(self.lib.rx_launch_count(self.ctx))

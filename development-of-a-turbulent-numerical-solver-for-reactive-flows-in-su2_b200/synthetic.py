@@ -76,3 +76,24 @@ def synthetic_state(mesh, chem, seed=12345, rans=False, fuel=0, oxidizer=2, Tpea
     U[:, 0] = rho; U[:, 1] = rho * u; U[:, 2] = rho * v; U[:, 3] = rho * (hmix + 0.5 * (u * u + v * v) + k) - P
     U[:, 4:] = rho[:, None] * Y
     return U, T.copy(), turb
+
+
+def synthetic_points(chem, n, seed=12345, fuel=0, oxidizer=2):
+    """Independent thermochemical states for the source-term microbenchmark: T ~ U[300, 2500] K,
+    P ~ U[0.9, 1.4] 1e5 Pa, Y = normalised U[0,1]^Ns with 30 % of the points pure oxidiser and 10 % pure fuel (the 1e-30 /
+    1e-15 / 1e-10 thresholds of the rate expressions), omega_turb ~ 10^U[2,7] 1/s.  Returns T, rho, Y[n][Ns], omega_turb, vol."""
+    rng = np.random.default_rng(seed)
+    Ns = chem["Ns"]
+    T = rng.uniform(300.0, 2500.0, n)
+    P = rng.uniform(0.9e5, 1.4e5, n)
+    Y = rng.uniform(0.0, 1.0, (n, Ns))
+    u = rng.uniform(0.0, 1.0, n)
+    Y[u < 0.3] = 0.0; Y[u < 0.3, oxidizer] = 1.0
+    pf = (u >= 0.3) & (u < 0.4)
+    Y[pf] = 0.0; Y[pf, fuel] = 1.0
+    Y /= Y.sum(1, keepdims=True)
+    Rg = (Y * (R_UNGAS / chem["mMasses"])[None, :]).sum(1)
+    rho = P / (Rg * T)
+    omT = 10.0 ** rng.uniform(2.0, 7.0, n)
+    vol = rng.uniform(0.5e-8, 2.0e-8, n)
+    return T, rho, Y, omT, vol

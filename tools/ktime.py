@@ -17,6 +17,6 @@ s = pk.CReactiveNSSolverGPU(mesh, chem, opts)
 s.SetSolution(U0); s.SetTemperature(T0); s.SetTurbulence(turb)
 for it in range(a.iters):
     rms = s.Iterate(it + 1, [0.66667, 0.66667, 1.0])
-names = [("edge_flux_visc", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("transport", 7), ("gradient", 4), ("update", 6)]
+names = [("edge_flux_visc", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("transport", 7), ("gradient", 4), ("update", 6), ("source", 5)]
 kt = {n: round(s.KernelTime(w, a.reps), 4) for n, w in names}
 print(json.dumps({"lib": os.environ.get("RX_CUDA_LIB", "default"), "rans": a.rans, "edges": s.nEdge, "rms0": float(rms[0]), "kernel_ms": kt}))
