@@ -454,7 +454,8 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
 #pragma unroll
   for (int s = 0; s < NS; ++s) { Ys[s] = clipy<NS>(Yin[s]); Cs[s] = 1.0e3 * rho * Ys[s]; }   // SetConcentration :701-705
   div_by_M(cc, Cs);
-  double wir[NRMAX][NS], kp[NRMAX];
+  // the per-reaction production terms are folded into omega as they are formed, in reaction order — the order of the sums in
+  // GetMassProductionTerm (:143-154 with the PaSR constants, :196-202 without) — so no per-reaction array is kept
   for (int r = 0; r < Nr; ++r) {
     // ComputeRateConstants :835-867 (K_eq from Gibbs only decides kb when no backward data are available)
     const double kf = cc.As[r] * pow_exp(T, cc.Betas[r]) * exp(-cc.Ta[r] / T);
@@ -493,9 +494,7 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
       br = eig_redux<NS, true>(tmp);
       br *= kb;
     }
-#pragma unroll
-    for (int s = 0; s < NS; ++s) wir[r][s] = 1.0e-3 * cc.M[s] * (cc.nuP[r][s] - cc.nuR[r][s]) * (fr - br);   // SetSourceTerm :99-114
-    kp[r] = 1.0;
+    double kpr = 1.0;
     if (pasr) {   // Set_DfrDrhos :122-136, GetTimeCombustion_r :208-227, AssemblePaSRConstant :161-190
       double hi = 0.0;
       bool first = true;
@@ -508,17 +507,16 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
         }
       const double tauMix = 1 / (cMu * omegaTurb);
       const double tauC = 1 / hi;
-      if (isinf(tauC)) kp[r] = 1.0;
-      else if ((tauC / (tauC + tauMix)) < pasrLb) kp[r] = pasrLb;
-      else kp[r] = tauC / (tauC + tauMix);
+      if (isinf(tauC)) kpr = 1.0;
+      else if ((tauC / (tauC + tauMix)) < pasrLb) kpr = pasrLb;
+      else kpr = tauC / (tauC + tauMix);
     }
-  }
-  if (pasr) {   // GetMassProductionTerm(i) :143-154
 #pragma unroll
-    for (int s = 0; s < NS; ++s) { double w = 0.0; for (int r = 0; r < Nr; ++r) w += kp[r] * wir[r][s]; omega[s] = w; }
-  } else {      // GetMassProductionTerm() :196-202 (rowwise sum)
-#pragma unroll
-    for (int s = 0; s < NS; ++s) { double w = wir[0][s]; for (int r = 1; r < Nr; ++r) w = w + wir[r][s]; omega[s] = w; }
+    for (int s = 0; s < NS; ++s) {
+      const double w = 1.0e-3 * cc.M[s] * (cc.nuP[r][s] - cc.nuR[r][s]) * (fr - br);   // SetSourceTerm :99-114
+      if (pasr) omega[s] = omega[s] + kpr * w;          // w = 0; w += kp[r] * wir[r][s]
+      else omega[s] = (r == 0) ? w : omega[s] + w;      // w = wir[0][s]; w = w + wir[r][s]
+    }
   }
 }
 

@@ -198,6 +198,9 @@ __global__ void __launch_bounds__(64) k_edge_conv2(const __grid_constant__ ChemC
   for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
 }
 
+#ifndef RX_SRC_MINB
+#define RX_SRC_MINB 5
+#endif
 // ---- Source_Residual (:2792-2874) + CSourceReactive::ComputeChemistry (numerics_direct_reactive.cpp:1728-1825), per owned point
 template <int NS>
 __device__ __forceinline__ void point_source(const ChemC<NS>& cc, const Opts& o, const Dev& d, long long p, double* src) {
@@ -211,7 +214,7 @@ __device__ __forceinline__ void point_source(const ChemC<NS>& cc, const Opts& o,
   for (int s = 0; s < NS; ++s) src[s] = src[s] * (-Volume / (1.0 / 1.0));
 }
 template <int NS>
-__global__ void __launch_bounds__(128) k_source(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+__global__ void __launch_bounds__(128, RX_SRC_MINB) k_source(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (p >= d.nPointDomain) return;
   double src[NS];
@@ -221,7 +224,7 @@ __global__ void __launch_bounds__(128) k_source(const __grid_constant__ ChemC<NS
 }
 // stand-alone form over independent points, SoA inputs Y[s*n+p], res[s*n+p]
 template <int NS>
-__global__ void __launch_bounds__(128) k_source_points(const __grid_constant__ ChemC<NS> cc, int rans, double cMu, double pasrLb, long long n,
+__global__ void __launch_bounds__(128, RX_SRC_MINB) k_source_points(const __grid_constant__ ChemC<NS> cc, int rans, double cMu, double pasrLb, long long n,
                                                        const double* __restrict__ T, const double* __restrict__ rho, const double* __restrict__ Y,
                                                        const double* __restrict__ omT, const double* __restrict__ vol, double* __restrict__ res) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -236,8 +239,11 @@ __global__ void __launch_bounds__(128) k_source_points(const __grid_constant__ C
 }
 
 // ---- owner-computes accumulation of edge fluxes into LinSysRes.  MODE: 1 conv (+i, -j), 2 visc (-i, +j), 3 conv, visc, then source
+#ifndef RX_ACC_MINB
+#define RX_ACC_MINB 4
+#endif
 template <int NS, int MODE>
-__global__ void __launch_bounds__(128) k_accumulate(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+__global__ void __launch_bounds__(128, RX_ACC_MINB) k_accumulate(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (p >= d.nPoint) return;
   constexpr int NV = 4 + NS;
@@ -245,6 +251,34 @@ __global__ void __launch_bounds__(128) k_accumulate(const __grid_constant__ Chem
 #pragma unroll
   for (int v = 0; v < NV; ++v) r[v] = d.R[v * d.np + p];
   const int k0 = d.incPtr[p], k1 = d.incPtr[p + 1];
+#ifdef RX_ACC_PREFETCH
+  // the flux words of the next incident edge are in flight while those of the current one are added (same order of additions)
+  auto sweep = [&](const double* __restrict__ flux, bool plusFirst) {
+    if (k0 >= k1) return;
+    double f[NV], g[NV];
+    int code = d.incEdge[k0];
+    {
+      const long long e = code >= 0 ? code : ~code;
+#pragma unroll
+      for (int v = 0; v < NV; ++v) f[v] = flux[v * d.ne + e];
+    }
+    for (int k = k0; k < k1; ++k) {
+      const bool add = (code >= 0) == plusFirst;
+      int codeN = code;
+      if (k + 1 < k1) {
+        codeN = d.incEdge[k + 1];
+        const long long e = codeN >= 0 ? codeN : ~codeN;
+#pragma unroll
+        for (int v = 0; v < NV; ++v) g[v] = flux[v * d.ne + e];
+      }
+#pragma unroll
+      for (int v = 0; v < NV; ++v) { r[v] = add ? r[v] + f[v] : r[v] - f[v]; f[v] = g[v]; }
+      code = codeN;
+    }
+  };
+  if (MODE & 1) sweep(d.fluxC, true);
+  if (MODE & 2) sweep(d.fluxV, false);
+#else
   if (MODE & 1) {
     for (int k = k0; k < k1; ++k) {
       const int code = d.incEdge[k];
@@ -263,6 +297,7 @@ __global__ void __launch_bounds__(128) k_accumulate(const __grid_constant__ Chem
       for (int v = 0; v < NV; ++v) { const double f = d.fluxV[v * d.ne + e]; r[v] = first ? r[v] - f : r[v] + f; }
     }
   }
+#endif
   if (MODE == 3 && p < d.nPointDomain) {
     double src[NS];
     point_source<NS>(cc, o, d, p, src);
