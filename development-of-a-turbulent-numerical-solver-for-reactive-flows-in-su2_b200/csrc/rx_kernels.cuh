@@ -6,6 +6,12 @@
 // and needs no atomics.
 #pragma once
 #include "rx_flux.cuh"
+#ifndef RX_PR_MINB
+#define RX_PR_MINB 4
+#endif
+#ifndef RX_GR_MINB
+#define RX_GR_MINB 4
+#endif
 #ifndef RX_TR_MINB
 #define RX_TR_MINB 3
 #endif
@@ -164,7 +170,7 @@ __global__ void __launch_bounds__(128, RX_TR_MINB) k_transport(const __grid_cons
 
 // ---- SetPrimitive_Variables (solver_direct_reactive.cpp:985-1038) + CReactiveNSVariable::SetPrimVar (variable_direct_reactive.cpp:1188-1228)
 template <int NS>
-__global__ void __launch_bounds__(128) k_primitive(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d,
+__global__ void __launch_bounds__(128, RX_PR_MINB) k_primitive(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d,
                                                    long long extIter, int output) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (p >= d.nPoint) return;
@@ -279,7 +285,7 @@ __device__ __forceinline__ bool ls_sums(const Dev& d, long long p, const double*
 }
 
 template <int NS>
-__global__ void __launch_bounds__(128) k_gradient_ls(const Dev d) {
+__global__ void __launch_bounds__(128, RX_GR_MINB) k_gradient_ls(const Dev d) {
   const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (p >= d.nPoint) return;
   constexpr int NG = 4 + NS;
