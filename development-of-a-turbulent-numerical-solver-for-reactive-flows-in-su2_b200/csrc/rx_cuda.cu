@@ -36,6 +36,9 @@ struct rx_ctx {
   size_t stageBytes = 0;
   int updBlocks = 0;
   long long launches = 0;
+  cudaStream_t bcStream = nullptr;   // second stream for boundary kernels of markers that share no vertex
+  cudaEvent_t evFork = nullptr, evJoin = nullptr;
+  bool bcConcurrent = false;
   bool splitSource = false;         // A/B hook (env RX_SPLIT_SOURCE=1): accumulation and source term as two kernels
   bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
@@ -290,6 +293,22 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     for (int q = 0; q < 16; ++q) md.Ys[q] = (s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
     c->markers.push_back(md);
   }
+  {   // may the first-group boundary kernels overlap?  Only if no point carries two of those markers.
+    std::vector<char> seen(nP, 0);
+    int nFirst = 0; bool disjoint = true;
+    for (int k = 0; k < m->nMarker; ++k) {
+      const rx_marker& s = m->markers[k];
+      if (!(s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || s.kind == RX_BC_OUTLET || s.kind == RX_BC_EULER_WALL) || !s.nVertex) continue;
+      ++nFirst;
+      for (int v = 0; v < s.nVertex; ++v) { if (seen[s.node[v]]) disjoint = false; seen[s.node[v]] = 1; }
+    }
+    const char* ev = getenv("RX_BC_SERIAL");
+    if (nFirst >= 2 && disjoint && !(ev && ev[0] == '1')) {
+      if (cudaStreamCreateWithFlags(&c->bcStream, cudaStreamNonBlocking) == cudaSuccess &&
+          cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming) == cudaSuccess &&
+          cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) == cudaSuccess) c->bcConcurrent = true;
+    }
+  }
   if (cudaDeviceSynchronize() != cudaSuccess) { g_create_error = "rx_create: upload failed"; rx_destroy(c); return RX_ERR_CUDA; }
   *out = c;
   return RX_OK;
@@ -300,6 +319,9 @@ void rx_destroy(rx_ctx* c) {
   cudaSetDevice(c->device);
   for (void* p : c->allocs) cudaFree(p);
   if (c->stage) cudaFree(c->stage);
+  if (c->evFork) cudaEventDestroy(c->evFork);
+  if (c->evJoin) cudaEventDestroy(c->evJoin);
+  if (c->bcStream) cudaStreamDestroy(c->bcStream);
   delete c;
 }
 
@@ -442,9 +464,8 @@ int rx_residual_source(rx_ctx* c) {
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
-static void launch_bc(rx_ctx* c, const MarkerDev& m) {
+static void launch_bc(rx_ctx* c, const MarkerDev& m, cudaStream_t s) {
   const Dev& d = c->d;
-  cudaStream_t s = c->stream;
   if (!m.nVertex) return;
   if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
   else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
@@ -453,16 +474,27 @@ static void launch_bc(rx_ctx* c, const MarkerDev& m) {
   else if (m.kind == RX_BC_EULER_WALL) { k_bc_euler_wall<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
 }
 int rx_bc(rx_ctx* c) {
+  // First group (inlet, outlet, Euler wall).  Each of these kernels is one partial wave of long serial threads (a Stefan-Maxwell
+  // solve per vertex), so markers that share no vertex — established at create — alternate between two streams; every
+  // residual row is still written by one kernel only, in the reference's order per point.
+  const bool fork = c->bcConcurrent;
+  if (fork) { RX_CK(cudaEventRecord(c->evFork, c->stream)); RX_CK(cudaStreamWaitEvent(c->bcStream, c->evFork, 0)); }
+  int nth = 0;
   for (const MarkerDev& m : c->markers)
-    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) launch_bc(c, m);
+    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) {
+      if (!m.nVertex) continue;
+      launch_bc(c, m, (fork && (nth & 1)) ? c->bcStream : c->stream);
+      ++nth;
+    }
+  if (fork) { RX_CK(cudaEventRecord(c->evJoin, c->bcStream)); RX_CK(cudaStreamWaitEvent(c->stream, c->evJoin, 0)); }
   for (const MarkerDev& m : c->markers)
-    if (m.kind == RX_BC_ISOTHERMAL || m.kind == RX_BC_HEATFLUX) launch_bc(c, m);
+    if (m.kind == RX_BC_ISOTHERMAL || m.kind == RX_BC_HEATFLUX) launch_bc(c, m, c->stream);
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
 int rx_bc_marker(rx_ctx* c, int marker) {
   if (marker < 0 || marker >= (int)c->markers.size()) { c->err = "rx_bc_marker: marker index out of range"; return RX_ERR_ARG; }
-  launch_bc(c, c->markers[marker]);
+  launch_bc(c, c->markers[marker], c->stream);
   RX_CK(cudaGetLastError());
   return RX_OK;
 }

@@ -48,22 +48,26 @@ def dual_mesh(coord, tri, boundaries, nPointDomain=None):
     fa = np.concatenate([tri[:, 0], tri[:, 1], tri[:, 2]])
     fb = np.concatenate([tri[:, 1], tri[:, 2], tri[:, 0]])
     ex = np.concatenate([ecx, ecx, ecx]); ey = np.concatenate([ecy, ecy, ecy])
-    lo = np.minimum(fa, fb); hi = np.maximum(fa, fb)
-    key = lo * nP + hi
+    key = np.minimum(fa, fb) * nP + np.maximum(fa, fb)
     ukey, inv = np.unique(key, return_inverse=True)
+    del key                                                    # the large meshes are built per rank: keep the peak down
     nE = ukey.shape[0]
     ei = ukey // nP; ej = ukey % nP
+    del ukey
     mx = 0.5 * (x[fa] + x[fb]); my = 0.5 * (y[fa] + y[fb])     # edge CG
     flip = fa > fb
     nxc = np.where(flip, my - ey, ey - my)
-    nyc = np.where(flip, -(mx - ex), -(ex - mx))
     enx = np.bincount(inv, weights=nxc, minlength=nE)
+    del nxc
+    nyc = np.where(flip, -(mx - ex), -(ex - mx))
     eny = np.bincount(inv, weights=nyc, minlength=nE)
+    del nyc, inv, flip
     # control volumes: 0.5*|(E - P) x (M - P)| for both end points of every element face
     def area(p):
-        ax = ex - x[p]; ay = ey - y[p]; bx = mx - x[p]; by = my - y[p]
-        return 0.5 * np.abs(ax * by - ay * bx)
+        xp = x[p]; yp = y[p]
+        return 0.5 * np.abs((ex - xp) * (my - yp) - (ey - yp) * (mx - xp))
     vol = np.bincount(fa, weights=area(fa), minlength=nP) + np.bincount(fb, weights=area(fb), minlength=nP)
+    del fa, fb, ex, ey, mx, my
     # neighbour CSR (sorted by neighbour index)
     src = np.concatenate([ei, ej]); dst = np.concatenate([ej, ei])
     order = np.lexsort((dst, src))
