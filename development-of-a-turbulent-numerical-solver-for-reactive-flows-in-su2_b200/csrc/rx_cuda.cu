@@ -216,6 +216,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     cudaError_t e = cudaFuncSetAttribute(k_edge_flux<9, true, true, true>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_flux<9, false, true, true>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
+    if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
     if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }

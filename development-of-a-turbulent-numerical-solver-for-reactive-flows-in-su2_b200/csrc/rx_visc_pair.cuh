@@ -27,7 +27,14 @@ namespace rx {
 constexpr int VP_BS = RX_VP_BS;       // threads per block (two per edge)
 constexpr int VP_MINB = RX_VP_MINB;   // resident blocks per SM the register budget is set for
 constexpr int VP_MREG = RX_VP_MREG;   // matrix slots held in registers; the others are read from shared memory
+#ifndef RX_VP_NO_ASYNC_D
+#define RX_VP_ASYNC_D 1   // 1/D prefetch through cp.async into shared memory (default); -DRX_VP_NO_ASYNC_D keeps it in registers
+#endif
+#ifdef RX_VP_ASYNC_D
+constexpr int VP_SMW = 5 * 9 + 2 * 9;   // shared-memory words per thread: the lane's five matrix rows + the staged 1/D words
+#else
 constexpr int VP_SMW = 5 * 9;   // shared-memory words per thread: the lane's five matrix rows
+#endif
 constexpr int VP_SMW_RANS = 13 * 5;   // SST closure: the pair shares a 9 x 13 array (operator, two right-hand sides, norms)
 constexpr unsigned VP_FULL = 0xffffffffu;
 
@@ -449,6 +456,24 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
     bool inOk = mid_range(rho);   // rho and the mole fractions enter every quotient of the assembly
 #pragma unroll
     for (int s = 0; s < NS; ++s) inOk = inOk && num_range(Xs[s]);
+#ifdef RX_VP_ASYNC_D
+    // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead by asynchronous copies straight into
+    // 18 thread-private shared-memory words (cp.async: no registers are held across the division batches of the current slot)
+    auto stageD = [&](int w) -> double* { return sm + (VP_SMW - 2 * NS + w) * VP_BS; };
+    auto fetchD = [&](int k) {
+      const int r = k < 4 ? 2 * k + l : 8;
+      const int base_r = r * NS - r * (r - 1) / 2 - r;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        const int up = c * NS - c * (c - 1) / 2 - c + r;
+        const size_t q = (size_t)(c >= r ? base_r + c : up) * np;
+        const unsigned sa = (unsigned)__cvta_generic_to_shared(stageD(c)), sb = (unsigned)__cvta_generic_to_shared(stageD(NS + c));
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(rdi + q) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sb), "l"(rdj + q) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#else
     double ra[NS], rb[NS];   // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead
     auto fetchD = [&](int k) {
       const int r = k < 4 ? 2 * k + l : 8;
@@ -462,14 +487,21 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
         ra[c] = rdi[q]; rb[c] = rdj[q];
       }
     };
+#endif
     fetchD(0);
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
       const int r = k < 4 ? 2 * k + l : 8;
       const double Xr = Xrow[0];
       double sD[NS];
+#ifdef RX_VP_ASYNC_D
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+      for (int c = 0; c < NS; ++c) sD[c] = *stageD(c) + *stageD(NS + c);
+#else
 #pragma unroll
       for (int c = 0; c < NS; ++c) sD[c] = ra[c] + rb[c];
+#endif
       if (k < 4) fetchD(k + 1);
       double tk = 0.0, dm[NS], gq[NS], tq[NS];
       const double sx = smm * Xr;

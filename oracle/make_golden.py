@@ -141,6 +141,12 @@ SPECS = {
                        dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
                             SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="BARTH_JESPERSEN", CFL_NUMBER="0.2"),
                        2, 1, 29, False),
+    # inviscid multispecies reactive Euler solver (CReactiveEulerSolver itself): AUSM + source, slip walls, explicit RK
+    "channel_euler": (dict(nx=41, ny=21, stretch=1.5),
+                      dict(CHANNEL_MARKERS, PHYSICAL_PROBLEM="REACTIVE_EULER", MARKER_ISOTHERMAL="( NONE )",
+                           MARKER_EULER="( upper_wall, lower_wall )", RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE",
+                           IGNITION="NO", TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )",
+                           CFL_NUMBER="0.2"), 2, 1, 31, False),
 }
 
 

@@ -13,7 +13,7 @@ import pytest
 
 from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 
-CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj"]
+CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler"]
 TOL = 1e-13
 
 
