@@ -3,6 +3,8 @@
 #include "../../include/rx_cuda.h"
 #include "rx_kernels2.cuh"
 #include "rx_visc_pair.cuh"
+#include "rx_visc_quad.cuh"
+#include "rx_order.cuh"
 
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -16,6 +18,7 @@
 using namespace rx;
 
 static constexpr size_t SM_PAIR = (size_t)VP_SMW * VP_BS * sizeof(double);
+static constexpr size_t SM_QUAD = (size_t)VQ_SMW * VQ_BS * sizeof(double);
 static constexpr size_t SM_PAIR_RANS = (size_t)VP_SMW_RANS * VP_BS * sizeof(double);
 static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
@@ -40,6 +43,9 @@ struct rx_ctx {
   cudaEvent_t evFork = nullptr, evJoin = nullptr;
   bool bcConcurrent = false;
   bool splitSource = false;         // A/B hook (env RX_SPLIT_SOURCE=1): accumulation and source term as two kernels
+  bool orderEdges = true;           // viscous kernel processes the edges grouped by their last iteration count (rx_order.cuh); env RX_VISC_NO_ORDER=1 turns it off
+  int* eOrderBuf = nullptr; int* ordHist = nullptr; int nOrdTiles = 0;
+  bool viscQuad = false;            // A/B hook (env RX_VISC_QUAD=1): four-lanes-per-edge laminar viscous kernel (rx_visc_quad.cuh)
   bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
 
@@ -170,6 +176,7 @@ static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   if (c->o.rans && c->ransThreadPerEdge) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
   if (CONV) { k_edge_flux<9, true, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; }
   if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(c->cc9, c->o, d);
+  else if (c->viscQuad) k_edge_visc_quad<9><<<nblk(4 * d.nEdge, VQ_BS), VQ_BS, SM_QUAD, s>>>(c->cc9, c->o, d);
   else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
   c->launches++;
 }
@@ -208,6 +215,8 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   rx_ctx* c = new rx_ctx();
   c->device = op->device;
   { const char* ev = getenv("RX_RANS_THREAD_PER_EDGE"); c->ransThreadPerEdge = ev && ev[0] == '1'; }
+  { const char* ev = getenv("RX_VISC_NO_ORDER"); c->orderEdges = !(ev && ev[0] == '1'); }
+  { const char* ev = getenv("RX_VISC_QUAD"); c->viscQuad = ev && ev[0] == '1'; }
   { const char* ev = getenv("RX_SPLIT_SOURCE"); c->splitSource = ev && ev[0] == '1'; }
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
   {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
@@ -217,6 +226,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_flux<9, false, true, true>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
     if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
+    if (e == cudaSuccess && SM_QUAD > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_quad<9>, at, (int)SM_QUAD);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
     if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }
@@ -269,6 +279,13 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.turb = dalloc<double>(c, np * 6); d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
   d.fluxV = o.viscous ? dalloc<double>(c, ne * c->nVar) : nullptr;
+  d.eOrder = nullptr;
+  d.eKey = o.viscous ? dalloc<unsigned char>(c, ne) : nullptr;
+  if (o.viscous && c->orderEdges) {
+    c->nOrdTiles = (int)((d.nEdge + ORD_TILE - 1) / ORD_TILE);
+    c->eOrderBuf = dalloc<int>(c, ne);
+    c->ordHist = dalloc<int>(c, (size_t)ORD_NB * std::max(c->nOrdTiles, 1));
+  }
   d.nonPhys = dalloc<int>(c, np); d.counters = dalloc<unsigned long long>(c, 4);
   c->updBlocks = (int)nblk(d.nPointDomain, 128);
   c->partial = dalloc<double>(c, (size_t)c->updBlocks * c->nVar);
@@ -599,8 +616,34 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
   return RX_OK;
 }
 
+// new processing order of the viscous edge kernel from the keys its last launch left (rx_order.cuh)
+static int order_edges(rx_ctx* c) {
+  Dev& d = c->d;
+  if (!c->orderEdges || !c->eOrderBuf || d.nEdge == 0) return RX_OK;
+  k_order_hist<<<c->nOrdTiles, ORD_BS, 0, c->stream>>>(d.eKey, d.nEdge, c->nOrdTiles, c->ordHist);
+  k_order_scan<<<1, 1024, 0, c->stream>>>(c->ordHist, (long long)ORD_NB * c->nOrdTiles);
+  k_order_scatter<<<c->nOrdTiles, ORD_BS, 0, c->stream>>>(d.eKey, d.nEdge, c->nOrdTiles, c->ordHist, c->eOrderBuf);
+  c->launches += 3;
+  RX_CK(cudaGetLastError());
+  d.eOrder = c->eOrderBuf;
+  return RX_OK;
+}
+
+int rx_get_edge_order(rx_ctx* c, int32_t* order, uint8_t* key) {
+  const Dev& d = c->d;
+  if (!d.eKey) { c->err = "rx_get_edge_order: inviscid context"; return RX_ERR_ARG; }
+  RX_CK(cudaStreamSynchronize(c->stream));
+  if (key) RX_CK(cudaMemcpy(key, d.eKey, (size_t)d.nEdge, cudaMemcpyDeviceToHost));
+  if (order) {
+    if (d.eOrder) RX_CK(cudaMemcpy(order, d.eOrder, (size_t)d.nEdge * sizeof(int), cudaMemcpyDeviceToHost));
+    else for (long long e = 0; e < d.nEdge; ++e) order[e] = (int32_t)e;
+  }
+  return RX_OK;
+}
+
 int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, double* resRms) {
   int rc;
+  if (c->o.viscous && (rc = order_edges(c))) return rc;
   for (int rk = 0; rk < nRK; ++rk) {
     if ((rc = rx_preprocess(c, extIter, 0, nullptr))) return rc;
     if (rk == 0) {

@@ -28,6 +28,8 @@ struct Dev {   // device pointers + sizes, passed by value to kernels
   // state
   double *U, *Uold, *V, *X, *Cp, *gam, *mu, *kap, *rD, *grad, *vort, *strain, *turb, *dt, *lamInv, *lamVisc, *R, *lim;
   double *fluxC, *fluxV;
+  const int* eOrder;        // processing order of the viscous edge kernel (rx_order.cuh); nullptr = edge order
+  unsigned char* eKey;      // per edge: iterations of its last Stefan–Maxwell solve (+19 if the SST closure ran its QR)
   int* nonPhys; unsigned long long* counters;   // counters[0] = non-physical points of the last preprocess
 };
 

@@ -292,6 +292,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   long long e = t >> 1;
   const bool keep = e < d.nEdge;
   if (!keep) e = d.nEdge - 1;   // the lane stays in the warp's shuffles and votes; nothing it computes is stored
+  if (d.eOrder) e = d.eOrder[e];   // processing slot -> edge (rx_order.cuh); every store below goes by edge index
   const int l = L.l;
   const long long np = d.np;
   const int pi = d.ei[e], pj = d.ej[e];
@@ -434,8 +435,11 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   // rolled over the slots — 135 IEEE divisions unrolled would be most of the kernel's code — with the per-slot operands
   // rotated through registers so that no register array is indexed dynamically.
   auto smA = [&](int k, int c) -> double& { return sm[(k * NS + c) * VP_BS]; };
-  double invd[5];
-  {
+  double invd[5] = {1.0, 1.0, 1.0, 1.0, 1.0};
+  // A zero right-hand side (uniform composition along the edge) makes BiCGSTAB return x = 0 without touching the matrix; a warp
+  // whose sixteen edges are all of that kind skips the assembly and the solve (x = 0 below, as the loop would have left it).
+  const bool anyRhs = __any_sync(VP_FULL, pair_dot(L, rhs, rhs) != 0);
+  if (anyRhs) {
     double sigma = 0.0, massTot = 0.0, yom9[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) sigma = sigma + Ys[s];
@@ -666,6 +670,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   double pS[5];
 #pragma unroll
   for (int k = 0; k < 5; ++k) pS[k] = -x[k];
+  bool ranQR = false;
   if (RANS) {
     // ---- SST closure, part 2: mass-fraction gradients from the mole-fraction ones through the molar->mass operator
     // (Get_Molar2MassGrad_Operator :861-880, solved with Eigen's ColPivHouseholderQR :743), then the turbulent species,
@@ -719,6 +724,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
       MG[dd][4] = 0.0;
       if (l) { Mt(8, NS + dd) = G[1][dd]; need = need || !(fabs(G[1][dd]) < 1e-8); }   // X_8 lives on the odd lane
     }
+    ranQR = need;
     if (__any_sync(VP_FULL, need)) pair_colpiv_qr_solve<NS>(L, smPair, MG);
 #pragma unroll
     for (int dd = 0; dd < 2; ++dd) {
@@ -766,6 +772,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
   if (l == 0) {
     d.fluxV[U_RHO * ne + e] = -sumJ;
     d.fluxV[U_E * ne + e] = pE;
+    d.eKey[e] = (unsigned char)(it + (ranQR ? 19 : 0));
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) d.fluxV[(U_S + row[k]) * ne + e] = pS[k];

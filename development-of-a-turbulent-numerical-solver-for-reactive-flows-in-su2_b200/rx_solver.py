@@ -75,7 +75,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
-           "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max"]
+           "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order"]
 
 _lib = None
 
@@ -251,6 +251,13 @@ class CReactiveNSSolverGPU:
         m = np.empty(self.nVar); ip = np.empty(self.nVar, dtype=np.int64)
         self._ck(self.lib.rx_get_residual_max(self.ctx, _d(m), _i(ip)))
         return m, ip
+
+    def EdgeOrder(self):
+        """(order[nEdge] int32, key[nEdge] uint8): processing order of the viscous edge kernel and the per-edge keys it is
+        built from (rx_get_edge_order; csrc/rx_order.cuh)."""
+        order = np.empty(self.nEdge, dtype=np.int32); key = np.empty(self.nEdge, dtype=np.uint8)
+        self._ck(self.lib.rx_get_edge_order(self.ctx, order.ctypes.data_as(C.POINTER(C.c_int32)), key.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return order, key
 
     def ExplicitEuler_Iteration(self, want_rms=True):
         return self.ExplicitRK_Iteration(1.0, want_rms)

@@ -123,6 +123,12 @@ int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + 
  * preprocess pass (integration_time.cpp:110-112).  resRms may be NULL. */
 int rx_iterate(rx_ctx*, int64_t extIter, int nRK, const double* rkAlpha, double* resRms);
 
+/* diagnostic of the viscous kernel's processing order (no reference counterpart; csrc/rx_order.cuh): order[nEdge] = edge
+ * handled by processing slot k (identity until the first rx_iterate, or always with env RX_VISC_NO_ORDER=1), key[nEdge] =
+ * BiCGSTAB iterations of the edge's last Stefan-Maxwell solve (Solve_SM :451-470), + 19 if the SST closure ran its QR.
+ * Either pointer may be NULL.  Results never depend on the order: fluxes are stored and summed by edge index. */
+int rx_get_edge_order(rx_ctx*, int32_t* order, uint8_t* key);
+
 /* stand-alone Arrhenius(+PaSR) source over independent points (CSourceReactive::ComputeChemistry,
  * numerics_direct_reactive.cpp:1728-1825).  Host-pointer and device-pointer forms. */
 int rx_source_points(const rx_chem*, int rans, double cMu, double pasrLb, int64_t n, const double* T, const double* rho,
