@@ -124,7 +124,7 @@ int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + 
 int rx_iterate(rx_ctx*, int64_t extIter, int nRK, const double* rkAlpha, double* resRms);
 
 /* diagnostic of the viscous kernel's processing order (no reference counterpart; csrc/rx_order.cuh): order[nEdge] = edge
- * handled by processing slot k (identity until the first rx_iterate, or always with env RX_VISC_NO_ORDER=1), key[nEdge] =
+ * handled by processing slot k (identity until the first rx_set_old_solution, which re-forms it once per iteration; on by default for the laminar path, off for RANS; env RX_VISC_ORDER=0/1 forces), key[nEdge] =
  * BiCGSTAB iterations of the edge's last Stefan-Maxwell solve (Solve_SM :451-470), + 19 if the SST closure ran its QR.
  * Either pointer may be NULL.  Results never depend on the order: fluxes are stored and summed by edge index. */
 int rx_get_edge_order(rx_ctx*, int32_t* order, uint8_t* key);
