@@ -560,10 +560,15 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_
 #pragma unroll
     for (int c = 0; c < NS; ++c) A[k][c] = smA(k, c);
   auto getA = [&](int k, int c) -> double { return k < VP_MREG ? A[k][c] : sm[(k * NS + c) * VP_BS]; };
+#ifdef RX_VP_ASYNC_D
+  constexpr int SW0 = VP_SMW - 2 * NS;   // rhs, r0 and x of the solve take the 1/D staging words, free once the matrix stands
+#else
+  constexpr int SW0 = 0;
   static_assert(VP_MREG * NS >= 15, "rhs, r0 and x reuse the words of the register-held rows");
-  auto s_rhs = [&](int k) -> double& { return sm[k * VP_BS]; };
-  auto s_r0 = [&](int k) -> double& { return sm[(5 + k) * VP_BS]; };
-  auto s_x = [&](int k) -> double& { return sm[(10 + k) * VP_BS]; };
+#endif
+  auto s_rhs = [&](int k) -> double& { return sm[(SW0 + k) * VP_BS]; };
+  auto s_r0 = [&](int k) -> double& { return sm[(SW0 + 5 + k) * VP_BS]; };
+  auto s_x = [&](int k) -> double& { return sm[(SW0 + 10 + k) * VP_BS]; };
 
   // ---- Eigen::BiCGSTAB with diagonal preconditioner, tol 1e-11, zero guess, at most 2N iterations (see bicgstab<> in
   // rx_flux.cuh for the serial form and its citations).  All scalars are identical on the two lanes of a pair.  Pairs of
