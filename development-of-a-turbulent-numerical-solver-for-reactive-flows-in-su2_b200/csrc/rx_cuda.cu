@@ -5,6 +5,7 @@
 #include "rx_visc_pair.cuh"
 #include "rx_visc_quad.cuh"
 #include "rx_order.cuh"
+#include "rx_turb.cuh"
 
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -45,6 +46,8 @@ struct rx_ctx {
   bool splitSource = false;         // A/B hook (env RX_SPLIT_SOURCE=1): accumulation and source term as two kernels
   bool orderEdges = true;           // viscous kernel processes the edges grouped by their last iteration count (rx_order.cuh); default: laminar on, RANS off; env RX_VISC_ORDER=0/1 forces
   int* eOrderBuf = nullptr; int nOrdTiles = 0;
+  double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
+  bool haveWallDist = false;
   bool viscQuad = false;            // A/B hook (env RX_VISC_QUAD=1): four-lanes-per-edge laminar viscous kernel (rx_visc_quad.cuh)
   bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
@@ -279,7 +282,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.lim = dalloc<double>(c, np * 4);
   d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
-  d.turb = dalloc<double>(c, np * 6); d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
+  d.turb = dalloc<double>(c, np * 6); c->tpost = o.rans ? dalloc<double>(c, np * TP_N) : nullptr; d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
   d.fluxV = o.viscous ? dalloc<double>(c, ne * c->nVar) : nullptr;
   d.eOrder = nullptr;
@@ -375,6 +378,32 @@ int rx_fp64_peak(rx_ctx* c, double* tflops) {
 
 int rx_set_solution(rx_ctx* c, const double* U) { return upload_aos(c, U, c->d.U, c->nVar); }
 int rx_set_turbulence(rx_ctx* c, const double* t) { return upload_aos(c, t, c->d.turb, 6); }
+// SST Postprocessing on the device (rx_turb.cuh)
+int rx_set_wall_distance(rx_ctx* c, const double* dist) {
+  if (!c->tpost) { c->err = "rx_set_wall_distance: not a RANS context"; return RX_ERR_ARG; }
+  const int rc = upload_aos(c, dist, c->tpost + (size_t)TP_DIST * c->d.np, 1);
+  if (rc == RX_OK) c->haveWallDist = true;
+  return rc;
+}
+int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stage) {
+  if (!c->tpost) { c->err = "rx_turb_postprocess: not a RANS context"; return RX_ERR_ARG; }
+  if (!c->haveWallDist) { c->err = "rx_turb_postprocess: rx_set_wall_distance has not been called"; return RX_ERR_ARG; }
+  if (stage < 0 || stage > 2 || (stage != 2 && !kOmega)) { c->err = "rx_turb_postprocess: bad stage / missing (k, omega)"; return RX_ERR_ARG; }
+  if (!c->o.leastSquares) { c->err = "rx_turb_postprocess: only the WEIGHTED_LEAST_SQUARES gradient of (k, omega) is built"; return RX_ERR_UNSUPPORTED; }
+  const Dev& d = c->d;
+  if (stage != 2) {
+    const int rc = upload_aos(c, kOmega, c->tpost, 2);
+    if (rc) return rc;
+    k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++;
+  }
+  if (stage != 1) { k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost, sigmaK); c->launches++; }
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+int rx_get_turbulence(rx_ctx* c, double* post12) {
+  if (!c->tpost) { c->err = "rx_get_turbulence: not a RANS context"; return RX_ERR_ARG; }
+  return download_aos(c, c->tpost, post12, TP_N);
+}
 int rx_set_temperature(rx_ctx* c, const double* T) { return upload_aos(c, T, c->d.V + V_T * c->d.np, 1); }
 int rx_get_solution(rx_ctx* c, double* U) { return download_aos(c, c->d.U, U, c->nVar); }
 int rx_get_residual(rx_ctx* c, double* R) { return download_aos(c, c->d.R, R, c->nVar); }
@@ -699,8 +728,8 @@ int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int
   return rc;
 }
 
-int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : 4; }
-static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : c->d.lim; }
+int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : 4; }   // 2: limiter, 3: grad k, grad omega
+static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np; }
 int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {
   if (n <= 0) return RX_OK;
   const int nv = rx_halo_width(c, what);

@@ -281,7 +281,12 @@ __device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* 
 }
 
 template <int NS, bool RANS>
-__global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+#ifdef RX_VP_MAXNREG   // explicit register cap instead of a resident-block target (tuning hook)
+__global__ void __maxnreg__(RX_VP_MAXNREG) k_edge_visc_pair(
+#else
+__global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
+#endif
+    const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   static_assert(NS == 9, "the row split {0,2,4,6 | 1,3,5,7,8} is laid out for nine species");
   extern __shared__ double vp_sm[];   // word w of thread t at vp_sm[w * VP_BS + t]
   double* const sm = vp_sm + threadIdx.x;

@@ -9,7 +9,7 @@ The path has no other collective: residual norms are reduced once per iteration 
 import torch
 import torch.distributed as dist
 
-WHAT_SOLUTION, WHAT_GRADIENT, WHAT_LIMITER = 0, 1, 2
+WHAT_SOLUTION, WHAT_GRADIENT, WHAT_LIMITER, WHAT_TURB_GRADIENT = 0, 1, 2, 3   # 3: grad k, grad omega of TurbPostprocessing (stage 1 -> exchange -> stage 2)
 
 
 class HaloExchanger:

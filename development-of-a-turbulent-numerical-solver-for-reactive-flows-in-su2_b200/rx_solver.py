@@ -75,7 +75,8 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
-           "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order"]
+           "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
+           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence"]
 
 _lib = None
 
@@ -251,6 +252,22 @@ class CReactiveNSSolverGPU:
         m = np.empty(self.nVar); ip = np.empty(self.nVar, dtype=np.int64)
         self._ck(self.lib.rx_get_residual_max(self.ctx, _d(m), _i(ip)))
         return m, ip
+
+    def SetWall_Distance(self, dist):
+        """geometry->node[]->GetWall_Distance() of every point, for TurbPostprocessing."""
+        self._ck(self.lib.rx_set_wall_distance(self.ctx, _d(_c(dist))))
+
+    def TurbPostprocessing(self, kOmega=None, sigma_k=0.85, stage=0):
+        """CTurbSSTSolver::Postprocessing on the device (rx_turb_postprocess): gradients of (k, omega), blending functions, eddy
+        viscosity; fills the turbulence fields the flow path reads.  stage 1 / 2: the two halves around the halo exchange."""
+        kw = _c(kOmega) if kOmega is not None else None
+        self._ck(self.lib.rx_turb_postprocess(self.ctx, _d(kw) if kw is not None else None, C.c_double(sigma_k), int(stage)))
+
+    def GetTurbulence(self):
+        """[nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k."""
+        out = np.empty((self.nPoint, 12))
+        self._ck(self.lib.rx_get_turbulence(self.ctx, _d(out)))
+        return out
 
     def EdgeOrder(self):
         """(order[nEdge] int32, key[nEdge] uint8): processing order of the viscous edge kernel and the per-edge keys it is

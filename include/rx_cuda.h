@@ -97,6 +97,18 @@ int rx_synchronize(rx_ctx*);
 int rx_set_solution(rx_ctx*, const double* U);
 int rx_set_temperature(rx_ctx*, const double* T);         /* V[T] = start value of the secant solve (variable_direct_reactive.cpp:622) */
 int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k, omega, dk/dx, dk/dy, sigma_k from CTurbSSTSolver */
+/* SST Postprocessing on the device (first slice; csrc/rx_turb.cuh): replaces the host-side
+ * CTurbSSTSolver::Postprocessing (solver_direct_turbulent.cpp:2953-3015) + rx_set_turbulence.  From the turbulence solution
+ * (k, omega) and the wall distance (CGeometry::ComputeWall_Distance, geometry_structure.cpp:8990) it forms grad k, grad omega
+ * (CSolver::SetSolution_Gradient_LS, solver_structure.cpp:580-722), CDkw, F1, F2 (CTurbSSTVariable::SetBlendingFunc) and
+ * muT = min(max(rho k min(1/omega, a1/(S F2)), 0), 1) with rho, laminar viscosity and strain magnitude of the last rx_preprocess,
+ * and leaves muT, k, omega, grad k, sigma_k where rx_set_turbulence would have put them.  RANS contexts with WLS gradients only.
+ * stage: 0 = all of it (single partition); 1 = upload + gradients only, 2 = blending + muT only — between the two a
+ * partitioned run exchanges the gradients of its halo points (rx_halo_pack/unpack with what = 3, Set_MPI_Solution_Gradient
+ * solver_direct_turbulent.cpp:227). */
+int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
+int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; may be NULL for stage 2 */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
+int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);
 int rx_get_solution(rx_ctx*, double* U);
 int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */
 int rx_get_dt(rx_ctx*, double* dt3);                      /* [nPoint][3]: Delta_Time, Max_Lambda_Inv, Max_Lambda_Visc */
@@ -137,7 +149,7 @@ int rx_source_points_dev(rx_ctx*, int64_t n, const double* T_dev, const double* 
                          const double* omegaTurb_dev, const double* vol_dev, double* res_dev /* [Ns][n] SoA */);
 
 /* halo exchange plumbing for one-process-per-GPU runs (replaces Set_MPI_Solution :1530, Set_MPI_Primitive_Gradient :1877):
- * pack `what` (0 = conserved U, 1 = primitive gradients, 2 = limiters of T,u,v,P: Set_MPI_Primitive_Limiter :1756) of the listed points into buf_dev[nVarOfWhat][n],
+ * pack `what` (0 = conserved U, 1 = primitive gradients, 2 = limiters of T,u,v,P: Set_MPI_Primitive_Limiter :1756, 3 = grad k and grad omega of rx_turb_postprocess: Set_MPI_Solution_Gradient solver_direct_turbulent.cpp:227) of the listed points into buf_dev[nVarOfWhat][n],
  * or unpack into them; the transport in between (NCCL send/recv) belongs to the caller. */
 int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double* buf_dev);
 int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);

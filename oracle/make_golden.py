@@ -176,9 +176,15 @@ def run_case(name):
             # the "prev_" dumps are only needed for T (secant start value); aux/grad copies are dropped to keep fixtures small
             if k.endswith("prev_aux") or k.endswith("prev_grad") or k.endswith("out_grad"):
                 continue
-            if lean and k.split("_", 2)[-1] in ("res_conv", "res_visc", "res_src", "out_V", "out_aux"):
+            if lean and k.split("_", 2)[-1] in ("res_conv", "res_visc", "res_src"):
                 continue
             a = np.load(os.path.join(out, f))
+            if k.endswith("out_V") and os.path.exists(os.path.join(out, k[:-5] + "tpost.npy")):
+                # flow fields CTurbSSTSolver::Postprocessing reads (rho, laminar viscosity, strain magnitude), kept even for lean fixtures
+                aux = np.load(os.path.join(out, k[:-1] + "aux.npy"))
+                arrs[k[:-5] + "tpost_flow"] = np.ascontiguousarray(np.stack([a[:, 4], aux[:, 2], aux[:, 5]], axis=1))
+            if lean and k.split("_", 2)[-1] in ("out_V", "out_aux"):
+                continue
             if k.endswith("prev_V"):
                 a = np.ascontiguousarray(a[:, :1])
             arrs[k] = a

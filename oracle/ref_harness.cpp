@@ -137,6 +137,23 @@ static void dump_turb(Ctx& c, const std::string& name) {
   }
   dump_f64(name, T, {c.nPoint, 6});
 }
+static void dump_turb_post(Ctx& c, const std::string& name) {
+  // state of CTurbSSTSolver right after its iteration, i.e. after CTurbSSTSolver::Postprocessing (solver_direct_turbulent.cpp:2953):
+  // columns k, omega, wall distance, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k
+  std::vector<double> T(c.nPoint * 12, 0.0);
+  if (c.rans) {
+    CSolver* ts = c.sol[TURB_SOL];
+    for (unsigned long p = 0; p < c.nPoint; ++p) {
+      CVariable* n = ts->node[p];
+      double* t = &T[p * 12];
+      t[0] = n->GetSolution(0); t[1] = n->GetSolution(1); t[2] = c.geo->node[p]->GetWall_Distance();
+      t[3] = n->GetF1blending(); t[4] = n->GetF2blending(); t[5] = n->GetCrossDiff(); t[6] = n->GetmuT();
+      t[7] = n->GetGradient()[0][0]; t[8] = n->GetGradient()[0][1]; t[9] = n->GetGradient()[1][0]; t[10] = n->GetGradient()[1][1];
+      t[11] = n->Get_Sigmak();
+    }
+  }
+  dump_f64(name, T, {c.nPoint, 12});
+}
 static void dump_dt(Ctx& c, const std::string& name) {
   std::vector<double> D(c.nPoint * 3, 0.0);
   for (unsigned long p = 0; p < c.nPointDomain; ++p) {
@@ -472,6 +489,7 @@ int main(int argc, char** argv) {
       drv->integration_container[ZONE_0][TURB_SOL]->SingleGrid_Iteration(drv->geometry_container, drv->solver_container,
                                                                          drv->numerics_container, drv->config_container,
                                                                          RUNTIME_TURB_SYS, it, ZONE_0);
+      if (dmp) dump_turb_post(c, tag(it, 0, "tpost"));   // flow state at this point: the out_ dump above
     }
     double r0 = log10(c.flow->GetRes_RMS(0)), r3 = log10(c.flow->GetRes_RMS(nDim + 1));
     printf("HARNESS it %lu  Res[Rho] %.6f  Res[RhoE] %.6f\n", it, r0, r3);

@@ -196,6 +196,14 @@ class Oracle:
     def set_temperature(self, T):
         T = np.ascontiguousarray(T, dtype=np.float64); self.lib.rxo_set_temperature(self.ctx, _p(T))
 
+    def turb_postprocess(self, kw, dist, flow3=None, sigma_k=0.85):
+        """rxo_turb_postprocess: [nPoint][12] = k, omega, dist, F1, F2, CDkw, muT, grad k, grad omega, sigma_k."""
+        kw = np.ascontiguousarray(kw, dtype=np.float64); dist = np.ascontiguousarray(dist, dtype=np.float64)
+        out = np.empty((kw.shape[0], 12))
+        f3 = np.ascontiguousarray(flow3, dtype=np.float64) if flow3 is not None else None
+        self.lib.rxo_turb_postprocess(self.ctx, _p(kw), _p(dist), _p(f3) if f3 is not None else None, C.c_double(sigma_k), _p(out))
+        return out
+
     def set_turbulence(self, t):
         t = np.ascontiguousarray(t, dtype=np.float64); self.lib.rxo_set_turbulence(self.ctx, _p(t))
 

@@ -79,3 +79,23 @@ def test_bicgstab_restatement_zero_rhs_and_identity():
     rhs = np.arange(1.0, n + 1)
     lib.rxo_bicgstab(n, P(A), P(rhs), P(x), C.byref(it))
     assert it.value == 1 and np.allclose(x, rhs / 2.0, rtol=1e-15)
+
+
+TPOST_COLS = ["k", "omega", "dist", "F1", "F2", "CDkw", "muT", "dk/dx", "dk/dy", "domega/dx", "domega/dy", "sigma_k"]
+
+
+@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped", "jet_rans_perturbed"])
+def test_oracle_turbulence_postprocessing_matches_reference(name):
+    """SURVEY.md 8(f) rank 1, first slice: CTurbSSTSolver::Postprocessing (gradient of k and omega, blending functions, eddy
+    viscosity) restated in rxo_turb_postprocess against the reference's own turbulence solver state after its iteration
+    (`tpost` dump; flow inputs = the reference's rho, laminar viscosity and strain magnitude, `tpost_flow`)."""
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    key = sorted(k for k in case.arr if k.endswith("_tpost"))[-1]
+    ref = case[key]
+    o = Oracle(case)
+    out = o.turb_postprocess(ref[:, 0:2], ref[:, 2], case[key + "_flow"], sigma_k=float(ref[0, 11]))
+    nD = case.nPointDomain
+    for c, nm in enumerate(TPOST_COLS):
+        scale = np.abs(ref[:nD, c]).max()
+        err = np.abs(out[:nD, c] - ref[:nD, c]).max() / (scale if scale > 0 else 1.0)
+        assert err <= TOL, "%s column %s: %.3e" % (name, nm, err)
