@@ -217,6 +217,107 @@ def bench_source(a, pk, chem, rank, world, local, dev, K, W):
         dist.destroy_process_group()
 
 
+def bench_turbpost(a, pk, chem, rank, world, local, dev, K, W):
+    """First slice of SURVEY.md 8(f) rank 1: CTurbSSTSolver::Postprocessing on the device (rx_turb_postprocess) over the points of
+    the bench mesh (every rank its own 1415 x 1415 strip-sized channel; no exchange is timed: one partition per rank).
+    value: device-timed passes of the two kernels on resident (k, omega); e2e: the host-buffer call — H2D of (k, omega),
+    kernels, D2H of the twelve fields (rx_get_turbulence)."""
+    import torch
+    import torch.distributed as dist
+    opts = pk.default_opts(rans=True, cfl=0.1)
+    mesh = pk.channel_mesh(a.nx, a.ny)
+    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345 + rank, rans=True)
+    solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
+    solver.SetSolution(U0); solver.SetTemperature(T0); solver.SetTurbulence(turb)
+    solver.Preprocessing(1, True, count_nonphysical=False)
+    xy = np.asarray(mesh["coord"]); x, y = xy[:, 0], xy[:, 1]
+    kw = np.ascontiguousarray(np.stack([1.0 + 0.5 * np.sin(40.0 * x) * np.cos(90.0 * y), 2.0e3 * (1.0 + 0.3 * np.cos(25.0 * x + 60.0 * y))], axis=1))
+    wall = np.minimum(y - y.min(), y.max() - y) + 1e-6
+    solver.SetWall_Distance(wall)
+    n = solver.nPoint
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    solver.TurbPostprocessing(kw)
+    for _ in range(max(W, 3)):
+        solver.TurbPostprocessing(None)     # (k, omega) resident
+    l0 = solver.LaunchCount()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        solver.TurbPostprocessing(None)
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1) / K
+    launches = solver.LaunchCount() - l0
+    solver.TurbPostprocessing(kw); out = solver.GetTurbulence()
+    if not np.all(np.isfinite(out)):
+        raise SystemExit("bench.py: non-finite turbulence fields")
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        solver.TurbPostprocessing(kw); out = solver.GetTurbulence()
+    barrier()
+    ms_e2e = 1e3 * (time.perf_counter() - t0) / K
+    clocks = sampler.stop()
+    kt = {"k_turb_gradient_ls": solver.KernelTime(8, 5), "k_turb_blend": solver.KernelTime(9, 5)}
+    tt = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_dev, ms_e2e = float(tt[0]), float(tt[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    # compulsory bytes per point: gradient kernel k, omega, x, y (32) + neighbour CSR (4 + 6 * 4) + 4 gradient words out (32);
+    # blending kernel rho, mu, strain, k, omega, dist (48) + 4 gradient words (32) + 5 + 6 words out (88)
+    bytes_per_point = 32.0 + 28.0 + 32.0 + 48.0 + 32.0 + 88.0
+    ach = bytes_per_point * n / (ms_dev * 1e-3) / 1e9
+    line = {"metric": "turbulence-postprocessing point updates/s", "value": world * n / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K,
+            "warmup": max(W, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "SST Postprocessing (gradients of k and omega by weighted least squares, blending functions, eddy viscosity) over the points of the synthetic triangulated channel",
+                       "points_per_gpu": int(n), "cache": "fields %.2f GB per GPU, larger than L2" % (n * 8 * 30 / 1e9)},
+            "e2e": {"value": world * n / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": int(n * 16), "d2h_bytes_per_step": int(n * 96)},
+            "gpu_launches": int(launches), "clocks": clocks, "kernel_ms": kt,
+            "roofline": {"kernel": "k_turb_gradient_ls + k_turb_blend", "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
+                         "traffic": None, "bytes_per_point": bytes_per_point,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback of B200_PROFILING.md"}}
+    if world == 1 and not a.no_cpu_baseline:
+        try:   # the CPU restatement (oracle/rx_oracle.cpp: rxo_turb_postprocess, one core) on a smaller mesh of the same kind
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import rxcase
+            ms = pk.channel_mesh(501, 501)
+            Us, Ts, tbs = pk.synthetic_state(ms, chem, seed=12345, rans=True)
+            o = rxcase.Oracle.from_mesh(ms, chem, opts)
+            o.set_solution(Us); o.set_temperature(Ts); o.set_turbulence(tbs); o.preprocess(1, output=True)
+            xs = np.asarray(ms["coord"]); kws = np.ascontiguousarray(np.stack([1.0 + 0.5 * np.sin(40.0 * xs[:, 0]), 2.0e3 + 0.0 * xs[:, 0]], axis=1))
+            ds = np.minimum(xs[:, 1] - xs[:, 1].min(), xs[:, 1].max() - xs[:, 1]) + 1e-6
+            o.turb_postprocess(kws, ds)
+            t0 = time.perf_counter(); reps = 0
+            while time.perf_counter() - t0 < 10.0:
+                o.turb_postprocess(kws, ds); reps += 1
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": reps * kws.shape[0] / dt, "unit": "updates/s", "cores": 1, "kind": "port",
+                                    "sample": "%d passes of the CPU restatement (oracle/rx_oracle.cpp: rxo_turb_postprocess) over a 501 x 501 channel, one core" % reps}
+        except Exception as ex:   # the oracle is test infrastructure: its absence must not hide the GPU numbers
+            line["cpu_baseline"] = {"value": None, "unit": "updates/s", "cores": 0, "kind": "port", "sample": "unavailable: %s" % ex}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -226,9 +327,10 @@ def main():
     ap.add_argument("--nx", type=int, default=1415)
     ap.add_argument("--ny", type=int, default=1415)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source"],
+    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source", "turbpost"],
                     help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share); "
-                         "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3])")
+                         "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3]); "
+                         "turbpost = SST Postprocessing on the device (first slice of SURVEY.md 8(f) rank 1)")
     ap.add_argument("--points", type=int, default=64_000_000)
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -241,7 +343,7 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        if rans or a.workload == "source":
+        if rans or a.workload in ("source", "turbpost"):
             print(json.dumps({"impl": "reference", "unavailable": "the reference arm is prepared for the laminar bench workload (configs[1]) only"}))
             return
         r = run_reference(K, W)
@@ -271,6 +373,8 @@ def main():
     chem = pk.load_mechanism()
     if a.workload == "source":
         return bench_source(a, pk, chem, rank, world, local, dev, K, W)
+    if a.workload == "turbpost":
+        return bench_turbpost(a, pk, chem, rank, world, local, dev, K, W)
     opts = pk.default_opts(rans=rans, cfl=0.1)
     nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
     if world > 1:

@@ -47,7 +47,7 @@ struct rx_ctx {
   bool orderEdges = true;           // viscous kernel processes the edges grouped by their last iteration count (rx_order.cuh); default: laminar on, RANS off; env RX_VISC_ORDER=0/1 forces
   int* eOrderBuf = nullptr; int nOrdTiles = 0;
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
-  bool haveWallDist = false;
+  bool haveWallDist = false; double sigmaK = 0.85;
   bool viscQuad = false;            // A/B hook (env RX_VISC_QUAD=1): four-lanes-per-edge laminar viscous kernel (rx_visc_quad.cuh)
   bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
@@ -388,14 +388,14 @@ int rx_set_wall_distance(rx_ctx* c, const double* dist) {
 int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stage) {
   if (!c->tpost) { c->err = "rx_turb_postprocess: not a RANS context"; return RX_ERR_ARG; }
   if (!c->haveWallDist) { c->err = "rx_turb_postprocess: rx_set_wall_distance has not been called"; return RX_ERR_ARG; }
-  if (stage < 0 || stage > 2 || (stage != 2 && !kOmega)) { c->err = "rx_turb_postprocess: bad stage / missing (k, omega)"; return RX_ERR_ARG; }
+  if (stage < 0 || stage > 2) { c->err = "rx_turb_postprocess: bad stage"; return RX_ERR_ARG; }
   if (!c->o.leastSquares) { c->err = "rx_turb_postprocess: only the WEIGHTED_LEAST_SQUARES gradient of (k, omega) is built"; return RX_ERR_UNSUPPORTED; }
   const Dev& d = c->d;
   if (stage != 2) {
-    const int rc = upload_aos(c, kOmega, c->tpost, 2);
-    if (rc) return rc;
+    if (kOmega) { const int rc = upload_aos(c, kOmega, c->tpost, 2); if (rc) return rc; }   // NULL: the (k, omega) of the previous call
     k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++;
   }
+  c->sigmaK = sigmaK;
   if (stage != 1) { k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost, sigmaK); c->launches++; }
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -644,6 +644,10 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
         case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
                 else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
         case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
+        case 8: if (!c->tpost) { c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
+                k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost); break;
+        case 9: if (!c->tpost) { c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
+                k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost, c->sigmaK); break;
         case 6: k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial, nullptr, nullptr); break;
         default: cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: unknown kernel id"; return RX_ERR_ARG;
       }

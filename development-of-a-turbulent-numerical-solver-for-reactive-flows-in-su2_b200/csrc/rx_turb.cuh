@@ -37,12 +37,22 @@ __global__ void __launch_bounds__(128) k_turb_gradient_ls(const Dev d, double* _
     weight += dx * dx;
     weight += dy * dy;
     if (weight != 0.0) {
-      r11 += dx * dx / weight;
-      r12 += dx * dy / weight;
-      r22 += dy * dy / weight;
       const double dk = tp[TP_K * np + q] - ki, dw = tp[TP_W * np + q] - wi;
-      C[0][0] += dx * dk / weight; C[0][1] += dy * dk / weight;
-      C[1][0] += dx * dw / weight; C[1][1] += dy * dw / weight;
+      // the seven quotients share the divisor: one refined reciprocal, nvcc's own fast-path sequence per quotient and its
+      // validity test ORed into one flag (rx_fdiv.cuh); the plain divisions are repeated if the flag comes up — same bits
+      const double num[7] = {dx * dx, dx * dy, dy * dy, dx * dk, dy * dk, dx * dw, dy * dw};
+      const Recip rw = frecip(weight);
+      bool bad = false;
+      double qv[7];
+#pragma unroll
+      for (int m = 0; m < 7; ++m) qv[m] = fdiv(num[m], rw, bad);
+      if (bad) {
+#pragma unroll
+        for (int m = 0; m < 7; ++m) qv[m] = num[m] / weight;
+      }
+      r11 += qv[0]; r12 += qv[1]; r22 += qv[2];
+      C[0][0] += qv[3]; C[0][1] += qv[4];
+      C[1][0] += qv[5]; C[1][1] += qv[6];
     }
   }
   if (r11 >= 0.0) r11 = sqrt(r11); else r11 = 0.0;

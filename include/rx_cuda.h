@@ -107,7 +107,7 @@ int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k
  * partitioned run exchanges the gradients of its halo points (rx_halo_pack/unpack with what = 3, Set_MPI_Solution_Gradient
  * solver_direct_turbulent.cpp:227). */
 int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
-int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; may be NULL for stage 2 */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
+int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the (k, omega) uploaded by the previous call */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
 int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);
 int rx_get_solution(rx_ctx*, double* U);
 int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */
