@@ -732,6 +732,29 @@ int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int
   return rc;
 }
 
+// CPhysicalGeometry::ComputeWall_Distance for host arrays (no context needed): dist[p] = distance to the nearest wall node
+int rx_wall_distance(int64_t nPoint, const double* xy, int64_t nWall, const double* wallXy, double* dist, int device) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_error = "rx_wall_distance: no CUDA device (no CPU path)"; return RX_ERR_NO_DEVICE; }
+  if (nPoint < 0 || nWall < 0 || !xy || !dist || (nWall > 0 && !wallXy)) { g_create_error = "rx_wall_distance: bad arguments"; return RX_ERR_ARG; }
+  if (nPoint == 0) return RX_OK;
+  if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "rx_wall_distance: cudaSetDevice failed"; return RX_ERR_CUDA; }
+  double *dXy = nullptr, *dW = nullptr, *dD = nullptr;
+  int rc = RX_OK;
+  if (cudaMalloc(&dXy, (size_t)nPoint * 2 * sizeof(double)) != cudaSuccess || cudaMalloc(&dD, (size_t)nPoint * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&dW, (size_t)std::max<int64_t>(nWall, 1) * 2 * sizeof(double)) != cudaSuccess) rc = RX_ERR_CUDA;
+  if (rc == RX_OK) {
+    cudaMemcpy(dXy, xy, (size_t)nPoint * 2 * sizeof(double), cudaMemcpyHostToDevice);
+    if (nWall > 0) cudaMemcpy(dW, wallXy, (size_t)nWall * 2 * sizeof(double), cudaMemcpyHostToDevice);
+    k_wall_distance<<<nblk(nPoint, 256), 256>>>((long long)nPoint, dXy, (long long)nWall, dW, dD);
+    if (cudaMemcpy(dist, dD, (size_t)nPoint * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+      g_create_error = "rx_wall_distance: kernel or copy failed"; rc = RX_ERR_CUDA;
+    }
+  } else g_create_error = "rx_wall_distance: out of device memory";
+  cudaFree(dXy); cudaFree(dW); cudaFree(dD);
+  return rc;
+}
+
 int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : 4; }   // 2: limiter, 3: grad k, grad omega
 static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np; }
 int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {

@@ -602,4 +602,31 @@ __global__ void k_unpack(double* __restrict__ soa, long long stride, int nv, lon
   soa[v * stride + pts[k]] = buf[t];
 }
 
+// ---- wall distance (CPhysicalGeometry::ComputeWall_Distance, geometry_structure.cpp:8990-9060): distance of every point to the
+// nearest NODE of the no-slip markers.  The reference searches an alternating digital tree; here every point scans the wall
+// nodes, staged through shared memory in tiles (nWall is O(sqrt(nPoint)) in 2-D): the minimum of the same squared distances.
+constexpr int WD_TILE = 1024;
+__global__ void __launch_bounds__(256) k_wall_distance(long long nPoint, const double* __restrict__ xy, long long nWall,
+                                                       const double* __restrict__ wall, double* __restrict__ dist) {
+  __shared__ double wx[WD_TILE], wy[WD_TILE];
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const bool in = p < nPoint;
+  const double x = in ? xy[2 * p] : 0.0, y = in ? xy[2 * p + 1] : 0.0;
+  double best = CUDART_INF;
+  for (long long w0 = 0; w0 < nWall; w0 += WD_TILE) {
+    const int n = (int)min((long long)WD_TILE, nWall - w0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) { wx[k] = wall[2 * (w0 + k)]; wy[k] = wall[2 * (w0 + k) + 1]; }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+      const double dx = x - wx[k], dy = y - wy[k];
+      double d2 = 0.0;
+      d2 += dx * dx;
+      d2 += dy * dy;
+      best = d2 < best ? d2 : best;
+    }
+  }
+  if (in) dist[p] = nWall > 0 ? sqrt(best) : 0.0;
+}
+
 }  // namespace rx

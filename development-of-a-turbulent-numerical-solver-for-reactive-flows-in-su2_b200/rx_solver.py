@@ -76,7 +76,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
-           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence"]
+           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance"]
 
 _lib = None
 

@@ -106,6 +106,8 @@ int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k
  * stage: 0 = all of it (single partition); 1 = upload + gradients only, 2 = blending + muT only — between the two a
  * partitioned run exchanges the gradients of its halo points (rx_halo_pack/unpack with what = 3, Set_MPI_Solution_Gradient
  * solver_direct_turbulent.cpp:227). */
+int rx_wall_distance(int64_t nPoint, const double* xy /* [nPoint][2] */, int64_t nWall, const double* wallXy /* [nWall][2]: nodes of the HEAT_FLUX / ISOTHERMAL markers */,
+                     double* dist /* [nPoint] */, int device);   /* CPhysicalGeometry::ComputeWall_Distance geometry_structure.cpp:8990 (nearest wall NODE), host arrays, no context */
 int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
 int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the (k, omega) uploaded by the previous call */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
 int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);

@@ -1,0 +1,149 @@
+"""Geometry preprocessing without the reference (package geometry.py + rx_wall_distance): from the content
+of an SU2 mesh file to the flat dual mesh, in the reference's own numbering.  Oracle: the geometry the reference itself built
+from the same files (`geo_*` arrays of the golden fixtures, exported by oracle/ref_harness.cpp) — every integer array must be
+identical, every floating-point array bit-equal."""
+import importlib
+import json
+
+import numpy as np
+import pytest
+
+from rxcase import GOLDEN, load_package
+
+
+def _geo():
+    pk = load_package()
+    return pk, importlib.import_module(pk.__name__ + ".geometry")
+
+
+def _jet_su2():
+    z = np.load("%s/jet_mesh_su2.npz" % GOLDEN)
+    tags = [str(t) for t in z["marker_tags"]]
+    return dict(coord=z["coord"], etype=z["etype"].astype(np.int64), elems=z["elems"].astype(np.int64),
+                markers=[(t, z["marker%d" % k].astype(np.int64)) for k, t in enumerate(tags)])
+
+
+def _compare(mesh, z, tags):
+    np.testing.assert_array_equal(mesh["globalIndex"], z["geo_global_index"])      # SetRCM_Ordering
+    np.testing.assert_array_equal(mesh["coord"], z["geo_coord"])
+    np.testing.assert_array_equal(mesh["nbPtr"], z["geo_nb_ptr"])                  # SetPoint_Connectivity
+    np.testing.assert_array_equal(mesh["nbPoint"], z["geo_nb_point"])
+    np.testing.assert_array_equal(mesh["edgeNodes"], z["geo_edge_nodes"])          # SetEdges
+    np.testing.assert_array_equal(mesh["edgeNormal"], z["geo_edge_normal"])        # SetControlVolume, bit for bit
+    np.testing.assert_array_equal(mesh["volume"], z["geo_volume"])
+    for k, tag in enumerate(tags):
+        m = [q for q in mesh["markers"] if q["tag"] == tag][0]
+        np.testing.assert_array_equal(m["node"], z["geo_marker%d_node" % k])                      # SetVertex
+        np.testing.assert_array_equal(m["normal"], z["geo_marker%d_normal" % k])                  # SetBoundControlVolume
+        np.testing.assert_array_equal(m["normalNeighbor"], z["geo_marker%d_normal_neighbor" % k])  # FindNormal_Neighbor
+
+
+def test_quadrilateral_jet_mesh_reproduces_reference_geometry():
+    pk, geo = _geo()
+    z = np.load("%s/jet_rans_shipped.npz" % GOLDEN)
+    tags = [m["tag"] for m in json.loads(bytes(z["meta_json"]).decode())["markers"]]
+    mesh = geo.su2_dual_mesh(_jet_su2())
+    assert mesh["nEdge"] == 17810 and mesh["nPoint"] == 9000
+    _compare(mesh, z, tags)
+
+
+def test_triangulated_channel_reproduces_reference_geometry():
+    """The 41 x 21 channel of the channel_* golden cases (oracle/make_golden.py: write_channel_su2), triangles."""
+    pk, geo = _geo()
+    mm = importlib.import_module(pk.__name__ + ".mesh")
+    z = np.load("%s/channel_lam_rk.npz" % GOLDEN)
+    tags = [m["tag"] for m in json.loads(bytes(z["meta_json"]).decode())["markers"]]
+    nx, ny = 41, 21
+    tri = mm.channel_triangles(nx, ny)
+    su2 = dict(coord=mm.channel_points(nx, ny, stretch=1.5), etype=np.full(tri.shape[0], geo.TRIANGLE, dtype=np.int64),
+               elems=np.concatenate([tri, np.full((tri.shape[0], 1), -1, dtype=np.int64)], axis=1),
+               markers=[(t, s) for t, s in mm.channel_boundaries(nx, ny)])
+    assert set(tags) == {t for t, _ in su2["markers"]}
+    mesh = geo.su2_dual_mesh(su2)
+    _compare(mesh, z, tags)
+
+
+def test_su2_file_round_trip(tmp_path):
+    pk, geo = _geo()
+    su2 = _jet_su2()
+    path = str(tmp_path / "jet.su2")
+    geo.write_su2(path, su2)
+    back = geo.read_su2(path)
+    np.testing.assert_array_equal(back["coord"], su2["coord"])
+    np.testing.assert_array_equal(back["etype"], su2["etype"])
+    np.testing.assert_array_equal(back["elems"], su2["elems"])
+    assert [t for t, _ in back["markers"]] == [t for t, _ in su2["markers"]]
+    for (_, a), (_, b) in zip(back["markers"], su2["markers"]):
+        np.testing.assert_array_equal(a, b)
+
+
+def test_orientation_is_repaired():
+    """Clockwise elements and inward boundary lines come out as the reference leaves them (Check_*_Orientation)."""
+    pk, geo = _geo()
+    su2 = _jet_su2()
+    want = geo.su2_dual_mesh(su2)
+    bad = dict(su2)
+    el = su2["elems"].copy(); el[::3, 1], el[::3, 3] = su2["elems"][::3, 3], su2["elems"][::3, 1]     # every third quad clockwise
+    bad["elems"] = el
+    bad["markers"] = [(t, s[:, ::-1].copy() if k % 2 else s) for k, (t, s) in enumerate(su2["markers"])]
+    got = geo.su2_dual_mesh(bad)
+    # the numbering may differ (neighbour lists are formed before the orientation check, as in the reference); the geometry not
+    c, el, nn = got["coord"], got["elems"], np.where(got["etype"] == geo.TRIANGLE, 3, 4)
+    a = c[el[:, 1]] - c[el[:, 0]]; b2 = c[el[:, 2]] - c[el[:, 0]]
+    assert (a[:, 0] * b2[:, 1] - a[:, 1] * b2[:, 0] > 0).all()                       # every element counter-clockwise
+
+    def edge_map(m):
+        g = m["globalIndex"]; out = {}
+        for (i, j), n in zip(m["edgeNodes"], m["edgeNormal"]):
+            gi, gj = int(g[i]), int(g[j])
+            out[(min(gi, gj), max(gi, gj))] = n if gi < gj else -n
+        return out
+    A, B = edge_map(got), edge_map(want)
+    assert A.keys() == B.keys()
+    assert max(np.abs(A[k] - B[k]).max() for k in A) <= 1e-18
+    vg = np.empty(got["nPoint"]); vg[got["globalIndex"]] = got["volume"]
+    vw = np.empty(want["nPoint"]); vw[want["globalIndex"]] = want["volume"]
+    np.testing.assert_allclose(vg, vw, rtol=1e-14)
+    for ma, mb in zip(got["markers"], want["markers"]):                               # vertex normals point out of the domain again
+        na = {int(got["globalIndex"][p]): n for p, n in zip(ma["node"], ma["normal"])}
+        nb = {int(want["globalIndex"][p]): n for p, n in zip(mb["node"], mb["normal"])}
+        assert na.keys() == nb.keys()
+        assert max(np.abs(na[k] - nb[k]).max() for k in na) <= 1e-18
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,walls", [("jet_rans_shipped", ["upper_wall", "lower_wall_pre", "lower_wall_post"]),
+                                        ("channel_rans", ["lower_wall", "upper_wall"])])
+def test_wall_distance_matches_reference(name, walls):
+    """rx_wall_distance against geometry->node[]->GetWall_Distance() of the reference (column 2 of the `tpost` dump)."""
+    pk, geo = _geo()
+    from rxcase import Case, mesh_dict
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    ref = case[sorted(k for k in case.arr if k.endswith("_tpost"))[-1]][:, 2]
+    mesh = mesh_dict(case)
+    meta = case.meta["markers"]
+    for m, mk in zip(mesh["markers"], meta):
+        m["tag"] = mk["tag"]
+    d = geo.wall_distance(mesh, walls)
+    np.testing.assert_allclose(d, ref, rtol=1e-15, atol=0)
+
+
+@pytest.mark.gpu
+def test_solver_runs_on_the_mesh_built_from_the_file():
+    """The dual mesh built here drives the CUDA path to the same residual norms as the geometry exported by the reference."""
+    pk, geo = _geo()
+    from rxcase import Case, chem_arrays, mesh_dict, opts_dict
+    case = Case("%s/jet_rans_perturbed.npz" % GOLDEN)
+    mine = geo.su2_dual_mesh(_jet_su2())
+    ref = mesh_dict(case)
+    for m, r in zip(mine["markers"], ref["markers"]):     # boundary data (kinds, states) from the case's cfg
+        for k, v in r.items():
+            if k not in ("node", "normal", "normalNeighbor"):
+                m[k] = v
+    it = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})[0]
+    out = []
+    for mesh in (mine, ref):
+        s = pk.CReactiveNSSolverGPU(mesh, chem_arrays(case), opts_dict(case))
+        s.SetSolution(case.stage(it, 0, "U0")); s.SetTemperature(case.stage(it, 0, "prev_V")[:, 0]); s.SetTurbulence(case.stage(it, 0, "turb"))
+        out.append(np.array(s.Iterate(it, [1.0])))
+    np.testing.assert_array_equal(out[0], out[1])
