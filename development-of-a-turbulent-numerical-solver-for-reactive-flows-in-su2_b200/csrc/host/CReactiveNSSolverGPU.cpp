@@ -25,6 +25,7 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
     : CReactiveNSSolver(geometry, config, iMesh) {
   using namespace Framework;
   mirror = env_int("SU2_RX_MIRROR", 1);
+  turbPost = env_int("SU2_RX_TURB_POST", 0) != 0;
   const unsigned short kind = config->GetKind_Solver();
   ransMode = (kind == REACTIVE_RANS);
   viscousMode = (kind == REACTIVE_RANS || kind == REACTIVE_NAVIER_STOKES);
@@ -162,6 +163,28 @@ void CReactiveNSSolverGPU::UploadTurbulence(CSolver** solver_container) {
   Check(rx_set_turbulence(ctx, bufT.data()), "rx_set_turbulence");
 }
 
+// The same fields formed on the device (rx_turb_postprocess = CTurbSSTSolver::Postprocessing, solver_direct_turbulent.cpp:2953-3015)
+// from the turbulence solution alone.  Called once per iteration, before the first Preprocessing of the flow step: the device
+// still holds the primitive state of the previous Output pass, which is the state the host-side Postprocessing saw.
+void CReactiveNSSolverGPU::DeviceTurbPostprocessing(CGeometry* geometry, CSolver** solver_container) {
+  CSolver* ts = solver_container[TURB_SOL];
+  if (!wallDistSet) {
+    std::vector<double> dist(nPoint);
+    for (unsigned long p = 0; p < nPoint; ++p) dist[p] = geometry->node[p]->GetWall_Distance();
+    Check(rx_set_wall_distance(ctx, dist.data()), "rx_set_wall_distance");
+    wallDistSet = true;
+  }
+  std::vector<double> kw((size_t)nPoint * 2), post((size_t)nPoint * 12);
+  for (unsigned long p = 0; p < nPoint; ++p) { kw[2 * p] = ts->node[p]->GetSolution(0); kw[2 * p + 1] = ts->node[p]->GetSolution(1); }
+  Check(rx_turb_postprocess(ctx, kw.data(), ts->node[0]->Get_Sigmak(), 0), "rx_turb_postprocess");
+  // host copy of the six fields, as UploadTurbulence leaves it: MirrorPrimitives hands the eddy viscosity to the flow variables
+  Check(rx_get_turbulence(ctx, post.data()), "rx_get_turbulence");
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    double* t = &bufT[p * 6]; const double* q = &post[p * 12];
+    t[0] = q[6]; t[1] = q[0]; t[2] = q[1]; t[3] = q[7]; t[4] = q[8]; t[5] = q[11];
+  }
+}
+
 void CReactiveNSSolverGPU::MirrorPrimitives() {
   Check(rx_get_primitive(ctx, bufV.data(), bufAux.data(), viscousMode ? bufGrad.data() : nullptr), "rx_get_primitive");
   for (unsigned long p = 0; p < nPoint; ++p) {
@@ -208,12 +231,19 @@ void CReactiveNSSolverGPU::MirrorTimeStep() {
 void CReactiveNSSolverGPU::Preprocessing(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh,
                                          unsigned short iRKStep, unsigned short RunTime_EqSystem, bool Output) {
   extIter = config->GetExtIter();
+  const bool wasDirty = hostDirty;   // a state set on the host (restart, initial condition) has no device primitives yet
   if (hostDirty) UploadState();
-  if (ransMode) UploadTurbulence(solver_container);
+  if (ransMode) {
+    const bool onDevice = turbPost && turbPostReady && !wasDirty;
+    if (!onDevice) UploadTurbulence(solver_container);
+    else if (iRKStep == 0 && !Output) DeviceTurbPostprocessing(geometry, solver_container);
+    // else: later RK stages and the Output pass keep the fields of stage 0 (the host copies are the same all iteration long)
+  }
   int64_t bad = 0;
   const bool count = (config->GetConsole_Output_Verb() == VERB_HIGH);
   Check(rx_preprocess(ctx, (int64_t)extIter, Output ? 1 : 0, count ? &bad : nullptr), "rx_preprocess");
   if (count && iMesh == MESH_0) config->SetNonphysical_Points((unsigned long)bad);
+  if (Output) turbPostReady = true;   // the device now holds the primitive state the next SST Postprocessing refers to
   if (mirror >= 1) MirrorPrimitives();
   if (mirror >= 2 && limiter && !Output) MirrorLimiter();
   if (mirror >= 2 && !Output) MirrorResidual();

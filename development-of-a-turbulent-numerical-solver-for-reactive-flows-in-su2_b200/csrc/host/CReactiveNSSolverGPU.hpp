@@ -56,6 +56,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void Check(int rc, const char* where);
   void UploadState();
   void UploadTurbulence(CSolver** solver_container);
+  void DeviceTurbPostprocessing(CGeometry* geometry, CSolver** solver_container);
   void MirrorPrimitives();
   void MirrorResidual();
   void MirrorLimiter();
@@ -66,6 +67,9 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   rx_ctx* ctx = nullptr;
   bool hostDirty = true, ransMode = false, viscousMode = true;
   int mirror = 1;
+  // SU2_RX_TURB_POST=1: the fields the flow path reads from the SST solver (muT, grad k, sigma_k) are formed on the device from
+  // (k, omega) by rx_turb_postprocess instead of being copied from CTurbSSTSolver::Postprocessing's results
+  bool turbPost = false, turbPostReady = false, wallDistSet = false;
   unsigned long extIter = 0;
   std::vector<double> bufU, bufV, bufAux, bufGrad, bufR, bufT;
 };

@@ -35,14 +35,19 @@ def _run(binary, d, out, nit, seed, env):
     return log.stdout
 
 
-@pytest.mark.parametrize("name", list(RUNS))
-def test_reference_driver_with_cuda_solver(name, tmp_path):
+# RANS cases once more with SU2_RX_TURB_POST=1: muT, grad k, sigma_k formed on the device by rx_turb_postprocess from (k, omega)
+# instead of copied from the host-side CTurbSSTSolver::Postprocessing
+PARAMS = [(n, False) for n in RUNS] + [("channel_rans", True), ("jet_rans_perturbed", True)]
+
+
+@pytest.mark.parametrize("name,turb_post", PARAMS)
+def test_reference_driver_with_cuda_solver(name, turb_post, tmp_path):
     d = os.path.join(CASES, name)
     if not (os.path.exists(HARNESS) and os.path.exists(HARNESS_CPU) and os.path.exists(os.path.join(d, "case.cfg"))):
         pytest.skip("oracle/_ref harnesses or the case directory are not in this snapshot (built by oracle/build_ref.sh where the reference tree is present)")
     nit, seed = RUNS[name]
     out_g, out_c = str(tmp_path / "gpu"), str(tmp_path / "cpu")
-    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2"))
+    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0"))
     assert "CReactiveNSSolverGPU" in txt
     _run(HARNESS_CPU, d, out_c, nit, seed, dict(os.environ))
     case = Case(os.path.join(GOLDEN, name + ".npz"))
