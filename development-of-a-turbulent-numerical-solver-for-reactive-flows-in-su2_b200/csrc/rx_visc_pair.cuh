@@ -695,19 +695,21 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
     double* const smPair = sm - l;
     const PairMat<NS> Mt{smPair};
     __syncwarp();   // the pair's words are about to be shared: both lanes are done with the solve's private words
-    Recip rM[NS];
+    // the divisors are the molar masses: their refined reciprocals were formed once at create (ChemC::rM, the value frecip()
+    // returns); the numerators' ranges are tested once for the whole operator (rx_fdiv.cuh: fdivu)
+    bool numOk = num_range(cc.Mtot);
 #pragma unroll
-    for (int c = 0; c < NS; ++c) rM[c] = frecip(cc.M[c]);
+    for (int s2 = 0; s2 < NS; ++s2) numOk = numOk && num_range(Ys[s2]) && num_range(Xs[s2]);
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
       const int r = k < 4 ? 2 * k + l : 8;
       const double Mr = cc.M[r];
-      const Recip rMr = frecip(Mr);
+      const Recip rMr{Mr, cc.rM[r]};
       double xom[NS];
-      bool bad = false;
-      double mom = fdiv(cc.Mtot, rMr, bad), yom = fdiv(Yr[0], rMr, bad);
+      const bool bad = !numOk;
+      double mom = fdivu(cc.Mtot, rMr), yom = fdivu(Yr[0], rMr);
 #pragma unroll
-      for (int c = 0; c < NS; ++c) xom[c] = fdiv(Xr[0], rM[c], bad);
+      for (int c = 0; c < NS; ++c) xom[c] = fdivu(Xr[0], Recip{cc.M[c], cc.rM[c]});
       if (bad) {
         mom = cc.Mtot / Mr; yom = Yr[0] / Mr;
 #pragma unroll
