@@ -186,11 +186,13 @@ __device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* 
       beta = sqrt(c0 * c0 + tailSq);
       if (c0 >= 0.0) beta = -beta;
       const double den = c0 - beta;
-      bool bad = false;
+      bool bad = !mid_range(den);   // operand ranges once per reflector instead of a validity test per quotient (rx_fdiv.cuh)
+#pragma unroll
+      for (int i = 1; i < NS; ++i) bad = bad || !num_range(vv[i]);
       const Recip rden = frecip(den);
       double vq[NS];
 #pragma unroll
-      for (int i = 1; i < NS; ++i) vq[i] = fdiv(vv[i], rden, bad);
+      for (int i = 1; i < NS; ++i) vq[i] = fdivu(vv[i], rden);
       if (bad) {
 #pragma unroll
         for (int i = 1; i < NS; ++i) vq[i] = vv[i] / den;
