@@ -389,11 +389,16 @@ int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stag
   if (!c->tpost) { c->err = "rx_turb_postprocess: not a RANS context"; return RX_ERR_ARG; }
   if (!c->haveWallDist) { c->err = "rx_turb_postprocess: rx_set_wall_distance has not been called"; return RX_ERR_ARG; }
   if (stage < 0 || stage > 2) { c->err = "rx_turb_postprocess: bad stage"; return RX_ERR_ARG; }
-  if (!c->o.leastSquares) { c->err = "rx_turb_postprocess: only the WEIGHTED_LEAST_SQUARES gradient of (k, omega) is built"; return RX_ERR_UNSUPPORTED; }
   const Dev& d = c->d;
   if (stage != 2) {
     if (kOmega) { const int rc = upload_aos(c, kOmega, c->tpost, 2); if (rc) return rc; }   // NULL: the (k, omega) of the previous call
-    k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++;
+    if (c->o.leastSquares) { k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++; }
+    else {
+      k_turb_gradient_gg_edges<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++;
+      for (const MarkerDev& m : c->markers)
+        if (m.nVertex) { k_turb_gradient_gg_boundary<<<nblk(m.nVertex, 64), 64, 0, c->stream>>>(d, m, c->tpost); c->launches++; }
+      k_turb_gradient_gg_finish<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost); c->launches++;
+    }
   }
   c->sigmaK = sigmaK;
   if (stage != 1) { k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost, sigmaK); c->launches++; }

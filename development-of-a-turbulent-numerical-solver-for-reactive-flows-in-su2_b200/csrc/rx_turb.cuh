@@ -2,6 +2,7 @@
 // (solver_direct_turbulent.cpp:2953-3015) leaves for the flow path — eddy viscosity, grad k, sigma_k — from the turbulence
 // solution (k, omega), the wall distance and the flow state already resident (rho, laminar viscosity, strain magnitude).
 // With it the host hands over 2 doubles per point and iteration instead of the 6 of rx_set_turbulence.
+//   k_turb_gradient_gg_* CSolver::SetSolution_Gradient_GG, solver_structure.cpp:519-579 (GREEN_GAUSS configurations)
 //   k_turb_gradient_ls   CSolver::SetSolution_Gradient_LS, solver_structure.cpp:580-722 (2-D branch, nVar = 2).  Its tests are
 //                        not those of the flow solver's own LS routine: weight != 0, r11 >= 0, |detR2| <= EPS.
 //   k_turb_blend         CTurbSSTVariable::SetBlendingFunc (variable_direct_turbulent.cpp: CDkw, F1, F2) and the eddy viscosity
@@ -75,6 +76,54 @@ __global__ void __launch_bounds__(128) k_turb_gradient_ls(const Dev d, double* _
     tp[(TP_GK + 2 * v) * np + p] = g0;
     tp[(TP_GK + 2 * v + 1) * np + p] = g1;
   }
+}
+
+// ---- CSolver::SetSolution_Gradient_GG (solver_structure.cpp:519-579) of (k, omega), owner-computes: a thread per owned point
+// adds the interior-edge terms 0.5 (s_i + s_j) n in ascending edge order (+ at the edge's first node, - at its second), the
+// marker kernels subtract s n_vertex in marker order, the last kernel divides by (volume + EPS) — the reference's order of sums.
+__global__ void __launch_bounds__(128) k_turb_gradient_gg_edges(const Dev d, double* __restrict__ tp) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPoint) return;
+  const long long np = d.np;
+  double g[4] = {0.0, 0.0, 0.0, 0.0};
+  if (p < d.nPointDomain) {
+    for (int k = d.incPtr[p]; k < d.incPtr[p + 1]; ++k) {
+      const int code = d.incEdge[k];
+      const bool first = code >= 0;
+      const long long e = first ? code : ~code;
+      const int i = d.ei[e], j = d.ej[e];
+      const double nx = d.enx[e], ny = d.eny[e];
+#pragma unroll
+      for (int v = 0; v < 2; ++v) {
+        const double avg = 0.5 * (tp[(TP_K + v) * np + i] + tp[(TP_K + v) * np + j]);
+        const double px = avg * nx, py = avg * ny;
+        g[2 * v] = first ? g[2 * v] + px : g[2 * v] - px;
+        g[2 * v + 1] = first ? g[2 * v + 1] + py : g[2 * v + 1] - py;
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) tp[(TP_GK + q) * np + p] = g[q];
+}
+__global__ void k_turb_gradient_gg_boundary(const Dev d, const MarkerDev m, double* __restrict__ tp) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int p = m.node[k];
+  if (p >= d.nPointDomain) return;
+  const long long np = d.np;
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    const double s = tp[(TP_K + v) * np + p];
+    tp[(TP_GK + 2 * v) * np + p] -= s * m.nx[k];
+    tp[(TP_GK + 2 * v + 1) * np + p] -= s * m.ny[k];
+  }
+}
+__global__ void __launch_bounds__(128) k_turb_gradient_gg_finish(const Dev d, double* __restrict__ tp) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  const double a = d.vol[p] + EPS;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) tp[(TP_GK + q) * d.np + p] = tp[(TP_GK + q) * d.np + p] / a;
 }
 
 // blending functions and eddy viscosity of every point (halo points included, as in the reference's loop over nPoint); fills

@@ -100,9 +100,10 @@ int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k
 /* SST Postprocessing on the device (first slice; csrc/rx_turb.cuh): replaces the host-side
  * CTurbSSTSolver::Postprocessing (solver_direct_turbulent.cpp:2953-3015) + rx_set_turbulence.  From the turbulence solution
  * (k, omega) and the wall distance (CGeometry::ComputeWall_Distance, geometry_structure.cpp:8990) it forms grad k, grad omega
- * (CSolver::SetSolution_Gradient_LS, solver_structure.cpp:580-722), CDkw, F1, F2 (CTurbSSTVariable::SetBlendingFunc) and
+ * (CSolver::SetSolution_Gradient_LS / _GG, solver_structure.cpp:580-722 / 519-579), CDkw, F1, F2 (CTurbSSTVariable::SetBlendingFunc) and
  * muT = min(max(rho k min(1/omega, a1/(S F2)), 0), 1) with rho, laminar viscosity and strain magnitude of the last rx_preprocess,
- * and leaves muT, k, omega, grad k, sigma_k where rx_set_turbulence would have put them.  RANS contexts with WLS gradients only.
+ * and leaves muT, k, omega, grad k, sigma_k where rx_set_turbulence would have put them.  RANS contexts; the gradient method is
+ * the context's (WLS, or Green-Gauss: SetSolution_Gradient_GG :519-579).
  * stage: 0 = all of it (single partition); 1 = upload + gradients only, 2 = blending + muT only — between the two a
  * partitioned run exchanges the gradients of its halo points (rx_halo_pack/unpack with what = 3, Set_MPI_Solution_Gradient
  * solver_direct_turbulent.cpp:227). */

@@ -147,6 +147,10 @@ SPECS = {
                            MARKER_EULER="( upper_wall, lower_wall )", RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE",
                            IGNITION="NO", TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )",
                            CFL_NUMBER="0.2"), 2, 1, 31, False),
+    # RANS + PaSR with GREEN_GAUSS gradients: the flow path's GG branch under the SST closure, and CSolver::SetSolution_Gradient_GG
+    # of (k, omega) for the turbulence postprocessing slice (tpost dump)
+    "channel_rans_gg": (dict(nx=41, ny=21, stretch=1.5),
+                        dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO", NUM_METHOD_GRAD="GREEN_GAUSS"), 2, 1, 37, True),
 }
 
 

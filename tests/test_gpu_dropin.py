@@ -17,7 +17,7 @@ HARNESS_CPU = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 # name -> (iterations, seed)   (oracle/make_golden.py SPECS)
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
-        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29)}
+        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37)}
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-11   # later iterations start from states that already differ by rounding (gradients amplify by 1/dx)
 # jet_rans_perturbed reaches 1.04e-12 in the mass group at iteration 0.  Traced: glibc's pow() is
@@ -37,7 +37,7 @@ def _run(binary, d, out, nit, seed, env):
 
 # RANS cases once more with SU2_RX_TURB_POST=1: muT, grad k, sigma_k formed on the device by rx_turb_postprocess from (k, omega)
 # instead of copied from the host-side CTurbSSTSolver::Postprocessing
-PARAMS = [(n, False) for n in RUNS] + [("channel_rans", True), ("jet_rans_perturbed", True)]
+PARAMS = [(n, False) for n in RUNS] + [("channel_rans", True), ("jet_rans_perturbed", True), ("channel_rans_gg", True)]
 
 
 @pytest.mark.parametrize("name,turb_post", PARAMS)

@@ -14,7 +14,7 @@ TOL = 1e-12
 WHAT_TURB_GRADIENT = 3
 
 
-@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped", "jet_rans_perturbed"])
+@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped", "jet_rans_perturbed", "channel_rans_gg"])
 def test_turbulence_postprocessing_matches_reference(name):
     case = Case("%s/%s.npz" % (GOLDEN, name))
     key = sorted(k for k in case.arr if k.endswith("_tpost"))[-1]

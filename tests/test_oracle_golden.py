@@ -13,7 +13,7 @@ import pytest
 
 from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 
-CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler"]
+CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler", "channel_rans_gg"]
 TOL = 1e-13
 
 
@@ -84,7 +84,7 @@ def test_bicgstab_restatement_zero_rhs_and_identity():
 TPOST_COLS = ["k", "omega", "dist", "F1", "F2", "CDkw", "muT", "dk/dx", "dk/dy", "domega/dx", "domega/dy", "sigma_k"]
 
 
-@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped", "jet_rans_perturbed"])
+@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped", "jet_rans_perturbed", "channel_rans_gg"])
 def test_oracle_turbulence_postprocessing_matches_reference(name):
     """SURVEY.md 8(f) rank 1, first slice: CTurbSSTSolver::Postprocessing (gradient of k and omega, blending functions, eddy
     viscosity) restated in rxo_turb_postprocess against the reference's own turbulence solver state after its iteration
