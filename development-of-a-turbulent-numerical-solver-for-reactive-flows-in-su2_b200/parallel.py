@@ -117,3 +117,11 @@ def distributed_iterate(solver, ex, ext_iter, rk_alpha, last_rms=False):
     if last_rms and rms is not None:
         rms = global_rms(rms, solver.nPoint, solver.nPointDomain, ex.device)
     return rms
+
+
+def distributed_turb_postprocess(solver, ex, k_omega, sigma_k=0.85):
+    """CTurbSSTSolver::Postprocessing on a partition: gradients of (k, omega) on the owned points, their halo values from the
+    owners (Set_MPI_Solution_Gradient, solver_direct_turbulent.cpp:227), then blending functions and eddy viscosity everywhere."""
+    solver.TurbPostprocessing(k_omega, sigma_k=sigma_k, stage=1)
+    ex.exchange(WHAT_TURB_GRADIENT)
+    solver.TurbPostprocessing(None, sigma_k=sigma_k, stage=2)

@@ -35,7 +35,7 @@ def _worker(rank, world, port, nxg, ny, out):
         gi, gj = plan["glob"]
         nP, nOwn = mesh["nPoint"], mesh["nPointDomain"]
         fields = {}
-        for what, nv in ((par.WHAT_SOLUTION, 13), (par.WHAT_GRADIENT, 26)):
+        for what, nv in ((par.WHAT_SOLUTION, 13), (par.WHAT_GRADIENT, 26), (par.WHAT_LIMITER, 4), (par.WHAT_TURB_GRADIENT, 4)):
             f = torch.full((nv, nP), float("nan"), dtype=torch.float64)
             for v in range(nv):
                 f[v, :nOwn] = torch.from_numpy(_field(gi[:nOwn], gj[:nOwn], v + 100 * what))
