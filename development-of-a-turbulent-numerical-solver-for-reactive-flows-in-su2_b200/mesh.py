@@ -42,7 +42,8 @@ def dual_mesh(coord, tri, boundaries, nPointDomain=None):
     """coord [nP,2], tri [nT,3], boundaries = list of (tag, line elements [nL,2]) -> flat mesh dict (see rx_cuda.h: rx_mesh)."""
     nP = coord.shape[0]
     x = coord[:, 0]; y = coord[:, 1]
-    # element CG: ((x0 + x1) + x2)/3  (CPrimalGrid::SetCG sums the nodes in order and divides by nNodes)
+    # element CG as ((x0 + x1) + x2)/3.  The reference adds x_n/3 node by node (CPrimalGrid::SetCoord_CG); geometry.su2_dual_mesh
+    # reproduces that bit for bit — this builder, used for the large synthetic meshes, is within one ulp of it.
     ecx = ((x[tri[:, 0]] + x[tri[:, 1]]) + x[tri[:, 2]]) / 3.0
     ecy = ((y[tri[:, 0]] + y[tri[:, 1]]) + y[tri[:, 2]]) / 3.0
     fa = np.concatenate([tri[:, 0], tri[:, 1], tri[:, 2]])
