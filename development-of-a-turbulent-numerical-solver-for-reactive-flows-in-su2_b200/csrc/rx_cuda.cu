@@ -385,6 +385,30 @@ int rx_set_wall_distance(rx_ctx* c, const double* dist) {
   if (rc == RX_OK) c->haveWallDist = true;
   return rc;
 }
+// wall distance of the context's own mesh, on the device: nodes of the ISOTHERMAL / HEAT_FLUX markers in marker order
+// (CPhysicalGeometry::ComputeWall_Distance :8990-9060).  Single-partition meshes: a partition sees only its own wall nodes.
+int rx_compute_wall_distance(rx_ctx* c) {
+  if (!c->tpost) { c->err = "rx_compute_wall_distance: not a RANS context"; return RX_ERR_ARG; }
+  const Dev& d = c->d;
+  long long nWall = 0;
+  for (const MarkerDev& m : c->markers) if (m.kind == 3 || m.kind == 4) nWall += m.nVertex;
+  int* wn = nullptr;
+  RX_CK(cudaMalloc(&wn, (size_t)std::max<long long>(nWall, 1) * sizeof(int)));
+  long long off = 0;
+  for (const MarkerDev& m : c->markers)
+    if ((m.kind == 3 || m.kind == 4) && m.nVertex) {
+      cudaMemcpyAsync(wn + off, m.node, (size_t)m.nVertex * sizeof(int), cudaMemcpyDeviceToDevice, c->stream);
+      off += m.nVertex;
+    }
+  k_wall_distance_ctx<<<nblk(d.nPoint, 256), 256, 0, c->stream>>>(d, nWall, wn, c->tpost + (size_t)TP_DIST * d.np);
+  c->launches++;
+  const cudaError_t e = cudaStreamSynchronize(c->stream);
+  cudaFree(wn);
+  RX_CK(e);
+  RX_CK(cudaGetLastError());
+  c->haveWallDist = true;
+  return RX_OK;
+}
 int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stage) {
   if (!c->tpost) { c->err = "rx_turb_postprocess: not a RANS context"; return RX_ERR_ARG; }
   if (!c->haveWallDist) { c->err = "rx_turb_postprocess: rx_set_wall_distance has not been called"; return RX_ERR_ARG; }

@@ -629,4 +629,27 @@ __global__ void __launch_bounds__(256) k_wall_distance(long long nPoint, const d
   if (in) dist[p] = nWall > 0 ? sqrt(best) : 0.0;
 }
 
+// the same for a context: coordinates as the SoA fields of Dev, wall nodes given by their point indices
+__global__ void __launch_bounds__(256) k_wall_distance_ctx(const Dev d, long long nWall, const int* __restrict__ wallNode, double* __restrict__ dist) {
+  __shared__ double wx[WD_TILE], wy[WD_TILE];
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const bool in = p < d.nPoint;
+  const double x = in ? d.x[p] : 0.0, y = in ? d.y[p] : 0.0;
+  double best = CUDART_INF;
+  for (long long w0 = 0; w0 < nWall; w0 += WD_TILE) {
+    const int n = (int)min((long long)WD_TILE, nWall - w0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) { const int q = wallNode[w0 + k]; wx[k] = d.x[q]; wy[k] = d.y[q]; }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+      const double dx = x - wx[k], dy = y - wy[k];
+      double d2 = 0.0;
+      d2 += dx * dx;
+      d2 += dy * dy;
+      best = d2 < best ? d2 : best;
+    }
+  }
+  if (in) dist[p] = nWall > 0 ? sqrt(best) : 0.0;
+}
+
 }  // namespace rx

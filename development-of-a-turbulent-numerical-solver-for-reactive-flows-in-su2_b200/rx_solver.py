@@ -76,7 +76,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
-           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance"]
+           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance"]
 
 _lib = None
 
@@ -256,6 +256,10 @@ class CReactiveNSSolverGPU:
     def SetWall_Distance(self, dist):
         """geometry->node[]->GetWall_Distance() of every point, for TurbPostprocessing."""
         self._ck(self.lib.rx_set_wall_distance(self.ctx, _d(_c(dist))))
+
+    def ComputeWall_Distance(self):
+        """CPhysicalGeometry::ComputeWall_Distance on the device, from the context's own isothermal / heat-flux markers."""
+        self._ck(self.lib.rx_compute_wall_distance(self.ctx))
 
     def TurbPostprocessing(self, kOmega=None, sigma_k=0.85, stage=0):
         """CTurbSSTSolver::Postprocessing on the device (rx_turb_postprocess): gradients of (k, omega), blending functions, eddy

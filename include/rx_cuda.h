@@ -110,6 +110,7 @@ int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k
 int rx_wall_distance(int64_t nPoint, const double* xy /* [nPoint][2] */, int64_t nWall, const double* wallXy /* [nWall][2]: nodes of the HEAT_FLUX / ISOTHERMAL markers */,
                      double* dist /* [nPoint] */, int device);   /* CPhysicalGeometry::ComputeWall_Distance geometry_structure.cpp:8990 (nearest wall NODE), host arrays, no context */
 int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
+int rx_compute_wall_distance(rx_ctx*);   /* the same from the context's own mesh, on the device: nearest node of its ISOTHERMAL / HEAT_FLUX markers (single-partition meshes) */
 int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the (k, omega) uploaded by the previous call */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
 int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);
 int rx_get_solution(rx_ctx*, double* U);

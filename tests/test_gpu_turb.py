@@ -96,3 +96,19 @@ def test_partitioned_turbulence_postprocessing_equals_single():
             scale = np.abs(want[:, c]).max()
             err = np.abs(got[n:, c] - want[glob[n:], c]).max() / scale
             assert err <= TOL, (TPOST_COLS[c], "halo", err)
+
+
+@pytest.mark.parametrize("name", ["channel_rans", "jet_rans_shipped"])
+def test_wall_distance_from_the_context_matches_reference(name):
+    """rx_compute_wall_distance (nearest node of the context's own isothermal / heat-flux markers, on the device) against the
+    reference's GetWall_Distance (column 2 of `tpost`)."""
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    ref = case[sorted(k for k in case.arr if k.endswith("_tpost"))[-1]]
+    s = gpu_solver(case)
+    s.ComputeWall_Distance()
+    drive(case, s, lambda k, a: None)
+    s.TurbPostprocessing(ref[:, 0:2], sigma_k=float(ref[0, 11]))
+    out = s.GetTurbulence()
+    s.close()
+    np.testing.assert_allclose(out[:, 2], ref[:, 2], rtol=1e-15, atol=0)
+    assert np.abs(out[:, 6] - ref[:, 6]).max() <= TOL * np.abs(ref[:, 6]).max()   # eddy viscosity with the device's own distances
