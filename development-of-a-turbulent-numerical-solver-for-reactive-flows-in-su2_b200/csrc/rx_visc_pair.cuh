@@ -314,8 +314,14 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
   const double T = 0.5 * (d.V[V_T * np + pi] + d.V[V_T * np + pj]);
   const double um = 0.5 * (d.V[V_VX * np + pi] + d.V[V_VX * np + pj]);
   const double vm = 0.5 * (d.V[(V_VX + 1) * np + pi] + d.V[(V_VX + 1) * np + pj]);
-  const double mu = 2.0 / (1.0 / d.mu[pi] + 1.0 / d.mu[pj]);
-  const double ktr = 2.0 / (1.0 / d.kap[pi] + 1.0 / d.kap[pj]);
+  double mu, ktr;   // harmonic means; the six quotients as two batches of independent fast-path divisions (rx_fdiv.cuh), same bits
+  {
+    const double a0 = d.mu[pi], a1 = d.mu[pj], b0 = d.kap[pi], b1 = d.kap[pj];
+    bool bad = false;
+    const double i0 = fdiv(1.0, a0, bad), i1 = fdiv(1.0, a1, bad), j0 = fdiv(1.0, b0, bad), j1 = fdiv(1.0, b1, bad);
+    mu = fdiv(2.0, i0 + i1, bad); ktr = fdiv(2.0, j0 + j1, bad);
+    if (bad) { mu = 2.0 / (1.0 / a0 + 1.0 / a1); ktr = 2.0 / (1.0 / b0 + 1.0 / b1); }
+  }
   double Ys[NS], Xs[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) Ys[s] = 0.5 * (d.V[(V_Y + s) * np + pi] + d.V[(V_Y + s) * np + pj]);
