@@ -103,7 +103,8 @@ def _cross_half(c, p1, p2, p3):
 
 
 def orient_elements(coord, etype, elems, boundaries):
-    """Counter-clockwise elements, boundary lines with the domain on their left (in place on copies); returns (elems, boundaries)."""
+    """Counter-clockwise elements, boundary lines with the domain on their left — their vertex normals then point into the domain,
+    SU2's convention (the BC routines negate them); returns (elems, boundaries)."""
     elems = elems.copy()
     tri = np.nonzero(etype == TRIANGLE)[0]
     if tri.size:

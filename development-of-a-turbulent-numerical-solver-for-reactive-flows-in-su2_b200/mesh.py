@@ -107,8 +107,8 @@ def dual_mesh(coord, tri, boundaries, nPointDomain=None):
 
 def channel_boundaries(nx, ny):
     j = np.arange(ny - 1); i = np.arange(nx - 1)
-    # line elements are oriented so that the vertex normal points out of the domain (SU2 re-orients boundary elements
-    # the same way: CPhysicalGeometry::Check_BoundElem_Orientation)
+    # line elements are oriented with the domain on their left, which is how CPhysicalGeometry::Check_BoundElem_Orientation leaves
+    # them; the vertex normals SetBoundControlVolume forms from them point INTO the domain (the BC routines negate them)
     return [("inlet", np.stack([(j + 1) * nx, j * nx], 1)),
             ("outlet", np.stack([j * nx + nx - 1, (j + 1) * nx + nx - 1], 1)),
             ("lower_wall", np.stack([i, i + 1], 1)),

@@ -104,7 +104,7 @@ def test_orientation_is_repaired():
     vg = np.empty(got["nPoint"]); vg[got["globalIndex"]] = got["volume"]
     vw = np.empty(want["nPoint"]); vw[want["globalIndex"]] = want["volume"]
     np.testing.assert_allclose(vg, vw, rtol=1e-14)
-    for ma, mb in zip(got["markers"], want["markers"]):                               # vertex normals point out of the domain again
+    for ma, mb in zip(got["markers"], want["markers"]):                               # vertex normals as the reference orients them (into the domain)
         na = {int(got["globalIndex"][p]): n for p, n in zip(ma["node"], ma["normal"])}
         nb = {int(want["globalIndex"][p]): n for p, n in zip(mb["node"], mb["normal"])}
         assert na.keys() == nb.keys()
@@ -147,3 +147,43 @@ def test_solver_runs_on_the_mesh_built_from_the_file():
         s.SetSolution(case.stage(it, 0, "U0")); s.SetTemperature(case.stage(it, 0, "prev_V")[:, 0]); s.SetTurbulence(case.stage(it, 0, "turb"))
         out.append(np.array(s.Iterate(it, [1.0])))
     np.testing.assert_array_equal(out[0], out[1])
+
+
+def test_mixed_triangle_quadrilateral_mesh_closes_every_control_volume():
+    """A mesh of quadrilaterals with every other one split into two triangles (given in mixed orientation): the dual control
+    volumes tile the domain and every one of them is closed — the outgoing edge normals around a point minus its (inward) boundary normals sum
+    to zero — which is the discrete property the residual loop relies on (a constant flux leaves no residual)."""
+    pk, geo = _geo()
+    nx, ny = 9, 7
+    xs = np.linspace(0.0, 2.0, nx) ** 1.3; ys = np.linspace(0.0, 1.0, ny) ** 0.8
+    X, Y = np.meshgrid(xs, ys)
+    coord = np.stack([X.ravel() + 0.01 * np.sin(7 * Y.ravel()), Y.ravel()], axis=1)
+    etype, elems = [], []
+    for j in range(ny - 1):
+        for i in range(nx - 1):
+            a = j * nx + i; b = a + 1; c = b + nx; d = a + nx
+            if (i + j) % 2 == 0:
+                etype.append(geo.QUADRILATERAL); elems.append([a, b, c, d] if (i % 3) else [a, d, c, b])     # some clockwise
+            else:
+                etype += [geo.TRIANGLE, geo.TRIANGLE]; elems += [[a, b, c, -1], [a, d, c, -1]]                # second one clockwise
+    i = np.arange(nx - 1); j = np.arange(ny - 1)
+    markers = [("bottom", np.stack([i + 1, i], 1)), ("right", np.stack([j * nx + nx - 1, (j + 1) * nx + nx - 1], 1)),
+               ("top", np.stack([(ny - 1) * nx + i, (ny - 1) * nx + i + 1], 1)), ("left", np.stack([j * nx, (j + 1) * nx], 1))]
+    su2 = dict(coord=coord, etype=np.array(etype, dtype=np.int64), elems=np.array(elems, dtype=np.int64), markers=markers)
+    for rcm in (True, False):
+        m = geo.su2_dual_mesh(su2, rcm=rcm)
+        # area of the domain from the boundary polygon (shoelace), in the file's numbering
+        ring = np.concatenate([np.arange(nx), np.arange(1, ny) * nx + nx - 1, (ny - 1) * nx + np.arange(nx - 2, -1, -1), np.arange(ny - 2, 0, -1) * nx])
+        px, py = coord[ring, 0], coord[ring, 1]
+        area = 0.5 * abs(np.dot(px, np.roll(py, -1)) - np.dot(py, np.roll(px, -1)))
+        assert abs(m["volume"].sum() - area) <= 1e-14 * area
+        assert (m["volume"] > 0).all()
+        close = np.zeros((m["nPoint"], 2))
+        np.add.at(close, m["edgeNodes"][:, 0], m["edgeNormal"]); np.add.at(close, m["edgeNodes"][:, 1], -m["edgeNormal"])
+        for mk in m["markers"]:
+            np.add.at(close, mk["node"], -mk["normal"])   # vertex normals point INTO the domain (the BC routines negate them, e.g. solver_direct_reactive.cpp BC_Inlet)
+        assert np.abs(close).max() <= 1e-15
+        assert m["nEdge"] == len({(min(a, b), max(a, b)) for a, b in m["edgeNodes"]})
+        # neighbour lists and edges describe the same graph
+        deg = np.diff(m["nbPtr"])
+        assert deg.sum() == 2 * m["nEdge"]
