@@ -804,3 +804,6 @@ int rx_halo_unpack(rx_ctx* c, int what, int64_t n, const int64_t* pts, const dou
 }
 
 }  // extern "C"
+
+// allocation-free residual norms over a static device scratch array (its own entry point; no existing path uses it)
+#include "rx_noalloc.cuh"

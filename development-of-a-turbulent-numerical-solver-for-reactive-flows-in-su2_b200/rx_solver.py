@@ -76,7 +76,8 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_residual_source", "rx_residual_all", "rx_kernel_time", "rx_bc", "rx_update_explicit", "rx_iterate", "rx_source_points", "rx_source_points_dev",
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
-           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance"]
+           "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
+           "rx_residual_rms_static"]
 
 _lib = None
 
@@ -137,6 +138,20 @@ def source_points(chem, T, rho, Y, vol, omegaTurb=None, rans=False, cMu=0.09, pa
     if rc != 0:
         raise RxError("rx_source_points failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
     return res
+
+
+STATIC_RMS_MAX_POINTS, STATIC_RMS_MAX_VARS = 4194304, 16   # include/rx_cuda.h: RX_STATIC_RMS_MAX_*
+
+
+def residual_rms_static(R_dev_ptr, nPointDomain, ld, nVar, nPointGlobal, rms_dev_ptr, device=0, stream=0):
+    """rx_residual_rms_static: residual norms of a device-resident SoA residual R_dev[nVar][ld] into rms_dev[nVar] without any
+    allocation (static device scratch; no counterpart in the reference, see include/rx_cuda.h).  Device pointers as integers
+    (e.g. torch tensor.data_ptr()); enqueued on `stream`, the host is not synchronised."""
+    L = load_library()
+    rc = L.rx_residual_rms_static(C.c_void_p(R_dev_ptr), C.c_int64(nPointDomain), C.c_int64(ld), int(nVar), C.c_int64(nPointGlobal),
+                                  C.c_void_p(rms_dev_ptr), int(device), C.c_void_p(stream))
+    if rc != 0:
+        raise RxError("rx_residual_rms_static failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
 
 
 class CReactiveNSSolverGPU:

@@ -184,6 +184,22 @@ int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, con
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t rx_launch_count(rx_ctx*);
 
+/* Allocation-free residual norms.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same
+ * reduction rx_update_explicit performs for CSolver::SetResidual_RMS — rms[v] = max(EPS^2, sqrt(sum_{p < nPointDomain}
+ * R[v][p]^2 / nPointGlobal)), same partial sums in the same order, so bit-equal to that entry point for the same LinSysRes —
+ * but context-free and with its scratch (per-block partial sums) in a file-scope static __device__ array of fixed size
+ * (4 MiB per GPU that loads the library, held until exit) instead of rx_ctx memory.  It calls no cudaMalloc / cudaFree / allocating
+ * routine.  Inputs and outputs are the caller's DEVICE pointers: R_dev[nVar][ld] structure-of-arrays (variable v of point p at
+ * v * ld + p, ld >= nPointDomain), rms_dev[nVar]; work is enqueued on cudaStream of `device` and the host is not synchronised.
+ * Limits: nPointDomain <= RX_STATIC_RMS_MAX_POINTS and nVar <= RX_STATIC_RMS_MAX_VARS, else RX_ERR_UNSUPPORTED with the
+ * limits in rx_last_error(NULL).  All calls on a GPU share the one array, which keeps the last call's contents (each call
+ * writes every slot it reads, nothing needs clearing): calls that overlap on the same GPU race — serialise them. */
+#define RX_STATIC_RMS_MAX_POINTS 4194304   /* 4 Mi owned points */
+#define RX_STATIC_RMS_MAX_VARS 16
+int rx_residual_rms_static(const double* R_dev, int64_t nPointDomain, int64_t ld, int nVar, int64_t nPointGlobal,
+                           double* rms_dev, int device, void* cudaStream);
+
 #ifdef __cplusplus
 }
 #endif
