@@ -34,6 +34,13 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
     throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN and BARTH_JESPERSEN limiters are on the CUDA path");
   if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
+  // A partitioned geometry needs the device halo exchange behind Set_MPI_Solution / _Primitive_Gradient / _Primitive_Limiter
+  // (solver_reactive.hpp:162,176,183), which this class does not override: the base class would exchange host node[] only and the
+  // device halos would go stale without any error.  Refuse instead (the Python host, parallel.py, drives partitioned runs).
+  if (nPoint != nPointDomain) throw std::runtime_error("CReactiveNSSolverGPU: partitioned geometry (halo points present) is not supported by the C++ drop-in");
+  for (unsigned short m = 0; m < config->GetnMarker_All(); ++m)
+    if (config->GetMarker_All_KindBC(m) == SEND_RECEIVE)
+      throw std::runtime_error("CReactiveNSSolverGPU: SEND_RECEIVE markers present; the C++ drop-in is single-partition");
 
   // ---- geometry -> rx_mesh (flat arrays; dual_grid_structure.hpp:140,747,884)
   const unsigned long nEdge = geometry->GetnEdge();
@@ -260,15 +267,15 @@ void CReactiveNSSolverGPU::SetTime_Step(CGeometry* geometry, CSolver** solver_co
 
 void CReactiveNSSolverGPU::Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) {
   Check(rx_residual_conv(ctx), "rx_residual_conv");
-  if (mirror >= 2) MirrorResidual();
+  if (mirror >= 2) { Check(rx_get_status(ctx, nullptr), "Upwind_Residual"); MirrorResidual(); }   // the reference throws in this stage on a NaN residual
 }
 void CReactiveNSSolverGPU::Viscous_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short, unsigned short) {
   Check(rx_residual_visc(ctx), "rx_residual_visc");
-  if (mirror >= 2) MirrorResidual();
+  if (mirror >= 2) { Check(rx_get_status(ctx, nullptr), "Viscous_Residual"); MirrorResidual(); }   // the reference throws in this stage on a NaN residual
 }
 void CReactiveNSSolverGPU::Source_Residual(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) {
   Check(rx_residual_source(ctx), "rx_residual_source");
-  if (mirror >= 2) MirrorResidual();
+  if (mirror >= 2) { Check(rx_get_status(ctx, nullptr), "Source_Residual"); MirrorResidual(); }   // the reference throws in this stage on a NaN residual
 }
 // the state imposed at the boundary is what CTurbSSTSolver::BC_Inlet / BC_Outlet read as GetCharacPrimVar
 void CReactiveNSSolverGPU::MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker) {

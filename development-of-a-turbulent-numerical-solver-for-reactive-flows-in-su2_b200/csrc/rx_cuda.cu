@@ -3,7 +3,6 @@
 #include "../../include/rx_cuda.h"
 #include "rx_kernels2.cuh"
 #include "rx_visc_pair.cuh"
-#include "rx_visc_quad.cuh"
 #include "rx_order.cuh"
 #include "rx_turb.cuh"
 
@@ -19,7 +18,6 @@
 using namespace rx;
 
 static constexpr size_t SM_PAIR = (size_t)VP_SMW * VP_BS * sizeof(double);
-static constexpr size_t SM_QUAD = (size_t)VQ_SMW * VQ_BS * sizeof(double);
 static constexpr size_t SM_PAIR_RANS = (size_t)VP_SMW_RANS * VP_BS * sizeof(double);
 static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
@@ -34,6 +32,7 @@ struct rx_ctx {
   ChemC<9> cc9{};
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
+  bool allocFailed = false;         // any cudaMalloc / cudaMemset / cudaMemcpy of dalloc / dupload failed (checked at the end of rx_create)
   double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr, *pmax = nullptr, *resMax = nullptr;
   int *pidx = nullptr, *resMaxPoint = nullptr;
   bool haveResMax = false;
@@ -43,13 +42,10 @@ struct rx_ctx {
   cudaStream_t bcStream = nullptr;   // second stream for boundary kernels of markers that share no vertex
   cudaEvent_t evFork = nullptr, evJoin = nullptr;
   bool bcConcurrent = false;
-  bool splitSource = false;         // A/B hook (env RX_SPLIT_SOURCE=1): accumulation and source term as two kernels
   bool orderEdges = true;           // viscous kernel processes the edges grouped by their last iteration count (rx_order.cuh); default: laminar on, RANS off; env RX_VISC_ORDER=0/1 forces
   int* eOrderBuf = nullptr; int nOrdTiles = 0;
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
   bool haveWallDist = false; double sigmaK = 0.85;
-  bool viscQuad = false;            // A/B hook (env RX_VISC_QUAD=1): four-lanes-per-edge laminar viscous kernel (rx_visc_quad.cuh)
-  bool ransThreadPerEdge = false;   // A/B hook (env RX_RANS_THREAD_PER_EDGE=1): the serial-per-edge RANS viscous kernel
 };
 
 #define RX_CK(call)                                                                                   \
@@ -65,15 +61,16 @@ namespace {
 template <class T>
 T* dalloc(rx_ctx* c, size_t n) {
   void* p = nullptr;
-  if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) return nullptr;
-  cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(T));
+  if (cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) { c->allocFailed = true; return nullptr; }
   c->allocs.push_back(p);
+  if (cudaMemset(p, 0, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) { c->allocFailed = true; return nullptr; }
   return (T*)p;
 }
 template <class T>
 T* dupload(rx_ctx* c, const std::vector<T>& h) {
   T* p = dalloc<T>(c, h.size());
-  if (p && !h.empty()) cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+  if (p && !h.empty() && cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { c->allocFailed = true; return nullptr; }
+  if (!p) c->allocFailed = true;
   return p;
 }
 inline unsigned nblk(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
@@ -165,37 +162,28 @@ int download_aos(rx_ctx* c, const double* soa, double* h, int nv) {
 }
 }  // namespace
 
-// launch of the edge-flux kernels.  Laminar viscous flux: the two-lanes-per-edge kernel (rx_visc_pair.cuh), with the AUSM
-// flux from its own bandwidth-bound kernel; RANS keeps the thread-per-edge kernel that also carries the SST closure.
+// launch of the edge-flux kernels: the AUSM flux from its own bandwidth-bound kernel (or the MUSCL kernel), the viscous flux
+// from the two-lanes-per-edge kernel (rx_visc_pair.cuh; the RANS instantiation carries the SST closure).
 template <bool CONV, bool VISC>
 static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   const Dev& d = c->d;
-  if (CONV && c->o.secondOrder) {   // MUSCL reconstruction: its own kernel, the viscous part (if any) follows unfused
-    k_edge_conv2<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++;
-    if (VISC) launch_edge_flux<false, true>(c, s);
-    return;
-  }
-  if (!VISC) { k_edge_flux<9, CONV, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; return; }
-  if (c->o.rans && c->ransThreadPerEdge) { k_edge_flux<9, CONV, VISC, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d); c->launches++; return; }
-  if (CONV) { k_edge_flux<9, true, false, false><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d); c->launches++; }
-  if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(c->cc9, c->o, d);
-  else if (c->viscQuad) k_edge_visc_quad<9><<<nblk(4 * d.nEdge, VQ_BS), VQ_BS, SM_QUAD, s>>>(c->cc9, c->o, d);
-  else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
-  c->launches++;
-}
-
-// conv + visc accumulation and the source term: one fused kernel, or (splitSource) the sums at high occupancy followed by
-// the Arrhenius/PaSR kernel — the same additions in the same order either way
-static void launch_accumulate_visc(rx_ctx* c, cudaStream_t s) {
-  const Dev& d = c->d;
-  if (c->splitSource) {
-    k_accumulate<9, 7><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    c->launches += 2;
-  } else {
-    k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+  if (CONV) {
+    if (c->o.secondOrder) k_edge_conv2<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    else k_edge_flux<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
     c->launches++;
   }
+  if (VISC) {
+    if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(c->cc9, c->o, d);
+    else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
+    c->launches++;
+  }
+}
+
+// conv + visc accumulation and the source term in one kernel
+static void launch_accumulate_visc(rx_ctx* c, cudaStream_t s) {
+  const Dev& d = c->d;
+  k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+  c->launches++;
 }
 
 extern "C" {
@@ -217,22 +205,16 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   if (m->nPoint >= (1LL << 31) || m->nEdge >= (1LL << 31)) { g_create_error = "rx_create: mesh exceeds int32 indices"; return RX_ERR_UNSUPPORTED; }
   rx_ctx* c = new rx_ctx();
   c->device = op->device;
-  { const char* ev = getenv("RX_RANS_THREAD_PER_EDGE"); c->ransThreadPerEdge = ev && ev[0] == '1'; }
   {   // measured on the bench mesh: laminar 6.08 -> 5.96 ms per launch, RANS 14.51 -> 14.75 ms (its closure gathers more per point)
     const char* ev = getenv("RX_VISC_ORDER");
     c->orderEdges = ev && (ev[0] == '0' || ev[0] == '1') ? ev[0] == '1' : !op->rans;
   }
-  { const char* ev = getenv("RX_VISC_QUAD"); c->viscQuad = ev && ev[0] == '1'; }
-  { const char* ev = getenv("RX_SPLIT_SOURCE"); c->splitSource = ev && ev[0] == '1'; }
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
   {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
     const int smv = (int)SM_VISC;
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
-    cudaError_t e = cudaFuncSetAttribute(k_edge_flux<9, true, true, true>, at, smv);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_flux<9, false, true, true>, at, smv);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
+    cudaError_t e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
     if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
-    if (e == cudaSuccess && SM_QUAD > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_quad<9>, at, (int)SM_QUAD);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
     if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }
@@ -291,13 +273,13 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     c->nOrdTiles = (int)((d.nEdge + ORD_TILE - 1) / ORD_TILE);
     c->eOrderBuf = dalloc<int>(c, ne);
   }
-  d.nonPhys = dalloc<int>(c, np); d.counters = dalloc<unsigned long long>(c, 4);
+  d.nonPhys = dalloc<int>(c, np); d.counters = dalloc<unsigned long long>(c, 8);   // [0] non-physical points of the last preprocess; sticky until read: [1..3] NaN in the conv / visc / source residual, [4] temperature solves that did not converge
   c->updBlocks = (int)nblk(d.nPointDomain, 128);
   c->partial = dalloc<double>(c, (size_t)c->updBlocks * c->nVar);
   c->rms = dalloc<double>(c, c->nVar); c->sumsq = dalloc<double>(c, c->nVar);
   c->pmax = dalloc<double>(c, (size_t)c->updBlocks * c->nVar); c->pidx = dalloc<int>(c, (size_t)c->updBlocks * c->nVar);
   c->resMax = dalloc<double>(c, c->nVar); c->resMaxPoint = dalloc<int>(c, c->nVar);
-  if (!d.counters || !c->sumsq || !d.fluxC || !d.grad || (o.viscous && !d.fluxV)) {
+  if (c->allocFailed || !d.counters || !c->sumsq || !d.fluxC || !d.grad || (o.viscous && !d.fluxV)) {
     g_create_error = "rx_create: device allocation failed"; rx_destroy(c); return RX_ERR_CUDA;
   }
   c->nMarker = m->nMarker;
@@ -389,6 +371,7 @@ int rx_set_wall_distance(rx_ctx* c, const double* dist) {
 // (CPhysicalGeometry::ComputeWall_Distance :8990-9060).  Single-partition meshes: a partition sees only its own wall nodes.
 int rx_compute_wall_distance(rx_ctx* c) {
   if (!c->tpost) { c->err = "rx_compute_wall_distance: not a RANS context"; return RX_ERR_ARG; }
+  if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_compute_wall_distance: partitioned context (a partition sees only its own wall nodes); use rx_set_wall_distance"; return RX_ERR_UNSUPPORTED; }
   const Dev& d = c->d;
   long long nWall = 0;
   for (const MarkerDev& m : c->markers) if (m.kind == 3 || m.kind == 4) nWall += m.nVertex;
@@ -602,6 +585,29 @@ int rx_get_bc_state(rx_ctx* c, int marker, double* V) {
     for (int v = 0; v < np_; ++v) V[(size_t)k * np_ + v] = soa[(size_t)v * m.nVertex + k];
   return RX_OK;
 }
+// The reference throws where a residual turns NaN or the temperature solve fails (solver_direct_reactive.cpp:2772, 2861, 5384;
+// variable_direct_reactive.cpp:683, 724).  The kernels count those events in d.counters[1..4]; they stay set until a host read.
+static int read_status(rx_ctx* c, unsigned long long* h5) {
+  RX_CK(cudaMemcpyAsync(h5, c->d.counters, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  if (h5[1] || h5[2] || h5[3] || h5[4]) RX_CK(cudaMemsetAsync(c->d.counters + 1, 0, 4 * sizeof(unsigned long long), c->stream));
+  return RX_OK;
+}
+static int status_error(rx_ctx* c, const unsigned long long* h) {
+  if (h[4]) { c->err = "Convergence not achieved for bisection method (temperature solve, " + std::to_string(h[4]) + " points)"; return RX_ERR_NAN; }
+  if (h[1]) { c->err = "NaN found in the upwind residual"; return RX_ERR_NAN; }
+  if (h[2]) { c->err = "NaN found in the viscous residual"; return RX_ERR_NAN; }
+  if (h[3]) { c->err = "NaN found in the source residual"; return RX_ERR_NAN; }
+  return RX_OK;
+}
+int rx_get_status(rx_ctx* c, int64_t* status5) {
+  unsigned long long h[5];
+  const int rc = read_status(c, h);
+  if (rc) return rc;
+  if (status5) for (int k = 0; k < 5; ++k) status5[k] = (int64_t)h[k];
+  return status_error(c, h);
+}
+
 int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
@@ -616,9 +622,12 @@ int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   k_rms_finish<<<c->nVar, 256, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
   c->launches += 2;
   RX_CK(cudaGetLastError());
-  if (resRms) {
+  if (resRms) {   // the host synchronises here anyway: the NaN / failed-solve flags come with the norms
+    unsigned long long h[5];
     RX_CK(cudaMemcpyAsync(resRms, c->rms, c->nVar * sizeof(double), cudaMemcpyDeviceToHost, s));
-    RX_CK(cudaStreamSynchronize(s));
+    const int rc = read_status(c, h);
+    if (rc) return rc;
+    return status_error(c, h);
   }
   return RX_OK;
 }
@@ -666,16 +675,16 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
                 else launch_edge_flux<true, false>(c, s);
                 c->launches--; break;   // the helper counts its own launch
         case 1: launch_edge_flux<true, false>(c, s); c->launches--; break;
-        case 2: if (c->o.viscous) { launch_accumulate_visc(c, s); c->launches -= c->splitSource ? 2 : 1; }
+        case 2: if (c->o.viscous) { launch_accumulate_visc(c, s); c->launches--; }
                 else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
         case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;
         case 7: k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); break;
         case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
                 else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
         case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
-        case 8: if (!c->tpost) { c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
+        case 8: if (!c->tpost) { cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
                 k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost); break;
-        case 9: if (!c->tpost) { c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
+        case 9: if (!c->tpost) { cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
                 k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost, c->sigmaK); break;
         case 6: k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial, nullptr, nullptr); break;
         default: cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: unknown kernel id"; return RX_ERR_ARG;
@@ -784,10 +793,17 @@ int rx_wall_distance(int64_t nPoint, const double* xy, int64_t nWall, const doub
   return rc;
 }
 
-int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : 4; }   // 2: limiter, 3: grad k, grad omega
+int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : (what == 2 || what == 3) ? 4 : 0; }   // 2: limiter, 3: grad k, grad omega
+static int halo_check(rx_ctx* c, int what, const void* pts, const void* buf) {
+  if (what < 0 || what > 3) { c->err = "rx_halo_pack/unpack: `what` must be 0 (U), 1 (gradients), 2 (limiters) or 3 (grad k, grad omega)"; return RX_ERR_ARG; }
+  if (what == 3 && !c->tpost) { c->err = "rx_halo_pack/unpack: what = 3 needs a RANS context"; return RX_ERR_ARG; }
+  if (!pts || !buf) { c->err = "rx_halo_pack/unpack: null device pointer"; return RX_ERR_ARG; }
+  return RX_OK;
+}
 static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np; }
 int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {
   if (n <= 0) return RX_OK;
+  { const int rc = halo_check(c, what, pts, buf); if (rc) return rc; }
   const int nv = rx_halo_width(c, what);
   k_pack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(halo_field(c, what), c->d.np, nv, n, (const long long*)pts, buf);
   c->launches++;
@@ -796,14 +812,47 @@ int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf
 }
 int rx_halo_unpack(rx_ctx* c, int what, int64_t n, const int64_t* pts, const double* buf) {
   if (n <= 0) return RX_OK;
+  { const int rc = halo_check(c, what, pts, buf); if (rc) return rc; }
   const int nv = rx_halo_width(c, what);
   k_unpack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(halo_field(c, what), c->d.np, nv, n, (const long long*)pts, buf);
   c->launches++;
+  if (what == 1 && c->o.viscous) {   // SetVorticity / SetStrainMag of the received points (:4716-4736 run after Set_MPI_Primitive_Gradient)
+    k_vort_strain_points<9><<<nblk(n, 128), 128, 0, c->stream>>>(c->d, (long long)n, (const long long*)pts);
+    c->launches++;
+  }
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
 
 }  // extern "C"
+
+// diagnostic: the glibc-exact exp / pow / log of rx_libm.cuh over host arrays (tests/test_gpu_libm.py compares with the host's libm)
+namespace rx {
+__global__ void k_libm_eval(int which, long long n, const double* __restrict__ x, const double* __restrict__ y, double* __restrict__ out) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  out[t] = which == 0 ? gl_exp(x[t]) : which == 1 ? gl_pow(x[t], y[t]) : gl_log(x[t]);
+}
+}  // namespace rx
+extern "C" int rx_libm_eval(int which, int64_t n, const double* x, const double* y, double* out, int device) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_error = "rx_libm_eval: no CUDA device (no CPU path)"; return RX_ERR_NO_DEVICE; }
+  if (which < 0 || which > 2 || n < 0 || !x || !out || (which == 1 && !y)) { g_create_error = "rx_libm_eval: bad arguments"; return RX_ERR_ARG; }
+  if (n == 0) return RX_OK;
+  if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "rx_libm_eval: cudaSetDevice failed"; return RX_ERR_CUDA; }
+  double *dx = nullptr, *dy = nullptr, *dout = nullptr;
+  int rc = RX_OK;
+  const size_t nb = (size_t)n * sizeof(double);
+  if (cudaMalloc(&dx, nb) != cudaSuccess || cudaMalloc(&dout, nb) != cudaSuccess || (which == 1 && cudaMalloc(&dy, nb) != cudaSuccess)) rc = RX_ERR_CUDA;
+  if (rc == RX_OK && (cudaMemcpy(dx, x, nb, cudaMemcpyHostToDevice) != cudaSuccess || (which == 1 && cudaMemcpy(dy, y, nb, cudaMemcpyHostToDevice) != cudaSuccess))) rc = RX_ERR_CUDA;
+  if (rc == RX_OK) {
+    rx::k_libm_eval<<<(unsigned)((n + 255) / 256), 256>>>(which, (long long)n, dx, dy, dout);
+    if (cudaMemcpy(out, dout, nb, cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess) rc = RX_ERR_CUDA;
+  }
+  if (rc != RX_OK) g_create_error = "rx_libm_eval: allocation, copy or kernel failed";
+  cudaFree(dx); cudaFree(dy); cudaFree(dout);
+  return rc;
+}
 
 // allocation-free residual norms over a static device scratch array (its own entry point; no existing path uses it)
 #include "rx_noalloc.cuh"

@@ -11,6 +11,7 @@
 #include <stdint.h>
 #ifdef __CUDACC__
 #include "rx_fdiv.cuh"
+#include "rx_libm.cuh"
 #endif
 
 #if defined(__CUDACC__)
@@ -34,6 +35,30 @@ enum { P_MU = 0, P_KAPPA = 1, P_CP = 2, P_H = 3, P_S = 4 };
 enum { U_RHO = 0, U_MX = 1, U_E = 3, U_S = 4 };
 enum { V_T = 0, V_VX = 1, V_P = 3, V_RHO = 4, V_H = 5, V_A = 6, V_Y = 7 };
 enum { G_T = 0, G_VX = 1, G_P = 3, G_X = 4 };
+
+// std::exp / std::pow / std::log of the reference: on the device the glibc-exact restatements of rx_libm.cuh (same bits as the
+// host libm the CPU code calls), on the host (oracle-side emulation only) libm itself
+RX_HD double rx_exp(double x) {
+#ifdef __CUDA_ARCH__
+  return gl_exp(x);
+#else
+  return exp(x);
+#endif
+}
+RX_HD double rx_pow(double x, double y) {
+#ifdef __CUDA_ARCH__
+  return gl_pow(x, y);
+#else
+  return pow(x, y);
+#endif
+}
+RX_HD double rx_log(double x) {
+#ifdef __CUDA_ARCH__
+  return gl_log(x);
+#else
+  return log(x);
+#endif
+}
 
 struct Knot { double y, y2; };
 
@@ -196,28 +221,15 @@ RX_HD void transport(const ChemC<NS>& cc, double T, const double* Y, double& muM
   }
 }
 
-// a^1.75 = a*sqrt(a)*sqrt(sqrt(a)) evaluated in double-double and rounded once: the correctly rounded value, which is what
-// glibc's pow(T, 1.75) returns (GetDij_SM, reacting_model_library.cpp:751-766).  CUDA's pow() is only accurate to 2 ulp,
-// and a 1-ulp change of the diffusion coefficients is amplified by the BiCGSTAB iteration of the Stefan–Maxwell solve to
-// ~1e-11 of the diffusion flux — above the 1e-12 residual parity target.  fma() here is an explicit, exact residual.
-RX_HD double pow175(double a) {
-  const double s0 = sqrt(a);
-  const double s1 = fma(-s0, s0, a) / (2.0 * s0);          // sqrt(a) = s0 + s1
-  const double q0 = sqrt(s0);
-  const double q1 = (fma(-q0, q0, s0) + s1) / (2.0 * q0);  // sqrt(sqrt(a)) = q0 + q1
-  const double p0 = a * s0;
-  const double p1 = fma(a, s0, -p0) + a * s1;              // a*sqrt(a) = p0 + p1
-  const double ph = p0 + p1;
-  const double pl = p1 - (ph - p0);
-  const double r0 = ph * q0;
-  const double r1 = fma(ph, q0, -r0) + (ph * q1 + pl * q0);
-  return r0 + r1;
-}
+// std::pow(temp, 1.75) of GetDij_SM (reacting_model_library.cpp:751-766) with glibc's own bits (rx_libm.cuh).  A one-ulp change of
+// the diffusion coefficients is amplified by the BiCGSTAB iteration of the Stefan-Maxwell solve to ~1e-11 of the diffusion flux;
+// CUDA's pow (2 ulp) and even the correctly rounded value (glibc's differs from it for 0.08 % of temperatures) are not enough.
+RX_HD double pow175(double a) { return rx_pow(a, 1.75); }
 
 // ---- cons -> prim (CReactiveEulerVariable::Cons2PrimVar, SU2_CFD/src/variable_direct_reactive.cpp:550-778) ----
 // U is modified in place where the reference modifies Solution (:571-583). V[V_T] holds the secant start value on entry.
 template <int NS>
-RX_HD bool cons2prim(const ChemC<NS>& cc, const Opts& o, long long extIter, double* U, double* V, double ke) {
+RX_HD bool cons2prim(const ChemC<NS>& cc, const Opts& o, long long extIter, double* U, double* V, double ke, bool* solveFailed = nullptr) {
   bool nonPhys = false;
 #pragma unroll
   for (int s = 0; s < NS; ++s)
@@ -258,6 +270,7 @@ RX_HD bool cons2prim(const ChemC<NS>& cc, const Opts& o, long long extIter, doub
         if (fabs(f) < Btol) { NRconvg = true; break; }
         if (f > 0) Ta = T; else Tb = T;
       }
+      if (!NRconvg && solveFailed) *solveFailed = true;   // "Convergence not achieved for bisection method after catching out of range" (:683)
       break;
     }
     f = T - C1 - C2 * hs;
@@ -269,14 +282,16 @@ RX_HD bool cons2prim(const ChemC<NS>& cc, const Opts& o, long long extIter, doub
   if (NRconvg) V[V_T] = T;
   else {
     double Ta = Tmin, Tb = Tmax;
+    bool Bconvg = false;
     for (int b = 0; b < 32; ++b) {
       T = (Ta + Tb) / 2.0;
       bool dummy = true;
       hs = enthalpy(cc, T, Y, dummy);
       f = T - C1 - C2 * hs;
-      if (fabs(f) < Btol) { V[V_T] = T; break; }
+      if (fabs(f) < Btol) { V[V_T] = T; Bconvg = true; break; }
       if (f > 0) Ta = T; else Tb = T;
     }
+    if (!Bconvg && solveFailed) *solveFailed = true;   // "Convergence not achieved for bisection method" (:724)
   }
   if (extIter > 0 && o.clipT) V[V_T] = fmin(fmax(V[V_T], 0.95 * old_temp), 1.05 * old_temp);
   if (V[V_T] < Tmin) { V[V_T] = Tmin; nonPhys = true; }

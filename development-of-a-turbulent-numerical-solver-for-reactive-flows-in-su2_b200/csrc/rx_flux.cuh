@@ -435,13 +435,12 @@ RX_HD void viscous_flux(const ChemC<NS>& cc, const Opts& o, const ViscEnd<NS>& I
 }
 
 // ---- Arrhenius + PaSR source (reacting_model_library.cpp:99-227, 803-920; numerics_direct_reactive.cpp:1728-1825) ----
-// pow(c, e) for the exponents that occur in mechanisms is short-circuited where the result is exact in both libms.
+// std::pow(c, e) (Eigen's ArrayXd::pow, reacting_model_library.cpp:893-895, 910-912; std::pow(temp, beta) :840): exponents 0 and 1
+// are exact in glibc (1 and c), everything else goes through the glibc-exact pow of rx_libm.cuh
 RX_HD double pow_exp(double c, double e) {
   if (e == 0.0) return 1.0;
   if (e == 1.0) return c;
-  if (e == 2.0) return c * c;
-  if (e == 0.5) return sqrt(c);   // glibc pow(x,0.5) is correctly rounded == sqrt(x) for finite positive x
-  return pow(c, e);
+  return rx_pow(c, e);
 }
 template <int NS>
 RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pasrLb, double T, double rho, const double* Yin,
@@ -458,7 +457,7 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
   // GetMassProductionTerm (:143-154 with the PaSR constants, :196-202 without) — so no per-reaction array is kept
   for (int r = 0; r < Nr; ++r) {
     // ComputeRateConstants :835-867 (K_eq from Gibbs only decides kb when no backward data are available)
-    const double kf = cc.As[r] * pow_exp(T, cc.Betas[r]) * exp(-cc.Ta[r] / T);
+    const double kf = cc.As[r] * pow_exp(T, cc.Betas[r]) * rx_exp(-cc.Ta[r] / T);
     double kb;
     if (!cc.avb[r]) {
       if (!cc.rev[r]) kb = 0.0;
@@ -470,10 +469,10 @@ RX_HD void mass_production(const ChemC<NS>& cc, bool pasr, double cMu, double pa
           if (dc != 0.0) { dG += dc * (spl_eval(cc, P_H, s, sp) - T * spl_eval(cc, P_S, s, sp)); dnu += dc; }
         }
         const double lnKp = -dG / (R_UNGAS * T);
-        const double lnKc = lnKp - dnu * log(R_UNGAS_ATM * T);
-        kb = (exp(lnKp) > 1.0e10) ? 0.0 : kf / exp(lnKc);
+        const double lnKc = lnKp - dnu * rx_log(R_UNGAS_ATM * T);
+        kb = (rx_exp(lnKp) > 1.0e10) ? 0.0 : kf / rx_exp(lnKc);
       }
-    } else kb = cc.AsB[r] * pow_exp(T, cc.BetasB[r]) * exp(-cc.TaB[r] / T);
+    } else kb = cc.AsB[r] * pow_exp(T, cc.BetasB[r]) * rx_exp(-cc.TaB[r] / T);
     // SetReactionRates :872-920
     double fr = 0.0, br = 0.0;
     bool zero = false;

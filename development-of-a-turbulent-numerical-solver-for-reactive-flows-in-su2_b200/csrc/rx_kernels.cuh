@@ -185,7 +185,9 @@ __global__ void __launch_bounds__(128, RX_PR_MINB) k_primitive(const __grid_cons
   bool np = false;
 #pragma unroll 1
   for (int attempt = 0; attempt < 2; ++attempt) {   // one copy of the temperature solve in the code; second pass = :1001-1008
-    const bool bad = cons2prim(cc, o, extIter, U, V, ke);
+    bool failed = false;
+    const bool bad = cons2prim(cc, o, extIter, U, V, ke, &failed);
+    if (failed) atomicAdd(d.counters + 4, 1ULL);   // the reference throws here (variable_direct_reactive.cpp:683, :724)
     if (attempt == 0) np = bad;
     if (!(bad && extIter > 0) || attempt == 1) break;
 #pragma unroll
@@ -234,6 +236,20 @@ __device__ __forceinline__ void store_vort_strain(const Dev& d, long long p, con
   t = g[2 * 2 + 1] - 1.0 / 3.0 * div; sm += t * t;
   t = 0.5 * (g[1 * 2 + 1] + g[2 * 2 + 0]); sm += 2.0 * (t * t);
   d.strain[p] = sqrt(2.0 * sm);
+}
+
+// Vorticity / strain magnitude of listed points from their stored gradients.  The reference forms both for ALL points after
+// Set_MPI_Primitive_Gradient (solver_direct_reactive.cpp:4716-4736, :5049): the gradient kernels above see a halo point before
+// its gradient has arrived, so the halo unpack of the gradients (rx_halo_unpack, what = 1) re-forms them for the received points.
+template <int NS>
+__global__ void k_vort_strain_points(const Dev d, long long n, const long long* __restrict__ pts) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const long long p = pts[t];
+  double g[(4 + NS) * 2];
+#pragma unroll
+  for (int k = 2; k < 6; ++k) g[k] = d.grad[k * d.np + p];   // rows u, v
+  store_vort_strain<NS>(d, p, g);
 }
 
 // ---- SetPrimitive_Gradient_LS (solver_direct_reactive.cpp:4887-5050), one thread per owned point.

@@ -25,37 +25,19 @@ __device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long 
   else { E.muT = 1.0; E.ke = 0.0; E.gk[0] = E.gk[1] = 0.0; }
 }
 
-// ---- Upwind_Residual (:2535-2785, 1st order) and Viscous_Residual (:5305-5386): one thread per edge, flux to edge arrays
-constexpr int EDGE_BS = 64;   // threads per block of the edge / boundary flux kernels
-template <int NS, bool CONV, bool VISC, bool RANS>
-__global__ void __launch_bounds__(EDGE_BS) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+// ---- Upwind_Residual (:2535-2785, 1st order): one thread per edge, AUSM flux to the edge array
+constexpr int EDGE_BS = 64;   // threads per block of the boundary flux kernels (thread-private Stefan-Maxwell matrix in shared memory)
+template <int NS>
+__global__ void __launch_bounds__(64) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= d.nEdge) return;
   constexpr int NV = 4 + NS;
   const int i = d.ei[e], j = d.ej[e];
-  const double nx = d.enx[e], ny = d.eny[e];
-  double res[NV];
-  if (VISC) {
-    ViscEnd<NS> I, J;
-    load_visc_end<NS>(d, o, i, I, true);
-    load_visc_end<NS>(d, o, j, J, true);
-    if (CONV) {
-      ausm<NS>(o.mInfty, I.V, J.V, nx, ny, res);
+  double res[NV], Vi[7 + NS], Vj[7 + NS];
+  load_V<NS>(d, i, Vi); load_V<NS>(d, j, Vj);
+  ausm<NS>(o.mInfty, Vi, Vj, d.enx[e], d.eny[e], res);
 #pragma unroll
-      for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
-    }
-    extern __shared__ double smat[];   // NS*NS doubles per thread, word k of thread t at smat[k*EDGE_BS + t]: conflict-free
-    const double sigma_k = RANS ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
-    viscous_flux<NS, true, EDGE_BS, RANS>(cc, o, I, J, nx, ny, sigma_k, smat + threadIdx.x, res);
-#pragma unroll
-    for (int v = 0; v < NV; ++v) d.fluxV[v * d.ne + e] = res[v];
-  } else {
-    double Vi[7 + NS], Vj[7 + NS];
-    load_V<NS>(d, i, Vi); load_V<NS>(d, j, Vj);
-    ausm<NS>(o.mInfty, Vi, Vj, nx, ny, res);
-#pragma unroll
-    for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
-  }
+  for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
 }
 
 // ---- SetPrimitive_Limiter (:1328-1523), Venkatakrishnan, owner-computes: one thread per point over its neighbours.
@@ -219,8 +201,10 @@ __global__ void __launch_bounds__(128, RX_SRC_MINB) k_source(const __grid_consta
   if (p >= d.nPointDomain) return;
   double src[NS];
   point_source<NS>(cc, o, d, p, src);
+  bool nanS = false;
 #pragma unroll
-  for (int s = 0; s < NS; ++s) d.R[(U_S + s) * d.np + p] += src[s];
+  for (int s = 0; s < NS; ++s) { nanS = nanS || src[s] != src[s]; d.R[(U_S + s) * d.np + p] += src[s]; }
+  if (nanS) atomicAdd(d.counters + 3, 1ULL);
 }
 // stand-alone form over independent points, SoA inputs Y[s*n+p], res[s*n+p]
 template <int NS>
@@ -278,14 +262,16 @@ __global__ void __launch_bounds__(128, RX_ACC_MINB) k_accumulate(const __grid_co
   };
   if (MODE & 1) sweep(d.fluxC, true);
   if (MODE & 2) sweep(d.fluxV, false);
+  bool nanC = false, nanV = false;
 #else
+  bool nanC = false, nanV = false;   // the reference tests every edge residual before adding it (:2744, :5361) and throws
   if (MODE & 1) {
     for (int k = k0; k < k1; ++k) {
       const int code = d.incEdge[k];
       const bool first = code >= 0;
       const long long e = first ? code : ~code;
 #pragma unroll
-      for (int v = 0; v < NV; ++v) { const double f = d.fluxC[v * d.ne + e]; r[v] = first ? r[v] + f : r[v] - f; }
+      for (int v = 0; v < NV; ++v) { const double f = d.fluxC[v * d.ne + e]; nanC = nanC || f != f; r[v] = first ? r[v] + f : r[v] - f; }
     }
   }
   if (MODE & 2) {
@@ -294,16 +280,20 @@ __global__ void __launch_bounds__(128, RX_ACC_MINB) k_accumulate(const __grid_co
       const bool first = code >= 0;
       const long long e = first ? code : ~code;
 #pragma unroll
-      for (int v = 0; v < NV; ++v) { const double f = d.fluxV[v * d.ne + e]; r[v] = first ? r[v] - f : r[v] + f; }
+      for (int v = 0; v < NV; ++v) { const double f = d.fluxV[v * d.ne + e]; nanV = nanV || f != f; r[v] = first ? r[v] - f : r[v] + f; }
     }
   }
 #endif
   if (MODE == 3 && p < d.nPointDomain) {
     double src[NS];
     point_source<NS>(cc, o, d, p, src);
+    bool nanS = false;
 #pragma unroll
-    for (int s = 0; s < NS; ++s) r[U_S + s] += src[s];
+    for (int s = 0; s < NS; ++s) { nanS = nanS || src[s] != src[s]; r[U_S + s] += src[s]; }
+    if (nanS) atomicAdd(d.counters + 3, 1ULL);   // "NaN found in the source residual" (:2861)
   }
+  if (nanC) atomicAdd(d.counters + 1, 1ULL);     // "NaN found in the upwind residual" (:2772)
+  if (nanV) atomicAdd(d.counters + 2, 1ULL);     // "NaN found in the viscous residual" (:5384)
 #pragma unroll
   for (int v = 0; v < NV; ++v) d.R[v * d.np + p] = r[v];
 }
@@ -385,13 +375,13 @@ __global__ void __launch_bounds__(64) k_bc_outlet(const __grid_constant__ ChemC<
 #pragma unroll
     for (int v = 0; v < 7 + NS; ++v) Vo[v] = Vd[v];
   } else {
-    const double Entropy = Pressure * pow(1.0 / Density, Gamma);
+    const double Entropy = Pressure * rx_pow(1.0 / Density, Gamma);
     const double Vn = 0.0 + Vel0 * un0 + Vel1 * un1;
     const double Gamma_Minus_One = Gamma - 1.0;
     const double Riemann = Vn + 2.0 * SoundSpeed / Gamma_Minus_One;
     const double P_Exit = m.P / 1.0;
     Vo[V_P] = P_Exit;
-    Vo[V_RHO] = pow(P_Exit / Entropy, 1.0 / Gamma);
+    Vo[V_RHO] = rx_pow(P_Exit / Entropy, 1.0 / Gamma);
     SoundSpeed = sqrt(Gamma * P_Exit / Vo[V_RHO]);
     const double Vn_Exit = Riemann - 2.0 * SoundSpeed / Gamma_Minus_One;
     Velocity2 = 0.0;
@@ -497,7 +487,10 @@ __global__ void __launch_bounds__(128) k_update(const Dev d, double alpha, doubl
     for (int v = 0; v < NV; ++v) {
       const double Res = d.R[v * d.np + p] + 0.0;
       const double lo = (v == U_MX || v == U_MX + 1 || v == U_E) ? -1.0 / EPS : 0.0, hi = 1.0 / EPS;
-      d.U[v * d.np + p] = fmin(fmax(d.Uold[v * d.np + p] + (-Res * Delta * alpha), lo), hi);
+      // CVariable::AddClippedSolution (variable_structure.cpp:207-212): std::min(std::max(x, lo), hi) — a NaN x stays NaN
+      const double x = d.Uold[v * d.np + p] + (-Res * Delta * alpha);
+      const double xl = (x < lo) ? lo : x;
+      d.U[v * d.np + p] = (hi < xl) ? hi : xl;
       sq[v] = Res * Res;
       ab[v] = fabs(Res);
     }

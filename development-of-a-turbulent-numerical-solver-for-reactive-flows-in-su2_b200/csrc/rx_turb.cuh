@@ -146,9 +146,9 @@ __global__ void __launch_bounds__(128) k_turb_blend(const Dev d, double* __restr
   const double arg2B = 500.0 * mu / (rho * dist * dist * omega + EPS * EPS);
   double arg2 = fmax(arg2A, arg2B);
   const double arg1 = fmin(arg2, 4.0 * rho * sigma_om2 * kine / (CDkw * dist * dist + EPS * EPS));
-  const double F1 = tanh(pow(arg1, 4.0));
+  const double F1 = tanh(rx_pow(arg1, 4.0));
   arg2 = fmax(2.0 * arg2A, arg2B);
-  const double F2 = tanh(pow(arg2, 2.0));
+  const double F2 = tanh(arg2 * arg2);   // g++ folds pow(x, 2.0) to x*x at -O2 (pow(x, 4.0) above stays a libm call)
   const double zeta = fmin(1.0 / omega, a1 / (strMag * F2));
   const double muT = fmin(fmax(rho * kine * zeta, 0.0), 1.0);
   tp[TP_F1 * np + p] = F1; tp[TP_F2 * np + p] = F2; tp[TP_CD * np + p] = CDkw; tp[TP_MUT * np + p] = muT; tp[TP_SIGK * np + p] = sigmaK;

@@ -77,7 +77,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static"]
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval"]
 
 _lib = None
 
@@ -138,6 +138,18 @@ def source_points(chem, T, rho, Y, vol, omegaTurb=None, rans=False, cMu=0.09, pa
     if rc != 0:
         raise RxError("rx_source_points failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
     return res
+
+
+def libm_eval(which, x, y=None, device=0):
+    """The device's glibc-exact exp ('exp'), pow ('pow', needs y) or log ('log') over host arrays (rx_libm_eval; csrc/rx_libm.cuh)."""
+    L = load_library()
+    w = {"exp": 0, "pow": 1, "log": 2}[which]
+    x = _c(x); out = np.empty_like(x)
+    yy = _c(y) if y is not None else None
+    rc = L.rx_libm_eval(w, C.c_int64(x.size), _d(x), _d(yy) if yy is not None else None, _d(out), int(device))
+    if rc != 0:
+        raise RxError("rx_libm_eval failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
+    return out
 
 
 STATIC_RMS_MAX_POINTS, STATIC_RMS_MAX_VARS = 4194304, 16   # include/rx_cuda.h: RX_STATIC_RMS_MAX_*
@@ -260,6 +272,13 @@ class CReactiveNSSolverGPU:
         rms = np.empty(self.nVar)
         self._ck(self.lib.rx_update_explicit(self.ctx, C.c_double(alpha), _d(rms) if want_rms else None))
         return rms if want_rms else None
+
+    def GetStatus(self):
+        """[non-physical points of the last Preprocessing, NaN conv, NaN visc, NaN source, failed temperature solves]; raises RxError
+        with the reference's message if any of the last four is set (rx_get_status)."""
+        st = np.zeros(5, dtype=np.int64)
+        self._ck(self.lib.rx_get_status(self.ctx, _i(st)))
+        return st
 
     def GetRes_Max(self):
         """(max |LinSysRes| per variable, local index of the first point attaining it) of the last update with norms —

@@ -131,6 +131,13 @@ int rx_bc_marker(rx_ctx*, int marker);                    /* one BC_* call of th
 int rx_get_bc_state(rx_ctx*, int marker, double* V /* [nVertex][nPrim] */);   /* state imposed by the last inlet/outlet BC of the marker = CharacPrimVar (:3274, :3844), read by the turbulence BCs */
 int rx_update_explicit(rx_ctx*, double rkAlpha, double* resRms /* [nVar] or NULL: no host sync */);  /* ExplicitEuler/RK_Iteration :2414,:2456 */
 
+/* Events at which the reference throws (solver_direct_reactive.cpp:2772 "NaN found in the upwind residual", :5384 viscous, :2861 source;
+ * variable_direct_reactive.cpp:683, :724 "Convergence not achieved for bisection method"), counted on the device:
+ * status5 = { non-physical points of the last rx_preprocess, NaN conv flux, NaN visc flux, NaN source, failed temperature solves }.
+ * Entries 1..4 stay set until read (this call, or rx_update_explicit / rx_iterate with resRms, which return RX_ERR_NAN with the
+ * reference's message in rx_last_error).  Synchronises the host.  status5 may be NULL. */
+int rx_get_status(rx_ctx*, int64_t* status5);
+
 int rx_get_residual_max(rx_ctx*, double* resMax /* [nVar] */, int64_t* point /* [nVar], local point index */);   /* CSolver::AddRes_Max of the last update that returned norms: largest |LinSysRes| per variable and the first point attaining it (:2436) */
 int rx_residual_all(rx_ctx*);                             /* Upwind + Viscous + Source residual in one pass (same sums, same order) */
 
@@ -168,6 +175,11 @@ int rx_kernel_time(rx_ctx*, int which, int reps, double* msAvg);
  * chains per thread, every SM filled), in TFLOP/s with one fused multiply-add counted as two operations.  The compute
  * roof of the viscous and source kernels (MEASURED_PEAKS.json carries no FP64 entry). */
 int rx_fp64_peak(rx_ctx*, double* tflops);
+
+/* diagnostic hook: the device's glibc-exact exp (which = 0), pow (1; y required) and log (2) of csrc/rx_libm.cuh over host arrays —
+ * the functions the kernels call where the reference calls std::exp / std::pow / std::log (reacting_model_library.cpp:751-766,
+ * 835-920; solver_direct_reactive.cpp:3901-3935).  tests/test_gpu_libm.py compares them bit for bit with the host's libm. */
+int rx_libm_eval(int which, int64_t n, const double* x, const double* y, double* out, int device);
 
 /* partitioning (host-side graph tools, no device work; csrc/host/rx_partition.cpp).
  * rx_partition_kway: k-way partition of the point adjacency graph (CSR nbPtr/nbPoint, the same arrays rx_mesh carries) into

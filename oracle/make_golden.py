@@ -108,6 +108,13 @@ CHANNEL_MARKERS = {
     "MARKER_PLOTTING": "( upper_wall )", "MARKER_MONITORING": "( upper_wall )",
 }
 
+# harness environment per case (oracle/ref_harness.cpp: RX_PERTURB_TAMP, RX_POKE_ITER, RX_POKE_MODE)
+ENVS = {
+    "channel_lam_edge": {"RX_PERTURB_TAMP": "2000", "RX_POKE_ITER": "1", "RX_POKE_MODE": "abc"},
+    "channel_lam_clip": {"RX_POKE_ITER": "1", "RX_POKE_MODE": "d"},
+    "channel_rans_ign": {"RX_PERTURB_TAMP": "2000"},
+}
+
 # name -> (case-dir kwargs, cfg replacements, nIter, dump_from, perturb_seed or None, lean fixture (drop intermediate residuals))
 SPECS = {
     # config[0]: the jet-reactor case as shipped (REACTIVE_RANS + SST + PaSR, AUSM 1st order, WLS, explicit Euler)
@@ -151,6 +158,21 @@ SPECS = {
     # of (k, omega) for the turbulence postprocessing slice (tpost dump)
     "channel_rans_gg": (dict(nx=41, ny=21, stretch=1.5),
                         dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO", NUM_METHOD_GRAD="GREEN_GAUSS"), 2, 1, 37, True),
+    # edge cases of Cons2PrimVar no smooth state reaches (variable_direct_reactive.cpp:296-301, 656-688, 698-724): hot state
+    # (T up to 2500 K), then at iteration 1 secant start values of 201 K and Tmax - 0.4 (exception -> bisection, secant not
+    # converged -> bisection) and non-physical species densities (fallback to Solution_Old)
+    "channel_lam_edge": (dict(nx=41, ny=21, stretch=1.5),
+                         dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                              TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )",
+                              CFL_NUMBER="0.02"), 2, 1, 41, True),
+    # CLIPPING_TEMPRATURE= YES (:728-739) with start values 20 % off at iteration 1
+    "channel_lam_clip": (dict(nx=41, ny=21, stretch=1.5),
+                         dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                              CLIPPING_TEMPRATURE="YES", CFL_NUMBER="0.02"), 2, 1, 43, True),
+    # RANS + PaSR on a burning state (T up to 2500 K) with the ignition overwrite switched off between iterations 1 and 2
+    # (IGNITION_ITER= 2, solver_direct_reactive.cpp:1013-1024)
+    "channel_rans_ign": (dict(nx=41, ny=21, stretch=1.5),
+                         dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="3", IGNITION="YES", IGNITION_ITER="2", CFL_NUMBER="0.02"), 3, 1, 47, True),
 }
 
 
@@ -168,8 +190,8 @@ def run_case(name):
     out = os.path.join(d, "dump")
     shutil.rmtree(out, ignore_errors=True)
     cmd = [HARNESS, "case.cfg", str(nit), out, str(dump_from)] + ([str(seed)] if seed is not None else [])
-    log = subprocess.run(cmd, cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    tail = "\n".join(log.stdout.splitlines()[-6:])
+    log = subprocess.run(cmd, cwd=d, env=dict(os.environ, **ENVS.get(name, {})), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    tail = "\n".join([l for l in log.stdout.splitlines() if "poke" in l or "bisection" in l][:6] + log.stdout.splitlines()[-6:])
     if log.returncode != 0:
         raise RuntimeError("harness failed for %s:\n%s" % (name, tail))
     print(tail)
@@ -202,6 +224,37 @@ def run_case(name):
     shutil.rmtree(out, ignore_errors=True)
 
 
+# long runs for the converged-field / residual-history parity (north_star: fields and history within 1e-10): same case directories
+# and cfgs as the stage fixtures of the same name, more iterations, checkpoints instead of stage dumps.
+# name -> (stage-fixture name, cfg overrides, harness environment, iterations, perturb seed or None, checkpoints)
+# The laminar channel: 3-stage RK at CFL 0.02 from a cool perturbed state (temperature bump of 300 K) — at the stage fixture's CFL 0.2
+# the reference itself diverges within five iterations, and a hot state ignites; this one relaxes steadily.
+LONG = {
+    "long_channel_lam_rk": ("channel_lam_rk", {"CFL_NUMBER": "0.02"}, {"RX_PERTURB_TAMP": "300"}, 2000, 11, [0, 1, 10, 100, 500, 1000, 2000]),
+    "long_jet_rans_shipped": ("jet_rans_shipped", {}, {}, 500, None, [0, 1, 10, 100, 250, 500]),
+}
+
+
+def run_long(name):
+    base, repl, envx, nit, seed, ckpt = LONG[name]
+    d = prepare_case(base)
+    cfg = "case_long.cfg"
+    derive_cfg(os.path.join(d, "case.cfg"), os.path.join(d, cfg), repl)
+    out = os.path.join(d, "dump_long")
+    shutil.rmtree(out, ignore_errors=True)
+    cmd = [HARNESS, cfg, str(nit), out, str(10 ** 9)] + ([str(seed)] if seed is not None else [])
+    env = dict(os.environ, RX_CKPT=",".join(map(str, ckpt)), RX_QUIET="1", **envx)
+    log = subprocess.run(cmd, cwd=d, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if log.returncode != 0:
+        raise RuntimeError("harness failed for %s:\n%s" % (name, log.stdout[-2000:]))
+    arrs = {f[:-4]: np.load(os.path.join(out, f)) for f in sorted(os.listdir(out)) if f.startswith(("ckpt", "history_rms"))}
+    arrs["meta_json"] = np.frombuffer(json.dumps(dict(base=base, cfg=repl, env=envx, nIter=nit, seed=seed, ckpt=ckpt)).encode(), dtype=np.uint8)
+    path = os.path.join(GOLDEN, name + ".npz")
+    np.savez_compressed(path, **arrs)
+    print("wrote %s  (%.2f MB)" % (path, os.path.getsize(path) / 1e6))
+    shutil.rmtree(out, ignore_errors=True)
+
+
 def prepare_bench_case(nx=101, ny=101):
     """Case directory for `bench.py --impl reference` / cpu_baseline: the bench workload (laminar reactive NS, 3-stage RK,
     WLS gradients, AUSM 1st order) at a size the serial CPU reference finishes in seconds per iteration."""
@@ -219,10 +272,15 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["prepare"]:   # case directories only; the committed fixtures are left alone
         for n in SPECS:
             prepare_case(n)
+        for base, repl, _e, _n, _s, _c in LONG.values():
+            derive_cfg(os.path.join(CASES, base, "case.cfg"), os.path.join(CASES, base, "case_long.cfg"), repl)
         prepare_bench_case()
         sys.exit(0)
     names = sys.argv[1:] or list(SPECS)
     for n in names:
         print("== %s" % n)
-        run_case(n)
+        if n in LONG:
+            run_long(n)
+        else:
+            run_case(n)
     prepare_bench_case()

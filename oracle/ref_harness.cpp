@@ -347,6 +347,7 @@ static void apply_bcs(Ctx& c) {
 // Smooth fields + seeded noise on (T, P, u, v, Y_s, k, omega); conserved variables are rebuilt with the
 // reference's own library (ComputeEnthalpy / ComputeRgas), so the state is thermodynamically consistent.
 #include <random>
+static double g_tamp = 800.0;   // env RX_PERTURB_TAMP: peak of the temperature bump (2000 => burning-state temperatures up to 2500 K)
 static void perturb_state(Ctx& c, unsigned long seed) {
   using namespace Framework;
   ReactingModelLibrary lib(c.cfg->GetConfigLibFile(), c.cfg->GetLibraryPath());
@@ -364,7 +365,7 @@ static void perturb_state(Ctx& c, unsigned long seed) {
     std::uniform_real_distribution<double> un(-1.0, 1.0);
     double xh = (c.geo->node[p]->GetCoord(0) - x0) / (x1 - x0), yh = (c.geo->node[p]->GetCoord(1) - y0) / (y1 - y0);
     double sh = 0.5 + 0.5 * std::tanh((yh - 0.5) * 6.0);
-    double T = 500.0 + 800.0 * std::exp(-std::pow((yh - 0.5) / 0.2, 2)) * (0.6 + 0.4 * std::sin(6.283185307179586 * xh)) + 8.0 * un(gen);
+    double T = 500.0 + g_tamp * std::exp(-std::pow((yh - 0.5) / 0.2, 2)) * (0.6 + 0.4 * std::sin(6.283185307179586 * xh)) + 8.0 * un(gen);
     double P = 101325.0 * (1.0 + 0.05 * std::sin(3.0 * xh + yh)) * (1.0 + 1e-3 * un(gen));
     double u = 30.0 * 4.0 * yh * (1.0 - yh) + 3.0 * std::sin(5.0 * xh) + 0.2 * un(gen);
     double v = 2.0 * std::sin(6.283185307179586 * xh) * std::cos(3.141592653589793 * yh) + 0.2 * un(gen);
@@ -390,6 +391,54 @@ static void perturb_state(Ctx& c, unsigned long seed) {
     U[0] = rho; U[1] = rho * u; U[2] = rho * v; U[3] = rho * (h + 0.5 * (u * u + v * v) + k) - P;
     for (unsigned short s = 0; s < Ns; ++s) U[4 + s] = rho * Y[s];
     for (unsigned short q = 0; q < c.nVar; ++q) { c.flow->node[p]->SetSolution(q, U[q]); c.flow->node[p]->SetSolution_Old(q, U[q]); }
+  }
+}
+
+// ---- edge cases of the cons->prim path that a smooth state never reaches ("What's weak" #2).  Applied to the
+// host state right before iteration `it` >= 1 (env RX_POKE_ITER / RX_POKE_MODE), on disjoint point sets chosen by global index:
+//   'a'  secant start value 201 K: depending on composition and temperature the secant converges late, leaves the spline table
+//        (std::out_of_range -> 10000-step bisection, variable_direct_reactive.cpp:656-688) or fails to converge in 7 steps
+//        (32-step bisection, :698-724)
+//   'b'  secant start value Tmax - 0.4: T_old = T + 1 is outside the table at the first evaluation (exception at iteration 0)
+//   'c'  species densities scaled by 0.8: |sum Y - 1| > 0.1 -> non-physical -> Solution_Old is restored (:296-301)
+//   'd'  start value 1.2 x the stored temperature: with CLIPPING_TEMPRATURE= YES the solved T is clipped to 0.95 x that (:728-739)
+static void poke_state(Ctx& c, const std::string& mode) {
+  const bool A = mode.find('a') != std::string::npos, B = mode.find('b') != std::string::npos,
+             C = mode.find('c') != std::string::npos, D = mode.find('d') != std::string::npos;
+  unsigned long n[4] = {0, 0, 0, 0};
+  for (unsigned long p = 0; p < c.nPoint; ++p) {
+    const unsigned long gi = c.geo->node[p]->GetGlobalIndex();
+    CVariable* nd = c.flow->node[p];
+    if (A && gi % 7 == 3) { nd->GetPrimitive()[0] = 201.0; ++n[0]; }
+    else if (B && gi % 7 == 5) { nd->GetPrimitive()[0] = c.cfg->GetTemperatureMax() - 0.4; ++n[1]; }
+    else if (C && gi % 11 == 2) { for (unsigned short s = 0; s < c.nSpecies; ++s) nd->SetSolution(4 + s, 0.8 * nd->GetSolution(4 + s)); ++n[2]; }
+    else if (D && gi % 13 == 4) { nd->GetPrimitive()[0] = 1.2 * nd->GetPrimitive()[0]; ++n[3]; }
+  }
+  printf("HARNESS poke '%s': %lu / %lu / %lu / %lu points (a/b/c/d)\n", mode.c_str(), n[0], n[1], n[2], n[3]);
+#ifdef RX_WITH_GPU
+  if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->MarkHostSolutionDirty();
+#endif
+}
+static void dump_solution_old(Ctx& c, const std::string& name) {
+  std::vector<double> U(c.nPoint * c.nVar);
+  for (unsigned long p = 0; p < c.nPoint; ++p)
+    for (unsigned short v = 0; v < c.nVar; ++v) U[p * c.nVar + v] = c.flow->node[p]->GetSolution_Old()[v];
+  dump_f64(name, U, {c.nPoint, c.nVar});
+}
+// long runs (env RX_CKPT="n1,n2,..."): after n completed iterations dump the conserved state, the temperature and (RANS) k, omega, muT
+static void dump_checkpoint(Ctx& c, unsigned long nDone) {
+  char b[64]; snprintf(b, sizeof b, "ckpt%06lu_", nDone);
+  dump_solution(c, std::string(b) + "U");
+  std::vector<double> T(c.nPoint);
+  for (unsigned long p = 0; p < c.nPoint; ++p) T[p] = c.flow->node[p]->GetPrimitive(0);
+  dump_f64(std::string(b) + "T", T, {c.nPoint});
+  if (c.rans) {
+    std::vector<double> K(c.nPoint * 3);
+    for (unsigned long p = 0; p < c.nPoint; ++p) {
+      CVariable* t = c.sol[TURB_SOL]->node[p];
+      K[3 * p] = t->GetSolution(0); K[3 * p + 1] = t->GetSolution(1); K[3 * p + 2] = t->GetmuT();
+    }
+    dump_f64(std::string(b) + "kw", K, {c.nPoint, 3});
   }
 }
 
@@ -441,16 +490,26 @@ int main(int argc, char** argv) {
   js << "}\n";
   { FILE* f = fopen((g_out + "/meta.json").c_str(), "w"); fputs(js.str().c_str(), f); fclose(f); }
 
+  if (getenv("RX_PERTURB_TAMP")) g_tamp = atof(getenv("RX_PERTURB_TAMP"));
   if (argc > 5) perturb_state(c, atol(argv[5]));
+  const long pokeIter = getenv("RX_POKE_ITER") ? atol(getenv("RX_POKE_ITER")) : -1;
+  const std::string pokeMode = getenv("RX_POKE_MODE") ? getenv("RX_POKE_MODE") : "";
+  std::vector<unsigned long> ckpt;
+  if (getenv("RX_CKPT")) { std::stringstream ss(getenv("RX_CKPT")); std::string tok; while (std::getline(ss, tok, ',')) ckpt.push_back(atol(tok.c_str())); }
+  const bool quiet = getenv("RX_QUIET") != nullptr;
 
-  std::vector<double> hist;
+  for (unsigned long n : ckpt) if (n == 0) dump_checkpoint(c, 0);   // the state the run starts from
+
+  std::vector<double> hist, histAll;
   for (unsigned long it = 0; it < nIter; ++it) {
     bool dmp = it >= dump_from;
     struct timespec ts0, ts1; clock_gettime(CLOCK_MONOTONIC, &ts0);
     drv->PreprocessExtIter(it);
     c.cfg->SetGlobalParam(kind, RUNTIME_REACTIVE_SYS, it);
+    if ((long)it == pokeIter) poke_state(c, pokeMode);
     if (dmp) {
       dump_solution(c, tag(it, 0, "U0"));
+      if (pokeIter >= 0) dump_solution_old(c, tag(it, 0, "Uold"));
       dump_primitive(c, tag(it, 0, "prev_"));   // V[T] here is the secant start value (variable_direct_reactive.cpp:622)
       dump_turb(c, tag(it, 0, "turb"));
     }
@@ -483,7 +542,7 @@ int main(int argc, char** argv) {
     c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
     if (dmp) dump_primitive(c, tag(it, 0, "out_"));
     clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
-    printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
+    if (!quiet) printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {
       c.cfg->SetGlobalParam(REACTIVE_RANS, RUNTIME_TURB_SYS, it);
       drv->integration_container[ZONE_0][TURB_SOL]->SingleGrid_Iteration(drv->geometry_container, drv->solver_container,
@@ -492,9 +551,12 @@ int main(int argc, char** argv) {
       if (dmp) dump_turb_post(c, tag(it, 0, "tpost"));   // flow state at this point: the out_ dump above
     }
     double r0 = log10(c.flow->GetRes_RMS(0)), r3 = log10(c.flow->GetRes_RMS(nDim + 1));
-    printf("HARNESS it %lu  Res[Rho] %.6f  Res[RhoE] %.6f\n", it, r0, r3);
+    if (!quiet || it % 100 == 0) printf("HARNESS it %lu  Res[Rho] %.6f  Res[RhoE] %.6f\n", it, r0, r3);
     hist.push_back(r0); hist.push_back(r3);
+    for (unsigned short v = 0; v < c.nVar; ++v) histAll.push_back(c.flow->GetRes_RMS(v));
+    for (unsigned long n : ckpt) if (n == it + 1) dump_checkpoint(c, n);
   }
   dump_f64("history", hist, {(size_t)nIter, 2});
+  dump_f64("history_rms", histAll, {(size_t)nIter, (size_t)c.nVar});   // CSolver::GetRes_RMS of every variable after every iteration
   return 0;
 }

@@ -265,6 +265,19 @@ def stage_rel_err(key, a, ref, Ns):
     return vec_rel_err(a, ref)
 
 
+def pointwise_rel_err(a, ref, floor=1e-12):
+    """The metric SURVEY.md 8(d) fixes:  max_p |a - ref| / max(|ref|, floor * max_p|ref[:, v]|)  per variable (column) v —
+    every point is judged against its own reference value, with a per-variable floor so that numerically-zero entries do not
+    divide by nothing.  Columns whose reference is identically zero are judged absolutely (must be below `floor` themselves)."""
+    a = np.asarray(a, dtype=np.float64).reshape(ref.shape[0], -1)
+    r = np.asarray(ref, dtype=np.float64).reshape(ref.shape[0], -1)
+    colmax = np.abs(r).max(axis=0)
+    den = np.maximum(np.abs(r), floor * colmax[None, :])
+    err = np.abs(a - r)
+    out = np.where(den > 0, err / np.where(den > 0, den, 1.0), err / floor)
+    return out.max(axis=0)
+
+
 def vec_rel_err(a, ref):
     """Per-variable vector-relative error  max_p|a-ref| / max_p|ref|  (columns = variables)."""
     a = np.asarray(a, dtype=np.float64).reshape(ref.shape[0], -1)

@@ -19,13 +19,8 @@ CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
         "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37)}
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
-TOL_CHAINED = 1e-11   # later iterations start from states that already differ by rounding (gradients amplify by 1/dx)
-# jet_rans_perturbed reaches 1.04e-12 in the mass group at iteration 0.  Traced: glibc's pow() is
-# accurate to 0.52 ulp, not correctly rounded — for 0.08 % of temperatures its T^1.75 is the wrong neighbour (near-ties),
-# and which neighbour also depends on the FMA variant glibc selects for the host CPU; the device evaluates the correctly
-# rounded value.  A 1-ulp difference of D_ij at those points is amplified to ~1e-11 of the diffusion flux by the
-# tolerance-1e-11 Krylov solve.  The reference itself is not reproducible across hosts below this level.
-TOL_FIRST_BY_CASE = {"jet_rans_perturbed": 2e-12}
+TOL_CHAINED = 1e-12   # later iterations too: with the glibc-exact exp / pow (csrc/rx_libm.cuh) the laminar chains are bit-identical
+TOL_FIRST_BY_CASE = {}
 
 
 def _run(binary, d, out, nit, seed, env):

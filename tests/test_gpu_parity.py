@@ -10,11 +10,24 @@ species that is absent from the whole field has residuals of O(1e-29) that carry
 import numpy as np
 import pytest
 
-from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err, gpu_solver
+import json
+import os
+
+from rxcase import Case, Oracle, GOLDEN, ROOT, vec_rel_err, stage_rel_err, pointwise_rel_err, gpu_solver
 from test_oracle_golden import CASES, drive
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-12
+# Point-wise metric of SURVEY.md 8(d) (every entry against its own reference value, floor 1e-12 of the column maximum),
+# reported for every stage next to the grouped one and written to gpurun_out/parity_pointwise.json (committed copy:
+# profiles/r2_parity_pointwise.json).  With the glibc-exact exp / pow of csrc/rx_libm.cuh every stage of every laminar / Euler case
+# is BIT-IDENTICAL to the reference dump (point-wise error 0; only the RMS norms, a sum in another order, differ by 1e-15).
+# The RANS cases keep one difference: the SST closure's pivoted Householder QR sums in natural order where Eigen sums in packet
+# order, 1e-16 of the flux scale (grouped: <= 4e-18 of the column maximum) — which an entry 1e-8 times smaller than the column
+# maximum sees as 1e-8 of itself.  Those stages are asserted at TOL_POINTWISE_RANS and listed in DESIGN.md section 2.
+TOL_POINTWISE = 1e-12
+TOL_POINTWISE_RANS = 1e-7
+_REPORT = {}
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -29,11 +42,22 @@ def test_cuda_matches_reference_dumps(name):
         err = stage_rel_err(key, a, ref, case.Ns).max()
         what = key.split("_", 2)[-1]
         worst[what] = max(worst.get(what, 0.0), err)
+        pw = pointwise_rel_err(a[:case.nPointDomain] if a.shape[0] == case.nPoint else a, ref[:case.nPointDomain] if a.shape[0] == case.nPoint else ref)
+        worst_pw[what] = max(worst_pw.get(what, 0.0), float(pw.max()))
 
+    worst_pw = {}
     s = gpu_solver(case)
     drive(case, s, check)
     s.close()
     print(name, {k: float("%.2e" % v) for k, v in worst.items()})
+    print(name, "point-wise", {k: float("%.2e" % v) for k, v in worst_pw.items()})
+    _REPORT[name] = {"grouped": {k: float(v) for k, v in worst.items()}, "pointwise": {k: float(v) for k, v in worst_pw.items()}}
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    json.dump(_REPORT, open(os.path.join(out, "parity_pointwise.json"), "w"), indent=1, sort_keys=True)
+    tol_pw = TOL_POINTWISE_RANS if case.meta["cfg"]["rans"] else TOL_POINTWISE
+    bad_pw = {k: v for k, v in worst_pw.items() if not (v <= (TOL_POINTWISE if k in ("pre_V", "pre_aux", "pre_grad", "pre_lim", "dt", "res_conv", "rms") else tol_pw))}
+    assert not bad_pw, "%s: stages over the point-wise tolerance: %s" % (name, bad_pw)
     bad = {k: v for k, v in worst.items() if not (v <= TOL)}
     assert not bad, "%s: stages over tolerance: %s" % (name, bad)
     assert len(worst) >= 6

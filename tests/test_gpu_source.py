@@ -30,6 +30,26 @@ def _oracle_source(chem, rans, cMu, lb, T, rho, Y, omT, vol):
 
 
 @pytest.mark.parametrize("rans", [False, True])
+def test_source_points_match_the_reference_library(rans):
+    """Against the reference's own Framework::ReactingModelLibrary driven directly (oracle/ref_source_harness.cpp, fixture
+    tests/golden/source_points.npz by oracle/make_source_golden.py): SetSourceTerm -> Set_DfrDrhos -> AssemblePaSRConstant ->
+    GetMassProductionTerm (reacting_model_library.cpp:99-227) on the microbenchmark's own states (T up to 2500 K, 30 % pure
+    oxidiser, 10 % pure fuel).  1e-12 of the largest production rate of a species, and 1e-11 point-wise with the 1e-12 floor."""
+    pk = load_package()
+    chem = pk.load_mechanism()
+    g = np.load(rxcase.GOLDEN + "/source_points.npz")
+    want = g["res_pasr" if rans else "res_laminar"]
+    got = pk.source_points(chem, g["T"], g["rho"], g["Y"], g["vol"], omegaTurb=g["omegaTurb"], rans=rans, cMu=float(g["cMu"]), pasrLb=float(g["pasrLb"]))
+    scale = np.abs(want).max(axis=0)
+    err = np.abs(got - want).max(axis=0) / np.where(scale > 0, scale, 1.0)
+    pw = rxcase.pointwise_rel_err(got, want)
+    print("source vs reference library (rans=%s): column-relative %.3e, point-wise %.3e" % (rans, err.max(), pw.max()))
+    assert err.max() < 1e-12, err
+    assert pw.max() < 1e-11, pw
+    assert np.array_equal(got == 0.0, want == 0.0)   # the thresholds (Y < 1e-15, single species) cut at the same points
+
+
+@pytest.mark.parametrize("rans", [False, True])
 @pytest.mark.parametrize("n", [1, 4097])
 def test_source_points_host_form_matches_oracle(rans, n):
     pk = load_package()

@@ -13,7 +13,8 @@ import pytest
 
 from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 
-CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler", "channel_rans_gg"]
+CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler", "channel_rans_gg",
+         "channel_lam_edge", "channel_lam_clip", "channel_rans_ign"]
 TOL = 1e-13
 
 
@@ -23,6 +24,8 @@ def drive(case, solver, check):
     its = sorted({int(re.match(r"it(\d+)_", k).group(1)) for k in case.arr if k.startswith("it")})
     nrk = cf["nRK"] if cf["time_scheme"] == 1 else 1
     for it in its:
+        if case.has("it%04d_rk0_Uold" % it):   # Solution_Old at the start of the iteration: the non-physical fallback reads it
+            solver.set_solution(case.stage(it, 0, "Uold")); solver.set_old_solution()
         solver.set_solution(case.stage(it, 0, "U0"))
         solver.set_temperature(case.stage(it, 0, "prev_V")[:, 0])
         solver.set_turbulence(case.stage(it, 0, "turb"))
@@ -99,3 +102,31 @@ def test_oracle_turbulence_postprocessing_matches_reference(name):
         scale = np.abs(ref[:nD, c]).max()
         err = np.abs(out[:nD, c] - ref[:nD, c]).max() / (scale if scale > 0 else 1.0)
         assert err <= TOL, "%s column %s: %.3e" % (name, nm, err)
+
+
+@pytest.mark.parametrize("rans", [False, True])
+def test_oracle_source_points_match_the_reference_library(rans):
+    """rxo_source_points against the reference's own Framework::ReactingModelLibrary driven directly over independent points
+    (oracle/ref_source_harness.cpp -> tests/golden/source_points.npz): pins the restatement — and through
+    it the stand-alone source kernel — on the states of the source microbenchmark (T up to 2500 K, pure-oxidiser / pure-fuel points)."""
+    import ctypes as C
+    import rxcase
+    pk = rxcase.load_package()
+    chem = pk.load_mechanism()
+    g = np.load(GOLDEN + "/source_points.npz")
+    lib = C.CDLL(rxcase.build_oracle())
+    keep = []
+    k = lambda a: (keep.append(np.ascontiguousarray(a, dtype=np.float64)), keep[-1])[1]
+    Ns, Nr = chem["Ns"], chem["Nr"]
+    ch = rxcase._Chem(Ns, Nr, chem["nKnots"], *[rxcase._p(k(np.asarray(chem[n]).reshape(-1))) for n in
+                     ["mMasses", "diffVol", "x", "y", "y2", "As", "Betas", "Ta", "reversible", "availBack", "AsB", "BetasB", "TaB",
+                      "nuR", "nuP", "expR", "expP"]])
+    n = len(g["T"])
+    res = np.empty((n, Ns))
+    lib.rxo_source_points.restype = None
+    lib.rxo_source_points(C.byref(ch), int(rans), C.c_double(float(g["cMu"])), C.c_double(float(g["pasrLb"])), C.c_int64(n), rxcase._p(k(g["T"])),
+                          rxcase._p(k(g["rho"])), rxcase._p(k(g["Y"])), rxcase._p(k(g["omegaTurb"])), rxcase._p(k(g["vol"])), rxcase._p(res))
+    want = g["res_pasr" if rans else "res_laminar"]
+    assert np.abs(want).max() > 0
+    pw = rxcase.pointwise_rel_err(res, want)
+    assert pw.max() <= TOL, pw
