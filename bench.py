@@ -28,6 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "development-of-a-turbulent-numerical-solver-for-reactive-flows-in-su2_b200"
 RK_ALPHA = [0.66667, 0.66667, 1.0]
+CONV_KERNEL_NAME = "k_edge_flux<9> (AUSM+-up edge flux)"
 METRIC = "edge-flux+source updates/s"
 REF_CASE = os.path.join(ROOT, "oracle", "_ref", "cases", "bench_ref")
 HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
@@ -75,7 +76,7 @@ def run_reference(steps, warmup, procs=None):
     """Times oracle/_ref/ref_harness (the reference's CReactiveNSSolver & co.) on the bounded bench case."""
     if not (os.path.exists(HARNESS) and os.path.isdir(REF_CASE)):
         return None
-    procs = procs or min(os.cpu_count() or 1, 64)
+    procs = procs or min(physical_cores(), REF_PROCS)
     nit = warmup + steps
     tmp = tempfile.mkdtemp(prefix="rxref_")
     ps = []
@@ -92,15 +93,17 @@ def run_reference(steps, warmup, procs=None):
             shutil.rmtree(tmp, ignore_errors=True)
             raise RuntimeError("reference harness failed:\n" + out[-2000:])
         times.append(t[warmup:])
+        rss = [int(m.group(1)) for m in re.finditer(r"HARNESS_RSS_KB (\d+)", out)]
     meta = json.load(open(os.path.join(tmp, "p0", "dump", "meta.json")))
     shutil.rmtree(tmp, ignore_errors=True)
     nE, nP = meta["nEdge"], meta["nPointDomain"]
     units = len(RK_ALPHA) * (nE + nP)
     per_proc = [units * steps / sum(t) for t in times]
     ms = 1e3 * max(sum(t) for t in times) / steps
-    return dict(value=float(sum(per_proc)), cores=procs, ms_per_step=ms, nEdge=nE, nPoint=nP,
-                sample="%d independent serial reference processes (no MPI runtime on the box), each the 3-stage-RK laminar reactive NS "
-                       "iteration on a %d-point / %d-edge triangulated channel, %d timed iterations; aggregate updates/s" % (procs, nP, nE, steps))
+    return dict(value=float(sum(per_proc)), cores=procs, ms_per_step=ms, nEdge=nE, nPoint=nP, rss_mb=(rss[0] / 1024.0 if rss else None),
+                sample="%d independent serial reference processes, one per physical core up to %d (no MPI runtime on the box), each the 3-stage-RK laminar "
+                       "reactive NS iteration of the GPU arm's cfg on a %d-point / %d-edge triangulated channel (peak resident set %s MB per process: far "
+                       "beyond the caches), %d timed iterations; aggregate updates/s" % (procs, REF_PROCS, nP, nE, ("%.0f" % (rss[0] / 1024.0)) if rss else "?", steps))
 
 
 def bench_source(a, pk, chem, rank, world, local, dev, K, W):
@@ -318,6 +321,150 @@ def bench_turbpost(a, pk, chem, rank, world, local, dev, K, W):
         dist.destroy_process_group()
 
 
+def physical_cores():
+    """Physical core count of the host (unique (package, core) pairs of /proc/cpuinfo; logical count / 2 if that fails)."""
+    try:
+        pairs, pid, cid = set(), None, None
+        for l in open("/proc/cpuinfo"):
+            if l.startswith("physical id"):
+                pid = l.split(":")[1].strip()
+            elif l.startswith("core id"):
+                cid = l.split(":")[1].strip()
+            elif not l.strip():
+                if pid is not None and cid is not None:
+                    pairs.add((pid, cid))
+                pid = cid = None
+        if pairs:
+            return len(pairs)
+    except Exception:
+        pass
+    return max(1, (os.cpu_count() or 2) // 2)
+
+
+REF_PROCS = 8   # fixed: one serial reference process per physical core, at most 8, so that every box times the same configuration
+
+
+def measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W, full):
+    """One flow workload (laminar or RANS) on this rank's mesh: W warm-up iterations from the synthetic state, then K timed
+    iterations that ALL start from the same warmed state (rx_state_snapshot: device-to-device restore outside the CUDA events),
+    so the timed work does not depend on K.  Returns a dict of local measurements (the caller reduces over ranks)."""
+    import torch
+    import torch.distributed as dist
+    opts = pk.default_opts(rans=rans, cfl=0.1)
+    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=rans, glob_xy=plan.get("bbox"))
+    solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
+    ex = par.HaloExchanger(par.GpuHaloState(solver), plan, dev)
+    nOwn, nE = solver.nPointDomain, solver.nEdge
+    own = np.zeros(solver.nPoint, dtype=bool); own[:nOwn] = True
+    en = mesh["edgeNodes"]
+    nE_counted = int(own[en[:, 0]].sum())   # an edge shared with a neighbour partition is counted once (by the owner of its first node)
+    units_local = len(RK_ALPHA) * (nE_counted + nOwn)
+    Uh = torch.empty((solver.nPoint, solver.nVar), dtype=torch.float64).pin_memory()
+    Uh.numpy()[:] = U0
+    solver.SetSolutionPtr(Uh.data_ptr()); solver.SetTemperature(T0); solver.SetTurbulence(turb)
+
+    def step(it, want_rms=False):
+        if world > 1:
+            return par.distributed_iterate(solver, ex, it, RK_ALPHA, last_rms=want_rms)
+        return solver.Iterate(it, RK_ALPHA, want_rms=want_rms)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    it = 1
+    for _ in range(max(W, 3)):
+        step(it); it += 1
+    solver.SaveState()                       # the state every timed step starts from
+    l0 = solver.LaunchCount()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for e0, e1 in ev:
+        solver.RestoreState()
+        e0.record()
+        step(it)
+        e1.record()
+    barrier()
+    per_step = [e0.elapsed_time(e1) for e0, e1 in ev]
+    ms_dev = float(sum(per_step) / K)
+    clocks = sampler.stop()
+    launches = solver.LaunchCount() - l0
+    out = dict(solver=solver, units_local=units_local, ms_dev=ms_dev, ms_step_min=float(min(per_step)), ms_step_max=float(max(per_step)),
+               launches=int(launches), clocks=clocks, nOwn=nOwn, nE=nE, nPoint=solver.nPoint, nVar=solver.nVar)
+    solver.RestoreState()
+    rms = step(it, want_rms=True)
+    if not np.all(np.isfinite(rms)):
+        raise SystemExit("bench.py: non-finite residual after the timed region")
+    out["rms_rho"] = float(rms[0])
+    if solver.opts["viscous"]:
+        _o, key = solver.EdgeOrder()         # BiCGSTAB iterations of every edge's Stefan-Maxwell solve in the timed state: the work is fixed
+        hist = np.bincount(key.astype(np.int64) % 19, minlength=19)
+        out["sm_iterations_histogram"] = {str(k): int(v) for k, v in enumerate(hist) if v}
+    if not full:
+        return out
+    # End to end through the public call with HOST buffers, the same iteration from the same state: the secant start values and the
+    # edge order are restored on the device, the conserved state comes from pinned host memory (rx_set_solution, H2D), the iteration
+    # runs, the residual norms AND the updated conserved state go back to pinned host memory (rx_get_solution, D2H).
+    solver.RestoreState()
+    solver.GetSolutionPtr(Uh.data_ptr())     # host copy of the timed state
+    Ur = torch.empty((solver.nPoint, solver.nVar), dtype=torch.float64).pin_memory()
+    for _ in range(2):
+        solver.RestoreState(); solver.SetSolutionPtr(Uh.data_ptr()); step(it, want_rms=True); solver.GetSolutionPtr(Ur.data_ptr())
+    barrier()
+    t0 = time.perf_counter()
+    Ke = max(3, min(K, 10))
+    for _ in range(Ke):
+        solver.RestoreState()
+        solver.SetSolutionPtr(Uh.data_ptr())
+        step(it, want_rms=True)
+        solver.GetSolutionPtr(Ur.data_ptr())
+    barrier()
+    out["ms_e2e"] = 1e3 * (time.perf_counter() - t0) / Ke
+    out["fp64_peak"] = solver.Fp64Peak()
+    out["kt"] = {n: solver.KernelTime(w, 5) for n, w in [("edge_flux_visc", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("transport", 7), ("gradient", 4), ("update", 6)]}
+    return out
+
+
+def reduce_flow(m, world, dev):
+    import torch
+    import torch.distributed as dist
+    tt = torch.tensor([m["ms_dev"], m.get("ms_e2e", 0.0), float(m["units_local"])], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        return float(mx[0]), float(mx[1]), float(sm[2])
+    return float(tt[0]), float(tt[1]), float(tt[2])
+
+
+def measure_source(pk, chem, rank, world, local, dev, n, K):
+    """configs[3] in short form for the default line: device-timed passes of k_source_points over n resident points per GPU."""
+    import torch
+    base = min(n, 4_000_000)
+    T, rho, Y, omT, vol = pk.synthetic_points(chem, base, seed=12345 + rank)
+    reps = (n + base - 1) // base
+    t = lambda x: torch.as_tensor(np.ascontiguousarray(x), device=dev)
+    tile = lambda x: t(x).repeat(reps)[:n].contiguous()
+    dT, dr, dO, dV = tile(T), tile(rho), tile(omT), tile(vol)
+    dY = t(Y.T).repeat(1, reps)[:, :n].contiguous()
+    dR = torch.empty((chem["Ns"], n), dtype=torch.float64, device=dev)
+    solver = pk.CReactiveNSSolverGPU(pk.channel_mesh(5, 4), chem, pk.default_opts(rans=True), device=local)
+    f = lambda: solver.SourcePointsDev(n, dT.data_ptr(), dr.data_ptr(), dY.data_ptr(), dO.data_ptr(), dV.data_ptr(), dR.data_ptr())
+    for _ in range(3):
+        f()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        f()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / K
+    ok = bool(torch.isfinite(dR).all())
+    solver.close()
+    return ms, ok
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -327,6 +474,7 @@ def main():
     ap.add_argument("--nx", type=int, default=1415)
     ap.add_argument("--ny", type=int, default=1415)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-workloads", action="store_true", help="skip the short RANS and source-term measurements embedded in the default line")
     ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source", "turbpost"],
                     help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share); "
                          "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3]); "
@@ -336,9 +484,9 @@ def main():
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 0); K = max(a.steps, 1)
     rans = a.workload == "rans"
-    workload = "laminar reactive NS (9 species, 2 reactions), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + Arrhenius source, WLS gradients"
-    if rans:
-        workload = "reactive RANS (9 species, 2 reactions, SST fields as inputs), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + SST closure + Arrhenius/PaSR source, WLS gradients"
+    WL = {False: "laminar reactive NS (9 species, 2 reactions), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + Arrhenius source, WLS gradients",
+          True: "reactive RANS (9 species, 2 reactions, SST fields as inputs), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + SST closure + Arrhenius/PaSR source, WLS gradients"}
+    workload = WL[rans]
 
     if a.impl == "reference":
         if rank != 0:
@@ -346,15 +494,17 @@ def main():
         if rans or a.workload in ("source", "turbpost"):
             print(json.dumps({"impl": "reference", "unavailable": "the reference arm is prepared for the laminar bench workload (configs[1]) only"}))
             return
-        r = run_reference(K, W)
+        r = run_reference(K, W, procs=min(physical_cores(), REF_PROCS))
         if r is None:
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_harness or its case directory is missing (run oracle/build_ref.sh and oracle/make_golden.py in the build container)"}))
             return
         print(json.dumps({
             "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "updates/s", "n_gpus": a.gpus, "steps": K, "warmup": W,
             "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload, "points": r["nPoint"], "edges": r["nEdge"], "rk_stages": len(RK_ALPHA)},
-            "cpu_baseline": {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"]},
+            "config": {"workload": workload, "points": r["nPoint"], "edges": r["nEdge"], "rk_stages": len(RK_ALPHA),
+                       "sample_note": "same cfg and mesh generator as the GPU arm at a bounded size (the CPU reference needs ~20 us per update: the 4.0M-cell mesh takes minutes per iteration); throughput is per update, see cpu_baseline.sample"},
+            "cpu_baseline": {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
+                             "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb")},
             "e2e": {"value": r["value"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
@@ -375,80 +525,36 @@ def main():
         return bench_source(a, pk, chem, rank, world, local, dev, K, W)
     if a.workload == "turbpost":
         return bench_turbpost(a, pk, chem, rank, world, local, dev, K, W)
-    opts = pk.default_opts(rans=rans, cfl=0.1)
     nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
     if world > 1:
         mesh, plan = pk.channel_strip_mesh(nxg, a.ny, rank, world)
     else:
         mesh = pk.channel_mesh(a.nx, a.ny); plan = dict(send={}, recv={}, bbox=None)
-    U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=rans, glob_xy=plan.get("bbox"))
-    solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
-    ex = par.HaloExchanger(par.GpuHaloState(solver), plan, dev)
-    nOwn, nE = solver.nPointDomain, solver.nEdge
-    own = np.zeros(solver.nPoint, dtype=bool); own[:nOwn] = True
-    en = mesh["edgeNodes"]
-    # an edge shared with a neighbour partition is counted once (by the owner of its first node)
-    nE_counted = int(own[en[:, 0]].sum())
-    units_local = len(RK_ALPHA) * (nE_counted + nOwn)
-    Uh = torch.empty((solver.nPoint, solver.nVar), dtype=torch.float64).pin_memory()
-    Uh.numpy()[:] = U0
-    solver.SetSolutionPtr(Uh.data_ptr()); solver.SetTemperature(T0); solver.SetTurbulence(turb)
-
-    def step(it, want_rms=False):
+    m = measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W, full=True)
+    ms_dev, ms_e2e, units = reduce_flow(m, world, dev)
+    solver = m["solver"]; kt = m["kt"]; nOwn, nE = m["nOwn"], m["nE"]; clocks = m["clocks"]; launches = m["launches"]
+    solver_fp64_peak = m["fp64_peak"]
+    extra = {}
+    if a.workload == "laminar" and not a.no_extra_workloads:
+        solver.close()
+        # the other two device workloads of BASELINE.json in short form, so that the driver's records carry them (full lines: --workload rans / source)
+        Kx = max(3, min(K, 5))
+        mr = measure_flow(pk, par, chem, mesh, plan, True, rank, world, local, dev, Kx, 3, full=False)
+        r_ms, _e, r_units = reduce_flow(mr, world, dev)
+        r_kt = mr["solver"].KernelTime(0, 3)
+        mr["solver"].close()
+        extra["rans"] = {"metric": METRIC, "value": r_units / (r_ms * 1e-3), "unit": "updates/s", "ms_per_step": r_ms, "steps": Kx, "n_gpus": world,
+                         "workload": WL[True], "turbulence": "SST fields (mu_t, k, omega, grad k) are inputs frozen during the timed iterations",
+                         "edge_flux_visc_ms": r_kt, "sm_iterations_histogram": mr.get("sm_iterations_histogram"), "gpu_launches": mr["launches"]}
+        torch.cuda.empty_cache()
+        npts = 64_000_000 if a.nx >= 1000 else 1_000_000
+        s_ms, s_ok = measure_source(pk, chem, rank, world, local, dev, npts, Kx)
+        tt = torch.tensor([s_ms], dtype=torch.float64, device=dev)
         if world > 1:
-            return par.distributed_iterate(solver, ex, it, RK_ALPHA, last_rms=want_rms)
-        return solver.Iterate(it, RK_ALPHA, want_rms=want_rms)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    it = 1
-    for _ in range(max(W, 3)):
-        step(it); it += 1
-    l0 = solver.LaunchCount()
-    sampler = ClockSampler(local); sampler.start()
-    barrier()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(K):
-        step(it); it += 1
-    e1.record()
-    barrier()
-    ms_dev = e0.elapsed_time(e1) / K
-    clocks = sampler.stop()
-    launches = solver.LaunchCount() - l0
-    rms = step(it, want_rms=True); it += 1
-    if not np.all(np.isfinite(rms)):
-        raise SystemExit("bench.py: non-finite residual after the timed region")
-
-    # end to end through the public call with HOST buffers: H2D of the conserved state from pinned memory (rx_set_solution),
-    # the iteration, D2H of the residual norms (the step's result)
-    solver.SetTemperature(T0)
-    for _ in range(2):
-        solver.SetSolutionPtr(Uh.data_ptr()); ex.exchange(par.WHAT_SOLUTION); step(it, want_rms=True)
-    barrier()
-    t0 = time.perf_counter()
-    Ke = max(3, min(K, 10))
-    for _ in range(Ke):
-        solver.SetSolutionPtr(Uh.data_ptr())
-        if world > 1:
-            ex.exchange(par.WHAT_SOLUTION)
-        r = step(it, want_rms=True)
-    barrier()
-    ms_e2e = 1e3 * (time.perf_counter() - t0) / Ke
-
-    # dominant kernel: viscous (Stefan-Maxwell) edge flux, timed alone with CUDA events on the launching stream
-    solver_fp64_peak = solver.Fp64Peak()
-    kt = {n: solver.KernelTime(w, 5) for n, w in [("edge_flux_visc", 0), ("edge_flux_conv", 1), ("accumulate_source", 2), ("primitive", 3), ("transport", 7), ("gradient", 4), ("update", 6)]}
-    tt = torch.tensor([ms_dev, ms_e2e, float(units_local)], dtype=torch.float64, device=dev)
-    if world > 1:
-        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms_dev, ms_e2e, units = float(mx[0]), float(mx[1]), float(sm[2])
-    else:
-        units = float(units_local)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        extra["source"] = {"metric": "source-point updates/s", "value": world * npts / (float(tt[0]) * 1e-3), "unit": "updates/s", "ms_per_step": float(tt[0]),
+                           "points_per_gpu": npts, "steps": Kx, "n_gpus": world, "finite": s_ok,
+                           "workload": "isolated Arrhenius + PaSR source term (9 species, 2 reactions) over independent points resident in HBM"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -460,51 +566,70 @@ def main():
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    # Dominant kernel: the viscous Stefan-Maxwell edge flux.  SURVEY.md 8(d) bounds it by the FP64 pipe, not by HBM:
-    # 1.5e4 FP64 operations per edge (reference operation sequence, FMA = 2; profiles/r1_summary.md measures 1.65e4 on the
-    # thread-per-edge kernel that follows it) against 24 + 608/3 = 226.7 compulsory bytes per edge.  The FP64 roof is measured
-    # here, on this device, by a DFMA loop (rx_fp64_peak).  The HBM view of the same kernel and the convective AUSM kernel
-    # (HBM-bound: 24 + (128 + 104)/(E/P) bytes per edge) are carried next to it.
+    # Dominant kernel: the viscous Stefan-Maxwell edge flux.  SURVEY.md 8(d) bounds it by the FP64 pipe, not by HBM.  Two operation
+    # counts per edge are carried: the reference operation sequence (SURVEY.md's estimate, FMA = 2) and the FP64 operations the kernel
+    # EXECUTES, counted by ncu (smsp__sass_thread_inst_executed_op_dadd/dmul/dfma_pred_on of the committed capture of this kernel at
+    # this mesh size, profiles/r2_traffic.json); `achieved` uses the executed count when the capture matches the mesh.  The FP64 roof is
+    # measured here, on this device, by a DFMA loop (rx_fp64_peak; MEASURED_PEAKS.json has no FP64 entry).  The HBM view of the same kernel
+    # and the convective AUSM pass (HBM-bound) are carried next to it.
     fp64_peak = solver_fp64_peak
-    flops_per_edge = 1.7e4 if rans else 1.5e4   # RANS: + the 9x9 pivoted Householder QR with two right-hand sides of the SST closure
+    flops_ref = 1.7e4 if rans else 1.5e4
     bytes_visc = 24.0 + (400.0 + 208.0) / (nE / float(nOwn))
     bytes_conv = 24.0 + (128.0 + 104.0) / (nE / float(nOwn))
     t_visc, t_conv = kt["edge_flux_visc"] * 1e-3, kt["edge_flux_conv"] * 1e-3
+    traffic, flops_exec, prof_src = None, None, None
+    for f in ("r2_traffic.json", "r1_traffic.json"):
+        try:   # dram bytes and executed FP64 operations of one launch from the committed ncu capture of this kernel at this workload size
+            pr = json.load(open(os.path.join(ROOT, "profiles", f)))
+            if pr.get("edges") == nE:
+                q = pr.get("k_edge_visc_pair_rans" if rans else "k_edge_visc_pair")
+                if isinstance(q, dict):
+                    traffic, flops_exec = q.get("dram_bytes"), q.get("fp64_flops_per_edge")
+                else:
+                    traffic = q
+                prof_src = "profiles/" + f
+                break
+        except Exception:
+            pass
+    flops_per_edge = flops_exec or flops_ref
     ach_tf = flops_per_edge * nE / t_visc / 1e12
     ach_hbm_visc = bytes_visc * nE / t_visc / 1e9
     ach_hbm_conv = bytes_conv * nE / t_conv / 1e9
-    traffic = None
-    try:   # dram__bytes_read+write of one launch from the committed ncu capture of this kernel at this workload size
-        pr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-        if pr.get("edges") == nE:
-            traffic = pr.get("k_edge_visc_pair_rans" if rans else "k_edge_visc_pair")
-    except Exception:
-        pass
     line = {
         "metric": METRIC, "value": units / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload, "points_per_gpu": nOwn, "edges_per_gpu": nE, "cells_per_gpu": 2 * (a.nx - 1) * (a.ny - 1), "rk_stages": len(RK_ALPHA),
-                   "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (solver.nPoint * 8 * 160 / 1e9),
+                   "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (m["nPoint"] * 8 * 160 / 1e9),
+                   "timed_state": "every timed step is the same iteration from the same state: the state after the warm-up iterations, restored device-to-device "
+                                  "(rx_state_snapshot) before each step, outside the CUDA events; ms_per_step = mean of the per-step event times",
                    "partition": "strips in x, one halo layer, NCCL send/recv of U and gradients" if world > 1 else "single partition"},
         "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": int(solver.nPoint * solver.nVar * 8), "d2h_bytes_per_step": int(solver.nVar * 8)},
+                "h2d_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8), "d2h_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8 + m["nVar"] * 8),
+                "what": "same iteration from the same state as `value`: conserved state H2D from pinned host memory (rx_set_solution), rx_iterate, residual norms and the UPDATED conserved state D2H to pinned host memory (rx_get_solution)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
+        "step_ms_min_max": [m["ms_step_min"], m["ms_step_max"]],
+        "sm_iterations_histogram": m.get("sm_iterations_histogram"),
         "roofline": {"kernel": "k_edge_visc_pair<9,%s> (Stefan-Maxwell/BiCGSTAB viscous edge flux%s, two lanes per edge)" % ("true" if rans else "false", " + SST closure (pivoted QR)" if rans else ""),
                      "bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak if fp64_peak else None,
-                     "traffic": traffic,
+                     "traffic": traffic, "traffic_source": prof_src,
                      "peak_source": "DFMA loop measured in this run (rx_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
-                     "flops_per_edge": flops_per_edge, "bytes_per_edge": bytes_visc,
+                     "flops_per_edge": flops_per_edge, "flops_per_edge_source": ("executed FP64 operations counted by ncu, " + str(prof_src)) if flops_exec else "reference operation sequence (SURVEY.md 8(d) estimate)",
+                     "flops_per_edge_reference_sequence": flops_ref, "frac_reference_sequence": flops_ref * nE / t_visc / 1e12 / fp64_peak if fp64_peak else None,
+                     "bytes_per_edge": bytes_visc,
                      "hbm_view": {"achieved": ach_hbm_visc, "peak": hbm, "unit": "GB/s", "frac": ach_hbm_visc / hbm, "peak_source": hbm_src},
-                     "conv_kernel": {"kernel": "k_edge_flux<9,conv> (AUSM+-up edge flux)", "bound": "hbm", "achieved": ach_hbm_conv, "peak": hbm,
+                     "conv_kernel": {"kernel": CONV_KERNEL_NAME, "bound": "hbm", "achieved": ach_hbm_conv, "peak": hbm,
                                      "unit": "GB/s", "frac": ach_hbm_conv / hbm, "bytes_per_edge": bytes_conv, "peak_source": hbm_src}},
         "kernel_ms": kt,
     }
+    if extra:
+        line["workloads"] = extra
     if world == 1 and not a.no_cpu_baseline and not rans:
         try:
-            r = run_reference(2, 1)
+            r = run_reference(2, 1, procs=min(physical_cores(), REF_PROCS))
             if r:
-                line["cpu_baseline"] = {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"]}
+                line["cpu_baseline"] = {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
+                                        "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb")}
         except Exception as e:   # the baseline is a reported number, never a reason to lose the GPU line
             line["cpu_baseline"] = {"value": None, "unit": "updates/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % str(e)[:200]}
     print(json.dumps(line))

@@ -32,6 +32,7 @@ struct rx_ctx {
   ChemC<9> cc9{};
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
+  std::vector<void*> snap;          // rx_state_snapshot: device copies of the evolving state, same order as snapshot_fields()
   bool allocFailed = false;         // any cudaMalloc / cudaMemset / cudaMemcpy of dalloc / dupload failed (checked at the end of rx_create)
   double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr, *pmax = nullptr, *resMax = nullptr;
   int *pidx = nullptr, *resMaxPoint = nullptr;
@@ -328,6 +329,33 @@ void rx_destroy(rx_ctx* c) {
   if (c->evJoin) cudaEventDestroy(c->evJoin);
   if (c->bcStream) cudaStreamDestroy(c->bcStream);
   delete c;
+}
+
+// The evolving state of a context: what one iteration reads from the previous one.  Saved / restored device-to-device so that a
+// measurement can run the SAME iteration from the SAME state any number of times (bench.py: the timed value must not depend on
+// how many steps are timed).  No reference counterpart (the reference has no such need).
+static std::vector<std::pair<void*, size_t>> snapshot_fields(rx_ctx* c) {
+  const Dev& d = c->d;
+  const size_t np = d.np, ne = d.ne, w = sizeof(double);
+  std::vector<std::pair<void*, size_t>> f = {{d.U, np * c->nVar * w}, {d.Uold, np * c->nVar * w}, {d.V, np * c->nPrim * w}, {d.turb, np * 6 * w}};
+  if (d.eKey) f.push_back({d.eKey, ne});
+  if (c->eOrderBuf) f.push_back({c->eOrderBuf, ne * sizeof(int)});
+  if (c->tpost) f.push_back({c->tpost, np * TP_N * w});
+  return f;
+}
+int rx_state_snapshot(rx_ctx* c, int restore) {
+  const auto f = snapshot_fields(c);
+  if (!restore && c->snap.empty()) {
+    for (const auto& q : f) {
+      void* p = nullptr;
+      RX_CK(cudaMalloc(&p, q.second));
+      c->allocs.push_back(p); c->snap.push_back(p);
+    }
+  }
+  if (c->snap.size() != f.size()) { c->err = "rx_state_snapshot: restore before any save"; return RX_ERR_ARG; }
+  for (size_t k = 0; k < f.size(); ++k)
+    RX_CK(cudaMemcpyAsync(restore ? f[k].first : c->snap[k], restore ? c->snap[k] : f[k].first, f[k].second, cudaMemcpyDeviceToDevice, c->stream));
+  return RX_OK;
 }
 
 int rx_set_stream(rx_ctx* c, void* s) { c->stream = (cudaStream_t)s; return RX_OK; }

@@ -77,7 +77,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval"]
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot"]
 
 _lib = None
 
@@ -335,6 +335,13 @@ class CReactiveNSSolverGPU:
         """Device-pointer form of source_points (SoA Y[Ns][n], res[Ns][n]); constants (rans, C_mu, PaSR bound) are the context's."""
         v = lambda p: C.c_void_p(p) if p else None
         self._ck(self.lib.rx_source_points_dev(self.ctx, C.c_int64(n), v(T_ptr), v(rho_ptr), v(Y_ptr), v(omegaTurb_ptr), v(vol_ptr), v(res_ptr)))
+
+    def SaveState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 0))
+    def RestoreState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 1))
+
+    def GetSolutionPtr(self, host_ptr):
+        """rx_get_solution into a raw host address (e.g. a pinned torch tensor's data_ptr())."""
+        self._ck(self.lib.rx_get_solution(self.ctx, C.c_void_p(host_ptr)))
 
     def Synchronize(self): self._ck(self.lib.rx_synchronize(self.ctx))
     def LaunchCount(self): return int(self.lib.rx_launch_count(self.ctx))

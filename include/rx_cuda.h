@@ -193,6 +193,11 @@ int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoi
                       int refinePasses, int64_t* owner, int64_t* edgeCut);
 int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld);
 
+/* measurement hook (no reference counterpart): save (restore = 0) or restore (restore = 1) the evolving state of the context — U,
+ * U_old, V (with the secant start temperature), the turbulence fields, the viscous kernel's edge order — device to device, on the
+ * context's stream, so that the same iteration can be timed from the same state any number of times. */
+int rx_state_snapshot(rx_ctx*, int restore);
+
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 int64_t rx_launch_count(rx_ctx*);
 

@@ -255,7 +255,7 @@ def run_long(name):
     shutil.rmtree(out, ignore_errors=True)
 
 
-def prepare_bench_case(nx=101, ny=101):
+def prepare_bench_case(nx=151, ny=151):
     """Case directory for `bench.py --impl reference` / cpu_baseline: the bench workload (laminar reactive NS, 3-stage RK,
     WLS gradients, AUSM 1st order) at a size the serial CPU reference finishes in seconds per iteration."""
     d = prepare_case_dir("bench_ref", nx=nx, ny=ny, stretch=1.0)

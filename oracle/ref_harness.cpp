@@ -21,6 +21,7 @@
 #include <cstring>
 #endif
 #include <cstdio>
+#include <cstring>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -555,6 +556,12 @@ int main(int argc, char** argv) {
     hist.push_back(r0); hist.push_back(r3);
     for (unsigned short v = 0; v < c.nVar; ++v) histAll.push_back(c.flow->GetRes_RMS(v));
     for (unsigned long n : ckpt) if (n == it + 1) dump_checkpoint(c, n);
+  }
+  {   // peak resident set of this process (bench.py reports it next to the CPU timing: the working set is far beyond the caches)
+    FILE* f = fopen("/proc/self/status", "r");
+    char line[256];
+    while (f && fgets(line, sizeof line, f)) if (!strncmp(line, "VmHWM:", 6)) printf("HARNESS_RSS_KB %ld\n", atol(line + 6));
+    if (f) fclose(f);
   }
   dump_f64("history", hist, {(size_t)nIter, 2});
   dump_f64("history_rms", histAll, {(size_t)nIter, (size_t)c.nVar});   // CSolver::GetRes_RMS of every variable after every iteration
