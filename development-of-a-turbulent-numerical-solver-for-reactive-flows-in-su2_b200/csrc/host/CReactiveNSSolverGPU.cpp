@@ -333,3 +333,18 @@ void CReactiveNSSolverGPU::ExplicitEuler_Iteration(CGeometry* geometry, CSolver*
 void CReactiveNSSolverGPU::ExplicitRK_Iteration(CGeometry* geometry, CSolver**, CConfig* config, unsigned short iRKStep) {
   Update(geometry, config->Get_Alpha_RKStep(iRKStep));
 }
+
+void CReactiveNSSolverGPU::WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename) {
+  std::vector<int64_t> gi(nPoint);
+  for (unsigned long p = 0; p < nPoint; ++p) gi[p] = (int64_t)geometry->node[p]->GetGlobalIndex();
+  std::vector<double> kw;
+  if (ransMode) {
+    kw.resize((size_t)nPoint * 2);
+    for (unsigned long p = 0; p < nPoint; ++p) { kw[2 * p] = solver_container[TURB_SOL]->node[p]->GetSolution(0); kw[2 * p + 1] = solver_container[TURB_SOL]->node[p]->GetSolution(1); }
+  }
+  rx_restart_info info{};
+  info.aoa = config->GetAoA() - config->GetAoA_Offset(); info.sideslip = config->GetAoS() - config->GetAoS_Offset();
+  info.bcThrust = config->GetInitial_BCThrust(); info.dCD_dCL = config->GetdCD_dCL();
+  info.extIter = (int64_t)(config->GetExtIter() + config->GetExtIter_OffSet() + 1);
+  Check(rx_restart_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, &info, 0), "rx_restart_write");
+}

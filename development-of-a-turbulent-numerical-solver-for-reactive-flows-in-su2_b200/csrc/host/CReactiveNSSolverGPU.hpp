@@ -13,6 +13,7 @@
 #include "solver_reactive.hpp"
 #include "rx_cuda.h"
 
+#include <string>
 #include <vector>
 
 class CReactiveNSSolverGPU : public CReactiveNSSolver {
@@ -47,6 +48,11 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void ExplicitEuler_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config) override;
   void ExplicitRK_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config,
                             unsigned short iRKStep) override;
+
+  // COutput::SetRestart for this solver, straight from the device state (rx_restart_write): the same bytes the reference's
+  // MergeSolution + SetRestart produce (output_structure.cpp:1991-2130, 3858-4060) without mirroring the state into node[].
+  // One call in COutput::SetResult_Files replaces the pair for a CReactiveNSSolverGPU flow solver.
+  void WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);
 
   // node[]->Solution was changed on the host (restart, initial condition): upload before the next stage
   void MarkHostSolutionDirty() { hostDirty = true; }

@@ -882,5 +882,8 @@ extern "C" int rx_libm_eval(int which, int64_t n, const double* x, const double*
   return rc;
 }
 
+// SU2 native restart files from / into the device-resident state (COutput::SetRestart, Load_Restart)
+#include "rx_restart.cuh"
+
 // allocation-free residual norms over a static device scratch array (its own entry point; no existing path uses it)
 #include "rx_noalloc.cuh"

@@ -70,6 +70,29 @@ class _Opts(C.Structure):
                 ("device", C.c_int)]
 
 
+class _RestartInfo(C.Structure):
+    _fields_ = [("aoa", C.c_double), ("sideslip", C.c_double), ("bcThrust", C.c_double), ("dCD_dCL", C.c_double), ("extIter", C.c_int64)]
+
+
+def merge_restart_pieces(pieces, path, header_from, ext_iter=0, aoa=0.0, sideslip=0.0, bc_thrust=4000.0, dcd_dcl=0.0):
+    """Per-partition pieces (WriteRestart(piece=True)) -> one restart file ordered by PointID, as COutput::MergeSolution + SetRestart
+    leave it on the master rank.  header_from: a solver of the run (for the column names)."""
+    lines = []
+    for p in pieces:
+        with open(p, "rb") as f:
+            lines += [l for l in f.read().split(b"\n") if l]
+    lines.sort(key=lambda l: int(l.split(b"\t", 1)[0]))
+    nCons = header_from.nVar + (2 if header_from.opts["rans"] else 0)
+    h = '"PointID"\t"x"\t"y"' + "".join('\t"Conservative_%d"' % (v + 1) for v in range(nCons)) + '\t"Pressure"\t"Temperature"\t"Mach"'
+    if header_from.opts["viscous"]:
+        h += '\t"Laminar_Viscosity"'
+    if header_from.opts["rans"]:
+        h += '\t"<greek>m</greek><sub>t</sub>"'
+    with open(path, "wb") as f:
+        f.write(h.encode() + b"\n" + b"\n".join(lines) + b"\n")
+        f.write(("AOA= %.15e\nSIDESLIP_ANGLE= %.15e\nINITIAL_BCTHRUST= %.15e\nDCD_DCL_VALUE= %.15e\nEXT_ITER= %d\n" % (aoa, sideslip, bc_thrust, dcd_dcl, ext_iter)).encode())
+
+
 EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "rx_set_stream", "rx_synchronize",
            "rx_set_solution", "rx_set_temperature", "rx_set_turbulence", "rx_get_solution", "rx_get_primitive", "rx_get_dt",
            "rx_get_residual", "rx_preprocess", "rx_set_old_solution", "rx_time_step", "rx_residual_conv", "rx_residual_visc",
@@ -77,7 +100,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot"]
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read"]
 
 _lib = None
 
@@ -335,6 +358,24 @@ class CReactiveNSSolverGPU:
         """Device-pointer form of source_points (SoA Y[Ns][n], res[Ns][n]); constants (rans, C_mu, PaSR bound) are the context's."""
         v = lambda p: C.c_void_p(p) if p else None
         self._ck(self.lib.rx_source_points_dev(self.ctx, C.c_int64(n), v(T_ptr), v(rho_ptr), v(Y_ptr), v(omegaTurb_ptr), v(vol_ptr), v(res_ptr)))
+
+    def WriteRestart(self, path, kOmega=None, globalIndex=None, ext_iter=0, piece=False, aoa=0.0, sideslip=0.0, bc_thrust=4000.0, dcd_dcl=0.0):
+        """COutput::SetRestart from the device state (rx_restart_write): the SU2 native ASCII restart file."""
+        info = _RestartInfo(aoa, sideslip, bc_thrust, dcd_dcl, int(ext_iter))
+        kw = _c(kOmega) if kOmega is not None else None
+        gi = _c(globalIndex, np.int64) if globalIndex is not None else None
+        self._ck(self.lib.rx_restart_write(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, _d(kw) if kw is not None else None,
+                                           C.byref(info), int(bool(piece))))
+
+    def LoadRestart(self, path, globalIndex=None, nGlobal=0):
+        """CReactiveNSSolver::Load_Restart + the turbulence reader (rx_restart_read): sets the conserved state from the file; returns
+        ((k, omega)[nPoint][2] or None, dict of the trailer values)."""
+        info = _RestartInfo()
+        kw = np.zeros((self.nPoint, 2)) if self.opts["rans"] else None
+        gi = _c(globalIndex, np.int64) if globalIndex is not None else None
+        self._ck(self.lib.rx_restart_read(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, C.c_int64(nGlobal),
+                                          _d(kw) if kw is not None else None, C.byref(info)))
+        return kw, dict(aoa=info.aoa, sideslip=info.sideslip, bcThrust=info.bcThrust, dCD_dCL=info.dCD_dCL, extIter=info.extIter)
 
     def SaveState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 0))
     def RestoreState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 1))

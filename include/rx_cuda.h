@@ -193,6 +193,21 @@ int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoi
                       int refinePasses, int64_t* owner, int64_t* edgeCut);
 int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld);
 
+/* SU2 native ASCII restart files straight from / into the device-resident state (csrc/rx_restart.cuh).
+ * rx_restart_write replaces COutput::SetRestart for the reactive solvers (output_structure.cpp:3858-4060; columns of MergeSolution
+ * :1991-2130): "PointID" x y Conservative_1..nVar [k omega] Pressure Temperature Mach [Laminar_Viscosity [mu_t]], every value as
+ * C++ `scientific` with precision 15, then the trailer (AOA, SIDESLIP_ANGLE, INITIAL_BCTHRUST, DCD_DCL_VALUE, EXT_ITER) — byte for byte the
+ * file the reference writes for the same state (tests/test_gpu_restart.py).  Primitive columns are those of the last rx_preprocess.
+ * globalIndex[nPoint] (NULL = identity) gives the PointID of every local point; kOmega[nPoint][2] is the turbulence solution (RANS;
+ * it lives in CTurbSSTSolver) ; piece != 0 writes the owned points' lines only (no header / trailer) for per-partition writers,
+ * merged by PointID afterwards.  The fields are staged through pinned memory in chunks: no host mirror of the state is needed.
+ * rx_restart_read replaces CReactiveNSSolver::Load_Restart (solver_direct_reactive.cpp:4390-4520) and the turbulence reader
+ * (solver_direct_turbulent.cpp:1046-1064): conserved variables of every local point (halo points included) are set from the file,
+ * kOmega (may be NULL) receives (k, omega); fails with the reference's message if the file does not cover the owned points. */
+typedef struct { double aoa, sideslip, bcThrust, dCD_dCL; int64_t extIter; } rx_restart_info;
+int rx_restart_write(rx_ctx*, const char* path, const int64_t* globalIndex, const double* kOmega, const rx_restart_info* info /* NULL: zeros, INITIAL_BCTHRUST 4000 */, int piece);
+int rx_restart_read(rx_ctx*, const char* path, const int64_t* globalIndex, int64_t nGlobal /* points in the file; <= 0: nPointDomain */, double* kOmega, rx_restart_info* info /* may be NULL */);
+
 /* measurement hook (no reference counterpart): save (restore = 0) or restore (restore = 1) the evolving state of the context — U,
  * U_old, V (with the secant start temperature), the turbulence fields, the viscous kernel's edge order — device to device, on the
  * context's stream, so that the same iteration can be timed from the same state any number of times. */

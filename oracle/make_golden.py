@@ -255,6 +255,30 @@ def run_long(name):
     shutil.rmtree(out, ignore_errors=True)
 
 
+# restart files written by the reference's own COutput (MergeCoordinates / MergeSolution / SetRestart through the harness) after the
+# last iteration of the stage fixture of the same name: the golden bytes for rx_restart_write
+RESTART = ["channel_lam_rk", "channel_rans"]
+
+
+def run_restart_files():
+    arrs = {}
+    for name in RESTART:
+        kw, repl, nit, dump_from, seed, lean = SPECS[name]
+        d = prepare_case(name)
+        out = os.path.join(d, "dump_rst")
+        shutil.rmtree(out, ignore_errors=True)
+        cmd = [HARNESS, "case.cfg", str(nit), out, str(10 ** 9)] + ([str(seed)] if seed is not None else [])
+        log = subprocess.run(cmd, cwd=d, env=dict(os.environ, RX_RESTART_OUT="1", **ENVS.get(name, {})), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if log.returncode != 0 or "HARNESS wrote" not in log.stdout:
+            raise RuntimeError("harness failed for %s:\n%s" % (name, log.stdout[-2000:]))
+        arrs[name] = np.frombuffer(open(os.path.join(d, "restart_flow.dat"), "rb").read(), dtype=np.uint8)
+        os.remove(os.path.join(d, "restart_flow.dat"))
+        shutil.rmtree(out, ignore_errors=True)
+    path = os.path.join(GOLDEN, "restart_files.npz")
+    np.savez_compressed(path, **arrs)
+    print("wrote %s  (%.2f MB)" % (path, os.path.getsize(path) / 1e6))
+
+
 def prepare_bench_case(nx=151, ny=151):
     """Case directory for `bench.py --impl reference` / cpu_baseline: the bench workload (laminar reactive NS, 3-stage RK,
     WLS gradients, AUSM 1st order) at a size the serial CPU reference finishes in seconds per iteration."""
@@ -272,6 +296,8 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["prepare"]:   # case directories only; the committed fixtures are left alone
         for n in SPECS:
             prepare_case(n)
+        for n in RESTART:   # cfg that starts from restart_flow.dat (round trip of rx_restart_write through the reference's readers)
+            derive_cfg(os.path.join(CASES, n, "case.cfg"), os.path.join(CASES, n, "case_restart.cfg"), {"RESTART_SOL": "YES"})
         for base, repl, _e, _n, _s, _c in LONG.values():
             derive_cfg(os.path.join(CASES, base, "case.cfg"), os.path.join(CASES, base, "case_long.cfg"), repl)
         prepare_bench_case()
@@ -279,7 +305,9 @@ if __name__ == "__main__":
     names = sys.argv[1:] or list(SPECS)
     for n in names:
         print("== %s" % n)
-        if n in LONG:
+        if n == "restart_files":
+            run_restart_files()
+        elif n in LONG:
             run_long(n)
         else:
             run_case(n)

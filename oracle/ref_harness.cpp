@@ -557,6 +557,19 @@ int main(int argc, char** argv) {
     for (unsigned short v = 0; v < c.nVar; ++v) histAll.push_back(c.flow->GetRes_RMS(v));
     for (unsigned long n : ckpt) if (n == it + 1) dump_checkpoint(c, n);
   }
+  if (getenv("RX_RESTART_OUT")) {   // the reference's own writer: COutput::SetResult_Files -> MergeCoordinates, MergeSolution, SetRestart (output_structure.cpp:7397-7470, :3858)
+    COutput* out = drv->output;
+    out->MergeCoordinates(c.cfg, c.geo);
+    out->MergeSolution(c.cfg, c.geo, c.sol, ZONE_0);
+    out->SetRestart(c.cfg, c.geo, c.sol, ZONE_0);
+    printf("HARNESS wrote %s\n", c.cfg->GetRestart_FlowFileName().c_str());
+#ifdef RX_WITH_GPU
+    if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) {   // the same file straight from the device state
+      g->WriteRestart(c.geo, c.sol, c.cfg, "restart_flow_gpu.dat");
+      printf("HARNESS wrote restart_flow_gpu.dat (rx_restart_write)\n");
+    }
+#endif
+  }
   {   // peak resident set of this process (bench.py reports it next to the CPU timing: the working set is far beyond the caches)
     FILE* f = fopen("/proc/self/status", "r");
     char line[256];
