@@ -341,6 +341,12 @@ def physical_cores():
     return max(1, (os.cpu_count() or 2) // 2)
 
 
+# Extrapolation anchor: the compiled reference on the GPU arm's own 1415 x 1415 mesh (2.0 M points, 6.0 M edges), one
+# serial process in the build container (same image, 8-core host), RUNGE-KUTTA 3 stages: 602.3 s and 508.8 s for two iterations =
+# 47.2 k updates/s per core, against 50.8 k updates/s per core for the 151 x 151 sample mesh on the same host the same hour — the bounded
+# sample overstates the CPU's per-update rate at full size by 7 %.  Measured once (it takes 25 minutes); quoted in every reference line.
+ANCHOR_4M = {"mesh": "1415 x 1415 points, 6001016 edges (the GPU arm's mesh)", "seconds_per_iteration": [602.27, 508.81], "updates_per_s_one_core": 47189.0,
+             "sample_mesh_updates_per_s_one_core_same_host": 50800.0, "ratio_full_size_to_sample": 0.93, "where": "build container, one serial process, measured once"}
 REF_PROCS = 8   # fixed: one serial reference process per physical core, at most 8, so that every box times the same configuration
 
 
@@ -504,7 +510,7 @@ def main():
             "config": {"workload": workload, "points": r["nPoint"], "edges": r["nEdge"], "rk_stages": len(RK_ALPHA),
                        "sample_note": "same cfg and mesh generator as the GPU arm at a bounded size (the CPU reference needs ~20 us per update: the 4.0M-cell mesh takes minutes per iteration); throughput is per update, see cpu_baseline.sample"},
             "cpu_baseline": {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
-                             "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb")},
+                             "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb"), "anchor_4m_cells": ANCHOR_4M},
             "e2e": {"value": r["value"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
@@ -629,7 +635,7 @@ def main():
             r = run_reference(2, 1, procs=min(physical_cores(), REF_PROCS))
             if r:
                 line["cpu_baseline"] = {"value": r["value"], "unit": "updates/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
-                                        "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb")}
+                                        "physical_cores_on_host": physical_cores(), "rss_mb_per_process": r.get("rss_mb"), "anchor_4m_cells": ANCHOR_4M}
         except Exception as e:   # the baseline is a reported number, never a reason to lose the GPU line
             line["cpu_baseline"] = {"value": None, "unit": "updates/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % str(e)[:200]}
     print(json.dumps(line))
