@@ -359,7 +359,9 @@ def measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W,
     opts = pk.default_opts(rans=rans, cfl=0.1)
     U0, T0, turb = pk.synthetic_state(mesh, chem, seed=12345, rans=rans, glob_xy=plan.get("bbox"))
     solver = pk.CReactiveNSSolverGPU(mesh, chem, opts, device=local)
-    ex = par.HaloExchanger(par.GpuHaloState(solver), plan, dev)
+    ex = None
+    if world > 1:
+        par.library_comm_init(solver, plan, dev)   # halo exchange and global norms inside the library over NCCL (rx_comm_init): rx_iterate is the whole step
     nOwn, nE = solver.nPointDomain, solver.nEdge
     own = np.zeros(solver.nPoint, dtype=bool); own[:nOwn] = True
     en = mesh["edgeNodes"]
@@ -608,7 +610,7 @@ def main():
                    "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (m["nPoint"] * 8 * 160 / 1e9),
                    "timed_state": "every timed step is the same iteration from the same state: the state after the warm-up iterations, restored device-to-device "
                                   "(rx_state_snapshot) before each step, outside the CUDA events; ms_per_step = mean of the per-step event times",
-                   "partition": "strips in x, one halo layer, NCCL send/recv of U and gradients" if world > 1 else "single partition"},
+                   "partition": "strips in x, one halo layer; halo U and gradients by ncclSend/ncclRecv inside the library (rx_halo_exchange), norms by one ncclAllReduce" if world > 1 else "single partition"},
         "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8), "d2h_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8 + m["nVar"] * 8),
                 "what": "same iteration from the same state as `value`: conserved state H2D from pinned host memory (rx_set_solution), rx_iterate, residual norms and the UPDATED conserved state D2H to pinned host memory (rx_get_solution)"},

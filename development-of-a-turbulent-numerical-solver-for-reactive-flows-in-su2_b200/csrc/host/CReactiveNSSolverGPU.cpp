@@ -37,10 +37,12 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   // A partitioned geometry needs the device halo exchange behind Set_MPI_Solution / _Primitive_Gradient / _Primitive_Limiter
   // (solver_reactive.hpp:162,176,183), which this class does not override: the base class would exchange host node[] only and the
   // device halos would go stale without any error.  Refuse instead (the Python host, parallel.py, drives partitioned runs).
-  if (nPoint != nPointDomain) throw std::runtime_error("CReactiveNSSolverGPU: partitioned geometry (halo points present) is not supported by the C++ drop-in");
+#ifndef HAVE_MPI
+  if (nPoint != nPointDomain) throw std::runtime_error("CReactiveNSSolverGPU: partitioned geometry (halo points present) in a build without MPI");
   for (unsigned short m = 0; m < config->GetnMarker_All(); ++m)
     if (config->GetMarker_All_KindBC(m) == SEND_RECEIVE)
-      throw std::runtime_error("CReactiveNSSolverGPU: SEND_RECEIVE markers present; the C++ drop-in is single-partition");
+      throw std::runtime_error("CReactiveNSSolverGPU: SEND_RECEIVE markers present in a build without MPI");
+#endif
 
   // ---- geometry -> rx_mesh (flat arrays; dual_grid_structure.hpp:140,747,884)
   const unsigned long nEdge = geometry->GetnEdge();
@@ -143,6 +145,45 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   bufU.resize((size_t)nPoint * nVar); bufR.resize((size_t)nPoint * nVar);
   bufV.resize((size_t)nPoint * nPrimVar); bufAux.resize((size_t)nPoint * 6);
   bufGrad.resize((size_t)nPoint * nPrimVarGrad * nDim); bufT.resize((size_t)nPoint * 6);
+#ifdef HAVE_MPI
+  InitComm(geometry, config);
+#endif
+}
+
+#ifdef HAVE_MPI
+// One rank per GPU.  The neighbour lists are the vertex lists of the SEND_RECEIVE marker pairs, in the order Set_MPI_Solution walks them
+// (solver_direct_reactive.cpp:1541-1560): marker S (SendRecv > 0) goes to rank SendRecv - 1, marker S + 1 receives from |SendRecv| - 1.
+// NOTE: compiled in MPI builds only; this container has no MPI, the same C entry points are exercised by tests/test_gpu_nccl.py.
+void CReactiveNSSolverGPU::InitComm(CGeometry* geometry, CConfig* config) {
+  int rank = 0, size = 1;
+  MPI_Comm_rank(MPI_COMM_WORLD, &rank); MPI_Comm_size(MPI_COMM_WORLD, &size);
+  if (size == 1) return;
+  std::vector<int> nb;
+  std::vector<int64_t> sp(1, 0), rp(1, 0), spts, rpts;
+  for (unsigned short m = 0; m < geometry->GetnMarker(); ++m) {
+    if (config->GetMarker_All_KindBC(m) != SEND_RECEIVE || config->GetMarker_All_SendRecv(m) <= 0) continue;
+    const unsigned short ms = m, mr = m + 1;
+    nb.push_back(config->GetMarker_All_SendRecv(ms) - 1);
+    for (unsigned long v = 0; v < geometry->nVertex[ms]; ++v) spts.push_back((int64_t)geometry->vertex[ms][v]->GetNode());
+    for (unsigned long v = 0; v < geometry->nVertex[mr]; ++v) rpts.push_back((int64_t)geometry->vertex[mr][v]->GetNode());
+    sp.push_back((int64_t)spts.size()); rp.push_back((int64_t)rpts.size());
+  }
+  char id[128];
+  if (rank == MASTER_NODE) Check(rx_comm_unique_id(id), "rx_comm_unique_id");
+  MPI_Bcast(id, 128, MPI_CHAR, MASTER_NODE, MPI_COMM_WORLD);
+  Check(rx_comm_init(ctx, id, rank, size, (int)nb.size(), nb.data(), sp.data(), spts.data(), rp.data(), rpts.data()), "rx_comm_init");
+  commReady = true;
+}
+#endif
+
+void CReactiveNSSolverGPU::Set_MPI_Solution(CGeometry*, CConfig*) {
+  if (commReady) Check(rx_halo_exchange(ctx, 0), "rx_halo_exchange(U)");
+}
+void CReactiveNSSolverGPU::Set_MPI_Primitive_Gradient(CGeometry*, CConfig*) {
+  if (commReady) Check(rx_halo_exchange(ctx, 1), "rx_halo_exchange(gradients)");
+}
+void CReactiveNSSolverGPU::Set_MPI_Primitive_Limiter(CGeometry*, CConfig*) {
+  if (commReady) Check(rx_halo_exchange(ctx, 2), "rx_halo_exchange(limiters)");
 }
 
 CReactiveNSSolverGPU::~CReactiveNSSolverGPU() { rx_destroy(ctx); }
@@ -250,6 +291,10 @@ void CReactiveNSSolverGPU::Preprocessing(CGeometry* geometry, CSolver** solver_c
   const bool count = (config->GetConsole_Output_Verb() == VERB_HIGH);
   Check(rx_preprocess(ctx, (int64_t)extIter, Output ? 1 : 0, count ? &bad : nullptr), "rx_preprocess");
   if (count && iMesh == MESH_0) config->SetNonphysical_Points((unsigned long)bad);
+  if (commReady) {   // the reference exchanges inside its Preprocessing (solver_direct_reactive.cpp:4716-4760)
+    if (viscousMode || second_order) Set_MPI_Primitive_Gradient(geometry, config);
+    if (limiter && !Output) Set_MPI_Primitive_Limiter(geometry, config);
+  }
   if (Output) turbPostReady = true;   // the device now holds the primitive state the next SST Postprocessing refers to
   if (mirror >= 1) MirrorPrimitives();
   if (mirror >= 2 && limiter && !Output) MirrorLimiter();
@@ -315,6 +360,10 @@ void CReactiveNSSolverGPU::BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*,
 void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha) {
   std::vector<double> rms(nVar);
   Check(rx_update_explicit(ctx, alpha, rms.data()), "rx_update_explicit");
+  if (commReady) {   // Set_MPI_Solution and the global norms, as ExplicitEuler/RK_Iteration do (:2442-2448)
+    Set_MPI_Solution(geometry, nullptr);
+    Check(rx_comm_allreduce_rms(ctx, rms.data()), "rx_comm_allreduce_rms");
+  }
   std::vector<double> rmax(nVar);
   std::vector<int64_t> pmax(nVar);
   Check(rx_get_residual_max(ctx, rmax.data(), pmax.data()), "rx_get_residual_max");

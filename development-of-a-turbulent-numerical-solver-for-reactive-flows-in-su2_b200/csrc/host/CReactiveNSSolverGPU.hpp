@@ -49,6 +49,13 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void ExplicitRK_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config,
                             unsigned short iRKStep) override;
 
+  // Halo exchanges (solver_reactive.hpp:162,176,183).  With a communicator (MPI builds: InitComm at construction) they run inside
+  // the library over NCCL between the device states (rx_halo_exchange); in a serial build there is no SEND_RECEIVE marker and they
+  // are no-ops, as the base versions are.
+  void Set_MPI_Solution(CGeometry* geometry, CConfig* config) override;
+  void Set_MPI_Primitive_Gradient(CGeometry* geometry, CConfig* config) override;
+  void Set_MPI_Primitive_Limiter(CGeometry* geometry, CConfig* config) override;
+
   // COutput::SetRestart for this solver, straight from the device state (rx_restart_write): the same bytes the reference's
   // MergeSolution + SetRestart produce (output_structure.cpp:1991-2130, 3858-4060) without mirroring the state into node[].
   // One call in COutput::SetResult_Files replaces the pair for a CReactiveNSSolverGPU flow solver.
@@ -70,7 +77,11 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
   void Update(CGeometry* geometry, double alpha);
 
+#ifdef HAVE_MPI
+  void InitComm(CGeometry* geometry, CConfig* config);   // neighbour lists from the SEND_RECEIVE marker pairs, NCCL id by MPI_Bcast
+#endif
   rx_ctx* ctx = nullptr;
+  bool commReady = false;
   bool hostDirty = true, ransMode = false, viscousMode = true;
   int mirror = 1;
   // SU2_RX_TURB_POST=1: the fields the flow path reads from the SST solver (muT, grad k, sigma_k) are formed on the device from

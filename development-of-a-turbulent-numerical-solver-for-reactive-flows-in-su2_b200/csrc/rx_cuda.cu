@@ -15,6 +15,8 @@
 #include <string>
 #include <vector>
 
+#include "rx_comm.cuh"
+
 using namespace rx;
 
 static constexpr size_t SM_PAIR = (size_t)VP_SMW * VP_BS * sizeof(double);
@@ -32,6 +34,7 @@ struct rx_ctx {
   ChemC<9> cc9{};
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
+  Comm* comm = nullptr;             // in-library halo exchange over NCCL (rx_comm_init); nullptr: single partition or caller-side transport
   std::vector<void*> snap;          // rx_state_snapshot: device copies of the evolving state, same order as snapshot_fields()
   bool allocFailed = false;         // any cudaMalloc / cudaMemset / cudaMemcpy of dalloc / dupload failed (checked at the end of rx_create)
   double *stage = nullptr, *partial = nullptr, *rms = nullptr, *sumsq = nullptr, *pmax = nullptr, *resMax = nullptr;
@@ -48,6 +51,11 @@ struct rx_ctx {
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
   bool haveWallDist = false; double sigmaK = 0.85;
 };
+
+extern "C" {
+static int halo_exchange_fork(rx_ctx* c, int what);
+static int comm_join(rx_ctx* c);
+}
 
 #define RX_CK(call)                                                                                   \
   do {                                                                                                \
@@ -328,6 +336,15 @@ void rx_destroy(rx_ctx* c) {
   if (c->evFork) cudaEventDestroy(c->evFork);
   if (c->evJoin) cudaEventDestroy(c->evJoin);
   if (c->bcStream) cudaStreamDestroy(c->bcStream);
+  if (c->comm) {
+    std::string why;
+    NcclApi* a = nccl_api(why);
+    if (a && c->comm->comm) a->CommDestroy(c->comm->comm);
+    if (c->comm->cs) cudaStreamDestroy(c->comm->cs);
+    if (c->comm->evReady) cudaEventDestroy(c->comm->evReady);
+    if (c->comm->evDone) cudaEventDestroy(c->comm->evDone);
+    delete c->comm;
+  }
   delete c;
 }
 
@@ -673,10 +690,15 @@ int rx_get_residual_max(rx_ctx* c, double* resMax, int64_t* point) {
 int rx_residual_all(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
+  int rc;
   if (c->o.viscous) {
-    launch_edge_flux<true, true>(c, s);
+    if (c->o.secondOrder && (rc = comm_join(c))) return rc;   // the MUSCL flux reads halo gradients and limiters
+    launch_edge_flux<true, false>(c, s);
+    if ((rc = comm_join(c))) return rc;                       // a forked gradient exchange (rx_iterate) must have landed before the viscous flux
+    launch_edge_flux<false, true>(c, s);
     launch_accumulate_visc(c, s);
   } else {
+    if ((rc = comm_join(c))) return rc;
     launch_edge_flux<true, false>(c, s);
     k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
     k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
@@ -744,18 +766,35 @@ int rx_get_edge_order(rx_ctx* c, int32_t* order, uint8_t* key) {
 }
 
 int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, double* resRms) {
+  // With a communicator (rx_comm_init) the exchanges sit where the reference has them: gradients (and limiters) after every
+  // Preprocessing — Set_MPI_Primitive_Gradient / _Limiter, solver_direct_reactive.cpp:4716-4760 — and the conserved variables after
+  // every update — Set_MPI_Solution, :2442 / :2487; the norms of the last stage are then those of the whole job.
   int rc;
+  const bool par = c->comm != nullptr;
   for (int rk = 0; rk < nRK; ++rk) {
     if ((rc = rx_preprocess(c, extIter, 0, nullptr))) return rc;
+    // forked onto the communicator's stream: U_old copy, time step and the first-order convective flux do not read halo gradients
+    if (par && (c->o.viscous || c->o.secondOrder) && (rc = halo_exchange_fork(c, 1))) return rc;
+    if (par && c->o.secondOrder && c->o.limiter && (rc = halo_exchange_fork(c, 2))) return rc;
     if (rk == 0) {
       if ((rc = rx_set_old_solution(c))) return rc;
       if ((rc = rx_time_step(c))) return rc;
     }
     if ((rc = rx_residual_all(c))) return rc;
     if ((rc = rx_bc(c))) return rc;
-    if ((rc = rx_update_explicit(c, rkAlpha ? rkAlpha[rk] : 1.0, (rk == nRK - 1) ? resRms : nullptr))) return rc;
+    const bool last = rk == nRK - 1;
+    if (par && last && resRms) {
+      if ((rc = rx_update_explicit(c, rkAlpha ? rkAlpha[rk] : 1.0, nullptr))) return rc;
+      if ((rc = rx_halo_exchange(c, 0))) return rc;
+      if ((rc = rx_comm_allreduce_rms(c, resRms))) return rc;
+    } else {
+      if ((rc = rx_update_explicit(c, rkAlpha ? rkAlpha[rk] : 1.0, last ? resRms : nullptr))) return rc;
+      if (par && (rc = rx_halo_exchange(c, 0))) return rc;
+    }
   }
-  return rx_preprocess(c, extIter, 1, nullptr);
+  if ((rc = rx_preprocess(c, extIter, 1, nullptr))) return rc;
+  if (par && (c->o.viscous || c->o.secondOrder) && (rc = rx_halo_exchange(c, 1))) return rc;
+  return RX_OK;
 }
 
 int rx_source_points_dev(rx_ctx* c, int64_t n, const double* T, const double* rho, const double* Y, const double* omT, const double* vol, double* res) {
@@ -819,6 +858,131 @@ int rx_wall_distance(int64_t nPoint, const double* xy, int64_t nWall, const doub
   } else g_create_error = "rx_wall_distance: out of device memory";
   cudaFree(dXy); cudaFree(dW); cudaFree(dD);
   return rc;
+}
+
+// ---- in-library communication (rx_comm.cuh)
+int rx_comm_unique_id(void* id128) {
+  std::string why;
+  NcclApi* a = nccl_api(why);
+  if (!a) { g_create_error = "rx_comm_unique_id: " + why; return RX_ERR_UNSUPPORTED; }
+  nccl_uid id;
+  const int e = a->GetUniqueId(&id);
+  if (e) { g_create_error = std::string("ncclGetUniqueId: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+  memcpy(id128, &id, sizeof id);
+  return RX_OK;
+}
+int rx_comm_init(rx_ctx* c, const void* id128, int rank, int nRanks, int nNeighbors, const int* neighborRank,
+                 const int64_t* sendPtr, const int64_t* sendPoints, const int64_t* recvPtr, const int64_t* recvPoints) {
+  if (c->comm) { c->err = "rx_comm_init: the context already has a communicator"; return RX_ERR_ARG; }
+  if (!id128 || rank < 0 || rank >= nRanks || nNeighbors < 0 || (nNeighbors && (!neighborRank || !sendPtr || !recvPtr))) { c->err = "rx_comm_init: bad arguments"; return RX_ERR_ARG; }
+  std::string why;
+  NcclApi* a = nccl_api(why);
+  if (!a) { c->err = "rx_comm_init: " + why; return RX_ERR_UNSUPPORTED; }
+  RX_CK(cudaSetDevice(c->device));
+  Comm* m = new Comm();
+  m->rank = rank; m->nRanks = nRanks;
+  m->nbRank.assign(neighborRank, neighborRank + nNeighbors);
+  m->sendPtr.assign(1, 0); m->recvPtr.assign(1, 0);
+  for (int k = 0; k < nNeighbors; ++k) { m->sendPtr.push_back(sendPtr[k + 1]); m->recvPtr.push_back(recvPtr[k + 1]); }
+  const long long nS = m->sendPtr.back(), nR = m->recvPtr.back();
+  for (long long k = 0; k < nS; ++k) if (sendPoints[k] < 0 || sendPoints[k] >= c->d.nPoint) { delete m; c->err = "rx_comm_init: send point out of range"; return RX_ERR_ARG; }
+  for (long long k = 0; k < nR; ++k) if (recvPoints[k] < 0 || recvPoints[k] >= c->d.nPoint) { delete m; c->err = "rx_comm_init: receive point out of range"; return RX_ERR_ARG; }
+  m->sendPts = dupload(c, std::vector<long long>(sendPoints, sendPoints + nS));
+  m->recvPts = dupload(c, std::vector<long long>(recvPoints, recvPoints + nR));
+  m->sendBuf = dalloc<double>(c, (size_t)std::max<long long>(nS, 1) * HALO_MAXW);
+  m->recvBuf = dalloc<double>(c, (size_t)std::max<long long>(nR, 1) * HALO_MAXW);
+  m->redBuf = dalloc<double>(c, 32);
+  if (c->allocFailed || !m->sendPts || !m->recvPts || !m->sendBuf || !m->recvBuf || !m->redBuf) { delete m; c->err = "rx_comm_init: device allocation failed"; return RX_ERR_CUDA; }
+  nccl_uid id;
+  memcpy(&id, id128, sizeof id);
+  const int e = a->CommInitRank(&m->comm, nRanks, id, rank);
+  if (e) { c->err = std::string("ncclCommInitRank: ") + a->GetErrorString(e); delete m; return RX_ERR_CUDA; }
+  if (cudaStreamCreateWithFlags(&m->cs, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&m->evReady, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&m->evDone, cudaEventDisableTiming) != cudaSuccess) { a->CommDestroy(m->comm); delete m; c->err = "rx_comm_init: stream / event creation failed"; return RX_ERR_CUDA; }
+  c->comm = m;
+  return RX_OK;
+}
+// pack -> grouped ncclSend / ncclRecv with every neighbour -> unpack, on the context's stream (Set_MPI_* of the reference)
+static int halo_exchange_on(rx_ctx* c, int what, cudaStream_t s);
+int rx_halo_exchange(rx_ctx* c, int what) {
+  if (!c->comm) { c->err = "rx_halo_exchange: no communicator (rx_comm_init)"; return RX_ERR_ARG; }
+  if (what < 0 || what > 3 || (what == 3 && !c->tpost)) { c->err = "rx_halo_exchange: bad `what`"; return RX_ERR_ARG; }
+  return halo_exchange_on(c, what, c->stream);
+}
+// the same exchange forked onto the communicator's stream (everything enqueued so far on the context's stream is waited for); the
+// context's stream continues and joins with comm_join() before the first kernel that reads the exchanged halo values
+static int halo_exchange_fork(rx_ctx* c, int what) {
+  Comm* m = c->comm;
+  if (!m->pending) {
+    RX_CK(cudaEventRecord(m->evReady, c->stream));
+    RX_CK(cudaStreamWaitEvent(m->cs, m->evReady, 0));
+  }
+  const int rc = halo_exchange_on(c, what, m->cs);
+  m->pending = true;
+  return rc;
+}
+static int comm_join(rx_ctx* c) {
+  Comm* m = c->comm;
+  if (!m || !m->pending) return RX_OK;
+  RX_CK(cudaEventRecord(m->evDone, m->cs));
+  RX_CK(cudaStreamWaitEvent(c->stream, m->evDone, 0));
+  m->pending = false;
+  return RX_OK;
+}
+static int halo_exchange_on(rx_ctx* c, int what, cudaStream_t s) {
+  Comm* m = c->comm;
+  std::string why;
+  NcclApi* a = nccl_api(why);
+  const int nv = rx_halo_width(c, what);
+  const int nNb = (int)m->nbRank.size();
+  double* field = what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np;
+  for (int k = 0; k < nNb; ++k) {
+    const long long n = m->sendPtr[k + 1] - m->sendPtr[k];
+    if (n <= 0) continue;
+    k_pack<<<nblk(n * nv, 256), 256, 0, s>>>(field, c->d.np, nv, n, m->sendPts + m->sendPtr[k], m->sendBuf + (size_t)m->sendPtr[k] * nv);
+    c->launches++;
+  }
+  RX_CK(cudaGetLastError());
+  int e = a->GroupStart();
+  for (int k = 0; k < nNb && !e; ++k) {
+    const long long ns = m->sendPtr[k + 1] - m->sendPtr[k], nr = m->recvPtr[k + 1] - m->recvPtr[k];
+    if (ns > 0) e = a->Send(m->sendBuf + (size_t)m->sendPtr[k] * nv, (size_t)ns * nv, NCCL_FLOAT64, m->nbRank[k], m->comm, s);
+    if (nr > 0 && !e) e = a->Recv(m->recvBuf + (size_t)m->recvPtr[k] * nv, (size_t)nr * nv, NCCL_FLOAT64, m->nbRank[k], m->comm, s);
+    m->bytesMoved += (ns + nr) * nv * 8;
+  }
+  if (!e) e = a->GroupEnd();
+  if (e) { c->err = std::string("rx_halo_exchange: NCCL: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+  for (int k = 0; k < nNb; ++k) {
+    const long long n = m->recvPtr[k + 1] - m->recvPtr[k];
+    if (n <= 0) continue;
+    k_unpack<<<nblk(n * nv, 256), 256, 0, s>>>(field, c->d.np, nv, n, m->recvPts + m->recvPtr[k], m->recvBuf + (size_t)m->recvPtr[k] * nv);
+    c->launches++;
+    if (what == 1 && c->o.viscous) { k_vort_strain_points<9><<<nblk(n, 128), 128, 0, s>>>(c->d, n, m->recvPts + m->recvPtr[k]); c->launches++; }
+  }
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+// norms of the whole job from the partitions' sums of squares (SetResidual_RMS with MPI, solver_structure.cpp:188-260): one all-reduce
+int rx_comm_allreduce_rms(rx_ctx* c, double* resRms) {
+  Comm* m = c->comm;
+  if (!m) { c->err = "rx_comm_allreduce_rms: no communicator (rx_comm_init)"; return RX_ERR_ARG; }
+  std::string why;
+  NcclApi* a = nccl_api(why);
+  cudaStream_t s = c->stream;
+  k_rms_pack<<<1, 32, 0, s>>>(c->sumsq, c->nVar, (double)c->d.nPointDomain, m->redBuf);
+  const int e = a->AllReduce(m->redBuf, m->redBuf, (size_t)c->nVar + 1, NCCL_FLOAT64, NCCL_SUM, m->comm, s);
+  if (e) { c->err = std::string("rx_comm_allreduce_rms: NCCL: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+  k_rms_global<<<1, 32, 0, s>>>(m->redBuf, c->nVar, c->rms);
+  c->launches += 2;
+  RX_CK(cudaGetLastError());
+  if (resRms) {
+    unsigned long long h[5];
+    RX_CK(cudaMemcpyAsync(resRms, c->rms, c->nVar * sizeof(double), cudaMemcpyDeviceToHost, s));
+    const int rc = read_status(c, h);
+    if (rc) return rc;
+    return status_error(c, h);
+  }
+  return RX_OK;
 }
 
 int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : (what == 2 || what == 3) ? 4 : 0; }   // 2: limiter, 3: grad k, grad omega

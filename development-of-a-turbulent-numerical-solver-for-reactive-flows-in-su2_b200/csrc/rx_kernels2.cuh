@@ -568,6 +568,17 @@ __global__ void __launch_bounds__(256) k_rms_finish(const double* __restrict__ p
   }
 }
 
+// norms of a partitioned job: this partition's sums of squares + its owned point count -> (all-reduce) -> global RMS
+__global__ void k_rms_pack(const double* __restrict__ sumsq, int nv, double nOwned, double* __restrict__ red) {
+  const int v = threadIdx.x;
+  if (v < nv) red[v] = sumsq[v];
+  if (v == nv) red[nv] = nOwned;
+}
+__global__ void k_rms_global(const double* __restrict__ red, int nv, double* __restrict__ rms) {
+  const int v = threadIdx.x;
+  if (v < nv) rms[v] = fmax(EPS * EPS, sqrt(red[v] / red[nv]));
+}
+
 // ---- FP64 roof: eight independent DFMA chains per thread, nothing else in the loop
 __global__ void __launch_bounds__(256) k_fp64_peak(int iters, double a, double* sink) {
   double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;

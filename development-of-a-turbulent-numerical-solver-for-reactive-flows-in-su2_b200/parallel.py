@@ -81,6 +81,19 @@ class TensorHaloState:
         self.fields[what][:, ids] = buf.view(self.fields[what].shape[0], -1)
 
 
+def library_comm_init(solver, plan, device):
+    """Hand the halo exchange to the library (rx_comm_init): rank 0 draws the NCCL unique id through the library, torch.distributed
+    (already initialised by the launcher) only carries its 128 bytes to the other ranks — the role MPI_Bcast has in an SU2 build.
+    From here on rx_iterate runs a whole partitioned iteration, exchanges included, without the host in the loop."""
+    from .rx_solver import comm_unique_id
+    rank, world = dist.get_rank(), dist.get_world_size()
+    t = torch.zeros(128, dtype=torch.uint8, device=device)
+    if rank == 0:
+        t.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(t, 0)
+    solver.CommInit(bytes(t.cpu().numpy().tobytes()), rank, world, plan)
+
+
 def global_rms(rms_local, n_local, n_owned, device):
     """Residual norms of the whole job from the per-partition ones (SetResidual_RMS, solver_structure.cpp:172-187: sqrt of
     the squares summed over all owned points / global owned point count): one all-reduce of nVar + 1 doubles.
@@ -99,6 +112,8 @@ def global_rms(rms_local, n_local, n_owned, device):
 def distributed_iterate(solver, ex, ext_iter, rk_alpha, last_rms=False):
     """One MultiGrid_Cycle on a partition, with the reference's exchange points: gradients after every Preprocessing
     (Set_MPI_Primitive_Gradient), conserved variables after every update (Set_MPI_Solution)."""
+    if getattr(solver, "has_comm", False):   # exchanges and the global norms inside the library (rx_comm_init)
+        return solver.Iterate(ext_iter, rk_alpha, want_rms=last_rms)
     rms = None
     for rk, a in enumerate(rk_alpha):
         solver.Preprocessing(ext_iter, False, count_nonphysical=False)
@@ -123,5 +138,8 @@ def distributed_turb_postprocess(solver, ex, k_omega, sigma_k=0.85):
     """CTurbSSTSolver::Postprocessing on a partition: gradients of (k, omega) on the owned points, their halo values from the
     owners (Set_MPI_Solution_Gradient, solver_direct_turbulent.cpp:227), then blending functions and eddy viscosity everywhere."""
     solver.TurbPostprocessing(k_omega, sigma_k=sigma_k, stage=1)
-    ex.exchange(WHAT_TURB_GRADIENT)
+    if getattr(solver, "has_comm", False):
+        solver.HaloExchange(WHAT_TURB_GRADIENT)
+    else:
+        ex.exchange(WHAT_TURB_GRADIENT)
     solver.TurbPostprocessing(None, sigma_k=sigma_k, stage=2)

@@ -100,7 +100,8 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read"]
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read",
+           "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
 _lib = None
 
@@ -175,6 +176,16 @@ def libm_eval(which, x, y=None, device=0):
     return out
 
 
+def comm_unique_id():
+    """ncclGetUniqueId through the library (rx_comm_unique_id): 128 bytes for rank 0 to hand to the other ranks."""
+    L = load_library()
+    buf = (C.c_char * 128)()
+    rc = L.rx_comm_unique_id(buf)
+    if rc != 0:
+        raise RxError("rx_comm_unique_id failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
+    return bytes(buf)
+
+
 STATIC_RMS_MAX_POINTS, STATIC_RMS_MAX_VARS = 4194304, 16   # include/rx_cuda.h: RX_STATIC_RMS_MAX_*
 
 
@@ -230,6 +241,7 @@ class CReactiveNSSolverGPU:
         if rc != 0:
             raise RxError("rx_create failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
         self.ctx = ctx
+        self.has_comm = False
 
     def _ck(self, rc):
         if rc != 0:
@@ -345,6 +357,25 @@ class CReactiveNSSolverGPU:
         a = _c(rk_alpha); rms = np.empty(self.nVar)
         self._ck(self.lib.rx_iterate(self.ctx, C.c_int64(ExtIter), len(a), _d(a), _d(rms) if want_rms else None))
         return rms if want_rms else None
+
+    def CommInit(self, uid, rank, nranks, plan):
+        """rx_comm_init: NCCL communicator + this partition's neighbour lists (plan["send"] / plan["recv"]: {neighbour rank: local point ids})."""
+        nbs = sorted(set(int(q) for q in plan["send"]) | set(int(q) for q in plan["recv"]))
+        sp, rp, spts, rpts = [0], [0], [], []
+        for q in nbs:
+            a = np.asarray(plan["send"].get(q, plan["send"].get(str(q), [])), dtype=np.int64); b = np.asarray(plan["recv"].get(q, plan["recv"].get(str(q), [])), dtype=np.int64)
+            spts.append(a); rpts.append(b); sp.append(sp[-1] + a.size); rp.append(rp[-1] + b.size)
+        cat = lambda l: _c(np.concatenate(l) if l else np.zeros(0), np.int64)
+        nb = _c(np.array(nbs, dtype=np.int32), np.int32)
+        spts, rpts, sp, rp = cat(spts), cat(rpts), _c(sp, np.int64), _c(rp, np.int64)
+        self._ck(self.lib.rx_comm_init(self.ctx, C.c_char_p(uid), int(rank), int(nranks), len(nbs), nb.ctypes.data_as(C.POINTER(C.c_int)),
+                                       _i(sp), _i(spts), _i(rp), _i(rpts)))
+        self.has_comm = True
+
+    def HaloExchange(self, what): self._ck(self.lib.rx_halo_exchange(self.ctx, int(what)))
+
+    def CommAllreduceRms(self):
+        rms = np.empty(self.nVar); self._ck(self.lib.rx_comm_allreduce_rms(self.ctx, _d(rms))); return rms
 
     def HaloWidth(self, what): return int(self.lib.rx_halo_width(self.ctx, int(what)))
 

@@ -166,6 +166,24 @@ int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double
 int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);
 int rx_halo_width(rx_ctx*, int what);
 
+/* The same exchange INSIDE the library, over NCCL (csrc/rx_comm.cuh; NCCL is bound at run time with dlopen, env RX_NCCL_LIB overrides
+ * the name): one process per GPU, one rx_ctx per process.
+ *   rx_comm_unique_id : ncclGetUniqueId on one rank; the 128 bytes travel to the others by the host's own means (MPI_Bcast in SU2).
+ *   rx_comm_init      : ncclCommInitRank + the neighbour lists of this partition: for neighbour k (rank neighborRank[k]) the local points
+ *                       sendPoints[sendPtr[k] .. sendPtr[k+1]) go out and recvPoints[recvPtr[k] .. recvPtr[k+1]) (halo points) come in, in the
+ *                       order both sides agreed on — the vertex order of the SEND_RECEIVE marker pair in SU2 (geometry->vertex[MarkerS/R]).
+ *   rx_halo_exchange  : Set_MPI_Solution (what 0, solver_direct_reactive.cpp:1530), Set_MPI_Primitive_Gradient (1, :1877),
+ *                       Set_MPI_Primitive_Limiter (2, :1756), Set_MPI_Solution_Gradient of (k, omega) (3): pack, grouped ncclSend/ncclRecv,
+ *                       unpack — enqueued on the context's stream, no host synchronisation.  rx_iterate calls it at the reference's points
+ *                       once a communicator exists, and returns the norms of the whole job.
+ *   rx_comm_allreduce_rms : residual norms of the whole job from every partition's sums of squares of the last rx_update_explicit
+ *                       (CSolver::SetResidual_RMS under MPI, solver_structure.cpp:188-260): one ncclAllReduce of nVar + 1 doubles. */
+int rx_comm_unique_id(void* id128);
+int rx_comm_init(rx_ctx*, const void* id128, int rank, int nRanks, int nNeighbors, const int* neighborRank,
+                 const int64_t* sendPtr, const int64_t* sendPoints, const int64_t* recvPtr, const int64_t* recvPoints);
+int rx_halo_exchange(rx_ctx*, int what);
+int rx_comm_allreduce_rms(rx_ctx*, double* resRms /* [nVar] host, or NULL */);
+
 /* measurement hook: average device time in ms (CUDA events on the context's stream) of `reps` launches of one kernel on the
  * current state; which = 0 viscous edge flux (convective if inviscid), 1 convective edge flux, 2 accumulation+source,
  * 3 cons->prim, 4 gradient, 5 source, 6 explicit update, 7 laminar transport */
