@@ -488,6 +488,10 @@ def main():
                          "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3]); "
                          "turbpost = SST Postprocessing on the device (first slice of SURVEY.md 8(f) rank 1)")
     ap.add_argument("--points", type=int, default=64_000_000)
+    ap.add_argument("--strong", action="store_true", help="strong scaling: --nx x --ny is the WHOLE mesh, split over the ranks (default: weak, --nx x --ny per rank)")
+    ap.add_argument("--partition", default="strips", choices=["strips", "graph"],
+                    help="strips: x-strips built per rank without the global mesh; graph: every rank builds the global mesh, partitions its point graph k-way "
+                         "(rx_partition_kway + RCM numbering, the ParMETIS / SetRCM_Ordering stand-ins) and keeps its own part")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W = max(a.warmup, 0); K = max(a.steps, 1)
@@ -533,11 +537,18 @@ def main():
         return bench_source(a, pk, chem, rank, world, local, dev, K, W)
     if a.workload == "turbpost":
         return bench_turbpost(a, pk, chem, rank, world, local, dev, K, W)
-    nxg = a.nx * world                     # weak scaling: every rank owns an nx x ny strip
-    if world > 1:
+    nxg = a.nx if a.strong else a.nx * world   # weak scaling: every rank owns an nx x ny strip; strong: nx x ny is the whole mesh
+    t_mesh = time.perf_counter()
+    if world > 1 and a.partition == "graph":
+        gm = pk.channel_mesh(nxg, a.ny)
+        part = pk.partition_graph(gm, world, rcm=True)[rank]
+        mesh, plan = part["mesh"], dict(send=part["send"], recv=part["recv"], bbox=(0.0, 0.25, 0.0, 0.025), glob=part["glob"])
+        del gm, part
+    elif world > 1:
         mesh, plan = pk.channel_strip_mesh(nxg, a.ny, rank, world)
     else:
-        mesh = pk.channel_mesh(a.nx, a.ny); plan = dict(send={}, recv={}, bbox=None)
+        mesh = pk.channel_mesh(nxg, a.ny); plan = dict(send={}, recv={}, bbox=None)
+    t_mesh = time.perf_counter() - t_mesh
     m = measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W, full=True)
     ms_dev, ms_e2e, units = reduce_flow(m, world, dev)
     solver = m["solver"]; kt = m["kt"]; nOwn, nE = m["nOwn"], m["nE"]; clocks = m["clocks"]; launches = m["launches"]
@@ -605,12 +616,12 @@ def main():
     ach_hbm_conv = bytes_conv * nE / t_conv / 1e9
     line = {
         "metric": METRIC, "value": units / (ms_dev * 1e-3), "unit": "updates/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
-        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload, "points_per_gpu": nOwn, "edges_per_gpu": nE, "cells_per_gpu": 2 * (a.nx - 1) * (a.ny - 1), "rk_stages": len(RK_ALPHA),
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload, "mesh_points_total": int(nxg * a.ny), "mesh_build_s_rank0": round(t_mesh, 1), "points_per_gpu": nOwn, "edges_per_gpu": nE, "cells_per_gpu": int(2 * (nxg - 1) * (a.ny - 1) / world) if a.strong else 2 * (a.nx - 1) * (a.ny - 1), "rk_stages": len(RK_ALPHA),
                    "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (m["nPoint"] * 8 * 160 / 1e9),
                    "timed_state": "every timed step is the same iteration from the same state: the state after the warm-up iterations, restored device-to-device "
                                   "(rx_state_snapshot) before each step, outside the CUDA events; ms_per_step = mean of the per-step event times",
-                   "partition": "strips in x, one halo layer; halo U and gradients by ncclSend/ncclRecv inside the library (rx_halo_exchange), norms by one ncclAllReduce" if world > 1 else "single partition"},
+                   "partition": ("k-way graph partition (rx_partition_kway) with RCM numbering" if a.partition == "graph" else "strips in x") + ", one halo layer; halo U and gradients by ncclSend/ncclRecv inside the library (rx_halo_exchange), norms by one ncclAllReduce" if world > 1 else "single partition"},
         "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8), "d2h_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8 + m["nVar"] * 8),
                 "what": "same iteration from the same state as `value`: conserved state H2D from pinned host memory (rx_set_solution), rx_iterate, residual norms and the UPDATED conserved state D2H to pinned host memory (rx_get_solution)"},
