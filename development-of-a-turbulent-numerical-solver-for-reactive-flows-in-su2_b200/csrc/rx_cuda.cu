@@ -5,6 +5,7 @@
 #include "rx_visc_pair.cuh"
 #include "rx_order.cuh"
 #include "rx_turb.cuh"
+#include "rx_turb_step.cuh"
 
 #include <cuda_runtime.h>
 #include <algorithm>
@@ -34,6 +35,14 @@ struct rx_ctx {
   ChemC<9> cc9{};
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
+  // SST transport step (rx_turb_step.cuh): work arrays, Krylov vectors, level lists of the LU-SGS sweeps
+  TurbW tw{};
+  bool turbStepReady = false;
+  int *lvlPtrF = nullptr, *lvlPtsF = nullptr, *lvlPtrB = nullptr, *lvlPtsB = nullptr, nLvlF = 0, nLvlB = 0;
+  std::vector<double*> kw, kz;      // FGMRES w[0..m], z[0..m]
+  double *tPartial = nullptr, *tScal = nullptr;
+  int tBlocks = 0, tDotBlocks = 0;
+  std::vector<int> hIncPtr, hNbOfSlot;   // host copy of the incident CSR (neighbour of every slot) for the level lists
   Comm* comm = nullptr;             // in-library halo exchange over NCCL (rx_comm_init); nullptr: single partition or caller-side transport
   std::vector<void*> snap;          // rx_state_snapshot: device copies of the evolving state, same order as snapshot_fields()
   bool allocFailed = false;         // any cudaMalloc / cudaMemset / cudaMemcpy of dalloc / dupload failed (checked at the end of rx_create)
@@ -263,6 +272,11 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     std::vector<int> fill(incPtr.begin(), incPtr.end() - 1);
     for (long long e = 0; e < nE; ++e) { incEdge[fill[ei[e]]++] = (int)e; incEdge[fill[ej[e]]++] = ~(int)e; }
   }
+  if (op->rans) {   // neighbour of every incident slot, for the level lists of the turbulence step's LU-SGS sweeps
+    c->hIncPtr = incPtr;
+    c->hNbOfSlot.resize(incEdge.size());
+    for (size_t k = 0; k < incEdge.size(); ++k) { const int code = incEdge[k]; c->hNbOfSlot[k] = code >= 0 ? ej[code] : ei[~code]; }
+  }
   d.ei = dupload(c, ei); d.ej = dupload(c, ej); d.enx = dupload(c, enx); d.eny = dupload(c, eny);
   d.x = dupload(c, x); d.y = dupload(c, y); d.vol = dupload(c, vol);
   d.nbPtr = dupload(c, nbPtr); d.nbIdx = dupload(c, nbIdx); d.incPtr = dupload(c, incPtr); d.incEdge = dupload(c, incEdge);
@@ -457,6 +471,189 @@ int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stag
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
+// ---- SST transport step (rx_turb_step.cuh)
+static int turb_step_setup(rx_ctx* c, int m) {
+  if (c->turbStepReady && (int)c->kw.size() >= m + 1) return RX_OK;
+  const Dev& d = c->d;
+  const size_t np = d.np;
+  if (!c->turbStepReady) {
+    c->tw.nInc = (long long)c->hNbOfSlot.size();
+    c->tw.res = dalloc<double>(c, 2 * np); c->tw.diag = dalloc<double>(c, 2 * np); c->tw.x = dalloc<double>(c, 2 * np); c->tw.old = dalloc<double>(c, 2 * np);
+    c->tw.off = dalloc<double>(c, 2 * (size_t)std::max<long long>(c->tw.nInc, 1));
+    c->tBlocks = (int)nblk(d.nPointDomain, 128); c->tDotBlocks = (int)nblk(2 * d.nPointDomain, 256);
+    c->tPartial = dalloc<double>(c, (size_t)std::max(2 * c->tBlocks, c->tDotBlocks) + 2);
+    c->tScal = dalloc<double>(c, 8);
+    // level lists: forward sweep level(p) = 1 + max over lower-numbered neighbours; backward sweep likewise over higher-numbered ones
+    const long long n = d.nPointDomain;
+    std::vector<int> lev(n, 0);
+    auto build = [&](bool fwd, std::vector<int>& ptr, std::vector<int>& pts) {
+      int nl = 0;
+      for (long long t = 0; t < n; ++t) {
+        const long long p = fwd ? t : n - 1 - t;
+        int l = 0;
+        for (int k = c->hIncPtr[p]; k < c->hIncPtr[p + 1]; ++k) {
+          const int q = c->hNbOfSlot[k];
+          if (q < n && (fwd ? q < p : q > p)) l = std::max(l, lev[q] + 1);
+        }
+        lev[p] = l; nl = std::max(nl, l + 1);
+      }
+      ptr.assign(nl + 1, 0);
+      for (long long p = 0; p < n; ++p) ptr[lev[p] + 1]++;
+      for (int l = 0; l < nl; ++l) ptr[l + 1] += ptr[l];
+      pts.resize(n);
+      std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+      for (long long p = 0; p < n; ++p) pts[fill[lev[p]]++] = (int)p;
+      return nl;
+    };
+    std::vector<int> ptr, pts;
+    c->nLvlF = build(true, ptr, pts); c->lvlPtrF = dupload(c, ptr); c->lvlPtsF = dupload(c, pts);
+    c->nLvlB = build(false, ptr, pts); c->lvlPtrB = dupload(c, ptr); c->lvlPtsB = dupload(c, pts);
+    if (c->allocFailed) { c->err = "rx_turb_iterate: device allocation failed"; return RX_ERR_CUDA; }
+    c->turbStepReady = true;
+  }
+  while ((int)c->kw.size() < m + 1) {
+    c->kw.push_back(dalloc<double>(c, 2 * np)); c->kz.push_back(dalloc<double>(c, 2 * np));
+    if (!c->kw.back() || !c->kz.back()) { c->err = "rx_turb_iterate: device allocation failed"; return RX_ERR_CUDA; }
+  }
+  return RX_OK;
+}
+// dot product of two [2][nOwn] vectors: fixed block partials + fixed tree, result on the host (FGMRES needs it there)
+static int turb_dot(rx_ctx* c, const double* a, const double* b, double* out) {
+  const Dev& d = c->d;
+  k_turb_dot<<<c->tDotBlocks, 256, 0, c->stream>>>(d.nPointDomain, d.np, a, b, c->tPartial);
+  k_turb_sum<<<1, 256, 0, c->stream>>>(c->tPartial, c->tDotBlocks, 1, 0, c->tScal);
+  c->launches += 2;
+  RX_CK(cudaMemcpyAsync(out, c->tScal, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  return RX_OK;
+}
+int rx_turb_set_state(rx_ctx* c, const double* kOmega, const double* blend3) {
+  if (!c->tpost) { c->err = "rx_turb_set_state: not a RANS context"; return RX_ERR_ARG; }
+  int rc = RX_OK;
+  if (kOmega) rc = upload_aos(c, kOmega, c->tpost, 2);
+  if (!rc && blend3) rc = upload_aos(c, blend3, c->tpost + (size_t)TP_F1 * c->d.np, 3);   // F1, F2, CDkw are consecutive columns
+  return rc;
+}
+int rx_turb_get_step(rx_ctx* c, double* res2, double* dx2) {
+  if (!c->turbStepReady) { c->err = "rx_turb_get_step: no turbulence step has run"; return RX_ERR_ARG; }
+  int rc = RX_OK;
+  if (res2) {   // the work array holds the right-hand side -Res of the implicit system
+    rc = download_aos(c, c->tw.res, res2, 2);
+    for (long long k = 0; k < 2 * c->d.nPoint; ++k) res2[k] = -res2[k];
+  }
+  if (!rc && dx2) rc = download_aos(c, c->tw.x, dx2, 2);
+  return rc;
+}
+int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* linIters) {
+  if (!c->tpost) { c->err = "rx_turb_iterate: not a RANS context"; return RX_ERR_ARG; }
+  if (!c->haveWallDist) { c->err = "rx_turb_iterate: the wall distance has not been set (rx_set_wall_distance / rx_compute_wall_distance)"; return RX_ERR_ARG; }
+  if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_turb_iterate: single partition only (the LU-SGS sweeps across partitions are not built)"; return RX_ERR_UNSUPPORTED; }
+  if (!to || to->linIter < 1 || to->linIter > 64) { c->err = "rx_turb_iterate: bad options"; return RX_ERR_ARG; }
+  const int m = to->linIter;
+  int rc = turb_step_setup(c, m);
+  if (rc) return rc;
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  double* tp = c->tpost;
+  TurbC tc;
+  tc.alfa_1 = tc.beta_1 / tc.beta_star - tc.sigma_om1 * 0.41 * 0.41 / std::sqrt(tc.beta_star);
+  tc.alfa_2 = tc.beta_2 / tc.beta_star - tc.sigma_om2 * 0.41 * 0.41 / std::sqrt(tc.beta_star);
+  tc.kineInf = to->kineInf; tc.omegaInf = to->omegaInf; tc.cflRed = to->cflRed; tc.relax = to->relax;
+  const TurbW& w = c->tw;
+  const long long n = d.nPointDomain;
+  // Preprocessing: gradients of (k, omega); Set_OldSolution
+  if (c->o.leastSquares) { k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, tp); c->launches++; }
+  else {
+    k_turb_gradient_gg_edges<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, tp); c->launches++;
+    for (const MarkerDev& mk : c->markers)
+      if (mk.nVertex) { k_turb_gradient_gg_boundary<<<nblk(mk.nVertex, 64), 64, 0, s>>>(d, mk, tp); c->launches++; }
+    k_turb_gradient_gg_finish<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, tp); c->launches++;
+  }
+  RX_CK(cudaMemcpyAsync(w.old, tp, 2 * (size_t)d.np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  // Space_Integration: rows, then the boundary conditions (weak ones first, walls last: integration_structure.cpp:89-190)
+  k_turb_rows<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
+  for (const MarkerDev& mk : c->markers)
+    if (mk.nVertex && (mk.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || mk.kind == RX_BC_OUTLET)) {
+      k_turb_bc_io<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w, mk.kind == RX_BC_INLET_TEMPERATURE_IMPOSE ? 1 : 0); c->launches++;
+    }
+  for (const MarkerDev& mk : c->markers)
+    if (mk.nVertex && (mk.kind == RX_BC_ISOTHERMAL || mk.kind == RX_BC_HEATFLUX)) { k_turb_bc_wall<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w); c->launches++; }
+  // ImplicitEuler_Iteration
+  k_turb_implicit_rhs<<<c->tBlocks, 128, 0, s>>>(tc, d, w, c->tPartial);
+  k_turb_sum<<<1, 256, 0, s>>>(c->tPartial, c->tBlocks, 2, 0, c->tScal + 2);
+  k_turb_sum<<<1, 256, 0, s>>>(c->tPartial, c->tBlocks, 2, 1, c->tScal + 2);
+  c->launches += 3;
+  double ss[2];
+  RX_CK(cudaMemcpyAsync(ss, c->tScal + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RX_CK(cudaStreamSynchronize(s));
+  if (resRms2) for (int v = 0; v < 2; ++v) resRms2[v] = std::max(EPS * EPS, std::sqrt(ss[v] / (double)d.nPoint));   // SetResidual_RMS
+  // FGMRES (linear_solvers_structure.cpp:309-445), x0 = 0: w0 = (A x0 - b) / (-beta) = b / beta
+  auto precond = [&](const double* in, double* out) {
+    k_turb_lusgs<<<2, 1024, 0, s>>>(d, w, c->lvlPtrF, c->lvlPtsF, c->nLvlF, c->lvlPtrB, c->lvlPtsB, c->nLvlB, in, out); c->launches++;
+  };
+  const unsigned gv = nblk(2 * n, 256);
+  std::vector<double> g(m + 1, 0.0), sn(m + 1, 0.0), cs(m + 1, 0.0), y(m, 0.0);
+  std::vector<std::vector<double>> H(m + 1, std::vector<double>(m, 0.0));
+  double bb;
+  if ((rc = turb_dot(c, w.res, w.res, &bb))) return rc;
+  double norm0 = std::sqrt(bb), beta = norm0;
+  int it = 0;
+  if (!(beta < to->linTol * norm0 || beta < 2.220446049250313e-16)) {   // eps = machine epsilon (matrix_structure.hpp:49)
+    k_turb_scale_div<<<gv, 256, 0, s>>>(n, d.np, -beta, -1.0, w.res, c->kw[0]); c->launches++;
+    g[0] = beta; norm0 = beta;
+    auto applyGivens = [](double sg, double cg, double& h1, double& h2) { const double t = cg * h1 + sg * h2; h2 = cg * h2 - sg * h1; h1 = t; };
+    auto sign = [](double x, double yv) { return yv == 0.0 ? 0.0 : (yv < 0 ? -std::fabs(x) : std::fabs(x)); };
+    for (it = 0; it < m; ++it) {
+      if (beta < to->linTol * norm0) break;
+      precond(c->kw[it], c->kz[it]);
+      k_turb_matvec<<<nblk(n, 128), 128, 0, s>>>(d, w, c->kz[it], c->kw[it + 1]); c->launches++;
+      // ModGramSchmidt (:87-175)
+      double nrm;
+      if ((rc = turb_dot(c, c->kw[it + 1], c->kw[it + 1], &nrm))) return rc;
+      double thr = nrm * 0.98;
+      if (nrm <= 0.0 || nrm != nrm) { c->err = "SU2 has diverged (FGMRES: the Krylov vector of the turbulence system has no norm)"; return RX_ERR_NAN; }
+      for (int k = 0; k < it + 1; ++k) {
+        double prod;
+        if ((rc = turb_dot(c, c->kw[it + 1], c->kw[k], &prod))) return rc;
+        H[k][it] = prod;
+        k_turb_axpy<<<gv, 256, 0, s>>>(n, d.np, -prod, c->kw[k], c->kw[it + 1]); c->launches++;
+        if (prod * prod > thr) {
+          if ((rc = turb_dot(c, c->kw[it + 1], c->kw[k], &prod))) return rc;
+          H[k][it] += prod;
+          k_turb_axpy<<<gv, 256, 0, s>>>(n, d.np, -prod, c->kw[k], c->kw[it + 1]); c->launches++;
+        }
+        nrm -= H[k][it] * H[k][it];
+        if (nrm < 0.0) nrm = 0.0;
+        thr = nrm * 0.98;
+      }
+      if ((rc = turb_dot(c, c->kw[it + 1], c->kw[it + 1], &nrm))) return rc;
+      nrm = std::sqrt(nrm);
+      H[it + 1][it] = nrm;
+      k_turb_scale_div<<<gv, 256, 0, s>>>(n, d.np, nrm, 1.0, c->kw[it + 1], c->kw[it + 1]); c->launches++;
+      for (int k = 0; k < it; ++k) applyGivens(sn[k], cs[k], H[k][it], H[k + 1][it]);
+      {   // GenerateGivens (:44-71)
+        double& dx = H[it][it]; double& dy = H[it + 1][it]; double& sg = sn[it]; double& cg = cs[it];
+        if (dx == 0.0 && dy == 0.0) { cg = 1.0; sg = 0.0; }
+        else if (std::fabs(dy) > std::fabs(dx)) { const double t = dx / dy; dx = std::sqrt(1.0 + t * t); sg = sign(1.0 / dx, dy); cg = t * sg; }
+        else if (std::fabs(dy) <= std::fabs(dx)) { const double t = dy / dx; dy = std::sqrt(1.0 + t * t); cg = sign(1.0 / dy, dx); sg = t * cg; }
+        else { dx = 0.0; dy = 0.0; cg = 1.0; sg = 0.0; }
+        dx = std::fabs(dx * dy); dy = 0.0;
+      }
+      applyGivens(sn[it], cs[it], g[it], g[it + 1]);
+      beta = std::fabs(g[it + 1]);
+    }
+    // SolveReduced + x += sum y_k z_k
+    for (int k = 0; k < it; ++k) y[k] = g[k];
+    for (int k = it - 1; k >= 0; --k) { y[k] /= H[k][k]; for (int j = k - 1; j >= 0; --j) y[j] -= H[j][k] * y[k]; }
+    for (int k = 0; k < it; ++k) { k_turb_axpy<<<gv, 256, 0, s>>>(n, d.np, y[k], c->kz[k], w.x); c->launches++; }
+  }
+  if (linIters) *linIters = it;
+  k_turb_update<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
+  RX_CK(cudaGetLastError());
+  // Postprocessing: gradients of the new (k, omega), blending functions, eddy viscosity -> the fields the flow path reads
+  return rx_turb_postprocess(c, nullptr, c->sigmaK, 0);
+}
+
 int rx_get_turbulence(rx_ctx* c, double* post12) {
   if (!c->tpost) { c->err = "rx_get_turbulence: not a RANS context"; return RX_ERR_ARG; }
   return download_aos(c, c->tpost, post12, TP_N);

@@ -70,6 +70,10 @@ class _Opts(C.Structure):
                 ("device", C.c_int)]
 
 
+class _TurbOpts(C.Structure):
+    _fields_ = [("kineInf", C.c_double), ("omegaInf", C.c_double), ("cflRed", C.c_double), ("relax", C.c_double), ("linIter", C.c_int), ("linTol", C.c_double)]
+
+
 class _RestartInfo(C.Structure):
     _fields_ = [("aoa", C.c_double), ("sideslip", C.c_double), ("bcThrust", C.c_double), ("dCD_dCL", C.c_double), ("extIter", C.c_int64)]
 
@@ -101,6 +105,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_partition_kway", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
            "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read",
+           "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
 _lib = None
@@ -335,6 +340,24 @@ class CReactiveNSSolverGPU:
         viscosity; fills the turbulence fields the flow path reads.  stage 1 / 2: the two halves around the halo exchange."""
         kw = _c(kOmega) if kOmega is not None else None
         self._ck(self.lib.rx_turb_postprocess(self.ctx, _d(kw) if kw is not None else None, C.c_double(sigma_k), int(stage)))
+
+    def TurbSetState(self, kOmega=None, blend3=None):
+        """(k, omega) of the turbulence solver and, optionally, F1, F2, CDkw of its previous Postprocessing (rx_turb_set_state)."""
+        a = _c(kOmega) if kOmega is not None else None; b = _c(blend3) if blend3 is not None else None
+        self._ck(self.lib.rx_turb_set_state(self.ctx, _d(a) if a is not None else None, _d(b) if b is not None else None))
+
+    def TurbIterate(self, kine_inf, omega_inf, cfl_red=1.0, relax=1.0, lin_iter=5, lin_tol=1e-6):
+        """One SingleGrid_Iteration of the SST solver on the device (rx_turb_iterate); returns (residual norms of k and omega, FGMRES iterations)."""
+        o = _TurbOpts(kine_inf, omega_inf, cfl_red, relax, int(lin_iter), lin_tol)
+        rms = np.empty(2); n = C.c_int(0)
+        self._ck(self.lib.rx_turb_iterate(self.ctx, C.byref(o), _d(rms), C.byref(n)))
+        return rms, n.value
+
+    def TurbGetStep(self):
+        """(LinSysRes before the solve, solution of the linear system) of the last TurbIterate, [nPoint][2] each."""
+        r = np.empty((self.nPoint, 2)); x = np.empty((self.nPoint, 2))
+        self._ck(self.lib.rx_turb_get_step(self.ctx, _d(r), _d(x)))
+        return r, x
 
     def GetTurbulence(self):
         """[nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k."""

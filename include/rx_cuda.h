@@ -112,6 +112,22 @@ int rx_wall_distance(int64_t nPoint, const double* xy /* [nPoint][2] */, int64_t
 int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
 int rx_compute_wall_distance(rx_ctx*);   /* the same from the context's own mesh, on the device: nearest node of its ISOTHERMAL / HEAT_FLUX markers (single-partition meshes) */
 int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the (k, omega) uploaded by the previous call */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
+/* The SST transport step on the device (remainder; csrc/rx_turb_step.cuh): one
+ * CSingleGridIntegration::SingleGrid_Iteration of CTurbSSTSolver (integration_time.cpp:777-834) — Preprocessing
+ * (solver_direct_turbulent.cpp:2923), Upwind / Viscous / Source_Residual (:429, :521, :3018 with CUpwSca_TurbSST,
+ * CAvgGradCorrected_TurbSST, CSourcePieceWise_TurbSST), BC_Inlet / BC_Outlet / BC_HeatFlux_Wall / BC_Isothermal_Wall (:3087-3450),
+ * ImplicitEuler_Iteration (:615: FGMRES + LU-SGS of Common/src/linear_solvers_structure.cpp:309 and matrix_structure.cpp, clipped
+ * conservative update) and Postprocessing — on the flow state the last rx_iterate / rx_preprocess left (primitives, gradients,
+ * time steps, the boundary states of the inlet / outlet markers).  First-order upwind (SPATIAL_ORDER_TURB default), single partition.
+ * rx_turb_set_state: the turbulence solution (k, omega) [nPoint][2] and, optionally, F1, F2, CDkw [nPoint][3] of the previous
+ * Postprocessing (a restart or a test hands them over; in a run they stay resident).  rx_turb_get_step: LinSysRes before the solve
+ * and the solution of the linear system of the last step (parity tests).  resRms2 / linIters may be NULL. */
+typedef struct { double kineInf, omegaInf;   /* free-stream k, omega (CTurbSSTSolver ctor :2751-2752) for the inlet */
+                 double cflRed, relax;       /* CFL_REDUCTION_TURB, RELAXATION_FACTOR_TURB */
+                 int linIter; double linTol; /* LINEAR_SOLVER_ITER, LINEAR_SOLVER_ERROR (FGMRES, LU_SGS) */ } rx_turb_opts;
+int rx_turb_set_state(rx_ctx*, const double* kOmega, const double* blend3);
+int rx_turb_iterate(rx_ctx*, const rx_turb_opts*, double* resRms2, int* linIters);
+int rx_turb_get_step(rx_ctx*, double* res2 /* [nPoint][2] */, double* dx2 /* [nPoint][2] */);
 int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);
 int rx_get_solution(rx_ctx*, double* U);
 int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */

@@ -306,6 +306,10 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"prandtl_lam\": " << f->GetPrandtl_Lam() << ", \"prandtl_turb\": " << f->GetPrandtl_Turb()
      << ", \"lewis_turb\": " << f->GetLewis_Turb() << ", \"c_mu\": " << f->Get_Cmu() << ", \"pasr_lb\": " << f->Get_PaSR_LB()
      << ", \"tke_inf\": " << (c.rans ? c.flow->GetTke_Inf() : 0.0)
+     << ", \"kine_inf\": " << (c.rans ? static_cast<CTurbSSTSolver*>(c.sol[TURB_SOL])->kine_Inf : 0.0) << ", \"omega_inf\": " << (c.rans ? static_cast<CTurbSSTSolver*>(c.sol[TURB_SOL])->omega_Inf : 0.0)
+     << ", \"cfl_red_turb\": " << f->GetCFLRedCoeff_Turb() << ", \"relax_turb\": " << f->GetRelaxation_Factor_Turb()
+     << ", \"lin_iter\": " << f->GetLinear_Solver_Iter() << ", \"lin_tol\": " << f->GetLinear_Solver_Error()
+     << ", \"spatial_order_turb\": " << f->GetSpatialOrder_Turb()
      << ", \"grad_method\": " << f->GetKind_Gradient_Method() << ", \"time_scheme\": " << f->GetKind_TimeIntScheme_Flow()
      << ", \"kind_inlet\": " << f->GetKind_Inlet()
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
@@ -545,10 +549,39 @@ int main(int argc, char** argv) {
     clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
     if (!quiet) printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {
+      // CSingleGridIntegration::SingleGrid_Iteration (integration_time.cpp:777-834) for the SST solver, stage by stage so that the
+      // residual before the solve, the solution of the linear system and the updated (k, omega) can be dumped (the convergence
+      // monitor at its end only sets flags)
       c.cfg->SetGlobalParam(REACTIVE_RANS, RUNTIME_TURB_SYS, it);
-      drv->integration_container[ZONE_0][TURB_SOL]->SingleGrid_Iteration(drv->geometry_container, drv->solver_container,
-                                                                         drv->numerics_container, drv->config_container,
-                                                                         RUNTIME_TURB_SYS, it, ZONE_0);
+      CSolver* ts = c.sol[TURB_SOL];
+      CIntegration* ti = drv->integration_container[ZONE_0][TURB_SOL];
+      if (dmp) {   // what the step reads from the previous Postprocessing besides (k, omega): F1, F2, cross diffusion
+        std::vector<double> B(c.nPoint * 3);
+        for (unsigned long p = 0; p < c.nPoint; ++p) { B[3 * p] = ts->node[p]->GetF1blending(); B[3 * p + 1] = ts->node[p]->GetF2blending(); B[3 * p + 2] = ts->node[p]->GetCrossDiff(); }
+        dump_f64(tag(it, 0, "tblend"), B, {c.nPoint, 3});
+      }
+      ts->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_TURB_SYS, false);
+      ts->Set_OldSolution(c.geo);
+      ts->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, it);
+      ti->Space_Integration(c.geo, c.sol, drv->numerics_container[ZONE_0][MESH_0][TURB_SOL], c.cfg, MESH_0, NO_RK_ITER, RUNTIME_TURB_SYS);
+      if (dmp) {
+        std::vector<double> R(c.nPoint * 2);
+        for (unsigned long p = 0; p < c.nPoint; ++p) { R[2 * p] = ts->LinSysRes[2 * p]; R[2 * p + 1] = ts->LinSysRes[2 * p + 1]; }
+        dump_f64(tag(it, 0, "tres"), R, {c.nPoint, 2});   // LinSysRes after Upwind, Viscous, Source and the boundary conditions
+      }
+      ti->Time_Integration(c.geo, c.sol, c.cfg, NO_RK_ITER, RUNTIME_TURB_SYS, it);
+      if (dmp) {
+        std::vector<double> X(c.nPoint * 2), S(c.nPoint * 2), Q(2);
+        for (unsigned long p = 0; p < c.nPoint; ++p) {
+          X[2 * p] = ts->LinSysSol[2 * p]; X[2 * p + 1] = ts->LinSysSol[2 * p + 1];
+          S[2 * p] = ts->node[p]->GetSolution(0); S[2 * p + 1] = ts->node[p]->GetSolution(1);
+        }
+        dump_f64(tag(it, 0, "tdx"), X, {c.nPoint, 2});    // solution of the implicit system (FGMRES + LU-SGS)
+        dump_f64(tag(it, 0, "tsol"), S, {c.nPoint, 2});   // (k, omega) after the clipped conservative update
+        Q[0] = ts->GetRes_RMS(0); Q[1] = ts->GetRes_RMS(1);
+        dump_f64(tag(it, 0, "trms"), Q, {2});
+      }
+      ts->Postprocessing(c.geo, c.sol, c.cfg, MESH_0);
       if (dmp) dump_turb_post(c, tag(it, 0, "tpost"));   // flow state at this point: the out_ dump above
     }
     double r0 = log10(c.flow->GetRes_RMS(0)), r3 = log10(c.flow->GetRes_RMS(nDim + 1));
