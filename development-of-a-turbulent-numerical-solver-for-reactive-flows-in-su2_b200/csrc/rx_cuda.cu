@@ -38,7 +38,9 @@ struct rx_ctx {
   // SST transport step (rx_turb_step.cuh): work arrays, Krylov vectors, level lists of the LU-SGS sweeps
   TurbW tw{};
   bool turbStepReady = false;
-  int *lvlPtrF = nullptr, *lvlPtsF = nullptr, *lvlPtrB = nullptr, *lvlPtsB = nullptr, nLvlF = 0, nLvlB = 0;
+  SweepList swF{}, swB{};
+  SweepData sdF{}, sdB{};
+  int* posF = nullptr;              // point -> position in the forward sweep's level order
   std::vector<double*> kw, kz;      // FGMRES w[0..m], z[0..m]
   double *tPartial = nullptr, *tScal = nullptr;
   int tBlocks = 0, tDotBlocks = 0;
@@ -486,7 +488,7 @@ static int turb_step_setup(rx_ctx* c, int m) {
     // level lists: forward sweep level(p) = 1 + max over lower-numbered neighbours; backward sweep likewise over higher-numbered ones
     const long long n = d.nPointDomain;
     std::vector<int> lev(n, 0);
-    auto build = [&](bool fwd, std::vector<int>& ptr, std::vector<int>& pts) {
+    auto build = [&](bool fwd, SweepList& sl, SweepData& sd) {
       int nl = 0;
       for (long long t = 0; t < n; ++t) {
         const long long p = fwd ? t : n - 1 - t;
@@ -497,17 +499,27 @@ static int turb_step_setup(rx_ctx* c, int m) {
         }
         lev[p] = l; nl = std::max(nl, l + 1);
       }
-      ptr.assign(nl + 1, 0);
+      std::vector<int> ptr(nl + 1, 0), pts(n), pos(n), start(n + 1, 0), col, slot;
       for (long long p = 0; p < n; ++p) ptr[lev[p] + 1]++;
       for (int l = 0; l < nl; ++l) ptr[l + 1] += ptr[l];
-      pts.resize(n);
       std::vector<int> fill(ptr.begin(), ptr.end() - 1);
-      for (long long p = 0; p < n; ++p) pts[fill[lev[p]]++] = (int)p;
-      return nl;
+      for (long long p = 0; p < n; ++p) { pos[p] = fill[lev[p]]; pts[fill[lev[p]]++] = (int)p; }
+      for (long long t = 0; t < n; ++t) {   // the point's lower (upper) neighbours in slot order, as POSITIONS in this level order
+        const int p = pts[t];
+        for (int k = c->hIncPtr[p]; k < c->hIncPtr[p + 1]; ++k) {
+          const int q = c->hNbOfSlot[k];
+          if (fwd ? q < p : q > p) { col.push_back(pos[q]); slot.push_back(k); }
+        }
+        start[t + 1] = (int)col.size();
+      }
+      sl.nEnt = (int)col.size();
+      if (col.empty()) { col.push_back(0); slot.push_back(0); }
+      sl.nLvl = nl; sl.lvlPtr = dupload(c, ptr); sl.perm = dupload(c, pts); sl.start = dupload(c, start); sl.colL = dupload(c, col); sl.slot = dupload(c, slot);
+      sd.coefL = dalloc<double>(c, 2 * (size_t)std::max(sl.nEnt, 1)); sd.dgL = dalloc<double>(c, 2 * (size_t)n); sd.bL = dalloc<double>(c, 2 * (size_t)n); sd.xL = dalloc<double>(c, 2 * (size_t)n);
+      if (fwd) c->posF = dupload(c, pos);
     };
-    std::vector<int> ptr, pts;
-    c->nLvlF = build(true, ptr, pts); c->lvlPtrF = dupload(c, ptr); c->lvlPtsF = dupload(c, pts);
-    c->nLvlB = build(false, ptr, pts); c->lvlPtrB = dupload(c, ptr); c->lvlPtsB = dupload(c, pts);
+    build(true, c->swF, c->sdF);
+    build(false, c->swB, c->sdB);
     if (c->allocFailed) { c->err = "rx_turb_iterate: device allocation failed"; return RX_ERR_CUDA; }
     c->turbStepReady = true;
   }
@@ -588,8 +600,18 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   RX_CK(cudaStreamSynchronize(s));
   if (resRms2) for (int v = 0; v < 2; ++v) resRms2[v] = std::max(EPS * EPS, std::sqrt(ss[v] / (double)d.nPoint));   // SetResidual_RMS
   // FGMRES (linear_solvers_structure.cpp:309-445), x0 = 0: w0 = (A x0 - b) / (-beta) = b / beta
+  // level-order copies of the assembled rows for the sweeps (once per step), then per application: permute in, forward sweep,
+  // re-order to the backward sweep's level order, backward sweep, permute out
+  k_turb_sweep_coef<<<nblk(std::max<long long>(c->swF.nEnt, n), 256), 256, 0, s>>>(c->swF, c->sdF, w, n, d.np);
+  k_turb_sweep_coef<<<nblk(std::max<long long>(c->swB.nEnt, n), 256), 256, 0, s>>>(c->swB, c->sdB, w, n, d.np);
+  c->launches += 2;
   auto precond = [&](const double* in, double* out) {
-    k_turb_lusgs<<<2, 1024, 0, s>>>(d, w, c->lvlPtrF, c->lvlPtsF, c->nLvlF, c->lvlPtrB, c->lvlPtsB, c->nLvlB, in, out); c->launches++;
+    k_turb_perm_in<<<nblk(n, 256), 256, 0, s>>>(c->swF.perm, n, d.np, in, c->sdF.bL);
+    k_turb_sweep<false><<<2, 1024, 0, s>>>(c->swF, c->sdF, n);
+    k_turb_perm_ab<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, c->posF, n, c->sdF.xL, c->sdB.xL);
+    k_turb_sweep<true><<<2, 1024, 0, s>>>(c->swB, c->sdB, n);
+    k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, n, d.np, c->sdB.xL, out);
+    c->launches += 5;
   };
   const unsigned gv = nblk(2 * n, 256);
   std::vector<double> g(m + 1, 0.0), sn(m + 1, 0.0), cs(m + 1, 0.0), y(m, 0.0);

@@ -246,42 +246,106 @@ __global__ void __launch_bounds__(128) k_turb_matvec(const Dev d, const TurbW w,
 }
 
 // LU-SGS (CSysMatrix::ComputeLU_SGSPreconditioner): (D + L) x* = b by ascending levels, then (D + U) x = D x* by descending levels.
-// One block per variable walks the level lists; points of a level only depend on earlier levels.
-__global__ void __launch_bounds__(1024) k_turb_lusgs(const Dev d, const TurbW w, const int* __restrict__ lvlPtrF, const int* __restrict__ lvlPtsF, int nLvlF,
-                                                    const int* __restrict__ lvlPtrB, const int* __restrict__ lvlPtsB, int nLvlB,
-                                                    const double* __restrict__ b, double* __restrict__ out) {
+// One block per variable walks the level lists; points of a level only depend on earlier levels.  A sweep is a chain of ~(nx + 2 ny)
+// dependent steps on ONE SM, so what counts per step is (1) the number of dependent memory round trips and (2) the bytes that SM's
+// load/store path moves.  Hence the sweep runs in LEVEL-ORDER space: right-hand side, diagonal, coefficients, the neighbour lists and
+// the unknown itself are held in the order in which the sweep visits the points (SweepList; permuted in and out by full-grid
+// kernels), so every access of a level is a contiguous stream except the gathers of the neighbours' x, which land in the adjacent
+// levels' contiguous ranges; measured on the bench mesh: 27.7 ms per application with point-order arrays (the SM's load path moves
+// ~320 KB of 32-byte sectors per level for 8-byte words), see profiles/r2_summary.md for the level-order figure.
+// The loop over the levels is software-pipelined, one stage per dependent load: while level L is relaxed, the level bounds of L+3,
+// the list offsets of L+2 and the neighbour positions, coefficients, right-hand side and diagonal of L+1 are in flight.
+struct SweepList {
+  const int* lvlPtr;   // [nLvl + 1] offsets of the levels in level order
+  const int* perm;     // [n] level-order position -> point
+  const int* start;    // [n + 1] offsets of a position's (lower or upper) neighbours in colL / slot
+  const int* colL;     // neighbour's POSITION in this list's level order
+  const int* slot;     // index of the coefficient in TurbW::off (for the per-step gather into coefL)
+  int nLvl, nEnt;      // levels; neighbour entries
+};
+struct SweepData {     // per variable, in level order of one SweepList
+  double *coefL, *dgL, *bL, *xL;   // [2][nEnt], [2][n], [2][n], [2][n]
+};
+constexpr int SW_PRE = 3;   // neighbours carried in registers per point (a triangulated mesh has ~3 lower and ~3 upper ones; more: a plain loop)
+struct SwS0 { int n0, n1; };
+struct SwS1 { int t, a, cnt; };                                      // cnt < 0: no point for this thread at that level
+struct SwS2 { int t, a, cnt; int col[SW_PRE]; double coef[SW_PRE]; double b, dg; };   // b: right-hand side (forward) or x* (backward)
+
+template <bool BACK>
+__device__ __forceinline__ void sweep_run(const SweepList& sl, const double* __restrict__ coefL, const double* __restrict__ dgL, const double* __restrict__ bL, double* xL) {
+  const int nL = sl.nLvl;
+  auto st0 = [&](int L) { SwS0 r; r.n0 = 0; r.n1 = 0; if (L < nL) { r.n0 = sl.lvlPtr[L]; r.n1 = sl.lvlPtr[L + 1]; } return r; };
+  auto st1 = [&](const SwS0& q) { SwS1 r; r.t = q.n0 + (int)threadIdx.x; r.a = 0; r.cnt = -1;
+                                  if (r.t < q.n1) { r.a = sl.start[r.t]; r.cnt = sl.start[r.t + 1] - r.a; } return r; };
+  auto st2 = [&](const SwS1& q) { SwS2 r; r.t = q.t; r.a = q.a; r.cnt = q.cnt; r.b = 0.0; r.dg = 1.0;
+#pragma unroll
+                                  for (int j = 0; j < SW_PRE; ++j) { r.col[j] = 0; r.coef[j] = 0.0; }
+                                  if (q.cnt >= 0) {
+#pragma unroll
+                                    for (int j = 0; j < SW_PRE; ++j) if (j < q.cnt) { r.col[j] = sl.colL[q.a + j]; r.coef[j] = coefL[q.a + j]; }
+                                    r.dg = dgL[q.t];
+                                    r.b = BACK ? xL[q.t] : bL[q.t];
+                                  } return r; };
+  SwS0 q0 = st0(2);
+  SwS1 q1 = st1(st0(1));
+  SwS2 q2 = st2(st1(st0(0)));
+  for (int L = 0; L < nL; ++L) {
+    const SwS0 n0 = st0(L + 3);
+    const SwS1 n1 = st1(q0);
+    const SwS2 n2 = st2(q1);
+    if (q2.cnt >= 0) {
+      double s = 0.0;
+#pragma unroll
+      for (int j = 0; j < SW_PRE; ++j)
+        if (j < q2.cnt) s += q2.coef[j] * xL[q2.col[j]];
+      for (int j = SW_PRE; j < q2.cnt; ++j) s += coefL[q2.a + j] * xL[sl.colL[q2.a + j]];
+      xL[q2.t] = BACK ? (q2.dg * q2.b - s) / q2.dg : (q2.b - s) / q2.dg;
+    }
+    {   // levels wider than the block: the rest, unpipelined
+      const int m0 = sl.lvlPtr[L], m1 = sl.lvlPtr[L + 1];
+      for (int t = m0 + (int)blockDim.x + (int)threadIdx.x; t < m1; t += blockDim.x) {
+        const int a = sl.start[t], e = sl.start[t + 1];
+        double s = 0.0;
+        for (int k = a; k < e; ++k) s += coefL[k] * xL[sl.colL[k]];
+        xL[t] = BACK ? (dgL[t] * xL[t] - s) / dgL[t] : (bL[t] - s) / dgL[t];
+      }
+    }
+    __syncthreads();
+    q0 = n0; q1 = n1; q2 = n2;
+  }
+}
+template <bool BACK>
+__global__ void __launch_bounds__(1024) k_turb_sweep(const SweepList sl, const SweepData sd, long long n) {
   const int v = blockIdx.x;
-  const long long np = d.np;
-  const double* dg = w.diag + v * np;
-  const double* of = w.off + v * w.nInc;
-  double* x = out + v * np;
-  const double* bb = b + v * np;
-  for (int L = 0; L < nLvlF; ++L) {
-    for (int t = lvlPtrF[L] + threadIdx.x; t < lvlPtrF[L + 1]; t += blockDim.x) {
-      const int p = lvlPtsF[t];
-      double s = 0.0;
-      for (int k = d.incPtr[p]; k < d.incPtr[p + 1]; ++k) {
-        const int code = d.incEdge[k];
-        const int q = code >= 0 ? d.ej[code] : d.ei[~code];
-        if (q < p) s += of[k] * x[q];
-      }
-      x[p] = (bb[p] - s) / dg[p];
-    }
-    __syncthreads();
+  sweep_run<BACK>(sl, sd.coefL + (size_t)v * sl.nEnt, sd.dgL + v * n, sd.bL + v * n, sd.xL + v * n);
+}
+// per step: coefficients and diagonal of the assembled rows into level order
+__global__ void k_turb_sweep_coef(const SweepList sl, const SweepData sd, const TurbW w, long long n, long long np) {
+  const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    if (k < sl.nEnt) sd.coefL[(size_t)v * sl.nEnt + k] = w.off[v * w.nInc + sl.slot[k]];
+    if (k < n) sd.dgL[v * n + k] = w.diag[v * np + sl.perm[k]];
   }
-  for (int L = 0; L < nLvlB; ++L) {
-    for (int t = lvlPtrB[L] + threadIdx.x; t < lvlPtrB[L + 1]; t += blockDim.x) {
-      const int p = lvlPtsB[t];
-      double s = 0.0;
-      for (int k = d.incPtr[p]; k < d.incPtr[p + 1]; ++k) {
-        const int code = d.incEdge[k];
-        const int q = code >= 0 ? d.ej[code] : d.ei[~code];
-        if (q > p) s += of[k] * x[q];
-      }
-      x[p] = (dg[p] * x[p] - s) / dg[p];
-    }
-    __syncthreads();
-  }
+}
+// per application: point order -> level order (dst[v][t] = src[v][perm[t]]), level order A -> level order B, level order -> point order
+__global__ void k_turb_perm_in(const int* __restrict__ perm, long long n, long long np, const double* __restrict__ src, double* __restrict__ dst) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int p = perm[t];
+  dst[t] = src[p]; dst[n + t] = src[np + p];
+}
+__global__ void k_turb_perm_ab(const int* __restrict__ permB, const int* __restrict__ posA, long long n, const double* __restrict__ xA, double* __restrict__ xB) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int s = posA[permB[t]];
+  xB[t] = xA[s]; xB[n + t] = xA[n + s];
+}
+__global__ void k_turb_perm_out(const int* __restrict__ perm, long long n, long long np, const double* __restrict__ src, double* __restrict__ dst) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int p = perm[t];
+  dst[p] = src[t]; dst[np + p] = src[n + t];
 }
 
 // vector kernels over [2][nOwn] (stride np): dot product partials (blocks of 256, fixed tree), axpy, scale
