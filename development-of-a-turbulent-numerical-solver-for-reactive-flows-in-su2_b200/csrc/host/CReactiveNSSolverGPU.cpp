@@ -281,7 +281,9 @@ void CReactiveNSSolverGPU::Preprocessing(CGeometry* geometry, CSolver** solver_c
   extIter = config->GetExtIter();
   const bool wasDirty = hostDirty;   // a state set on the host (restart, initial condition) has no device primitives yet
   if (hostDirty) UploadState();
-  if (ransMode) {
+  if (ransMode && turbOnDevice) {
+    // CTurbSSTSolverGPU keeps (mu_t, k, omega, grad k, sigma_k) current on the device: nothing to hand over
+  } else if (ransMode) {
     const bool onDevice = turbPost && turbPostReady && !wasDirty;
     if (!onDevice) UploadTurbulence(solver_container);
     else if (iRKStep == 0 && !Output) DeviceTurbPostprocessing(geometry, solver_container);
@@ -396,4 +398,12 @@ void CReactiveNSSolverGPU::WriteRestart(CGeometry* geometry, CSolver** solver_co
   info.bcThrust = config->GetInitial_BCThrust(); info.dCD_dCL = config->GetdCD_dCL();
   info.extIter = (int64_t)(config->GetExtIter() + config->GetExtIter_OffSet() + 1);
   Check(rx_restart_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, &info, 0), "rx_restart_write");
+}
+
+void CReactiveNSSolverGPU::SetTurbulenceOnDevice(const double* post12) {
+  turbOnDevice = true;
+  for (unsigned long p = 0; p < nPoint; ++p) {
+    double* t = &bufT[p * 6]; const double* q = &post12[p * 12];
+    t[0] = q[6]; t[1] = q[0]; t[2] = q[1]; t[3] = q[7]; t[4] = q[8]; t[5] = q[11];
+  }
 }

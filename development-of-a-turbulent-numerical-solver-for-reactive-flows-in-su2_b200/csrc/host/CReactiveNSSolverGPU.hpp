@@ -62,8 +62,11 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);
 
   // node[]->Solution was changed on the host (restart, initial condition): upload before the next stage
-  void MarkHostSolutionDirty() { hostDirty = true; }
+  void MarkHostSolutionDirty() { hostDirty = true; turbOnDevice = false; }   // the turbulence fields are taken from the host again, too
   rx_ctx* Context() { return ctx; }
+  // called by CTurbSSTSolverGPU after its step: the six turbulence fields the flow path reads are current on the device (no upload at
+  // the next Preprocessing); post12 = rx_get_turbulence rows, for the host mirror of the eddy viscosity
+  void SetTurbulenceOnDevice(const double* post12);
 
  private:
   void Check(int rc, const char* where);
@@ -86,7 +89,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   int mirror = 1;
   // SU2_RX_TURB_POST=1: the fields the flow path reads from the SST solver (muT, grad k, sigma_k) are formed on the device from
   // (k, omega) by rx_turb_postprocess instead of being copied from CTurbSSTSolver::Postprocessing's results
-  bool turbPost = false, turbPostReady = false, wallDistSet = false;
+  bool turbPost = false, turbPostReady = false, wallDistSet = false, turbOnDevice = false;
   unsigned long extIter = 0;
   std::vector<double> bufU, bufV, bufAux, bufGrad, bufR, bufT;
 };

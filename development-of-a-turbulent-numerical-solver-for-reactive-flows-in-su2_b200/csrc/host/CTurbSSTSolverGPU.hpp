@@ -1,0 +1,39 @@
+// CTurbSSTSolverGPU — the turbulence half of the drop-in: a CTurbSSTSolver whose whole iteration (Preprocessing, Upwind / Viscous /
+// Source residual, boundary conditions, implicit Euler step with FGMRES + LU-SGS, Postprocessing) runs on the device state of the
+// flow solver (a CReactiveNSSolverGPU in solver_container[FLOW_SOL]) through rx_turb_iterate (include/rx_cuda.h,
+// csrc/rx_turb_step.cuh).  CSingleGridIntegration::SingleGrid_Iteration (integration_time.cpp:777-834) drives it unchanged: the residual
+// and boundary virtuals are no-ops, ImplicitEuler_Iteration does the step, the (k, omega, mu_t, F1, F2, CDkw, gradients) mirrors in
+// node[] are refreshed for output and restart.  With it a RANS run hands nothing per point across PCIe between the two solvers.
+// Factory switch: the `new CTurbSSTSolver(...)` of driver_structure.cpp:817.
+#pragma once
+#include "solver_structure.hpp"
+#include "rx_cuda.h"
+
+class CReactiveNSSolverGPU;
+
+class CTurbSSTSolverGPU : public CTurbSSTSolver {
+ public:
+  CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {}
+
+  void Preprocessing(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short, bool) override {}
+  void Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) override {}
+  void Viscous_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short, unsigned short) override {}
+  void Source_Residual(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void BC_HeatFlux_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void BC_Inlet(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void BC_Outlet(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void ImplicitEuler_Iteration(CGeometry* geometry, CSolver** solver_container, CConfig* config) override;
+  // done on the device at the end of every step; the one call the driver makes right after constructing the solver
+  // (driver_structure.cpp:817-819: flow Preprocessing, then this) forms the initial blending functions and eddy viscosity on the device
+  void Postprocessing(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iMesh) override;
+
+  // node[]->Solution was changed on the host (restart, initial condition): hand (k, omega, F1, F2, CDkw) to the device before the next step
+  void MarkHostSolutionDirty() { hostDirty = true; }
+
+ private:
+  void MirrorFromDevice(rx_ctx* ctx, CReactiveNSSolverGPU* flow);
+  void SetWallDistance(rx_ctx* ctx, CGeometry* geometry);
+  bool hostDirty = true, wallDistSet = false, stepped = false;
+  int mirror = 1;   // env SU2_RX_MIRROR as for the flow solver: 2 also mirrors LinSysRes / LinSysSol (parity dumps)
+};

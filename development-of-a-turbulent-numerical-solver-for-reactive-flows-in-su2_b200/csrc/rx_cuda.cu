@@ -59,6 +59,7 @@ struct rx_ctx {
   bool bcConcurrent = false;
   bool orderEdges = true;           // viscous kernel processes the edges grouped by their last iteration count (rx_order.cuh); default: laminar on, RANS off; env RX_VISC_ORDER=0/1 forces
   int* eOrderBuf = nullptr; int nOrdTiles = 0;
+  double* eddyFlow = nullptr;       // RANS: eddy viscosity as the flow variables hold it (copied at every rx_preprocess, CReactiveNSVariable::SetPrimVar :1193) — what COutput writes
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
   bool haveWallDist = false; double sigmaK = 0.85;
 };
@@ -289,7 +290,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.lim = dalloc<double>(c, np * 4);
   d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
-  d.turb = dalloc<double>(c, np * 6); c->tpost = o.rans ? dalloc<double>(c, np * TP_N) : nullptr; d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
+  d.turb = dalloc<double>(c, np * 6); c->tpost = o.rans ? dalloc<double>(c, np * TP_N) : nullptr; c->eddyFlow = o.rans ? dalloc<double>(c, np) : nullptr; d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
   d.fluxV = o.viscous ? dalloc<double>(c, ne * c->nVar) : nullptr;
   d.eOrder = nullptr;
@@ -717,6 +718,7 @@ int rx_preprocess(rx_ctx* c, int64_t extIter, int output, int64_t* nonPhysical) 
   cudaStream_t s = c->stream;
   RX_CK(cudaMemsetAsync(d.counters, 0, sizeof(unsigned long long), s));
   k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, (long long)extIter, output);
+  if (c->eddyFlow) RX_CK(cudaMemcpyAsync(c->eddyFlow, d.turb, (size_t)d.np * sizeof(double), cudaMemcpyDeviceToDevice, s));
   if (c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }
   c->launches++;
   if (c->o.viscous || c->o.secondOrder) {

@@ -23,7 +23,7 @@ namespace rx {
 constexpr long long RST_CHUNK = 1 << 18;   // points per staging chunk
 
 // one chunk of fields, SoA on the device -> [field][point] in the pinned buffer
-__global__ void k_restart_gather(const Dev d, int rans, int viscous, long long p0, long long n, int nv, const long long* __restrict__ order,
+__global__ void k_restart_gather(const Dev d, const double* __restrict__ eddyFlow, int rans, int viscous, long long p0, long long n, int nv, const long long* __restrict__ order,
                                  double* __restrict__ out) {
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (t >= n) return;
@@ -42,7 +42,7 @@ __global__ void k_restart_gather(const Dev d, int rans, int viscous, long long p
     out[(f++) * n + t] = sqrt(v2) / d.V[V_A * d.np + p];
   }
   if (viscous) out[(f++) * n + t] = d.mu[p];
-  if (rans) out[(f++) * n + t] = d.turb[p];   // eddy viscosity as the flow variable holds it (SetEddyViscosity)
+  if (rans) out[(f++) * n + t] = eddyFlow[p];   // eddy viscosity as the flow variable holds it (set at the last Preprocessing), not the turbulence solver's newer one
 }
 
 inline void restart_format(const double* buf, long long n, int nf, const long long* ids, std::string& out) {
@@ -114,7 +114,7 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
   int rc = RX_OK;
   for (long long p0 = 0; p0 < nOwn && rc == RX_OK; p0 += chunk) {
     const long long n = std::min(chunk, nOwn - p0);
-    k_restart_gather<<<nblk(n, 256), 256, 0, c->stream>>>(d, rans ? 1 : 0, visc ? 1 : 0, p0, n, c->nVar, dOrder, dev);
+    k_restart_gather<<<nblk(n, 256), 256, 0, c->stream>>>(d, c->eddyFlow, rans ? 1 : 0, visc ? 1 : 0, p0, n, c->nVar, dOrder, dev);
     c->launches++;
     if (cudaMemcpyAsync(pin, dev, (size_t)n * nf * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
         cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "rx_restart_write: device copy failed"; rc = RX_ERR_CUDA; break; }

@@ -18,6 +18,7 @@
 // ref_harness_gpu: the same driver loop and dumps, with the flow solver object replaced by the CUDA-backed subclass
 // (package csrc/host/CReactiveNSSolverGPU) when SU2_RX_BACKEND=cuda — the drop-in demonstration of INTEGRATION.md.
 #include "CReactiveNSSolverGPU.hpp"
+#include "CTurbSSTSolverGPU.hpp"
 #include <cstring>
 #endif
 #include <cstdio>
@@ -397,6 +398,10 @@ static void perturb_state(Ctx& c, unsigned long seed) {
     for (unsigned short s = 0; s < Ns; ++s) U[4 + s] = rho * Y[s];
     for (unsigned short q = 0; q < c.nVar; ++q) { c.flow->node[p]->SetSolution(q, U[q]); c.flow->node[p]->SetSolution_Old(q, U[q]); }
   }
+#ifdef RX_WITH_GPU
+  if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->MarkHostSolutionDirty();
+  if (c.rans) if (CTurbSSTSolverGPU* t = dynamic_cast<CTurbSSTSolverGPU*>(c.sol[TURB_SOL])) t->MarkHostSolutionDirty();
+#endif
 }
 
 // ---- edge cases of the cons->prim path that a smooth state never reaches ("What's weak" #2).  Applied to the
@@ -473,6 +478,14 @@ int main(int argc, char** argv) {
     // the factory switch of driver_structure.cpp:795-801, applied after the driver built its containers
     c.sol[FLOW_SOL] = new CReactiveNSSolverGPU(c.geo, c.cfg, MESH_0);
     printf("HARNESS flow solver: CReactiveNSSolverGPU (librx_cuda)\n");
+    // the factory switch of driver_structure.cpp:817: the SST solver's iteration on the device as well (SU2_RX_TURB=device)
+    if (getenv("SU2_RX_TURB") && !strcmp(getenv("SU2_RX_TURB"), "device") && c.cfg->GetKind_Solver() == REACTIVE_RANS) {
+      c.sol[TURB_SOL] = new CTurbSSTSolverGPU(c.geo, c.cfg, MESH_0);
+      // what the driver does right after constructing the SST solver (driver_structure.cpp:818-819)
+      c.sol[FLOW_SOL]->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, false);
+      c.sol[TURB_SOL]->Postprocessing(c.geo, c.sol, c.cfg, MESH_0);
+      printf("HARNESS turbulence solver: CTurbSSTSolverGPU (rx_turb_iterate)\n");
+    }
   }
 #endif
   c.flow = dynamic_cast<CReactiveEulerSolver*>(c.sol[FLOW_SOL]);

@@ -32,18 +32,23 @@ def _run(binary, d, out, nit, seed, env):
 
 # RANS cases once more with SU2_RX_TURB_POST=1: muT, grad k, sigma_k formed on the device by rx_turb_postprocess from (k, omega)
 # instead of copied from the host-side CTurbSSTSolver::Postprocessing
-PARAMS = [(n, False) for n in RUNS] + [("channel_rans", True), ("jet_rans_perturbed", True), ("channel_rans_gg", True)]
+# and with SU2_RX_TURB=device: the SST solver object replaced by CTurbSSTSolverGPU as well — its whole iteration (residuals, boundary
+# conditions, FGMRES + LU-SGS, update, Postprocessing) runs on the device (rx_turb_iterate); the reference's driver and integration
+# classes still drive both solvers
+PARAMS = [(n, False, False) for n in RUNS] + [("channel_rans", True, False), ("jet_rans_perturbed", True, False), ("channel_rans_gg", True, False)] + \
+         [("channel_rans", False, True), ("jet_rans_perturbed", False, True), ("channel_rans_gg", False, True)]
 
 
-@pytest.mark.parametrize("name,turb_post", PARAMS)
-def test_reference_driver_with_cuda_solver(name, turb_post, tmp_path):
+@pytest.mark.parametrize("name,turb_post,turb_dev", PARAMS)
+def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
     d = os.path.join(CASES, name)
     if not (os.path.exists(HARNESS) and os.path.exists(HARNESS_CPU) and os.path.exists(os.path.join(d, "case.cfg"))):
         pytest.skip("oracle/_ref harnesses or the case directory are not in this snapshot (built by oracle/build_ref.sh where the reference tree is present)")
     nit, seed = RUNS[name]
     out_g, out_c = str(tmp_path / "gpu"), str(tmp_path / "cpu")
-    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1"))
-    assert "CReactiveNSSolverGPU" in txt
+    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1",
+                                                     SU2_RX_TURB="device" if turb_dev else "host"))
+    assert "CReactiveNSSolverGPU" in txt and (("CTurbSSTSolverGPU" in txt) == turb_dev)
     # restart file: the reference's COutput (fed by the subclass's host mirrors) and the subclass's own device writer, same run
     if "rx_restart_write" in txt:
         a = open(os.path.join(d, "restart_flow.dat"), "rb").read(); b = open(os.path.join(d, "restart_flow_gpu.dat"), "rb").read()
@@ -57,12 +62,14 @@ def test_reference_driver_with_cuda_solver(name, turb_post, tmp_path):
         if not f.endswith(".npy") or not k.startswith("it"):
             continue
         what = k.split("_", 2)[-1]
-        if what in ("U0", "turb") or what.startswith("prev_"):
+        if what in ("U0", "turb", "tblend") or what.startswith("prev_"):
             continue   # inputs of the iteration (checked through what they produce)
+        if turb_dev and what == "tres":
+            continue   # the device assembles and solves in one call: LinSysRes is not mirrored before the solve (tests/test_gpu_turb_step.py compares it)
         a = np.load(os.path.join(out_g, f)); ref = np.load(os.path.join(out_c, f))
         if case.has(k) and case[k].shape == ref.shape:
             assert np.array_equal(ref, case[k]), "CPU reference run differs from the committed golden fixture: " + k
-        if what == "rms":
+        if what in ("rms", "trms"):
             a = a.reshape(1, -1); ref = ref.reshape(1, -1)
         if what == "dt":
             err = np.abs(a - ref).max(axis=0) / np.maximum(np.abs(ref).max(axis=0), 1e-300)

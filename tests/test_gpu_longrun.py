@@ -101,19 +101,22 @@ def test_laminar_channel_2000_iterations_fields_and_history():
     assert hd.max() <= TOL_HIST, rec
 
 
-def test_shipped_jet_rans_500_iterations_through_the_dropin(tmp_path):
+@pytest.mark.parametrize("turb", ["host", "device"])
+def test_shipped_jet_rans_500_iterations_through_the_dropin(turb, tmp_path):
+    """turb = host: the reference's CTurbSSTSolver on the CPU next to the CUDA flow solver; device: CTurbSSTSolverGPU as well — both
+    solvers' iterations on the device (rx_iterate-equivalent staged calls + rx_turb_iterate), the reference's driver / integration on top."""
     d = os.path.join(CASES, "jet_rans_shipped")
     if not (os.path.exists(HARNESS_GPU) and os.path.exists(os.path.join(d, "case_long.cfg"))):
         pytest.skip("oracle/_ref/ref_harness_gpu or the case directory is not in this snapshot")
     g = np.load(os.path.join(GOLDEN, "long_jet_rans_shipped.npz"))
     meta = json.loads(bytes(g["meta_json"]).decode())
     out = str(tmp_path / "gpu")
-    env = dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="1", RX_CKPT=",".join(map(str, meta["ckpt"])), RX_QUIET="1")
+    env = dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="1", SU2_RX_TURB=turb, RX_CKPT=",".join(map(str, meta["ckpt"])), RX_QUIET="1")
     log = subprocess.run([HARNESS_GPU, "case_long.cfg", str(meta["nIter"]), out, str(10 ** 9)], cwd=d, env=env,
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
     assert log.returncode == 0, log.stdout[-3000:]
-    assert "CReactiveNSSolverGPU" in log.stdout
-    rec = {"iterations": meta["nIter"], "checkpoints": {}}
+    assert "CReactiveNSSolverGPU" in log.stdout and (("CTurbSSTSolverGPU" in log.stdout) == (turb == "device"))
+    rec = {"iterations": meta["nIter"], "checkpoints": {}, "turbulence_solver": turb}
     worst = 0.0
     nVar = g["ckpt000000_U"].shape[1]
     for n in meta["ckpt"]:
@@ -129,7 +132,7 @@ def test_shipped_jet_rans_500_iterations_through_the_dropin(tmp_path):
     rec["history_max_dlog10"] = float(hd.max()); rec["history_argmax_iter"] = int(hd.argmax())
     rec["history_dlog10_at"] = {str(k): float(hd[:k].max()) for k in (1, 10, 100, 250, 500) if k <= meta["nIter"]}
     rec["history_raw_max_dlog10_per_variable"] = [float(x) for x in hraw]
-    _report("long_jet_rans_shipped", rec)
+    _report("long_jet_rans_shipped_turb_" + turb, rec)
     print(json.dumps(rec, indent=1))
     assert worst <= TOL_FIELD, rec
     assert hd.max() <= TOL_HIST, rec
