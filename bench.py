@@ -610,7 +610,7 @@ def main():
     bytes_visc = 24.0 + (400.0 + 208.0) / (nE / float(nOwn))
     bytes_conv = 24.0 + (128.0 + 104.0) / (nE / float(nOwn))
     t_visc, t_conv = kt["edge_flux_visc"] * 1e-3, kt["edge_flux_conv"] * 1e-3
-    traffic, flops_exec, prof_src = None, None, None
+    traffic, flops_exec, prof_src, inst_exec, pipe_pct = None, None, None, None, None
     for f in ("r2_traffic.json", "r1_traffic.json"):
         try:   # dram bytes and executed FP64 operations of one launch from the committed ncu capture of this kernel at this workload size
             pr = json.load(open(os.path.join(ROOT, "profiles", f)))
@@ -618,6 +618,7 @@ def main():
                 q = pr.get("k_edge_visc_pair_rans" if rans else "k_edge_visc_pair")
                 if isinstance(q, dict):
                     traffic, flops_exec = q.get("dram_bytes"), q.get("fp64_flops_per_edge")
+                    inst_exec, pipe_pct = q.get("fp64_inst_per_edge"), q.get("fp64_pipe_pct_of_peak")
                 else:
                     traffic = q
                 prof_src = "profiles/" + f
@@ -651,6 +652,12 @@ def main():
                      "flops_per_edge": flops_per_edge, "flops_per_edge_source": ("executed FP64 operations counted by ncu, " + str(prof_src)) if flops_exec else "reference operation sequence (SURVEY.md 8(d) estimate)",
                      "flops_per_edge_reference_sequence": flops_ref, "frac_reference_sequence": flops_ref * nE / t_visc / 1e12 / fp64_peak if fp64_peak else None,
                      "bytes_per_edge": bytes_visc,
+                     # the same kernel in FP64 INSTRUCTION slots: -fmad=false (parity with the x86-64 reference) leaves two thirds of the
+                     # FP64 instructions as plain DADD / DMUL, which occupy a pipe slot for one FLOP; slots/s against the DFMA slot rate
+                     # (peak / 2) is what the pipe sees (ncu: sm__pipe_fp64_cycles_active of the committed capture next to it)
+                     "fp64_inst_per_edge": inst_exec,
+                     "pipe_slot_frac": (inst_exec * nE / t_visc / (fp64_peak * 1e12 / 2.0)) if (inst_exec and fp64_peak) else None,
+                     "ncu_fp64_pipe_pct_of_peak": pipe_pct,
                      "hbm_view": {"achieved": ach_hbm_visc, "peak": hbm, "unit": "GB/s", "frac": ach_hbm_visc / hbm, "peak_source": hbm_src},
                      "conv_kernel": {"kernel": CONV_KERNEL_NAME, "bound": "hbm", "achieved": ach_hbm_conv, "peak": hbm,
                                      "unit": "GB/s", "frac": ach_hbm_conv / hbm, "bytes_per_edge": bytes_conv, "peak_source": hbm_src}},
