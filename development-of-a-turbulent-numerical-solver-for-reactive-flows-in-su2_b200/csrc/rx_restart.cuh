@@ -65,6 +65,7 @@ inline void restart_format(const double* buf, long long n, int nf, const long lo
 extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* globalIndex, const double* kOmega, const rx_restart_info* info, int piece) {
   using namespace rx;
   if (!c || !path) { if (c) c->err = "rx_restart_write: null argument"; return RX_ERR_ARG; }
+  { const int rc = ensure_output(c); if (rc) return rc; }   // laminar viscosity of the Output pass
   const Dev& d = c->d;
   const bool rans = c->o.rans != 0, visc = c->o.viscous != 0;
   if (rans && !kOmega) { c->err = "rx_restart_write: a RANS restart carries the turbulence solution (k, omega): kOmega must not be NULL"; return RX_ERR_ARG; }
