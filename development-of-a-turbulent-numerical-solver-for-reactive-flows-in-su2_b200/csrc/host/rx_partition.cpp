@@ -16,6 +16,10 @@
 #include <numeric>
 #include <utility>
 #include <vector>
+#include <dlfcn.h>
+#include <cstdlib>
+#include <cstring>
+#include <string>
 
 #include "../../../include/rx_cuda.h"
 
@@ -123,9 +127,67 @@ void refine_kway(const Graph& g, int nParts, int64_t* owner, int passes, double 
 
 }  // namespace
 
+// ---- optional METIS backend: METIS_PartGraphKway of the copy vendored in the reference tree (csrc/host/build_metis.sh ->
+// librx_metis.so next to this library, or RX_METIS_LIB), bound with dlopen.  The reference partitions with ParMETIS_V3_PartKway
+// (geometry_structure.cpp:11524); the serial multilevel k-way routine is the same algorithm family.  32-bit idx_t, 40 option words.
+namespace {
+typedef int (*metis_kway_fn)(int32_t*, int32_t*, int32_t*, int32_t*, int32_t*, int32_t*, int32_t*, int32_t*, float*, float*, int32_t*, int32_t*, int32_t*);
+typedef int (*metis_opts_fn)(int32_t*);
+struct MetisApi { void* h = nullptr; metis_kway_fn kway = nullptr; metis_opts_fn defaults = nullptr; bool tried = false; };
+MetisApi& metis_api() {
+  static MetisApi m;
+  if (m.tried) return m;
+  m.tried = true;
+  std::string path;
+  if (const char* e = std::getenv("RX_METIS_LIB")) path = e;
+  else {
+    Dl_info info;
+    if (dladdr((void*)&metis_api, &info) && info.dli_fname) {
+      path = info.dli_fname;
+      const size_t k = path.find_last_of('/');
+      path = (k == std::string::npos ? std::string(".") : path.substr(0, k)) + "/librx_metis.so";
+    }
+  }
+  if (path.empty()) return m;
+  m.h = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+  if (!m.h) return m;
+  m.kway = (metis_kway_fn)dlsym(m.h, "METIS_PartGraphKway");
+  m.defaults = (metis_opts_fn)dlsym(m.h, "METIS_SetDefaultOptions");
+  if (!m.kway || !m.defaults) { dlclose(m.h); m.h = nullptr; }
+  return m;
+}
+bool want_metis() {
+  const char* e = std::getenv("RX_PARTITIONER");
+  if (e && !std::strcmp(e, "own")) return false;
+  return metis_api().h != nullptr;
+}
+int64_t cut_of(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const int64_t* owner) {
+  int64_t cut = 0;
+  for (int64_t v = 0; v < nPoint; ++v)
+    for (int64_t q = nbPtr[v]; q < nbPtr[v + 1]; ++q)
+      if (nbPoint[q] > v && nbPoint[q] < nPoint && owner[nbPoint[q]] != owner[v]) ++cut;
+  return cut;
+}
+}  // namespace
+
+extern "C" int rx_partition_backend(void) { return want_metis() ? 1 : 0; }   // 1: METIS (librx_metis.so found), 0: the library's own partitioner
+
 extern "C" int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const double* coord, int nParts,
                                  int refinePasses, int64_t* owner, int64_t* edgeCut) {
   if (nPoint < 0 || nParts < 1 || !nbPtr || !nbPoint || !coord || !owner || (int64_t)nParts > std::max<int64_t>(nPoint, 1)) return RX_ERR_ARG;
+  if (want_metis() && nParts > 1 && nPoint < (1LL << 31) && nbPtr[nPoint] < (1LL << 31)) {
+    MetisApi& m = metis_api();
+    std::vector<int32_t> xadj(nPoint + 1), adj(nbPtr[nPoint]), part(nPoint);
+    for (int64_t v = 0; v <= nPoint; ++v) xadj[v] = (int32_t)nbPtr[v];
+    for (int64_t q = 0; q < nbPtr[nPoint]; ++q) adj[q] = (int32_t)nbPoint[q];
+    int32_t nv = (int32_t)nPoint, ncon = 1, np = nParts, cut = 0, opts[40];
+    m.defaults(opts);
+    if (m.kway(&nv, &ncon, xadj.data(), adj.data(), nullptr, nullptr, nullptr, &np, nullptr, nullptr, opts, &cut, part.data()) == 1) {   // METIS_OK
+      for (int64_t v = 0; v < nPoint; ++v) owner[v] = part[v];
+      if (edgeCut) *edgeCut = cut_of(nPoint, nbPtr, nbPoint, owner);
+      return RX_OK;
+    }
+  }
   const Graph g{nPoint, nbPtr, nbPoint};
   const double tol = 0.02;
   {
@@ -137,13 +199,7 @@ extern "C" int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int
     bisect(g, coord, ids, 0, nParts, label, side, nextSub, std::max(refinePasses, 0), tol, owner);
   }
   if (nParts > 2 && refinePasses > 0) refine_kway(g, nParts, owner, refinePasses, tol);
-  if (edgeCut) {
-    int64_t cut = 0;
-    for (int64_t v = 0; v < nPoint; ++v)
-      for (int64_t q = nbPtr[v]; q < nbPtr[v + 1]; ++q)
-        if (nbPoint[q] > v && nbPoint[q] < nPoint && owner[nbPoint[q]] != owner[v]) ++cut;
-    *edgeCut = cut;
-  }
+  if (edgeCut) *edgeCut = cut_of(nPoint, nbPtr, nbPoint, owner);
   return RX_OK;
 }
 

@@ -219,12 +219,16 @@ int rx_libm_eval(int which, int64_t n, const double* x, const double* y, double*
  * rx_partition_kway: k-way partition of the point adjacency graph (CSR nbPtr/nbPoint, the same arrays rx_mesh carries) into
  * nParts parts of equal size (2 % tolerance) with a small edge cut: recursive inertial bisection on coord[nPoint][2] +
  * boundary refinement (refinePasses sweeps; 0 = geometric split only).  owner[nPoint] receives the part of every point,
- * *edgeCut (may be NULL) the number of cut edges.  Stands where the reference calls ParMETIS_V3_PartKway
+ * *edgeCut (may be NULL) the number of cut edges.  When librx_metis.so is present the partition is METIS's (coord and refinePasses unused).
+ * Stands where the reference calls ParMETIS_V3_PartKway
  * (Common/src/geometry_structure.cpp:11524 via SetColorGrid_Parallel, driver_structure.cpp:126).
  * rx_rcm_order: reverse Cuthill-McKee numbering of the first nPointDomain (owned) points, halo points stay last;
  * newToOld[nPoint].  Role of CPhysicalGeometry::SetRCM_Ordering (geometry_structure.cpp:9200, called driver_structure.cpp:560). */
 int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const double* coord, int nParts,
                       int refinePasses, int64_t* owner, int64_t* edgeCut);
+int rx_partition_backend(void);   /* 1: rx_partition_kway calls METIS_PartGraphKway of librx_metis.so (METIS 5 as vendored in the reference tree, built by
+                                    csrc/host/build_metis.sh; found next to the library or through RX_METIS_LIB); 0: the library's own partitioner
+                                    (also forced by RX_PARTITIONER=own) */
 int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld);
 
 /* SU2 native ASCII restart files straight from / into the device-resident state (csrc/rx_restart.cuh).

@@ -182,3 +182,29 @@ def test_halo_exchange_over_graph_partition_gloo():
         p.join(180)
         assert p.exitcode == 0
     assert list(out) == [1] * world
+
+
+def test_metis_backend_when_built():
+    """rx_partition_kway with the METIS backend (librx_metis.so: METIS 5 as vendored in the reference tree, csrc/host/build_metis.sh)
+    against the library's own partitioner on the same graph: valid owners, balance within METIS's 3 %, and a cut no larger than the
+    own partitioner's (the reference partitions with ParMETIS_V3_PartKway, geometry_structure.cpp:11524)."""
+    import os
+    pk = load_package()
+    L = pk.load_library()
+    old = os.environ.pop("RX_PARTITIONER", None)
+    try:
+        if L.rx_partition_backend() != 1:
+            pytest.skip("librx_metis.so is not in this snapshot (built from /root/reference/externals/metis where the reference tree is present)")
+        g = pk.channel_mesh(121, 61)
+        for k in (2, 5, 8):
+            om, cm = pk.graph_owner(g, k)
+            os.environ["RX_PARTITIONER"] = "own"
+            oo, co = pk.graph_owner(g, k)
+            os.environ.pop("RX_PARTITIONER")
+            sizes = np.bincount(om, minlength=k)
+            assert om.min() == 0 and om.max() == k - 1 and sizes.min() > 0
+            assert sizes.max() <= 1.031 * g["nPoint"] / k + 1
+            assert cm <= 1.05 * co + 4, (k, cm, co)   # a straight cut of a rectangle (k = 2) is already optimal; METIS wins as k grows
+    finally:
+        if old is not None:
+            os.environ["RX_PARTITIONER"] = old
