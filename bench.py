@@ -487,6 +487,45 @@ def measure_source(pk, chem, rank, world, local, dev, n, K):
     return ms, ok
 
 
+def bench_dropin(a, K, W):
+    """The real cost of the C++ drop-in: the reference's own driver / integration classes with the flow solver
+    replaced by CReactiveNSSolverGPU (oracle/_ref/ref_harness_gpu) on a 251 001-point channel, at SU2_RX_MIRROR=0 (conserved variables and
+    norms mirrored into node[] after every update) and 1 (+ primitives, gradients, transport after every Preprocessing), next to the
+    compiled CPU reference on the same mesh.  Times are the harness's flow-iteration wall times (HARNESS_TIME)."""
+    d = os.path.join(ROOT, "oracle", "_ref", "cases", "dropin_250k")
+    hg = os.path.join(ROOT, "oracle", "_ref", "ref_harness_gpu")
+    if not (os.path.exists(hg) and os.path.exists(os.path.join(d, "case.cfg"))):
+        print(json.dumps({"metric": "dropin_e2e", "unavailable": "oracle/_ref/ref_harness_gpu or the dropin_250k case is not in this snapshot"}))
+        return
+
+    def run(binary, nit, env):
+        t0 = time.perf_counter()
+        out = subprocess.run([binary, "case.cfg", str(nit), "dump_dropin", str(10 ** 9), "11"], cwd=d, env=dict(os.environ, **env),
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        shutil.rmtree(os.path.join(d, "dump_dropin"), ignore_errors=True)
+        if out.returncode != 0:
+            raise RuntimeError(out.stdout[-2000:])
+        t = [float(m.group(1)) for m in re.finditer(r"HARNESS_TIME it \d+ flow_seconds ([0-9.eE+-]+)", out.stdout)]
+        return t, time.perf_counter() - t0
+
+    nit = W + K
+    res = {}
+    for mirror in ("0", "1"):
+        t, wall = run(hg, nit, {"SU2_RX_BACKEND": "cuda", "SU2_RX_MIRROR": mirror})
+        res["mirror%s" % mirror] = {"ms_per_iteration": 1e3 * float(np.mean(t[W:])), "iterations": K, "process_wall_s": wall}
+    tc, wallc = run(HARNESS, 2, {})
+    meta_pts, meta_edges = 251001, 751000
+    units = len(RK_ALPHA) * (meta_edges + meta_pts)
+    cpu_ms = 1e3 * float(tc[-1])
+    line = {"metric": "dropin_e2e", "unit": "ms per flow iteration", "higher_is_better": False, "n_gpus": 1, "steps": K, "warmup": W, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "the reference's CFluidDriver / CMultiGridIntegration on CReactiveNSSolverGPU (ref_harness_gpu), laminar reactive NS, 3-stage RK, 501 x 501 channel",
+                       "points": meta_pts, "edges": meta_edges},
+            "dropin": res, "cpu_reference": {"ms_per_iteration": cpu_ms, "cores": 1, "iterations_timed": 1},
+            "updates_per_s": {k: units / (v["ms_per_iteration"] * 1e-3) for k, v in res.items()},
+            "speedup_vs_one_core": {k: cpu_ms / v["ms_per_iteration"] for k, v in res.items()}}
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -497,7 +536,7 @@ def main():
     ap.add_argument("--ny", type=int, default=1415)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra-workloads", action="store_true", help="skip the short RANS and source-term measurements embedded in the default line")
-    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source", "turbpost"],
+    ap.add_argument("--workload", default="laminar", choices=["laminar", "rans", "source", "turbpost", "dropin"],
                     help="laminar = BASELINE.json configs[1] (the bench line); rans = the RANS + PaSR variant of the same mesh (configs[2]/[4] per-GPU share); "
                          "source = isolated Arrhenius + PaSR source term over --points independent points per GPU (configs[3]); "
                          "turbpost = SST Postprocessing on the device (first slice of SURVEY.md 8(f) rank 1)")
@@ -514,6 +553,10 @@ def main():
           True: "reactive RANS (9 species, 2 reactions, SST), synthetic triangulated 2-D channel, explicit 3-stage RK, AUSM + Stefan-Maxwell viscous + SST closure + Arrhenius/PaSR source, WLS gradients"}
     workload = WL[rans]
 
+    if a.workload == "dropin":
+        if rank == 0:
+            bench_dropin(a, K, W)
+        return
     if a.impl == "reference":
         if rank != 0:
             return

@@ -359,7 +359,7 @@ void CReactiveNSSolverGPU::BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*,
 
 // U = clip(U_old - alpha * Res * dt / Vol), residual norms; mirrors what output, restart and the host-side
 // CSolver::Set_OldSolution read (solver_direct_reactive.cpp:2414-2493, solver_structure.cpp:172-260)
-void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha) {
+void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha, bool lastStage) {
   std::vector<double> rms(nVar);
   Check(rx_update_explicit(ctx, alpha, rms.data()), "rx_update_explicit");
   if (commReady) {   // Set_MPI_Solution and the global norms, as ExplicitEuler/RK_Iteration do (:2442-2448)
@@ -376,13 +376,19 @@ void CReactiveNSSolverGPU::Update(CGeometry* geometry, double alpha) {
     if (rmax[v] > 0.0)
       AddRes_Max(v, rmax[v], geometry->node[pmax[v]]->GetGlobalIndex(), geometry->node[pmax[v]]->GetCoord());
   }
-  Check(rx_get_solution(ctx, bufU.data()), "rx_get_solution");
-  for (unsigned long p = 0; p < nPoint; ++p)
-    for (unsigned short v = 0; v < nVar; ++v) node[p]->SetSolution(v, bufU[p * nVar + v]);
+  // node[]->Solution is what output, restart and monitors read — after the iteration; the intermediate RK stages are read by nobody on
+  // the host (mirror level 2 keeps them for the stage-by-stage parity dumps)
+  if (lastStage || mirror >= 2) {
+    Check(rx_get_solution(ctx, bufU.data()), "rx_get_solution");
+    for (unsigned long p = 0; p < nPoint; ++p) {
+      su2double* sol = node[p]->GetSolution();
+      for (unsigned short v = 0; v < nVar; ++v) sol[v] = bufU[p * nVar + v];
+    }
+  }
 }
-void CReactiveNSSolverGPU::ExplicitEuler_Iteration(CGeometry* geometry, CSolver**, CConfig*) { Update(geometry, 1.0); }
+void CReactiveNSSolverGPU::ExplicitEuler_Iteration(CGeometry* geometry, CSolver**, CConfig*) { Update(geometry, 1.0, true); }
 void CReactiveNSSolverGPU::ExplicitRK_Iteration(CGeometry* geometry, CSolver**, CConfig* config, unsigned short iRKStep) {
-  Update(geometry, config->Get_Alpha_RKStep(iRKStep));
+  Update(geometry, config->Get_Alpha_RKStep(iRKStep), iRKStep + 1 == config->GetnRKStep());
 }
 
 void CReactiveNSSolverGPU::WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename) {

@@ -78,7 +78,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void MirrorLimiter();
   void MirrorTimeStep();
   void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
-  void Update(CGeometry* geometry, double alpha);
+  void Update(CGeometry* geometry, double alpha, bool lastStage);
 
 #ifdef HAVE_MPI
   void InitComm(CGeometry* geometry, CConfig* config);   // neighbour lists from the SEND_RECEIVE marker pairs, NCCL id by MPI_Bcast

@@ -289,6 +289,16 @@ def prepare_bench_case(nx=151, ny=151):
     print("prepared %s" % d)
 
 
+def prepare_dropin_case(nx=501, ny=501):
+    """Case directory for `bench.py --workload dropin`: the bench cfg on a 251 001-point channel — the real cost of the C++ drop-in
+    (ref_harness_gpu at SU2_RX_MIRROR=0 / 1) next to the CPU reference on the same mesh."""
+    d = prepare_case_dir("dropin_250k", nx=nx, ny=ny, stretch=1.0)
+    derive_cfg(os.path.join(SHIPPED, "my_combustion_first_chem_PaSR.cfg"), os.path.join(d, "case.cfg"),
+               dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="100000", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                    TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.1"))
+    print("prepared %s" % d)
+
+
 if __name__ == "__main__":
     if sys.argv[1:] == ["bench_ref"]:
         prepare_bench_case()
@@ -301,6 +311,7 @@ if __name__ == "__main__":
         for base, repl, _e, _n, _s, _c in LONG.values():
             derive_cfg(os.path.join(CASES, base, "case.cfg"), os.path.join(CASES, base, "case_long.cfg"), repl)
         prepare_bench_case()
+        prepare_dropin_case()
         sys.exit(0)
     names = sys.argv[1:] or list(SPECS)
     for n in names:
