@@ -1301,6 +1301,71 @@ extern "C" int rx_libm_eval(int which, int64_t n, const double* x, const double*
   return rc;
 }
 
+// diagnostic hook: the two device forms of Eigen::ColPivHouseholderQR<MatrixXd>::solve (serial colpiv_qr_solve<9, 2, 1>, used at boundary
+// vertices, and the two-lanes-per-system pair_colpiv_qr_solve<9> of the viscous edge kernel) over host arrays of 9 x 9 systems
+namespace rx {
+__global__ void __launch_bounds__(VP_BS) k_qr_eval(long long n, const double* __restrict__ A, const double* __restrict__ b,
+                                                   double* __restrict__ xs, double* __restrict__ xp) {
+  constexpr int NS = 9;
+  extern __shared__ double vp_sm[];
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  PairLane L;
+  L.l = (int)(threadIdx.x & 1);
+  L.odd = (int)(threadIdx.x & 31) | 1;
+  const int l = L.l;
+  long long e = t >> 1;
+  const bool keep = e < n;
+  if (!keep) e = n - 1;   // whole warps take part in the pair routine's warp synchronisations
+  double* const smPair = vp_sm + threadIdx.x - l;
+  const PairMat<NS> Mt{smPair};
+  const double* Ae = A + e * NS * NS;
+  const double* be = b + e * 2 * NS;
+  for (int i = l; i < NS; i += 2) {
+    for (int j = 0; j < NS; ++j) Mt(i, j) = Ae[j * NS + i];
+    for (int dd = 0; dd < 2; ++dd) Mt(i, NS + dd) = be[dd * NS + i];
+  }
+  double MG[2][5];
+  pair_colpiv_qr_solve<NS>(L, smPair, MG);
+  if (keep) {
+    for (int dd = 0; dd < 2; ++dd) {
+      for (int q = 0; q < 4; ++q) xp[(e * 2 + dd) * NS + 2 * q + l] = MG[dd][q];
+      if (l) xp[(e * 2 + dd) * NS + 8] = MG[dd][4];
+    }
+    if (l == 0) {
+      double Al[NS * NS], bl[2][NS], xl[2][NS];
+      for (int k = 0; k < NS * NS; ++k) Al[k] = Ae[k];
+      for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) bl[dd][i] = be[dd * NS + i];
+      colpiv_qr_solve<NS, 2, 1>(Al, bl, xl);
+      for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) xs[(e * 2 + dd) * NS + i] = xl[dd][i];
+    }
+  }
+}
+}  // namespace rx
+extern "C" int rx_qr_eval(int64_t n, const double* A, const double* b, double* xSerial, double* xPair, int device) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_error = "rx_qr_eval: no CUDA device (no CPU path)"; return RX_ERR_NO_DEVICE; }
+  if (n < 0 || !A || !b || !xSerial || !xPair) { g_create_error = "rx_qr_eval: bad arguments"; return RX_ERR_ARG; }
+  if (n == 0) return RX_OK;
+  if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "rx_qr_eval: cudaSetDevice failed"; return RX_ERR_CUDA; }
+  double *dA = nullptr, *db = nullptr, *dxs = nullptr, *dxp = nullptr;
+  int rc = RX_OK;
+  const size_t nA = (size_t)n * 81 * sizeof(double), nb = (size_t)n * 18 * sizeof(double);
+  if (cudaMalloc(&dA, nA) != cudaSuccess || cudaMalloc(&db, nb) != cudaSuccess || cudaMalloc(&dxs, nb) != cudaSuccess || cudaMalloc(&dxp, nb) != cudaSuccess) rc = RX_ERR_CUDA;
+  if (rc == RX_OK && (cudaMemcpy(dA, A, nA, cudaMemcpyHostToDevice) != cudaSuccess || cudaMemcpy(db, b, nb, cudaMemcpyHostToDevice) != cudaSuccess)) rc = RX_ERR_CUDA;
+  if (rc == RX_OK) {
+    const size_t smem = (size_t)rx::VP_SMW_RANS * rx::VP_BS * sizeof(double);
+    if (cudaFuncSetAttribute(rx::k_qr_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) rc = RX_ERR_CUDA;
+    if (rc == RX_OK) {
+      rx::k_qr_eval<<<(unsigned)((2 * n + rx::VP_BS - 1) / rx::VP_BS), rx::VP_BS, smem>>>((long long)n, dA, db, dxs, dxp);
+      if (cudaMemcpy(xSerial, dxs, nb, cudaMemcpyDeviceToHost) != cudaSuccess || cudaMemcpy(xPair, dxp, nb, cudaMemcpyDeviceToHost) != cudaSuccess ||
+          cudaGetLastError() != cudaSuccess) rc = RX_ERR_CUDA;
+    }
+  }
+  if (rc != RX_OK) g_create_error = "rx_qr_eval: allocation, copy or kernel failed";
+  cudaFree(dA); cudaFree(db); cudaFree(dxs); cudaFree(dxp);
+  return rc;
+}
+
 // SU2 native restart files from / into the device-resident state (COutput::SetRestart, Load_Restart)
 #include "rx_restart.cuh"
 

@@ -125,8 +125,67 @@ RX_HD int bicgstab(MatF A, const double* rhs, double* r0, double* x) {
   return it;
 }
 
-// Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) for `nrhs` right-hand sides (externals/Eigen/src/QR/ColPivHouseholderQR.h,
-// Householder/Householder.h).  Same pivot rule, rank threshold and norm down-dating; natural summation order.
+// ---- the summation orders of Eigen::ColPivHouseholderQR<MatrixXd>::solve on a 9 x 9 matrix (Eigen 3.3.7, SSE2, no FMA) ----------
+// glibc's malloc hands Eigen 16-byte aligned storage, so entry (i, j) of the 9 x 9 factor is packet-aligned exactly when i + j is even;
+// the orders below follow from that one fact and are checked bit for bit against the real headers (oracle/eigen_qr_check.cpp).
+//  * squaredNorm / dot of a coefficient-wise expression: eig_redux<> above with packets from entry 0 (Core/Redux.h:208-256;
+//    first_default_aligned() of an expression without direct access is 0);
+//  * one entry of essential^T * bottom in applyHouseholderOnTheLeft (Householder/Householder.h:122): the row-major matrix-vector
+//    kernel (Core/products/GeneralMatrixVector.h:363-612) with the essential vector as right-hand side; that vector starts one
+//    entry below the diagonal (entry 10k + 1 of the storage: odd), so alignedStart = 1: one scalar product, packets {1,2},{3,4},...
+//    accumulated from zero, reduced, then the scalar tail.  (The kernel's leading 0 + x additions are dropped: they matter to the
+//    sign of a zero only.)
+template <int M>
+RX_HD double eig_gemv_row(const double* t) {
+  constexpr int AS = 1 + ((M - 1) & ~1);
+  double r = t[0];
+  if (AS > 1) {
+    double p0 = t[1], p1 = t[2];
+#pragma unroll
+    for (int j = 3; j < AS; j += 2) { p0 += t[j]; p1 += t[j + 1]; }
+    r += p0 + p1;
+  }
+#pragma unroll
+  for (int j = AS; j < M; ++j) r += t[j];
+  return r;
+}
+// run-time lengths (serial factorisation below); `as` = entries before the first aligned one
+template <class F>
+RX_HD double eig_redux_n(int n, F term) {
+  if (n == 0) return 0.0;
+  const int n2 = n & ~1, n4 = n & ~3;
+  if (n2 == 0) return term(0);
+  double a0 = term(0), a1 = term(1);
+  if (n2 > 2) {
+    double b0 = term(2), b1 = term(3);
+    for (int i = 4; i < n4; i += 4) { a0 += term(i); a1 += term(i + 1); b0 += term(i + 2); b1 += term(i + 3); }
+    a0 += b0; a1 += b1;
+    if (n2 > n4) { a0 += term(n4); a1 += term(n4 + 1); }
+  }
+  double r = a0 + a1;
+  for (int i = n2; i < n; ++i) r += term(i);
+  return r;
+}
+template <class F>
+RX_HD double eig_gemv_row_n(int m, int as, F term) {
+  if (as > m) as = m;
+  const int aSize = as + ((m - as) & ~1);
+  double t = 0.0;
+  for (int j = 0; j < as; ++j) t += term(j);
+  if (aSize > as) {
+    double p0 = 0.0, p1 = 0.0;
+    for (int j = as; j < aSize; j += 2) { p0 += term(j); p1 += term(j + 1); }
+    t += p0 + p1;
+  }
+  for (int j = aSize; j < m; ++j) t += term(j);
+  return t;
+}
+
+// Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) for `nrhs` right-hand sides (externals/Eigen/src/QR/ColPivHouseholderQR.h:480-609,
+// Householder/Householder.h:65-131, Core/products/TriangularSolverVector.h: back substitution in panels of 8 columns, the rows above a
+// panel updated by the column-major matrix-vector kernel — for the single row above the panel of a full-rank 9 x 9 system, its
+// columns in ascending order).  Same pivot rule, rank threshold, norm down-dating and, sum by sum, Eigen's own order: the result
+// equals the reference's bit for bit.
 // A is N x N column-major in caller-provided scratch (destroyed); b/x are [nrhs][N].
 // Strided view of one column of a thread-private matrix: element i lives at base[i*S] (S = 1 for local memory,
 // S = block size for the shared-memory layout in which consecutive threads own consecutive 8-byte words).
@@ -138,13 +197,13 @@ struct ColView {
 };
 template <int N, int NRHS, int S>
 RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
+  static_assert(N <= 9, "one row at most above the 8-column panel of the back substitution");
   double hC[N], nU[N], nD[N];
   int trans[N];
   auto col = [&](int j) { return ColView<S>{A + j * N * S}; };
   for (int k = 0; k < N; ++k) {
-    double s = 0.0;
-    for (int i = 0; i < N; ++i) s += col(k)[i] * col(k)[i];
-    nD[k] = nU[k] = sqrt(s);
+    const ColView<S> a = col(k);
+    nD[k] = nU[k] = sqrt(eig_redux_n(N, [&](int i) { return a[i] * a[i]; }));
   }
   const double eps = 2.220446049250313e-16;
   double mx = nU[0];
@@ -165,8 +224,7 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
     }
     const ColView<S> v = col(k) + k;
     const int m = N - k;
-    double tailSq = 0.0;
-    for (int i = 1; i < m; ++i) tailSq += v[i] * v[i];
+    const double tailSq = eig_redux_n(m - 1, [&](int i) { return v[1 + i] * v[1 + i]; });
     const double c0 = v[0];
     double beta, tau;
     if (tailSq <= 2.2250738585072014e-308) {
@@ -185,8 +243,7 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
     } else if (tau != 0.0) {
       for (int j = k + 1; j < N; ++j) {
         const ColView<S> w = col(j) + k;
-        double t = 0.0;
-        for (int i = 1; i < m; ++i) t += v[i] * w[i];
+        double t = eig_gemv_row_n(m - 1, (k * (N + 1) + 1) & 1, [&](int i) { return w[1 + i] * v[1 + i]; });
         t += w[0];
         w[0] -= tau * t;
         for (int i = 1; i < m; ++i) w[i] -= tau * v[i] * t;
@@ -200,9 +257,8 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
         const double q = nU[j] / nD[j];
         const double temp2 = temp * (q * q);
         if (temp2 <= downdate) {
-          double s = 0.0;
-          for (int i = k + 1; i < N; ++i) s += col(j)[i] * col(j)[i];
-          nD[j] = sqrt(s); nU[j] = nD[j];
+          const ColView<S> a = col(j) + (k + 1);
+          nD[j] = sqrt(eig_redux_n(N - k - 1, [&](int i) { return a[i] * a[i]; })); nU[j] = nD[j];
         } else nU[j] *= sqrt(temp);
       }
     }
@@ -221,16 +277,21 @@ RX_HD void colpiv_qr_solve(double* A, const double (*b)[N], double (*xout)[N]) {
       double* w = c + k;
       if (m == 1) w[0] *= (1.0 - tau);
       else if (tau != 0.0) {
-        double t = 0.0;
-        for (int i = 1; i < m; ++i) t += v[i] * w[i];
+        double t = eig_redux_n(m - 1, [&](int i) { return v[1 + i] * w[1 + i]; });   // 1 x m by m x 1: an inner product
         t += w[0];
         w[0] -= tau * t;
         for (int i = 1; i < m; ++i) w[i] -= tau * v[i] * t;
       }
     }
-    for (int i = nonzero - 1; i >= 0; --i) {
-      c[i] = c[i] / col(i)[i];
-      for (int r = 0; r < i; ++r) c[r] -= c[i] * col(i)[r];
+    for (int pi = nonzero; pi > 0; pi -= 8) {
+      const int pw = pi < 8 ? pi : 8, start = pi - pw;
+      for (int kk = 0; kk < pw; ++kk) {
+        const int i = pi - kk - 1;
+        c[i] = c[i] / col(i)[i];
+        for (int r = start; r < i; ++r) c[r] -= c[i] * col(i)[r];
+      }
+      for (int r = 0; r < start; ++r)
+        for (int j = start; j < pi; ++j) c[r] -= col(j)[r] * c[j];
     }
     for (int i = 0; i < nonzero; ++i) xout[q][perm[i]] = c[i];
     for (int i = nonzero; i < N; ++i) xout[q][perm[i]] = 0.0;

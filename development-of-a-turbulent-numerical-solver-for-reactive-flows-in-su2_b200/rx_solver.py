@@ -104,7 +104,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read",
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -179,6 +179,18 @@ def libm_eval(which, x, y=None, device=0):
     if rc != 0:
         raise RxError("rx_libm_eval failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
     return out
+
+
+def qr_eval(A, b, device=0):
+    """Eigen's pivoted-QR solve of n 9 x 9 systems on the device (rx_qr_eval): A [n, 81] column-major, b [n, 2, 9] -> (xSerial, xPair)."""
+    L = load_library()
+    A = _c(A); b = _c(b)
+    n = A.size // 81
+    xs = np.empty_like(b); xp = np.empty_like(b)
+    rc = L.rx_qr_eval(C.c_int64(n), _d(A), _d(b), _d(xs), _d(xp), int(device))
+    if rc != 0:
+        raise RxError("rx_qr_eval failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
+    return xs, xp
 
 
 def comm_unique_id():

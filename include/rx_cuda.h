@@ -215,6 +215,13 @@ int rx_fp64_peak(rx_ctx*, double* tflops);
  * 835-920; solver_direct_reactive.cpp:3901-3935).  tests/test_gpu_libm.py compares them bit for bit with the host's libm. */
 int rx_libm_eval(int which, int64_t n, const double* x, const double* y, double* out, int device);
 
+/* diagnostic hook: x = Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) for n independent 9 x 9 systems (A[n][81] column-major, two
+ * right-hand sides b[n][2][9]) — the call of the SST closure, numerics_direct_reactive.cpp:743 — by both device forms: the serial routine
+ * (boundary vertices) into xSerial and the two-lanes-per-system routine of the viscous edge kernel into xPair.  Both follow Eigen 3.3.7's
+ * own summation orders (externals/Eigen/src/QR/ColPivHouseholderQR.h:480-609); tests/test_gpu_qr.py compares them bit for bit with the
+ * oracle's restatement, which oracle/eigen_qr_check.cpp pins against the real Eigen headers. */
+int rx_qr_eval(int64_t n, const double* A, const double* b, double* xSerial, double* xPair, int device);
+
 /* partitioning (host-side graph tools, no device work; csrc/host/rx_partition.cpp).
  * rx_partition_kway: k-way partition of the point adjacency graph (CSR nbPtr/nbPoint, the same arrays rx_mesh carries) into
  * nParts parts of equal size (2 % tolerance) with a small edge cut: recursive inertial bisection on coord[nPoint][2] +

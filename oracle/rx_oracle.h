@@ -93,6 +93,8 @@ void rxo_explicit_update(rxo_ctx*, double rkAlpha, double* resRms);
 void rxo_source_points(const rxo_chem*, int rans, double cMu, double pasrLb, int64_t n, const double* T, const double* rho,
                        const double* Y /*[n][Ns]*/, const double* omegaTurb, const double* vol, double* res /*[n][Ns]*/);
 int rxo_bicgstab(int n, const double* A /*col-major*/, const double* rhs, double* x, int* iters);
+/* Eigen::ColPivHouseholderQR<MatrixXd>(A).solve(b) in Eigen 3.3.7's own summation order (n <= 9) */
+void rxo_colpiv_qr_solve(int n, const double* A /*col-major*/, const double* b, double* x);
 double rxo_spline(const rxo_chem*, int prop, int species, double T);
 
 #ifdef __cplusplus
