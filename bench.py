@@ -371,19 +371,27 @@ def measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W,
     Uh.numpy()[:] = U0
     solver.SetSolutionPtr(Uh.data_ptr()); solver.SetTemperature(T0); solver.SetTurbulence(turb)
 
-    # RANS on one partition: the SST transport step runs on the device after every flow iteration (rx_turb_iterate: residuals, boundary
-    # conditions, FGMRES + LU-SGS, update, Postprocessing), as SU2's iteration does; partitioned runs keep the turbulence fields frozen
-    # (the turbulence step is single-partition)
-    turb_dev = bool(rans) and world == 1
+    # RANS: the SST transport step runs on the device after every flow iteration (rx_turb_iterate: residuals, boundary conditions,
+    # FGMRES + LU-SGS, update, Postprocessing), as SU2's iteration does — on a partition too: the step exchanges its gradients, LU-SGS
+    # and Krylov vectors and (k, omega) over the library's communicator and all-reduces its dot products (the reference's MPI points)
+    turb_dev = bool(rans)
     lin_its = []
     if turb_dev:
-        solver.ComputeWall_Distance()
-        solver.TurbPostprocessing(np.ascontiguousarray(turb[:, 1:3]))
+        if world == 1:
+            solver.ComputeWall_Distance()
+            solver.TurbPostprocessing(np.ascontiguousarray(turb[:, 1:3]))
+        else:   # a partition sees only its own wall nodes: the channel's walls are the lines y = y_min, y_max of the WHOLE mesh, each
+                # point has a wall node straight below and above it, so the nearest-wall-node distance is the vertical one
+            xy = np.asarray(mesh["coord"], dtype=np.float64)
+            y0, y1 = plan["bbox"][2], plan["bbox"][3]
+            solver.SetWall_Distance(np.ascontiguousarray(np.minimum(xy[:, 1] - y0, y1 - xy[:, 1])))
+            par.distributed_turb_postprocess(solver, None, np.ascontiguousarray(turb[:, 1:3]))
 
     def step(it, want_rms=False):
         if world > 1:
-            return par.distributed_iterate(solver, ex, it, RK_ALPHA, last_rms=want_rms)
-        r = solver.Iterate(it, RK_ALPHA, want_rms=want_rms)
+            r = par.distributed_iterate(solver, ex, it, RK_ALPHA, last_rms=want_rms)
+        else:
+            r = solver.Iterate(it, RK_ALPHA, want_rms=want_rms)
         if turb_dev:
             lin_its.append(solver.TurbIterate(0.135, 2.0e3)[1])
         return r
@@ -419,7 +427,7 @@ def measure_flow(pk, par, chem, mesh, plan, rans, rank, world, local, dev, K, W,
         raise SystemExit("bench.py: non-finite residual after the timed region")
     out["rms_rho"] = float(rms[0])
     out["turbulence"] = ("SST transport step on the device after every flow iteration (rx_turb_iterate; FGMRES iterations per step: %s), inside the timed region" % sorted(set(lin_its))) if turb_dev else \
-                        ("SST fields (mu_t, k, omega, grad k) are inputs, frozen during the timed iterations (the device turbulence step is single-partition)" if rans else None)
+                        None
     if solver.opts["viscous"]:
         _o, key = solver.EdgeOrder()         # BiCGSTAB iterations of every edge's Stefan-Maxwell solve in the timed state: the work is fixed
         hist = np.bincount(key.astype(np.int64) % 19, minlength=19)

@@ -70,6 +70,8 @@ extern "C" {
 static int halo_exchange_fork(rx_ctx* c, int what);
 static int comm_join(rx_ctx* c);
 static int ensure_output(rx_ctx* c);
+static int halo_exchange_field(rx_ctx* c, double* field, int nv, bool vortStrain, cudaStream_t s);
+static int comm_allreduce_sum(rx_ctx* c, double* dev, int n);
 }
 
 #define RX_CK(call)                                                                                   \
@@ -476,6 +478,10 @@ int rx_turb_postprocess(rx_ctx* c, const double* kOmega, double sigmaK, int stag
     }
   }
   c->sigmaK = sigmaK;
+  if (stage == 0 && c->comm) {   // Set_MPI_Solution_Gradient (solver_direct_turbulent.cpp:227) between the two halves
+    const int rc = halo_exchange_field(c, c->tpost + (size_t)TP_GK * d.np, 4, false, c->stream);
+    if (rc) return rc;
+  }
   if (stage != 1) { k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(d, c->tpost, sigmaK); c->launches++; }
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -515,14 +521,15 @@ static int turb_step_setup(rx_ctx* c, int m) {
         const int p = pts[t];
         for (int k = c->hIncPtr[p]; k < c->hIncPtr[p + 1]; ++k) {
           const int q = c->hNbOfSlot[k];
-          if (fwd ? q < p : q > p) { col.push_back(pos[q]); slot.push_back(k); }
+          if (fwd ? q < p : q > p) { col.push_back(q < n ? pos[q] : q); slot.push_back(k); }   // a halo column: its x* sits at position q of the backward list's x
         }
         start[t + 1] = (int)col.size();
       }
       sl.nEnt = (int)col.size();
       if (col.empty()) { col.push_back(0); slot.push_back(0); }
       sl.nLvl = nl; sl.lvlPtr = dupload(c, ptr); sl.perm = dupload(c, pts); sl.start = dupload(c, start); sl.colL = dupload(c, col); sl.slot = dupload(c, slot);
-      sd.coefL = dalloc<double>(c, 2 * (size_t)std::max(sl.nEnt, 1)); sd.dgL = dalloc<double>(c, 2 * (size_t)n); sd.bL = dalloc<double>(c, 2 * (size_t)n); sd.xL = dalloc<double>(c, 2 * (size_t)n);
+      sl.nX = (int)(fwd ? n : d.nPoint);
+      sd.coefL = dalloc<double>(c, 2 * (size_t)std::max(sl.nEnt, 1)); sd.dgL = dalloc<double>(c, 2 * (size_t)n); sd.bL = dalloc<double>(c, 2 * (size_t)n); sd.xL = dalloc<double>(c, 2 * (size_t)sl.nX);
       if (fwd) c->posF = dupload(c, pos);
     };
     build(true, c->swF, c->sdF);
@@ -542,6 +549,7 @@ static int turb_dot(rx_ctx* c, const double* a, const double* b, double* out) {
   k_turb_dot<<<c->tDotBlocks, 256, 0, c->stream>>>(d.nPointDomain, d.np, a, b, c->tPartial);
   k_turb_sum<<<1, 256, 0, c->stream>>>(c->tPartial, c->tDotBlocks, 1, 0, c->tScal);
   c->launches += 2;
+  if (c->comm) { const int rc = comm_allreduce_sum(c, c->tScal, 1); if (rc) return rc; }
   RX_CK(cudaMemcpyAsync(out, c->tScal, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   RX_CK(cudaStreamSynchronize(c->stream));
   return RX_OK;
@@ -566,7 +574,7 @@ int rx_turb_get_step(rx_ctx* c, double* res2, double* dx2) {
 int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* linIters) {
   if (!c->tpost) { c->err = "rx_turb_iterate: not a RANS context"; return RX_ERR_ARG; }
   if (!c->haveWallDist) { c->err = "rx_turb_iterate: the wall distance has not been set (rx_set_wall_distance / rx_compute_wall_distance)"; return RX_ERR_ARG; }
-  if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_turb_iterate: single partition only (the LU-SGS sweeps across partitions are not built)"; return RX_ERR_UNSUPPORTED; }
+  if (c->d.nPoint != c->d.nPointDomain && !c->comm) { c->err = "rx_turb_iterate: a partition needs the in-library communicator (rx_comm_init): the step exchanges its Krylov and LU-SGS vectors"; return RX_ERR_UNSUPPORTED; }
   if (!to || to->linIter < 1 || to->linIter > 64) { c->err = "rx_turb_iterate: bad options"; return RX_ERR_ARG; }
   const int m = to->linIter;
   int rc = ensure_output(c);
@@ -589,6 +597,8 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
       if (mk.nVertex) { k_turb_gradient_gg_boundary<<<nblk(mk.nVertex, 64), 64, 0, s>>>(d, mk, tp); c->launches++; }
     k_turb_gradient_gg_finish<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, tp); c->launches++;
   }
+  const bool par = c->comm != nullptr;   // partition of a multi-GPU job: the exchanges of the reference's MPI build, over NCCL on the context's stream
+  if (par && (rc = halo_exchange_field(c, tp + (size_t)TP_GK * d.np, 4, false, s))) return rc;
   RX_CK(cudaMemcpyAsync(w.old, tp, 2 * (size_t)d.np * sizeof(double), cudaMemcpyDeviceToDevice, s));
   // Space_Integration: rows, then the boundary conditions (weak ones first, walls last: integration_structure.cpp:89-190)
   k_turb_rows<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
@@ -603,23 +613,36 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   k_turb_sum<<<1, 256, 0, s>>>(c->tPartial, c->tBlocks, 2, 0, c->tScal + 2);
   k_turb_sum<<<1, 256, 0, s>>>(c->tPartial, c->tBlocks, 2, 1, c->tScal + 2);
   c->launches += 3;
-  double ss[2];
-  RX_CK(cudaMemcpyAsync(ss, c->tScal + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  double ss[3];
+  if (par) {   // sums of squares and the owned-point count over the ranks (SetResidual_RMS with MPI, solver_structure.cpp:188-260)
+    const double nOwn = (double)n;
+    RX_CK(cudaMemcpyAsync(c->tScal + 4, &nOwn, sizeof(double), cudaMemcpyHostToDevice, s));
+    if ((rc = comm_allreduce_sum(c, c->tScal + 2, 3))) return rc;
+  }
+  RX_CK(cudaMemcpyAsync(ss, c->tScal + 2, 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
   RX_CK(cudaStreamSynchronize(s));
-  if (resRms2) for (int v = 0; v < 2; ++v) resRms2[v] = std::max(EPS * EPS, std::sqrt(ss[v] / (double)d.nPoint));   // SetResidual_RMS
+  if (resRms2) for (int v = 0; v < 2; ++v) resRms2[v] = std::max(EPS * EPS, std::sqrt(ss[v] / (par ? ss[2] : (double)d.nPoint)));   // SetResidual_RMS
   // FGMRES (linear_solvers_structure.cpp:309-445), x0 = 0: w0 = (A x0 - b) / (-beta) = b / beta
   // level-order copies of the assembled rows for the sweeps (once per step), then per application: permute in, forward sweep,
   // re-order to the backward sweep's level order, backward sweep, permute out
   k_turb_sweep_coef<<<nblk(std::max<long long>(c->swF.nEnt, n), 256), 256, 0, s>>>(c->swF, c->sdF, w, n, d.np);
   k_turb_sweep_coef<<<nblk(std::max<long long>(c->swB.nEnt, n), 256), 256, 0, s>>>(c->swB, c->sdB, w, n, d.np);
   c->launches += 2;
-  auto precond = [&](const double* in, double* out) {
+  auto precond = [&](const double* in, double* out) -> int {
     k_turb_perm_in<<<nblk(n, 256), 256, 0, s>>>(c->swF.perm, n, d.np, in, c->sdF.bL);
     k_turb_sweep<false><<<2, 1024, 0, s>>>(c->swF, c->sdF, n);
-    k_turb_perm_ab<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, c->posF, n, c->sdF.xL, c->sdB.xL);
+    if (par && d.nPoint > n) {   // x* of the neighbours' points -> the halo tail of the backward list (SendReceive_Solution between the sweeps, :1689)
+      k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swF.perm, n, n, d.np, c->sdF.xL, out);
+      const int e = halo_exchange_field(c, out, 2, false, s);
+      if (e) return e;
+      k_turb_halo_in<<<nblk(d.nPoint - n, 256), 256, 0, s>>>(n, d.nPoint, d.np, out, c->sdB.xL);
+      c->launches += 2;
+    }
+    k_turb_perm_ab<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, c->posF, n, c->swB.nX, c->sdF.xL, c->sdB.xL);
     k_turb_sweep<true><<<2, 1024, 0, s>>>(c->swB, c->sdB, n);
-    k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, n, d.np, c->sdB.xL, out);
+    k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, n, c->swB.nX, d.np, c->sdB.xL, out);
     c->launches += 5;
+    return par ? halo_exchange_field(c, out, 2, false, s) : RX_OK;   // the matrix-vector product reads the neighbours' entries (:1707)
   };
   const unsigned gv = nblk(2 * n, 256);
   std::vector<double> g(m + 1, 0.0), sn(m + 1, 0.0), cs(m + 1, 0.0), y(m, 0.0);
@@ -635,7 +658,7 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
     auto sign = [](double x, double yv) { return yv == 0.0 ? 0.0 : (yv < 0 ? -std::fabs(x) : std::fabs(x)); };
     for (it = 0; it < m; ++it) {
       if (beta < to->linTol * norm0) break;
-      precond(c->kw[it], c->kz[it]);
+      if ((rc = precond(c->kw[it], c->kz[it]))) return rc;
       k_turb_matvec<<<nblk(n, 128), 128, 0, s>>>(d, w, c->kz[it], c->kw[it + 1]); c->launches++;
       // ModGramSchmidt (:87-175)
       double nrm;
@@ -680,6 +703,7 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   if (linIters) *linIters = it;
   k_turb_update<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
   RX_CK(cudaGetLastError());
+  if (par && (rc = halo_exchange_field(c, tp + (size_t)TP_K * d.np, 2, false, s))) return rc;   // Set_MPI_Solution (solver_direct_turbulent.cpp:707)
   // Postprocessing: gradients of the new (k, omega), blending functions, eddy viscosity -> the fields the flow path reads
   return rx_turb_postprocess(c, nullptr, c->sigmaK, 0);
 }
@@ -1160,7 +1184,7 @@ int rx_comm_init(rx_ctx* c, const void* id128, int rank, int nRanks, int nNeighb
 static int halo_exchange_on(rx_ctx* c, int what, cudaStream_t s);
 int rx_halo_exchange(rx_ctx* c, int what) {
   if (!c->comm) { c->err = "rx_halo_exchange: no communicator (rx_comm_init)"; return RX_ERR_ARG; }
-  if (what < 0 || what > 3 || (what == 3 && !c->tpost)) { c->err = "rx_halo_exchange: bad `what`"; return RX_ERR_ARG; }
+  if (what < 0 || what > 4 || (what >= 3 && !c->tpost)) { c->err = "rx_halo_exchange: bad `what`"; return RX_ERR_ARG; }
   return halo_exchange_on(c, what, c->stream);
 }
 // the same exchange forked onto the communicator's stream (everything enqueued so far on the context's stream is waited for); the
@@ -1183,13 +1207,17 @@ static int comm_join(rx_ctx* c) {
   m->pending = false;
   return RX_OK;
 }
+static double* halo_field(rx_ctx* c, int what);
 static int halo_exchange_on(rx_ctx* c, int what, cudaStream_t s) {
+  return halo_exchange_field(c, halo_field(c, what), rx_halo_width(c, what), what == 1 && c->o.viscous, s);
+}
+// `nv` columns (stride np) of any point field: the turbulence step also exchanges its Krylov / LU-SGS vectors this way
+// (CSysMatrix::SendReceive_Solution, matrix_structure.cpp:794)
+static int halo_exchange_field(rx_ctx* c, double* field, int nv, bool vortStrain, cudaStream_t s) {
   Comm* m = c->comm;
   std::string why;
   NcclApi* a = nccl_api(why);
-  const int nv = rx_halo_width(c, what);
   const int nNb = (int)m->nbRank.size();
-  double* field = what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np;
   for (int k = 0; k < nNb; ++k) {
     const long long n = m->sendPtr[k + 1] - m->sendPtr[k];
     if (n <= 0) continue;
@@ -1211,9 +1239,18 @@ static int halo_exchange_on(rx_ctx* c, int what, cudaStream_t s) {
     if (n <= 0) continue;
     k_unpack<<<nblk(n * nv, 256), 256, 0, s>>>(field, c->d.np, nv, n, m->recvPts + m->recvPtr[k], m->recvBuf + (size_t)m->recvPtr[k] * nv);
     c->launches++;
-    if (what == 1 && c->o.viscous) { k_vort_strain_points<9><<<nblk(n, 128), 128, 0, s>>>(c->d, n, m->recvPts + m->recvPtr[k]); c->launches++; }
+    if (vortStrain) { k_vort_strain_points<9><<<nblk(n, 128), 128, 0, s>>>(c->d, n, m->recvPts + m->recvPtr[k]); c->launches++; }
   }
   RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+// in-place sum over the ranks of n <= 8 doubles on the device (dotProd / SetResidual_RMS with MPI: vector_structure.cpp:397-419)
+static int comm_allreduce_sum(rx_ctx* c, double* dev, int n) {
+  Comm* m = c->comm;
+  std::string why;
+  NcclApi* a = nccl_api(why);
+  const int e = a->AllReduce(dev, dev, (size_t)n, NCCL_FLOAT64, NCCL_SUM, m->comm, c->stream);
+  if (e) { c->err = std::string("rx_turb_iterate: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
   return RX_OK;
 }
 // norms of the whole job from the partitions' sums of squares (SetResidual_RMS with MPI, solver_structure.cpp:188-260): one all-reduce
@@ -1239,14 +1276,14 @@ int rx_comm_allreduce_rms(rx_ctx* c, double* resRms) {
   return RX_OK;
 }
 
-int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : (what == 2 || what == 3) ? 4 : 0; }   // 2: limiter, 3: grad k, grad omega
+int rx_halo_width(rx_ctx* c, int what) { return what == 0 ? c->nVar : what == 1 ? c->nGrad * 2 : (what == 2 || what == 3) ? 4 : what == 4 ? 2 : 0; }   // 2: limiter, 3: grad k, grad omega, 4: k, omega
 static int halo_check(rx_ctx* c, int what, const void* pts, const void* buf) {
-  if (what < 0 || what > 3) { c->err = "rx_halo_pack/unpack: `what` must be 0 (U), 1 (gradients), 2 (limiters) or 3 (grad k, grad omega)"; return RX_ERR_ARG; }
-  if (what == 3 && !c->tpost) { c->err = "rx_halo_pack/unpack: what = 3 needs a RANS context"; return RX_ERR_ARG; }
+  if (what < 0 || what > 4) { c->err = "rx_halo_pack/unpack: `what` must be 0 (U), 1 (gradients), 2 (limiters), 3 (grad k, grad omega) or 4 (k, omega)"; return RX_ERR_ARG; }
+  if (what >= 3 && !c->tpost) { c->err = "rx_halo_pack/unpack: what = 3, 4 need a RANS context"; return RX_ERR_ARG; }
   if (!pts || !buf) { c->err = "rx_halo_pack/unpack: null device pointer"; return RX_ERR_ARG; }
   return RX_OK;
 }
-static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : c->tpost + (size_t)TP_GK * c->d.np; }
+static double* halo_field(rx_ctx* c, int what) { return what == 0 ? c->d.U : what == 1 ? c->d.grad : what == 2 ? c->d.lim : what == 3 ? c->tpost + (size_t)TP_GK * c->d.np : c->tpost + (size_t)TP_K * c->d.np; }
 int rx_halo_pack(rx_ctx* c, int what, int64_t n, const int64_t* pts, double* buf) {
   if (n <= 0) return RX_OK;
   if (what == 1) { const int rc = ensure_output(c); if (rc) return rc; }
@@ -1305,7 +1342,7 @@ extern "C" int rx_libm_eval(int which, int64_t n, const double* x, const double*
 // vertices, and the two-lanes-per-system pair_colpiv_qr_solve<9> of the viscous edge kernel) over host arrays of 9 x 9 systems
 namespace rx {
 __global__ void __launch_bounds__(VP_BS) k_qr_eval(long long n, const double* __restrict__ A, const double* __restrict__ b,
-                                                   double* __restrict__ xs, double* __restrict__ xp) {
+                                                   double* __restrict__ xp) {
   constexpr int NS = 9;
   extern __shared__ double vp_sm[];
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -1331,14 +1368,17 @@ __global__ void __launch_bounds__(VP_BS) k_qr_eval(long long n, const double* __
       for (int q = 0; q < 4; ++q) xp[(e * 2 + dd) * NS + 2 * q + l] = MG[dd][q];
       if (l) xp[(e * 2 + dd) * NS + 8] = MG[dd][4];
     }
-    if (l == 0) {
-      double Al[NS * NS], bl[2][NS], xl[2][NS];
-      for (int k = 0; k < NS * NS; ++k) Al[k] = Ae[k];
-      for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) bl[dd][i] = be[dd * NS + i];
-      colpiv_qr_solve<NS, 2, 1>(Al, bl, xl);
-      for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) xs[(e * 2 + dd) * NS + i] = xl[dd][i];
-    }
   }
+}
+__global__ void k_qr_eval_serial(long long n, const double* __restrict__ A, const double* __restrict__ b, double* __restrict__ xs) {
+  constexpr int NS = 9;
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  double Al[NS * NS], bl[2][NS], xl[2][NS];
+  for (int k = 0; k < NS * NS; ++k) Al[k] = A[e * NS * NS + k];
+  for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) bl[dd][i] = b[(e * 2 + dd) * NS + i];
+  colpiv_qr_solve<NS, 2, 1>(Al, bl, xl);
+  for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) xs[(e * 2 + dd) * NS + i] = xl[dd][i];
 }
 }  // namespace rx
 extern "C" int rx_qr_eval(int64_t n, const double* A, const double* b, double* xSerial, double* xPair, int device) {
@@ -1356,7 +1396,8 @@ extern "C" int rx_qr_eval(int64_t n, const double* A, const double* b, double* x
     const size_t smem = (size_t)rx::VP_SMW_RANS * rx::VP_BS * sizeof(double);
     if (cudaFuncSetAttribute(rx::k_qr_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) rc = RX_ERR_CUDA;
     if (rc == RX_OK) {
-      rx::k_qr_eval<<<(unsigned)((2 * n + rx::VP_BS - 1) / rx::VP_BS), rx::VP_BS, smem>>>((long long)n, dA, db, dxs, dxp);
+      rx::k_qr_eval<<<(unsigned)((2 * n + rx::VP_BS - 1) / rx::VP_BS), rx::VP_BS, smem>>>((long long)n, dA, db, dxp);
+      rx::k_qr_eval_serial<<<(unsigned)((n + 63) / 64), 64>>>((long long)n, dA, db, dxs);
       if (cudaMemcpy(xSerial, dxs, nb, cudaMemcpyDeviceToHost) != cudaSuccess || cudaMemcpy(xPair, dxp, nb, cudaMemcpyDeviceToHost) != cudaSuccess ||
           cudaGetLastError() != cudaSuccess) rc = RX_ERR_CUDA;
     }

@@ -262,9 +262,11 @@ struct SweepList {
   const int* colL;     // neighbour's POSITION in this list's level order
   const int* slot;     // index of the coefficient in TurbW::off (for the per-step gather into coefL)
   int nLvl, nEnt;      // levels; neighbour entries
+  int nX;              // entries of x per variable: n, plus (backward list of a partition) the halo points, whose x* the upper
+                       // triangle reads at positions n .. nPoint-1 (CSysMatrix::UpperProduct over columns received from the neighbours)
 };
 struct SweepData {     // per variable, in level order of one SweepList
-  double *coefL, *dgL, *bL, *xL;   // [2][nEnt], [2][n], [2][n], [2][n]
+  double *coefL, *dgL, *bL, *xL;   // [2][nEnt], [2][n], [2][n], [2][nX]
 };
 constexpr int SW_PRE = 3;   // neighbours carried in registers per point (a triangulated mesh has ~3 lower and ~3 upper ones; more: a plain loop)
 struct SwS0 { int n0, n1; };
@@ -317,7 +319,7 @@ __device__ __forceinline__ void sweep_run(const SweepList& sl, const double* __r
 template <bool BACK>
 __global__ void __launch_bounds__(1024) k_turb_sweep(const SweepList sl, const SweepData sd, long long n) {
   const int v = blockIdx.x;
-  sweep_run<BACK>(sl, sd.coefL + (size_t)v * sl.nEnt, sd.dgL + v * n, sd.bL + v * n, sd.xL + v * n);
+  sweep_run<BACK>(sl, sd.coefL + (size_t)v * sl.nEnt, sd.dgL + v * n, sd.bL + v * n, sd.xL + (size_t)v * sl.nX);
 }
 // per step: coefficients and diagonal of the assembled rows into level order
 __global__ void k_turb_sweep_coef(const SweepList sl, const SweepData sd, const TurbW w, long long n, long long np) {
@@ -335,17 +337,23 @@ __global__ void k_turb_perm_in(const int* __restrict__ perm, long long n, long l
   const int p = perm[t];
   dst[t] = src[p]; dst[n + t] = src[np + p];
 }
-__global__ void k_turb_perm_ab(const int* __restrict__ permB, const int* __restrict__ posA, long long n, const double* __restrict__ xA, double* __restrict__ xB) {
+__global__ void k_turb_perm_ab(const int* __restrict__ permB, const int* __restrict__ posA, long long n, long long nXB, const double* __restrict__ xA, double* __restrict__ xB) {
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (t >= n) return;
   const int s = posA[permB[t]];
-  xB[t] = xA[s]; xB[n + t] = xA[n + s];
+  xB[t] = xA[s]; xB[nXB + t] = xA[n + s];
 }
-__global__ void k_turb_perm_out(const int* __restrict__ perm, long long n, long long np, const double* __restrict__ src, double* __restrict__ dst) {
+__global__ void k_turb_perm_out(const int* __restrict__ perm, long long n, long long nXsrc, long long np, const double* __restrict__ src, double* __restrict__ dst) {
   const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (t >= n) return;
   const int p = perm[t];
-  dst[p] = src[t]; dst[np + p] = src[n + t];
+  dst[p] = src[t]; dst[np + p] = src[nXsrc + t];
+}
+// partition: the neighbours' x* (received into the halo entries of a point-order vector) -> the tail of the backward list's x
+__global__ void k_turb_halo_in(long long n, long long nPoint, long long np, const double* __restrict__ src, double* __restrict__ xB) {
+  const long long h = n + blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (h >= nPoint) return;
+  xB[h] = src[h]; xB[nPoint + h] = src[np + h];
 }
 
 // vector kernels over [2][nOwn] (stride np): dot product partials (blocks of 256, fixed tree), axpy, scale

@@ -108,8 +108,8 @@ __device__ __forceinline__ void pair_gemv(MatF A, const double* f, double* res) 
 // Eigen's own order — so the result equals the serial routine's, and the reference's, bit for bit).  The work is split by
 // COLUMNS: after the reflector of step k is formed, lane l applies it to columns k+1+l, k+3+l, ... and down-dates their norms;
 // the two right-hand sides are columns 9 and 10, one per lane at every step (the lane whose column parity it matches), and each
-// lane back-substitutes one right-hand side.  No sum crosses lanes.  The nine steps are instantiated one by one (K is a
-// compile-time constant), so each works on exactly the 8 - K entries below the diagonal.
+// lane back-substitutes one right-hand side.  No sum crosses lanes.  The step loop stays rolled (nine instantiated steps were
+// measured 9 % slower: instruction fetch); entries at or above the diagonal take part as zeros, which no sum order notices.
 // Storage (pair-shared: the words of both lanes): entry (i, j) at smPair[(i & 1) + (j*5 + (i >> 1)) * VP_BS], j = 0..10;
 // updated / direct column norms at column slots 11 and 12 (i = column index).
 template <int NS>
@@ -121,135 +121,16 @@ struct PairMat {
 };
 constexpr int VP_QR_COLS = 13;   // 9 matrix columns, 2 right-hand sides, 2 norm vectors
 
-struct PairQR {
-  double threshold_helper, downdate;
-  int nonzero;
-  unsigned long long perm;   // nibble i = original column now at position i
-};
-
-template <int NS, int K>
-__device__ __forceinline__ void pair_qr_step(const PairMat<NS>& M, const int l, PairQR& q) {
-  using PM = PairMat<NS>;
-  constexpr int MM = NS - 1 - K;   // entries below the diagonal
-  double* const nU = M.col(NS + 2);
-  double* const nD = M.col(NS + 3);
-  // pivot: first column of largest updated norm (both lanes, same result)
-  int big = K;
-  double nb = nU[PM::off(K)];
-#pragma unroll
-  for (int j = K + 1; j < NS; ++j) { const double nj = nU[PM::off(j)]; if (nj > nb) { nb = nj; big = j; } }
-  if (q.nonzero == NS && nb * nb < q.threshold_helper * (double)(NS - K)) q.nonzero = K;
-  if constexpr (MM == 0) return;   // last column: tail norm 0, tau = 0, beta = the entry itself; nothing to apply
-  else {
-    if (big != K) {
-      double* ck = M.col(K); double* cb = M.col(big);
-#pragma unroll
-      for (int h = 0; h < 5; ++h) {   // lane l swaps the rows of its parity
-        const int i = 2 * h + l;
-        if (i < NS) { const double t = ck[PM::off(i)]; ck[PM::off(i)] = cb[PM::off(i)]; cb[PM::off(i)] = t; }
-      }
-      if (l == 0) {
-        nU[PM::off(big)] = nU[PM::off(K)]; nU[PM::off(K)] = nb;
-        const double t = nD[PM::off(K)]; nD[PM::off(K)] = nD[PM::off(big)]; nD[PM::off(big)] = t;
-      }
-      const unsigned long long pk = (q.perm >> (4 * K)) & 15ULL, pb = (q.perm >> (4 * big)) & 15ULL;
-      q.perm = (q.perm & ~((15ULL << (4 * K)) | (15ULL << (4 * big)))) | (pb << (4 * K)) | (pk << (4 * big));
-    }
-    __syncwarp();
-    // reflector of column K: both lanes form the scalars, each normalises the entries of its parity
-    double* const ck = M.col(K);
-    double vv[MM], sq[MM];
-#pragma unroll
-    for (int r = 0; r < MM; ++r) { vv[r] = ck[PM::off(K + 1 + r)]; sq[r] = vv[r] * vv[r]; }
-    const double c0 = ck[PM::off(K)];
-    __syncwarp();   // both lanes hold the raw column before either overwrites its half
-    const double tailSq = eig_redux<MM, false>(sq);
-    double beta, tau;
-    if (tailSq <= 2.2250738585072014e-308) {
-      tau = 0.0; beta = c0;
-#pragma unroll
-      for (int r = 0; r < MM; ++r) vv[r] = 0.0;
-    } else {
-      beta = sqrt(c0 * c0 + tailSq);
-      if (c0 >= 0.0) beta = -beta;
-      const double den = c0 - beta;
-      bool bad = !mid_range(den);   // operand ranges once per reflector instead of a validity test per quotient (rx_fdiv.cuh)
-#pragma unroll
-      for (int r = 0; r < MM; ++r) bad = bad || !num_range(vv[r]);
-      const Recip rden = frecip(den);
-      double vq[MM];
-#pragma unroll
-      for (int r = 0; r < MM; ++r) vq[r] = fdivu(vv[r], rden);
-      if (bad) {
-#pragma unroll
-        for (int r = 0; r < MM; ++r) vq[r] = vv[r] / den;
-      }
-#pragma unroll
-      for (int r = 0; r < MM; ++r) vv[r] = vq[r];
-      tau = (beta - c0) / beta;
-    }
-#pragma unroll
-    for (int r = 0; r < MM; ++r) if (((K + 1 + r) & 1) == l) ck[PM::off(K + 1 + r)] = vv[r];
-    if (l == (K & 1)) ck[PM::off(K)] = beta;
-    // columns of this lane: t = v.w + w_k,  w_k -= tau t,  w_i -= (tau v_i) t;  then the norm down-date
-    if (tau != 0.0) {
-      double tvv[MM];
-#pragma unroll
-      for (int r = 0; r < MM; ++r) tvv[r] = tau * vv[r];
-#pragma unroll 1
-      for (int j = K + 1 + l; j < NS; j += 2) {
-        double* const cj = M.col(j);
-        double w[MM], pr[MM];
-#pragma unroll
-        for (int r = 0; r < MM; ++r) { w[r] = cj[PM::off(K + 1 + r)]; pr[r] = w[r] * vv[r]; }
-        const double wk = cj[PM::off(K)];
-        const double t = eig_gemv_row<MM>(pr) + wk;
-        cj[PM::off(K)] = wk - tau * t;
-#pragma unroll
-        for (int r = 0; r < MM; ++r) cj[PM::off(K + 1 + r)] = w[r] - tvv[r] * t;
-      }
-      if (q.nonzero == NS) {   // solve() applies the first `nonzero` reflectors to the right-hand sides: an inner product each
-        double* const cj = M.col(((K + 1 + l) & 1) ? NS : NS + 1);
-        double w[MM], pr[MM];
-#pragma unroll
-        for (int r = 0; r < MM; ++r) { w[r] = cj[PM::off(K + 1 + r)]; pr[r] = vv[r] * w[r]; }
-        const double wk = cj[PM::off(K)];
-        const double t = eig_redux<MM, false>(pr) + wk;
-        cj[PM::off(K)] = wk - tau * t;
-#pragma unroll
-        for (int r = 0; r < MM; ++r) cj[PM::off(K + 1 + r)] = w[r] - tvv[r] * t;
-      }
-    }
-#pragma unroll 1
-    for (int j = K + 1 + l; j < NS; j += 2) {
-      const double nu = nU[PM::off(j)];
-      if (nu != 0.0) {
-        const double* cj = M.col(j);
-        const double ndj = nD[PM::off(j)];
-        const double akj = fabs(cj[PM::off(K)]);
-        bool bad = false;
-        double temp = fdiv(akj, nu, bad);
-        double qq = fdiv(nu, ndj, bad);
-        if (bad) { temp = akj / nu; qq = nu / ndj; }
-        temp = (1.0 + temp) * (1.0 - temp);
-        temp = temp < 0.0 ? 0.0 : temp;
-        const double temp2 = temp * (qq * qq);
-        if (temp2 <= q.downdate) {
-          double a2[MM];
-#pragma unroll
-          for (int r = 0; r < MM; ++r) { const double a = cj[PM::off(K + 1 + r)]; a2[r] = a * a; }
-          const double n = sqrt(eig_redux<MM, false>(a2));
-          nD[PM::off(j)] = n; nU[PM::off(j)] = n;
-        } else {
-          bool bad2 = false;
-          double rt = fsqrt(temp, bad2);
-          if (bad2) rt = sqrt(temp);
-          nU[PM::off(j)] = nu * rt;
-        }
-      }
-    }
-    __syncwarp();
-  }
+// Eigen's packet-ordered sum (eig_redux<8 - k> of rx_flux.cuh) over the entries k+1 .. 8 of a zero-padded T[0..8] (T[i] = 0 for
+// i <= k).  Written out for the eight lengths, the trees are
+//   k = 0: ((T1+T5)+(T3+T7)) + ((T2+T6)+(T4+T8))        k = 1: (((T2+T4)+T6) + ((T3+T5)+T7)) + T8      k = 2: ((T3+T5)+T7) + ((T4+T6)+T8)
+//   k = 3: ((T4+T6)+(T5+T7)) + T8     k = 4: (T5+T7)+(T6+T8)     k = 5: (T6+T7)+T8     k = 6: T7+T8     k = 7: T8
+// and with the padding zeros in place every odd k is (B + A) + T8 and every even k >= 2 is A + C, where A = (T3+T5)+T7,
+// B = (T2+T4)+T6, C = (T4+T6)+T8 (adding a zero changes nothing).  k is uniform across the warp.
+__device__ __forceinline__ double eig_redux_tail(int k, const double* T) {
+  if (k == 0) return ((T[1] + T[5]) + (T[3] + T[7])) + ((T[2] + T[6]) + (T[4] + T[8]));
+  const double A = (T[3] + T[5]) + T[7], e46 = T[4] + T[6];
+  return (k & 1) ? (((T[2] + T[4]) + T[6]) + A) + T[8] : A + (e46 + T[8]);
 }
 
 template <int NS>
@@ -274,16 +155,139 @@ __device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* 
   double mx = nU[PM::off(0)];
 #pragma unroll
   for (int j = 1; j < NS; ++j) mx = fmax(mx, nU[PM::off(j)]);
-  PairQR q;
-  q.threshold_helper = (mx * eps) * (mx * eps) / (double)NS;
-  q.downdate = sqrt(eps);
-  q.nonzero = NS;
-  q.perm = 0x876543210ULL;
-  pair_qr_step<NS, 0>(M, l, q); pair_qr_step<NS, 1>(M, l, q); pair_qr_step<NS, 2>(M, l, q);
-  pair_qr_step<NS, 3>(M, l, q); pair_qr_step<NS, 4>(M, l, q); pair_qr_step<NS, 5>(M, l, q);
-  pair_qr_step<NS, 6>(M, l, q); pair_qr_step<NS, 7>(M, l, q); pair_qr_step<NS, 8>(M, l, q);
-  const int nonzero = q.nonzero;
-  const unsigned long long perm = q.perm;
+  const double threshold_helper = (mx * eps) * (mx * eps) / (double)NS;
+  const double downdate = sqrt(eps);
+  int nonzero = NS;
+  unsigned long long perm = 0x876543210ULL;   // nibble i = original column now at position i
+#pragma unroll 1
+  for (int k = 0; k < NS; ++k) {
+    // pivot: first column of largest updated norm (both lanes, same result)
+    int big = k;
+    double nb = nU[PM::off(k)];
+    for (int j = k + 1; j < NS; ++j) { const double nj = nU[PM::off(j)]; if (nj > nb) { nb = nj; big = j; } }
+    if (nonzero == NS && nb * nb < threshold_helper * (double)(NS - k)) nonzero = k;
+    if (big != k) {
+      double* ck = M.col(k); double* cb = M.col(big);
+#pragma unroll
+      for (int h = 0; h < 5; ++h) {   // lane l swaps the rows of its parity
+        const int i = 2 * h + l;
+        if (i < NS) { const double t = ck[PM::off(i)]; ck[PM::off(i)] = cb[PM::off(i)]; cb[PM::off(i)] = t; }
+      }
+      if (l == 0) {
+        nU[PM::off(big)] = nU[PM::off(k)]; nU[PM::off(k)] = nb;
+        const double t = nD[PM::off(k)]; nD[PM::off(k)] = nD[PM::off(big)]; nD[PM::off(big)] = t;
+      }
+      const unsigned long long pk = (perm >> (4 * k)) & 15ULL, pb = (perm >> (4 * big)) & 15ULL;
+      perm = (perm & ~((15ULL << (4 * k)) | (15ULL << (4 * big)))) | (pb << (4 * k)) | (pk << (4 * big));
+    }
+    __syncwarp();
+    // reflector of column k: both lanes form the scalars, each normalises the entries of its parity
+    double* const ck = M.col(k);
+    double vv[NS];   // entries below the diagonal, zero elsewhere
+    vv[0] = 0.0;
+#pragma unroll
+    for (int i = 1; i < NS; ++i) vv[i] = i > k ? ck[PM::off(i)] : 0.0;
+    const double c0 = M(k, k);
+    __syncwarp();   // both lanes hold the raw column before either overwrites its half
+    double T[NS];
+    T[0] = 0.0;
+#pragma unroll
+    for (int i = 1; i < NS; ++i) T[i] = vv[i] * vv[i];
+    const double tailSq = eig_redux_tail(k, T);
+    double beta, tau;
+    if (tailSq <= 2.2250738585072014e-308) {
+      tau = 0.0; beta = c0;
+#pragma unroll
+      for (int i = 1; i < NS; ++i) vv[i] = 0.0;
+    } else {
+      beta = sqrt(c0 * c0 + tailSq);
+      if (c0 >= 0.0) beta = -beta;
+      const double den = c0 - beta;
+      bool bad = !mid_range(den);   // operand ranges once per reflector instead of a validity test per quotient (rx_fdiv.cuh)
+#pragma unroll
+      for (int i = 1; i < NS; ++i) bad = bad || !num_range(vv[i]);
+      const Recip rden = frecip(den);
+      double vq[NS];
+#pragma unroll
+      for (int i = 1; i < NS; ++i) vq[i] = fdivu(vv[i], rden);
+      if (bad) {
+#pragma unroll
+        for (int i = 1; i < NS; ++i) vq[i] = vv[i] / den;
+      }
+#pragma unroll
+      for (int i = 1; i < NS; ++i) vv[i] = vq[i];
+      tau = (beta - c0) / beta;
+    }
+#pragma unroll
+    for (int i = 1; i < NS; ++i) if (i > k && (i & 1) == l) ck[PM::off(i)] = vv[i];
+    if (l == (k & 1)) M(k, k) = beta;
+    // columns of this lane: t = v.w + w_k,  w_k -= tau t,  w_i -= (tau v_i) t;  then the norm down-date
+    if (tau != 0.0) {   // never at k = 8
+      double tvv[NS];
+#pragma unroll
+      for (int i = 1; i < NS; ++i) tvv[i] = tau * vv[i];
+      if (nonzero == NS) {   // solve() applies the first `nonzero` reflectors to the right-hand sides: an inner product each
+        double* const cj = M.col(((k + 1 + l) & 1) ? NS : NS + 1);   // one right-hand side per lane at every step
+        double w[NS];
+#pragma unroll
+        for (int i = 1; i < NS; ++i) { w[i] = cj[PM::off(i)]; T[i] = vv[i] * w[i]; }
+        const double wk = cj[PM::off(k)];
+        const double t = eig_redux_tail(k, T) + wk;
+        cj[PM::off(k)] = wk - tau * t;
+#pragma unroll
+        for (int i = 1; i < NS; ++i) if (i > k) cj[PM::off(i)] = w[i] - tvv[i] * t;
+      }
+      // matrix columns: the first entry of the essential vector is the row kernel's scalar head (eig_gemv_row, rx_flux.cuh); it
+      // is taken out of vv[] so that the two packet lanes are plain sums over the even and the odd entries
+      double vv0 = 0.0;
+#pragma unroll
+      for (int i = 1; i < NS; ++i) { const bool head = i == k + 1; vv0 = head ? vv[i] : vv0; vv[i] = head ? 0.0 : vv[i]; }
+      const int offHead = PM::off(k + 1);
+      const bool kOdd = k & 1;
+      for (int j = k + 1 + l; j < NS; j += 2) {
+        double* const cj = M.col(j);
+        double w[NS];
+#pragma unroll
+        for (int i = 1; i < NS; ++i) w[i] = cj[PM::off(i)];
+        const double t0 = cj[offHead] * vv0;
+        const double se6 = (w[2] * vv[2] + w[4] * vv[4]) + w[6] * vv[6], so = (w[3] * vv[3] + w[5] * vv[5]) + w[7] * vv[7];
+        const double t8 = w[8] * vv[8];
+        double t = kOdd ? t0 + (so + (se6 + t8)) : (t0 + (se6 + so)) + t8;
+        const double wk = cj[PM::off(k)];
+        t += wk;
+        cj[PM::off(k)] = wk - tau * t;
+#pragma unroll
+        for (int i = 1; i < NS; ++i) if (i > k) cj[PM::off(i)] = w[i] - tvv[i] * t;
+      }
+    }
+    for (int j = k + 1 + l; j < NS; j += 2) {
+      const double nu = nU[PM::off(j)];
+      if (nu != 0.0) {
+        const double* cj = M.col(j);
+        const double ndj = nD[PM::off(j)];
+        const double akj = fabs(cj[PM::off(k)]);
+        bool bad = false;
+        double temp = fdiv(akj, nu, bad);
+        double qq = fdiv(nu, ndj, bad);
+        if (bad) { temp = akj / nu; qq = nu / ndj; }
+        temp = (1.0 + temp) * (1.0 - temp);
+        temp = temp < 0.0 ? 0.0 : temp;
+        const double temp2 = temp * (qq * qq);
+        if (temp2 <= downdate) {
+#pragma unroll
+          for (int i = 1; i < NS; ++i) { const double a = i > k ? cj[PM::off(i)] : 0.0; T[i] = a * a; }
+          const double n = sqrt(eig_redux_tail(k, T));
+          nD[PM::off(j)] = n; nU[PM::off(j)] = n;
+        } else {
+          bool bad2 = false;
+          double rt = fsqrt(temp, bad2);
+          if (bad2) rt = sqrt(temp);
+          nU[PM::off(j)] = nu * rt;
+        }
+      }
+    }
+    __syncwarp();
+  }
   // back substitution with R (upper triangle) as Eigen's triangular solver does it: within the panel of the last 8 columns a
   // solved unknown is subtracted from the rows above it in the panel; row 0 of a full-rank system (above the panel) then takes
   // the panel's columns in ascending order.  Lane l owns right-hand side l (column 9 + l); entries >= nonzero are zero.

@@ -1,6 +1,7 @@
 """Halo exchange inside the library over NCCL (rx_comm_init / rx_halo_exchange / rx_comm_allreduce_rms; csrc/rx_comm.cuh): a run
 partitioned over the GPUs of the box — strips and graph partitions with RCM numbering, laminar and RANS — equals the single-partition
-run to 1e-12, with rx_iterate doing exchanges and global norms without the host in the loop.  Needs at least two GPUs."""
+run to 1e-12, with rx_iterate doing exchanges and global norms without the host in the loop.  Mode "turb": the SST transport step on
+every partition as well (rx_turb_iterate with a communicator; criteria in nccl_worker.turb_mode).  Needs at least two GPUs."""
 import os
 import subprocess
 import sys
@@ -12,7 +13,7 @@ from rxcase import ROOT
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", ["strips", "graph"])
+@pytest.mark.parametrize("mode", ["strips", "graph", "turb"])
 def test_partitioned_run_with_library_side_exchange_equals_single(mode):
     import torch
     n = torch.cuda.device_count()
