@@ -32,7 +32,7 @@ struct rx_ctx {
   std::string err;
   Dev d{};
   Opts o{};
-  ChemC<9> cc9{};
+  ChemC<9> cc9{}; ChemC<5> cc5{}; ChemC<3> cc3{};   // the one matching Ns is filled (RX_NS below)
   std::vector<MarkerDev> markers;
   std::vector<void*> allocs;
   // SST transport step (rx_turb_step.cuh): work arrays, Krylov vectors, level lists of the LU-SGS sweeps
@@ -83,6 +83,15 @@ static int comm_allreduce_sum(rx_ctx* c, double* dev, int n);
     }                                                                                                 \
   } while (0)
 
+// Kernels are instantiated for the species counts of the mixtures the reference ships: 9 (jet reactor, TURBOLENT_COMBUSTION), 5 and 3
+// (TURBOLENT_FLAT_PLATE: test.txt, test_air.txt).  A launch site names its kernel once, with NS and cc bound by the dispatch.
+template <int N> struct ChemOf;
+template <> struct ChemOf<9> { static ChemC<9>& get(rx_ctx* c) { return c->cc9; } };
+template <> struct ChemOf<5> { static ChemC<5>& get(rx_ctx* c) { return c->cc5; } };
+template <> struct ChemOf<3> { static ChemC<3>& get(rx_ctx* c) { return c->cc3; } };
+#define RX_NS_CASE(N, ...) case N: { constexpr int NS = N; const ChemC<N>& cc = ChemOf<N>::get(c); (void)cc; (void)NS; __VA_ARGS__; } break;
+#define RX_NS(...) do { switch (c->Ns) { RX_NS_CASE(9, __VA_ARGS__) RX_NS_CASE(5, __VA_ARGS__) RX_NS_CASE(3, __VA_ARGS__) default: break; } } while (0)
+
 namespace {
 template <class T>
 T* dalloc(rx_ctx* c, size_t n) {
@@ -102,11 +111,10 @@ T* dupload(rx_ctx* c, const std::vector<T>& h) {
 inline unsigned nblk(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
 // host-side constants of the mechanism; libm calls are the ones the reference makes (reacting_model_library.cpp:634-696,751-766)
-int fill_chem(rx_ctx* c, const rx_chem* ch) {
-  if (ch->Ns != 9) return RX_ERR_UNSUPPORTED;
+template <int NS>
+int fill_chem_ns(rx_ctx* c, const rx_chem* ch) {
   if (ch->Nr > NRMAX) return RX_ERR_UNSUPPORTED;
-  constexpr int NS = 9;
-  ChemC<NS>& cc = c->cc9;
+  ChemC<NS>& cc = ChemOf<NS>::get(c);
   cc.Nr = ch->Nr; cc.nKnots = ch->nKnots;
   std::vector<double> x(ch->x, ch->x + ch->nKnots);
   cc.x = dupload(c, x);
@@ -156,6 +164,15 @@ int fill_chem(rx_ctx* c, const rx_chem* ch) {
   return RX_OK;
 }
 
+int fill_chem(rx_ctx* c, const rx_chem* ch) {
+  switch (ch->Ns) {
+    case 9: return fill_chem_ns<9>(c, ch);
+    case 5: return fill_chem_ns<5>(c, ch);
+    case 3: return fill_chem_ns<3>(c, ch);
+    default: return RX_ERR_UNSUPPORTED;
+  }
+}
+
 int ensure_stage(rx_ctx* c, size_t bytes) {
   if (bytes <= c->stageBytes) return RX_OK;
   if (c->stage) cudaFree(c->stage);
@@ -188,19 +205,49 @@ int download_aos(rx_ctx* c, const double* soa, double* h, int nv) {
 }
 }  // namespace
 
+// viscous edge flux: nine species (the mechanism every BASELINE configuration uses) go through the two-lanes-per-edge kernel, whose row
+// split and storage are laid out for nine rows; the other instantiated species counts take the thread-per-edge form of the same
+// arithmetic (viscous_flux<NS, EDGE = true>, rx_flux.cuh), with the thread-private Stefan–Maxwell scratch in shared memory
+template <int NS>
+static void launch_edge_visc(rx_ctx* c, const ChemC<NS>& cc, cudaStream_t s) {
+  const Dev& d = c->d;
+  if constexpr (NS == 9) {
+    if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(cc, c->o, d);
+    else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(cc, c->o, d);
+  } else {
+    if (c->o.rans) k_edge_visc_generic<NS, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d);
+    else k_edge_visc_generic<NS, false><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d);
+  }
+}
+template <int NS>
+static cudaError_t set_kernel_attributes() {
+  const int smv = (int)SM_VISC;
+  const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+  cudaError_t e = cudaSuccess;
+  if constexpr (NS == 9) {
+    e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
+    if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
+  } else {
+    e = cudaFuncSetAttribute(k_edge_visc_generic<NS, true>, at, smv);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_generic<NS, false>, at, smv);
+  }
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<NS>, at, smv);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<NS>, at, smv);
+  return e;
+}
+
 // launch of the edge-flux kernels: the AUSM flux from its own bandwidth-bound kernel (or the MUSCL kernel), the viscous flux
 // from the two-lanes-per-edge kernel (rx_visc_pair.cuh; the RANS instantiation carries the SST closure).
 template <bool CONV, bool VISC>
 static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   const Dev& d = c->d;
   if (CONV) {
-    if (c->o.secondOrder) k_edge_conv2<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
-    else k_edge_flux<9><<<nblk(d.nEdge, 64), 64, 0, s>>>(c->cc9, c->o, d);
+    if (c->o.secondOrder) RX_NS(k_edge_conv2<NS><<<nblk(d.nEdge, 64), 64, 0, s>>>(cc, c->o, d));
+    else RX_NS(k_edge_flux<NS><<<nblk(d.nEdge, 64), 64, 0, s>>>(cc, c->o, d));
     c->launches++;
   }
   if (VISC) {
-    if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(c->cc9, c->o, d);
-    else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(c->cc9, c->o, d);
+    RX_NS(launch_edge_visc<NS>(c, cc, s));
     c->launches++;
   }
 }
@@ -208,13 +255,13 @@ static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
 // conv + visc accumulation and the source term in one kernel
 static void launch_accumulate_visc(rx_ctx* c, cudaStream_t s) {
   const Dev& d = c->d;
-  k_accumulate<9, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
+  RX_NS(k_accumulate<NS, 3><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, c->o, d));
   c->launches++;
 }
 
 extern "C" {
 
-int rx_supported_species(int Ns) { return Ns == 9; }
+int rx_supported_species(int Ns) { return Ns == 9 || Ns == 5 || Ns == 3; }
 
 const char* rx_last_error(rx_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
 
@@ -226,7 +273,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     g_create_error = "rx_create: no CUDA device (this library has no CPU path)";
     return RX_ERR_NO_DEVICE;
   }
-  if (!rx_supported_species(ch->Ns)) { g_create_error = "rx_create: kernels are instantiated for Ns = 9 only"; return RX_ERR_UNSUPPORTED; }
+  if (!rx_supported_species(ch->Ns)) { g_create_error = "rx_create: kernels are instantiated for Ns = 9, 5 and 3 (the mixtures the reference ships)"; return RX_ERR_UNSUPPORTED; }
   if (ch->Nr > NRMAX) { g_create_error = "rx_create: more reactions than NRMAX"; return RX_ERR_UNSUPPORTED; }
   if (m->nPoint >= (1LL << 31) || m->nEdge >= (1LL << 31)) { g_create_error = "rx_create: mesh exceeds int32 indices"; return RX_ERR_UNSUPPORTED; }
   rx_ctx* c = new rx_ctx();
@@ -236,17 +283,14 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     c->orderEdges = ev && (ev[0] == '0' || ev[0] == '1') ? ev[0] == '1' : !op->rans;
   }
   if (cudaSetDevice(c->device) != cudaSuccess) { g_create_error = "rx_create: cudaSetDevice failed"; delete c; return RX_ERR_CUDA; }
-  {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
-    const int smv = (int)SM_VISC;
-    const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
-    cudaError_t e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
-    if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<9>, at, smv);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<9>, at, smv);
-    if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }
-  }
   const int Ns = ch->Ns;
   c->Ns = Ns; c->nVar = Ns + 4; c->nPrim = Ns + 7; c->nGrad = Ns + 4;
+  {   // the thread-private Stefan–Maxwell scratch exceeds the default 48 KB of dynamic shared memory per block
+    cudaError_t e = cudaSuccess;
+    RX_NS(e = set_kernel_attributes<NS>());
+    if (e != cudaSuccess) { g_create_error = std::string("rx_create: cudaFuncSetAttribute: ") + cudaGetErrorString(e); delete c; return RX_ERR_CUDA; }
+  }
+  if (Ns != 9) c->orderEdges = false;   // the processing order by iteration count belongs to the pair kernel
   Opts& o = c->o;
   o.viscous = op->viscous; o.rans = op->rans; o.leastSquares = op->leastSquares;
   o.mInfty = op->mInfty; o.cfl = op->cfl; o.maxDt = op->maxDt; o.Tmin = op->Tmin; o.Tmax = op->Tmax;
@@ -752,7 +796,7 @@ static int preprocess_primitive(rx_ctx* c, int64_t extIter, int output) {
   cudaStream_t s = c->stream;
   c->outputPending = false;
   RX_CK(cudaMemsetAsync(d.counters, 0, sizeof(unsigned long long), s));
-  k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, (long long)extIter, output);
+  RX_NS(k_primitive<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, c->o, d, (long long)extIter, output));
   c->launches++;
   if (c->eddyFlow) RX_CK(cudaMemcpyAsync(c->eddyFlow, d.turb, (size_t)d.np * sizeof(double), cudaMemcpyDeviceToDevice, s));
   return RX_OK;
@@ -760,17 +804,17 @@ static int preprocess_primitive(rx_ctx* c, int64_t extIter, int output) {
 static int preprocess_derived(rx_ctx* c, int output) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
-  if (c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }
+  if (c->o.viscous) { RX_NS(k_transport<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, d)); c->launches++; }
   if (c->o.viscous || c->o.secondOrder) {
     if (c->o.leastSquares) {
-      k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+      RX_NS(k_gradient_ls<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(d));
       c->launches++;
     } else {
-      k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d);
+      RX_NS(k_gradient_gg_edges<NS><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d));
       c->launches++;
       for (const MarkerDev& m : c->markers)
-        if (m.nVertex) { k_gradient_gg_boundary<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
-      k_gradient_gg_finish<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
+        if (m.nVertex) { RX_NS(k_gradient_gg_boundary<NS><<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m)); c->launches++; }
+      RX_NS(k_gradient_gg_finish<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(d));
       c->launches++;
     }
   }
@@ -840,7 +884,7 @@ int rx_time_step(rx_ctx* c) {
 int rx_residual_conv(rx_ctx* c) {
   const Dev& d = c->d;
   launch_edge_flux<true, false>(c, c->stream);
-  k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  RX_NS(k_accumulate<NS, 1><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(cc, c->o, d));
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -849,14 +893,14 @@ int rx_residual_visc(rx_ctx* c) {
   if (!c->o.viscous) return RX_OK;
   const Dev& d = c->d;
   launch_edge_flux<false, true>(c, c->stream);
-  k_accumulate<9, 2><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  RX_NS(k_accumulate<NS, 2><<<nblk(d.nPoint, 128), 128, 0, c->stream>>>(cc, c->o, d));
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
 int rx_residual_source(rx_ctx* c) {
   const Dev& d = c->d;
-  k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, c->stream>>>(c->cc9, c->o, d);
+  RX_NS(k_source<NS><<<nblk(d.nPointDomain, 128), 128, 0, c->stream>>>(cc, c->o, d));
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -864,9 +908,9 @@ int rx_residual_source(rx_ctx* c) {
 static void launch_bc(rx_ctx* c, const MarkerDev& m, cudaStream_t s) {
   const Dev& d = c->d;
   if (!m.nVertex) return;
-  if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { k_bc_inlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
-  else if (m.kind == RX_BC_OUTLET) { k_bc_outlet<9><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(c->cc9, c->o, d, m); c->launches++; }
-  else if (m.kind == RX_BC_ISOTHERMAL) { k_bc_isothermal<9><<<nblk(m.nVertex, 64), 64, 0, s>>>(c->cc9, c->o, d, m); c->launches++; }
+  if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { RX_NS(k_bc_inlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
+  else if (m.kind == RX_BC_OUTLET) { RX_NS(k_bc_outlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
+  else if (m.kind == RX_BC_ISOTHERMAL) { RX_NS(k_bc_isothermal<NS><<<nblk(m.nVertex, 64), 64, 0, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_HEATFLUX) { k_bc_heatflux<<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
   else if (m.kind == RX_BC_EULER_WALL) { k_bc_euler_wall<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
 }
@@ -934,12 +978,12 @@ int rx_update_explicit(rx_ctx* c, double alpha, double* resRms) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
   if (resRms) {   // norms wanted on the host: the location of the largest residual comes with them (rx_get_residual_max)
-    k_update<9, true><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, c->pmax, c->pidx);
+    RX_NS(k_update<NS, true><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, c->pmax, c->pidx));
     k_resmax_finish<<<c->nVar, 256, 0, s>>>(c->pmax, c->pidx, c->updBlocks, c->nVar, c->resMax, c->resMaxPoint);
     c->launches++;
     c->haveResMax = true;
   } else {
-    k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, nullptr, nullptr);
+    RX_NS(k_update<NS, false><<<c->updBlocks, 128, 0, s>>>(d, alpha, c->partial, nullptr, nullptr));
   }
   k_rms_finish<<<c->nVar, 256, 0, s>>>(c->partial, c->updBlocks, c->nVar, d.nPoint, c->rms, c->sumsq);
   c->launches += 2;
@@ -977,8 +1021,8 @@ int rx_residual_all(rx_ctx* c) {
   } else {
     if ((rc = comm_join(c))) return rc;
     launch_edge_flux<true, false>(c, s);
-    k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d);
-    k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d);
+    RX_NS(k_accumulate<NS, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, c->o, d));
+    RX_NS(k_source<NS><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(cc, c->o, d));
     c->launches += 2;
   }
   RX_CK(cudaGetLastError());
@@ -1004,17 +1048,17 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
                 c->launches--; break;   // the helper counts its own launch
         case 1: launch_edge_flux<true, false>(c, s); c->launches--; break;
         case 2: if (c->o.viscous) { launch_accumulate_visc(c, s); c->launches--; }
-                else k_accumulate<9, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
-        case 3: k_primitive<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, c->o, d, 1LL, 1); break;
-        case 7: k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); break;
-        case 4: if (c->o.leastSquares) k_gradient_ls<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(d);
-                else k_gradient_gg_edges<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d); break;
-        case 5: k_source<9><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->cc9, c->o, d); break;
+                else RX_NS(k_accumulate<NS, 1><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, c->o, d)); break;
+        case 3: RX_NS(k_primitive<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, c->o, d, 1LL, 1)); break;
+        case 7: RX_NS(k_transport<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, d)); break;
+        case 4: if (c->o.leastSquares) RX_NS(k_gradient_ls<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(d));
+                else RX_NS(k_gradient_gg_edges<NS><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(d)); break;
+        case 5: RX_NS(k_source<NS><<<nblk(d.nPointDomain, 128), 128, 0, s>>>(cc, c->o, d)); break;
         case 8: if (!c->tpost) { cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
                 k_turb_gradient_ls<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost); break;
         case 9: if (!c->tpost) { cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: not a RANS context"; return RX_ERR_ARG; }
                 k_turb_blend<<<nblk(d.nPoint, 128), 128, 0, s>>>(d, c->tpost, c->sigmaK); break;
-        case 6: k_update<9, false><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial, nullptr, nullptr); break;
+        case 6: RX_NS(k_update<NS, false><<<c->updBlocks, 128, 0, s>>>(d, 0.0, c->partial, nullptr, nullptr)); break;
         default: cudaEventDestroy(e0); cudaEventDestroy(e1); c->err = "rx_kernel_time: unknown kernel id"; return RX_ERR_ARG;
       }
       c->launches++;
@@ -1026,7 +1070,7 @@ int rx_kernel_time(rx_ctx* c, int which, int reps, double* msAvg) {
     RX_CK(cudaEventElapsedTime(&ms, e0, e1));
     if (pass == 1 && msAvg) *msAvg = (double)ms / n;
   }
-  if (which == 3 && c->o.viscous) { k_transport<9><<<nblk(d.nPoint, 128), 128, 0, s>>>(c->cc9, d); c->launches++; }   // mu[p] held T
+  if (which == 3 && c->o.viscous) { RX_NS(k_transport<NS><<<nblk(d.nPoint, 128), 128, 0, s>>>(cc, d)); c->launches++; }   // mu[p] held T
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   return RX_OK;
 }
@@ -1076,7 +1120,7 @@ int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, doubl
 }
 
 int rx_source_points_dev(rx_ctx* c, int64_t n, const double* T, const double* rho, const double* Y, const double* omT, const double* vol, double* res) {
-  k_source_points<9><<<nblk(n, 128), 128, 0, c->stream>>>(c->cc9, c->o.rans, c->o.cMu, c->o.pasrLb, (long long)n, T, rho, Y, omT, vol, res);
+  RX_NS(k_source_points<NS><<<nblk(n, 128), 128, 0, c->stream>>>(cc, c->o.rans, c->o.cMu, c->o.pasrLb, (long long)n, T, rho, Y, omT, vol, res));
   c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -1105,7 +1149,7 @@ int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int
     if (omT) cudaMemcpy(dO, omT, n * sizeof(double), cudaMemcpyHostToDevice);
     cudaMemcpy(dA, Y, n * Ns * sizeof(double), cudaMemcpyHostToDevice);
     k_aos_to_soa<<<nblk(n * Ns, 256), 256>>>(dA, dY, n, Ns, n);
-    k_source_points<9><<<nblk(n, 128), 128>>>(c->cc9, rans, cMu, pasrLb, (long long)n, dT, dr, dY, omT ? dO : nullptr, dV, dR);
+    RX_NS(k_source_points<NS><<<nblk(n, 128), 128>>>(cc, rans, cMu, pasrLb, (long long)n, dT, dr, dY, omT ? dO : nullptr, dV, dR));
     k_soa_to_aos<<<nblk(n * Ns, 256), 256>>>(dR, dA, n, Ns, n);
     if (cudaMemcpy(res, dA, n * Ns * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
       g_create_error = "rx_source_points: kernel or copy failed"; rc = RX_ERR_CUDA;
@@ -1239,7 +1283,7 @@ static int halo_exchange_field(rx_ctx* c, double* field, int nv, bool vortStrain
     if (n <= 0) continue;
     k_unpack<<<nblk(n * nv, 256), 256, 0, s>>>(field, c->d.np, nv, n, m->recvPts + m->recvPtr[k], m->recvBuf + (size_t)m->recvPtr[k] * nv);
     c->launches++;
-    if (vortStrain) { k_vort_strain_points<9><<<nblk(n, 128), 128, 0, s>>>(c->d, n, m->recvPts + m->recvPtr[k]); c->launches++; }
+    if (vortStrain) { RX_NS(k_vort_strain_points<NS><<<nblk(n, 128), 128, 0, s>>>(c->d, n, m->recvPts + m->recvPtr[k])); c->launches++; }
   }
   RX_CK(cudaGetLastError());
   return RX_OK;
@@ -1301,7 +1345,7 @@ int rx_halo_unpack(rx_ctx* c, int what, int64_t n, const int64_t* pts, const dou
   k_unpack<<<nblk(n * nv, 256), 256, 0, c->stream>>>(halo_field(c, what), c->d.np, nv, n, (const long long*)pts, buf);
   c->launches++;
   if (what == 1 && c->o.viscous) {   // SetVorticity / SetStrainMag of the received points (:4716-4736 run after Set_MPI_Primitive_Gradient)
-    k_vort_strain_points<9><<<nblk(n, 128), 128, 0, c->stream>>>(c->d, (long long)n, (const long long*)pts);
+    RX_NS(k_vort_strain_points<NS><<<nblk(n, 128), 128, 0, c->stream>>>(c->d, (long long)n, (const long long*)pts));
     c->launches++;
   }
   RX_CK(cudaGetLastError());

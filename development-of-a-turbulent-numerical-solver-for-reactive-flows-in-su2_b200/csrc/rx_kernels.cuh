@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(128, RX_TR_MINB) k_transport(const __grid_cons
   const double Patm = P * 1.0 / 101325.0;
   const Recip r1e4 = frecip(1.0 * 1.0 * 1.0e4);
   const bool dOk = mid_range(T175) && mid_range(Patm);   // then every quotient below has mid-range operands (pair constants are O(1..100))
-  constexpr int NQ = NS * (NS + 1) / 2, QB = 5;   // 45 pairs in batches of five
+  constexpr int NQ = NS * (NS + 1) / 2, QB = NQ % 5 == 0 ? 5 : (NQ % 3 == 0 ? 3 : 1);   // nine species: 45 pairs in batches of five
   static_assert(NQ % QB == 0, "pair batches");
   int s = 0, t = 0;
 #pragma unroll 1

@@ -323,6 +323,26 @@ __device__ __forceinline__ void boundary_fluxes(const ChemC<NS>& cc, const Opts&
 #pragma unroll
   for (int v = 0; v < NV; ++v) d.R[v * d.np + i] = r[v];
 }
+// ---- Viscous_Residual (:5283-5397) for the species counts the pair kernel is not laid out for: one thread per edge, the serial
+// form of the same arithmetic (viscous_flux<NS, EDGE = true>: CAvgGradReactive_Flow::ComputeResidual with the edge correction)
+template <int NS, bool RANS>
+__global__ void __launch_bounds__(EDGE_BS) k_edge_visc_generic(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= d.nEdge) return;
+  constexpr int NV = 4 + NS;
+  const int i = d.ei[e], j = d.ej[e];
+  ViscEnd<NS> I, J;
+  load_visc_end<NS>(d, o, i, I, true);
+  load_visc_end<NS>(d, o, j, J, true);
+  extern __shared__ double smat[];
+  const double sigma_k = RANS ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
+  double res[NV];
+  viscous_flux<NS, true, EDGE_BS, RANS>(cc, o, I, J, d.enx[e], d.eny[e], sigma_k, smat + threadIdx.x, res);
+#pragma unroll
+  for (int v = 0; v < NV; ++v) d.fluxV[v * d.ne + e] = res[v];
+  if (d.eKey) d.eKey[e] = 0;
+}
+
 // BC_Inlet, case TEMPERATURE_IMPOSE (solver_direct_reactive.cpp:3226-3674, :3467-3500)
 template <int NS>
 __global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {

@@ -325,6 +325,16 @@ __device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* 
   }
 }
 
+// upper-triangle index of entry (r, c) of the symmetric 1/D array (tri_idx of rx_flux.cuh with the smaller index first)
+struct TriQ { int q[81]; };
+constexpr TriQ make_triq() {
+  TriQ t{};
+  for (int r = 0; r < 9; ++r)
+    for (int c = 0; c < 9; ++c) { const int a = r < c ? r : c, b = r < c ? c : r; t.q[r * 9 + c] = a * 9 - a * (a - 1) / 2 + (b - a); }
+  return t;
+}
+__constant__ TriQ c_triq = make_triq();
+
 template <int NS, bool RANS>
 #ifdef RX_VP_MAXNREG   // explicit register cap instead of a resident-block target (tuning hook)
 __global__ void __maxnreg__(RX_VP_MAXNREG) k_edge_visc_pair(
@@ -351,6 +361,29 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
 #pragma unroll
   for (int k = 0; k < 4; ++k) row[k] = 2 * k + l;
   row[4] = 8;
+  const double* rdi = d.rD + pi;
+  const double* rdj = d.rD + pj;
+#ifdef RX_VP_ASYNC_D
+  // 1/D_rc of the two end points for the Stefan–Maxwell slot being assembled, fetched one slot ahead by asynchronous copies straight
+  // into 18 thread-private shared-memory words (cp.async: no registers are held across the division batches of the current slot).
+  // Slot 0 is requested HERE, before anything else of the edge is loaded, so that its latency lies under the mean state and the
+  // gradients; the upper-triangle index of (row, column) comes from a constant table (one LDC + one IMAD.WIDE per address).
+  const unsigned npB = (unsigned)(np * 8);   // np < 2^29 points
+  auto stageD = [&](int w) -> double* { return sm + (VP_SMW - 2 * NS + w) * VP_BS; };
+  auto fetchD = [&](int k) {
+    const int r = k < 4 ? 2 * k + l : 8;
+    const int* tq = c_triq.q + r * NS;
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+      const unsigned long long off = (unsigned long long)(unsigned)tq[c] * npB;
+      const unsigned sa = (unsigned)__cvta_generic_to_shared(stageD(c)), sb = (unsigned)__cvta_generic_to_shared(stageD(NS + c));
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"((const char*)rdi + off) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sb), "l"((const char*)rdj + off) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  fetchD(0);
+#endif
 
   // ---- mean state, both lanes
   const double rho = 0.5 * (d.V[V_RHO * np + pi] + d.V[V_RHO * np + pj]);
@@ -506,8 +539,6 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
     for (int s = 0; s < NS; ++s) massTot += yom9[s];
     massTot = 1.0 / massTot;
     const double smm = -sigma * massTot;
-    const double* rdi = d.rD + pi;
-    const double* rdj = d.rD + pj;
     double maxD = 0.0;
     double Xrow[5], Yrow[5];
 #pragma unroll
@@ -516,24 +547,7 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
     bool inOk = mid_range(rho);   // rho and the mole fractions enter every quotient of the assembly
 #pragma unroll
     for (int s = 0; s < NS; ++s) inOk = inOk && num_range(Xs[s]);
-#ifdef RX_VP_ASYNC_D
-    // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead by asynchronous copies straight into
-    // 18 thread-private shared-memory words (cp.async: no registers are held across the division batches of the current slot)
-    auto stageD = [&](int w) -> double* { return sm + (VP_SMW - 2 * NS + w) * VP_BS; };
-    auto fetchD = [&](int k) {
-      const int r = k < 4 ? 2 * k + l : 8;
-      const int base_r = r * NS - r * (r - 1) / 2 - r;
-#pragma unroll
-      for (int c = 0; c < NS; ++c) {
-        const int up = c * NS - c * (c - 1) / 2 - c + r;
-        const size_t q = (size_t)(c >= r ? base_r + c : up) * np;
-        const unsigned sa = (unsigned)__cvta_generic_to_shared(stageD(c)), sb = (unsigned)__cvta_generic_to_shared(stageD(NS + c));
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(rdi + q) : "memory");
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sb), "l"(rdj + q) : "memory");
-      }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-#else
+#ifndef RX_VP_ASYNC_D
     double ra[NS], rb[NS];   // 1/D_rc of the two end points for the slot being assembled, fetched one slot ahead
     auto fetchD = [&](int k) {
       const int r = k < 4 ? 2 * k + l : 8;
@@ -547,8 +561,8 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
         ra[c] = rdi[q]; rb[c] = rdj[q];
       }
     };
-#endif
     fetchD(0);
+#endif
 #pragma unroll 1
     for (int k = 0; k < 5; ++k) {
       const int r = k < 4 ? 2 * k + l : 8;
@@ -609,6 +623,9 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
 #pragma unroll
     for (int k = 0; k < 5; ++k) { const double dg = smA(k, row[k]); invd[k] = dg != 0.0 ? 1.0 / dg : 1.0; }
   }
+#ifdef RX_VP_ASYNC_D
+  asm volatile("cp.async.wait_group 0;" ::: "memory");   // a warp that skipped the assembly still has slot 0's copies in flight
+#endif
   // rows of the first VP_MREG slots move to registers; their shared-memory words then hold rhs, r0 and x of the solve
   double A[VP_MREG > 0 ? VP_MREG : 1][NS];
 #pragma unroll

@@ -84,7 +84,10 @@ def derive_cfg(src, dst, repl):
     open(dst, "w").writelines(out)
 
 
-def prepare_case_dir(name, shipped_mesh=False, nx=0, ny=0, stretch=1.0):
+FLATPLATE = os.path.join(REF, "Test_Cases", "TURBOLENT", "TURBOLENT_FLAT_PLATE")
+
+
+def prepare_case_dir(name, shipped_mesh=False, nx=0, ny=0, stretch=1.0, other_mixture=False):
     d = os.path.join(CASES, name)
     os.makedirs(d, exist_ok=True)
     for sub in ["Chemistry", "Mixture", "Thermo", "Transp"]:
@@ -92,6 +95,12 @@ def prepare_case_dir(name, shipped_mesh=False, nx=0, ny=0, stretch=1.0):
             shutil.copytree(os.path.join(SHIPPED, sub), os.path.join(d, sub))
     for f in ["test_chem_first.txt", "test_chem_second.txt", "test_no_chem.txt"]:
         shutil.copy(os.path.join(SHIPPED, f), d)
+    if other_mixture:   # the reference's other two mixtures (TURBOLENT_FLAT_PLATE): 3-species air (the shipped flat-plate cfg) and 5 species
+        for sub in ["Mixture", "Thermo", "Transp"]:
+            for f in os.listdir(os.path.join(FLATPLATE, sub)):
+                shutil.copy(os.path.join(FLATPLATE, sub, f), os.path.join(d, sub, f))
+        for f in ["test_air.txt", "test.txt"]:
+            shutil.copy(os.path.join(FLATPLATE, f), d)
     if shipped_mesh:
         shutil.copy(os.path.join(SHIPPED, "mesh_stretched.su2"), d)
     else:
@@ -173,6 +182,24 @@ SPECS = {
     # (IGNITION_ITER= 2, solver_direct_reactive.cpp:1013-1024)
     "channel_rans_ign": (dict(nx=41, ny=21, stretch=1.5),
                          dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="3", IGNITION="YES", IGNITION_ITER="2", CFL_NUMBER="0.02"), 3, 1, 47, True),
+    # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
+    # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
+    "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),
+                         dict(CHANNEL_MARKERS, CONFIG_LIB_FILE="test_air.txt", FREESTREAM_MASS_FRAC="(0.2197, 0.0302, 0.7501)",
+                              SPECIES_ORDER="(O2, CO2, N2)", INLET_MASS_FRAC="(inlet, 0.2197, 0.0302, 0.7501)", FUEL_INDEX="1", OXIDIZER_INDEX="0",
+                              RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                              TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.2"), 2, 1, 53, False),
+    # the same mixture, RANS (SST closure with a 3 x 3 molar->mass operator)
+    "channel_air3_rans": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),
+                          dict(CHANNEL_MARKERS, CONFIG_LIB_FILE="test_air.txt", FREESTREAM_MASS_FRAC="(0.2197, 0.0302, 0.7501)",
+                               SPECIES_ORDER="(O2, CO2, N2)", INLET_MASS_FRAC="(inlet, 0.2197, 0.0302, 0.7501)", FUEL_INDEX="1", OXIDIZER_INDEX="0",
+                               RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO"), 2, 1, 59, False),
+    # 5 species (C4H6, H2O, O2, CO, CO2; test.txt), laminar, MUSCL + Venkatakrishnan
+    "channel_mix5_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),
+                         dict(CHANNEL_MARKERS, CONFIG_LIB_FILE="test.txt", FREESTREAM_MASS_FRAC="(0.0, 0.0, 1.0, 0.0, 0.0)",
+                              SPECIES_ORDER="(C4H6, H2O, O2, CO, CO2)", INLET_MASS_FRAC="(inlet, 0.0, 0.0, 1.0, 0.0, 0.0)",
+                              RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                              SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="VENKATAKRISHNAN", CFL_NUMBER="0.2"), 2, 1, 61, False),
 }
 
 

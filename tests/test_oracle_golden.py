@@ -15,7 +15,9 @@ import pytest
 from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 
 CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler", "channel_rans_gg",
-         "channel_lam_edge", "channel_lam_clip", "channel_rans_ign"]
+         "channel_lam_edge", "channel_lam_clip", "channel_rans_ign",
+         # species-count generality: the reference's other two mixtures (TURBOLENT_FLAT_PLATE): 3-species air laminar / RANS, 5 species MUSCL
+         "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam"]
 TOL = 0.0
 
 
