@@ -611,6 +611,8 @@ def main():
         del gm, part
     elif world > 1:
         mesh, plan = pk.channel_strip_mesh(nxg, a.ny, rank, world)
+        if a.strong:   # narrow strips: number the points with the short side slow, which shortens the level chains of the SST step's sweeps
+            mesh, plan = pk.strip_short_side_slow(mesh, plan)
     else:
         mesh = pk.channel_mesh(nxg, a.ny); plan = dict(send={}, recv={}, bbox=None)
     t_mesh = time.perf_counter() - t_mesh

@@ -1136,9 +1136,10 @@ int rx_source_points(const rx_chem* ch, int rans, double cMu, double pasrLb, int
   if (!rx_supported_species(ch->Ns) || ch->Nr > NRMAX) { g_create_error = "rx_source_points: unsupported mechanism size"; return RX_ERR_UNSUPPORTED; }
   rx_ctx tmp; rx_ctx* c = &tmp;
   c->device = device;
+  const int Ns = ch->Ns;
+  c->Ns = Ns;   // the species-count dispatch of the launch below reads it
   RX_CK(cudaSetDevice(device));
   int rc = fill_chem(c, ch);
-  const int Ns = ch->Ns;
   double *dT = dalloc<double>(c, n), *dr = dalloc<double>(c, n), *dY = dalloc<double>(c, n * Ns), *dO = dalloc<double>(c, n),
          *dV = dalloc<double>(c, n), *dR = dalloc<double>(c, n * Ns), *dA = dalloc<double>(c, n * Ns);
   if (rc == RX_OK && !(dT && dr && dY && dO && dV && dR && dA)) rc = RX_ERR_CUDA;

@@ -17,7 +17,8 @@ HARNESS_CPU = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 # name -> (iterations, seed)   (oracle/make_golden.py SPECS)
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
-        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37)}
+        "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37),
+        "channel_air3_rans": (2, 59), "channel_mix5_lam": (2, 61)}   # the reference's 3- and 5-species mixtures
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-12   # later iterations too: with the glibc-exact exp / pow (csrc/rx_libm.cuh) the laminar chains are bit-identical
 TOL_FIRST_BY_CASE = {}
@@ -36,7 +37,7 @@ def _run(binary, d, out, nit, seed, env):
 # conditions, FGMRES + LU-SGS, update, Postprocessing) runs on the device (rx_turb_iterate); the reference's driver and integration
 # classes still drive both solvers
 PARAMS = [(n, False, False) for n in RUNS] + [("channel_rans", True, False), ("jet_rans_perturbed", True, False), ("channel_rans_gg", True, False)] + \
-         [("channel_rans", False, True), ("jet_rans_perturbed", False, True), ("channel_rans_gg", False, True)]
+         [("channel_rans", False, True), ("jet_rans_perturbed", False, True), ("channel_rans_gg", False, True), ("channel_air3_rans", False, True)]
 
 
 @pytest.mark.parametrize("name,turb_post,turb_dev", PARAMS)

@@ -94,3 +94,35 @@ def test_strip_meshes_tile_the_global_mesh(pk, nranks):
     assert counted_edges == len(g["edgeNodes"])
     nb = sum(len(pk.channel_strip_mesh(nxg, ny, r, nranks)[0]["markers"][k]["node"]) for r in range(nranks) for k in range(4))
     assert nb == sum(len(mk["node"]) for mk in g["markers"])
+
+
+def test_strip_renumbering_short_side_slow_is_the_same_mesh_with_shorter_sweep_chains():
+    """strip_short_side_slow: same points, edges, markers and exchange lists under another numbering; the dependency levels of a
+    Gauss-Seidel sweep in index order (what rx_turb_iterate's LU-SGS follows) drop from about nx + 2 ny to ny + 2 nx."""
+    import numpy as np
+    from rxcase import load_package
+    pk = load_package()
+    m, plan = pk.channel_strip_mesh(160, 101, 1, 8)
+    m2, p2 = pk.strip_short_side_slow(m, plan)
+    n = m["nPointDomain"]
+    assert m2["nPointDomain"] == n and m2["nPoint"] == m["nPoint"] and m2["nEdge"] == m["nEdge"]
+    key = lambda mm, pp: {(int(a), int(b)) for a, b in zip(pp["glob"][0] * 1000 + pp["glob"][1], range(len(pp["glob"][0])))}
+    ga, gb = plan["glob"][0] * 1000 + plan["glob"][1], p2["glob"][0] * 1000 + p2["glob"][1]
+    assert sorted(ga[:n]) == sorted(gb[:n]) and list(ga[n:]) == list(gb[n:])            # owned set kept, halo layer untouched
+    o = {int(g): i for i, g in enumerate(ga)}
+    perm = np.array([o[int(g)] for g in gb])                                             # new -> old
+    assert np.array_equal(m2["coord"], m["coord"][perm]) and np.array_equal(m2["volume"], m["volume"][perm])
+    ea = {(int(ga[a]), int(ga[b])) for a, b in m["edgeNodes"]}; eb = {(int(gb[a]), int(gb[b])) for a, b in m2["edgeNodes"]}
+    assert ea == eb
+    for r in plan["send"]:
+        assert list(ga[plan["send"][r]]) == list(gb[p2["send"][r]]) and list(ga[plan["recv"][r]]) == list(gb[p2["recv"][r]])
+
+    def levels(mm):
+        ptr, nb = mm["nbPtr"], mm["nbPoint"]
+        lev = np.zeros(n, dtype=np.int64)
+        for p in range(n):
+            q = nb[ptr[p]:ptr[p + 1]]; q = q[q < p]
+            lev[p] = lev[q].max() + 1 if len(q) else 0
+        return int(lev.max()) + 1
+    la, lb = levels(m), levels(m2)
+    assert lb < 0.7 * la, (la, lb)
