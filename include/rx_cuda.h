@@ -118,7 +118,12 @@ int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the 
  * CAvgGradCorrected_TurbSST, CSourcePieceWise_TurbSST), BC_Inlet / BC_Outlet / BC_HeatFlux_Wall / BC_Isothermal_Wall (:3087-3450),
  * ImplicitEuler_Iteration (:615: FGMRES + LU-SGS of Common/src/linear_solvers_structure.cpp:309 and matrix_structure.cpp, clipped
  * conservative update) and Postprocessing — on the flow state the last rx_iterate / rx_preprocess left (primitives, gradients,
- * time steps, the boundary states of the inlet / outlet markers).  First-order upwind (SPATIAL_ORDER_TURB default), single partition.
+ * time steps, the boundary states of the inlet / outlet markers).  First-order upwind (SPATIAL_ORDER_TURB default).  On a partition
+ * (a context with halo points) the step needs the library's communicator (rx_comm_init) and performs the reference's MPI steps over
+ * NCCL on the context's stream: Set_MPI_Solution_Gradient after Preprocessing and Postprocessing (solver_direct_turbulent.cpp:227), the
+ * neighbours' x* between the two LU-SGS sweeps and the preconditioned vector after them (CSysMatrix::SendReceive_Solution,
+ * matrix_structure.cpp:1689, 1707), Set_MPI_Solution of (k, omega) after the update (:707), one all-reduce per inner product and for
+ * the residual norms (dotProd, vector_structure.cpp:397-419); every rank must call it.
  * rx_turb_set_state: the turbulence solution (k, omega) [nPoint][2] and, optionally, F1, F2, CDkw [nPoint][3] of the previous
  * Postprocessing (a restart or a test hands them over; in a run they stay resident).  rx_turb_get_step: LinSysRes before the solve
  * and the solution of the linear system of the last step (parity tests).  resRms2 / linIters may be NULL. */
@@ -176,7 +181,7 @@ int rx_source_points_dev(rx_ctx*, int64_t n, const double* T_dev, const double* 
                          const double* omegaTurb_dev, const double* vol_dev, double* res_dev /* [Ns][n] SoA */);
 
 /* halo exchange plumbing for one-process-per-GPU runs (replaces Set_MPI_Solution :1530, Set_MPI_Primitive_Gradient :1877):
- * pack `what` (0 = conserved U, 1 = primitive gradients, 2 = limiters of T,u,v,P: Set_MPI_Primitive_Limiter :1756, 3 = grad k and grad omega of rx_turb_postprocess: Set_MPI_Solution_Gradient solver_direct_turbulent.cpp:227) of the listed points into buf_dev[nVarOfWhat][n],
+ * pack `what` (0 = conserved U, 1 = primitive gradients, 2 = limiters of T,u,v,P: Set_MPI_Primitive_Limiter :1756, 3 = grad k and grad omega of rx_turb_postprocess: Set_MPI_Solution_Gradient solver_direct_turbulent.cpp:227, 4 = the turbulence solution k, omega: CTurbSolver::Set_MPI_Solution :111) of the listed points into buf_dev[nVarOfWhat][n],
  * or unpack into them; the transport in between (NCCL send/recv) belongs to the caller. */
 int rx_halo_pack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, double* buf_dev);
 int rx_halo_unpack(rx_ctx*, int what, int64_t n, const int64_t* points_dev, const double* buf_dev);
@@ -189,7 +194,7 @@ int rx_halo_width(rx_ctx*, int what);
  *                       sendPoints[sendPtr[k] .. sendPtr[k+1]) go out and recvPoints[recvPtr[k] .. recvPtr[k+1]) (halo points) come in, in the
  *                       order both sides agreed on — the vertex order of the SEND_RECEIVE marker pair in SU2 (geometry->vertex[MarkerS/R]).
  *   rx_halo_exchange  : Set_MPI_Solution (what 0, solver_direct_reactive.cpp:1530), Set_MPI_Primitive_Gradient (1, :1877),
- *                       Set_MPI_Primitive_Limiter (2, :1756), Set_MPI_Solution_Gradient of (k, omega) (3): pack, grouped ncclSend/ncclRecv,
+ *                       Set_MPI_Primitive_Limiter (2, :1756), Set_MPI_Solution_Gradient of (k, omega) (3), Set_MPI_Solution of (k, omega) (4): pack, grouped ncclSend/ncclRecv,
  *                       unpack — enqueued on the context's stream, no host synchronisation.  rx_iterate calls it at the reference's points
  *                       once a communicator exists, and returns the norms of the whole job.
  *   rx_comm_allreduce_rms : residual norms of the whole job from every partition's sums of squares of the last rx_update_explicit
