@@ -406,6 +406,25 @@ void CReactiveNSSolverGPU::WriteRestart(CGeometry* geometry, CSolver** solver_co
   Check(rx_restart_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, &info, 0), "rx_restart_write");
 }
 
+// COutput::SetTecplotASCII for the volume solution (output_tecplot.cpp:46-420) straight from the device state: triangles of the
+// (single-partition) geometry in element order, global point indices as MergeConnectivity writes them (:881)
+void CReactiveNSSolverGPU::WriteTecplot(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename) {
+  std::vector<int64_t> gi(nPoint), tria, quad;
+  for (unsigned long p = 0; p < nPoint; ++p) gi[p] = (int64_t)geometry->node[p]->GetGlobalIndex();
+  for (unsigned long e = 0; e < geometry->GetnElem(); ++e) {
+    const unsigned short vtk = geometry->elem[e]->GetVTK_Type();
+    if (vtk != TRIANGLE && vtk != QUADRILATERAL) throw std::runtime_error("CReactiveNSSolverGPU::WriteTecplot: 2-D meshes of triangles and quadrilaterals only");
+    std::vector<int64_t>& dst = vtk == TRIANGLE ? tria : quad;
+    for (unsigned short k = 0; k < (vtk == TRIANGLE ? 3 : 4); ++k) dst.push_back((int64_t)geometry->node[geometry->elem[e]->GetNode(k)]->GetGlobalIndex());
+  }
+  std::vector<double> kw;
+  if (ransMode) {
+    kw.resize((size_t)nPoint * 2);
+    for (unsigned long p = 0; p < nPoint; ++p) { kw[2 * p] = solver_container[TURB_SOL]->node[p]->GetSolution(0); kw[2 * p + 1] = solver_container[TURB_SOL]->node[p]->GetSolution(1); }
+  }
+  Check(rx_tecplot_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, (int64_t)(tria.size() / 3), tria.data(), (int64_t)(quad.size() / 4), quad.data()), "rx_tecplot_write");
+}
+
 void CReactiveNSSolverGPU::SetTurbulenceOnDevice(const double* post12) {
   turbOnDevice = true;
   for (unsigned long p = 0; p < nPoint; ++p) {

@@ -60,6 +60,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   // MergeSolution + SetRestart produce (output_structure.cpp:1991-2130, 3858-4060) without mirroring the state into node[].
   // One call in COutput::SetResult_Files replaces the pair for a CReactiveNSSolverGPU flow solver.
   void WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);
+  void WriteTecplot(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);   // rx_tecplot_write
 
   // node[]->Solution was changed on the host (restart, initial condition): upload before the next stage
   void MarkHostSolutionDirty() { hostDirty = true; turbOnDevice = false; }   // the turbulence fields are taken from the host again, too

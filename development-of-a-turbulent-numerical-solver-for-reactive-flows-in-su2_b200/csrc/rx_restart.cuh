@@ -45,15 +45,16 @@ __global__ void k_restart_gather(const Dev d, const double* __restrict__ eddyFlo
   if (rans) out[(f++) * n + t] = eddyFlow[p];   // eddy viscosity as the flow variable holds it (set at the last Preprocessing), not the turbulence solver's newer one
 }
 
-inline void restart_format(const double* buf, long long n, int nf, const long long* ids, std::string& out) {
+// tecplot: no PointID column and the stream's default precision (C++ `scientific` = printf "%e"), COutput::SetTecplotASCII (output_tecplot.cpp:299-318)
+inline void restart_format(const double* buf, long long n, int nf, const long long* ids, bool tecplot, std::string& out) {
   char tmp[64];
   out.clear();
   out.reserve((size_t)n * (nf * 23 + 12));
   for (long long t = 0; t < n; ++t) {
-    int m = snprintf(tmp, sizeof tmp, "%lld\t", ids[t]);
-    out.append(tmp, m);
+    int m;
+    if (!tecplot) { m = snprintf(tmp, sizeof tmp, "%lld\t", ids[t]); out.append(tmp, m); }
     for (int f = 0; f < nf; ++f) {
-      m = snprintf(tmp, sizeof tmp, "%.15e\t", buf[(size_t)f * n + t]);
+      m = snprintf(tmp, sizeof tmp, tecplot ? "%e\t" : "%.15e\t", buf[(size_t)f * n + t]);
       out.append(tmp, m);
     }
     out.push_back('\n');
@@ -62,13 +63,11 @@ inline void restart_format(const double* buf, long long n, int nf, const long lo
 
 }  // namespace rx
 
-extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* globalIndex, const double* kOmega, const rx_restart_info* info, int piece) {
+// the per-point lines of a restart (tecplot = false) or Tecplot volume file (true) of the owned points, by ascending PointID
+static int restart_points(rx_ctx* c, FILE* fo, const int64_t* globalIndex, const double* kOmega, bool tecplot) {
   using namespace rx;
-  if (!c || !path) { if (c) c->err = "rx_restart_write: null argument"; return RX_ERR_ARG; }
-  { const int rc = ensure_output(c); if (rc) return rc; }   // laminar viscosity of the Output pass
   const Dev& d = c->d;
   const bool rans = c->o.rans != 0, visc = c->o.viscous != 0;
-  if (rans && !kOmega) { c->err = "rx_restart_write: a RANS restart carries the turbulence solution (k, omega): kOmega must not be NULL"; return RX_ERR_ARG; }
   const long long nOwn = d.nPointDomain;
   const int nCons = c->nVar + (rans ? 2 : 0);
   const int nf = 2 + nCons + 3 + (visc ? 1 : 0) + (rans ? 1 : 0);
@@ -90,23 +89,11 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
       }
     }
   }
-  FILE* fo = fopen(path, "w");
-  if (!fo) { if (dOrder) cudaFree(dOrder); c->err = std::string("rx_restart_write: cannot open ") + path; return RX_ERR_ARG; }
-  if (!piece) {
-    std::string h = "\"PointID\"\t\"x\"\t\"y\"";
-    for (int v = 0; v < nCons; ++v) h += "\t\"Conservative_" + std::to_string(v + 1) + "\"";
-    h += "\t\"Pressure\"\t\"Temperature\"\t\"Mach\"";
-    if (visc) h += "\t\"Laminar_Viscosity\"";
-    if (rans) h += "\t\"<greek>m</greek><sub>t</sub>\"";
-    h += "\n";
-    fwrite(h.data(), 1, h.size(), fo);
-  }
   const long long chunk = std::min<long long>(RST_CHUNK, std::max<long long>(nOwn, 1));
   double *pin = nullptr, *dev = nullptr;
   if (cudaMallocHost((void**)&pin, (size_t)chunk * nf * sizeof(double)) != cudaSuccess || cudaMalloc((void**)&dev, (size_t)chunk * nf * sizeof(double)) != cudaSuccess) {
     if (pin) cudaFreeHost(pin);
     if (dOrder) cudaFree(dOrder);
-    fclose(fo);
     c->err = "rx_restart_write: staging allocation failed"; return RX_ERR_CUDA;
   }
   const int nThreads = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
@@ -135,7 +122,7 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
         const long long m = b - a;
         std::vector<double> loc((size_t)m * nf);
         for (int f = 0; f < nf; ++f) memcpy(&loc[(size_t)f * m], pin + (size_t)f * n + a, (size_t)m * sizeof(double));
-        restart_format(loc.data(), m, nf, ids.data() + a, parts[k]);
+        restart_format(loc.data(), m, nf, ids.data() + a, tecplot, parts[k]);
       });
     }
     for (auto& t : th) t.join();
@@ -144,6 +131,28 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
   }
   cudaFreeHost(pin); cudaFree(dev);
   if (dOrder) cudaFree(dOrder);
+  return rc;
+}
+
+extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* globalIndex, const double* kOmega, const rx_restart_info* info, int piece) {
+  using namespace rx;
+  if (!c || !path) { if (c) c->err = "rx_restart_write: null argument"; return RX_ERR_ARG; }
+  { const int rc = ensure_output(c); if (rc) return rc; }   // laminar viscosity of the Output pass
+  const bool rans = c->o.rans != 0, visc = c->o.viscous != 0;
+  if (rans && !kOmega) { c->err = "rx_restart_write: a RANS restart carries the turbulence solution (k, omega): kOmega must not be NULL"; return RX_ERR_ARG; }
+  const int nCons = c->nVar + (rans ? 2 : 0);
+  FILE* fo = fopen(path, "w");
+  if (!fo) { c->err = std::string("rx_restart_write: cannot open ") + path; return RX_ERR_ARG; }
+  if (!piece) {
+    std::string h = "\"PointID\"\t\"x\"\t\"y\"";
+    for (int v = 0; v < nCons; ++v) h += "\t\"Conservative_" + std::to_string(v + 1) + "\"";
+    h += "\t\"Pressure\"\t\"Temperature\"\t\"Mach\"";
+    if (visc) h += "\t\"Laminar_Viscosity\"";
+    if (rans) h += "\t\"<greek>m</greek><sub>t</sub>\"";
+    h += "\n";
+    fwrite(h.data(), 1, h.size(), fo);
+  }
+  int rc = restart_points(c, fo, globalIndex, kOmega, false);
   if (rc == RX_OK && !piece) {
     rx_restart_info z{};
     z.bcThrust = 4000.0;   // CConfig default of INITIAL_BCTHRUST
@@ -152,6 +161,48 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
             (long long)q.extIter);
   }
   if (fclose(fo) != 0 && rc == RX_OK) { c->err = "rx_restart_write: close failed"; rc = RX_ERR_ARG; }
+  return rc;
+}
+
+// Tecplot ASCII volume solution file (COutput::SetTecplotASCII, SU2_CFD/src/output_tecplot.cpp:46-420, for the reactive solvers): title,
+// the VARIABLES line exactly as the reference prints it (for REACTIVE_RANS it names more variables than it writes, :163-178 — kept,
+// the file is what SU2 users' scripts read), the ZONE line (2-D volume zones are FEQUADRILATERAL, triangles repeat their third node),
+// one line per point — x, y and the restart file's columns, default `scientific` precision — then the 1-based connectivity, all triangles
+// before all quadrilaterals as MergeConnectivity collects them (output_structure.cpp:881).
+extern "C" int rx_tecplot_write(rx_ctx* c, const char* path, const int64_t* globalIndex, const double* kOmega, int64_t nTria, const int64_t* tria,
+                                int64_t nQuad, const int64_t* quad) {
+  using namespace rx;
+  if (!c || !path || (nTria > 0 && !tria) || (nQuad > 0 && !quad) || nTria < 0 || nQuad < 0) { if (c) c->err = "rx_tecplot_write: bad argument"; return RX_ERR_ARG; }
+  if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_tecplot_write: one partition holds part of the zone only; merge restart pieces and post-process (SU2_SOL) instead"; return RX_ERR_UNSUPPORTED; }
+  { const int rc = ensure_output(c); if (rc) return rc; }
+  const bool rans = c->o.rans != 0, visc = c->o.viscous != 0;
+  if (rans && !kOmega) { c->err = "rx_tecplot_write: a RANS file carries the turbulence solution (k, omega): kOmega must not be NULL"; return RX_ERR_ARG; }
+  const int nCons = c->nVar + (rans ? 2 : 0);
+  FILE* fo = fopen(path, "w");
+  if (!fo) { c->err = std::string("rx_tecplot_write: cannot open ") + path; return RX_ERR_ARG; }
+  std::string h = "TITLE = \"Visualization of the volumetric solution\"\nVARIABLES = \"x\",\"y\"";
+  for (int v = 0; v < nCons; ++v) h += ",\"Conservative_" + std::to_string(v + 1) + "\"";
+  h += ",\"Pressure\",\"Temperature\",\"Mach\"";
+  if (visc) h += ", \"<greek>m</greek>\"";
+  if (rans) h += ",\"Pressure\",\"Temperature\",\"C<sub>p</sub>\",\"Mach\", \"<greek>m</greek>\", \"C<sub>f</sub>_x\", \"C<sub>f</sub>_y\", \"h\", \"y<sup>+</sup>\", \"<greek>m</greek><sub>t</sub>\"";
+  h += "\nZONE NODES= " + std::to_string((long long)c->d.nPointDomain) + ", ELEMENTS= " + std::to_string((long long)(nTria + nQuad)) + ", DATAPACKING=POINT, ZONETYPE=FEQUADRILATERAL\n";
+  fwrite(h.data(), 1, h.size(), fo);
+  int rc = restart_points(c, fo, globalIndex, kOmega, true);
+  if (rc == RX_OK) {
+    std::string body;
+    body.reserve((size_t)(nTria + nQuad) * 32);
+    char tmp[96];
+    for (int64_t e = 0; e < nTria; ++e) {
+      const int m = snprintf(tmp, sizeof tmp, "%lld\t%lld\t%lld\t%lld\n", (long long)tria[3 * e] + 1, (long long)tria[3 * e + 1] + 1, (long long)tria[3 * e + 2] + 1, (long long)tria[3 * e + 2] + 1);
+      body.append(tmp, m);
+    }
+    for (int64_t e = 0; e < nQuad; ++e) {
+      const int m = snprintf(tmp, sizeof tmp, "%lld\t%lld\t%lld\t%lld\n", (long long)quad[4 * e] + 1, (long long)quad[4 * e + 1] + 1, (long long)quad[4 * e + 2] + 1, (long long)quad[4 * e + 3] + 1);
+      body.append(tmp, m);
+    }
+    if (fwrite(body.data(), 1, body.size(), fo) != body.size()) { c->err = "rx_tecplot_write: short write"; rc = RX_ERR_ARG; }
+  }
+  if (fclose(fo) != 0 && rc == RX_OK) { c->err = "rx_tecplot_write: close failed"; rc = RX_ERR_ARG; }
   return rc;
 }
 

@@ -104,7 +104,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read",
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -432,6 +432,15 @@ class CReactiveNSSolverGPU:
         gi = _c(globalIndex, np.int64) if globalIndex is not None else None
         self._ck(self.lib.rx_restart_write(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, _d(kw) if kw is not None else None,
                                            C.byref(info), int(bool(piece))))
+
+    def WriteTecplot(self, path, triangles, kOmega=None, globalIndex=None, quads=None):
+        """COutput::SetTecplotASCII (volume solution) from the device state (rx_tecplot_write); triangles [nTria][3], quads [nQuad][4], 0-based."""
+        kw = _c(kOmega) if kOmega is not None else None
+        gi = _c(globalIndex, np.int64) if globalIndex is not None else None
+        tr = _c(triangles if triangles is not None else np.zeros((0, 3)), np.int64).reshape(-1, 3)
+        qd = _c(quads if quads is not None else np.zeros((0, 4)), np.int64).reshape(-1, 4)
+        self._ck(self.lib.rx_tecplot_write(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, _d(kw) if kw is not None else None,
+                                           C.c_int64(tr.shape[0]), _i(tr) if tr.shape[0] else None, C.c_int64(qd.shape[0]), _i(qd) if qd.shape[0] else None))
 
     def LoadRestart(self, path, globalIndex=None, nGlobal=0):
         """CReactiveNSSolver::Load_Restart + the turbulence reader (rx_restart_read): sets the conserved state from the file; returns

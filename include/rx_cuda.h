@@ -256,6 +256,13 @@ int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, con
  * kOmega (may be NULL) receives (k, omega); fails with the reference's message if the file does not cover the owned points. */
 typedef struct { double aoa, sideslip, bcThrust, dCD_dCL; int64_t extIter; } rx_restart_info;
 int rx_restart_write(rx_ctx*, const char* path, const int64_t* globalIndex, const double* kOmega, const rx_restart_info* info /* NULL: zeros, INITIAL_BCTHRUST 4000 */, int piece);
+/* rx_tecplot_write replaces COutput::SetTecplotASCII for the volume solution of the reactive solvers (SU2_CFD/src/output_tecplot.cpp:46-420,
+ * fed by MergeConnectivity / MergeSolution): title, the VARIABLES line as the reference prints it, the ZONE line, one line per point
+ * (x, y and the restart file's columns in C++ `scientific` with the stream's default precision) and the 1-based connectivity of the
+ * nTria triangles tria[nTria][3] (point indices in the numbering of globalIndex, or local if NULL).  Single partition (a partition
+ * writes a restart piece; the merged restart goes through SU2_SOL).  Byte-identical to the reference's file for the laminar case. */
+int rx_tecplot_write(rx_ctx*, const char* path, const int64_t* globalIndex, const double* kOmega, int64_t nTria, const int64_t* tria,
+                     int64_t nQuad, const int64_t* quad /* [nQuad][4], written after the triangles */);
 int rx_restart_read(rx_ctx*, const char* path, const int64_t* globalIndex, int64_t nGlobal /* points in the file; <= 0: nPointDomain */, double* kOmega, rx_restart_info* info /* may be NULL */);
 
 /* measurement hook (no reference counterpart): save (restore = 0) or restore (restore = 1) the evolving state of the context — U,

@@ -295,11 +295,14 @@ def run_restart_files():
         out = os.path.join(d, "dump_rst")
         shutil.rmtree(out, ignore_errors=True)
         cmd = [HARNESS, "case.cfg", str(nit), out, str(10 ** 9)] + ([str(seed)] if seed is not None else [])
-        log = subprocess.run(cmd, cwd=d, env=dict(os.environ, RX_RESTART_OUT="1", **ENVS.get(name, {})), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        log = subprocess.run(cmd, cwd=d, env=dict(os.environ, RX_RESTART_OUT="1", RX_TECPLOT_OUT="1", **ENVS.get(name, {})), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if log.returncode != 0 or "HARNESS wrote" not in log.stdout:
             raise RuntimeError("harness failed for %s:\n%s" % (name, log.stdout[-2000:]))
         arrs[name] = np.frombuffer(open(os.path.join(d, "restart_flow.dat"), "rb").read(), dtype=np.uint8)
         os.remove(os.path.join(d, "restart_flow.dat"))
+        # the Tecplot ASCII volume file of the same state (COutput::SetTecplotASCII): golden bytes for rx_tecplot_write
+        arrs[name + "_tecplot"] = np.frombuffer(open(os.path.join(d, "flow.dat"), "rb").read(), dtype=np.uint8)
+        os.remove(os.path.join(d, "flow.dat"))
         shutil.rmtree(out, ignore_errors=True)
     path = os.path.join(GOLDEN, "restart_files.npz")
     np.savez_compressed(path, **arrs)

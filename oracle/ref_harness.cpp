@@ -609,10 +609,16 @@ int main(int argc, char** argv) {
     out->MergeSolution(c.cfg, c.geo, c.sol, ZONE_0);
     out->SetRestart(c.cfg, c.geo, c.sol, ZONE_0);
     printf("HARNESS wrote %s\n", c.cfg->GetRestart_FlowFileName().c_str());
+    if (getenv("RX_TECPLOT_OUT")) {   // the volume solution file as well: MergeConnectivity + SetTecplotASCII (output_tecplot.cpp:46-420), "flow.dat"
+      out->MergeConnectivity(c.cfg, c.geo, ZONE_0);
+      out->SetTecplotASCII(c.cfg, c.geo, c.sol, ZONE_0, 1, false);
+      printf("HARNESS wrote %s.dat\n", c.cfg->GetFlow_FileName().c_str());
+    }
 #ifdef RX_WITH_GPU
     if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) {   // the same file straight from the device state
       g->WriteRestart(c.geo, c.sol, c.cfg, "restart_flow_gpu.dat");
       printf("HARNESS wrote restart_flow_gpu.dat (rx_restart_write)\n");
+      if (getenv("RX_TECPLOT_OUT")) { g->WriteTecplot(c.geo, c.sol, c.cfg, "flow_gpu.dat"); printf("HARNESS wrote flow_gpu.dat (rx_tecplot_write)\n"); }
     }
 #endif
   }

@@ -47,7 +47,7 @@ def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
         pytest.skip("oracle/_ref harnesses or the case directory are not in this snapshot (built by oracle/build_ref.sh where the reference tree is present)")
     nit, seed = RUNS[name]
     out_g, out_c = str(tmp_path / "gpu"), str(tmp_path / "cpu")
-    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1",
+    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1", RX_TECPLOT_OUT="1",
                                                      SU2_RX_TURB="device" if turb_dev else "host"))
     assert "CReactiveNSSolverGPU" in txt and (("CTurbSSTSolverGPU" in txt) == turb_dev)
     # restart file: the reference's COutput (fed by the subclass's host mirrors) and the subclass's own device writer, same run
@@ -55,6 +55,10 @@ def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
         a = open(os.path.join(d, "restart_flow.dat"), "rb").read(); b = open(os.path.join(d, "restart_flow_gpu.dat"), "rb").read()
         os.remove(os.path.join(d, "restart_flow.dat")); os.remove(os.path.join(d, "restart_flow_gpu.dat"))
         assert a == b, "rx_restart_write differs from COutput::SetRestart on the same state"
+    if "rx_tecplot_write" in txt:   # likewise the Tecplot volume file: COutput::SetTecplotASCII and the subclass's WriteTecplot
+        a = open(os.path.join(d, "flow.dat"), "rb").read(); b = open(os.path.join(d, "flow_gpu.dat"), "rb").read()
+        os.remove(os.path.join(d, "flow.dat")); os.remove(os.path.join(d, "flow_gpu.dat"))
+        assert a == b, "rx_tecplot_write differs from COutput::SetTecplotASCII on the same state"
     _run(HARNESS_CPU, d, out_c, nit, seed, dict(os.environ))
     case = Case(os.path.join(GOLDEN, name + ".npz"))
     checked, worst = 0, (0.0, "")

@@ -1,9 +1,9 @@
-"""SU2 native restart files from / into the device-resident state (rx_restart_write / rx_restart_read).
+"""SU2 native restart files and the Tecplot volume file from / into the device-resident state (rx_restart_write / rx_restart_read /
+rx_tecplot_write).
 
 Golden bytes: the file the reference's own COutput::MergeSolution + SetRestart (output_structure.cpp:1991-2130, 3858-4060) wrote after
 the last iteration of the stage fixtures channel_lam_rk and channel_rans (tests/golden/restart_files.npz, oracle/make_golden.py).
- * laminar: the device path is bit-identical to the reference, so the file must be IDENTICAL BYTE FOR BYTE;
- * RANS: same header / layout / trailer, every number within 1e-12 (the SST closure differs in the last bits);
+ * the device path is bit-identical to the reference, laminar and RANS, so the files must be IDENTICAL BYTE FOR BYTE;
  * round trip: a file written from the device state is read back by the reference's own Load_Restart + turbulence reader
    (solver_direct_reactive.cpp:4390-4520, solver_direct_turbulent.cpp:1046-1064) through ref_harness and by rx_restart_read;
  * per-partition pieces merged by PointID equal the single-partition file."""
@@ -49,13 +49,40 @@ def test_restart_file_equals_the_reference_writers(name, tmp_path):
     gl, wl = got.decode().split("\n"), want.decode().split("\n")
     assert gl[0] == wl[0], "header line differs"
     assert len(gl) == len(wl) and gl[-6:] == wl[-6:], "line count or trailer differs"
-    if not case.meta["cfg"]["rans"]:
-        assert got == want, "laminar restart file is not byte-identical to the reference's"
+    assert got == want, "restart file is not byte-identical to the reference's"
     a, b = _numbers(got.decode()), _numbers(want.decode())
     assert a.shape == b.shape
     scale = np.abs(b).max(axis=0)
     assert (np.abs(a - b).max(axis=0) <= 1e-12 * np.where(scale > 0, scale, 1.0)).all()
     assert all(len(x) == len(y) for x, y in zip(gl, wl)), "field widths differ"
+
+
+def _channel_triangles(nx, ny):
+    """element list of oracle/make_golden.py: write_channel_su2 (every quad split in two, alternating diagonal)"""
+    idx = lambda i, j: j * nx + i
+    tr = []
+    for j in range(ny - 1):
+        for i in range(nx - 1):
+            a, b, c, d = idx(i, j), idx(i + 1, j), idx(i + 1, j + 1), idx(i, j + 1)
+            tr += [(a, b, c), (a, c, d)] if (i + j) % 2 == 0 else [(a, b, d), (b, c, d)]
+    return np.array(tr, dtype=np.int64)
+
+
+@pytest.mark.parametrize("name", ["channel_lam_rk", "channel_rans"])
+def test_tecplot_file_equals_the_reference_writers(name, tmp_path):
+    """rx_tecplot_write against the bytes of COutput::MergeConnectivity + SetTecplotASCII (output_tecplot.cpp:46-420) after the last
+    iteration of the stage fixture: every state of the path is bit-identical, so the whole file must be IDENTICAL BYTE FOR BYTE
+    (RANS: (k, omega) and the eddy viscosity column come from the reference's turbulence dump, as in the restart test)."""
+    want = bytes(np.load(os.path.join(GOLDEN, "restart_files.npz"))[name + "_tecplot"])
+    case, s, kw, it = _state_at_write(name)
+    path = str(tmp_path / "flow.dat")
+    s.WriteTecplot(path, _channel_triangles(41, 21), kOmega=kw, globalIndex=case["geo_global_index"])
+    got = open(path, "rb").read()
+    s.close()
+    gl, wl = got.decode().split("\n"), want.decode().split("\n")
+    assert gl[:3] == wl[:3], "title / VARIABLES / ZONE lines differ"
+    assert len(gl) == len(wl) and gl[-1601:] == wl[-1601:], "connectivity differs"
+    assert got == want, "Tecplot file is not byte-identical to the reference's"
 
 
 @pytest.mark.parametrize("name", ["channel_lam_rk", "channel_rans"])
