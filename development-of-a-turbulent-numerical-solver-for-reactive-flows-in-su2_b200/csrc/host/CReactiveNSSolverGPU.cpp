@@ -76,8 +76,12 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
     const std::string tag = config->GetMarker_All_TagBound(m);
     switch (config->GetMarker_All_KindBC(m)) {
       case INLET_FLOW:
-        if (config->GetKind_Inlet() != TEMPERATURE_IMPOSE) throw std::runtime_error("CReactiveNSSolverGPU: inlet type other than TEMPERATURE_IMPOSE");
-        r.kind = RX_BC_INLET_TEMPERATURE_IMPOSE;
+        switch (config->GetKind_Inlet()) {   // INLET_TYPE: the three kinds BC_Inlet implements (:3280-3500)
+          case TEMPERATURE_IMPOSE: r.kind = RX_BC_INLET_TEMPERATURE_IMPOSE; break;
+          case TOTAL_CONDITIONS: r.kind = RX_BC_INLET_TOTAL_CONDITIONS; break;
+          case MASS_FLOW: r.kind = RX_BC_INLET_MASS_FLOW; break;
+          default: throw std::runtime_error("CReactiveNSSolverGPU: INLET_TYPE not implemented by the reference's BC_Inlet either");
+        }
         r.T = config->GetInlet_Ttotal(tag); r.Vmag = config->GetInlet_Ptotal(tag);
         r.dir[0] = config->GetInlet_FlowDir(tag)[0]; r.dir[1] = config->GetInlet_FlowDir(tag)[1];
         for (unsigned short s = 0; s < nSpecies; ++s) vys[m][s] = config->GetInlet_MassFrac(tag)[s];

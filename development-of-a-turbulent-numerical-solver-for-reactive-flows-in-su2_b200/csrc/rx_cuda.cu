@@ -25,6 +25,7 @@ static constexpr size_t SM_PAIR_RANS = (size_t)VP_SMW_RANS * VP_BS * sizeof(doub
 static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
 static thread_local std::string g_create_error;
+static inline bool is_inlet(int kind) { return kind == RX_BC_INLET_TEMPERATURE_IMPOSE || kind == RX_BC_INLET_TOTAL_CONDITIONS || kind == RX_BC_INLET_MASS_FLOW; }
 
 struct rx_ctx {
   int device = 0, Ns = 0, nVar = 0, nPrim = 0, nGrad = 0, nMarker = 0;
@@ -370,7 +371,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     md.node = dupload(c, node); md.nn = dupload(c, nn); md.nx = dupload(c, nx); md.ny = dupload(c, ny);
     md.ghost = dalloc<double>(c, (size_t)std::max(s.nVertex, 1) * (7 + Ns));
     md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall; md.heatFlux = s.heatFlux;
-    for (int q = 0; q < 16; ++q) md.Ys[q] = (s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
+    for (int q = 0; q < 16; ++q) md.Ys[q] = (is_inlet(s.kind) && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
     c->markers.push_back(md);
   }
   {   // may the first-group boundary kernels overlap?  Only if no point carries two of those markers.
@@ -378,7 +379,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     int nFirst = 0; bool disjoint = true;
     for (int k = 0; k < m->nMarker; ++k) {
       const rx_marker& s = m->markers[k];
-      if (!(s.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || s.kind == RX_BC_OUTLET || s.kind == RX_BC_EULER_WALL) || !s.nVertex) continue;
+      if (!(is_inlet(s.kind) || s.kind == RX_BC_OUTLET || s.kind == RX_BC_EULER_WALL) || !s.nVertex) continue;
       ++nFirst;
       for (int v = 0; v < s.nVertex; ++v) { if (seen[s.node[v]]) disjoint = false; seen[s.node[v]] = 1; }
     }
@@ -647,8 +648,8 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   // Space_Integration: rows, then the boundary conditions (weak ones first, walls last: integration_structure.cpp:89-190)
   k_turb_rows<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
   for (const MarkerDev& mk : c->markers)
-    if (mk.nVertex && (mk.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || mk.kind == RX_BC_OUTLET)) {
-      k_turb_bc_io<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w, mk.kind == RX_BC_INLET_TEMPERATURE_IMPOSE ? 1 : 0); c->launches++;
+    if (mk.nVertex && (is_inlet(mk.kind) || mk.kind == RX_BC_OUTLET)) {
+      k_turb_bc_io<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w, is_inlet(mk.kind) ? 1 : 0); c->launches++;
     }
   for (const MarkerDev& mk : c->markers)
     if (mk.nVertex && (mk.kind == RX_BC_ISOTHERMAL || mk.kind == RX_BC_HEATFLUX)) { k_turb_bc_wall<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w); c->launches++; }
@@ -908,7 +909,7 @@ int rx_residual_source(rx_ctx* c) {
 static void launch_bc(rx_ctx* c, const MarkerDev& m, cudaStream_t s) {
   const Dev& d = c->d;
   if (!m.nVertex) return;
-  if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE) { RX_NS(k_bc_inlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
+  if (is_inlet(m.kind)) { RX_NS(k_bc_inlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_OUTLET) { RX_NS(k_bc_outlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_ISOTHERMAL) { RX_NS(k_bc_isothermal<NS><<<nblk(m.nVertex, 64), 64, 0, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_HEATFLUX) { k_bc_heatflux<<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
@@ -922,7 +923,7 @@ int rx_bc(rx_ctx* c) {
   if (fork) { RX_CK(cudaEventRecord(c->evFork, c->stream)); RX_CK(cudaStreamWaitEvent(c->bcStream, c->evFork, 0)); }
   int nth = 0;
   for (const MarkerDev& m : c->markers)
-    if (m.kind == RX_BC_INLET_TEMPERATURE_IMPOSE || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) {
+    if (is_inlet(m.kind) || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) {
       if (!m.nVertex) continue;
       launch_bc(c, m, (fork && (nth & 1)) ? c->bcStream : c->stream);
       ++nth;

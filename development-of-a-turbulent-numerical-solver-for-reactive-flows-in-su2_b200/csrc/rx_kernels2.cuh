@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(EDGE_BS) k_edge_visc_generic(const __grid_cons
   if (d.eKey) d.eKey[e] = 0;
 }
 
-// BC_Inlet, case TEMPERATURE_IMPOSE (solver_direct_reactive.cpp:3226-3674, :3467-3500)
+// BC_Inlet (solver_direct_reactive.cpp:3226-3674): TEMPERATURE_IMPOSE :3467-3500 (marker kind 1), TOTAL_CONDITIONS :3283-3409 (6), MASS_FLOW :3411-3465 (7)
 template <int NS>
 __global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -354,16 +354,99 @@ __global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<N
   double Vg[7 + NS], Ys[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) Ys[s] = m.Ys[s];
-  Vg[V_T] = m.T;
-  Vg[V_VX] = m.Vmag * m.dir0; Vg[V_VX + 1] = m.Vmag * m.dir1;
-  Vg[V_P] = d.V[V_P * d.np + i];
-  const double Rg = rgas(cc, Ys);
-  Vg[V_RHO] = Vg[V_P] / (Vg[V_T] * Rg) * 1.0;
   bool ok = true;
-  Vg[V_H] = enthalpy(cc, m.T, Ys, ok) / 1.0 + (o.rans ? 1 : 0) * o.tkeInf;
-  Vg[V_H] += 0.5 * m.Vmag * m.Vmag;
-  const double g = frozen_gamma(cc, m.T, Ys);
-  Vg[V_A] = sqrt(g * Rg * m.T);
+  if (m.kind == 6) {
+    // TOTAL_CONDITIONS (:3283-3409): static temperature from the outgoing Riemann invariant and the total enthalpy — secant from
+    // (T_tot, T_tot + 1), at most 15 steps to 1e-9, else bisection on [300, T_tot], 100 steps to 1e-6 — then the isentropic state
+    const double Area = sqrt(0.0 + m.nx[k] * m.nx[k] + m.ny[k] * m.ny[k]);
+    const double un0 = nx / Area, un1 = ny / Area;
+    const double Ttot = m.T / 1.0, Ptot = m.Vmag / 1.0;
+    double Vn = 0.0;
+    Vn += d.V[V_VX * d.np + i] * un0; Vn += d.V[(V_VX + 1) * d.np + i] * un1;
+    const double SoundSpeed = d.V[V_A * d.np + i];
+    double Gamma = d.gam[i];
+    const double Gamma_Tot = frozen_gamma(cc, Ttot, Ys);
+    Gamma = 2.0 / (1.0 / Gamma + 1.0 / Gamma_Tot);
+    const double Gamma_Minus_One = Gamma - 1.0;
+    const double Riemann = Vn + 2.0 * SoundSpeed / Gamma_Minus_One;
+    double Tot_Enthalpy = enthalpy(cc, Ttot, Ys, ok);
+    double alpha = 0.0;
+    alpha = alpha + un0 * m.dir0; alpha = alpha + un1 * m.dir1;
+    const double Rg = rgas(cc, Ys) / 1.0;
+    auto f = [&](double T) {
+      const double hb = enthalpy(cc, T, Ys, ok);
+      const double cb = sqrt(Gamma * Rg * T);
+      const double Vb = (Riemann - 2.0 * cb / Gamma_Minus_One) / alpha;
+      return hb + 0.5 * Vb * Vb;
+    };
+    double Told = Ttot + 1.0, Tcurr = Ttot, Tnew;
+    bool NRconvg = false;
+#pragma unroll 1
+    for (int it = 0; it < 15; ++it) {
+      const double tmp = f(Tcurr);
+      const double F = tmp - Tot_Enthalpy;
+      const double dF = tmp - f(Told);
+      Tnew = Tcurr - F * (Tcurr - Told) / dF;
+      if (fabs(Tnew - Tcurr) < 1.0e-9) { NRconvg = true; break; }
+      Told = Tcurr; Tcurr = Tnew;
+    }
+    if (NRconvg) Vg[V_T] = Tcurr;
+    else {
+      double Ta = 300.0 / 1.0, Tb = Ttot;
+      bool Bconvg = false;
+#pragma unroll 1
+      for (int it = 0; it < 100; ++it) {
+        Tcurr = (Ta + Tb) / 2.0;
+        const double F = f(Tcurr) - Tot_Enthalpy;
+        if (fabs(F) < 1.0e-6) { Vg[V_T] = Tcurr; Bconvg = true; break; }
+        if (F > 0.0) Ta = Tcurr; else Tb = Tcurr;
+      }
+      if (!Bconvg) { Vg[V_T] = CUDART_NAN; atomicAdd(d.counters + 4, 1ULL); }   // the reference throws here (:3377); counted with the failed temperature solves
+    }
+    if (o.rans) Tot_Enthalpy += o.tkeInf;
+    Vg[V_H] = Tot_Enthalpy;
+    const double rho_tot = Ptot / (Rg * Ttot);
+    Vg[V_RHO] = rho_tot * rx_pow(Vg[V_T] / Ttot, 1.0 / Gamma_Minus_One);
+    Vg[V_P] = Vg[V_RHO] * Rg * Vg[V_T];
+    Vg[V_A] = sqrt(Vg[V_T] * Gamma * Rg);
+    const double Vel_Mag = fabs((Riemann - 2.0 * Vg[V_A] / Gamma_Minus_One) / alpha);
+    Vg[V_VX] = Vel_Mag * m.dir0; Vg[V_VX + 1] = Vel_Mag * m.dir1;
+  } else if (m.kind == 7) {
+    // MASS_FLOW (:3411-3465): density and velocity imposed, the speed of sound from the outgoing Riemann invariant
+    const double Area = sqrt(0.0 + m.nx[k] * m.nx[k] + m.ny[k] * m.ny[k]);
+    const double un0 = nx / Area, un1 = ny / Area;
+    const double Density = m.T / 1.0, Vel_Mag = m.Vmag / 1.0;
+    double SoundSpeed = d.V[V_A * d.np + i];
+    const double Gamma = d.gam[i];
+    const double Gamma_Minus_One = Gamma - 1.0;
+    double Vn = 0.0;
+    Vn = Vn + d.V[V_VX * d.np + i] * un0; Vn = Vn + d.V[(V_VX + 1) * d.np + i] * un1;
+    const double Riemann = Vn + 2.0 * SoundSpeed / Gamma_Minus_One;
+    double alpha = 0.0;
+    alpha = alpha + un0 * m.dir0; alpha = alpha + un1 * m.dir1;
+    SoundSpeed = Riemann - Vel_Mag * alpha;
+    SoundSpeed = fmax(0.0, 0.5 * Gamma_Minus_One * SoundSpeed);
+    const double Pressure = SoundSpeed * SoundSpeed * Density / Gamma;
+    Vg[V_T] = Pressure / (Density * rgas(cc, Ys)) * 1.0;
+    Vg[V_VX] = Vel_Mag * m.dir0; Vg[V_VX + 1] = Vel_Mag * m.dir1;
+    Vg[V_P] = Pressure;
+    Vg[V_RHO] = Density;
+    double Aux_Ent = enthalpy(cc, Vg[V_T] * 1.0, Ys, ok) / 1.0;
+    if (o.rans) Aux_Ent += o.tkeInf;
+    Vg[V_H] = Aux_Ent;
+    Vg[V_H] += 0.5 * Vel_Mag * Vel_Mag;
+    Vg[V_A] = SoundSpeed;
+  } else {
+    Vg[V_T] = m.T;
+    Vg[V_VX] = m.Vmag * m.dir0; Vg[V_VX + 1] = m.Vmag * m.dir1;
+    Vg[V_P] = d.V[V_P * d.np + i];
+    const double Rg = rgas(cc, Ys);
+    Vg[V_RHO] = Vg[V_P] / (Vg[V_T] * Rg) * 1.0;
+    Vg[V_H] = enthalpy(cc, m.T, Ys, ok) / 1.0 + (o.rans ? 1 : 0) * o.tkeInf;
+    Vg[V_H] += 0.5 * m.Vmag * m.Vmag;
+    const double g = frozen_gamma(cc, m.T, Ys);
+    Vg[V_A] = sqrt(g * Rg * m.T);
+  }
 #pragma unroll
   for (int s = 0; s < NS; ++s) Vg[V_Y + s] = Ys[s];
 #pragma unroll

@@ -122,6 +122,7 @@ ENVS = {
     "channel_lam_edge": {"RX_PERTURB_TAMP": "2000", "RX_POKE_ITER": "1", "RX_POKE_MODE": "abc"},
     "channel_lam_clip": {"RX_POKE_ITER": "1", "RX_POKE_MODE": "d"},
     "channel_rans_ign": {"RX_PERTURB_TAMP": "2000"},
+    "channel_lam_inlet_total": {"RX_PERTURB_TAMP": "0", "RX_PERTURB_NOISE": "0"},   # total conditions need an interior state consistent with them
 }
 
 # name -> (case-dir kwargs, cfg replacements, nIter, dump_from, perturb_seed or None, lean fixture (drop intermediate residuals))
@@ -182,6 +183,14 @@ SPECS = {
     # (IGNITION_ITER= 2, solver_direct_reactive.cpp:1013-1024)
     "channel_rans_ign": (dict(nx=41, ny=21, stretch=1.5),
                          dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="3", IGNITION="YES", IGNITION_ITER="2", CFL_NUMBER="0.02"), 3, 1, 47, True),
+    # ---- the other two kinds of BC_Inlet (solver_direct_reactive.cpp:3283-3466): total conditions (the flat-plate cfg's kind) and mass flow
+    "channel_lam_inlet_total": (dict(nx=41, ny=21, stretch=1.5),
+                                dict(CHANNEL_MARKERS, INLET_TYPE="TOTAL_CONDITIONS", MARKER_INLET="( inlet, 500.5, 104000.0, 1.0, 0.0, 0.0 )",
+                                     RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                                     TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.2"), 2, 1, 67, True),
+    "channel_rans_inlet_massflow": (dict(nx=41, ny=21, stretch=1.5),
+                                    dict(CHANNEL_MARKERS, INLET_TYPE="MASS_FLOW", MARKER_INLET="( inlet, 1.1, 25.0, 1.0, 0.0, 0.0 )",
+                                         RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO"), 2, 1, 71, True),
     # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
     # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
     "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),

@@ -353,6 +353,7 @@ static void apply_bcs(Ctx& c) {
 // Smooth fields + seeded noise on (T, P, u, v, Y_s, k, omega); conserved variables are rebuilt with the
 // reference's own library (ComputeEnthalpy / ComputeRgas), so the state is thermodynamically consistent.
 #include <random>
+static double g_noise = 1.0;  // env RX_PERTURB_NOISE: scale of the point-wise random part (0: smooth fields, for boundary conditions that need a consistent state)
 static double g_tamp = 800.0;   // env RX_PERTURB_TAMP: peak of the temperature bump (2000 => burning-state temperatures up to 2500 K)
 static void perturb_state(Ctx& c, unsigned long seed) {
   using namespace Framework;
@@ -371,12 +372,12 @@ static void perturb_state(Ctx& c, unsigned long seed) {
     std::uniform_real_distribution<double> un(-1.0, 1.0);
     double xh = (c.geo->node[p]->GetCoord(0) - x0) / (x1 - x0), yh = (c.geo->node[p]->GetCoord(1) - y0) / (y1 - y0);
     double sh = 0.5 + 0.5 * std::tanh((yh - 0.5) * 6.0);
-    double T = 500.0 + g_tamp * std::exp(-std::pow((yh - 0.5) / 0.2, 2)) * (0.6 + 0.4 * std::sin(6.283185307179586 * xh)) + 8.0 * un(gen);
-    double P = 101325.0 * (1.0 + 0.05 * std::sin(3.0 * xh + yh)) * (1.0 + 1e-3 * un(gen));
-    double u = 30.0 * 4.0 * yh * (1.0 - yh) + 3.0 * std::sin(5.0 * xh) + 0.2 * un(gen);
-    double v = 2.0 * std::sin(6.283185307179586 * xh) * std::cos(3.141592653589793 * yh) + 0.2 * un(gen);
+    double T = 500.0 + g_tamp * std::exp(-std::pow((yh - 0.5) / 0.2, 2)) * (0.6 + 0.4 * std::sin(6.283185307179586 * xh)) + 8.0 * g_noise * un(gen);
+    double P = 101325.0 * (1.0 + 0.05 * std::sin(3.0 * xh + yh)) * (1.0 + 1e-3 * g_noise * un(gen));
+    double u = 30.0 * 4.0 * yh * (1.0 - yh) + 3.0 * std::sin(5.0 * xh) + 0.2 * g_noise * un(gen);
+    double v = 2.0 * std::sin(6.283185307179586 * xh) * std::cos(3.141592653589793 * yh) + 0.2 * g_noise * un(gen);
     std::vector<double> Y(Ns, 0.0);
-    for (unsigned short s = 0; s < Ns; ++s) Y[s] = 0.02 * (1.0 + std::sin(1.7 * s + 4.0 * xh + 2.0 * yh)) * (1.0 + 0.1 * un(gen));
+    for (unsigned short s = 0; s < Ns; ++s) Y[s] = 0.02 * (1.0 + std::sin(1.7 * s + 4.0 * xh + 2.0 * yh)) * (1.0 + 0.1 * g_noise * un(gen));
     Y[c.cfg->GetFuelIndex()] += 1.0 - sh;
     Y[c.cfg->GetOxidizerIndex()] += sh;
     if (yh > 0.7) Y[c.cfg->GetFuelIndex()] = 0.0;          // exact zeros: exercise the 1e-15 / 1e-10 thresholds
@@ -386,8 +387,8 @@ static void perturb_state(Ctx& c, unsigned long seed) {
     for (double& w : Y) w /= sum;
     double k = 0.0;
     if (c.rans) {
-      k = 0.05 + 5.0 * yh * (1.0 - yh) * (1.0 + 0.2 * un(gen));
-      double om = 2.0e3 * (1.0 + 0.8 * std::sin(3.0 * xh) * std::cos(2.0 * yh)) * (1.0 + 0.1 * un(gen));
+      k = 0.05 + 5.0 * yh * (1.0 - yh) * (1.0 + 0.2 * g_noise * un(gen));
+      double om = 2.0e3 * (1.0 + 0.8 * std::sin(3.0 * xh) * std::cos(2.0 * yh)) * (1.0 + 0.1 * g_noise * un(gen));
       CVariable* t = c.sol[TURB_SOL]->node[p];
       double rho_ = P / (lib.ComputeRgas(Y) * T);
       t->SetSolution(0, k); t->SetSolution(1, om); t->SetSolution_Old(0, k); t->SetSolution_Old(1, om);
@@ -509,6 +510,7 @@ int main(int argc, char** argv) {
   { FILE* f = fopen((g_out + "/meta.json").c_str(), "w"); fputs(js.str().c_str(), f); fclose(f); }
 
   if (getenv("RX_PERTURB_TAMP")) g_tamp = atof(getenv("RX_PERTURB_TAMP"));
+  if (getenv("RX_PERTURB_NOISE")) g_noise = atof(getenv("RX_PERTURB_NOISE"));
   if (argc > 5) perturb_state(c, atol(argv[5]));
   const long pokeIter = getenv("RX_POKE_ITER") ? atol(getenv("RX_POKE_ITER")) : -1;
   const std::string pokeMode = getenv("RX_POKE_MODE") ? getenv("RX_POKE_MODE") : "";

@@ -15,7 +15,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 ORACLE_SRC = os.path.join(ROOT, "oracle", "rx_oracle.cpp")
 ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "librx_oracle.so")
 
-KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL = 1, 2, 3, 4, 5
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL, KIND_INLET_TOTAL, KIND_INLET_MASSFLOW = 1, 2, 3, 4, 5, 6, 7
 _BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL, "heatflux": KIND_HEATFLUX, "euler_wall": KIND_EULER_WALL}
 
 
@@ -120,7 +120,10 @@ def opts_dict(case):
 def marker_list(case):
     out = []
     for k, mk in enumerate(case.meta["markers"]):
-        d = dict(kind=_BC_KIND.get(mk["bc"], 0), tag=mk["tag"],
+        kind = _BC_KIND.get(mk["bc"], 0)
+        if mk["bc"] == "inlet":   # CConfig::GetKind_Inlet (option_structure.hpp:880-886): 1 total conditions, 2 mass flow, 4 temperature imposed
+            kind = {1: KIND_INLET_TOTAL, 2: KIND_INLET_MASSFLOW}.get(int(case.meta["cfg"].get("kind_inlet", 4)), KIND_INLET)
+        d = dict(kind=kind, tag=mk["tag"],
                  node=np.ascontiguousarray(case["geo_marker%d_node" % k], dtype=np.int64),
                  normalNeighbor=np.ascontiguousarray(case["geo_marker%d_normal_neighbor" % k], dtype=np.int64),
                  normal=np.ascontiguousarray(case["geo_marker%d_normal" % k], dtype=np.float64),

@@ -18,7 +18,9 @@ CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 # name -> (iterations, seed)   (oracle/make_golden.py SPECS)
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
         "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37),
-        "channel_air3_rans": (2, 59), "channel_mix5_lam": (2, 61)}   # the reference's 3- and 5-species mixtures
+        "channel_air3_rans": (2, 59), "channel_mix5_lam": (2, 61),   # the reference's 3- and 5-species mixtures
+        "channel_lam_inlet_total": (2, 67), "channel_rans_inlet_massflow": (2, 71)}   # INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW
+CASE_ENV = {"channel_lam_inlet_total": {"RX_PERTURB_TAMP": "0", "RX_PERTURB_NOISE": "0"}}   # oracle/make_golden.py ENVS
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-12   # later iterations too: with the glibc-exact exp / pow (csrc/rx_libm.cuh) the laminar chains are bit-identical
 TOL_FIRST_BY_CASE = {}
@@ -47,7 +49,7 @@ def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
         pytest.skip("oracle/_ref harnesses or the case directory are not in this snapshot (built by oracle/build_ref.sh where the reference tree is present)")
     nit, seed = RUNS[name]
     out_g, out_c = str(tmp_path / "gpu"), str(tmp_path / "cpu")
-    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1", RX_TECPLOT_OUT="1",
+    txt = _run(HARNESS, d, out_g, nit, seed, dict(os.environ, **CASE_ENV.get(name, {}), SU2_RX_BACKEND="cuda", SU2_RX_MIRROR="2", SU2_RX_TURB_POST="1" if turb_post else "0", RX_RESTART_OUT="1", RX_TECPLOT_OUT="1",
                                                      SU2_RX_TURB="device" if turb_dev else "host"))
     assert "CReactiveNSSolverGPU" in txt and (("CTurbSSTSolverGPU" in txt) == turb_dev)
     # restart file: the reference's COutput (fed by the subclass's host mirrors) and the subclass's own device writer, same run
@@ -59,7 +61,7 @@ def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
         a = open(os.path.join(d, "flow.dat"), "rb").read(); b = open(os.path.join(d, "flow_gpu.dat"), "rb").read()
         os.remove(os.path.join(d, "flow.dat")); os.remove(os.path.join(d, "flow_gpu.dat"))
         assert a == b, "rx_tecplot_write differs from COutput::SetTecplotASCII on the same state"
-    _run(HARNESS_CPU, d, out_c, nit, seed, dict(os.environ))
+    _run(HARNESS_CPU, d, out_c, nit, seed, dict(os.environ, **CASE_ENV.get(name, {})))
     case = Case(os.path.join(GOLDEN, name + ".npz"))
     checked, worst = 0, (0.0, "")
     for f in sorted(os.listdir(out_c)):

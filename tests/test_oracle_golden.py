@@ -17,7 +17,9 @@ from rxcase import Case, Oracle, GOLDEN, vec_rel_err, stage_rel_err
 CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler", "channel_rans_gg",
          "channel_lam_edge", "channel_lam_clip", "channel_rans_ign",
          # species-count generality: the reference's other two mixtures (TURBOLENT_FLAT_PLATE): 3-species air laminar / RANS, 5 species MUSCL
-         "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam"]
+         "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam",
+         # the other two kinds of BC_Inlet (INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW, solver_direct_reactive.cpp:3283-3465)
+         "channel_lam_inlet_total", "channel_rans_inlet_massflow"]
 TOL = 0.0
 
 
