@@ -86,6 +86,16 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
         r.dir[0] = config->GetInlet_FlowDir(tag)[0]; r.dir[1] = config->GetInlet_FlowDir(tag)[1];
         for (unsigned short s = 0; s < nSpecies; ++s) vys[m][s] = config->GetInlet_MassFrac(tag)[s];
         break;
+      case SUPERSONIC_INLET:
+        if (ransMode) throw std::runtime_error("CReactiveNSSolverGPU: BC_Supersonic_Inlet leaves the turbulence inputs of the viscous numerics unset in the reference; RANS is not supported with it");
+        r.kind = RX_BC_SUPERSONIC_INLET;
+        r.T = config->GetInlet_Temperature(tag); r.P = config->GetInlet_Pressure(tag);
+        r.dir[0] = config->GetInlet_Velocity(tag)[0]; r.dir[1] = config->GetInlet_Velocity(tag)[1];
+        for (unsigned short s = 0; s < nSpecies; ++s) vys[m][s] = config->GetInlet_MassFrac(tag)[s];
+        break;
+      case SUPERSONIC_OUTLET:
+        if (ransMode) throw std::runtime_error("CReactiveNSSolverGPU: BC_Supersonic_Outlet leaves the turbulence inputs of the viscous numerics unset in the reference; RANS is not supported with it");
+        r.kind = RX_BC_SUPERSONIC_OUTLET; break;
       case OUTLET_FLOW: r.kind = RX_BC_OUTLET; r.P = config->GetOutlet_Pressure(tag); break;
       case ISOTHERMAL: r.kind = RX_BC_ISOTHERMAL; r.Twall = config->GetIsothermal_Temperature(tag); break;
       case HEAT_FLUX: r.kind = RX_BC_HEATFLUX; r.heatFlux = config->GetWall_HeatFlux(tag); break;
@@ -346,6 +356,14 @@ void CReactiveNSSolverGPU::BC_Inlet(CGeometry* geometry, CSolver**, CNumerics*, 
 void CReactiveNSSolverGPU::BC_Outlet(CGeometry* geometry, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
   Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
   if (mirror >= 1 && ransMode) MirrorBoundaryState(geometry, val_marker);
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_Supersonic_Inlet(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
+  if (mirror >= 2) MirrorResidual();
+}
+void CReactiveNSSolverGPU::BC_Supersonic_Outlet(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {
+  Check(rx_bc_marker(ctx, val_marker), "rx_bc_marker");
   if (mirror >= 2) MirrorResidual();
 }
 void CReactiveNSSolverGPU::BC_HeatFlux_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short val_marker) {

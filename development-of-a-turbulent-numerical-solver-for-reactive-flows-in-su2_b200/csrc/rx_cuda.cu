@@ -25,6 +25,7 @@ static constexpr size_t SM_PAIR_RANS = (size_t)VP_SMW_RANS * VP_BS * sizeof(doub
 static constexpr size_t SM_VISC = (size_t)(9 * 9 + 3 * 9) * EDGE_BS * sizeof(double);   // thread-private 9x9 matrix + three 9-vectors in shared memory
 
 static thread_local std::string g_create_error;
+static inline bool is_supersonic(int kind) { return kind == RX_BC_SUPERSONIC_INLET || kind == RX_BC_SUPERSONIC_OUTLET; }
 static inline bool is_inlet(int kind) { return kind == RX_BC_INLET_TEMPERATURE_IMPOSE || kind == RX_BC_INLET_TOTAL_CONDITIONS || kind == RX_BC_INLET_MASS_FLOW; }
 
 struct rx_ctx {
@@ -234,6 +235,7 @@ static cudaError_t set_kernel_attributes() {
   }
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_inlet<NS>, at, smv);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_outlet<NS>, at, smv);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bc_supersonic<NS>, at, smv);
   return e;
 }
 
@@ -361,6 +363,10 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   c->nMarker = m->nMarker;
   for (int k = 0; k < m->nMarker; ++k) {
     const rx_marker& s = m->markers[k];
+    if (s.kind < RX_BC_NONE || s.kind > RX_BC_SUPERSONIC_OUTLET) { g_create_error = "rx_create: unknown marker kind"; rx_destroy(c); return RX_ERR_ARG; }
+    if (is_supersonic(s.kind) && o.rans) {   // the reference's two supersonic conditions never hand the turbulence inputs to the viscous numerics (:3150-3190)
+      g_create_error = "rx_create: supersonic inlet / outlet markers are supported for laminar and inviscid contexts only"; rx_destroy(c); return RX_ERR_UNSUPPORTED;
+    }
     MarkerDev md{};
     md.kind = s.kind; md.nVertex = s.nVertex;
     std::vector<int> node(s.nVertex), nn(s.nVertex);
@@ -371,7 +377,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     md.node = dupload(c, node); md.nn = dupload(c, nn); md.nx = dupload(c, nx); md.ny = dupload(c, ny);
     md.ghost = dalloc<double>(c, (size_t)std::max(s.nVertex, 1) * (7 + Ns));
     md.T = s.T; md.Vmag = s.Vmag; md.dir0 = s.dir[0]; md.dir1 = s.dir[1]; md.P = s.P; md.Twall = s.Twall; md.heatFlux = s.heatFlux;
-    for (int q = 0; q < 16; ++q) md.Ys[q] = (is_inlet(s.kind) && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
+    for (int q = 0; q < 16; ++q) md.Ys[q] = ((is_inlet(s.kind) || s.kind == RX_BC_SUPERSONIC_INLET) && s.Ys && q < Ns) ? s.Ys[q] : 0.0;
     c->markers.push_back(md);
   }
   {   // may the first-group boundary kernels overlap?  Only if no point carries two of those markers.
@@ -379,7 +385,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
     int nFirst = 0; bool disjoint = true;
     for (int k = 0; k < m->nMarker; ++k) {
       const rx_marker& s = m->markers[k];
-      if (!(is_inlet(s.kind) || s.kind == RX_BC_OUTLET || s.kind == RX_BC_EULER_WALL) || !s.nVertex) continue;
+      if (!(is_inlet(s.kind) || is_supersonic(s.kind) || s.kind == RX_BC_OUTLET || s.kind == RX_BC_EULER_WALL) || !s.nVertex) continue;
       ++nFirst;
       for (int v = 0; v < s.nVertex; ++v) { if (seen[s.node[v]]) disjoint = false; seen[s.node[v]] = 1; }
     }
@@ -909,7 +915,8 @@ int rx_residual_source(rx_ctx* c) {
 static void launch_bc(rx_ctx* c, const MarkerDev& m, cudaStream_t s) {
   const Dev& d = c->d;
   if (!m.nVertex) return;
-  if (is_inlet(m.kind)) { RX_NS(k_bc_inlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
+  if (is_supersonic(m.kind)) { RX_NS(k_bc_supersonic<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
+  else if (is_inlet(m.kind)) { RX_NS(k_bc_inlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_OUTLET) { RX_NS(k_bc_outlet<NS><<<nblk(m.nVertex, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_ISOTHERMAL) { RX_NS(k_bc_isothermal<NS><<<nblk(m.nVertex, 64), 64, 0, s>>>(cc, c->o, d, m)); c->launches++; }
   else if (m.kind == RX_BC_HEATFLUX) { k_bc_heatflux<<<nblk(m.nVertex, 64), 64, 0, s>>>(d, m); c->launches++; }
@@ -923,7 +930,7 @@ int rx_bc(rx_ctx* c) {
   if (fork) { RX_CK(cudaEventRecord(c->evFork, c->stream)); RX_CK(cudaStreamWaitEvent(c->bcStream, c->evFork, 0)); }
   int nth = 0;
   for (const MarkerDev& m : c->markers)
-    if (is_inlet(m.kind) || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) {
+    if (is_inlet(m.kind) || is_supersonic(m.kind) || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) {
       if (!m.nVertex) continue;
       launch_bc(c, m, (fork && (nth & 1)) ? c->bcStream : c->stream);
       ++nth;

@@ -453,6 +453,42 @@ __global__ void __launch_bounds__(64) k_bc_inlet(const __grid_constant__ ChemC<N
   for (int v = 0; v < 7 + NS; ++v) m.ghost[(size_t)v * m.nVertex + k] = Vg[v];   // CharacPrimVar (:3274), read by the turbulence BCs
   boundary_fluxes<NS>(cc, o, d, i, Vg, nx, ny);
 }
+// BC_Supersonic_Inlet (:2998-3214; kind 8: every primitive imposed, no turbulent kinetic energy in the enthalpy) and
+// BC_Supersonic_Outlet (:3681-3807; kind 9: the outer state is the interior one)
+template <int NS>
+__global__ void __launch_bounds__(64) k_bc_supersonic(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= m.nVertex) return;
+  const int i = m.node[k];
+  if (i >= d.nPointDomain) return;
+  const double nx = -m.nx[k], ny = -m.ny[k];
+  double Vb[7 + NS];
+  if (m.kind == 8) {
+    double Ys[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) Ys[s] = m.Ys[s];
+    bool ok = true;
+    const double Temperature = m.T, Pressure = m.P;
+    const double Rg = rgas(cc, Ys);
+    const double Density = Pressure / (Temperature * Rg) * 1.0;
+    const double Enthalpy = enthalpy(cc, Temperature, Ys, ok);
+    const double SoundSpeed = sqrt(frozen_gamma(cc, Temperature, Ys) * rgas(cc, Ys) * Temperature);
+    Vb[V_T] = Temperature / 1.0;
+    Vb[V_VX] = m.dir0 / 1.0; Vb[V_VX + 1] = m.dir1 / 1.0;
+    Vb[V_P] = Pressure / 1.0; Vb[V_RHO] = Density / 1.0;
+    double Velocity2 = 0.0;
+    Velocity2 = Velocity2 + Vb[V_VX] * Vb[V_VX]; Velocity2 = Velocity2 + Vb[V_VX + 1] * Vb[V_VX + 1];
+    Vb[V_H] = Enthalpy / 1.0 + 0.5 * Velocity2;
+    Vb[V_A] = SoundSpeed / 1.0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) Vb[V_Y + s] = Ys[s];
+  } else {
+    load_V<NS>(d, i, Vb);
+  }
+#pragma unroll
+  for (int v = 0; v < 7 + NS; ++v) m.ghost[(size_t)v * m.nVertex + k] = Vb[v];   // CharacPrimVar
+  boundary_fluxes<NS>(cc, o, d, i, Vb, nx, ny);
+}
 // BC_Outlet (solver_direct_reactive.cpp:3808-4123)
 template <int NS>
 __global__ void __launch_bounds__(64) k_bc_outlet(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d, const MarkerDev m) {

@@ -12,7 +12,7 @@ against the reference's geometry dump of the same .su2 mesh.
 """
 import numpy as np
 
-KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL, KIND_INLET_TOTAL, KIND_INLET_MASSFLOW = 1, 2, 3, 4, 5, 6, 7
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL, KIND_INLET_TOTAL, KIND_INLET_MASSFLOW, KIND_SUPERSONIC_INLET, KIND_SUPERSONIC_OUTLET = 1, 2, 3, 4, 5, 6, 7, 8, 9
 
 
 def channel_points(nx, ny, L=0.25, H=0.025, stretch=1.0):

@@ -31,7 +31,9 @@ enum rx_status { RX_OK = 0, RX_ERR_ARG = -1, RX_ERR_NO_DEVICE = -2, RX_ERR_CUDA 
 /* the three kinds of BC_Inlet's switch (INLET_TYPE, solver_direct_reactive.cpp:3280-3500): TEMPERATURE_IMPOSE reads T = temperature, Vmag = velocity;
  * TOTAL_CONDITIONS T = total temperature, Vmag = total pressure; MASS_FLOW T = density, Vmag = velocity (the second and third value of MARKER_INLET) */
 enum rx_bc_kind { RX_BC_NONE = 0, RX_BC_INLET_TEMPERATURE_IMPOSE = 1, RX_BC_OUTLET = 2, RX_BC_ISOTHERMAL = 3, RX_BC_HEATFLUX = 4, RX_BC_EULER_WALL = 5,
-                  RX_BC_INLET_TOTAL_CONDITIONS = 6, RX_BC_INLET_MASS_FLOW = 7 };
+                  RX_BC_INLET_TOTAL_CONDITIONS = 6, RX_BC_INLET_MASS_FLOW = 7,
+                  RX_BC_SUPERSONIC_INLET = 8,    /* BC_Supersonic_Inlet :2998-3214: T, P, velocity vector in dir[], Ys; laminar / inviscid contexts */
+                  RX_BC_SUPERSONIC_OUTLET = 9 }; /* BC_Supersonic_Outlet :3681-3807 */
 
 /* Tables held by Framework::ReactingModelLibrary after Setup() (Common/src/Framework/reacting_model_library.cpp:1520-1586,
  * members reacting_model_library.hpp:655-766).  Matrices are [reaction][species]. */

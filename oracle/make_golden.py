@@ -191,6 +191,12 @@ SPECS = {
     "channel_rans_inlet_massflow": (dict(nx=41, ny=21, stretch=1.5),
                                     dict(CHANNEL_MARKERS, INLET_TYPE="MASS_FLOW", MARKER_INLET="( inlet, 1.1, 25.0, 1.0, 0.0, 0.0 )",
                                          RESTART_SOL="NO", EXT_ITER="2", IGNITION="NO"), 2, 1, 71, True),
+    # BC_Supersonic_Inlet / BC_Supersonic_Outlet (:2998-3214, :3681-3807) on the two ends of the channel, laminar
+    "channel_lam_supersonic": (dict(nx=41, ny=21, stretch=1.5),
+                               dict(CHANNEL_MARKERS, MARKER_INLET="( NONE )", MARKER_OUTLET="( NONE )",
+                                    MARKER_SUPERSONIC_INLET="( inlet, 520.0, 101325.0, 700.0, 5.0, 0.0 )", MARKER_SUPERSONIC_OUTLET="( outlet )",
+                                    RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                                    TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.05"), 2, 1, 73, True),
     # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
     # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
     "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),

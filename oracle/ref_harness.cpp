@@ -221,6 +221,13 @@ static void dump_geometry(Ctx& c, std::ostringstream& js) {
          << ", \"dir\": [" << c.cfg->GetInlet_FlowDir(t)[0] << ", " << c.cfg->GetInlet_FlowDir(t)[1] << "], \"Ys\": [";
       for (unsigned short s = 0; s < c.nSpecies; ++s) js << (s ? ", " : "") << c.cfg->GetInlet_MassFrac(t)[s];
       js << "]";
+    } else if (kind == SUPERSONIC_INLET) {   // BC_Supersonic_Inlet (:2998): temperature, pressure, velocity vector, mass fractions
+      js << ", \"bc\": \"supersonic_inlet\", \"T\": " << c.cfg->GetInlet_Temperature(t) << ", \"P\": " << c.cfg->GetInlet_Pressure(t)
+         << ", \"dir\": [" << c.cfg->GetInlet_Velocity(t)[0] << ", " << c.cfg->GetInlet_Velocity(t)[1] << "], \"Ys\": [";
+      for (unsigned short s = 0; s < c.nSpecies; ++s) js << (s ? ", " : "") << c.cfg->GetInlet_MassFrac(t)[s];
+      js << "]";
+    } else if (kind == SUPERSONIC_OUTLET) {
+      js << ", \"bc\": \"supersonic_outlet\"";
     } else if (kind == OUTLET_FLOW) {
       js << ", \"bc\": \"outlet\", \"P\": " << c.cfg->GetOutlet_Pressure(t);
     } else if (kind == ISOTHERMAL) {

@@ -15,8 +15,9 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 ORACLE_SRC = os.path.join(ROOT, "oracle", "rx_oracle.cpp")
 ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "librx_oracle.so")
 
-KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL, KIND_INLET_TOTAL, KIND_INLET_MASSFLOW = 1, 2, 3, 4, 5, 6, 7
-_BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL, "heatflux": KIND_HEATFLUX, "euler_wall": KIND_EULER_WALL}
+KIND_INLET, KIND_OUTLET, KIND_ISOTHERMAL, KIND_HEATFLUX, KIND_EULER_WALL, KIND_INLET_TOTAL, KIND_INLET_MASSFLOW, KIND_SUPERSONIC_INLET, KIND_SUPERSONIC_OUTLET = 1, 2, 3, 4, 5, 6, 7, 8, 9
+_BC_KIND = {"inlet": KIND_INLET, "outlet": KIND_OUTLET, "isothermal": KIND_ISOTHERMAL, "heatflux": KIND_HEATFLUX, "euler_wall": KIND_EULER_WALL,
+            "supersonic_inlet": KIND_SUPERSONIC_INLET, "supersonic_outlet": KIND_SUPERSONIC_OUTLET}
 
 
 def build_oracle(force=False):

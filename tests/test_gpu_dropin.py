@@ -19,7 +19,8 @@ CASES = os.path.join(ROOT, "oracle", "_ref", "cases")
 RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2, 17), "jet_rans_perturbed": (2, 7),
         "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37),
         "channel_air3_rans": (2, 59), "channel_mix5_lam": (2, 61),   # the reference's 3- and 5-species mixtures
-        "channel_lam_inlet_total": (2, 67), "channel_rans_inlet_massflow": (2, 71)}   # INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW
+        "channel_lam_inlet_total": (2, 67), "channel_rans_inlet_massflow": (2, 71),   # INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW
+        "channel_lam_supersonic": (2, 73)}   # MARKER_SUPERSONIC_INLET / _OUTLET
 CASE_ENV = {"channel_lam_inlet_total": {"RX_PERTURB_TAMP": "0", "RX_PERTURB_NOISE": "0"}}   # oracle/make_golden.py ENVS
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-12   # later iterations too: with the glibc-exact exp / pow (csrc/rx_libm.cuh) the laminar chains are bit-identical

@@ -19,7 +19,9 @@ CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_la
          # species-count generality: the reference's other two mixtures (TURBOLENT_FLAT_PLATE): 3-species air laminar / RANS, 5 species MUSCL
          "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam",
          # the other two kinds of BC_Inlet (INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW, solver_direct_reactive.cpp:3283-3465)
-         "channel_lam_inlet_total", "channel_rans_inlet_massflow"]
+         "channel_lam_inlet_total", "channel_rans_inlet_massflow",
+         # BC_Supersonic_Inlet / BC_Supersonic_Outlet (:2998-3214, :3681-3807)
+         "channel_lam_supersonic"]
 TOL = 0.0
 
 
