@@ -246,7 +246,7 @@ static void launch_edge_flux(rx_ctx* c, cudaStream_t s) {
   const Dev& d = c->d;
   if (CONV) {
     if (c->o.secondOrder) RX_NS(k_edge_conv2<NS><<<nblk(d.nEdge, 64), 64, 0, s>>>(cc, c->o, d));
-    else RX_NS(k_edge_flux<NS><<<nblk(d.nEdge, 64), 64, 0, s>>>(cc, c->o, d));
+    else RX_NS(k_edge_flux<NS><<<nblk(d.nEdge, 128), 128, 0, s>>>(cc, c->o, d));
     c->launches++;
   }
   if (VISC) {

@@ -307,15 +307,16 @@ RX_HD bool cons2prim(const ChemC<NS>& cc, const Opts& o, long long extIter, doub
 }
 
 // ---- AUSM+-up (CUpwReactiveAUSM::ComputeResidual, SU2_CFD/src/numerics_direct_reactive.cpp:53-189) --------
-template <int NS>
-RX_HD void ausm(double mInfty, const double* Vi, const double* Vj, double nx, double ny, double* res) {
-  const double Area = sqrt(0.0 + nx * nx + ny * ny);
-  const double un0 = nx / Area, un1 = ny / Area;
-  const double rho_i = Vi[V_RHO], P_i = Vi[V_P], H_i = Vi[V_H], a_i = Vi[V_A];
-  const double rho_j = Vj[V_RHO], P_j = Vj[V_P], H_j = Vj[V_H], a_j = Vj[V_A];
+// The interface quantities every row of the flux shares: mass flux M12, its modulus, the pressure flux, the unit normal and the area.
+struct AusmIface { double M12, aM, pLF, un0, un1, Area; };
+RX_HD AusmIface ausm_iface(double mInfty, double rho_i, double u_i, double v_i, double P_i, double a_i,
+                           double rho_j, double u_j, double v_j, double P_j, double a_j, double nx, double ny) {
+  AusmIface f;
+  f.Area = sqrt(0.0 + nx * nx + ny * ny);
+  f.un0 = nx / f.Area; f.un1 = ny / f.Area;
   double pv_i = 0.0, pv_j = 0.0;
-  pv_i += Vi[V_VX] * un0; pv_j += Vj[V_VX] * un0;
-  pv_i += Vi[V_VX + 1] * un1; pv_j += Vj[V_VX + 1] * un1;
+  pv_i += u_i * f.un0; pv_j += u_j * f.un0;
+  pv_i += v_i * f.un1; pv_j += v_j * f.un1;
   const double am = 0.5 * (a_i + a_j);
   const double mL = pv_i / am, mR = pv_j / am;
   const double mF2 = 0.5 * (mL * mL + mR * mR);
@@ -344,19 +345,27 @@ RX_HD void ausm(double mInfty, const double* Vi, const double* Vj, double nx, do
   m12 -= kP / fa * fmax(1.0 - sigma * mF2, 0.0) * (P_j - P_i) / (0.5 * (rho_i + rho_j) * am * am);
   const double mLF = 0.5 * (m12 + fabs(m12));
   const double mRF = 0.5 * (m12 - fabs(m12));
-  const double M12 = am * (mLF * rho_i + mRF * rho_j);
-  const double aM = fabs(M12);
-  res[U_RHO] = 0.5 * (M12 * (1.0 + 1.0) + aM * (1.0 - 1.0)) * Area;
-  res[U_MX] = 0.5 * (M12 * (Vi[V_VX] + Vj[V_VX]) + aM * (Vi[V_VX] - Vj[V_VX])) * Area;
-  res[U_MX + 1] = 0.5 * (M12 * (Vi[V_VX + 1] + Vj[V_VX + 1]) + aM * (Vi[V_VX + 1] - Vj[V_VX + 1])) * Area;
-  res[U_E] = 0.5 * (M12 * (H_i + H_j) + aM * (H_i - H_j)) * Area;
-#pragma unroll
-  for (int s = 0; s < NS; ++s) res[U_S + s] = 0.5 * (M12 * (Vi[V_Y + s] + Vj[V_Y + s]) + aM * (Vi[V_Y + s] - Vj[V_Y + s])) * Area;
+  f.M12 = am * (mLF * rho_i + mRF * rho_j);
+  f.aM = fabs(f.M12);
   const double Ku = 0.75;
   double pLF = pLP * P_i + pRM * P_j;
   pLF -= Ku * pLP * pRM * (rho_i + rho_j) * fa * am * (pv_j - pv_i);
-  res[U_MX] += pLF * un0 * Area;
-  res[U_MX + 1] += pLF * un1 * Area;
+  f.pLF = pLF;
+  return f;
+}
+// one transported row: 0.5 (M12 (phi_i + phi_j) + |M12| (phi_i - phi_j)) Area
+RX_HD double ausm_row(const AusmIface& f, double phi_i, double phi_j) { return 0.5 * (f.M12 * (phi_i + phi_j) + f.aM * (phi_i - phi_j)) * f.Area; }
+template <int NS>
+RX_HD void ausm(double mInfty, const double* Vi, const double* Vj, double nx, double ny, double* res) {
+  const AusmIface f = ausm_iface(mInfty, Vi[V_RHO], Vi[V_VX], Vi[V_VX + 1], Vi[V_P], Vi[V_A], Vj[V_RHO], Vj[V_VX], Vj[V_VX + 1], Vj[V_P], Vj[V_A], nx, ny);
+  res[U_RHO] = ausm_row(f, 1.0, 1.0);
+  res[U_MX] = ausm_row(f, Vi[V_VX], Vj[V_VX]);
+  res[U_MX + 1] = ausm_row(f, Vi[V_VX + 1], Vj[V_VX + 1]);
+  res[U_E] = ausm_row(f, Vi[V_H], Vj[V_H]);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) res[U_S + s] = ausm_row(f, Vi[V_Y + s], Vj[V_Y + s]);
+  res[U_MX] += f.pLF * f.un0 * f.Area;
+  res[U_MX + 1] += f.pLF * f.un1 * f.Area;
 }
 
 }  // namespace rx

@@ -27,17 +27,33 @@ __device__ __forceinline__ void load_visc_end(const Dev& d, const Opts& o, long 
 
 // ---- Upwind_Residual (:2535-2785, 1st order): one thread per edge, AUSM flux to the edge array
 constexpr int EDGE_BS = 64;   // threads per block of the boundary flux kernels (thread-private Stefan-Maxwell matrix in shared memory)
+#ifndef RX_EF_MINB
+#define RX_EF_MINB 6
+#endif
+// The kernel is bound by HBM (it reads both end states and writes 13 flux words per edge), so it is written for many resident warps:
+// the interface quantities come from twelve scalars, then the rows stream through two registers each — the same operations as ausm<>.
 template <int NS>
-__global__ void __launch_bounds__(64) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
+__global__ void __launch_bounds__(128, RX_EF_MINB) k_edge_flux(const __grid_constant__ ChemC<NS> cc, const __grid_constant__ Opts o, const Dev d) {
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= d.nEdge) return;
-  constexpr int NV = 4 + NS;
   const int i = d.ei[e], j = d.ej[e];
-  double res[NV], Vi[7 + NS], Vj[7 + NS];
-  load_V<NS>(d, i, Vi); load_V<NS>(d, j, Vj);
-  ausm<NS>(o.mInfty, Vi, Vj, d.enx[e], d.eny[e], res);
+  const long long np = d.np, ne = d.ne;
+  const double ui = d.V[V_VX * np + i], uj = d.V[V_VX * np + j], vi = d.V[(V_VX + 1) * np + i], vj = d.V[(V_VX + 1) * np + j];
+  const double Hi = d.V[V_H * np + i], Hj = d.V[V_H * np + j];
+  double Yi[NS], Yj[NS];
 #pragma unroll
-  for (int v = 0; v < NV; ++v) d.fluxC[v * d.ne + e] = res[v];
+  for (int s = 0; s < NS; ++s) { Yi[s] = d.V[(V_Y + s) * np + i]; Yj[s] = d.V[(V_Y + s) * np + j]; }   // issued before the divisions of the interface
+  const AusmIface f = ausm_iface(o.mInfty, d.V[V_RHO * np + i], ui, vi, d.V[V_P * np + i], d.V[V_A * np + i],
+                                 d.V[V_RHO * np + j], uj, vj, d.V[V_P * np + j], d.V[V_A * np + j], d.enx[e], d.eny[e]);
+  d.fluxC[U_RHO * ne + e] = ausm_row(f, 1.0, 1.0);
+  double mx = ausm_row(f, ui, uj), my = ausm_row(f, vi, vj);
+  d.fluxC[U_E * ne + e] = ausm_row(f, Hi, Hj);
+#pragma unroll
+  for (int s = 0; s < NS; ++s) d.fluxC[(U_S + s) * ne + e] = ausm_row(f, Yi[s], Yj[s]);
+  mx += f.pLF * f.un0 * f.Area;
+  my += f.pLF * f.un1 * f.Area;
+  d.fluxC[U_MX * ne + e] = mx;
+  d.fluxC[(U_MX + 1) * ne + e] = my;
 }
 
 // ---- SetPrimitive_Limiter (:1328-1523), Venkatakrishnan, owner-computes: one thread per point over its neighbours.
