@@ -4,6 +4,7 @@
 
 #include "reacting_model_library.hpp"
 
+#include <sstream>
 #include <cstdlib>
 #include <stdexcept>
 #include <string>
@@ -152,6 +153,9 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   o.cMu = config->Get_Cmu(); o.pasrLb = config->Get_PaSR_LB(); o.tkeInf = ransMode ? GetTke_Inf() : 0.0;
   o.secondOrder = second_order ? 1 : 0; o.limiter = limiter ? (config->GetKind_SlopeLimit_Flow() == BARTH_JESPERSEN ? 2 : 1) : 0;
   o.limCoeff = config->GetLimiterCoeff(); o.refElemLength = config->GetRefElemLength();
+  o.timeStepping = config->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0; o.unstCfl = config->GetUnst_CFL(); o.deltaUnstTime = config->GetDelta_UnstTime();
+  if (config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND)
+    throw std::runtime_error("CReactiveNSSolverGPU: dual time stepping is not on the CUDA path");
   o.device = env_int("SU2_RX_DEVICE", 0);
 
   const int rc = rx_create(&ctx, &mesh, &chem, &o);
@@ -444,7 +448,12 @@ void CReactiveNSSolverGPU::WriteTecplot(CGeometry* geometry, CSolver** solver_co
     kw.resize((size_t)nPoint * 2);
     for (unsigned long p = 0; p < nPoint; ++p) { kw[2 * p] = solver_container[TURB_SOL]->node[p]->GetSolution(0); kw[2 * p + 1] = solver_container[TURB_SOL]->node[p]->GetSolution(1); }
   }
-  Check(rx_tecplot_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, (int64_t)(tria.size() / 3), tria.data(), (int64_t)(quad.size() / 4), quad.data()), "rx_tecplot_write");
+  std::ostringstream zone;   // unsteady runs label the zone (output_tecplot.cpp:277-279), with the stream's default formatting
+  if (config->GetUnsteady_Simulation() && config->GetWrt_Unsteady())
+    zone << "STRANDID=" << SU2_TYPE::Int(config->GetExtIter() + 1) << ", SOLUTIONTIME=" << config->GetDelta_UnstTime() * config->GetExtIter() << ", ";
+  const std::string zp = zone.str();
+  Check(rx_tecplot_write(ctx, filename.c_str(), gi.data(), ransMode ? kw.data() : nullptr, (int64_t)(tria.size() / 3), tria.data(), (int64_t)(quad.size() / 4), quad.data(),
+                         zp.empty() ? nullptr : zp.c_str()), "rx_tecplot_write");
 }
 
 void CReactiveNSSolverGPU::SetTurbulenceOnDevice(const double* post12) {

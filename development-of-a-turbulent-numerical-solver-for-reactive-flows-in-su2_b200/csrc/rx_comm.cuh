@@ -16,7 +16,7 @@ namespace rx {
 
 typedef struct ncclComm* nccl_comm_t;
 struct nccl_uid { char internal[128]; };
-enum { NCCL_FLOAT64 = 8, NCCL_SUM = 0 };
+enum { NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MIN = 3 };   // ncclDataType_t / ncclRedOp_t values of nccl.h
 
 struct NcclApi {
   void* h = nullptr;

@@ -66,6 +66,7 @@ struct rx_ctx {
   double* eddyFlow = nullptr;       // RANS: eddy viscosity as the flow variables hold it (copied at every rx_preprocess, CReactiveNSVariable::SetPrimVar :1193) — what COutput writes
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
   bool haveWallDist = false; double sigmaK = 0.85;
+  double* dtPartial = nullptr; int dtBlocks = 0;   // TIME_STEPPING: block minima of the local time steps + the global one
 };
 
 extern "C" {
@@ -301,6 +302,7 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   o.fuelIndex = op->fuelIndex; o.oxidizerIndex = op->oxidizerIndex;
   o.prandtlLam = op->prandtlLam; o.prandtlTurb = op->prandtlTurb; o.lewisTurb = op->lewisTurb; o.cMu = op->cMu;
   o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
+  o.timeStepping = op->timeStepping; o.unstCfl = op->unstCfl; o.deltaUnstTime = op->deltaUnstTime;
   o.secondOrder = op->secondOrder; o.limiter = op->secondOrder ? op->limiter : 0; o.limCoeff = op->limCoeff; o.refElemLength = op->refElemLength;
   int rc = fill_chem(c, ch);
   if (rc) { g_create_error = "rx_create: chemistry upload failed"; rx_destroy(c); return rc; }
@@ -884,6 +886,27 @@ int rx_time_step(rx_ctx* c) {
     if (m.nVertex) { k_timestep_boundary<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
   k_timestep_finish<<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->o, d);
   c->launches++;
+  if (c->o.timeStepping) {
+    if (!c->dtPartial) {
+      c->dtBlocks = (int)nblk(d.nPointDomain, 256);
+      c->dtPartial = dalloc<double>(c, (size_t)c->dtBlocks + 1);
+      if (!c->dtPartial) { c->err = "rx_time_step: device allocation failed"; return RX_ERR_CUDA; }
+    }
+    double* glob = c->dtPartial + c->dtBlocks;
+    k_dt_min_partial<<<c->dtBlocks, 256, 0, s>>>(d, c->dtPartial);
+    k_dt_min_final<<<1, 256, 0, s>>>(c->dtPartial, c->dtBlocks, glob);
+    if (c->comm) {   // MPI_MIN over the ranks (:5264-5269)
+      std::string why;
+      NcclApi* a = nccl_api(why);
+      const int e = a->AllReduce(glob, glob, 1, NCCL_FLOAT64, NCCL_MIN, c->comm->comm, s);
+      if (e) { c->err = std::string("rx_time_step: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+    }
+    // the Euler solver's variant (:2121-2139): from now on the CFL is UNST_CFL_NUMBER; if that is zero every point takes UNST_TIMESTEP
+    if (!c->o.viscous) c->o.cfl = c->o.unstCfl;
+    const int useFixed = (!c->o.viscous && c->o.cfl < EPS) ? 1 : 0;
+    k_dt_fill<<<nblk(d.nPointDomain, 256), 256, 0, s>>>(d, glob, c->o.deltaUnstTime, useFixed);
+    c->launches += 3;
+  }
   RX_CK(cudaGetLastError());
   return RX_OK;
 }

@@ -90,6 +90,7 @@ struct Opts {
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
   int secondOrder, limiter;
   double limCoeff, refElemLength;
+  int timeStepping; double unstCfl, deltaUnstTime;
 };
 
 // ---- spline (MathTools::GetSpline, Common/src/Tools/spline.cpp:61-77) ---------------------------

@@ -469,9 +469,34 @@ __global__ void __launch_bounds__(128) k_timestep_finish(const __grid_constant__
   if (Vol > EPS) {
     dt = o.cfl * Vol / d.lamInv[p];
     if (o.viscous) dt = fmin(dt, o.cfl * 0.25 * Vol * Vol / d.lamVisc[p]);
-    if (dt > o.maxDt) dt = o.maxDt;
+    if (dt > o.maxDt && !o.timeStepping) dt = o.maxDt;   // time stepping: the global minimum is taken over the unclamped steps (:5227) and then overwrites them all
   }
   d.dt[p] = dt;
+}
+// UNSTEADY_SIMULATION = TIME_STEPPING (:5262-5272): minimum over the owned points with positive volume (the reference's loop skips the
+// others), in two stages; then every owned point receives it.  A minimum does not depend on the order.
+__global__ void __launch_bounds__(256) k_dt_min_partial(const Dev d, double* __restrict__ partial) {
+  __shared__ double sh[256];
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  double v = 1.0e6;   // Global_Delta_Time starts at 1e6 (:5064)
+  if (p < d.nPointDomain && d.vol[p] > EPS) v = fmin(v, d.dt[p]);
+  sh[threadIdx.x] = v;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) { if ((int)threadIdx.x < w) sh[threadIdx.x] = fmin(sh[threadIdx.x], sh[threadIdx.x + w]); __syncthreads(); }
+  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(256) k_dt_min_final(const double* __restrict__ partial, int n, double* __restrict__ out) {
+  __shared__ double sh[256];
+  double v = 1.0e6;
+  for (int b = threadIdx.x; b < n; b += 256) v = fmin(v, partial[b]);
+  sh[threadIdx.x] = v;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) { if ((int)threadIdx.x < w) sh[threadIdx.x] = fmin(sh[threadIdx.x], sh[threadIdx.x + w]); __syncthreads(); }
+  if (threadIdx.x == 0) out[0] = sh[0];
+}
+__global__ void k_dt_fill(const Dev d, const double* __restrict__ global, double fixed, int useFixed) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p < d.nPointDomain) d.dt[p] = useFixed ? fixed : global[0];
 }
 
 }  // namespace rx

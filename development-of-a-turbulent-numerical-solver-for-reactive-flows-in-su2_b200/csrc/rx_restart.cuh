@@ -170,7 +170,7 @@ extern "C" int rx_restart_write(rx_ctx* c, const char* path, const int64_t* glob
 // one line per point — x, y and the restart file's columns, default `scientific` precision — then the 1-based connectivity, all triangles
 // before all quadrilaterals as MergeConnectivity collects them (output_structure.cpp:881).
 extern "C" int rx_tecplot_write(rx_ctx* c, const char* path, const int64_t* globalIndex, const double* kOmega, int64_t nTria, const int64_t* tria,
-                                int64_t nQuad, const int64_t* quad) {
+                                int64_t nQuad, const int64_t* quad, const char* zonePrefix) {
   using namespace rx;
   if (!c || !path || (nTria > 0 && !tria) || (nQuad > 0 && !quad) || nTria < 0 || nQuad < 0) { if (c) c->err = "rx_tecplot_write: bad argument"; return RX_ERR_ARG; }
   if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_tecplot_write: one partition holds part of the zone only; merge restart pieces and post-process (SU2_SOL) instead"; return RX_ERR_UNSUPPORTED; }
@@ -185,7 +185,7 @@ extern "C" int rx_tecplot_write(rx_ctx* c, const char* path, const int64_t* glob
   h += ",\"Pressure\",\"Temperature\",\"Mach\"";
   if (visc) h += ", \"<greek>m</greek>\"";
   if (rans) h += ",\"Pressure\",\"Temperature\",\"C<sub>p</sub>\",\"Mach\", \"<greek>m</greek>\", \"C<sub>f</sub>_x\", \"C<sub>f</sub>_y\", \"h\", \"y<sup>+</sup>\", \"<greek>m</greek><sub>t</sub>\"";
-  h += "\nZONE NODES= " + std::to_string((long long)c->d.nPointDomain) + ", ELEMENTS= " + std::to_string((long long)(nTria + nQuad)) + ", DATAPACKING=POINT, ZONETYPE=FEQUADRILATERAL\n";
+  h += std::string("\nZONE ") + (zonePrefix ? zonePrefix : "") + "NODES= " + std::to_string((long long)c->d.nPointDomain) + ", ELEMENTS= " + std::to_string((long long)(nTria + nQuad)) + ", DATAPACKING=POINT, ZONETYPE=FEQUADRILATERAL\n";
   fwrite(h.data(), 1, h.size(), fo);
   int rc = restart_points(c, fo, globalIndex, kOmega, true);
   if (rc == RX_OK) {

@@ -67,7 +67,7 @@ class _Opts(C.Structure):
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
                 ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
-                ("device", C.c_int)]
+                ("device", C.c_int), ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double)]
 
 
 class _TurbOpts(C.Structure):
@@ -247,7 +247,7 @@ class CReactiveNSSolverGPU:
         self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
         ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),
                    _d(k(mesh["volume"])), _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
-        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1)
+        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0)
         od.update(opts)
         od["device"] = device
         self.opts = od
@@ -433,14 +433,15 @@ class CReactiveNSSolverGPU:
         self._ck(self.lib.rx_restart_write(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, _d(kw) if kw is not None else None,
                                            C.byref(info), int(bool(piece))))
 
-    def WriteTecplot(self, path, triangles, kOmega=None, globalIndex=None, quads=None):
+    def WriteTecplot(self, path, triangles, kOmega=None, globalIndex=None, quads=None, zone_prefix=None):
         """COutput::SetTecplotASCII (volume solution) from the device state (rx_tecplot_write); triangles [nTria][3], quads [nQuad][4], 0-based."""
         kw = _c(kOmega) if kOmega is not None else None
         gi = _c(globalIndex, np.int64) if globalIndex is not None else None
         tr = _c(triangles if triangles is not None else np.zeros((0, 3)), np.int64).reshape(-1, 3)
         qd = _c(quads if quads is not None else np.zeros((0, 4)), np.int64).reshape(-1, 4)
         self._ck(self.lib.rx_tecplot_write(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, _d(kw) if kw is not None else None,
-                                           C.c_int64(tr.shape[0]), _i(tr) if tr.shape[0] else None, C.c_int64(qd.shape[0]), _i(qd) if qd.shape[0] else None))
+                                           C.c_int64(tr.shape[0]), _i(tr) if tr.shape[0] else None, C.c_int64(qd.shape[0]), _i(qd) if qd.shape[0] else None,
+                                           zone_prefix.encode() if zone_prefix else None))
 
     def LoadRestart(self, path, globalIndex=None, nGlobal=0):
         """CReactiveNSSolver::Load_Restart + the turbulence reader (rx_restart_read): sets the conserved state from the file; returns

@@ -89,6 +89,9 @@ typedef struct {
   int secondOrder, limiter;   /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER] (MUSCL on T,u,v,P :2554-2681); limiter: 1 = VENKATAKRISHNAN (:1443-1523), 2 = BARTH_JESPERSEN as coded (:1380-1439) */
   double limCoeff, refElemLength;   /* LIMITER_COEFF, REF_ELEM_LENGTH */
   int device;               /* CUDA device ordinal */
+  int timeStepping;         /* UNSTEADY_SIMULATION = TIME_STEPPING: rx_time_step gives every point the global minimum time step (over all partitions
+                               when a communicator exists), SetTime_Step :5262-5272; inviscid contexts follow the Euler solver's variant :2121-2139 */
+  double unstCfl, deltaUnstTime;   /* UNST_CFL_NUMBER, UNST_TIMESTEP (the Euler variant replaces the CFL by the former and, when it is zero, uses the latter) */
 } rx_opts;
 
 int rx_supported_species(int Ns);            /* 1 if kernels for this species count are compiled in */
@@ -267,7 +270,8 @@ int rx_restart_write(rx_ctx*, const char* path, const int64_t* globalIndex, cons
  * nTria triangles tria[nTria][3] (point indices in the numbering of globalIndex, or local if NULL).  Single partition (a partition
  * writes a restart piece; the merged restart goes through SU2_SOL).  Byte-identical to the reference's file for the laminar case. */
 int rx_tecplot_write(rx_ctx*, const char* path, const int64_t* globalIndex, const double* kOmega, int64_t nTria, const int64_t* tria,
-                     int64_t nQuad, const int64_t* quad /* [nQuad][4], written after the triangles */);
+                     int64_t nQuad, const int64_t* quad /* [nQuad][4], written after the triangles */,
+                     const char* zonePrefix /* NULL, or what an unsteady run puts between "ZONE " and "NODES=": "STRANDID=3, SOLUTIONTIME=2e-07, " (:277-279) */);
 int rx_restart_read(rx_ctx*, const char* path, const int64_t* globalIndex, int64_t nGlobal /* points in the file; <= 0: nPointDomain */, double* kOmega, rx_restart_info* info /* may be NULL */);
 
 /* measurement hook (no reference counterpart): save (restore = 0) or restore (restore = 1) the evolving state of the context — U,

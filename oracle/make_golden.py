@@ -197,6 +197,20 @@ SPECS = {
                                     MARKER_SUPERSONIC_INLET="( inlet, 520.0, 101325.0, 700.0, 5.0, 0.0 )", MARKER_SUPERSONIC_OUTLET="( outlet )",
                                     RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
                                     TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.05"), 2, 1, 73, True),
+    # UNSTEADY_SIMULATION= TIME_STEPPING: every point advances with the global minimum time step (SetTime_Step :5262-5272); the Euler solver's
+    # variant (:2121-2139) also swaps the CFL for UNST_CFL_NUMBER after the first call and takes UNST_TIMESTEP when that is zero
+    "channel_lam_unsteady": (dict(nx=41, ny=21, stretch=1.5),
+                             dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="3", KIND_TURB_MODEL="NONE", IGNITION="NO", UNSTEADY_SIMULATION="TIME_STEPPING",
+                                  UNST_CFL_NUMBER="0.1", UNST_TIMESTEP="1e-7", UNST_TIME="1.0",
+                                  TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.2"), 3, 0, 79, True),
+    "channel_euler_unsteady": (dict(nx=41, ny=21, stretch=1.5),
+                               dict(CHANNEL_MARKERS, PHYSICAL_PROBLEM="REACTIVE_EULER", MARKER_ISOTHERMAL="( NONE )", MARKER_EULER="( upper_wall, lower_wall )",
+                                    RESTART_SOL="NO", EXT_ITER="3", KIND_TURB_MODEL="NONE", IGNITION="NO", UNSTEADY_SIMULATION="TIME_STEPPING",
+                                    UNST_CFL_NUMBER="0.1", UNST_TIMESTEP="1e-7", UNST_TIME="1.0", CFL_NUMBER="0.2"), 3, 0, 83, True),
+    "channel_euler_unsteady_fixed": (dict(nx=41, ny=21, stretch=1.5),
+                                     dict(CHANNEL_MARKERS, PHYSICAL_PROBLEM="REACTIVE_EULER", MARKER_ISOTHERMAL="( NONE )", MARKER_EULER="( upper_wall, lower_wall )",
+                                          RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO", UNSTEADY_SIMULATION="TIME_STEPPING",
+                                          UNST_CFL_NUMBER="0.0", UNST_TIMESTEP="2e-8", UNST_TIME="1.0", CFL_NUMBER="0.2"), 2, 0, 89, True),
     # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
     # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
     "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),

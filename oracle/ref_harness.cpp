@@ -320,6 +320,8 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"spatial_order_turb\": " << f->GetSpatialOrder_Turb()
      << ", \"grad_method\": " << f->GetKind_Gradient_Method() << ", \"time_scheme\": " << f->GetKind_TimeIntScheme_Flow()
      << ", \"kind_inlet\": " << f->GetKind_Inlet()
+     << ", \"time_stepping\": " << (f->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0) << ", \"unst_cfl\": " << f->GetUnst_CFL()
+     << ", \"unst_dt\": " << f->GetDelta_UnstTime()
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
      << ", \"limiter_kind\": " << f->GetKind_SlopeLimit_Flow() << ", \"limiter_coeff\": " << f->GetLimiterCoeff()
      << ", \"ref_elem_length\": " << f->GetRefElemLength() << ", \"limiter_iter\": " << f->GetLimiterIter()

@@ -64,6 +64,8 @@ typedef struct {
   double prandtlLam, prandtlTurb, lewisTurb, cMu, pasrLb, tkeInf;
   int secondOrder, limiter;            /* SPATIAL_ORDER_FLOW = 2ND_ORDER[_LIMITER]; limiter: 1 = VENKATAKRISHNAN */
   double limCoeff, refElemLength;      /* LIMITER_COEFF, REF_ELEM_LENGTH */
+  int timeStepping;                    /* UNSTEADY_SIMULATION = TIME_STEPPING: every point advances with the global minimum time step */
+  double unstCfl, deltaUnstTime;       /* UNST_CFL_NUMBER, UNST_TIMESTEP (read by the Euler solver's variant only) */
 } rxo_opts;
 
 rxo_ctx* rxo_create(const rxo_mesh*, const rxo_chem*, const rxo_opts*);

@@ -88,7 +88,8 @@ class _Opts(C.Structure):
                 ("fuelIndex", C.c_int), ("oxidizerIndex", C.c_int),
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
-                ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double)]
+                ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
+                ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double)]
 
 
 def chem_arrays(case):
@@ -115,7 +116,8 @@ def opts_dict(case):
                 prandtlTurb=cf["prandtl_turb"], lewisTurb=cf["lewis_turb"], cMu=cf["c_mu"], pasrLb=cf["pasr_lb"],
                 tkeInf=cf["tke_inf"], secondOrder=cf.get("second_order", 0),
                 limiter=(2 if cf.get("limiter_kind", 0) == 1 else 1) if cf.get("limiter", 0) else 0,   # 1 VENKATAKRISHNAN, 2 BARTH_JESPERSEN
-                limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1))
+                limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1),
+                timeStepping=cf.get("time_stepping", 0), unstCfl=cf.get("unst_cfl", 0.0), deltaUnstTime=cf.get("unst_dt", 0.0))
 
 
 def marker_list(case):

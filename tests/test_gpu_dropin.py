@@ -20,7 +20,8 @@ RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2
         "channel_lam_walls": (2, 19), "channel_lam_muscl": (2, 23), "channel_lam_bj": (2, 29), "channel_rans_gg": (2, 37),
         "channel_air3_rans": (2, 59), "channel_mix5_lam": (2, 61),   # the reference's 3- and 5-species mixtures
         "channel_lam_inlet_total": (2, 67), "channel_rans_inlet_massflow": (2, 71),   # INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW
-        "channel_lam_supersonic": (2, 73)}   # MARKER_SUPERSONIC_INLET / _OUTLET
+        "channel_lam_supersonic": (2, 73),   # MARKER_SUPERSONIC_INLET / _OUTLET
+        "channel_lam_unsteady": (3, 79), "channel_euler_unsteady": (3, 83), "channel_euler_unsteady_fixed": (2, 89)}   # TIME_STEPPING
 CASE_ENV = {"channel_lam_inlet_total": {"RX_PERTURB_TAMP": "0", "RX_PERTURB_NOISE": "0"}}   # oracle/make_golden.py ENVS
 TOL_FIRST = 1e-12     # first iteration: identical inputs on both sides
 TOL_CHAINED = 1e-12   # later iterations too: with the glibc-exact exp / pow (csrc/rx_libm.cuh) the laminar chains are bit-identical
@@ -54,13 +55,18 @@ def test_reference_driver_with_cuda_solver(name, turb_post, turb_dev, tmp_path):
                                                      SU2_RX_TURB="device" if turb_dev else "host"))
     assert "CReactiveNSSolverGPU" in txt and (("CTurbSSTSolverGPU" in txt) == turb_dev)
     # restart file: the reference's COutput (fed by the subclass's host mirrors) and the subclass's own device writer, same run
+    def _pair(stem):   # the reference's file (an unsteady run appends the time iteration: restart_flow_00002.dat) and the subclass's
+        import glob
+        ref = [f for f in glob.glob(os.path.join(d, stem + "*.dat")) if not f.endswith("_gpu.dat")]
+        assert len(ref) == 1, ref
+        a = open(ref[0], "rb").read(); b = open(os.path.join(d, stem + "_gpu.dat"), "rb").read()
+        os.remove(ref[0]); os.remove(os.path.join(d, stem + "_gpu.dat"))
+        return a, b
     if "rx_restart_write" in txt:
-        a = open(os.path.join(d, "restart_flow.dat"), "rb").read(); b = open(os.path.join(d, "restart_flow_gpu.dat"), "rb").read()
-        os.remove(os.path.join(d, "restart_flow.dat")); os.remove(os.path.join(d, "restart_flow_gpu.dat"))
+        a, b = _pair("restart_flow")
         assert a == b, "rx_restart_write differs from COutput::SetRestart on the same state"
     if "rx_tecplot_write" in txt:   # likewise the Tecplot volume file: COutput::SetTecplotASCII and the subclass's WriteTecplot
-        a = open(os.path.join(d, "flow.dat"), "rb").read(); b = open(os.path.join(d, "flow_gpu.dat"), "rb").read()
-        os.remove(os.path.join(d, "flow.dat")); os.remove(os.path.join(d, "flow_gpu.dat"))
+        a, b = _pair("flow")
         assert a == b, "rx_tecplot_write differs from COutput::SetTecplotASCII on the same state"
     _run(HARNESS_CPU, d, out_c, nit, seed, dict(os.environ, **CASE_ENV.get(name, {})))
     case = Case(os.path.join(GOLDEN, name + ".npz"))

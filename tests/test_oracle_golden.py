@@ -21,7 +21,9 @@ CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_la
          # the other two kinds of BC_Inlet (INLET_TYPE= TOTAL_CONDITIONS / MASS_FLOW, solver_direct_reactive.cpp:3283-3465)
          "channel_lam_inlet_total", "channel_rans_inlet_massflow",
          # BC_Supersonic_Inlet / BC_Supersonic_Outlet (:2998-3214, :3681-3807)
-         "channel_lam_supersonic"]
+         "channel_lam_supersonic",
+         # UNSTEADY_SIMULATION= TIME_STEPPING (global minimum time step; the Euler solver's CFL swap and fixed UNST_TIMESTEP)
+         "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed"]
 TOL = 0.0
 
 
