@@ -326,7 +326,10 @@ void CReactiveNSSolverGPU::SetTime_Step(CGeometry* geometry, CSolver** solver_co
   // MultiGrid_Cycle calls the (non-virtual) CSolver::Set_OldSolution immediately before SetTime_Step at RK stage 0
   // (integration_time.cpp:158-163); the device copy of U_old is taken here, at the same point of the sequence.
   Check(rx_set_old_solution(ctx), "rx_set_old_solution");
+  Check(rx_set_cfl(ctx, config->GetCFL(iMesh)), "rx_set_cfl");   // read at every call, as the reference does: CFL_ADAPT changes it between iterations
   Check(rx_time_step(ctx), "rx_time_step");
+  // the Euler solver's SetTime_Step replaces the CFL by UNST_CFL_NUMBER in a time-accurate run (:2129); the library did the same inside
+  if (!viscousMode && config->GetUnsteady_Simulation() == TIME_STEPPING) config->SetCFL(iMesh, config->GetUnst_CFL());
   if (mirror >= 2 || (mirror >= 1 && ransMode)) MirrorTimeStep();   // the SST implicit step uses the flow time step
 }
 

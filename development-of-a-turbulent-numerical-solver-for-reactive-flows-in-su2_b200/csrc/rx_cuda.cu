@@ -877,6 +877,11 @@ int rx_set_old_solution(rx_ctx* c) {
   return RX_OK;
 }
 
+int rx_set_cfl(rx_ctx* c, double cfl) {
+  if (!(cfl >= 0.0)) { c->err = "rx_set_cfl: the CFL number must be non-negative"; return RX_ERR_ARG; }
+  c->o.cfl = cfl;
+  return RX_OK;
+}
 int rx_time_step(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;

@@ -104,7 +104,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write",
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -452,6 +452,11 @@ class CReactiveNSSolverGPU:
         self._ck(self.lib.rx_restart_read(self.ctx, os.fsencode(path), _i(gi) if gi is not None else None, C.c_int64(nGlobal),
                                           _d(kw) if kw is not None else None, C.byref(info)))
         return kw, dict(aoa=info.aoa, sideslip=info.sideslip, bcThrust=info.bcThrust, dCD_dCL=info.dCD_dCL, extIter=info.extIter)
+
+    def SetCFL(self, cfl):
+        """config->SetCFL between iterations (CFL_ADAPT): the value SetTime_Step reads from now on (rx_set_cfl)."""
+        self._ck(self.lib.rx_set_cfl(self.ctx, C.c_double(cfl)))
+        self.opts["cfl"] = float(cfl)
 
     def SaveState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 0))
     def RestoreState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 1))

@@ -152,6 +152,8 @@ int rx_get_limiter(rx_ctx*, double* lim4);                /* [nPoint][4]: Limite
 int rx_preprocess(rx_ctx*, int64_t extIter, int output, int64_t* nonPhysical /* may be NULL: no host sync */);  /* Preprocessing :4693 */
 int rx_set_old_solution(rx_ctx*);                         /* CSolver::Set_OldSolution, solver_structure.inl:898 */
 int rx_time_step(rx_ctx*);                                /* SetTime_Step :5057 */
+int rx_set_cfl(rx_ctx*, double cfl);                      /* config->GetCFL(iMesh) as SetTime_Step reads it at every call: CFL_ADAPT (COutput::SetCFL_Number,
+                                                              output_structure.cpp:5990-6030, driver_structure.cpp:2804) changes it between iterations */
 int rx_residual_conv(rx_ctx*);                            /* Upwind_Residual :2535 */
 int rx_residual_visc(rx_ctx*);                            /* Viscous_Residual :5305 */
 int rx_residual_source(rx_ctx*);                          /* Source_Residual :2792 */

@@ -95,3 +95,23 @@ def test_qr_hook_handles_empty_input():
     pk = load_package()
     xs, xp = pk.qr_eval(np.zeros((0, 81)), np.zeros((0, 2, 9)))
     assert xs.shape == (0, 2, 9) and xp.shape == (0, 2, 9)
+
+
+def test_cfl_can_change_between_iterations_as_cfl_adapt_does():
+    """rx_set_cfl (config->SetCFL by COutput::SetCFL_Number, driver_structure.cpp:2804): the time step of the next SetTime_Step equals
+    the one of a context created with that CFL, bit for bit; a negative value is refused."""
+    pk = load_package()
+    a, mesh = _ctx(pk, False)
+    chem = pk.load_mechanism()
+    b = pk.CReactiveNSSolverGPU(mesh, chem, pk.default_opts(rans=False, cfl=0.37))
+    U, T, tb = pk.synthetic_state(mesh, chem, seed=5, rans=False)
+    b.SetSolution(U); b.SetTemperature(T); b.SetTurbulence(tb)
+    for s in (a, b):
+        s.Preprocessing(1, False, count_nonphysical=False)
+    a.SetTime_Step(); dt0 = a.dt()[:, 0].copy()
+    a.SetCFL(0.37)
+    a.SetTime_Step(); b.SetTime_Step()
+    assert np.array_equal(a.dt(), b.dt()) and not np.array_equal(a.dt()[:, 0], dt0)
+    with pytest.raises(pk.RxError):
+        a.SetCFL(-1.0)
+    a.close(); b.close()
