@@ -35,6 +35,10 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
     throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN and BARTH_JESPERSEN limiters are on the CUDA path");
   if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
+  // every *_Ref is 1 on the CUDA path, as in all shipped cfgs (REF_DIMENSIONALIZATION= DIMENSIONAL, SI units: solver_direct_reactive.cpp:846-887)
+  if (config->GetRef_NonDim() != DIMENSIONAL) throw std::runtime_error("CReactiveNSSolverGPU: REF_DIMENSIONALIZATION other than DIMENSIONAL is not on the CUDA path");
+  if (config->GetViscous_Limiter_Flow()) throw std::runtime_error("CReactiveNSSolverGPU: VISCOUS_LIMITER_FLOW (limited gradients in vorticity / strain) is not on the CUDA path");
+  if (config->GetSystemMeasurements() == US) throw std::runtime_error("CReactiveNSSolverGPU: SYSTEM_MEASUREMENTS= US is not on the CUDA path");
   // A partitioned geometry needs the device halo exchange behind Set_MPI_Solution / _Primitive_Gradient / _Primitive_Limiter
   // (solver_reactive.hpp:162,176,183), which this class does not override: the base class would exchange host node[] only and the
   // device halos would go stale without any error.  Refuse instead (the Python host, parallel.py, drives partitioned runs).
