@@ -76,6 +76,36 @@ def turb_mode(rank, world, local, dev, chem):
         print("NCCL_WORKER mode turb ranks %d | %s | %s" % (world, " | ".join(report), "OK" if ok else "FAIL"))
 
 
+def unsteady_mode(rank, world, local, dev, chem):
+    """UNSTEADY_SIMULATION= TIME_STEPPING on partitions: the global minimum time step is the minimum over ALL partitions (one ncclAllReduce
+    with ncclMin inside rx_time_step, SetTime_Step :5264-5269), so two iterations of a partitioned run equal the single-partition run."""
+    opts = dict(pk.default_opts(rans=False, cfl=0.1), timeStepping=1, unstCfl=0.1, deltaUnstTime=1e-7)
+    nx, ny = 61, 23
+    g = pk.channel_mesh(nx, ny)
+    m, plan = pk.channel_strip_mesh(nx, ny, rank, world)
+    glob = plan["glob"][1] * nx + plan["glob"][0]
+    Ug, Tg, tg = pk.synthetic_state(g, chem, seed=3, rans=False)
+    s = pk.CReactiveNSSolverGPU(m, chem, opts, device=local)
+    s.SetSolution(Ug[glob]); s.SetTemperature(Tg[glob]); s.SetTurbulence(tg[glob])
+    par.library_comm_init(s, plan, dev)
+    ref = pk.CReactiveNSSolverGPU(g, chem, opts, device=local)
+    ref.SetSolution(Ug); ref.SetTemperature(Tg); ref.SetTurbulence(tg)
+    alphas = [0.66667, 0.66667, 1.0]
+    for it in range(2):
+        s.Iterate(it + 1, alphas); ref.Iterate(it + 1, alphas)
+    n = s.nPointDomain
+    dt_p, dt_r = s.dt()[:n, 0], ref.dt()[:, 0]
+    same_dt = bool(np.all(dt_p == dt_p[0]) and np.all(dt_r == dt_r[0]) and dt_p[0] == dt_r[0])
+    Ur = ref.solution()[glob[:n]]
+    err = float((np.abs(s.solution()[:n] - Ur).max(axis=0) / np.abs(Ur).max(axis=0)).max())
+    t = torch.tensor([0.0 if same_dt else 1.0, err], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    s.close(); ref.close()
+    if rank == 0:
+        ok = float(t[0]) == 0.0 and float(t[1]) <= 1e-12
+        print("NCCL_WORKER mode unsteady ranks %d dt_equal %s worst %.3e %s" % (world, float(t[0]) == 0.0, float(t[1]), "OK" if ok else "FAIL"))
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -83,8 +113,8 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     chem = pk.load_mechanism()
     mode = sys.argv[1] if len(sys.argv) > 1 else "strips"
-    if mode == "turb":
-        turb_mode(rank, world, local, dev, chem)
+    if mode in ("turb", "unsteady"):
+        (turb_mode if mode == "turb" else unsteady_mode)(rank, world, local, dev, chem)
         dist.destroy_process_group()
         return
     worst = 0.0

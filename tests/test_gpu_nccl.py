@@ -13,7 +13,7 @@ from rxcase import ROOT
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", ["strips", "graph", "turb"])
+@pytest.mark.parametrize("mode", ["strips", "graph", "turb", "unsteady"])
 def test_partitioned_run_with_library_side_exchange_equals_single(mode):
     import torch
     n = torch.cuda.device_count()
