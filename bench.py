@@ -72,10 +72,38 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+_ALL_CPUS = None   # affinity of the process at start (bind_to_gpu_numa narrows it for the GPU arm; the CPU reference gets all of it back)
+
+
+def bind_to_gpu_numa(local):
+    """Multi-GPU runs: keep this rank (and the pinned host buffers it allocates) on the CPUs NVML reports as local to its GPU, so that
+    eight ranks do not pull 8 x 416 MB per step through one socket's memory.  Returns a note for the JSON line, or None."""
+    global _ALL_CPUS
+    try:
+        import pynvml
+        import torch
+        _ALL_CPUS = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local)
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        ncpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {i for i in range(ncpu) if (mask[i // 64] >> (i % 64)) & 1} & _ALL_CPUS
+        if cpus and cpus != _ALL_CPUS:
+            os.sched_setaffinity(0, cpus)
+            return "rank bound to the %d CPUs NVML reports as local to its GPU" % len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def run_reference(steps, warmup, procs=None):
     """Times oracle/_ref/ref_harness (the reference's CReactiveNSSolver & co.) on the bounded bench case."""
     if not (os.path.exists(HARNESS) and os.path.isdir(REF_CASE)):
         return None
+    if _ALL_CPUS:
+        os.sched_setaffinity(0, _ALL_CPUS)   # the CPU arm uses the whole host, whatever the GPU arm bound itself to
     procs = procs or min(physical_cores(), REF_PROCS)
     nit = warmup + steps
     tmp = tempfile.mkdtemp(prefix="rxref_")
@@ -592,6 +620,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_note = bind_to_gpu_numa(local) if world > 1 else None
     dev = torch.device("cuda", local)
     if world > 1:
         import torch.distributed as dist
@@ -689,7 +718,8 @@ def main():
                    "cache": "inputs larger than L2 (state ~%.1f GB per GPU vs 126 MB L2); no flush needed" % (m["nPoint"] * 8 * 160 / 1e9),
                    "timed_state": "every timed step is the same iteration from the same state: the state after the warm-up iterations, restored device-to-device "
                                   "(rx_state_snapshot) before each step, outside the CUDA events; ms_per_step = mean of the per-step event times",
-                   "partition": ("k-way graph partition (rx_partition_kway) with RCM numbering" if a.partition == "graph" else "strips in x") + ", one halo layer; halo U and gradients by ncclSend/ncclRecv inside the library (rx_halo_exchange), norms by one ncclAllReduce" if world > 1 else "single partition"},
+                   "partition": ("k-way graph partition (rx_partition_kway) with RCM numbering" if a.partition == "graph" else "strips in x") + ", one halo layer; halo U and gradients by ncclSend/ncclRecv inside the library (rx_halo_exchange), norms by one ncclAllReduce" if world > 1 else "single partition",
+                   "host_affinity": numa_note},
         "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "updates/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8), "d2h_bytes_per_step": int(m["nPoint"] * m["nVar"] * 8 + m["nVar"] * 8),
                 "what": "same iteration from the same state as `value`: conserved state H2D from pinned host memory (rx_set_solution), rx_iterate, residual norms and the UPDATED conserved state D2H to pinned host memory (rx_get_solution)"},
