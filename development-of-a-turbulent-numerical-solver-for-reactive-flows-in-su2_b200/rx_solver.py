@@ -17,6 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "librx_cuda.so")
 CSRC = os.path.join(HERE, "csrc")
 HOST_PARTITION = os.path.join(CSRC, "host", "rx_partition.cpp")   # host-only graph tools of the same library
+HOST_GEOMETRY = os.path.join(CSRC, "host", "rx_geometry.cpp")     # host-only dual-mesh builder
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
@@ -28,11 +29,11 @@ class RxError(RuntimeError):
 
 def build_library(force=False, verbose=False):
     """nvcc cross-compiles the CUDA extension for sm_100a (works without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + [HOST_PARTITION]
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + [HOST_PARTITION, HOST_GEOMETRY]
     srcs.append(os.path.join(os.path.dirname(HERE), "include", "rx_cuda.h"))
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "rx_cuda.cu"), HOST_PARTITION]
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "rx_cuda.cu"), HOST_PARTITION, HOST_GEOMETRY]
     subprocess.check_call(cmd)
     return LIB_PATH
 
@@ -104,7 +105,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl",
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl", "rx_dual_mesh_tri", "rx_dual_mesh_free",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -191,6 +192,31 @@ def qr_eval(A, b, device=0):
     if rc != 0:
         raise RxError("rx_qr_eval failed (%d): %s" % (rc, L.rx_last_error(None).decode()))
     return xs, xp
+
+
+class _DualMesh(C.Structure):
+    _fields_ = [("nEdge", C.c_int64), ("edgeNodes", C.POINTER(C.c_int64)), ("edgeNormal", C.POINTER(C.c_double)), ("volume", C.POINTER(C.c_double)),
+                ("nbPtr", C.POINTER(C.c_int64)), ("nbPoint", C.POINTER(C.c_int64))]
+
+
+def dual_mesh_tri(coord, tri):
+    """Median-dual mesh of a triangulation by the library's host builder (rx_dual_mesh_tri): dict with nEdge, edgeNodes, edgeNormal,
+    volume, nbPtr, nbPoint (numpy copies; the library's buffers are released)."""
+    L = load_library()
+    coord = _c(coord); tri = _c(tri, np.int64)
+    nP, nT = coord.shape[0], tri.shape[0]
+    dm = _DualMesh()
+    L.rx_dual_mesh_free.restype = None
+    rc = L.rx_dual_mesh_tri(C.c_int64(nP), _d(coord), C.c_int64(nT), _i(tri), C.byref(dm))
+    if rc != 0:
+        raise RxError("rx_dual_mesh_tri failed (%d)" % rc)
+    try:
+        nE = int(dm.nEdge)
+        A = lambda p, n, shape: np.ctypeslib.as_array(p, shape=(n,)).reshape(shape).copy()
+        return dict(nEdge=nE, edgeNodes=A(dm.edgeNodes, 2 * nE, (nE, 2)), edgeNormal=A(dm.edgeNormal, 2 * nE, (nE, 2)), volume=A(dm.volume, nP, (nP,)),
+                    nbPtr=A(dm.nbPtr, nP + 1, (nP + 1,)), nbPoint=A(dm.nbPoint, 2 * nE, (2 * nE,)))
+    finally:
+        L.rx_dual_mesh_free(C.byref(dm))
 
 
 def comm_unique_id():

@@ -253,6 +253,22 @@ int rx_partition_backend(void);   /* 1: rx_partition_kway calls METIS_PartGraphK
                                     (also forced by RX_PARTITIONER=own) */
 int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t* nbPtr, const int64_t* nbPoint, int64_t* newToOld);
 
+/* geometry (host-side, no device work; csrc/host/rx_geometry.cpp).
+ * rx_dual_mesh_tri: the median-dual mesh of a triangulated 2-D point set — what CGeometry::SetEdges and CPhysicalGeometry::SetControlVolume
+ * (Common/src/geometry_structure.cpp:10457) leave in edge[] / node[]: edges (lower, higher point) in that order, edge normals, dual volumes
+ * and the point-to-point CSR sorted by neighbour index — as flat arrays in the layout of rx_mesh.  The arrays are malloc'ed by the
+ * library; release them with rx_dual_mesh_free. */
+typedef struct {
+  int64_t nEdge;
+  int64_t* edgeNodes;   /* [nEdge][2] */
+  double* edgeNormal;   /* [nEdge][2] */
+  double* volume;       /* [nPoint]   */
+  int64_t* nbPtr;       /* [nPoint+1] */
+  int64_t* nbPoint;     /* [2 nEdge]  */
+} rx_dual_mesh;
+int rx_dual_mesh_tri(int64_t nPoint, const double* coord /* [nPoint][2] */, int64_t nTri, const int64_t* tri /* [nTri][3] */, rx_dual_mesh* out);
+void rx_dual_mesh_free(rx_dual_mesh*);
+
 /* SU2 native ASCII restart files straight from / into the device-resident state (csrc/rx_restart.cuh).
  * rx_restart_write replaces COutput::SetRestart for the reactive solvers (output_structure.cpp:3858-4060; columns of MergeSolution
  * :1991-2130): "PointID" x y Conservative_1..nVar [k omega] Pressure Temperature Mach [Laminar_Viscosity [mu_t]], every value as

@@ -126,3 +126,36 @@ def test_strip_renumbering_short_side_slow_is_the_same_mesh_with_shorter_sweep_c
         return int(lev.max()) + 1
     la, lb = levels(m), levels(m2)
     assert lb < 0.7 * la, (la, lb)
+
+
+def test_native_dual_mesh_builder_equals_the_numpy_specification_bit_for_bit():
+    """rx_dual_mesh_tri (csrc/host/rx_geometry.cpp: per-point buckets, one linear pass per array) against the numpy statements of
+    mesh.dual_mesh, which restate CPhysicalGeometry::SetControlVolume (geometry_structure.cpp:10457): edges, normals, volumes, neighbour
+    CSR and the boundary arrays derived from them, on stretched and jittered channels with shuffled element order and orientation."""
+    import importlib
+    import numpy as np
+    from rxcase import load_package
+    pk = load_package()
+    mm = importlib.import_module(pk.__name__ + ".mesh")
+    rng = np.random.default_rng(3)
+    for nx, ny, st in [(41, 21, 1.5), (7, 5, 1.0), (64, 33, 1.0), (3, 3, 1.0)]:
+        coord = mm.channel_points(nx, ny, stretch=st)
+        inner = np.ones(nx * ny, dtype=bool).reshape(ny, nx); inner[0, :] = inner[-1, :] = False; inner[:, 0] = inner[:, -1] = False
+        ys = np.unique(coord[:, 1])
+        jit = (rng.random(coord.shape) - 0.5) * 0.2 * min(0.25 / nx, np.diff(ys).min())   # small against every spacing: no element inverts
+        coord = coord + jit * inner.ravel()[:, None]                      # interior points jittered: no two contributions are equal by symmetry
+        tri = mm.channel_triangles(nx, ny)
+        tri = tri[rng.permutation(len(tri))]
+        roll = rng.integers(0, 3, len(tri))
+        tri = np.stack([tri[np.arange(len(tri)), (roll + k) % 3] for k in range(3)], axis=1)   # same orientation, another first node
+        bnd = mm.channel_boundaries(nx, ny)
+        a = mm.dual_mesh(coord, tri, bnd, native=True); b = mm.dual_mesh(coord, tri, bnd, native=False)
+        for k in ["nEdge", "edgeNodes", "edgeNormal", "volume", "nbPtr", "nbPoint"]:
+            assert np.array_equal(a[k], b[k]), (nx, ny, k)
+        for ma, mb in zip(a["markers"], b["markers"]):
+            for k in ["node", "normalNeighbor", "normal"]:
+                assert np.array_equal(ma[k], mb[k]), (nx, ny, ma["tag"], k)
+        assert abs(a["volume"].sum() - 0.25 * 0.025) <= 1e-12 * 0.25 * 0.025   # the dual volumes tile the channel
+    L = pk.load_library()
+    import ctypes as C
+    assert L.rx_dual_mesh_tri(C.c_int64(0), None, C.c_int64(0), None, None) != 0   # argument errors are statuses, not crashes
