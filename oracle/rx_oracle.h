@@ -99,6 +99,12 @@ int rxo_bicgstab(int n, const double* A /*col-major*/, const double* rhs, double
 void rxo_colpiv_qr_solve(int n, const double* A /*col-major*/, const double* b, double* x);
 double rxo_spline(const rxo_chem*, int prop, int species, double T);
 
+/* SST transport step restated (CTurbSSTSolver's SingleGrid_Iteration on the context's flow state; see rx_oracle.cpp): kw[nPoint][2],
+ * blend3[nPoint][3] = F1, F2, CDkw of the previous Postprocessing, dist[nPoint]; outputs (any may be NULL): res2 = LinSysRes before the solve,
+ * dx2 = LinSysSol, rms2[2], linIters, post12[nPoint][12] = the state after Postprocessing. */
+int rxo_turb_iterate(rxo_ctx*, const double* kw, const double* blend3, const double* dist, double sigmaK, double kineInf, double omegaInf,
+                     double cflRed, double relax, int linIter, double linTol, double* res2, double* dx2, double* rms2, int* linIters, double* post12);
+
 #ifdef __cplusplus
 }
 #endif

@@ -210,6 +210,17 @@ class Oracle:
         self.lib.rxo_turb_postprocess(self.ctx, _p(kw), _p(dist), _p(f3) if f3 is not None else None, C.c_double(sigma_k), _p(out))
         return out
 
+    def turb_iterate(self, kw, blend3, dist, sigma_k, kine_inf, omega_inf, cfl_red, relax, lin_iter, lin_tol):
+        """rxo_turb_iterate: one SingleGrid_Iteration of the SST solver on the context's flow state -> dict(res, dx, rms, iters, post)."""
+        kw = np.ascontiguousarray(kw, dtype=np.float64); bl = np.ascontiguousarray(blend3, dtype=np.float64); dist = np.ascontiguousarray(dist, dtype=np.float64)
+        n = kw.shape[0]
+        res = np.empty((n, 2)); dx = np.empty((n, 2)); rms = np.empty(2); post = np.empty((n, 12)); it = C.c_int(0)
+        self.lib.rxo_turb_iterate.restype = C.c_int
+        rc = self.lib.rxo_turb_iterate(self.ctx, _p(kw), _p(bl), _p(dist), C.c_double(sigma_k), C.c_double(kine_inf), C.c_double(omega_inf), C.c_double(cfl_red),
+                                       C.c_double(relax), C.c_int(lin_iter), C.c_double(lin_tol), _p(res), _p(dx), _p(rms), C.byref(it), _p(post))
+        assert rc == 0
+        return dict(res=res, dx=dx, rms=rms, iters=it.value, post=post)
+
     def set_turbulence(self, t):
         t = np.ascontiguousarray(t, dtype=np.float64); self.lib.rxo_set_turbulence(self.ctx, _p(t))
 

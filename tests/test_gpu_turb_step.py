@@ -12,7 +12,7 @@ import pytest
 from rxcase import Case, GOLDEN, gpu_solver
 
 pytestmark = pytest.mark.gpu
-CASES = ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed"]
+CASES = ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed", "channel_air3_rans", "channel_rans_inlet_massflow"]
 
 
 def colerr(a, ref):

@@ -93,6 +93,44 @@ def test_bicgstab_restatement_zero_rhs_and_identity():
     assert it.value == 1 and np.allclose(x, rhs / 2.0, rtol=1e-15)
 
 
+@pytest.mark.parametrize("name", ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed",
+                                  "channel_air3_rans", "channel_rans_inlet_massflow"])
+def test_oracle_sst_transport_step_matches_reference(name):
+    """rxo_turb_iterate — the restatement of CTurbSSTSolver's SingleGrid_Iteration (residuals, boundary conditions, FGMRES + LU-SGS in the
+    reference's own order of operations, clipped update, Postprocessing) — against the harness dumps of the reference's turbulence solver
+    after every dumped flow iteration: tres (LinSysRes before the solve), tdx (LinSysSol), tsol ((k, omega) after the update), trms, tpost."""
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    cf = case.meta["cfg"]
+    nrk = cf["nRK"] if cf["time_scheme"] == 1 else 1
+    its = sorted({int(k[2:6]) for k in case.arr if k.startswith("it") and k.endswith("_tres")})
+    assert its
+    o = Oracle(case)
+    worst = {}
+    for it in its:
+        tpost = case.stage(it, 0, "tpost")
+        o.set_solution(case.stage(it, 0, "U0")); o.set_temperature(case.stage(it, 0, "prev_V")[:, 0]); o.set_turbulence(case.stage(it, 0, "turb"))
+        for rk in range(nrk):
+            o.preprocess(it, False)
+            if rk == 0:
+                o.set_old_solution(); o.time_step()
+            o.upwind_residual(); o.viscous_residual(); o.source_residual(); o.boundary_conditions()
+            o.explicit_update(cf["rk_alpha"][rk] if nrk > 1 else 1.0)
+        o.preprocess(it, True)
+        r = o.turb_iterate(case.stage(it, 0, "turb")[:, 1:3], case.stage(it, 0, "tblend"), tpost[:, 2], float(tpost[0, 11]), cf["kine_inf"], cf["omega_inf"],
+                           cf["cfl_red_turb"], cf["relax_turb"], cf["lin_iter"], cf["lin_tol"])
+        nD = case.nPointDomain
+        def col(a, ref):
+            sc = np.abs(ref).max(axis=0)
+            return float((np.abs(a - ref).max(axis=0) / np.where(sc > 0, sc, 1.0)).max())
+        e = {"tres": col(r["res"][:nD], case.stage(it, 0, "tres")[:nD]), "tdx": col(r["dx"][:nD], case.stage(it, 0, "tdx")[:nD]),
+             "tsol": col(r["post"][:nD, 0:2], case.stage(it, 0, "tsol")[:nD]), "trms": float(np.abs(r["rms"] / case.stage(it, 0, "trms") - 1.0).max()),
+             "tpost": col(r["post"][:nD], tpost[:nD])}
+        for k, v in e.items():
+            worst[k] = max(worst.get(k, 0.0), v)
+    print(name, worst)
+    assert all(v == 0.0 for v in worst.values()), worst   # the restatement follows the reference's order of operations: identical bits
+
+
 def test_qr_restatement_equals_eigen_bit_for_bit():
     """oracle/_ref/eigen_qr_check (built by oracle/build_ref.sh against the Eigen headers the reference vendors): the oracle's
     colPivQRSolve against Eigen::ColPivHouseholderQR<MatrixXd>::solve on the SST closure's operator for random compositions, dense
