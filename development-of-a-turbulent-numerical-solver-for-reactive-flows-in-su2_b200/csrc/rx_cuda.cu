@@ -66,6 +66,7 @@ struct rx_ctx {
   double* eddyFlow = nullptr;       // RANS: eddy viscosity as the flow variables hold it (copied at every rx_preprocess, CReactiveNSVariable::SetPrimVar :1193) — what COutput writes
   double* tpost = nullptr;          // SST Postprocessing fields (rx_turb.cuh), allocated for RANS contexts
   bool haveWallDist = false; double sigmaK = 0.85;
+  int sweepThreads = 1024;           // block size of the LU-SGS sweep kernels (test hook RX_SWEEP_THREADS: a small block sends the levels through the wide-level loop)
   double* dtPartial = nullptr; int dtBlocks = 0;   // TIME_STEPPING: block minima of the local time steps + the global one
 };
 
@@ -588,6 +589,7 @@ static int turb_step_setup(rx_ctx* c, int m) {
     build(true, c->swF, c->sdF);
     build(false, c->swB, c->sdB);
     if (c->allocFailed) { c->err = "rx_turb_iterate: device allocation failed"; return RX_ERR_CUDA; }
+    if (const char* ev = getenv("RX_SWEEP_THREADS")) { const int t = atoi(ev); if (t >= 32 && t <= 1024 && t % 32 == 0) c->sweepThreads = t; }
     c->turbStepReady = true;
   }
   while ((int)c->kw.size() < m + 1) {
@@ -683,7 +685,7 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   c->launches += 2;
   auto precond = [&](const double* in, double* out) -> int {
     k_turb_perm_in<<<nblk(n, 256), 256, 0, s>>>(c->swF.perm, n, d.np, in, c->sdF.bL);
-    k_turb_sweep<false><<<2, 1024, 0, s>>>(c->swF, c->sdF, n);
+    k_turb_sweep<false><<<2, c->sweepThreads, 0, s>>>(c->swF, c->sdF, n);
     if (par && d.nPoint > n) {   // x* of the neighbours' points -> the halo tail of the backward list (SendReceive_Solution between the sweeps, :1689)
       k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swF.perm, n, n, d.np, c->sdF.xL, out);
       const int e = halo_exchange_field(c, out, 2, false, s);
@@ -692,7 +694,7 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
       c->launches += 2;
     }
     k_turb_perm_ab<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, c->posF, n, c->swB.nX, c->sdF.xL, c->sdB.xL);
-    k_turb_sweep<true><<<2, 1024, 0, s>>>(c->swB, c->sdB, n);
+    k_turb_sweep<true><<<2, c->sweepThreads, 0, s>>>(c->swB, c->sdB, n);
     k_turb_perm_out<<<nblk(n, 256), 256, 0, s>>>(c->swB.perm, n, c->swB.nX, d.np, c->sdB.xL, out);
     c->launches += 5;
     return par ? halo_exchange_field(c, out, 2, false, s) : RX_OK;   // the matrix-vector product reads the neighbours' entries (:1707)

@@ -50,3 +50,50 @@ def test_sst_step_matches_reference(name):
     print(name, {k: float("%.2e" % v) for k, v in worst.items()})
     assert worst["tres"] <= 1e-12 and worst["trms"] <= 1e-12, worst
     assert worst["tdx"] <= 1e-10 and worst["tsol"] <= 1e-10 and worst["tpost"] <= 1e-10, worst
+
+
+def test_sst_step_on_a_larger_mesh_equals_the_oracle_and_does_not_depend_on_the_sweep_block(monkeypatch):
+    """A 160 x 90 channel (14 400 points, levels up to 45 points wide): the device step against the CPU restatement (rxo_turb_iterate,
+    pinned bit for bit to the reference on the fixtures), and once more with 32-thread sweep blocks (RX_SWEEP_THREADS), which sends every
+    level wider than the block through the loop the 16 M-point meshes use for their widest levels — same bits as the default block."""
+    from rxcase import Oracle, load_package
+    pk = load_package()
+    chem = pk.load_mechanism()
+    opts = pk.default_opts(rans=True, cfl=0.1)
+    mesh = pk.channel_mesh(160, 90)
+    U, T, tb = pk.synthetic_state(mesh, chem, seed=21, rans=True)
+    alphas = [0.66667, 0.66667, 1.0]
+
+    def gpu(threads):
+        if threads:
+            monkeypatch.setenv("RX_SWEEP_THREADS", str(threads))
+        else:
+            monkeypatch.delenv("RX_SWEEP_THREADS", raising=False)
+        s = pk.CReactiveNSSolverGPU(mesh, chem, opts)
+        s.SetSolution(U); s.SetTemperature(T); s.SetTurbulence(tb)
+        s.ComputeWall_Distance()
+        s.TurbPostprocessing(np.ascontiguousarray(tb[:, 1:3]))
+        t0 = s.GetTurbulence()
+        s.Iterate(1, alphas)
+        rms, nlin = s.TurbIterate(0.135, 2.0e3)
+        res, dx = s.TurbGetStep()
+        out = (t0, res, dx, s.GetTurbulence(), rms, nlin)
+        s.close()
+        return out
+
+    t0, res, dx, post, rms, nlin = gpu(0)
+    _t, res32, dx32, post32, rms32, nlin32 = gpu(32)
+    assert np.array_equal(dx, dx32) and np.array_equal(post, post32) and np.array_equal(res, res32) and nlin == nlin32
+    o = Oracle.from_mesh(mesh, chem, opts)
+    # the flow iteration on the device read the eddy viscosity, grad k and sigma_k its own Postprocessing formed from (k, omega)
+    turb6 = np.ascontiguousarray(np.stack([t0[:, 6], t0[:, 0], t0[:, 1], t0[:, 7], t0[:, 8], t0[:, 11]], axis=1))
+    o.set_solution(U); o.set_temperature(T); o.set_turbulence(turb6)
+    for rk in range(3):
+        o.preprocess(1, False)
+        if rk == 0:
+            o.set_old_solution(); o.time_step()
+        o.upwind_residual(); o.viscous_residual(); o.source_residual(); o.boundary_conditions()
+        o.explicit_update(alphas[rk])
+    o.preprocess(1, True)
+    r = o.turb_iterate(tb[:, 1:3], t0[:, 3:6], t0[:, 2], 0.85, 0.135, 2.0e3, 1.0, 1.0, 5, 1e-6)
+    assert colerr(res, r["res"]) <= 1e-12 and colerr(dx, r["dx"]) <= 1e-10 and colerr(post, r["post"]) <= 1e-10 and nlin == r["iters"]
