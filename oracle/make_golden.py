@@ -211,6 +211,17 @@ SPECS = {
                                      dict(CHANNEL_MARKERS, PHYSICAL_PROBLEM="REACTIVE_EULER", MARKER_ISOTHERMAL="( NONE )", MARKER_EULER="( upper_wall, lower_wall )",
                                           RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO", UNSTEADY_SIMULATION="TIME_STEPPING",
                                           UNST_CFL_NUMBER="0.0", UNST_TIMESTEP="2e-8", UNST_TIME="1.0", CFL_NUMBER="0.2"), 2, 0, 89, True),
+    # ---- dual time stepping, explicit pseudo-time iterations with a fixed physical time step: 2nd order on the laminar RK case,
+    # 1st order on the Euler case with the physical step taken from UNST_CFL_NUMBER on iteration 0; the time levels are shifted after every second pseudo-time iteration (RX_DUAL_INNER)
+    "channel_lam_dualtime2": (dict(nx=41, ny=21, stretch=1.5),
+                              dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="3", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                                   UNSTEADY_SIMULATION="DUAL_TIME_STEPPING-2ND_ORDER", UNST_CFL_NUMBER="0.0", UNST_TIMESTEP="5e-8", UNST_TIME="1.0",
+                                   TIME_DISCRE_FLOW="RUNGE-KUTTA_EXPLICIT", RK_ALPHA_COEFF="( 0.66667, 0.66667, 1.000000 )", CFL_NUMBER="0.2"), 3, 1, 97, True),
+    "channel_euler_dualtime1": (dict(nx=41, ny=21, stretch=1.5),
+                                dict(CHANNEL_MARKERS, PHYSICAL_PROBLEM="REACTIVE_EULER", MARKER_ISOTHERMAL="( NONE )", MARKER_EULER="( upper_wall, lower_wall )",
+                                     RESTART_SOL="NO", EXT_ITER="4", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                                     UNSTEADY_SIMULATION="DUAL_TIME_STEPPING-1ST_ORDER", UNST_CFL_NUMBER="1.5", UNST_TIMESTEP="4e-8", UNST_TIME="1.0",
+                                     CFL_NUMBER="0.2"), 4, 0, 101, True),
     # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
     # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
     "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),

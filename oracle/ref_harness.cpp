@@ -322,6 +322,8 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"kind_inlet\": " << f->GetKind_Inlet()
      << ", \"time_stepping\": " << (f->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0) << ", \"unst_cfl\": " << f->GetUnst_CFL()
      << ", \"unst_dt\": " << f->GetDelta_UnstTime()
+     << ", \"dual_time\": " << (f->GetUnsteady_Simulation() == DT_STEPPING_1ST ? 1 : f->GetUnsteady_Simulation() == DT_STEPPING_2ND ? 2 : 0)
+     << ", \"unst_dt_nd\": " << f->GetDelta_UnstTimeND()
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
      << ", \"limiter_kind\": " << f->GetKind_SlopeLimit_Flow() << ", \"limiter_coeff\": " << f->GetLimiterCoeff()
      << ", \"ref_elem_length\": " << f->GetRefElemLength() << ", \"limiter_iter\": " << f->GetLimiterIter()
@@ -439,6 +441,14 @@ static void poke_state(Ctx& c, const std::string& mode) {
   if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->MarkHostSolutionDirty();
 #endif
 }
+// dual time stepping: the two stored time levels U^n, U^(n-1) (CVariable::Solution_time_n / _time_n1)
+static void dump_time_levels(Ctx& c, const std::string& base) {
+  std::vector<double> A(c.nPoint * c.nVar), B(c.nPoint * c.nVar);
+  for (unsigned long p = 0; p < c.nPoint; ++p)
+    for (unsigned short v = 0; v < c.nVar; ++v) { A[p * c.nVar + v] = c.flow->node[p]->GetSolution_time_n()[v]; B[p * c.nVar + v] = c.flow->node[p]->GetSolution_time_n1()[v]; }
+  dump_f64(base + "Un", A, {c.nPoint, c.nVar});
+  dump_f64(base + "Un1", B, {c.nPoint, c.nVar});
+}
 static void dump_solution_old(Ctx& c, const std::string& name) {
   std::vector<double> U(c.nPoint * c.nVar);
   for (unsigned long p = 0; p < c.nPoint; ++p)
@@ -529,6 +539,10 @@ int main(int argc, char** argv) {
 
   for (unsigned long n : ckpt) if (n == 0) dump_checkpoint(c, 0);   // the state the run starts from
 
+  // dual time stepping: every harness iteration is one pseudo-time iteration; after every RX_DUAL_INNER of them (default 2) the physical
+  // time step is closed as CFluidIteration::Update does (iteration_structure.cpp:623: CIntegration::SetDualTime_Solver shifts the time levels)
+  const bool dualTime = c.cfg->GetUnsteady_Simulation() == DT_STEPPING_1ST || c.cfg->GetUnsteady_Simulation() == DT_STEPPING_2ND;
+  const unsigned long dualInner = getenv("RX_DUAL_INNER") ? atol(getenv("RX_DUAL_INNER")) : 2;
   std::vector<double> hist, histAll;
   for (unsigned long it = 0; it < nIter; ++it) {
     bool dmp = it >= dump_from;
@@ -539,6 +553,7 @@ int main(int argc, char** argv) {
     if (dmp) {
       dump_solution(c, tag(it, 0, "U0"));
       if (pokeIter >= 0) dump_solution_old(c, tag(it, 0, "Uold"));
+      if (dualTime) dump_time_levels(c, tag(it, 0, ""));
       dump_primitive(c, tag(it, 0, "prev_"));   // V[T] here is the secant start value (variable_direct_reactive.cpp:622)
       dump_turb(c, tag(it, 0, "turb"));
     }
@@ -557,6 +572,10 @@ int main(int argc, char** argv) {
       if (dmp) dump_residual(c, tag(it, rk, "res_visc"));
       c.flow->Source_Residual(c.geo, c.sol, c.num[SOURCE_FIRST_TERM], c.num[SOURCE_SECOND_TERM], c.cfg, MESH_0);
       if (dmp) dump_residual(c, tag(it, rk, "res_src"));
+      if (dualTime) {   // CIntegration::Space_Integration :86-87: the dual time source term comes between the source term and the boundary conditions
+        c.flow->SetResidual_DualTime(c.geo, c.sol, c.cfg, rk, MESH_0, RUNTIME_REACTIVE_SYS);
+        if (dmp) dump_residual(c, tag(it, rk, "res_dual"));
+      }
       apply_bcs(c);
       if (dmp) dump_residual(c, tag(it, rk, "res_bc"));
       c.integ->Time_Integration(c.geo, c.sol, c.cfg, rk, RUNTIME_REACTIVE_SYS, it);
@@ -570,6 +589,7 @@ int main(int argc, char** argv) {
     }
     c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
     if (dmp) dump_primitive(c, tag(it, 0, "out_"));
+    if (dualTime && (it + 1) % dualInner == 0) c.integ->SetDualTime_Solver(c.geo, c.flow, c.cfg, MESH_0);
     clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
     if (!quiet) printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {

@@ -66,6 +66,8 @@ typedef struct {
   double limCoeff, refElemLength;      /* LIMITER_COEFF, REF_ELEM_LENGTH */
   int timeStepping;                    /* UNSTEADY_SIMULATION = TIME_STEPPING: every point advances with the global minimum time step */
   double unstCfl, deltaUnstTime;       /* UNST_CFL_NUMBER, UNST_TIMESTEP (read by the Euler solver's variant only) */
+  int dualTime;                        /* UNSTEADY_SIMULATION = DUAL_TIME_STEPPING-1ST_ORDER (1) / -2ND_ORDER (2), explicit pseudo-time iterations */
+  double deltaUnstTimeND;              /* the physical time step (CConfig::GetDelta_UnstTimeND); recomputed from unstCfl when that is not zero */
 } rxo_opts;
 
 rxo_ctx* rxo_create(const rxo_mesh*, const rxo_chem*, const rxo_opts*);
@@ -85,6 +87,14 @@ void rxo_get_limiter(rxo_ctx*, double* lim4);            /* [nPoint][4]: limiter
 int64_t rxo_preprocess(rxo_ctx*, int64_t extIter, int output);
 void rxo_set_old_solution(rxo_ctx*);
 void rxo_time_step(rxo_ctx*);
+/* dual time stepping: the stored time levels U^n, U^(n-1), the pseudo-time iteration index SetTime_Step receives (the physical time step
+   follows UNST_CFL_NUMBER on iteration 0), the source term of SetResidual_DualTime and CIntegration::SetDualTime_Solver's level shift */
+void rxo_set_time_levels(rxo_ctx*, const double* Un, const double* Un1);
+void rxo_get_time_levels(rxo_ctx*, double* Un, double* Un1);
+void rxo_set_inner_iteration(rxo_ctx*, int64_t intIter);
+double rxo_get_delta_unst_time(rxo_ctx*);
+void rxo_dual_time_residual(rxo_ctx*);
+void rxo_shift_time_levels(rxo_ctx*);
 void rxo_upwind_residual(rxo_ctx*);
 void rxo_viscous_residual(rxo_ctx*);
 void rxo_source_residual(rxo_ctx*);

@@ -89,7 +89,8 @@ class _Opts(C.Structure):
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
                 ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
-                ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double)]
+                ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double),
+                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double)]
 
 
 def chem_arrays(case):
@@ -117,7 +118,8 @@ def opts_dict(case):
                 tkeInf=cf["tke_inf"], secondOrder=cf.get("second_order", 0),
                 limiter=(2 if cf.get("limiter_kind", 0) == 1 else 1) if cf.get("limiter", 0) else 0,   # 1 VENKATAKRISHNAN, 2 BARTH_JESPERSEN
                 limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1),
-                timeStepping=cf.get("time_stepping", 0), unstCfl=cf.get("unst_cfl", 0.0), deltaUnstTime=cf.get("unst_dt", 0.0))
+                timeStepping=cf.get("time_stepping", 0), unstCfl=cf.get("unst_cfl", 0.0), deltaUnstTime=cf.get("unst_dt", 0.0),
+                dualTime=cf.get("dual_time", 0), deltaUnstTimeND=cf.get("unst_dt_nd", 0.0))
 
 
 def marker_list(case):
@@ -243,6 +245,16 @@ class Oracle:
     def preprocess(self, ext_iter, output=False):
         return self.lib.rxo_preprocess(self.ctx, C.c_int64(ext_iter), int(output))
 
+    def set_time_levels(self, Un, Un1):
+        Un = np.ascontiguousarray(Un, dtype=np.float64); Un1 = np.ascontiguousarray(Un1, dtype=np.float64)
+        self.lib.rxo_set_time_levels(self.ctx, _p(Un), _p(Un1))
+
+    def time_levels(self):
+        a = np.empty((self.nP, self.nVar)); b = np.empty((self.nP, self.nVar)); self.lib.rxo_get_time_levels(self.ctx, _p(a), _p(b)); return a, b
+
+    def set_inner_iteration(self, it): self.lib.rxo_set_inner_iteration(self.ctx, C.c_int64(it))
+    def dual_time_residual(self): self.lib.rxo_dual_time_residual(self.ctx)
+    def shift_time_levels(self): self.lib.rxo_shift_time_levels(self.ctx)
     def set_old_solution(self): self.lib.rxo_set_old_solution(self.ctx)
     def time_step(self): self.lib.rxo_time_step(self.ctx)
     def upwind_residual(self): self.lib.rxo_upwind_residual(self.ctx)

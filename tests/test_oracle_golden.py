@@ -23,7 +23,9 @@ CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_la
          # BC_Supersonic_Inlet / BC_Supersonic_Outlet (:2998-3214, :3681-3807)
          "channel_lam_supersonic",
          # UNSTEADY_SIMULATION= TIME_STEPPING (global minimum time step; the Euler solver's CFL swap and fixed UNST_TIMESTEP)
-         "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed"]
+         "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed",
+         # explicit dual time stepping (SetResidual_DualTime :2172-2215, the pseudo-time step clamp :5274-5297, the level shift)
+         "channel_lam_dualtime2", "channel_euler_dualtime1"]
 TOL = 0.0
 
 
@@ -32,7 +34,16 @@ def drive(case, solver, check):
     cf = case.meta["cfg"]
     its = sorted({int(re.match(r"it(\d+)_", k).group(1)) for k in case.arr if k.startswith("it")})
     nrk = cf["nRK"] if cf["time_scheme"] == 1 else 1
+    dual, prevUn = cf.get("dual_time", 0), None
     for it in its:
+        if dual:   # dual time stepping: the stored time levels; where the reference closed a physical time step, shift them as it does
+            Un, Un1 = case.stage(it, 0, "Un"), case.stage(it, 0, "Un1")
+            if prevUn is not None and not np.array_equal(Un, prevUn):
+                solver.shift_time_levels()
+                a, b = solver.time_levels()
+                check("it%04d_rk0_Un" % it, a); check("it%04d_rk0_Un1" % it, b)
+            solver.set_time_levels(Un, Un1); solver.set_inner_iteration(it)
+            prevUn = Un
         if case.has("it%04d_rk0_Uold" % it):   # Solution_Old at the start of the iteration: the non-physical fallback reads it
             solver.set_solution(case.stage(it, 0, "Uold")); solver.set_old_solution()
         solver.set_solution(case.stage(it, 0, "U0"))
@@ -52,6 +63,8 @@ def drive(case, solver, check):
             solver.upwind_residual(); check(key("res_conv"), solver.residual())
             solver.viscous_residual(); check(key("res_visc"), solver.residual())
             solver.source_residual(); check(key("res_src"), solver.residual())
+            if dual:
+                solver.dual_time_residual(); check(key("res_dual"), solver.residual())
             solver.boundary_conditions(); check(key("res_bc"), solver.residual())
             rms = solver.explicit_update(cf["rk_alpha"][rk] if nrk > 1 else 1.0)
             check(key("U1"), solver.solution()); check(key("rms"), rms.reshape(1, -1))
