@@ -158,8 +158,11 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   o.secondOrder = second_order ? 1 : 0; o.limiter = limiter ? (config->GetKind_SlopeLimit_Flow() == BARTH_JESPERSEN ? 2 : 1) : 0;
   o.limCoeff = config->GetLimiterCoeff(); o.refElemLength = config->GetRefElemLength();
   o.timeStepping = config->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0; o.unstCfl = config->GetUnst_CFL(); o.deltaUnstTime = config->GetDelta_UnstTime();
-  if (config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND)
-    throw std::runtime_error("CReactiveNSSolverGPU: dual time stepping is not on the CUDA path");
+  // dual time stepping with explicit pseudo-time iterations (SetResidual_DualTime :2172-2215, the pseudo-time step clamp :5274-5297)
+  dualTime = config->GetUnsteady_Simulation() == DT_STEPPING_1ST ? 1 : config->GetUnsteady_Simulation() == DT_STEPPING_2ND ? 2 : 0;
+  if (dualTime && ransMode)
+    throw std::runtime_error("CReactiveNSSolverGPU: dual time stepping of a REACTIVE_RANS run is not on the CUDA path (the turbulence solver's time levels stay on the host)");
+  o.dualTime = dualTime; o.deltaUnstTimeND = config->GetDelta_UnstTimeND();
   o.device = env_int("SU2_RX_DEVICE", 0);
 
   const int rc = rx_create(&ctx, &mesh, &chem, &o);
@@ -331,12 +334,44 @@ void CReactiveNSSolverGPU::SetTime_Step(CGeometry* geometry, CSolver** solver_co
   // (integration_time.cpp:158-163); the device copy of U_old is taken here, at the same point of the sequence.
   Check(rx_set_old_solution(ctx), "rx_set_old_solution");
   Check(rx_set_cfl(ctx, config->GetCFL(iMesh)), "rx_set_cfl");   // read at every call, as the reference does: CFL_ADAPT changes it between iterations
+  if (dualTime) {
+    // `Iteration` is the pseudo-time iteration index of the running physical time step.  On its iteration 0 the stored time levels are
+    // taken from node[] (CIntegration::SetDualTime_Solver, a restart or the initial condition wrote them there; Solution itself is
+    // current on the host at every mirror level) unless ShiftTimeLevels() already moved them on the device.
+    Check(rx_set_inner_iteration(ctx, (int64_t)Iteration), "rx_set_inner_iteration");
+    if (Iteration == 0) {   // a new physical time step begins
+      if (!levelsOnDevice) UploadTimeLevels();
+      levelsOnDevice = false; levelsUploaded = true;
+    } else if (!levelsUploaded) { UploadTimeLevels(); levelsUploaded = true; }
+  }
   Check(rx_time_step(ctx), "rx_time_step");
+  if (dualTime && Iteration == 0 && config->GetUnst_CFL() != 0.0 && iMesh == MESH_0) {   // :5276-5289
+    double dtND = 0.0;
+    Check(rx_get_delta_unst_time(ctx, &dtND), "rx_get_delta_unst_time");
+    config->SetDelta_UnstTimeND(dtND);
+  }
   // the Euler solver's SetTime_Step replaces the CFL by UNST_CFL_NUMBER in a time-accurate run (:2129); the library did the same inside
   if (!viscousMode && config->GetUnsteady_Simulation() == TIME_STEPPING) config->SetCFL(iMesh, config->GetUnst_CFL());
   if (mirror >= 2 || (mirror >= 1 && ransMode)) MirrorTimeStep();   // the SST implicit step uses the flow time step
 }
 
+void CReactiveNSSolverGPU::UploadTimeLevels() {
+  std::vector<double> A((size_t)nPoint * nVar), B((size_t)nPoint * nVar);
+  for (unsigned long p = 0; p < nPoint; ++p)
+    for (unsigned short v = 0; v < nVar; ++v) { A[p * nVar + v] = node[p]->GetSolution_time_n()[v]; B[p * nVar + v] = node[p]->GetSolution_time_n1()[v]; }
+  Check(rx_set_time_levels(ctx, A.data(), B.data()), "rx_set_time_levels");
+}
+void CReactiveNSSolverGPU::ShiftTimeLevels() {
+  if (!dualTime) return;
+  if (!levelsUploaded) UploadTimeLevels();   // nothing on the device yet: the shift starts from what node[] holds
+  Check(rx_shift_time_levels(ctx), "rx_shift_time_levels");
+  levelsOnDevice = true; levelsUploaded = true;
+}
+void CReactiveNSSolverGPU::SetResidual_DualTime(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short) {
+  if (!levelsUploaded) { UploadTimeLevels(); levelsUploaded = true; }
+  Check(rx_residual_dual_time(ctx), "rx_residual_dual_time");
+  if (mirror >= 2) MirrorResidual();
+}
 void CReactiveNSSolverGPU::Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) {
   Check(rx_residual_conv(ctx), "rx_residual_conv");
   if (mirror >= 2) { Check(rx_get_status(ctx, nullptr), "Upwind_Residual"); MirrorResidual(); }   // the reference throws in this stage on a NaN residual

@@ -35,6 +35,8 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
                         unsigned short iMesh, unsigned short iRKStep) override;
   void Source_Residual(CGeometry* geometry, CSolver** solver_container, CNumerics* numerics, CNumerics* second_numerics,
                        CConfig* config, unsigned short iMesh) override;
+  void SetResidual_DualTime(CGeometry* geometry, CSolver** solver_container, CConfig* config, unsigned short iRKStep,
+                            unsigned short iMesh, unsigned short RunTime_EqSystem) override;
   void BC_Inlet(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics, CNumerics* visc_numerics,
                 CConfig* config, unsigned short val_marker) override;
   void BC_Outlet(CGeometry* geometry, CSolver** solver_container, CNumerics* conv_numerics, CNumerics* visc_numerics,
@@ -66,8 +68,12 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void WriteRestart(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);
   void WriteTecplot(CGeometry* geometry, CSolver** solver_container, CConfig* config, const std::string& filename);   // rx_tecplot_write
 
+  // Dual time stepping.  CIntegration::SetDualTime_Solver (integration_structure.cpp:568-584) is not virtual: it shifts the time levels in
+  // node[], and the next physical time step's first SetTime_Step uploads them.  Calling ShiftTimeLevels() next to it (one line,
+  // INTEGRATION.md 4f) shifts them on the device instead and saves that upload.
+  void ShiftTimeLevels();
   // node[]->Solution was changed on the host (restart, initial condition): upload before the next stage
-  void MarkHostSolutionDirty() { hostDirty = true; turbOnDevice = false; }   // the turbulence fields are taken from the host again, too
+  void MarkHostSolutionDirty() { hostDirty = true; turbOnDevice = false; levelsUploaded = levelsOnDevice = false; }   // the turbulence fields are taken from the host again, too
   rx_ctx* Context() { return ctx; }
   // called by CTurbSSTSolverGPU after its step: the six turbulence fields the flow path reads are current on the device (no upload at
   // the next Preprocessing); post12 = rx_get_turbulence rows, for the host mirror of the eddy viscosity
@@ -80,6 +86,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void DeviceTurbPostprocessing(CGeometry* geometry, CSolver** solver_container);
   void MirrorPrimitives();
   void MirrorResidual();
+  void UploadTimeLevels();
   void MirrorLimiter();
   void MirrorTimeStep();
   void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
@@ -91,6 +98,8 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   rx_ctx* ctx = nullptr;
   bool commReady = false;
   bool hostDirty = true, ransMode = false, viscousMode = true;
+  int dualTime = 0;                                        // 0, or the order of DUAL_TIME_STEPPING
+  bool levelsUploaded = false, levelsOnDevice = false;     // the device holds time levels at all / holds the ones of the coming physical step
   int mirror = 1;
   // SU2_RX_TURB_POST=1: the fields the flow path reads from the SST solver (muT, grad k, sigma_k) are formed on the device from
   // (k, omega) by rx_turb_postprocess instead of being copied from CTurbSSTSolver::Postprocessing's results

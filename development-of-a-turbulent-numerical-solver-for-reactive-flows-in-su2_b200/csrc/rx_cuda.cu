@@ -68,6 +68,9 @@ struct rx_ctx {
   bool haveWallDist = false; double sigmaK = 0.85;
   int sweepThreads = 1024;           // block size of the LU-SGS sweep kernels (test hook RX_SWEEP_THREADS: a small block sends the levels through the wide-level loop)
   double* dtPartial = nullptr; int dtBlocks = 0;   // TIME_STEPPING: block minima of the local time steps + the global one
+  double* Un = nullptr; double* Un1 = nullptr;     // dual time stepping: U^n, U^(n-1), laid out like U
+  double* dtND = nullptr;                          // dual time stepping: the physical time step, on the device (rx_time_step may recompute it)
+  bool timeLevelsSet = false; long long intIter = 0;
 };
 
 extern "C" {
@@ -304,6 +307,9 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   o.prandtlLam = op->prandtlLam; o.prandtlTurb = op->prandtlTurb; o.lewisTurb = op->lewisTurb; o.cMu = op->cMu;
   o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
   o.timeStepping = op->timeStepping; o.unstCfl = op->unstCfl; o.deltaUnstTime = op->deltaUnstTime;
+  o.dualTime = op->dualTime; o.deltaUnstTimeND = op->deltaUnstTimeND;
+  if (o.dualTime < 0 || o.dualTime > 2 || (o.dualTime && o.timeStepping)) { g_create_error = "rx_create: dualTime must be 0, 1 or 2 and excludes timeStepping"; delete c; return RX_ERR_ARG; }
+  if (o.dualTime && !(o.deltaUnstTimeND > 0.0) && o.unstCfl == 0.0) { g_create_error = "rx_create: dual time stepping needs a physical time step (deltaUnstTimeND) or an unsteady CFL number"; delete c; return RX_ERR_ARG; }
   o.secondOrder = op->secondOrder; o.limiter = op->secondOrder ? op->limiter : 0; o.limCoeff = op->limCoeff; o.refElemLength = op->refElemLength;
   int rc = fill_chem(c, ch);
   if (rc) { g_create_error = "rx_create: chemistry upload failed"; rx_destroy(c); return rc; }
@@ -344,6 +350,8 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.Cp = dalloc<double>(c, np); d.gam = dalloc<double>(c, np); d.mu = dalloc<double>(c, np); d.kap = dalloc<double>(c, np);
   d.lim = dalloc<double>(c, np * 4);
   d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
+  if (o.dualTime) { c->Un = dalloc<double>(c, np * c->nVar); c->Un1 = dalloc<double>(c, np * c->nVar); c->dtND = dalloc<double>(c, 1);
+    if (c->dtND && cudaMemcpy(c->dtND, &o.deltaUnstTimeND, sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) c->allocFailed = true; }
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
   d.turb = dalloc<double>(c, np * 6); c->tpost = o.rans ? dalloc<double>(c, np * TP_N) : nullptr; c->eddyFlow = o.rans ? dalloc<double>(c, np) : nullptr; d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
@@ -435,6 +443,7 @@ static std::vector<std::pair<void*, size_t>> snapshot_fields(rx_ctx* c) {
   if (d.eKey) f.push_back({d.eKey, ne});
   if (c->eOrderBuf) f.push_back({c->eOrderBuf, ne * sizeof(int)});
   if (c->tpost) f.push_back({c->tpost, np * TP_N * w});
+  if (c->Un) { f.push_back({c->Un, np * c->nVar * w}); f.push_back({c->Un1, np * c->nVar * w}); f.push_back({c->dtND, w}); }
   return f;
 }
 int rx_state_snapshot(rx_ctx* c, int restore) {
@@ -891,7 +900,11 @@ int rx_time_step(rx_ctx* c) {
   c->launches++;
   for (const MarkerDev& m : c->markers)
     if (m.nVertex) { k_timestep_boundary<<<nblk(m.nVertex, 64), 64, 0, s>>>(c->o, d, m); c->launches++; }
-  k_timestep_finish<<<nblk(d.nPointDomain, 128), 128, 0, s>>>(c->o, d);
+  {
+    Opts of = c->o;
+    if (of.dualTime) of.timeStepping = 1;   // leave the steps unclamped: k_dual_dt_clamp applies Max_DeltaTime after the global minimum has been taken
+    k_timestep_finish<<<nblk(d.nPointDomain, 128), 128, 0, s>>>(of, d);
+  }
   c->launches++;
   if (c->o.timeStepping) {
     if (!c->dtPartial) {
@@ -914,6 +927,82 @@ int rx_time_step(rx_ctx* c) {
     k_dt_fill<<<nblk(d.nPointDomain, 256), 256, 0, s>>>(d, glob, c->o.deltaUnstTime, useFixed);
     c->launches += 3;
   }
+  if (c->o.dualTime) {
+    if (c->intIter == 0 && c->o.unstCfl != 0.0) {   // the physical step follows UNST_CFL_NUMBER (:5276-5289): global minimum of the unclamped local steps
+      if (!c->dtPartial) {
+        c->dtBlocks = (int)nblk(d.nPointDomain, 256);
+        c->dtPartial = dalloc<double>(c, (size_t)c->dtBlocks + 1);
+        if (!c->dtPartial) { c->err = "rx_time_step: device allocation failed"; return RX_ERR_CUDA; }
+      }
+      double* glob = c->dtPartial + c->dtBlocks;
+      k_dt_min_partial<<<c->dtBlocks, 256, 0, s>>>(d, c->dtPartial);
+      k_dt_min_final<<<1, 256, 0, s>>>(c->dtPartial, c->dtBlocks, glob);
+      if (c->comm) {
+        std::string why;
+        NcclApi* a = nccl_api(why);
+        const int e = a->AllReduce(glob, glob, 1, NCCL_FLOAT64, NCCL_MIN, c->comm->comm, s);
+        if (e) { c->err = std::string("rx_time_step: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+      }
+      k_dual_unst_dt<<<1, 1, 0, s>>>(glob, c->o.unstCfl, c->o.cfl, c->dtND);
+      c->launches += 3;
+    }
+    k_dual_dt_clamp<<<nblk(d.nPointDomain, 256), 256, 0, s>>>(d, c->o.maxDt, c->dtND);
+    c->launches++;
+  }
+  RX_CK(cudaGetLastError());
+  return RX_OK;
+}
+
+// ---- dual time stepping ---------------------------------------------------------------------------------------------------------
+static int ensure_time_levels(rx_ctx* c, const char* who) {
+  if (!c->o.dualTime) { c->err = std::string(who) + ": the context was not created for dual time stepping (rx_opts.dualTime)"; return RX_ERR_ARG; }
+  if (!c->timeLevelsSet) {   // SetInitialCondition leaves U^n = U^(n-1) = U
+    const size_t b = (size_t)c->d.np * c->nVar * sizeof(double);
+    RX_CK(cudaMemcpyAsync(c->Un, c->d.U, b, cudaMemcpyDeviceToDevice, c->stream));
+    RX_CK(cudaMemcpyAsync(c->Un1, c->d.U, b, cudaMemcpyDeviceToDevice, c->stream));
+    c->timeLevelsSet = true;
+  }
+  return RX_OK;
+}
+int rx_set_time_levels(rx_ctx* c, const double* Un, const double* Un1) {
+  if (!c->o.dualTime) { c->err = "rx_set_time_levels: the context was not created for dual time stepping (rx_opts.dualTime)"; return RX_ERR_ARG; }
+  if (!Un || !Un1) { c->err = "rx_set_time_levels: NULL argument"; return RX_ERR_ARG; }
+  int rc = upload_aos(c, Un, c->Un, c->nVar);
+  if (!rc) rc = upload_aos(c, Un1, c->Un1, c->nVar);
+  if (!rc) c->timeLevelsSet = true;
+  return rc;
+}
+int rx_get_time_levels(rx_ctx* c, double* Un, double* Un1) {
+  int rc = ensure_time_levels(c, "rx_get_time_levels");
+  if (!rc && Un) rc = download_aos(c, c->Un, Un, c->nVar);
+  if (!rc && Un1) rc = download_aos(c, c->Un1, Un1, c->nVar);
+  return rc;
+}
+int rx_shift_time_levels(rx_ctx* c) {
+  const int rc = ensure_time_levels(c, "rx_shift_time_levels");
+  if (rc) return rc;
+  const size_t b = (size_t)c->d.np * c->nVar * sizeof(double);
+  RX_CK(cudaMemcpyAsync(c->Un1, c->Un, b, cudaMemcpyDeviceToDevice, c->stream));
+  RX_CK(cudaMemcpyAsync(c->Un, c->d.U, b, cudaMemcpyDeviceToDevice, c->stream));
+  return RX_OK;
+}
+int rx_set_inner_iteration(rx_ctx* c, int64_t intIter) {
+  if (intIter < 0) { c->err = "rx_set_inner_iteration: negative iteration index"; return RX_ERR_ARG; }
+  c->intIter = intIter;
+  return RX_OK;
+}
+int rx_get_delta_unst_time(rx_ctx* c, double* dtND) {
+  if (!c->o.dualTime || !dtND) { c->err = "rx_get_delta_unst_time: not a dual time stepping context, or NULL argument"; return RX_ERR_ARG; }
+  RX_CK(cudaMemcpyAsync(dtND, c->dtND, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RX_CK(cudaStreamSynchronize(c->stream));
+  return RX_OK;
+}
+int rx_residual_dual_time(rx_ctx* c) {
+  const int rc = ensure_time_levels(c, "rx_residual_dual_time");
+  if (rc) return rc;
+  const Dev& d = c->d;
+  k_dual_time_residual<<<nblk(d.nPointDomain, 128), 128, 0, c->stream>>>(d, c->nVar, c->o.dualTime, c->dtND, c->Un, c->Un1);
+  c->launches++;
   RX_CK(cudaGetLastError());
   return RX_OK;
 }
@@ -1141,6 +1230,7 @@ int rx_iterate(rx_ctx* c, int64_t extIter, int nRK, const double* rkAlpha, doubl
       if ((rc = rx_time_step(c))) return rc;
     }
     if ((rc = rx_residual_all(c))) return rc;
+    if (c->o.dualTime && (rc = rx_residual_dual_time(c))) return rc;   // CIntegration::Space_Integration :86-87: after the source term, before the boundary conditions
     if ((rc = rx_bc(c))) return rc;
     const bool last = rk == nRK - 1;
     if (par && last && resRms) {

@@ -91,6 +91,7 @@ struct Opts {
   int secondOrder, limiter;
   double limCoeff, refElemLength;
   int timeStepping; double unstCfl, deltaUnstTime;
+  int dualTime; double deltaUnstTimeND;
 };
 
 // ---- spline (MathTools::GetSpline, Common/src/Tools/spline.cpp:61-77) ---------------------------

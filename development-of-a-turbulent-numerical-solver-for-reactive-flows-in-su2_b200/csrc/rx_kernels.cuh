@@ -499,4 +499,31 @@ __global__ void k_dt_fill(const Dev d, const double* __restrict__ global, double
   if (p < d.nPointDomain) d.dt[p] = useFixed ? fixed : global[0];
 }
 
+// dual time stepping (:5274-5297, Euler :2141-2165).  k_dual_unst_dt: on pseudo-time iteration 0 with UNST_CFL_NUMBER set, the physical time
+// step is UNST_CFL * (global minimum of the unclamped local steps) / CFL.  k_dual_dt_clamp: the local step, clamped to Max_DeltaTime as
+// SetTime_Step does for every steady run, is then at most two thirds of the physical step.
+__global__ void k_dual_unst_dt(const double* __restrict__ global, double unstCfl, double cfl, double* __restrict__ dtND) { dtND[0] = unstCfl * global[0] / cfl; }
+__global__ void k_dual_dt_clamp(const Dev d, double maxDt, const double* __restrict__ dtND) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  double dt = d.dt[p];
+  if (dt > maxDt) dt = maxDt;
+  d.dt[p] = fmin((2.0 / 3.0) * dtND[0], dt);
+}
+// SetResidual_DualTime (:2172-2215): backward difference of the conserved variables in physical time, first or second order, times the
+// dual volume, added to the residual of every owned point
+__global__ void k_dual_time_residual(const Dev d, int nVar, int order, const double* __restrict__ dtND, const double* __restrict__ Un, const double* __restrict__ Un1) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  const double Vol = d.vol[p], TimeStep = dtND[0];
+  for (int v = 0; v < nVar; ++v) {
+    const size_t k = (size_t)v * d.np + p;
+    const double up1 = d.U[k], un = Un[k];
+    double r;
+    if (order == 1) r = (up1 - un) * Vol / TimeStep;
+    else r = (3.0 * up1 - 4.0 * un + Un1[k]) * Vol / (2.0 * TimeStep);
+    d.R[k] += r;
+  }
+}
+
 }  // namespace rx

@@ -68,7 +68,8 @@ class _Opts(C.Structure):
                 ("prandtlLam", C.c_double), ("prandtlTurb", C.c_double), ("lewisTurb", C.c_double), ("cMu", C.c_double),
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
                 ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
-                ("device", C.c_int), ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double)]
+                ("device", C.c_int), ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double),
+                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double)]
 
 
 class _TurbOpts(C.Structure):
@@ -106,6 +107,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
            "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl", "rx_dual_mesh_tri", "rx_dual_mesh_free",
+           "rx_set_time_levels", "rx_get_time_levels", "rx_shift_time_levels", "rx_set_inner_iteration", "rx_get_delta_unst_time", "rx_residual_dual_time",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -273,7 +275,7 @@ class CReactiveNSSolverGPU:
         self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
         ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),
                    _d(k(mesh["volume"])), _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
-        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0)
+        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0, dualTime=0, deltaUnstTimeND=0.0)
         od.update(opts)
         od["device"] = device
         self.opts = od
@@ -484,6 +486,27 @@ class CReactiveNSSolverGPU:
         self._ck(self.lib.rx_set_cfl(self.ctx, C.c_double(cfl)))
         self.opts["cfl"] = float(cfl)
 
+    # ---- dual time stepping (rx_opts.dualTime): stored time levels, the pseudo-time iteration index, the physical-time source term
+    def SetTimeLevels(self, Un, Un1):
+        Un = np.ascontiguousarray(Un, dtype=np.float64); Un1 = np.ascontiguousarray(Un1, dtype=np.float64)
+        self._ck(self.lib.rx_set_time_levels(self.ctx, _d(Un), _d(Un1)))
+
+    def GetTimeLevels(self):
+        a = np.empty((self.nPoint, self.nVar)); b = np.empty((self.nPoint, self.nVar))
+        self._ck(self.lib.rx_get_time_levels(self.ctx, _d(a), _d(b)))
+        return a, b
+
+    def SetDualTime_Solver(self):
+        """CIntegration::SetDualTime_Solver (integration_structure.cpp:568-584): close a physical time step, U^(n-1) <- U^n <- U."""
+        self._ck(self.lib.rx_shift_time_levels(self.ctx))
+
+    def SetInnerIteration(self, it): self._ck(self.lib.rx_set_inner_iteration(self.ctx, C.c_int64(it)))
+
+    def GetDelta_UnstTimeND(self):
+        v = C.c_double(0.0); self._ck(self.lib.rx_get_delta_unst_time(self.ctx, C.byref(v))); return v.value
+
+    def SetResidual_DualTime(self): self._ck(self.lib.rx_residual_dual_time(self.ctx))
+
     def SaveState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 0))
     def RestoreState(self): self._ck(self.lib.rx_state_snapshot(self.ctx, 1))
 
@@ -506,4 +529,6 @@ class CReactiveNSSolverGPU:
     def preprocess(self, it, output=False): return self.Preprocessing(it, output)
     set_old_solution = Set_OldSolution; time_step = SetTime_Step; upwind_residual = Upwind_Residual
     viscous_residual = Viscous_Residual; source_residual = Source_Residual; boundary_conditions = BC_All
+    set_time_levels = SetTimeLevels; time_levels = GetTimeLevels; shift_time_levels = SetDualTime_Solver
+    set_inner_iteration = SetInnerIteration; dual_time_residual = SetResidual_DualTime
     def explicit_update(self, alpha=1.0): return self.ExplicitRK_Iteration(alpha)

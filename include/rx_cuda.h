@@ -92,6 +92,9 @@ typedef struct {
   int timeStepping;         /* UNSTEADY_SIMULATION = TIME_STEPPING: rx_time_step gives every point the global minimum time step (over all partitions
                                when a communicator exists), SetTime_Step :5262-5272; inviscid contexts follow the Euler solver's variant :2121-2139 */
   double unstCfl, deltaUnstTime;   /* UNST_CFL_NUMBER, UNST_TIMESTEP (the Euler variant replaces the CFL by the former and, when it is zero, uses the latter) */
+  int dualTime;             /* UNSTEADY_SIMULATION = DUAL_TIME_STEPPING-1ST_ORDER (1) / -2ND_ORDER (2) with explicit pseudo-time iterations: rx_time_step
+                               clamps the pseudo-time step to 2/3 of the physical one (:5274-5297), rx_residual_dual_time adds the physical-time source term */
+  double deltaUnstTimeND;   /* the physical time step, CConfig::GetDelta_UnstTimeND; when unstCfl != 0 rx_time_step recomputes it on pseudo-time iteration 0 */
 } rx_opts;
 
 int rx_supported_species(int Ns);            /* 1 if kernels for this species count are compiled in */
@@ -152,6 +155,14 @@ int rx_get_limiter(rx_ctx*, double* lim4);                /* [nPoint][4]: Limite
 int rx_preprocess(rx_ctx*, int64_t extIter, int output, int64_t* nonPhysical /* may be NULL: no host sync */);  /* Preprocessing :4693 */
 int rx_set_old_solution(rx_ctx*);                         /* CSolver::Set_OldSolution, solver_structure.inl:898 */
 int rx_time_step(rx_ctx*);                                /* SetTime_Step :5057 */
+/* dual time stepping.  The stored time levels U^n, U^(n-1) (CVariable::Solution_time_n / _time_n1) live on the device; until they are set or
+ * shifted for the first time they equal the current solution (what the reference's SetInitialCondition leaves). */
+int rx_set_time_levels(rx_ctx*, const double* Un, const double* Un1);   /* [nPoint][nVar] each */
+int rx_get_time_levels(rx_ctx*, double* Un, double* Un1);               /* either may be NULL */
+int rx_shift_time_levels(rx_ctx*);                        /* CIntegration::SetDualTime_Solver, integration_structure.cpp:568-584: U^(n-1) <- U^n, U^n <- U */
+int rx_set_inner_iteration(rx_ctx*, int64_t intIter);     /* the `Iteration` argument of SetTime_Step (the pseudo-time iteration index, :5057) */
+int rx_get_delta_unst_time(rx_ctx*, double* dtND);        /* the physical time step in use (config->SetDelta_UnstTimeND, :5288); synchronises the stream */
+int rx_residual_dual_time(rx_ctx*);                       /* SetResidual_DualTime :2172-2215 (static mesh, explicit) */
 int rx_set_cfl(rx_ctx*, double cfl);                      /* config->GetCFL(iMesh) as SetTime_Step reads it at every call: CFL_ADAPT (COutput::SetCFL_Number,
                                                               output_structure.cpp:5990-6030, driver_structure.cpp:2804) changes it between iterations */
 int rx_residual_conv(rx_ctx*);                            /* Upwind_Residual :2535 */

@@ -323,7 +323,7 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"time_stepping\": " << (f->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0) << ", \"unst_cfl\": " << f->GetUnst_CFL()
      << ", \"unst_dt\": " << f->GetDelta_UnstTime()
      << ", \"dual_time\": " << (f->GetUnsteady_Simulation() == DT_STEPPING_1ST ? 1 : f->GetUnsteady_Simulation() == DT_STEPPING_2ND ? 2 : 0)
-     << ", \"unst_dt_nd\": " << f->GetDelta_UnstTimeND()
+     << ", \"unst_dt_nd\": " << f->GetDelta_UnstTimeND() << ", \"dual_inner\": " << (getenv("RX_DUAL_INNER") ? atol(getenv("RX_DUAL_INNER")) : 2)
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
      << ", \"limiter_kind\": " << f->GetKind_SlopeLimit_Flow() << ", \"limiter_coeff\": " << f->GetLimiterCoeff()
      << ", \"ref_elem_length\": " << f->GetRefElemLength() << ", \"limiter_iter\": " << f->GetLimiterIter()
@@ -563,7 +563,7 @@ int main(int argc, char** argv) {
       if (dmp) dump_primitive(c, tag(it, rk, "pre_"));
       if (rk == 0) {
         c.flow->Set_OldSolution(c.geo);
-        c.flow->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, it);
+        c.flow->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, dualTime ? it % dualInner : it);   // dual time: the pseudo-time iteration index of the physical step (CFluidIteration::Iterate: IntIter)
         if (dmp) dump_dt(c, tag(it, rk, "dt"));
       }
       c.flow->Upwind_Residual(c.geo, c.sol, c.num[CONV_TERM], c.cfg, MESH_0);
@@ -589,7 +589,14 @@ int main(int argc, char** argv) {
     }
     c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
     if (dmp) dump_primitive(c, tag(it, 0, "out_"));
-    if (dualTime && (it + 1) % dualInner == 0) c.integ->SetDualTime_Solver(c.geo, c.flow, c.cfg, MESH_0);
+    if (dualTime && (it + 1) % dualInner == 0) {
+      c.integ->SetDualTime_Solver(c.geo, c.flow, c.cfg, MESH_0);
+#ifdef RX_WITH_GPU
+      // the optional device-side shift; without it the next SetTime_Step uploads the levels the line above shifted in node[]
+      if (getenv("RX_DUAL_SHIFT_DEVICE") && atoi(getenv("RX_DUAL_SHIFT_DEVICE")))
+        if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->ShiftTimeLevels();
+#endif
+    }
     clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
     if (!quiet) printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {

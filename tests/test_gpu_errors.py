@@ -115,3 +115,26 @@ def test_cfl_can_change_between_iterations_as_cfl_adapt_does():
     with pytest.raises(pk.RxError):
         a.SetCFL(-1.0)
     a.close(); b.close()
+
+
+def test_dual_time_entry_points_need_a_dual_time_context():
+    pk = load_package()
+    lam, mesh = _ctx(pk, False)
+    z = np.zeros((lam.nPoint, lam.nVar))
+    for call in (lambda: lam.SetTimeLevels(z, z), lam.GetTimeLevels, lam.SetDualTime_Solver, lam.SetResidual_DualTime, lam.GetDelta_UnstTimeND):
+        with pytest.raises(pk.RxError, match="dual time"):
+            call()
+    lam.close()
+    chem = pk.load_mechanism()
+    with pytest.raises(pk.RxError):   # neither a physical time step nor an unsteady CFL number
+        pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), dualTime=2))
+    with pytest.raises(pk.RxError):   # excludes TIME_STEPPING
+        pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), dualTime=1, deltaUnstTimeND=1e-7, timeStepping=1))
+    s = pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), dualTime=2, deltaUnstTimeND=1e-7))
+    U, T, tb = pk.synthetic_state(mesh, chem, seed=5, rans=False)
+    s.SetSolution(U); s.SetTemperature(T); s.SetTurbulence(tb)
+    a, b = s.GetTimeLevels()          # before any set / shift the levels equal the current solution (SetInitialCondition)
+    assert np.array_equal(a, U) and np.array_equal(b, U)
+    with pytest.raises(pk.RxError):
+        s.SetInnerIteration(-1)
+    s.close()

@@ -89,6 +89,36 @@ def test_fused_iteration_matches_staged(name):
     assert stage_rel_err(last, out[1][0], case[last], case.Ns).max() <= TOL
 
 
+@pytest.mark.parametrize("name", ["channel_lam_dualtime2", "channel_euler_dualtime1"])
+def test_dual_time_fused_iterations_and_level_shift(name):
+    """Dual time stepping through rx_iterate: two physical time steps of two pseudo-time iterations each (the golden's own sequence),
+    the levels shifted on the device between them, against the reference's dumps of the last iteration — solution, time levels and,
+    for the case driven by UNST_CFL_NUMBER, the physical time step the library derived on pseudo-time iteration 0."""
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    cf = case.meta["cfg"]
+    its = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})
+    alphas = cf["rk_alpha"] if cf["time_scheme"] == 1 else [1.0]
+    inner = cf.get("dual_inner", 2)
+    s = gpu_solver(case)
+    it0 = its[0]
+    s.set_solution(case.stage(it0, 0, "U0")); s.set_temperature(case.stage(it0, 0, "prev_V")[:, 0]); s.set_turbulence(case.stage(it0, 0, "turb"))
+    s.set_time_levels(case.stage(it0, 0, "Un"), case.stage(it0, 0, "Un1"))
+    for it in its:
+        s.set_inner_iteration(it % inner)
+        s.Iterate(it, alphas)
+        last = "it%04d_rk%d_U1" % (it, len(alphas) - 1)
+        assert np.array_equal(s.solution(), case[last]), last
+        if (it + 1) % inner == 0:
+            s.shift_time_levels()
+            if it + 1 in its:
+                a, b = s.time_levels()
+                assert np.array_equal(a, case.stage(it + 1, 0, "Un")) and np.array_equal(b, case.stage(it + 1, 0, "Un1"))
+    if cf["unst_cfl"] != 0.0:
+        dt = case.stage(its[-1], 0, "dt")[:, 0]
+        assert np.isclose(dt.max(), (2.0 / 3.0) * s.GetDelta_UnstTimeND(), rtol=0, atol=0)   # the clamp binds somewhere, with the library's own physical step
+    s.close()
+
+
 def test_residual_max_and_location():
     """CSolver::AddRes_Max (solver_direct_reactive.cpp:2436): largest |LinSysRes| per variable and the FIRST point attaining it,
     reduced on the device with the residual norms."""

@@ -42,7 +42,7 @@ def drive(case, solver, check):
                 solver.shift_time_levels()
                 a, b = solver.time_levels()
                 check("it%04d_rk0_Un" % it, a); check("it%04d_rk0_Un1" % it, b)
-            solver.set_time_levels(Un, Un1); solver.set_inner_iteration(it)
+            solver.set_time_levels(Un, Un1); solver.set_inner_iteration(it % cf.get("dual_inner", 2))
             prevUn = Un
         if case.has("it%04d_rk0_Uold" % it):   # Solution_Old at the start of the iteration: the non-physical fallback reads it
             solver.set_solution(case.stage(it, 0, "Uold")); solver.set_old_solution()
