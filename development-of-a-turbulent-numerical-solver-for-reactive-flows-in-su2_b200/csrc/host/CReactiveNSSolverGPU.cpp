@@ -160,8 +160,8 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   o.timeStepping = config->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0; o.unstCfl = config->GetUnst_CFL(); o.deltaUnstTime = config->GetDelta_UnstTime();
   // dual time stepping with explicit pseudo-time iterations (SetResidual_DualTime :2172-2215, the pseudo-time step clamp :5274-5297)
   dualTime = config->GetUnsteady_Simulation() == DT_STEPPING_1ST ? 1 : config->GetUnsteady_Simulation() == DT_STEPPING_2ND ? 2 : 0;
-  if (dualTime && ransMode)
-    throw std::runtime_error("CReactiveNSSolverGPU: dual time stepping of a REACTIVE_RANS run is not on the CUDA path (the turbulence solver's time levels stay on the host)");
+  // (REACTIVE_RANS: the reference's host SST solver keeps its own time levels and reads the flow density of the three levels from node[],
+  // where CIntegration::SetDualTime_Solver keeps them current; the device SST solver refuses dual time stepping)
   o.dualTime = dualTime; o.deltaUnstTimeND = config->GetDelta_UnstTimeND();
   o.device = env_int("SU2_RX_DEVICE", 0);
 

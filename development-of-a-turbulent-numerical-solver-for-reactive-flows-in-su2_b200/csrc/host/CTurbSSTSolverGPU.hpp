@@ -6,6 +6,7 @@
 // node[] are refreshed for output and restart.  With it a RANS run hands nothing per point across PCIe between the two solvers.
 // Factory switch: the `new CTurbSSTSolver(...)` of driver_structure.cpp:817.
 #pragma once
+#include <stdexcept>
 #include "solver_structure.hpp"
 #include "rx_cuda.h"
 
@@ -13,7 +14,11 @@ class CReactiveNSSolverGPU;
 
 class CTurbSSTSolverGPU : public CTurbSSTSolver {
  public:
-  CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {}
+  CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {
+    // the SST solver's own time levels and SetResidual_DualTime (solver_direct_turbulent.cpp:730-830) are not built on the device
+    if (config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND)
+      throw std::runtime_error("CTurbSSTSolverGPU: dual time stepping of the SST solver is not on the CUDA path (SU2_RX_TURB=host keeps the reference's own turbulence solver next to the CUDA flow solver)");
+  }
 
   void Preprocessing(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short, bool) override {}
   void Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) override {}

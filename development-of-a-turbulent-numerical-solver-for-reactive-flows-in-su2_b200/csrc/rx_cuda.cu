@@ -640,6 +640,7 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   if (!c->haveWallDist) { c->err = "rx_turb_iterate: the wall distance has not been set (rx_set_wall_distance / rx_compute_wall_distance)"; return RX_ERR_ARG; }
   if (c->d.nPoint != c->d.nPointDomain && !c->comm) { c->err = "rx_turb_iterate: a partition needs the in-library communicator (rx_comm_init): the step exchanges its Krylov and LU-SGS vectors"; return RX_ERR_UNSUPPORTED; }
   if (!to || to->linIter < 1 || to->linIter > 64) { c->err = "rx_turb_iterate: bad options"; return RX_ERR_ARG; }
+  if (c->o.dualTime) { c->err = "rx_turb_iterate: dual time stepping (the SST solver's own time levels and its SetResidual_DualTime, solver_direct_turbulent.cpp:730-830) is not built; run the reference's host SST solver"; return RX_ERR_UNSUPPORTED; }
   const int m = to->linIter;
   int rc = ensure_output(c);
   if (!rc) rc = turb_step_setup(c, m);

@@ -222,6 +222,11 @@ SPECS = {
                                      RESTART_SOL="NO", EXT_ITER="4", KIND_TURB_MODEL="NONE", IGNITION="NO",
                                      UNSTEADY_SIMULATION="DUAL_TIME_STEPPING-1ST_ORDER", UNST_CFL_NUMBER="1.5", UNST_TIMESTEP="4e-8", UNST_TIME="1.0",
                                      CFL_NUMBER="0.2"), 4, 0, 101, True),
+    # RANS: the flow path of a dual-time run with the reference's own (host) SST solver, whose SetResidual_DualTime reads the flow
+    # solver's density at the three time levels (solver_direct_turbulent.cpp:778-780)
+    "channel_rans_dualtime2": (dict(nx=41, ny=21, stretch=1.5),
+                               dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="4", IGNITION="NO",
+                                    UNSTEADY_SIMULATION="DUAL_TIME_STEPPING-2ND_ORDER", UNST_CFL_NUMBER="0.0", UNST_TIMESTEP="5e-8", UNST_TIME="1.0"), 4, 2, 103, True),
     # ---- species-count generality: the reference's other mixtures (Test_Cases/TURBOLENT/TURBOLENT_FLAT_PLATE) on the same channel
     # 3-species air (O2, CO2, N2; the mixture of the shipped flat-plate cfg, no reactions), laminar, explicit RK
     "channel_air3_lam": (dict(nx=41, ny=21, stretch=1.5, other_mixture=True),

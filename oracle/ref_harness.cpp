@@ -589,14 +589,6 @@ int main(int argc, char** argv) {
     }
     c.flow->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_REACTIVE_SYS, true);
     if (dmp) dump_primitive(c, tag(it, 0, "out_"));
-    if (dualTime && (it + 1) % dualInner == 0) {
-      c.integ->SetDualTime_Solver(c.geo, c.flow, c.cfg, MESH_0);
-#ifdef RX_WITH_GPU
-      // the optional device-side shift (INTEGRATION.md 4f); without it the next SetTime_Step uploads the levels the line above shifted in node[]
-      if (getenv("RX_DUAL_SHIFT_DEVICE") && atoi(getenv("RX_DUAL_SHIFT_DEVICE")))
-        if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->ShiftTimeLevels();
-#endif
-    }
     clock_gettime(CLOCK_MONOTONIC, &ts1);   // flow iteration only (the hot path); the SST step below is outside it
     if (!quiet) printf("HARNESS_TIME it %lu flow_seconds %.6f\n", it, (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec));
     if (c.rans) {
@@ -613,7 +605,7 @@ int main(int argc, char** argv) {
       }
       ts->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_TURB_SYS, false);
       ts->Set_OldSolution(c.geo);
-      ts->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, it);
+      ts->SetTime_Step(c.geo, c.sol, c.cfg, MESH_0, dualTime ? it % dualInner : it);
       ti->Space_Integration(c.geo, c.sol, drv->numerics_container[ZONE_0][MESH_0][TURB_SOL], c.cfg, MESH_0, NO_RK_ITER, RUNTIME_TURB_SYS);
       if (dmp) {
         std::vector<double> R(c.nPoint * 2);
@@ -634,6 +626,16 @@ int main(int argc, char** argv) {
       }
       ts->Postprocessing(c.geo, c.sol, c.cfg, MESH_0);
       if (dmp) dump_turb_post(c, tag(it, 0, "tpost"));   // flow state at this point: the out_ dump above
+    }
+    if (dualTime && (it + 1) % dualInner == 0) {
+      // CFluidIteration::Update (iteration_structure.cpp:623-640): the flow solver's levels, then the turbulence solver's
+      c.integ->SetDualTime_Solver(c.geo, c.flow, c.cfg, MESH_0);
+      if (c.rans) drv->integration_container[ZONE_0][TURB_SOL]->SetDualTime_Solver(c.geo, c.sol[TURB_SOL], c.cfg, MESH_0);
+#ifdef RX_WITH_GPU
+      // the optional device-side shift (INTEGRATION.md 4f); without it the next SetTime_Step uploads the levels the line above shifted in node[]
+      if (getenv("RX_DUAL_SHIFT_DEVICE") && atoi(getenv("RX_DUAL_SHIFT_DEVICE")))
+        if (CReactiveNSSolverGPU* g = dynamic_cast<CReactiveNSSolverGPU*>(c.flow)) g->ShiftTimeLevels();
+#endif
     }
     double r0 = log10(c.flow->GetRes_RMS(0)), r3 = log10(c.flow->GetRes_RMS(nDim + 1));
     if (!quiet || it % 100 == 0) printf("HARNESS it %lu  Res[Rho] %.6f  Res[RhoE] %.6f\n", it, r0, r3);

@@ -138,3 +138,10 @@ def test_dual_time_entry_points_need_a_dual_time_context():
     with pytest.raises(pk.RxError):
         s.SetInnerIteration(-1)
     s.close()
+    rans = pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=True, cfl=0.1), dualTime=2, deltaUnstTimeND=1e-7))
+    U, T, tb = pk.synthetic_state(mesh, chem, seed=5, rans=True)
+    rans.SetSolution(U); rans.SetTemperature(T); rans.SetTurbulence(tb)
+    rans.ComputeWall_Distance()
+    with pytest.raises(pk.RxError, match="dual time"):   # the device SST step has no dual-time source term: refused, not silently steady
+        rans.TurbIterate(0.135, 2.0e3)
+    rans.close()
