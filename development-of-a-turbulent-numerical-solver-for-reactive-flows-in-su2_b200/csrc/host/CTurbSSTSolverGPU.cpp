@@ -71,6 +71,14 @@ void CTurbSSTSolverGPU::ImplicitEuler_Iteration(CGeometry* geometry, CSolver** s
     check(rx_turb_set_state(ctx, kw.data(), bl.data()), "rx_turb_set_state");
     hostDirty = false;
   }
+  if (dualTime) {
+    // node[] holds (k, omega) after every step (MirrorFromDevice), so CIntegration::SetDualTime_Solver shifts the right values there; the two
+    // levels — 4 doubles per point, against the 12 the mirror brings back — go up with every step, which needs no hook in the integration class
+    std::vector<double> a((size_t)nPoint * 2), b((size_t)nPoint * 2);
+    for (unsigned long p = 0; p < nPoint; ++p)
+      for (unsigned short v = 0; v < 2; ++v) { a[2 * p + v] = node[p]->GetSolution_time_n()[v]; b[2 * p + v] = node[p]->GetSolution_time_n1()[v]; }
+    check(rx_turb_set_time_levels(ctx, a.data(), b.data()), "rx_turb_set_time_levels");
+  }
   rx_turb_opts o{};
   o.kineInf = kine_Inf; o.omegaInf = omega_Inf;
   o.cflRed = config->GetCFLRedCoeff_Turb(); o.relax = config->GetRelaxation_Factor_Turb();

@@ -15,15 +15,14 @@ class CReactiveNSSolverGPU;
 class CTurbSSTSolverGPU : public CTurbSSTSolver {
  public:
   CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {
-    // the SST solver's own time levels and SetResidual_DualTime (solver_direct_turbulent.cpp:730-830) are not built on the device
-    if (config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND)
-      throw std::runtime_error("CTurbSSTSolverGPU: dual time stepping of the SST solver is not on the CUDA path (SU2_RX_TURB=host keeps the reference's own turbulence solver next to the CUDA flow solver)");
+    dualTime = config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND;
   }
 
   void Preprocessing(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short, bool) override {}
   void Upwind_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short) override {}
   void Viscous_Residual(CGeometry*, CSolver**, CNumerics*, CConfig*, unsigned short, unsigned short) override {}
   void Source_Residual(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
+  void SetResidual_DualTime(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short) override {}   // inside rx_turb_iterate
   void BC_HeatFlux_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
   void BC_Isothermal_Wall(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
   void BC_Inlet(CGeometry*, CSolver**, CNumerics*, CNumerics*, CConfig*, unsigned short) override {}
@@ -40,5 +39,6 @@ class CTurbSSTSolverGPU : public CTurbSSTSolver {
   void MirrorFromDevice(rx_ctx* ctx, CReactiveNSSolverGPU* flow);
   void SetWallDistance(rx_ctx* ctx, CGeometry* geometry);
   bool hostDirty = true, wallDistSet = false, stepped = false;
+  bool dualTime = false;   // DUAL_TIME_STEPPING: the stored levels (k, omega)^n, (k, omega)^(n-1) go to the device before every step
   int mirror = 1;   // env SU2_RX_MIRROR as for the flow solver: 2 also mirrors LinSysRes / LinSysSol (parity dumps)
 };

@@ -71,10 +71,12 @@ struct rx_ctx {
   double* Un = nullptr; double* Un1 = nullptr;     // dual time stepping: U^n, U^(n-1), laid out like U
   double* dtND = nullptr;                          // dual time stepping: the physical time step, on the device (rx_time_step may recompute it)
   bool timeLevelsSet = false; long long intIter = 0;
+  double* tkwN = nullptr; double* tkwN1 = nullptr; bool turbLevelsSet = false;   // ... and the SST solver's (k, omega)^n, (k, omega)^(n-1) (RANS contexts)
 };
 
 extern "C" {
 static int halo_exchange_fork(rx_ctx* c, int what);
+static int ensure_time_levels(rx_ctx* c, const char* who);
 static int comm_join(rx_ctx* c);
 static int ensure_output(rx_ctx* c);
 static int halo_exchange_field(rx_ctx* c, double* field, int nv, bool vortStrain, cudaStream_t s);
@@ -351,7 +353,8 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   d.lim = dalloc<double>(c, np * 4);
   d.rD = o.viscous ? dalloc<double>(c, np * (size_t)(Ns * (Ns + 1) / 2)) : nullptr;
   if (o.dualTime) { c->Un = dalloc<double>(c, np * c->nVar); c->Un1 = dalloc<double>(c, np * c->nVar); c->dtND = dalloc<double>(c, 1);
-    if (c->dtND && cudaMemcpy(c->dtND, &o.deltaUnstTimeND, sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) c->allocFailed = true; }
+    if (c->dtND && cudaMemcpy(c->dtND, &o.deltaUnstTimeND, sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) c->allocFailed = true;
+    if (o.rans) { c->tkwN = dalloc<double>(c, np * 2); c->tkwN1 = dalloc<double>(c, np * 2); } }
   d.grad = dalloc<double>(c, np * c->nGrad * 2); d.vort = dalloc<double>(c, np); d.strain = dalloc<double>(c, np);
   d.turb = dalloc<double>(c, np * 6); c->tpost = o.rans ? dalloc<double>(c, np * TP_N) : nullptr; c->eddyFlow = o.rans ? dalloc<double>(c, np) : nullptr; d.dt = dalloc<double>(c, np); d.lamInv = dalloc<double>(c, np); d.lamVisc = dalloc<double>(c, np);
   d.fluxC = dalloc<double>(c, ne * c->nVar);
@@ -444,6 +447,7 @@ static std::vector<std::pair<void*, size_t>> snapshot_fields(rx_ctx* c) {
   if (c->eOrderBuf) f.push_back({c->eOrderBuf, ne * sizeof(int)});
   if (c->tpost) f.push_back({c->tpost, np * TP_N * w});
   if (c->Un) { f.push_back({c->Un, np * c->nVar * w}); f.push_back({c->Un1, np * c->nVar * w}); f.push_back({c->dtND, w}); }
+  if (c->tkwN) { f.push_back({c->tkwN, np * 2 * w}); f.push_back({c->tkwN1, np * 2 * w}); }
   return f;
 }
 int rx_state_snapshot(rx_ctx* c, int restore) {
@@ -625,6 +629,39 @@ int rx_turb_set_state(rx_ctx* c, const double* kOmega, const double* blend3) {
   if (!rc && blend3) rc = upload_aos(c, blend3, c->tpost + (size_t)TP_F1 * c->d.np, 3);   // F1, F2, CDkw are consecutive columns
   return rc;
 }
+// dual time stepping: the SST solver's stored time levels.  Until set or shifted for the first time they equal the current (k, omega).
+static int ensure_turb_levels(rx_ctx* c, const char* who) {
+  if (!c->tkwN) { c->err = std::string(who) + ": not a RANS context created for dual time stepping"; return RX_ERR_ARG; }
+  if (!c->turbLevelsSet) {
+    const size_t b = 2 * (size_t)c->d.np * sizeof(double);   // k, omega are the first two columns of the Postprocessing block
+    RX_CK(cudaMemcpyAsync(c->tkwN, c->tpost, b, cudaMemcpyDeviceToDevice, c->stream));
+    RX_CK(cudaMemcpyAsync(c->tkwN1, c->tpost, b, cudaMemcpyDeviceToDevice, c->stream));
+    c->turbLevelsSet = true;
+  }
+  return RX_OK;
+}
+int rx_turb_set_time_levels(rx_ctx* c, const double* kwN, const double* kwN1) {
+  if (!c->tkwN) { c->err = "rx_turb_set_time_levels: not a RANS context created for dual time stepping"; return RX_ERR_ARG; }
+  if (!kwN || !kwN1) { c->err = "rx_turb_set_time_levels: NULL argument"; return RX_ERR_ARG; }
+  int rc = upload_aos(c, kwN, c->tkwN, 2);
+  if (!rc) rc = upload_aos(c, kwN1, c->tkwN1, 2);
+  if (!rc) c->turbLevelsSet = true;
+  return rc;
+}
+int rx_turb_get_time_levels(rx_ctx* c, double* kwN, double* kwN1) {
+  int rc = ensure_turb_levels(c, "rx_turb_get_time_levels");
+  if (!rc && kwN) rc = download_aos(c, c->tkwN, kwN, 2);
+  if (!rc && kwN1) rc = download_aos(c, c->tkwN1, kwN1, 2);
+  return rc;
+}
+int rx_turb_shift_time_levels(rx_ctx* c) {
+  const int rc = ensure_turb_levels(c, "rx_turb_shift_time_levels");
+  if (rc) return rc;
+  const size_t b = 2 * (size_t)c->d.np * sizeof(double);
+  RX_CK(cudaMemcpyAsync(c->tkwN1, c->tkwN, b, cudaMemcpyDeviceToDevice, c->stream));
+  RX_CK(cudaMemcpyAsync(c->tkwN, c->tpost, b, cudaMemcpyDeviceToDevice, c->stream));
+  return RX_OK;
+}
 int rx_turb_get_step(rx_ctx* c, double* res2, double* dx2) {
   if (!c->turbStepReady) { c->err = "rx_turb_get_step: no turbulence step has run"; return RX_ERR_ARG; }
   int rc = RX_OK;
@@ -640,7 +677,6 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   if (!c->haveWallDist) { c->err = "rx_turb_iterate: the wall distance has not been set (rx_set_wall_distance / rx_compute_wall_distance)"; return RX_ERR_ARG; }
   if (c->d.nPoint != c->d.nPointDomain && !c->comm) { c->err = "rx_turb_iterate: a partition needs the in-library communicator (rx_comm_init): the step exchanges its Krylov and LU-SGS vectors"; return RX_ERR_UNSUPPORTED; }
   if (!to || to->linIter < 1 || to->linIter > 64) { c->err = "rx_turb_iterate: bad options"; return RX_ERR_ARG; }
-  if (c->o.dualTime) { c->err = "rx_turb_iterate: dual time stepping (the SST solver's own time levels and its SetResidual_DualTime, solver_direct_turbulent.cpp:730-830) is not built; run the reference's host SST solver"; return RX_ERR_UNSUPPORTED; }
   const int m = to->linIter;
   int rc = ensure_output(c);
   if (!rc) rc = turb_step_setup(c, m);
@@ -667,6 +703,10 @@ int rx_turb_iterate(rx_ctx* c, const rx_turb_opts* to, double* resRms2, int* lin
   RX_CK(cudaMemcpyAsync(w.old, tp, 2 * (size_t)d.np * sizeof(double), cudaMemcpyDeviceToDevice, s));
   // Space_Integration: rows, then the boundary conditions (weak ones first, walls last: integration_structure.cpp:89-190)
   k_turb_rows<<<nblk(n, 128), 128, 0, s>>>(tc, d, tp, w); c->launches++;
+  if (c->o.dualTime) {   // SetResidual_DualTime comes between the source term and the boundary conditions (integration_structure.cpp:86-87)
+    if ((rc = ensure_time_levels(c, "rx_turb_iterate")) || (rc = ensure_turb_levels(c, "rx_turb_iterate"))) return rc;
+    k_turb_dual_time<<<nblk(n, 128), 128, 0, s>>>(d, tp, w, c->o.dualTime, c->dtND, c->Un, c->Un1, c->tkwN, c->tkwN1); c->launches++;
+  }
   for (const MarkerDev& mk : c->markers)
     if (mk.nVertex && (is_inlet(mk.kind) || mk.kind == RX_BC_OUTLET)) {
       k_turb_bc_io<<<nblk(mk.nVertex, 64), 64, 0, s>>>(tc, d, mk, tp, w, is_inlet(mk.kind) ? 1 : 0); c->launches++;

@@ -152,6 +152,28 @@ __global__ void __launch_bounds__(128) k_turb_rows(const __grid_constant__ TurbC
   for (int v = 0; v < 2; ++v) { w.res[v * np + p] = res[v]; w.diag[v * np + p] = dg[v]; }
 }
 
+// CTurbSolver::SetResidual_DualTime (solver_direct_turbulent.cpp:730-815; static mesh, SST: conservative variables, the flow solver's density
+// of the three time levels :778-780): AddBlock of the residual and of the diagonal Jacobian, after the source term, before the boundary conditions
+__global__ void __launch_bounds__(128) k_turb_dual_time(const Dev d, const double* __restrict__ tp, const TurbW w, int order, const double* __restrict__ dtND,
+                                                        const double* __restrict__ Un, const double* __restrict__ Un1,
+                                                        const double* __restrict__ kwN, const double* __restrict__ kwN1) {
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (p >= d.nPointDomain) return;
+  const long long np = d.np;
+  const double Vol = d.vol[p], TimeStep = dtND[0];
+  const double rP1 = d.U[p], rN = Un[p], rM1 = Un1[p];   // row 0 of the conserved variables: the mixture density
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    double r, jd;
+    if (order == 1) { r = (rP1 * tp[(TP_K + v) * np + p] - rN * kwN[v * np + p]) * Vol / TimeStep; jd = Vol / TimeStep; }
+    else {
+      r = (3.0 * rP1 * tp[(TP_K + v) * np + p] - 4.0 * rN * kwN[v * np + p] + 1.0 * rM1 * kwN1[v * np + p]) * Vol / (2.0 * TimeStep);
+      jd = (Vol * 3.0) / (2.0 * TimeStep);
+    }
+    w.res[v * np + p] += r; w.diag[v * np + p] += jd;
+  }
+}
+
 // BC_Inlet (inlet = 1: free-stream k, omega outside) / BC_Outlet (Neumann: the interior values outside) of one marker
 __global__ void k_turb_bc_io(const __grid_constant__ TurbC tc, const Dev d, const MarkerDev m, const double* __restrict__ tp, const TurbW w, int inlet) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;

@@ -108,6 +108,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
            "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl", "rx_dual_mesh_tri", "rx_dual_mesh_free",
            "rx_set_time_levels", "rx_get_time_levels", "rx_shift_time_levels", "rx_set_inner_iteration", "rx_get_delta_unst_time", "rx_residual_dual_time",
+           "rx_turb_set_time_levels", "rx_turb_get_time_levels", "rx_turb_shift_time_levels",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",
            "rx_comm_unique_id", "rx_comm_init", "rx_halo_exchange", "rx_comm_allreduce_rms"]
 
@@ -499,6 +500,17 @@ class CReactiveNSSolverGPU:
     def SetDualTime_Solver(self):
         """CIntegration::SetDualTime_Solver (integration_structure.cpp:568-584): close a physical time step, U^(n-1) <- U^n <- U."""
         self._ck(self.lib.rx_shift_time_levels(self.ctx))
+
+    def TurbSetTimeLevels(self, kwN, kwN1):
+        a = np.ascontiguousarray(kwN, dtype=np.float64); b = np.ascontiguousarray(kwN1, dtype=np.float64)
+        self._ck(self.lib.rx_turb_set_time_levels(self.ctx, _d(a), _d(b)))
+
+    def TurbGetTimeLevels(self):
+        a = np.empty((self.nPoint, 2)); b = np.empty((self.nPoint, 2))
+        self._ck(self.lib.rx_turb_get_time_levels(self.ctx, _d(a), _d(b)))
+        return a, b
+
+    def TurbSetDualTime_Solver(self): self._ck(self.lib.rx_turb_shift_time_levels(self.ctx))
 
     def SetInnerIteration(self, it): self._ck(self.lib.rx_set_inner_iteration(self.ctx, C.c_int64(it)))
 

@@ -144,6 +144,12 @@ typedef struct { double kineInf, omegaInf;   /* free-stream k, omega (CTurbSSTSo
 int rx_turb_set_state(rx_ctx*, const double* kOmega, const double* blend3);
 int rx_turb_iterate(rx_ctx*, const rx_turb_opts*, double* resRms2, int* linIters);
 int rx_turb_get_step(rx_ctx*, double* res2 /* [nPoint][2] */, double* dx2 /* [nPoint][2] */);
+/* dual time stepping of the SST solver: in a dual-time RANS context rx_turb_iterate adds CTurbSolver::SetResidual_DualTime
+ * (solver_direct_turbulent.cpp:730-815: rho k, rho omega with the flow density of the three time levels) to the residual and the diagonal
+ * Jacobian.  Its stored levels (k, omega)^n, (k, omega)^(n-1), [nPoint][2] each, live on the device like the flow solver's. */
+int rx_turb_set_time_levels(rx_ctx*, const double* kwN, const double* kwN1);
+int rx_turb_get_time_levels(rx_ctx*, double* kwN, double* kwN1);   /* either may be NULL */
+int rx_turb_shift_time_levels(rx_ctx*);                            /* CIntegration::SetDualTime_Solver on the SST solver (iteration_structure.cpp:631) */
 int rx_get_turbulence(rx_ctx*, double* post12 /* [nPoint][12]: k, omega, dist, F1, F2, CDkw, muT, dk/dx, dk/dy, domega/dx, domega/dy, sigma_k */);
 int rx_get_solution(rx_ctx*, double* U);
 int rx_get_primitive(rx_ctx*, double* V, double* aux6, double* grad);   /* aux: Cp, gamma, mu, kappa, vorticity_z, strain mag; any may be NULL */

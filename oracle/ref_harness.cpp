@@ -602,6 +602,13 @@ int main(int argc, char** argv) {
         std::vector<double> B(c.nPoint * 3);
         for (unsigned long p = 0; p < c.nPoint; ++p) { B[3 * p] = ts->node[p]->GetF1blending(); B[3 * p + 1] = ts->node[p]->GetF2blending(); B[3 * p + 2] = ts->node[p]->GetCrossDiff(); }
         dump_f64(tag(it, 0, "tblend"), B, {c.nPoint, 3});
+        if (dualTime) {   // the turbulence solver's own time levels (read by CTurbSolver::SetResidual_DualTime, solver_direct_turbulent.cpp:762-764)
+          std::vector<double> A1(c.nPoint * 2), A2(c.nPoint * 2);
+          for (unsigned long p = 0; p < c.nPoint; ++p)
+            for (int v = 0; v < 2; ++v) { A1[2 * p + v] = ts->node[p]->GetSolution_time_n()[v]; A2[2 * p + v] = ts->node[p]->GetSolution_time_n1()[v]; }
+          dump_f64(tag(it, 0, "tUn"), A1, {c.nPoint, 2});
+          dump_f64(tag(it, 0, "tUn1"), A2, {c.nPoint, 2});
+        }
       }
       ts->Preprocessing(c.geo, c.sol, c.cfg, MESH_0, NO_RK_ITER, RUNTIME_TURB_SYS, false);
       ts->Set_OldSolution(c.geo);

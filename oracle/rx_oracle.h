@@ -95,6 +95,8 @@ void rxo_set_inner_iteration(rxo_ctx*, int64_t intIter);
 double rxo_get_delta_unst_time(rxo_ctx*);
 void rxo_dual_time_residual(rxo_ctx*);
 void rxo_shift_time_levels(rxo_ctx*);
+/* the SST solver's time levels (k, omega)^n, (k, omega)^(n-1), [nPoint][2] each: read by rxo_turb_iterate in a dual-time context */
+void rxo_turb_set_time_levels(rxo_ctx*, const double* kwN, const double* kwN1);
 void rxo_upwind_residual(rxo_ctx*);
 void rxo_viscous_residual(rxo_ctx*);
 void rxo_source_residual(rxo_ctx*);

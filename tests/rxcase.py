@@ -252,6 +252,10 @@ class Oracle:
     def time_levels(self):
         a = np.empty((self.nP, self.nVar)); b = np.empty((self.nP, self.nVar)); self.lib.rxo_get_time_levels(self.ctx, _p(a), _p(b)); return a, b
 
+    def turb_set_time_levels(self, kwN, kwN1):
+        a = np.ascontiguousarray(kwN, dtype=np.float64); b = np.ascontiguousarray(kwN1, dtype=np.float64)
+        self.lib.rxo_turb_set_time_levels(self.ctx, _p(a), _p(b))
+
     def set_inner_iteration(self, it): self.lib.rxo_set_inner_iteration(self.ctx, C.c_int64(it))
     def dual_time_residual(self): self.lib.rxo_dual_time_residual(self.ctx)
     def shift_time_levels(self): self.lib.rxo_shift_time_levels(self.ctx)

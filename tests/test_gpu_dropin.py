@@ -46,7 +46,8 @@ def _run(binary, d, out, nit, seed, env):
 # conditions, FGMRES + LU-SGS, update, Postprocessing) runs on the device (rx_turb_iterate); the reference's driver and integration
 # classes still drive both solvers
 PARAMS = [(n, False, False) for n in RUNS] + [("channel_rans", True, False), ("jet_rans_perturbed", True, False), ("channel_rans_gg", True, False)] + \
-         [("channel_rans", False, True), ("jet_rans_perturbed", False, True), ("channel_rans_gg", False, True), ("channel_air3_rans", False, True)]
+         [("channel_rans", False, True), ("jet_rans_perturbed", False, True), ("channel_rans_gg", False, True), ("channel_air3_rans", False, True),
+          ("channel_rans_dualtime2", False, True)]   # dual time stepping with both solvers on the device
 
 
 @pytest.mark.parametrize("name,turb_post,turb_dev", PARAMS)

@@ -137,11 +137,13 @@ def test_dual_time_entry_points_need_a_dual_time_context():
     assert np.array_equal(a, U) and np.array_equal(b, U)
     with pytest.raises(pk.RxError):
         s.SetInnerIteration(-1)
+    with pytest.raises(pk.RxError, match="dual time"):   # the SST solver's levels exist in dual-time RANS contexts only
+        s.TurbGetTimeLevels()
     s.close()
     rans = pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=True, cfl=0.1), dualTime=2, deltaUnstTimeND=1e-7))
     U, T, tb = pk.synthetic_state(mesh, chem, seed=5, rans=True)
     rans.SetSolution(U); rans.SetTemperature(T); rans.SetTurbulence(tb)
-    rans.ComputeWall_Distance()
-    with pytest.raises(pk.RxError, match="dual time"):   # the device SST step has no dual-time source term: refused, not silently steady
-        rans.TurbIterate(0.135, 2.0e3)
+    rans.TurbSetState(np.ascontiguousarray(tb[:, 1:3]), None)
+    a, b = rans.TurbGetTimeLevels()   # before any set / shift: the current (k, omega)
+    assert np.array_equal(a, tb[:, 1:3]) and np.array_equal(b, tb[:, 1:3])
     rans.close()

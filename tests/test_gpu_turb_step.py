@@ -12,7 +12,8 @@ import pytest
 from rxcase import Case, GOLDEN, gpu_solver
 
 pytestmark = pytest.mark.gpu
-CASES = ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed", "channel_air3_rans", "channel_rans_inlet_massflow"]
+CASES = ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed", "channel_air3_rans", "channel_rans_inlet_massflow",
+         "channel_rans_dualtime2"]   # dual time stepping: CTurbSolver::SetResidual_DualTime (:730-815) inside the step
 
 
 def colerr(a, ref):
@@ -33,9 +34,13 @@ def test_sst_step_matches_reference(name):
     for it in its:
         tpost = case.stage(it, 0, "tpost")
         s.set_solution(case.stage(it, 0, "U0")); s.set_temperature(case.stage(it, 0, "prev_V")[:, 0]); s.set_turbulence(case.stage(it, 0, "turb"))
+        if cf.get("dual_time", 0):   # the stored time levels of both solvers; the pseudo-time iteration index of the flow step
+            s.set_time_levels(case.stage(it, 0, "Un"), case.stage(it, 0, "Un1")); s.set_inner_iteration(it % cf.get("dual_inner", 2))
         s.Iterate(it, alphas)
         s.SetWall_Distance(tpost[:, 2])
         s.TurbSetState(case.stage(it, 0, "turb")[:, 1:3], case.stage(it, 0, "tblend"))
+        if cf.get("dual_time", 0):
+            s.TurbSetTimeLevels(case.stage(it, 0, "tUn"), case.stage(it, 0, "tUn1"))
         rms, nlin = s.TurbIterate(cf["kine_inf"], cf["omega_inf"], cf["cfl_red_turb"], cf["relax_turb"], cf["lin_iter"], cf["lin_tol"])
         res, dx = s.TurbGetStep()
         post = s.GetTurbulence()

@@ -107,7 +107,7 @@ def test_bicgstab_restatement_zero_rhs_and_identity():
 
 
 @pytest.mark.parametrize("name", ["channel_rans", "channel_rans_gg", "channel_rans_ign", "jet_rans_shipped", "jet_rans_perturbed",
-                                  "channel_air3_rans", "channel_rans_inlet_massflow"])
+                                  "channel_air3_rans", "channel_rans_inlet_massflow", "channel_rans_dualtime2"])
 def test_oracle_sst_transport_step_matches_reference(name):
     """rxo_turb_iterate — the restatement of CTurbSSTSolver's SingleGrid_Iteration (residuals, boundary conditions, FGMRES + LU-SGS in the
     reference's own order of operations, clipped update, Postprocessing) — against the harness dumps of the reference's turbulence solver
@@ -122,11 +122,18 @@ def test_oracle_sst_transport_step_matches_reference(name):
     for it in its:
         tpost = case.stage(it, 0, "tpost")
         o.set_solution(case.stage(it, 0, "U0")); o.set_temperature(case.stage(it, 0, "prev_V")[:, 0]); o.set_turbulence(case.stage(it, 0, "turb"))
+        dual = cf.get("dual_time", 0)
+        if dual:   # the flow solver's and the SST solver's stored time levels (the latter's dual-time source term reads both, :762-780)
+            o.set_time_levels(case.stage(it, 0, "Un"), case.stage(it, 0, "Un1")); o.set_inner_iteration(it % cf.get("dual_inner", 2))
+            o.turb_set_time_levels(case.stage(it, 0, "tUn"), case.stage(it, 0, "tUn1"))
         for rk in range(nrk):
             o.preprocess(it, False)
             if rk == 0:
                 o.set_old_solution(); o.time_step()
-            o.upwind_residual(); o.viscous_residual(); o.source_residual(); o.boundary_conditions()
+            o.upwind_residual(); o.viscous_residual(); o.source_residual()
+            if dual:
+                o.dual_time_residual()
+            o.boundary_conditions()
             o.explicit_update(cf["rk_alpha"][rk] if nrk > 1 else 1.0)
         o.preprocess(it, True)
         r = o.turb_iterate(case.stage(it, 0, "turb")[:, 1:3], case.stage(it, 0, "tblend"), tpost[:, 2], float(tpost[0, 11]), cf["kine_inf"], cf["omega_inf"],
