@@ -934,6 +934,28 @@ int rx_set_cfl(rx_ctx* c, double cfl) {
   c->o.cfl = cfl;
   return RX_OK;
 }
+// minimum of the local time steps over the owned points of every partition (Global_Delta_Time and its MPI_MIN reduction, :5227, :5264-5269):
+// two-stage minimum on the device, then one ncclAllReduce when a communicator exists; *glob points at the result on the device
+static int global_dt_min(rx_ctx* c, double** glob) {
+  const Dev& d = c->d;
+  cudaStream_t s = c->stream;
+  if (!c->dtPartial) {
+    c->dtBlocks = (int)nblk(d.nPointDomain, 256);
+    c->dtPartial = dalloc<double>(c, (size_t)c->dtBlocks + 1);
+    if (!c->dtPartial) { c->err = "rx_time_step: device allocation failed"; return RX_ERR_CUDA; }
+  }
+  *glob = c->dtPartial + c->dtBlocks;
+  k_dt_min_partial<<<c->dtBlocks, 256, 0, s>>>(d, c->dtPartial);
+  k_dt_min_final<<<1, 256, 0, s>>>(c->dtPartial, c->dtBlocks, *glob);
+  c->launches += 2;
+  if (c->comm) {
+    std::string why;
+    NcclApi* a = nccl_api(why);
+    const int e = a->AllReduce(*glob, *glob, 1, NCCL_FLOAT64, NCCL_MIN, c->comm->comm, s);
+    if (e) { c->err = std::string("rx_time_step: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+  }
+  return RX_OK;
+}
 int rx_time_step(rx_ctx* c) {
   const Dev& d = c->d;
   cudaStream_t s = c->stream;
@@ -948,44 +970,20 @@ int rx_time_step(rx_ctx* c) {
   }
   c->launches++;
   if (c->o.timeStepping) {
-    if (!c->dtPartial) {
-      c->dtBlocks = (int)nblk(d.nPointDomain, 256);
-      c->dtPartial = dalloc<double>(c, (size_t)c->dtBlocks + 1);
-      if (!c->dtPartial) { c->err = "rx_time_step: device allocation failed"; return RX_ERR_CUDA; }
-    }
-    double* glob = c->dtPartial + c->dtBlocks;
-    k_dt_min_partial<<<c->dtBlocks, 256, 0, s>>>(d, c->dtPartial);
-    k_dt_min_final<<<1, 256, 0, s>>>(c->dtPartial, c->dtBlocks, glob);
-    if (c->comm) {   // MPI_MIN over the ranks (:5264-5269)
-      std::string why;
-      NcclApi* a = nccl_api(why);
-      const int e = a->AllReduce(glob, glob, 1, NCCL_FLOAT64, NCCL_MIN, c->comm->comm, s);
-      if (e) { c->err = std::string("rx_time_step: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
-    }
+    double* glob = nullptr;
+    { const int rc = global_dt_min(c, &glob); if (rc) return rc; }
     // the Euler solver's variant (:2121-2139): from now on the CFL is UNST_CFL_NUMBER; if that is zero every point takes UNST_TIMESTEP
     if (!c->o.viscous) c->o.cfl = c->o.unstCfl;
     const int useFixed = (!c->o.viscous && c->o.cfl < EPS) ? 1 : 0;
     k_dt_fill<<<nblk(d.nPointDomain, 256), 256, 0, s>>>(d, glob, c->o.deltaUnstTime, useFixed);
-    c->launches += 3;
+    c->launches++;
   }
   if (c->o.dualTime) {
     if (c->intIter == 0 && c->o.unstCfl != 0.0) {   // the physical step follows UNST_CFL_NUMBER (:5276-5289): global minimum of the unclamped local steps
-      if (!c->dtPartial) {
-        c->dtBlocks = (int)nblk(d.nPointDomain, 256);
-        c->dtPartial = dalloc<double>(c, (size_t)c->dtBlocks + 1);
-        if (!c->dtPartial) { c->err = "rx_time_step: device allocation failed"; return RX_ERR_CUDA; }
-      }
-      double* glob = c->dtPartial + c->dtBlocks;
-      k_dt_min_partial<<<c->dtBlocks, 256, 0, s>>>(d, c->dtPartial);
-      k_dt_min_final<<<1, 256, 0, s>>>(c->dtPartial, c->dtBlocks, glob);
-      if (c->comm) {
-        std::string why;
-        NcclApi* a = nccl_api(why);
-        const int e = a->AllReduce(glob, glob, 1, NCCL_FLOAT64, NCCL_MIN, c->comm->comm, s);
-        if (e) { c->err = std::string("rx_time_step: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
-      }
+      double* glob = nullptr;
+      { const int rc = global_dt_min(c, &glob); if (rc) return rc; }
       k_dual_unst_dt<<<1, 1, 0, s>>>(glob, c->o.unstCfl, c->o.cfl, c->dtND);
-      c->launches += 3;
+      c->launches++;
     }
     k_dual_dt_clamp<<<nblk(d.nPointDomain, 256), 256, 0, s>>>(d, c->o.maxDt, c->dtND);
     c->launches++;
