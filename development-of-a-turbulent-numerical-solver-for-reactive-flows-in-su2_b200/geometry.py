@@ -230,6 +230,73 @@ def su2_dual_mesh(su2, rcm=True):
                 elems=elems, etype=etype)
 
 
+class _Su2Mesh(C.Structure):
+    _fields_ = [("nPoint", C.c_int64), ("nEdge", C.c_int64), ("nElem", C.c_int64), ("coord", C.POINTER(C.c_double)),
+                ("globalIndex", C.POINTER(C.c_int64)), ("etype", C.POINTER(C.c_int64)), ("elems", C.POINTER(C.c_int64)),
+                ("edgeNodes", C.POINTER(C.c_int64)), ("edgeNormal", C.POINTER(C.c_double)), ("volume", C.POINTER(C.c_double)),
+                ("nbPtr", C.POINTER(C.c_int64)), ("nbPoint", C.POINTER(C.c_int64)), ("nMarker", C.c_int),
+                ("markerTag", C.POINTER(C.c_char_p)), ("markerNVertex", C.POINTER(C.c_int64)),
+                ("markerNode", C.POINTER(C.POINTER(C.c_int64))), ("markerNormalNeighbor", C.POINTER(C.POINTER(C.c_int64))),
+                ("markerNormal", C.POINTER(C.POINTER(C.c_double)))]
+
+
+def _su2_mesh_dict(L, out):
+    """rx_su2_mesh -> the mesh dict of su2_dual_mesh (arrays copied, the struct released)."""
+    try:
+        nP, nE, nEl = out.nPoint, out.nEdge, out.nElem
+        arr = lambda ptr, n, shape=None: np.ctypeslib.as_array(ptr, shape=(n,)).copy().reshape(shape or (n,))
+        markers = []
+        for m in range(out.nMarker):
+            nv = out.markerNVertex[m]
+            markers.append(dict(tag=out.markerTag[m].decode(), kind=0, node=arr(out.markerNode[m], nv) if nv else np.zeros(0, np.int64),
+                                normalNeighbor=arr(out.markerNormalNeighbor[m], nv) if nv else np.zeros(0, np.int64),
+                                normal=arr(out.markerNormal[m], 2 * nv, (nv, 2)) if nv else np.zeros((0, 2))))
+        return dict(nPoint=nP, nPointDomain=nP, nEdge=nE, edgeNodes=arr(out.edgeNodes, 2 * nE, (nE, 2)), edgeNormal=arr(out.edgeNormal, 2 * nE, (nE, 2)),
+                    coord=arr(out.coord, 2 * nP, (nP, 2)), volume=arr(out.volume, nP), nbPtr=arr(out.nbPtr, nP + 1), nbPoint=arr(out.nbPoint, 2 * nE),
+                    markers=markers, globalIndex=arr(out.globalIndex, nP), elems=arr(out.elems, 4 * nEl, (nEl, 4)), etype=arr(out.etype, nEl))
+    finally:
+        L.rx_su2_mesh_free(C.byref(out))
+
+
+def _su2_lib():
+    from .rx_solver import load_library
+    L = load_library()
+    L.rx_su2_mesh_error.restype = C.c_char_p
+    return L
+
+
+def load_su2_mesh(path, rcm=True):
+    """An ASCII .su2 file -> the flat mesh dict of su2_dual_mesh, by the library's host code (rx_su2_mesh_read, csrc/host/rx_su2_mesh.cpp):
+    parse, point connectivity, RCM numbering, orientation, edges, control volumes, vertices and normal neighbours in one native pass —
+    the same arrays, bit for bit, as su2_dual_mesh(read_su2(path)), which stays as the readable specification."""
+    L = _su2_lib()
+    out = _Su2Mesh()
+    rc = L.rx_su2_mesh_read(str(path).encode(), C.c_int(1 if rcm else 0), C.byref(out))
+    if rc != 0:
+        raise ValueError(L.rx_su2_mesh_error().decode())
+    return _su2_mesh_dict(L, out)
+
+
+def su2_dual_mesh_native(su2, rcm=True):
+    """su2_dual_mesh on a read_su2()-style dict through the library (rx_su2_mesh_build)."""
+    L = _su2_lib()
+    coord = np.ascontiguousarray(su2["coord"], dtype=np.float64); etype = np.ascontiguousarray(su2["etype"], dtype=np.int64)
+    elems = np.ascontiguousarray(su2["elems"], dtype=np.int64)
+    segs = [np.ascontiguousarray(s, dtype=np.int64).reshape(-1, 2) for _, s in su2["markers"]]
+    ptr = np.zeros(len(segs) + 1, dtype=np.int64)
+    if segs:
+        np.cumsum([s.shape[0] for s in segs], out=ptr[1:])
+    seg = np.ascontiguousarray(np.concatenate(segs) if segs else np.zeros((0, 2), np.int64))
+    tags = (C.c_char_p * max(len(segs), 1))(*[t.encode() for t, _ in su2["markers"]])
+    pi = lambda a: a.ctypes.data_as(C.POINTER(C.c_int64))
+    out = _Su2Mesh()
+    rc = L.rx_su2_mesh_build(C.c_int64(coord.shape[0]), coord.ctypes.data_as(C.POINTER(C.c_double)), C.c_int64(etype.shape[0]), pi(etype), pi(elems),
+                             C.c_int(len(segs)), tags, pi(ptr), pi(seg), C.c_int(1 if rcm else 0), C.byref(out))
+    if rc != 0:
+        raise ValueError(L.rx_su2_mesh_error().decode())
+    return _su2_mesh_dict(L, out)
+
+
 def wall_distance(mesh, wall_tags, device=0):
     """ComputeWall_Distance on the GPU (rx_wall_distance): distance of every point to the nearest node of the named markers."""
     from .rx_solver import load_library, RxError

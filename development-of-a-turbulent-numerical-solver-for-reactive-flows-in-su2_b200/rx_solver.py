@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(HERE, "librx_cuda.so")
 CSRC = os.path.join(HERE, "csrc")
 HOST_PARTITION = os.path.join(CSRC, "host", "rx_partition.cpp")   # host-only graph tools of the same library
 HOST_GEOMETRY = os.path.join(CSRC, "host", "rx_geometry.cpp")     # host-only dual-mesh builder
+HOST_SU2_MESH = os.path.join(CSRC, "host", "rx_su2_mesh.cpp")     # host-only .su2 reader + geometry preprocessing
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
@@ -29,11 +30,11 @@ class RxError(RuntimeError):
 
 def build_library(force=False, verbose=False):
     """nvcc cross-compiles the CUDA extension for sm_100a (works without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + [HOST_PARTITION, HOST_GEOMETRY]
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + [HOST_PARTITION, HOST_GEOMETRY, HOST_SU2_MESH]
     srcs.append(os.path.join(os.path.dirname(HERE), "include", "rx_cuda.h"))
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "rx_cuda.cu"), HOST_PARTITION, HOST_GEOMETRY]
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "rx_cuda.cu"), HOST_PARTITION, HOST_GEOMETRY, HOST_SU2_MESH]
     subprocess.check_call(cmd)
     return LIB_PATH
 
@@ -106,7 +107,7 @@ EXPORTS = ["rx_supported_species", "rx_create", "rx_destroy", "rx_last_error", "
            "rx_halo_pack", "rx_halo_unpack", "rx_halo_width", "rx_launch_count", "rx_fp64_peak", "rx_bc_marker", "rx_get_bc_state", "rx_get_limiter",
            "rx_partition_kway", "rx_partition_backend", "rx_rcm_order", "rx_get_residual_max", "rx_get_edge_order",
            "rx_set_wall_distance", "rx_turb_postprocess", "rx_get_turbulence", "rx_wall_distance", "rx_compute_wall_distance",
-           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl", "rx_dual_mesh_tri", "rx_dual_mesh_free",
+           "rx_residual_rms_static", "rx_get_status", "rx_libm_eval", "rx_qr_eval", "rx_state_snapshot", "rx_restart_write", "rx_restart_read", "rx_tecplot_write", "rx_set_cfl", "rx_dual_mesh_tri", "rx_dual_mesh_free", "rx_su2_mesh_read", "rx_su2_mesh_build", "rx_su2_mesh_free", "rx_su2_mesh_error",
            "rx_set_time_levels", "rx_get_time_levels", "rx_shift_time_levels", "rx_set_inner_iteration", "rx_get_delta_unst_time", "rx_residual_dual_time",
            "rx_turb_set_time_levels", "rx_turb_get_time_levels", "rx_turb_shift_time_levels",
            "rx_turb_set_state", "rx_turb_iterate", "rx_turb_get_step",

@@ -286,6 +286,36 @@ typedef struct {
 int rx_dual_mesh_tri(int64_t nPoint, const double* coord /* [nPoint][2] */, int64_t nTri, const int64_t* tri /* [nTri][3] */, rx_dual_mesh* out);
 void rx_dual_mesh_free(rx_dual_mesh*);
 
+/* An ASCII .su2 mesh file (2-D, triangles and quadrilaterals) -> the flat dual mesh in the REFERENCE's point, edge, neighbour and vertex
+ * numbering (csrc/host/rx_su2_mesh.cpp): CPhysicalGeometry::Read_SU2_Format (geometry_structure.cpp:4819), SetPoint_Connectivity :9145,
+ * SetRCM_Ordering :9200 (rcm != 0), Check_IntElem_/Check_BoundElem_Orientation :8542/:8825, SetEdges :8680, SetControlVolume :10457, SetVertex :9451,
+ * SetBoundControlVolume :9595, FindNormal_Neighbor.  rx_su2_mesh_build takes the parsed arrays instead of a file (elems [nElem][4], -1 padded;
+ * boundary lines of marker m = seg[segPtr[m] .. segPtr[m+1]) as node pairs).  Arrays are malloc'ed; release with rx_su2_mesh_free.
+ * rx_su2_mesh_error: message of the calling thread's last failed call. */
+typedef struct {
+  int64_t nPoint, nEdge, nElem;
+  double* coord;          /* [nPoint][2], in the new numbering */
+  int64_t* globalIndex;   /* [nPoint]: the file's index of every point (CPoint::GetGlobalIndex) */
+  int64_t* etype;         /* [nElem]: 5 triangle, 9 quadrilateral */
+  int64_t* elems;         /* [nElem][4], oriented, -1 padded */
+  int64_t* edgeNodes;     /* [nEdge][2] */
+  double* edgeNormal;     /* [nEdge][2] */
+  double* volume;         /* [nPoint] */
+  int64_t* nbPtr;         /* [nPoint+1] */
+  int64_t* nbPoint;       /* [2 nEdge] */
+  int nMarker;
+  char** markerTag;                 /* [nMarker] */
+  int64_t* markerNVertex;           /* [nMarker] */
+  int64_t** markerNode;             /* [nMarker][nVertex] */
+  int64_t** markerNormalNeighbor;   /* [nMarker][nVertex] */
+  double** markerNormal;            /* [nMarker][nVertex][2], pointing into the domain (SU2's convention) */
+} rx_su2_mesh;
+int rx_su2_mesh_read(const char* path, int rcm, rx_su2_mesh* out);
+int rx_su2_mesh_build(int64_t nPoint, const double* coord, int64_t nElem, const int64_t* etype, const int64_t* elems, int nMarker,
+                      const char* const* tags, const int64_t* segPtr, const int64_t* seg, int rcm, rx_su2_mesh* out);
+void rx_su2_mesh_free(rx_su2_mesh*);
+const char* rx_su2_mesh_error(void);
+
 /* SU2 native ASCII restart files straight from / into the device-resident state (csrc/rx_restart.cuh).
  * rx_restart_write replaces COutput::SetRestart for the reactive solvers (output_structure.cpp:3858-4060; columns of MergeSolution
  * :1991-2130): "PointID" x y Conservative_1..nVar [k omega] Pressure Temperature Mach [Laminar_Viscosity [mu_t]], every value as

@@ -232,3 +232,66 @@ def test_uniform_state_leaves_no_convective_residual_on_a_mixed_mesh():
     assert (~boundary).sum() > 10
     assert (np.abs(R[~boundary]) / scale).max() <= 1e-12
     assert np.abs(R[boundary]).max() > 0   # open boundary faces do carry flux until the BCs close them
+
+
+def _same_mesh(a, b):
+    for k in ("nPoint", "nPointDomain", "nEdge"):
+        assert a[k] == b[k], k
+    for k in ("globalIndex", "coord", "nbPtr", "nbPoint", "edgeNodes", "edgeNormal", "volume", "elems", "etype"):
+        np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+    assert [m["tag"] for m in a["markers"]] == [m["tag"] for m in b["markers"]]
+    for ma, mb in zip(a["markers"], b["markers"]):
+        for k in ("node", "normal", "normalNeighbor"):
+            np.testing.assert_array_equal(ma[k], mb[k], err_msg=ma["tag"] + " " + k)
+
+
+def test_native_su2_preprocessing_equals_the_specification_and_the_reference(tmp_path):
+    """rx_su2_mesh_read / rx_su2_mesh_build (csrc/host/rx_su2_mesh.cpp: parse, connectivity, RCM, orientation, edges, control volumes,
+    vertices in one native pass) against su2_dual_mesh, array by array and bit for bit — on the shipped quadrilateral jet mesh (also against
+    the geometry the reference built from it), a mixed mesh with mis-oriented elements, with and without the RCM numbering, from arrays and
+    from a file."""
+    pk, geo = _geo()
+    jet = _jet_su2()
+    z = np.load("%s/jet_rans_shipped.npz" % GOLDEN)
+    tags = [m["tag"] for m in json.loads(bytes(z["meta_json"]).decode())["markers"]]
+    nat = geo.su2_dual_mesh_native(jet)
+    _compare(nat, z, tags)                                   # the reference's own geometry
+    _same_mesh(nat, geo.su2_dual_mesh(jet))
+    path = str(tmp_path / "jet.su2")
+    geo.write_su2(path, jet)
+    _same_mesh(geo.load_su2_mesh(path), nat)                 # through the file parser
+    bad = dict(jet)
+    el = jet["elems"].copy(); el[::3, 1], el[::3, 3] = jet["elems"][::3, 3], jet["elems"][::3, 1]
+    bad["elems"] = el
+    bad["markers"] = [(t, s[:, ::-1].copy() if k % 2 else s) for k, (t, s) in enumerate(jet["markers"])]
+    _same_mesh(geo.su2_dual_mesh_native(bad), geo.su2_dual_mesh(bad))
+    mixed = _mixed_su2(geo)
+    for rcm in (True, False):
+        _same_mesh(geo.su2_dual_mesh_native(mixed, rcm=rcm), geo.su2_dual_mesh(mixed, rcm=rcm))
+    p2 = str(tmp_path / "mixed.su2")
+    geo.write_su2(p2, mixed)
+    _same_mesh(geo.load_su2_mesh(p2, rcm=False), geo.su2_dual_mesh(geo.read_su2(p2), rcm=False))
+
+
+def test_native_su2_reader_refuses_malformed_files(tmp_path):
+    pk, geo = _geo()
+    with pytest.raises(ValueError, match="cannot open"):
+        geo.load_su2_mesh(str(tmp_path / "absent.su2"))
+    mixed = _mixed_su2(geo)
+    good = str(tmp_path / "m.su2")
+    geo.write_su2(good, mixed)
+    txt = open(good).read()
+    cases = {"3d.su2": (txt.replace("NDIME= 2", "NDIME= 3"), "2-D"),
+             "cut.su2": (txt[:len(txt) // 3], "ends inside|no points"),
+             "hex.su2": (txt.replace("\n9 ", "\n12 ", 1), "not a triangle or quadrilateral")}
+    for name, (body, msg) in cases.items():
+        p = str(tmp_path / name)
+        open(p, "w").write(body)
+        with pytest.raises(ValueError, match=msg):
+            geo.load_su2_mesh(p)
+    far = dict(mixed); far["markers"] = [("bottom", np.array([[0, mixed["coord"].shape[0] - 1]]))] + mixed["markers"][1:]
+    with pytest.raises(ValueError, match="not a face"):
+        geo.su2_dual_mesh_native(far)
+    out = dict(mixed); e2 = mixed["elems"].copy(); e2[0, 0] = 10 ** 6; out["elems"] = e2
+    with pytest.raises(ValueError, match="outside the mesh"):
+        geo.su2_dual_mesh_native(out)
