@@ -507,7 +507,7 @@ int rx_set_wall_distance(rx_ctx* c, const double* dist) {
 // (CPhysicalGeometry::ComputeWall_Distance :8990-9060).  Single-partition meshes: a partition sees only its own wall nodes.
 int rx_compute_wall_distance(rx_ctx* c) {
   if (!c->tpost) { c->err = "rx_compute_wall_distance: not a RANS context"; return RX_ERR_ARG; }
-  if (c->d.nPoint != c->d.nPointDomain) { c->err = "rx_compute_wall_distance: partitioned context (a partition sees only its own wall nodes); use rx_set_wall_distance"; return RX_ERR_UNSUPPORTED; }
+  if (c->d.nPoint != c->d.nPointDomain && !c->comm) { c->err = "rx_compute_wall_distance: a partition sees only its own wall nodes: give it the communicator (rx_comm_init), or use rx_set_wall_distance"; return RX_ERR_UNSUPPORTED; }
   const Dev& d = c->d;
   long long nWall = 0;
   for (const MarkerDev& m : c->markers) if (m.kind == 3 || m.kind == 4) nWall += m.nVertex;
@@ -519,6 +519,42 @@ int rx_compute_wall_distance(rx_ctx* c) {
       cudaMemcpyAsync(wn + off, m.node, (size_t)m.nVertex * sizeof(int), cudaMemcpyDeviceToDevice, c->stream);
       off += m.nVertex;
     }
+  if (c->comm) {
+    // the wall nodes of every partition (the reference gathers them over the ranks, geometry_structure.cpp:9010-9040).  Two sum-reductions
+    // do the gather: the counts, each rank in its own slot, then the coordinates, each rank in its own segment of a zeroed list — a sum
+    // with zeros is exact, and a minimum does not depend on the order of the list
+    const int nr = c->comm->nRanks, me = c->comm->rank;
+    double* cnt = nullptr;
+    int rc = RX_OK;
+    if (cudaMalloc(&cnt, (size_t)nr * sizeof(double)) != cudaSuccess) { cudaFree(wn); c->err = "rx_compute_wall_distance: device allocation failed"; return RX_ERR_CUDA; }
+    std::vector<double> h((size_t)nr, 0.0);
+    h[(size_t)me] = (double)nWall;
+    cudaMemcpyAsync(cnt, h.data(), (size_t)nr * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+    rc = comm_allreduce_sum(c, cnt, nr);
+    const char* cudaFail = "rx_compute_wall_distance: CUDA error while gathering the wall nodes over the partitions";
+    if (!rc && cudaMemcpyAsync(h.data(), cnt, (size_t)nr * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) { rc = RX_ERR_CUDA; c->err = cudaFail; }
+    if (!rc && cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = RX_ERR_CUDA; c->err = cudaFail; }
+    cudaFree(cnt);
+    long long total = 0, mine = 0;
+    for (int r = 0; r < nr; ++r) { if (r == me) mine = total; total += (long long)h[(size_t)r]; }
+    double* wall = nullptr;
+    if (!rc && 2 * total > 0x7fffffffLL) { rc = RX_ERR_UNSUPPORTED; c->err = "rx_compute_wall_distance: more than 2^30 wall nodes"; }
+    if (!rc && cudaMalloc(&wall, (size_t)std::max<long long>(2 * total, 1) * sizeof(double)) != cudaSuccess) { rc = RX_ERR_CUDA; c->err = cudaFail; }
+    if (!rc) {
+      cudaMemsetAsync(wall, 0, (size_t)std::max<long long>(2 * total, 1) * sizeof(double), c->stream);
+      if (nWall) { k_wall_gather<<<nblk(nWall, 256), 256, 0, c->stream>>>(d, nWall, wn, wall + 2 * mine); c->launches++; }
+      if (total) rc = comm_allreduce_sum(c, wall, (int)(2 * total));
+    }
+    if (!rc) {
+      k_wall_distance_list<<<nblk(d.nPoint, 256), 256, 0, c->stream>>>(d, total, wall, c->tpost + (size_t)TP_DIST * d.np);
+      c->launches++;
+      if (cudaStreamSynchronize(c->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) { rc = RX_ERR_CUDA; c->err = cudaFail; }
+    }
+    cudaFree(wall); cudaFree(wn);
+    if (rc) return rc;
+    c->haveWallDist = true;
+    return RX_OK;
+  }
   k_wall_distance_ctx<<<nblk(d.nPoint, 256), 256, 0, c->stream>>>(d, nWall, wn, c->tpost + (size_t)TP_DIST * d.np);
   c->launches++;
   const cudaError_t e = cudaStreamSynchronize(c->stream);
@@ -1462,7 +1498,7 @@ static int comm_allreduce_sum(rx_ctx* c, double* dev, int n) {
   std::string why;
   NcclApi* a = nccl_api(why);
   const int e = a->AllReduce(dev, dev, (size_t)n, NCCL_FLOAT64, NCCL_SUM, m->comm, c->stream);
-  if (e) { c->err = std::string("rx_turb_iterate: NCCL all-reduce: ") + a->GetErrorString(e); return RX_ERR_CUDA; }
+  if (e) { c->err = std::string("NCCL all-reduce (sum): ") + a->GetErrorString(e); return RX_ERR_CUDA; }
   return RX_OK;
 }
 // norms of the whole job from the partitions' sums of squares (SetResidual_RMS with MPI, solver_structure.cpp:188-260): one all-reduce

@@ -811,4 +811,31 @@ __global__ void __launch_bounds__(256) k_wall_distance_ctx(const Dev d, long lon
   if (in) dist[p] = nWall > 0 ? sqrt(best) : 0.0;
 }
 
+// ... and for a partition of a multi-GPU job: the wall nodes of ALL partitions, gathered as coordinates (rx_compute_wall_distance)
+__global__ void k_wall_gather(const Dev d, long long n, const int* __restrict__ wallNode, double* __restrict__ out) {
+  const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (k < n) { const int q = wallNode[k]; out[2 * k] = d.x[q]; out[2 * k + 1] = d.y[q]; }
+}
+__global__ void __launch_bounds__(256) k_wall_distance_list(const Dev d, long long nWall, const double* __restrict__ wall, double* __restrict__ dist) {
+  __shared__ double wx[WD_TILE], wy[WD_TILE];
+  const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const bool in = p < d.nPoint;
+  const double x = in ? d.x[p] : 0.0, y = in ? d.y[p] : 0.0;
+  double best = CUDART_INF;
+  for (long long w0 = 0; w0 < nWall; w0 += WD_TILE) {
+    const int n = (int)min((long long)WD_TILE, nWall - w0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) { wx[k] = wall[2 * (w0 + k)]; wy[k] = wall[2 * (w0 + k) + 1]; }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+      const double dx = x - wx[k], dy = y - wy[k];
+      double d2 = 0.0;
+      d2 += dx * dx;
+      d2 += dy * dy;
+      best = d2 < best ? d2 : best;
+    }
+  }
+  if (in) dist[p] = nWall > 0 ? sqrt(best) : 0.0;
+}
+
 }  // namespace rx

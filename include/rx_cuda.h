@@ -121,7 +121,7 @@ int rx_set_turbulence(rx_ctx*, const double* turb6);      /* [nPoint][6]: muT, k
 int rx_wall_distance(int64_t nPoint, const double* xy /* [nPoint][2] */, int64_t nWall, const double* wallXy /* [nWall][2]: nodes of the HEAT_FLUX / ISOTHERMAL markers */,
                      double* dist /* [nPoint] */, int device);   /* CPhysicalGeometry::ComputeWall_Distance geometry_structure.cpp:8990 (nearest wall NODE), host arrays, no context */
 int rx_set_wall_distance(rx_ctx*, const double* dist /* [nPoint] */);
-int rx_compute_wall_distance(rx_ctx*);   /* the same from the context's own mesh, on the device: nearest node of its ISOTHERMAL / HEAT_FLUX markers (single-partition meshes) */
+int rx_compute_wall_distance(rx_ctx*);   /* the same from the context's own mesh, on the device: nearest node of its ISOTHERMAL / HEAT_FLUX markers; a partition with a communicator (rx_comm_init) gathers the wall nodes of all partitions first, as the reference's MPI build does (collective: every rank calls it) */
 int rx_turb_postprocess(rx_ctx*, const double* kOmega /* [nPoint][2]; NULL: the (k, omega) uploaded by the previous call */, double sigmaK /* CTurbSSTVariable::sigma_k = constants[0] */, int stage);
 /* The SST transport step on the device (remainder; csrc/rx_turb_step.cuh): one
  * CSingleGridIntegration::SingleGrid_Iteration of CTurbSSTSolver (integration_time.cpp:777-834) — Preprocessing

@@ -44,7 +44,15 @@ def turb_mode(rank, world, local, dev, chem):
         s = pk.CReactiveNSSolverGPU(m, chem, opts, device=local)
         s.SetSolution(Ug[glob]); s.SetTemperature(Tg[glob]); s.SetTurbulence(tg[glob])
         par.library_comm_init(s, plan, dev)
-        s.SetWall_Distance(dist_g[glob])
+        # wall distance of a partition: the wall nodes of all partitions gathered inside the library (rx_compute_wall_distance with a
+        # communicator) — the same distances, bit for bit, as the whole mesh gives; owned and halo points alike
+        s.ComputeWall_Distance()
+        wd_bad = int(np.sum(s.GetTurbulence()[:, 2] != dist_g[glob]))
+        tw = torch.tensor([float(wd_bad)], dtype=torch.float64, device=dev)
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        if float(tw[0]) != 0.0:
+            ok = False
+            report.append("%s: partitioned wall distance differs at %d points" % (label, int(tw[0])))
         par.distributed_turb_postprocess(s, None, np.ascontiguousarray(tg[glob, 1:3]))
         its_p, its_r = [], []
         for it in range(3):
