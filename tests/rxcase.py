@@ -191,6 +191,7 @@ class Oracle:
         o = _Opts(**od)
         self.ctx = C.c_void_p(L.rxo_create(C.byref(ms), C.byref(ch), C.byref(o)))
         self.nP, self.nVar, self.nPrim, self.nGrad = nP, Ns + 4, Ns + 7, Ns + 4
+        self._nE = nE
 
     def __del__(self):
         try:
@@ -255,6 +256,12 @@ class Oracle:
     def turb_set_time_levels(self, kwN, kwN1):
         a = np.ascontiguousarray(kwN, dtype=np.float64); b = np.ascontiguousarray(kwN1, dtype=np.float64)
         self.lib.rxo_turb_set_time_levels(self.ctx, _p(a), _p(b))
+
+    def sm_iteration_counts(self):
+        """BiCGSTAB iteration count of the Stefan-Maxwell solve of every interior edge, on the context's current primitive state."""
+        it = np.zeros(self._nE, dtype=np.int32)
+        self.lib.rxo_sm_iteration_counts(self.ctx, it.ctypes.data_as(C.POINTER(C.c_int32)))
+        return it
 
     def set_inner_iteration(self, it): self.lib.rxo_set_inner_iteration(self.ctx, C.c_int64(it))
     def dual_time_residual(self): self.lib.rxo_dual_time_residual(self.ctx)

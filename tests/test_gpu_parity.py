@@ -119,6 +119,28 @@ def test_dual_time_fused_iterations_and_level_shift(name):
     s.close()
 
 
+@pytest.mark.parametrize("name", ["channel_lam_rk", "channel_lam_edge", "channel_rans", "jet_rans_perturbed"])
+def test_stefan_maxwell_iteration_counts_match_the_restatement(name):
+    """SURVEY.md 8(d), last parity metric: the BiCGSTAB iteration count of the Stefan-Maxwell solve of EVERY interior edge — what the
+    viscous kernel records as its ordering key (rx_get_edge_order; + 19 where the SST closure's QR ran) — equals the count of the CPU
+    restatement of Eigen's solver on the same state, edge by edge, hence the same histogram."""
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    it = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})[0]
+    o, s = Oracle(case), gpu_solver(case)
+    for q in (o, s):
+        q.set_solution(case.stage(it, 0, "U0")); q.set_temperature(case.stage(it, 0, "prev_V")[:, 0]); q.set_turbulence(case.stage(it, 0, "turb"))
+        q.preprocess(it, False)
+    s.set_old_solution(); s.viscous_residual()
+    _, key = s.EdgeOrder()
+    want = o.sm_iteration_counts()
+    got = key.astype(np.int32) % 19
+    hist = np.bincount(want, minlength=19)
+    print(name, "S-M iterations histogram", {int(k): int(v) for k, v in enumerate(hist) if v})
+    assert np.array_equal(got, want), "%d of %d edges differ" % (int((got != want).sum()), want.size)
+    assert hist[1:].sum() > 0   # some edge did iterate
+    s.close()
+
+
 def test_residual_max_and_location():
     """CSolver::AddRes_Max (solver_direct_reactive.cpp:2436): largest |LinSysRes| per variable and the FIRST point attaining it,
     reduced on the device with the residual norms."""
