@@ -37,7 +37,10 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
   // every *_Ref is 1 on the CUDA path, as in all shipped cfgs (REF_DIMENSIONALIZATION= DIMENSIONAL, SI units: solver_direct_reactive.cpp:846-887)
   if (config->GetRef_NonDim() != DIMENSIONAL) throw std::runtime_error("CReactiveNSSolverGPU: REF_DIMENSIONALIZATION other than DIMENSIONAL is not on the CUDA path");
-  if (config->GetViscous_Limiter_Flow()) throw std::runtime_error("CReactiveNSSolverGPU: VISCOUS_LIMITER_FLOW (limited gradients in vorticity / strain) is not on the CUDA path");
+  // VISCOUS_LIMITER_FLOW: CAvgGradReactive_Flow multiplies the gradients of T, u, v by the limiters (numerics_direct_reactive.cpp:1482-1505), which
+  // Viscous_Residual hands over only under SPATIAL_ORDER_FLOW= 2ND_ORDER_LIMITER (:5326); without it the reference dereferences an unset array
+  if (config->GetViscous_Limiter_Flow() && config->GetSpatialOrder_Flow() != SECOND_ORDER_LIMITER)
+    throw std::runtime_error("CReactiveNSSolverGPU: VISCOUS_LIMITER_FLOW needs SPATIAL_ORDER_FLOW= 2ND_ORDER_LIMITER (the reference reads an unset limiter array otherwise)");
   if (config->GetSystemMeasurements() == US) throw std::runtime_error("CReactiveNSSolverGPU: SYSTEM_MEASUREMENTS= US is not on the CUDA path");
   // A partitioned geometry needs the device halo exchange behind Set_MPI_Solution / _Primitive_Gradient / _Primitive_Limiter
   // (solver_reactive.hpp:162,176,183), which this class does not override: the base class would exchange host node[] only and the
@@ -163,6 +166,7 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   // (REACTIVE_RANS: the reference's host SST solver keeps its own time levels and reads the flow density of the three levels from node[],
   // where CIntegration::SetDualTime_Solver keeps them current; the device SST solver refuses dual time stepping)
   o.dualTime = dualTime; o.deltaUnstTimeND = config->GetDelta_UnstTimeND();
+  o.viscLimiter = (viscousMode && config->GetViscous_Limiter_Flow()) ? 1 : 0;
   o.device = env_int("SU2_RX_DEVICE", 0);
 
   const int rc = rx_create(&ctx, &mesh, &chem, &o);

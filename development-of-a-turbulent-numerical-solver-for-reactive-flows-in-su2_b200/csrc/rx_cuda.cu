@@ -221,7 +221,11 @@ template <int NS>
 static void launch_edge_visc(rx_ctx* c, const ChemC<NS>& cc, cudaStream_t s) {
   const Dev& d = c->d;
   if constexpr (NS == 9) {
-    if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(cc, c->o, d);
+    if (c->o.viscLimiter) {   // VISCOUS_LIMITER_FLOW: the same kernel with the limited mean gradients compiled in
+      if (c->o.rans) k_edge_visc_pair<9, true, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(cc, c->o, d);
+      else k_edge_visc_pair<9, false, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(cc, c->o, d);
+    }
+    else if (c->o.rans) k_edge_visc_pair<9, true><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR_RANS, s>>>(cc, c->o, d);
     else k_edge_visc_pair<9, false><<<nblk(2 * d.nEdge, VP_BS), VP_BS, SM_PAIR, s>>>(cc, c->o, d);
   } else {
     if (c->o.rans) k_edge_visc_generic<NS, true><<<nblk(d.nEdge, EDGE_BS), EDGE_BS, SM_VISC, s>>>(cc, c->o, d);
@@ -236,6 +240,8 @@ static cudaError_t set_kernel_attributes() {
   if constexpr (NS == 9) {
     e = cudaFuncSetAttribute(k_edge_visc_pair<9, true>, at, (int)SM_PAIR_RANS);
     if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false>, at, (int)SM_PAIR);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_pair<9, true, true>, at, (int)SM_PAIR_RANS);
+    if (e == cudaSuccess && SM_PAIR > 48 * 1024) e = cudaFuncSetAttribute(k_edge_visc_pair<9, false, true>, at, (int)SM_PAIR);
   } else {
     e = cudaFuncSetAttribute(k_edge_visc_generic<NS, true>, at, smv);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_edge_visc_generic<NS, false>, at, smv);
@@ -310,6 +316,8 @@ int rx_create(rx_ctx** out, const rx_mesh* m, const rx_chem* ch, const rx_opts* 
   o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
   o.timeStepping = op->timeStepping; o.unstCfl = op->unstCfl; o.deltaUnstTime = op->deltaUnstTime;
   o.dualTime = op->dualTime; o.deltaUnstTimeND = op->deltaUnstTimeND;
+  o.viscLimiter = op->viscLimiter ? 1 : 0;
+  if (o.viscLimiter && !(op->viscous && op->secondOrder && op->limiter)) { g_create_error = "rx_create: viscLimiter (VISCOUS_LIMITER_FLOW) needs a viscous context with secondOrder and limiter set: the limiters are those of SPATIAL_ORDER_FLOW= 2ND_ORDER_LIMITER"; delete c; return RX_ERR_ARG; }
   if (o.dualTime < 0 || o.dualTime > 2 || (o.dualTime && o.timeStepping)) { g_create_error = "rx_create: dualTime must be 0, 1 or 2 and excludes timeStepping"; delete c; return RX_ERR_ARG; }
   if (o.dualTime && !(o.deltaUnstTimeND > 0.0) && o.unstCfl == 0.0) { g_create_error = "rx_create: dual time stepping needs a physical time step (deltaUnstTimeND) or an unsteady CFL number"; delete c; return RX_ERR_ARG; }
   o.secondOrder = op->secondOrder; o.limiter = op->secondOrder ? op->limiter : 0; o.limCoeff = op->limCoeff; o.refElemLength = op->refElemLength;

@@ -92,6 +92,7 @@ struct Opts {
   double limCoeff, refElemLength;
   int timeStepping; double unstCfl, deltaUnstTime;
   int dualTime; double deltaUnstTimeND;
+  int viscLimiter;
 };
 
 // ---- spline (MathTools::GetSpline, Common/src/Tools/spline.cpp:61-77) ---------------------------

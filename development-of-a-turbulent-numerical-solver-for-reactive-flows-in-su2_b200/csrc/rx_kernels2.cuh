@@ -350,6 +350,14 @@ __global__ void __launch_bounds__(EDGE_BS) k_edge_visc_generic(const __grid_cons
   ViscEnd<NS> I, J;
   load_visc_end<NS>(d, o, i, I, true);
   load_visc_end<NS>(d, o, j, J, true);
+  if (o.viscLimiter) {   // VISCOUS_LIMITER_FLOW (numerics_direct_reactive.cpp:1482-1505): gradients of T, u, v times the limiter of their variable
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const double li = d.lim[r * d.np + i], lj = d.lim[r * d.np + j];
+      const int g = (r == 0 ? G_T : G_VX + r - 1) * 2;
+      I.g[g] = I.g[g] * li; I.g[g + 1] = I.g[g + 1] * li; J.g[g] = J.g[g] * lj; J.g[g + 1] = J.g[g + 1] * lj;
+    }
+  }
   extern __shared__ double smat[];
   const double sigma_k = RANS ? d.turb[5 * d.np + i] : 1.0;   // sigma_k of the first node (:5345)
   double res[NV];

@@ -335,7 +335,7 @@ constexpr TriQ make_triq() {
 }
 __constant__ TriQ c_triq = make_triq();
 
-template <int NS, bool RANS>
+template <int NS, bool RANS, bool VLIM = false>   // VLIM: VISCOUS_LIMITER_FLOW (its own instantiation: the default kernel is untouched)
 #ifdef RX_VP_MAXNREG   // explicit register cap instead of a resident-block target (tuning hook)
 __global__ void __maxnreg__(RX_VP_MAXNREG) k_edge_visc_pair(
 #else
@@ -420,6 +420,17 @@ __global__ void __launch_bounds__(VP_BS, VP_MINB) k_edge_visc_pair(
       const double* g = d.grad + (size_t)(gr * 2) * np;
       gi0[q] = g[pi]; gj0[q] = g[pj]; gi1[q] = g[np + pi]; gj1[q] = g[np + pj];
       vi[q] = val[pi]; vj[q] = val[pj];
+    }
+    if constexpr (VLIM) {
+      // numerics_direct_reactive.cpp:1482-1505: the gradients of T, u, v enter the mean times the limiter of their variable (Limiter_Primitive rows
+      // T, u, v); mole-fraction rows are not limited.  Slot 0 holds T | v, slot 1 holds u | X_8.
+      const int r0 = l ? 2 : 0;
+      const double li0 = d.lim[r0 * np + pi], lj0 = d.lim[r0 * np + pj];
+      gi0[0] = gi0[0] * li0; gi1[0] = gi1[0] * li0; gj0[0] = gj0[0] * lj0; gj1[0] = gj1[0] * lj0;
+      if (!l) {
+        const double li1 = d.lim[1 * np + pi], lj1 = d.lim[1 * np + pj];
+        gi0[1] = gi0[1] * li1; gi1[1] = gi1[1] * li1; gj0[1] = gj0[1] * lj1; gj1[1] = gj1[1] * lj1;
+      }
     }
     const Recip rd2 = frecip(dist2);   // one refined reciprocal serves the twelve quotients
     bool bad = false;

@@ -70,7 +70,7 @@ class _Opts(C.Structure):
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
                 ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
                 ("device", C.c_int), ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double),
-                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double)]
+                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double), ("viscLimiter", C.c_int)]
 
 
 class _TurbOpts(C.Structure):
@@ -277,7 +277,7 @@ class CReactiveNSSolverGPU:
         self.nPoint, self.nPointDomain, self.nEdge = int(mesh["nPoint"]), int(mesh["nPointDomain"]), int(en.shape[0])
         ms = _Mesh(self.nPoint, self.nPointDomain, self.nEdge, _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])),
                    _d(k(mesh["volume"])), _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
-        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0, dualTime=0, deltaUnstTimeND=0.0)
+        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0, dualTime=0, deltaUnstTimeND=0.0, viscLimiter=0)
         od.update(opts)
         od["device"] = device
         self.opts = od

@@ -95,6 +95,8 @@ typedef struct {
   int dualTime;             /* UNSTEADY_SIMULATION = DUAL_TIME_STEPPING-1ST_ORDER (1) / -2ND_ORDER (2) with explicit pseudo-time iterations: rx_time_step
                                clamps the pseudo-time step to 2/3 of the physical one (:5274-5297), rx_residual_dual_time adds the physical-time source term */
   double deltaUnstTimeND;   /* the physical time step, CConfig::GetDelta_UnstTimeND; when unstCfl != 0 rx_time_step recomputes it on pseudo-time iteration 0 */
+  int viscLimiter;          /* VISCOUS_LIMITER_FLOW: the interior viscous flux forms its mean gradients of T, u, v from gradients times the limiter of their
+                               variable (numerics_direct_reactive.cpp:1482-1505); needs limiter != 0 (the reference reads an unset limiter array otherwise) */
 } rx_opts;
 
 int rx_supported_species(int Ns);            /* 1 if kernels for this species count are compiled in */

@@ -153,6 +153,11 @@ SPECS = {
                           dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
                                SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="VENKATAKRISHNAN", CFL_NUMBER="0.2"),
                           2, 1, 23, False),
+    # same with VISCOUS_LIMITER_FLOW= YES: the interior viscous flux forms its mean gradients of T, u, v from limited gradients (numerics_direct_reactive.cpp:1482-1505)
+    "channel_lam_visclim": (dict(nx=41, ny=21, stretch=1.5),
+                            dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",
+                                 SPATIAL_ORDER_FLOW="2ND_ORDER_LIMITER", SLOPE_LIMITER_FLOW="VENKATAKRISHNAN", VISCOUS_LIMITER_FLOW="YES", CFL_NUMBER="0.2"),
+                            2, 1, 107, True),
     # same, BARTH_JESPERSEN branch of SetPrimitive_Limiter (as coded, order dependent)
     "channel_lam_bj": (dict(nx=41, ny=21, stretch=1.5),
                        dict(CHANNEL_MARKERS, RESTART_SOL="NO", EXT_ITER="2", KIND_TURB_MODEL="NONE", IGNITION="NO",

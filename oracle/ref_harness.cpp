@@ -323,7 +323,7 @@ static void dump_config(Ctx& c, std::ostringstream& js) {
      << ", \"time_stepping\": " << (f->GetUnsteady_Simulation() == TIME_STEPPING ? 1 : 0) << ", \"unst_cfl\": " << f->GetUnst_CFL()
      << ", \"unst_dt\": " << f->GetDelta_UnstTime()
      << ", \"dual_time\": " << (f->GetUnsteady_Simulation() == DT_STEPPING_1ST ? 1 : f->GetUnsteady_Simulation() == DT_STEPPING_2ND ? 2 : 0)
-     << ", \"unst_dt_nd\": " << f->GetDelta_UnstTimeND() << ", \"dual_inner\": " << (getenv("RX_DUAL_INNER") ? atol(getenv("RX_DUAL_INNER")) : 2)
+     << ", \"visc_limiter\": " << (f->GetViscous_Limiter_Flow() ? 1 : 0) << ", \"unst_dt_nd\": " << f->GetDelta_UnstTimeND() << ", \"dual_inner\": " << (getenv("RX_DUAL_INNER") ? atol(getenv("RX_DUAL_INNER")) : 2)
      << ", \"second_order\": " << (c.flow->second_order ? 1 : 0) << ", \"limiter\": " << (c.flow->limiter ? 1 : 0)
      << ", \"limiter_kind\": " << f->GetKind_SlopeLimit_Flow() << ", \"limiter_coeff\": " << f->GetLimiterCoeff()
      << ", \"ref_elem_length\": " << f->GetRefElemLength() << ", \"limiter_iter\": " << f->GetLimiterIter()

@@ -68,6 +68,7 @@ typedef struct {
   double unstCfl, deltaUnstTime;       /* UNST_CFL_NUMBER, UNST_TIMESTEP (read by the Euler solver's variant only) */
   int dualTime;                        /* UNSTEADY_SIMULATION = DUAL_TIME_STEPPING-1ST_ORDER (1) / -2ND_ORDER (2), explicit pseudo-time iterations */
   double deltaUnstTimeND;              /* the physical time step (CConfig::GetDelta_UnstTimeND); recomputed from unstCfl when that is not zero */
+  int viscLimiter;                     /* VISCOUS_LIMITER_FLOW: the mean gradients of T, u, v of the interior viscous flux are formed from limited gradients */
 } rxo_opts;
 
 rxo_ctx* rxo_create(const rxo_mesh*, const rxo_chem*, const rxo_opts*);

@@ -90,7 +90,7 @@ class _Opts(C.Structure):
                 ("pasrLb", C.c_double), ("tkeInf", C.c_double),
                 ("secondOrder", C.c_int), ("limiter", C.c_int), ("limCoeff", C.c_double), ("refElemLength", C.c_double),
                 ("timeStepping", C.c_int), ("unstCfl", C.c_double), ("deltaUnstTime", C.c_double),
-                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double)]
+                ("dualTime", C.c_int), ("deltaUnstTimeND", C.c_double), ("viscLimiter", C.c_int)]
 
 
 def chem_arrays(case):
@@ -119,7 +119,7 @@ def opts_dict(case):
                 limiter=(2 if cf.get("limiter_kind", 0) == 1 else 1) if cf.get("limiter", 0) else 0,   # 1 VENKATAKRISHNAN, 2 BARTH_JESPERSEN
                 limCoeff=cf.get("limiter_coeff", 0.3), refElemLength=cf.get("ref_elem_length", 0.1),
                 timeStepping=cf.get("time_stepping", 0), unstCfl=cf.get("unst_cfl", 0.0), deltaUnstTime=cf.get("unst_dt", 0.0),
-                dualTime=cf.get("dual_time", 0), deltaUnstTimeND=cf.get("unst_dt_nd", 0.0))
+                dualTime=cf.get("dual_time", 0), deltaUnstTimeND=cf.get("unst_dt_nd", 0.0), viscLimiter=cf.get("visc_limiter", 0))
 
 
 def marker_list(case):

@@ -23,7 +23,8 @@ RUNS = {"channel_lam_rk": (2, 11), "channel_lam_gg": (1, 13), "channel_rans": (2
         "channel_lam_supersonic": (2, 73),   # MARKER_SUPERSONIC_INLET / _OUTLET
         "channel_lam_unsteady": (3, 79), "channel_euler_unsteady": (3, 83), "channel_euler_unsteady_fixed": (2, 89),   # TIME_STEPPING
         "channel_lam_dualtime2": (3, 97), "channel_euler_dualtime1": (4, 101),
-        "channel_rans_dualtime2": (4, 103)}   # DUAL_TIME_STEPPING-2ND_ORDER / -1ST_ORDER, explicit pseudo-time iterations
+        "channel_rans_dualtime2": (4, 103),
+        "channel_lam_visclim": (2, 107)}   # VISCOUS_LIMITER_FLOW= YES   # DUAL_TIME_STEPPING-2ND_ORDER / -1ST_ORDER, explicit pseudo-time iterations
 CASE_ENV = {"channel_lam_inlet_total": {"RX_PERTURB_TAMP": "0", "RX_PERTURB_NOISE": "0"},   # oracle/make_golden.py ENVS
             # the time levels shifted on the device (CReactiveNSSolverGPU::ShiftTimeLevels next to CIntegration::SetDualTime_Solver); the Euler
             # case takes the default route, where the next physical step's first SetTime_Step uploads the levels the reference shifted in node[]

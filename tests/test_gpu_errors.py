@@ -147,3 +147,17 @@ def test_dual_time_entry_points_need_a_dual_time_context():
     a, b = rans.TurbGetTimeLevels()   # before any set / shift: the current (k, omega)
     assert np.array_equal(a, tb[:, 1:3]) and np.array_equal(b, tb[:, 1:3])
     rans.close()
+
+
+def test_viscous_limiter_needs_the_slope_limiter():
+    """VISCOUS_LIMITER_FLOW multiplies gradients by the limiters of SPATIAL_ORDER_FLOW= 2ND_ORDER_LIMITER; without them the reference reads an
+    unset array (solver_direct_reactive.cpp:5326) — rx_create refuses instead."""
+    pk = load_package()
+    chem = pk.load_mechanism()
+    mesh = pk.channel_mesh(12, 8)
+    with pytest.raises(pk.RxError, match="viscLimiter"):
+        pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), viscLimiter=1))
+    with pytest.raises(pk.RxError, match="viscLimiter"):
+        pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), viscLimiter=1, secondOrder=1, limiter=0))
+    s = pk.CReactiveNSSolverGPU(mesh, chem, dict(pk.default_opts(rans=False, cfl=0.1), viscLimiter=1, secondOrder=1, limiter=1))
+    s.close()

@@ -25,7 +25,9 @@ CASES = ["jet_rans_shipped", "jet_rans_perturbed", "channel_lam_rk", "channel_la
          # UNSTEADY_SIMULATION= TIME_STEPPING (global minimum time step; the Euler solver's CFL swap and fixed UNST_TIMESTEP)
          "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed",
          # explicit dual time stepping (SetResidual_DualTime :2172-2215, the pseudo-time step clamp :5274-5297, the level shift)
-         "channel_lam_dualtime2", "channel_euler_dualtime1", "channel_rans_dualtime2"]
+         "channel_lam_dualtime2", "channel_euler_dualtime1", "channel_rans_dualtime2",
+         # VISCOUS_LIMITER_FLOW= YES (limited mean gradients in the interior viscous flux, numerics_direct_reactive.cpp:1482-1505)
+         "channel_lam_visclim"]
 TOL = 0.0
 
 
