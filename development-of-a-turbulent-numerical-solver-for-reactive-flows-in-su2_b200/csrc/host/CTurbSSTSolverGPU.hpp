@@ -16,6 +16,10 @@ class CTurbSSTSolverGPU : public CTurbSSTSolver {
  public:
   CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {
     dualTime = config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND;
+    // the device step is the first-order scheme of every shipped cfg (SPATIAL_ORDER_TURB defaults to 1ST_ORDER, config_structure.cpp:1189); the
+    // reference's second-order branch (solver_direct_turbulent.cpp:463-520) indexes the four flow limiters with thirteen rows
+    if (config->GetSpatialOrder_Turb() != FIRST_ORDER)
+      throw std::runtime_error("CTurbSSTSolverGPU: SPATIAL_ORDER_TURB other than 1ST_ORDER is not on the CUDA path (SU2_RX_TURB=host keeps the reference's own turbulence solver)");
   }
 
   void Preprocessing(CGeometry*, CSolver**, CConfig*, unsigned short, unsigned short, unsigned short, bool) override {}
