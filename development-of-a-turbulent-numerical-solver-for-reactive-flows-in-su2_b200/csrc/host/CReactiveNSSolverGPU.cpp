@@ -35,6 +35,11 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
     throw std::runtime_error("CReactiveNSSolverGPU: only the VENKATAKRISHNAN and BARTH_JESPERSEN limiters are on the CUDA path");
   if (grid_movement) throw std::runtime_error("CReactiveNSSolverGPU: moving grids are not on the CUDA path");
   if (nDim != 2) throw std::runtime_error("CReactiveNSSolverGPU: two space dimensions only");
+  // one grid level (MGLEVEL= 0 in every shipped cfg): the coarse levels' restriction / prolongation (integration_time.cpp:183-330) work on node[] only
+  if (config->GetnMGLevels() > 0 || iMesh != MESH_0) throw std::runtime_error("CReactiveNSSolverGPU: multigrid (MGLEVEL > 0) is not on the CUDA path");
+  // the reference computes gradients for GREEN_GAUSS and WEIGHTED_LEAST_SQUARES only (Preprocessing :4713-4716; any other kind leaves them unset)
+  if (config->GetKind_Gradient_Method() != GREEN_GAUSS && config->GetKind_Gradient_Method() != WEIGHTED_LEAST_SQUARES)
+    throw std::runtime_error("CReactiveNSSolverGPU: NUM_METHOD_GRAD must be GREEN_GAUSS or WEIGHTED_LEAST_SQUARES");
   // every *_Ref is 1 on the CUDA path, as in all shipped cfgs (REF_DIMENSIONALIZATION= DIMENSIONAL, SI units: solver_direct_reactive.cpp:846-887)
   if (config->GetRef_NonDim() != DIMENSIONAL) throw std::runtime_error("CReactiveNSSolverGPU: REF_DIMENSIONALIZATION other than DIMENSIONAL is not on the CUDA path");
   // VISCOUS_LIMITER_FLOW: CAvgGradReactive_Flow multiplies the gradients of T, u, v by the limiters (numerics_direct_reactive.cpp:1482-1505), which
