@@ -17,7 +17,8 @@ class CTurbSSTSolverGPU : public CTurbSSTSolver {
   CTurbSSTSolverGPU(CGeometry* geometry, CConfig* config, unsigned short iMesh) : CTurbSSTSolver(geometry, config, iMesh) {
     dualTime = config->GetUnsteady_Simulation() == DT_STEPPING_1ST || config->GetUnsteady_Simulation() == DT_STEPPING_2ND;
     // the device step is the first-order scheme of every shipped cfg (SPATIAL_ORDER_TURB defaults to 1ST_ORDER, config_structure.cpp:1189); the
-    // reference's second-order branch (solver_direct_turbulent.cpp:463-520) indexes the four flow limiters with thirteen rows
+    // reference's second-order branch (solver_direct_turbulent.cpp:463-520) indexes the four flow limiters with thirteen rows, and the compiled
+    // reference ends in a segmentation fault on the channel case with SPATIAL_ORDER_TURB= 2ND_ORDER
     // rx_turb_iterate solves with FGMRES preconditioned by LU-SGS (CSysSolve::Solve, linear_solvers_structure.cpp:626-665), the pair of the shipped cfgs
     if (config->GetKind_Linear_Solver() != FGMRES || config->GetKind_Linear_Solver_Prec() != LU_SGS)
       throw std::runtime_error("CTurbSSTSolverGPU: LINEAR_SOLVER / LINEAR_SOLVER_PREC other than FGMRES / LU_SGS are not on the CUDA path (SU2_RX_TURB=host keeps the reference's own turbulence solver)");
