@@ -635,7 +635,7 @@ def main():
     t_mesh = time.perf_counter()
     if world > 1 and a.partition == "graph":
         gm = pk.channel_mesh(nxg, a.ny)
-        part = pk.partition_graph(gm, world, rcm=True)[rank]
+        part = pk.partition_graph_rank(gm, world, rank, rcm=True)   # this rank's part only (rx_partition_mesh)
         mesh, plan = part["mesh"], dict(send=part["send"], recv=part["recv"], bbox=(0.0, 0.25, 0.0, 0.025), glob=part["glob"])
         del gm, part
     elif world > 1:

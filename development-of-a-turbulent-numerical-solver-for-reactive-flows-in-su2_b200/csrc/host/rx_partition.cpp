@@ -233,3 +233,156 @@ extern "C" int rx_rcm_order(int64_t nPoint, int64_t nPointDomain, const int64_t*
   for (int64_t q = n; q < nPoint; ++q) newToOld[q] = q;
   return RX_OK;
 }
+
+// ---- one rank's share of a partitioned mesh ---------------------------------------------------------------------------------------------
+// rx_partition_mesh: from the whole flat mesh and an owner array, the local mesh of ONE rank in SU2's scheme (the role of the
+// partitioned CPhysicalGeometry constructor and SetSendReceive, geometry_structure.cpp:540-1480, :2262-2540): owned points first (ascending global
+// index), then one halo layer grouped by owner rank (ascending global index inside a group); every edge with at least one owned end, in the
+// whole mesh's edge order; the neighbour lists restricted to local points; boundary vertices on owned points only; optionally the owned points
+// renumbered by reverse Cuthill-McKee with the edges re-sorted by (lower, higher) local index and the neighbour lists by neighbour index.
+// The send list towards a neighbour rank q holds the owned points that q's halo contains, in q's halo order (ascending global index), so that
+// send and receive lists match without any negotiation.  Every rank builds its own part: the cost is one pass over the whole mesh per rank.
+extern "C" void rx_part_free(rx_part* p) {
+  if (!p) return;
+  free(p->glob); free(p->edgeNodes); free(p->edgeNormal); free(p->coord); free(p->volume); free(p->nbPtr); free(p->nbPoint);
+  free(p->markerPtr); free(p->markerNode); free(p->markerNormalNeighbor); free(p->markerNormal);
+  free(p->nbRank); free(p->sendPtr); free(p->sendPts); free(p->recvPtr); free(p->recvPts);
+  memset(p, 0, sizeof *p);
+}
+
+namespace {
+template <class T>
+T* dup_vec(const std::vector<T>& v) {
+  T* p = (T*)malloc(sizeof(T) * std::max<size_t>(v.size(), 1));
+  if (p && !v.empty()) memcpy(p, v.data(), sizeof(T) * v.size());
+  return p;
+}
+}  // namespace
+
+extern "C" int rx_partition_mesh(int64_t nPoint, int64_t nEdge, const int64_t* edgeNodes, const double* edgeNormal, const double* coord,
+                                 const double* volume, const int64_t* nbPtr, const int64_t* nbPoint, int nMarker, const int64_t* markerPtr,
+                                 const int64_t* markerNode, const int64_t* markerNormalNeighbor, const double* markerNormal,
+                                 const int64_t* owner, int rank, int rcm, rx_part* out) {
+  if (!out) return RX_ERR_ARG;
+  memset(out, 0, sizeof *out);
+  if (nPoint <= 0 || nEdge < 0 || !edgeNodes || !edgeNormal || !coord || !volume || !nbPtr || !nbPoint || !owner || rank < 0 || nMarker < 0 ||
+      (nMarker > 0 && (!markerPtr || !markerNode || !markerNormalNeighbor || !markerNormal))) return RX_ERR_ARG;
+  // owned points, kept edges, halo
+  std::vector<int64_t> glob;
+  for (int64_t p = 0; p < nPoint; ++p) if (owner[p] == rank) glob.push_back(p);
+  const int64_t nOwn = (int64_t)glob.size();
+  if (nOwn == 0) return RX_ERR_ARG;
+  std::vector<char> touched((size_t)nPoint, 0);
+  std::vector<int64_t> keep;
+  for (int64_t e = 0; e < nEdge; ++e) {
+    const int64_t i = edgeNodes[2 * e], j = edgeNodes[2 * e + 1];
+    if (i < 0 || i >= nPoint || j < 0 || j >= nPoint) return RX_ERR_ARG;
+    if (owner[i] == rank || owner[j] == rank) { keep.push_back(e); touched[(size_t)i] = 1; touched[(size_t)j] = 1; }
+  }
+  std::vector<int64_t> halo;
+  for (int64_t p = 0; p < nPoint; ++p) if (touched[(size_t)p] && owner[p] != rank) halo.push_back(p);
+  std::stable_sort(halo.begin(), halo.end(), [&](int64_t a, int64_t b) { return owner[a] < owner[b]; });   // ascending global index inside a group
+  glob.insert(glob.end(), halo.begin(), halo.end());
+  const int64_t nLoc = (int64_t)glob.size(), nE = (int64_t)keep.size();
+  std::vector<int64_t> g2l((size_t)nPoint, -1);
+  for (int64_t q = 0; q < nLoc; ++q) g2l[(size_t)glob[(size_t)q]] = q;
+  // local arrays in the construction numbering
+  std::vector<int64_t> en((size_t)2 * nE), lptr((size_t)nLoc + 1, 0), lnb;
+  std::vector<double> enr((size_t)2 * nE), xy((size_t)2 * nLoc), vol((size_t)nLoc);
+  for (int64_t k = 0; k < nE; ++k) {
+    const int64_t e = keep[(size_t)k];
+    en[2 * k] = g2l[(size_t)edgeNodes[2 * e]]; en[2 * k + 1] = g2l[(size_t)edgeNodes[2 * e + 1]];
+    enr[2 * k] = edgeNormal[2 * e]; enr[2 * k + 1] = edgeNormal[2 * e + 1];
+  }
+  for (int64_t q = 0; q < nLoc; ++q) {
+    const int64_t p = glob[(size_t)q];
+    xy[2 * q] = coord[2 * p]; xy[2 * q + 1] = coord[2 * p + 1]; vol[(size_t)q] = volume[p];
+    for (int64_t t = nbPtr[p]; t < nbPtr[p + 1]; ++t) { const int64_t l = g2l[(size_t)nbPoint[t]]; if (l >= 0) lnb.push_back(l); }
+    lptr[(size_t)q + 1] = (int64_t)lnb.size();
+  }
+  std::vector<int64_t> mptr((size_t)nMarker + 1, 0), mnode, mnn;
+  std::vector<double> mnr;
+  for (int m = 0; m < nMarker; ++m) {
+    for (int64_t k = markerPtr[m]; k < markerPtr[m + 1]; ++k)
+      if (owner[markerNode[k]] == rank) {
+        mnode.push_back(g2l[(size_t)markerNode[k]]); mnn.push_back(g2l[(size_t)markerNormalNeighbor[k]]);
+        mnr.push_back(markerNormal[2 * k]); mnr.push_back(markerNormal[2 * k + 1]);
+      }
+    mptr[(size_t)m + 1] = (int64_t)mnode.size();
+  }
+  if (rcm) {
+    std::vector<int64_t> n2o((size_t)nLoc), o2n((size_t)nLoc);
+    if (rx_rcm_order(nLoc, nOwn, lptr.data(), lnb.data(), n2o.data()) != RX_OK) return RX_ERR_ARG;
+    for (int64_t q = 0; q < nLoc; ++q) o2n[(size_t)n2o[(size_t)q]] = q;
+    // edges keep their orientation and are re-sorted by (lower, higher) new index
+    std::vector<int64_t> eo((size_t)nE);
+    std::iota(eo.begin(), eo.end(), (int64_t)0);
+    for (auto& v : en) v = o2n[(size_t)v];
+    std::sort(eo.begin(), eo.end(), [&](int64_t a, int64_t b) {
+      const int64_t la = std::min(en[2 * a], en[2 * a + 1]), lb = std::min(en[2 * b], en[2 * b + 1]);
+      if (la != lb) return la < lb;
+      const int64_t ha = std::max(en[2 * a], en[2 * a + 1]), hb = std::max(en[2 * b], en[2 * b + 1]);
+      if (ha != hb) return ha < hb;
+      return a < b;
+    });
+    std::vector<int64_t> en2((size_t)2 * nE); std::vector<double> enr2((size_t)2 * nE);
+    for (int64_t k = 0; k < nE; ++k) { const int64_t e = eo[(size_t)k]; en2[2 * k] = en[2 * e]; en2[2 * k + 1] = en[2 * e + 1]; enr2[2 * k] = enr[2 * e]; enr2[2 * k + 1] = enr[2 * e + 1]; }
+    en.swap(en2); enr.swap(enr2);
+    std::vector<double> xy2((size_t)2 * nLoc), vol2((size_t)nLoc);
+    std::vector<int64_t> glob2((size_t)nLoc), ptr2((size_t)nLoc + 1, 0), nb2;
+    nb2.reserve(lnb.size());
+    for (int64_t q = 0; q < nLoc; ++q) {
+      const int64_t o = n2o[(size_t)q];
+      xy2[2 * q] = xy[2 * o]; xy2[2 * q + 1] = xy[2 * o + 1]; vol2[(size_t)q] = vol[(size_t)o]; glob2[(size_t)q] = glob[(size_t)o];
+      const size_t s0 = nb2.size();
+      for (int64_t t = lptr[(size_t)o]; t < lptr[(size_t)o + 1]; ++t) nb2.push_back(o2n[(size_t)lnb[(size_t)t]]);
+      std::sort(nb2.begin() + (std::ptrdiff_t)s0, nb2.end());   // neighbour lists stay sorted by neighbour index
+      ptr2[(size_t)q + 1] = (int64_t)nb2.size();
+    }
+    xy.swap(xy2); vol.swap(vol2); glob.swap(glob2); lptr.swap(ptr2); lnb.swap(nb2);
+    for (auto& v : mnode) v = o2n[(size_t)v];
+    for (auto& v : mnn) v = o2n[(size_t)v];
+    for (int64_t q = 0; q < nLoc; ++q) g2l[(size_t)glob[(size_t)q]] = q;
+  }
+  // neighbour ranks, receive lists (the halo groups) and send lists (owned points some point of the neighbour rank is joined to by an edge)
+  std::vector<int> nbRank;
+  std::vector<int64_t> recvPtr(1, 0), recvPts, sendPtr(1, 0), sendPts;
+  for (size_t h = 0; h < halo.size();) {
+    const int64_t q = owner[halo[h]];
+    nbRank.push_back((int)q);
+    for (; h < halo.size() && owner[halo[h]] == q; ++h) recvPts.push_back(g2l[(size_t)halo[h]]);
+    recvPtr.push_back((int64_t)recvPts.size());
+  }
+  {
+    std::vector<std::vector<int64_t>> lists(nbRank.size());
+    std::vector<int> slotOf;                         // rank -> slot
+    int maxRank = rank;
+    for (int q : nbRank) maxRank = std::max(maxRank, q);
+    slotOf.assign((size_t)maxRank + 1, -1);
+    for (size_t s = 0; s < nbRank.size(); ++s) slotOf[(size_t)nbRank[s]] = (int)s;
+    // an owned point p belongs to the halo of rank q exactly if an edge joins it to a point owned by q; walking the owned points in ascending
+    // global index gives every list in the neighbour's halo order
+    for (int64_t p = 0; p < nPoint; ++p) {
+      if (owner[p] != rank) continue;
+      for (int64_t t = nbPtr[p]; t < nbPtr[p + 1]; ++t) {
+        const int64_t q = owner[nbPoint[t]];
+        if (q == rank) continue;
+        if (q < 0 || q > maxRank || slotOf[(size_t)q] < 0) return RX_ERR_ARG;   // the neighbour lists and the edges describe different graphs
+        std::vector<int64_t>& l = lists[(size_t)slotOf[(size_t)q]];
+        if (l.empty() || l.back() != p) l.push_back(p);   // the neighbours of p are walked together: p can only be the list's last entry
+      }
+    }
+    for (size_t s = 0; s < nbRank.size(); ++s) {
+      for (int64_t p : lists[s]) sendPts.push_back(g2l[(size_t)p]);
+      sendPtr.push_back((int64_t)sendPts.size());
+    }
+  }
+  out->nPoint = nLoc; out->nPointDomain = nOwn; out->nEdge = nE; out->nMarker = nMarker; out->nNb = (int)nbRank.size();
+  out->glob = dup_vec(glob); out->edgeNodes = dup_vec(en); out->edgeNormal = dup_vec(enr); out->coord = dup_vec(xy); out->volume = dup_vec(vol);
+  out->nbPtr = dup_vec(lptr); out->nbPoint = dup_vec(lnb);
+  out->markerPtr = dup_vec(mptr); out->markerNode = dup_vec(mnode); out->markerNormalNeighbor = dup_vec(mnn); out->markerNormal = dup_vec(mnr);
+  out->nbRank = dup_vec(nbRank); out->sendPtr = dup_vec(sendPtr); out->sendPts = dup_vec(sendPts); out->recvPtr = dup_vec(recvPtr); out->recvPts = dup_vec(recvPts);
+  if (!out->glob || !out->edgeNodes || !out->edgeNormal || !out->coord || !out->volume || !out->nbPtr || !out->nbPoint || !out->markerPtr || !out->markerNode ||
+      !out->markerNormalNeighbor || !out->markerNormal || !out->nbRank || !out->sendPtr || !out->sendPts || !out->recvPtr || !out->recvPts) { rx_part_free(out); return RX_ERR_CUDA; }
+  return RX_OK;
+}

@@ -289,6 +289,57 @@ def partition_mesh(mesh, owner, rcm=False):
     return parts
 
 
+def partition_rank(mesh, owner, rank, rcm=False):
+    """One rank's entry of partition_mesh(mesh, owner, rcm), built by the library's host code (rx_partition_mesh, csrc/host/rx_partition.cpp):
+    every rank of a job builds its own part in one pass over the whole mesh instead of all of them.  Same arrays, same send / receive lists."""
+    import ctypes as C
+    from .rx_solver import load_library, RxError
+
+    class _Part(C.Structure):
+        _fields_ = [("nPoint", C.c_int64), ("nPointDomain", C.c_int64), ("nEdge", C.c_int64), ("glob", C.POINTER(C.c_int64)),
+                    ("edgeNodes", C.POINTER(C.c_int64)), ("edgeNormal", C.POINTER(C.c_double)), ("coord", C.POINTER(C.c_double)),
+                    ("volume", C.POINTER(C.c_double)), ("nbPtr", C.POINTER(C.c_int64)), ("nbPoint", C.POINTER(C.c_int64)), ("nMarker", C.c_int),
+                    ("markerPtr", C.POINTER(C.c_int64)), ("markerNode", C.POINTER(C.c_int64)), ("markerNormalNeighbor", C.POINTER(C.c_int64)),
+                    ("markerNormal", C.POINTER(C.c_double)), ("nNb", C.c_int), ("nbRank", C.POINTER(C.c_int)),
+                    ("sendPtr", C.POINTER(C.c_int64)), ("sendPts", C.POINTER(C.c_int64)), ("recvPtr", C.POINTER(C.c_int64)), ("recvPts", C.POINTER(C.c_int64))]
+    L = load_library()
+    k64 = lambda a: np.ascontiguousarray(a, dtype=np.int64); kf = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    I = lambda a: a.ctypes.data_as(C.POINTER(C.c_int64)); D = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    en, nr, xy, vol = k64(mesh["edgeNodes"]), kf(mesh["edgeNormal"]), kf(mesh["coord"]), kf(mesh["volume"])
+    ptr, nb, ow = k64(mesh["nbPtr"]), k64(mesh["nbPoint"]), k64(owner)
+    mk = mesh["markers"]
+    mptr = np.zeros(len(mk) + 1, dtype=np.int64)
+    if mk:
+        np.cumsum([len(m["node"]) for m in mk], out=mptr[1:])
+    cat = lambda key, dt, shape: np.ascontiguousarray(np.concatenate([np.asarray(m[key], dtype=dt).reshape(shape) for m in mk]) if mk else np.zeros(shape, dt).reshape(shape)[:0])
+    mnode, mnn, mnr = cat("node", np.int64, (-1,)), cat("normalNeighbor", np.int64, (-1,)), cat("normal", np.float64, (-1, 2))
+    out = _Part()
+    rc = L.rx_partition_mesh(C.c_int64(int(mesh["nPoint"])), C.c_int64(en.shape[0]), I(en), D(nr), D(xy), D(vol), I(ptr), I(nb), C.c_int(len(mk)), I(mptr),
+                             I(mnode), I(mnn), D(mnr), I(ow), C.c_int(int(rank)), C.c_int(1 if rcm else 0), C.byref(out))
+    if rc != 0:
+        raise RxError("rx_partition_mesh failed (%d): rank %d owns no point, or the mesh arrays are inconsistent" % (rc, rank))
+    try:
+        arr = lambda p, n, shape=None: (np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.zeros(0, dtype=np.ctypeslib.as_array(p, shape=(1,)).dtype)).reshape(shape or (n,))
+        nP, nE, nM, nN = out.nPoint, out.nEdge, out.nMarker, out.nNb
+        lp = arr(out.markerPtr, nM + 1)
+        nV = int(lp[-1])
+        lnode, lnn, lnr = arr(out.markerNode, nV), arr(out.markerNormalNeighbor, nV), arr(out.markerNormal, 2 * nV, (nV, 2))
+        markers = []
+        for k, m in enumerate(mk):
+            d = dict(m); a, b = int(lp[k]), int(lp[k + 1])
+            d.update(node=lnode[a:b], normalNeighbor=lnn[a:b], normal=lnr[a:b]); markers.append(d)
+        loc = dict(nPoint=nP, nPointDomain=out.nPointDomain, nEdge=nE, edgeNodes=arr(out.edgeNodes, 2 * nE, (nE, 2)), edgeNormal=arr(out.edgeNormal, 2 * nE, (nE, 2)),
+                   coord=arr(out.coord, 2 * nP, (nP, 2)), volume=arr(out.volume, nP), nbPtr=arr(out.nbPtr, nP + 1), nbPoint=arr(out.nbPoint, int(out.nbPtr[nP])),
+                   markers=markers)
+        ranks = arr(out.nbRank, nN); sp, rp = arr(out.sendPtr, nN + 1), arr(out.recvPtr, nN + 1)
+        spts, rpts = arr(out.sendPts, int(sp[-1])), arr(out.recvPts, int(rp[-1]))
+        send = {int(q): spts[sp[k]:sp[k + 1]] for k, q in enumerate(ranks)}
+        recv = {int(q): rpts[rp[k]:rp[k + 1]] for k, q in enumerate(ranks)}
+        return dict(mesh=loc, glob=arr(out.glob, nP), recv=recv, send=send)
+    finally:
+        L.rx_part_free(C.byref(out))
+
+
 def partition_strips(mesh, nParts):
     """Strip partition in x (deterministic, no graph partitioner): partition_mesh over strip_owner."""
     return partition_mesh(mesh, strip_owner(mesh, nParts))
@@ -298,6 +349,13 @@ def partition_graph(mesh, nParts, rcm=True, refine_passes=8):
     """k-way graph partition of any flat mesh (unstructured included) + RCM numbering inside every part."""
     owner, _ = graph_owner(mesh, nParts, refine_passes)
     return partition_mesh(mesh, owner, rcm=rcm)
+
+
+def partition_graph_rank(mesh, nParts, rank, rcm=True, refine_passes=8):
+    """partition_graph(mesh, nParts, rcm, refine_passes)[rank] without building the other ranks' parts (rx_partition_mesh): what each rank of a
+    multi-GPU job calls — the k-way partition is deterministic, so every rank computes the same owner array."""
+    owner, _ = graph_owner(mesh, nParts, refine_passes)
+    return partition_rank(mesh, owner, rank, rcm=rcm)
 
 
 def strip_short_side_slow(mesh, plan, min_ratio=3.0):

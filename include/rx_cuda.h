@@ -267,6 +267,27 @@ int rx_qr_eval(int64_t n, const double* A, const double* b, double* xSerial, dou
  * newToOld[nPoint].  Role of CPhysicalGeometry::SetRCM_Ordering (geometry_structure.cpp:9200, called driver_structure.cpp:560). */
 int rx_partition_kway(int64_t nPoint, const int64_t* nbPtr, const int64_t* nbPoint, const double* coord, int nParts,
                       int refinePasses, int64_t* owner, int64_t* edgeCut);
+/* One rank's share of a partitioned mesh in SU2's scheme (owned points, one halo layer grouped by owner rank, every edge with an owned end,
+ * boundary vertices on owned points, matching send / receive lists per neighbour rank; rcm != 0: owned points renumbered by rx_rcm_order, edges
+ * re-sorted) — the role of the partitioned CPhysicalGeometry constructor and SetSendReceive (geometry_structure.cpp:540-1480, :2262-2540).
+ * Markers of the whole mesh are passed concatenated: vertices of marker m = [markerPtr[m], markerPtr[m+1]).  All local indices refer to the
+ * part's numbering; glob[] maps them back.  Arrays are malloc'ed; release with rx_part_free. */
+typedef struct {
+  int64_t nPoint, nPointDomain, nEdge;
+  int64_t* glob;          /* [nPoint] local -> global point index */
+  int64_t* edgeNodes; double* edgeNormal; double* coord; double* volume; int64_t* nbPtr; int64_t* nbPoint;   /* as rx_mesh */
+  int nMarker;
+  int64_t* markerPtr;     /* [nMarker+1] */
+  int64_t* markerNode; int64_t* markerNormalNeighbor; double* markerNormal;
+  int nNb;                /* neighbour ranks, ascending */
+  int* nbRank;            /* [nNb] */
+  int64_t* sendPtr; int64_t* sendPts;   /* [nNb+1], owned local points to send to neighbour k, in that neighbour's halo order */
+  int64_t* recvPtr; int64_t* recvPts;   /* [nNb+1], local halo points received from neighbour k */
+} rx_part;
+int rx_partition_mesh(int64_t nPoint, int64_t nEdge, const int64_t* edgeNodes, const double* edgeNormal, const double* coord, const double* volume,
+                      const int64_t* nbPtr, const int64_t* nbPoint, int nMarker, const int64_t* markerPtr, const int64_t* markerNode,
+                      const int64_t* markerNormalNeighbor, const double* markerNormal, const int64_t* owner, int rank, int rcm, rx_part* out);
+void rx_part_free(rx_part*);
 int rx_partition_backend(void);   /* 1: rx_partition_kway calls METIS_PartGraphKway of librx_metis.so (METIS 5 as vendored in the reference tree, built by
                                     csrc/host/build_metis.sh; found next to the library or through RX_METIS_LIB); 0: the library's own partitioner
                                     (also forced by RX_PARTITIONER=own) */

@@ -34,8 +34,22 @@ static int builders() {
     const int rc2 = rc ? rc : rx_rcm_order(nP, nP, m.nbPtr, m.nbPoint, n2o.data());
     int rc3 = 0;
     for (int k : {1, 2, 3, 8}) if (!rc) rc3 |= rx_partition_kway(nP, m.nbPtr, m.nbPoint, xy.data(), k, 8, part.data(), &cut);
-    printf("builders nP %lld nE %lld rc %d %d %d\n", (long long)nP, (long long)m.nEdge, rc, rc2, rc3);
-    bad |= rc | rc2 | rc3;
+    // this rank's share of the mesh for every rank of the last (8-way) partition, with and without the RCM renumbering; no markers
+    int rc4 = 0;
+    if (!rc && !rc3)
+      for (int r = 0; r < 8; ++r)
+        for (int rcm = 0; rcm < 2; ++rcm) {
+          bool owns = false;
+          for (int64_t p = 0; p < nP; ++p) owns = owns || part[p] == r;
+          rx_part q;
+          const int e = rx_partition_mesh(nP, m.nEdge, m.edgeNodes, m.edgeNormal, xy.data(), m.volume, m.nbPtr, m.nbPoint, 0, nullptr, nullptr, nullptr, nullptr,
+                                          part.data(), r, rcm, &q);
+          if (owns ? e != 0 : e == 0) rc4 = 1;
+          if (!e && (q.nPointDomain <= 0 || q.nPoint < q.nPointDomain || q.sendPtr[q.nNb] <= 0 || q.recvPtr[q.nNb] != q.nPoint - q.nPointDomain)) rc4 = 1;
+          rx_part_free(&q);
+        }
+    printf("builders nP %lld nE %lld rc %d %d %d %d\n", (long long)nP, (long long)m.nEdge, rc, rc2, rc3, rc4);
+    bad |= rc | rc2 | rc3 | rc4;
     rx_dual_mesh_free(&m);
   }
   rx_dual_mesh m;

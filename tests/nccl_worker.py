@@ -27,7 +27,7 @@ def turb_mode(rank, world, local, dev, chem):
     opts = pk.default_opts(rans=True, cfl=0.1)
     nx, ny = 61, 23
     g = pk.channel_mesh(nx, ny)
-    plan = pk.partition_graph(g, world, rcm=True)[rank]
+    plan = pk.partition_graph_rank(g, world, rank, rcm=True)
     m = plan["mesh"]
     glob = np.asarray(plan["glob"])
     Ug, Tg, tg = pk.synthetic_state(g, chem, seed=3, rans=True)
@@ -131,7 +131,7 @@ def main():
         nx, ny = 61, 23
         g = pk.channel_mesh(nx, ny)
         if mode == "graph":
-            plan = pk.partition_graph(g, world, rcm=True)[rank]   # deterministic: every rank computes the same partition
+            plan = pk.partition_graph_rank(g, world, rank, rcm=True)   # deterministic: every rank computes the same owner array and builds its own part
             m = plan["mesh"]
             glob = np.asarray(plan["glob"])
         else:

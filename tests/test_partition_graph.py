@@ -148,7 +148,7 @@ def _worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         g = mesh_dict(Case(os.path.join(GOLDEN, "jet_rans_perturbed.npz")))
-        part = pk.partition_graph(g, world)[rank]             # deterministic: every rank computes the same partition
+        part = pk.partition_graph_rank(g, world, rank)        # deterministic: every rank computes the same owner array and builds its own part
         m, glob = part["mesh"], part["glob"]
         nP, nOwn = m["nPoint"], m["nPointDomain"]
         fields = {}
@@ -208,3 +208,39 @@ def test_metis_backend_when_built():
     finally:
         if old is not None:
             os.environ["RX_PARTITIONER"] = old
+
+
+def _same_part(a, b):
+    ma, mb = a["mesh"], b["mesh"]
+    for k in ("nPoint", "nPointDomain", "nEdge"):
+        assert int(ma[k]) == int(mb[k]), k
+    np.testing.assert_array_equal(a["glob"], b["glob"])
+    for k in ("edgeNodes", "edgeNormal", "coord", "volume", "nbPtr", "nbPoint"):
+        np.testing.assert_array_equal(ma[k], mb[k], err_msg=k)
+    assert len(ma["markers"]) == len(mb["markers"])
+    for x, y in zip(ma["markers"], mb["markers"]):
+        assert x["kind"] == y["kind"]
+        for k in ("node", "normalNeighbor", "normal"):
+            np.testing.assert_array_equal(np.asarray(x[k]).reshape(np.asarray(y[k]).shape), y[k], err_msg=k)
+    for side in ("send", "recv"):
+        assert sorted(a[side]) == sorted(b[side]), side
+        for q in a[side]:
+            np.testing.assert_array_equal(a[side][q], b[side][q], err_msg="%s[%d]" % (side, q))
+
+
+@pytest.mark.parametrize("rcm", [False, True])
+def test_native_partition_builder_equals_the_numpy_specification(pk, jet, rcm):
+    """rx_partition_mesh (one rank's part, built natively in one pass over the whole mesh) against partition_mesh (all parts, numpy) on the shipped
+    unstructured jet mesh under a 5-way graph partition and on a triangulated channel under strips: every array, the local-to-global map and the
+    send / receive lists of every rank identical."""
+    owner, _ = pk.graph_owner(jet, 5)
+    want = pk.partition_mesh(jet, owner, rcm=rcm)
+    for r in range(5):
+        _same_part(pk.partition_rank(jet, owner, r, rcm=rcm), want[r])
+    ch = pk.channel_mesh(23, 11)
+    ow = pk.strip_owner(ch, 3)
+    want = pk.partition_mesh(ch, ow, rcm=rcm)
+    for r in range(3):
+        _same_part(pk.partition_rank(ch, ow, r, rcm=rcm), want[r])
+    with pytest.raises(pk.RxError):
+        pk.partition_rank(ch, ow, 7)          # a rank that owns nothing
