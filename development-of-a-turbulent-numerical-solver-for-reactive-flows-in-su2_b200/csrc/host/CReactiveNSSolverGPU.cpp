@@ -179,15 +179,16 @@ CReactiveNSSolverGPU::CReactiveNSSolverGPU(CGeometry* geometry, CConfig* config,
   bufU.resize((size_t)nPoint * nVar); bufR.resize((size_t)nPoint * nVar);
   bufV.resize((size_t)nPoint * nPrimVar); bufAux.resize((size_t)nPoint * 6);
   bufGrad.resize((size_t)nPoint * nPrimVarGrad * nDim); bufT.resize((size_t)nPoint * 6);
-#ifdef HAVE_MPI
+#ifdef RX_COMM_BLOCK
   InitComm(geometry, config);
 #endif
 }
 
-#ifdef HAVE_MPI
+#ifdef RX_COMM_BLOCK
 // One rank per GPU.  The neighbour lists are the vertex lists of the SEND_RECEIVE marker pairs, in the order Set_MPI_Solution walks them
 // (solver_direct_reactive.cpp:1541-1560): marker S (SendRecv > 0) goes to rank SendRecv - 1, marker S + 1 receives from |SendRecv| - 1.
-// NOTE: compiled in MPI builds only; this container has no MPI, the same C entry points are exercised by tests/test_gpu_nccl.py.
+// Compiled in MPI builds; this container has no MPI, so oracle/build_ref.sh compiles the block once more against the five single-rank
+// stand-ins of RX_MPI_STUB (CReactiveNSSolverGPU.hpp) as a syntax and type check, and tests/test_gpu_nccl.py drives the same C entry points.
 void CReactiveNSSolverGPU::InitComm(CGeometry* geometry, CConfig* config) {
   int rank = 0, size = 1;
   MPI_Comm_rank(MPI_COMM_WORLD, &rank); MPI_Comm_size(MPI_COMM_WORLD, &size);

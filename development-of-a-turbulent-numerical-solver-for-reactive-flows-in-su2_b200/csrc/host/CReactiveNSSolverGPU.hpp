@@ -16,6 +16,21 @@
 #include <string>
 #include <vector>
 
+// The communicator set-up (InitComm) needs five MPI symbols.  In an MPI build they are the real ones; RX_MPI_STUB supplies single-rank stand-ins
+// so that the block can be compiled (syntax and types) where no MPI exists (oracle/build_ref.sh does, into a discarded object).
+#if defined(HAVE_MPI)
+#define RX_COMM_BLOCK 1
+#elif defined(RX_MPI_STUB)
+#define RX_COMM_BLOCK 1
+typedef int MPI_Comm;
+typedef int MPI_Datatype;
+static const MPI_Comm MPI_COMM_WORLD = 0;
+static const MPI_Datatype MPI_CHAR = 1;
+static inline int MPI_Comm_rank(MPI_Comm, int* rank) { *rank = 0; return 0; }
+static inline int MPI_Comm_size(MPI_Comm, int* size) { *size = 1; return 0; }
+static inline int MPI_Bcast(void*, int, MPI_Datatype, int, MPI_Comm) { return 0; }
+#endif
+
 class CReactiveNSSolverGPU : public CReactiveNSSolver {
  public:
   // mirror levels (env SU2_RX_MIRROR, default 1):
@@ -92,7 +107,7 @@ class CReactiveNSSolverGPU : public CReactiveNSSolver {
   void MirrorBoundaryState(CGeometry* geometry, unsigned short val_marker);
   void Update(CGeometry* geometry, double alpha, bool lastStage);
 
-#ifdef HAVE_MPI
+#ifdef RX_COMM_BLOCK
   void InitComm(CGeometry* geometry, CConfig* config);   // neighbour lists from the SEND_RECEIVE marker pairs, NCCL id by MPI_Bcast
 #endif
   rx_ctx* ctx = nullptr;
