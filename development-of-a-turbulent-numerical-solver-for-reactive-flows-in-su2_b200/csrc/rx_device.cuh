@@ -3,7 +3,7 @@
 // One thread owns one point or one edge; all per-species work (NS is a template constant) is unrolled into registers.
 // Compiled with -fmad=false: where the reference's result is tolerance-limited (secant temperature solve, BiCGSTAB
 // Stefan–Maxwell solve) the operation order below is the reference's, so iteration counts agree with the CPU code.
-// The same header compiles for the host (RX_HD empty) ONLY in tests/host_emu, to check the arithmetic without a GPU.
+// The same header compiles for the host (RX_HD plain inline) ONLY in tests/host_emu.cpp (tests/test_host_emulation.py): the arithmetic checked without a GPU.
 //
 // Reference citations are relative to /root/reference.
 #pragma once
