@@ -24,8 +24,11 @@ def emu(tmp_path_factory):
     if shutil.which("g++") is None:
         pytest.skip("no g++")
     so = str(tmp_path_factory.mktemp("host_emu") / "libhost_emu.so")
+    # RX_EMU_UBSAN=1 (set by test_kernel_arithmetic_is_free_of_undefined_behaviour, which runs this file once more in a child process with libubsan
+    # preloaded): the same source under UndefinedBehaviorSanitizer, any report aborts
+    san = ["-O1", "-g", "-fsanitize=undefined", "-fno-sanitize-recover=undefined"] if os.environ.get("RX_EMU_UBSAN") == "1" else ["-O2"]
     # -ffp-contract=off: no fused multiply-add, as the CUDA build (-fmad=false) and the reference's own x86-64 build
-    cc = subprocess.run(["g++", "-std=c++17", "-O2", "-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"),
+    cc = subprocess.run(["g++", "-std=c++17"] + san + ["-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"),
                          "-I", os.path.join(PKG, "csrc"), os.path.join(ROOT, "tests", "host_emu.cpp"), "-o", so],
                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert cc.returncode == 0, cc.stdout[-3000:]
@@ -159,3 +162,20 @@ def test_mass_production_source_equals_the_restatement_and_the_reference_library
     scale = np.abs(lib).max(axis=0)
     assert (np.abs(res - lib).max(axis=0) / np.where(scale > 0, scale, 1.0)).max() < 1e-12
     assert np.array_equal(res == 0.0, lib == 0.0)
+
+
+def test_kernel_arithmetic_is_free_of_undefined_behaviour():
+    """The tests above once more in a child process, with tests/host_emu.cpp built under UndefinedBehaviorSanitizer (array bounds of the unrolled
+    per-species arrays, shifts, integer overflow, misaligned or null accesses): no report on any fixture."""
+    if os.environ.get("RX_EMU_UBSAN") == "1":
+        pytest.skip("this is the child run")
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    ub = subprocess.run(["g++", "-print-file-name=libubsan.so"], stdout=subprocess.PIPE, text=True).stdout.strip()
+    if not os.path.isabs(ub) or not os.path.exists(ub):
+        pytest.skip("this g++ has no UBSan runtime")
+    import sys
+    env = dict(os.environ, RX_EMU_UBSAN="1", LD_PRELOAD=ub, UBSAN_OPTIONS="print_stacktrace=1")
+    run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider"], cwd=os.path.dirname(os.path.abspath(__file__)),
+                         env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1200)
+    assert run.returncode == 0 and "runtime error" not in run.stdout and " passed" in run.stdout, run.stdout[-4000:]
