@@ -6,6 +6,7 @@
 //   emu_transport   transport<NS> (Wilke rules)
 //   emu_ausm        ausm<NS>, one interior edge at a time
 //   emu_source      mass_production<NS> as k_source_points scales it
+//   emu_qr          colpiv_qr_solve<9, 2, 1> as k_qr_eval_serial calls it (the SST closure's pivoted Householder QR, serial form)
 //   emu_viscous     viscous_flux<NS, EDGE = true> (Stefan-Maxwell / BiCGSTAB, SST closure / pivoted QR; the thread-per-edge form the boundary
 //                   kernels and the five- and three-species edge kernels run), one interior edge at a time, with 1/D_st formed as k_transport does
 // On the host exp / pow / log are libm's — the bits the device's glibc-exact restatements (rx_libm.cuh) reproduce — and every division is the
@@ -203,5 +204,16 @@ extern "C" int emu_source(const rx_chem* ch, int rans, double cMu, double pasrLb
 extern "C" int emu_viscous(const rx_chem* ch, const rx_opts* op, int64_t nE, const int64_t* en, const double* normal, int64_t nP, const double* V,
                            const double* grad, const double* mu, const double* kap, const double* xy, const double* turb6, double* res) {
   EMU_NS(ch->Ns, viscous_ns<NS>(ch, op, nE, en, normal, nP, V, grad, mu, kap, xy, turb6, res));
+  return 0;
+}
+extern "C" int emu_qr(int64_t n, const double* A, const double* b, double* xs) {   // k_qr_eval_serial (rx_cuda.cu)
+  constexpr int NS = 9;
+  for (int64_t e = 0; e < n; ++e) {
+    double Al[NS * NS], bl[2][NS], xl[2][NS];
+    for (int k = 0; k < NS * NS; ++k) Al[k] = A[e * NS * NS + k];
+    for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) bl[dd][i] = b[(e * 2 + dd) * NS + i];
+    rx::colpiv_qr_solve<NS, 2, 1>(Al, bl, xl);
+    for (int dd = 0; dd < 2; ++dd) for (int i = 0; i < NS; ++i) xs[(e * 2 + dd) * NS + i] = xl[dd][i];
+  }
   return 0;
 }

@@ -164,6 +164,21 @@ def test_mass_production_source_equals_the_restatement_and_the_reference_library
     assert np.array_equal(res == 0.0, lib == 0.0)
 
 
+def test_pivoted_qr_source_equals_the_eigen_pinned_restatement(emu):
+    """colpiv_qr_solve<9, 2, 1> as the serial device form calls it, on the systems of the QR hooks (the SST closure's operator for random
+    compositions with trace species, dense matrices over several decades, rank-deficient ones, zero rows / columns, the zero matrix): every
+    entry equal to the oracle's restatement, which oracle/_ref/eigen_qr_check pins to Eigen 3.3.7's ColPivHouseholderQR bit for bit."""
+    from test_oracle_golden import qr_test_systems, oracle_qr
+    A, b = qr_test_systems(600)
+    want = oracle_qr(A, b)
+    Acm = np.ascontiguousarray(np.transpose(A, (0, 2, 1))).reshape(A.shape[0], 81)   # column-major, as the device form takes it
+    b = np.ascontiguousarray(b)
+    x = np.empty_like(b)
+    assert emu.emu_qr(C.c_int64(A.shape[0]), _d(Acm), _d(b), _d(x)) == 0
+    same = (x == want) | (np.isnan(x) & np.isnan(want))
+    assert same.all(), "%d entries differ" % int((~same).sum())
+
+
 def test_kernel_arithmetic_is_free_of_undefined_behaviour():
     """The tests above once more in a child process, with tests/host_emu.cpp built under UndefinedBehaviorSanitizer (array bounds of the unrolled
     per-species arrays, shifts, integer overflow, misaligned or null accesses): no report on any fixture."""
