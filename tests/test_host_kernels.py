@@ -1,0 +1,142 @@
+"""The CUDA kernels of the residual path run on the HOST, one simulated thread after another (tests/host_kernels.cpp over tests/cuda_host_shim.h),
+in the launch order of rx_cuda.cu, against the reference's stage dumps — bit for bit, in the CPU test tier.  Where tests/test_host_emulation.py
+checks the per-item arithmetic, this runs the kernels themselves: the structure-of-arrays indexing, the incident-edge lists of the owner-computes
+accumulation, the neighbour loops of the gradient and limiter kernels, the marker blocks of the boundary kernels.  One staged residual evaluation
+(RK stage 0) of every dumped iteration: primitives, transport, gradients, limiters, time step, the residual after the convective, viscous and
+source terms and after the boundary conditions.  Interior viscous edges go through the thread-per-edge kernel (on the device nine species use
+the two-lanes-per-edge kernel of the same arithmetic, a `-m gpu` test); TIME_STEPPING / dual-time cases are left to the GPU tier as well."""
+import ctypes as C
+import importlib
+import os
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+from rxcase import Case, GOLDEN, ROOT, load_package, chem_arrays, mesh_dict, opts_dict
+
+PKG = os.path.join(ROOT, "development-of-a-turbulent-numerical-solver-for-reactive-flows-in-su2_b200")
+_d = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+@pytest.fixture(scope="module")
+def hk(tmp_path_factory):
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    so = str(tmp_path_factory.mktemp("host_kernels") / "libhost_kernels.so")
+    # RX_HK_SAN=1 (set by test_kernels_on_the_host_are_clean_under_sanitizers, which runs this file once more in a child process with the
+    # sanitizer runtimes preloaded): every simulated thread under AddressSanitizer and UndefinedBehaviorSanitizer
+    san = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"] if os.environ.get("RX_HK_SAN") == "1" else ["-O2"]
+    cc = subprocess.run(["g++", "-std=c++17"] + san + ["-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "tests"),
+                         "-I", os.path.join(ROOT, "include"), "-I", os.path.join(PKG, "csrc"), os.path.join(ROOT, "tests", "host_kernels.cpp"), "-o", so],
+                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert cc.returncode == 0, cc.stdout[-3000:]
+    L = C.CDLL(so)
+    L.hk_create.restype = C.c_void_p
+    return L
+
+
+class HostKernels:
+    def __init__(self, L, case):
+        pk = load_package()
+        rs = importlib.import_module(pk.__name__ + ".rx_solver")
+        self.L, self.case = L, case
+        self.keep = []
+        k = lambda a, dt=np.float64: (self.keep.append(np.ascontiguousarray(a, dtype=dt)), self.keep[-1])[1]
+        _i = lambda a: a.ctypes.data_as(C.POINTER(C.c_int64))
+        mesh = mesh_dict(case)
+        Ns = case.Ns
+        ch = rs._chem_struct(chem_arrays(case), self.keep)
+        mks = mesh["markers"]
+        arr = (rs._Marker * max(len(mks), 1))()
+        for q, m in enumerate(mks):
+            node = k(m["node"], np.int64)
+            arr[q] = rs._Marker(int(m["kind"]), len(node), _i(node), _i(k(m["normalNeighbor"], np.int64)), _d(k(m["normal"])), float(m.get("T", 0.0)),
+                                float(m.get("Vmag", 0.0)), (C.c_double * 2)(*m.get("dir", [0.0, 0.0])), _d(k(m.get("Ys", np.zeros(Ns)))), float(m.get("P", 0.0)),
+                                float(m.get("Twall", 0.0)), float(m.get("heatFlux", 0.0)))
+        en = k(mesh["edgeNodes"], np.int64)
+        ms = rs._Mesh(case.nPoint, case.nPointDomain, int(en.shape[0]), _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])), _d(k(mesh["volume"])),
+                      _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
+        od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0, dualTime=0, deltaUnstTimeND=0.0,
+                  viscLimiter=0, device=0)
+        od.update(opts_dict(case))
+        o = rs._Opts(**{f[0]: od[f[0]] for f in rs._Opts._fields_})
+        self.keep += [arr, ms, ch, o]
+        self.h = C.c_void_p(L.hk_create(C.byref(ms), C.byref(ch), C.byref(o)))
+        assert self.h
+        self.nP, self.nVar, self.nPrim, self.nGrad = case.nPoint, Ns + 4, Ns + 7, Ns + 4
+
+    def close(self):
+        self.L.hk_destroy(self.h)
+
+    def get(self, what, shape):
+        out = np.empty(shape)
+        self.L.hk_get(self.h, what, _d(out))
+        return out
+
+
+NAMES = ["jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler",
+         "channel_rans_gg", "channel_lam_edge", "channel_lam_clip", "channel_rans_ign", "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam",
+         "channel_lam_inlet_total", "channel_rans_inlet_massflow", "channel_lam_supersonic", "channel_lam_visclim"]
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
+    case = Case("%s/%s.npz" % (GOLDEN, name))
+    cf = case.meta["cfg"]
+    s = HostKernels(hk, case)
+    nD = case.nPointDomain
+    its = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})
+    seen = set()
+
+    def check(it, what, a):
+        key = "it%04d_rk0_%s" % (it, what)
+        if not case.has(key):
+            return
+        ref = case[key].reshape(a.shape)
+        rows = slice(0, nD) if what.startswith("res") or what == "dt" else slice(None)
+        assert np.array_equal(a[rows], ref[rows]), "%s %s: %d entries differ, worst %.3e" % (name, key, int((a[rows] != ref[rows]).sum()), float(np.abs(a[rows] - ref[rows]).max()))
+        seen.add(what)
+
+    for it in its:
+        U = np.ascontiguousarray(case.stage(it, 0, "U0")); T = np.ascontiguousarray(case.stage(it, 0, "prev_V")[:, 0]); tb = np.ascontiguousarray(case.stage(it, 0, "turb"))
+        if case.has("it%04d_rk0_Uold" % it):   # Solution_Old at the start of the iteration: the non-physical fallback reads it
+            Uo = np.ascontiguousarray(case.stage(it, 0, "Uold"))
+            hk.hk_set_state(s.h, _d(Uo), _d(T), _d(tb)); hk.hk_set_old(s.h)
+        hk.hk_set_state(s.h, _d(U), _d(T), _d(tb))
+        hk.hk_preprocess(s.h, C.c_int64(it), 0)
+        check(it, "pre_V", s.get(0, (s.nP, s.nPrim))); check(it, "pre_aux", s.get(1, (s.nP, 6)))
+        if cf["viscous"]:
+            check(it, "pre_grad", s.get(2, (s.nP, s.nGrad, 2)))
+        if cf.get("limiter", 0):
+            check(it, "pre_lim", s.get(3, (s.nP, 4)))
+        hk.hk_set_old(s.h); hk.hk_time_step(s.h)
+        check(it, "dt", s.get(4, (s.nP, 3)))
+        hk.hk_residual(s.h, 1); check(it, "res_conv", s.get(5, (s.nP, s.nVar)))
+        hk.hk_residual(s.h, 2); check(it, "res_visc", s.get(5, (s.nP, s.nVar)))
+        hk.hk_residual(s.h, 3); check(it, "res_src", s.get(5, (s.nP, s.nVar)))
+        hk.hk_bc(s.h); check(it, "res_bc", s.get(5, (s.nP, s.nVar)))
+    s.close()
+    print(name, "stages compared bit for bit:", sorted(seen))
+    assert {"pre_V", "pre_aux", "dt", "res_bc"} <= seen, seen
+    if cf["viscous"]:
+        assert "pre_grad" in seen
+
+
+def test_kernels_on_the_host_are_clean_under_sanitizers():
+    """The same runs in a child process with tests/host_kernels.cpp built under AddressSanitizer and UndefinedBehaviorSanitizer: every access of
+    every simulated thread — structure-of-arrays indexing, incident-edge and neighbour lists, marker blocks, the thread-private matrices in the
+    stand-in for shared memory — stays inside its array, on all fixtures."""
+    if os.environ.get("RX_HK_SAN") == "1":
+        pytest.skip("this is the child run")
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    libs = [subprocess.run(["g++", "-print-file-name=" + n], stdout=subprocess.PIPE, text=True).stdout.strip() for n in ("libasan.so", "libubsan.so")]
+    if not all(os.path.isabs(p) and os.path.exists(p) for p in libs):
+        pytest.skip("this g++ has no sanitizer runtimes")
+    import sys
+    env = dict(os.environ, RX_HK_SAN="1", LD_PRELOAD=" ".join(libs), ASAN_OPTIONS="detect_leaks=0:verify_asan_link_order=0")
+    run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider"], cwd=os.path.dirname(os.path.abspath(__file__)),
+                         env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=2400)
+    assert run.returncode == 0 and "AddressSanitizer" not in run.stdout and "runtime error" not in run.stdout and " passed" in run.stdout, run.stdout[-4000:]
