@@ -37,6 +37,9 @@ struct CtxBase {
   virtual void residual(int what) = 0;   // 1 conv, 2 visc, 3 source
   virtual void bc() = 0;
   virtual void get(int what, double* out) = 0;   // 0 V, 1 aux6, 2 grad, 3 lim, 4 dt3, 5 R
+  virtual void set_time_levels(const double* Un, const double* Un1) = 0;
+  virtual void dual_time() = 0;
+  long long intIter = 0;
   int nVar = 0, nPrim = 0, nGrad = 0;
   long long nP = 0;
 };
@@ -51,6 +54,7 @@ struct Ctx : CtxBase {
   std::vector<double> sx; std::vector<Knot> stab;
   std::vector<int> ei, ej, nbPtr, nbIdx, incPtr, incEdge, nonPhys;
   std::vector<double> enx, eny, x, y, vol, U, Uold, V, X, Cp, gam, mu, kap, rD, grad, vort, strain, turb, dt, lamInv, lamVisc, R, lim, fluxC, fluxV;
+  std::vector<double> Un, Un1; double dtND = 0.0;   // dual time stepping: the stored time levels and the physical time step
   std::vector<unsigned char> eKey;
   std::vector<unsigned long long> counters;
   std::vector<std::vector<int>> mNode, mNn; std::vector<std::vector<double>> mNx, mNy, mGhost;
@@ -92,6 +96,8 @@ struct Ctx : CtxBase {
     o.prandtlLam = op->prandtlLam; o.prandtlTurb = op->prandtlTurb; o.lewisTurb = op->lewisTurb; o.cMu = op->cMu; o.pasrLb = op->pasrLb; o.tkeInf = op->tkeInf;
     o.secondOrder = op->secondOrder; o.limiter = op->secondOrder ? op->limiter : 0; o.limCoeff = op->limCoeff; o.refElemLength = op->refElemLength;
     o.viscLimiter = op->viscLimiter ? 1 : 0;
+    o.timeStepping = op->timeStepping; o.unstCfl = op->unstCfl; o.deltaUnstTime = op->deltaUnstTime; o.dualTime = op->dualTime; o.deltaUnstTimeND = op->deltaUnstTimeND;
+    dtND = o.deltaUnstTimeND;
     // ---- mesh as rx_create lays it out (no padding here: np = nPoint, ne = nEdge)
     const long long nE = m->nEdge;
     memset(&d, 0, sizeof d);
@@ -163,11 +169,33 @@ struct Ctx : CtxBase {
       else launch(d.nPoint, 128, [&] { k_limiter(o, d); });
     }
   }
-  void time_step() override {   // rx_time_step, steady form
+  double global_min() {   // k_dt_min_partial / k_dt_min_final (block reductions on the device; a minimum does not depend on the order)
+    double g = 1.0e6;
+    for (long long p = 0; p < d.nPointDomain; ++p) if (d.vol[p] > EPS) g = fmin(g, d.dt[p]);
+    return g;
+  }
+  void time_step() override {   // rx_time_step
     launch(d.nPointDomain, 128, [&] { k_timestep_edges(o, d); });
     for (const MarkerDev& m : markers) if (m.nVertex) launch(m.nVertex, 64, [&] { k_timestep_boundary(o, d, m); });
-    launch(d.nPointDomain, 128, [&] { k_timestep_finish(o, d); });
+    Opts of = o;
+    if (of.dualTime) of.timeStepping = 1;
+    launch(d.nPointDomain, 128, [&] { k_timestep_finish(of, d); });
+    if (o.timeStepping) {
+      const double glob = global_min();
+      if (!o.viscous) o.cfl = o.unstCfl;
+      const int useFixed = (!o.viscous && o.cfl < EPS) ? 1 : 0;
+      launch(d.nPointDomain, 256, [&] { k_dt_fill(d, &glob, o.deltaUnstTime, useFixed); });
+    }
+    if (o.dualTime) {
+      if (intIter == 0 && o.unstCfl != 0.0) { const double glob = global_min(); k_dual_unst_dt(&glob, o.unstCfl, o.cfl, &dtND); }
+      launch(d.nPointDomain, 256, [&] { k_dual_dt_clamp(d, o.maxDt, &dtND); });
+    }
   }
+  void set_time_levels(const double* a, const double* b) override {
+    Un.assign((size_t)nP * nVar, 0.0); Un1.assign((size_t)nP * nVar, 0.0);
+    for (long long p = 0; p < nP; ++p) for (int v = 0; v < nVar; ++v) { Un[v * nP + p] = a[p * nVar + v]; Un1[v * nP + p] = b[p * nVar + v]; }
+  }
+  void dual_time() override { launch(d.nPointDomain, 128, [&] { k_dual_time_residual(d, nVar, o.dualTime, &dtND, Un.data(), Un1.data()); }); }
   void residual(int what) override {
     if (what == 1) {
       if (o.secondOrder) launch(d.nEdge, 64, [&] { k_edge_conv2<NS>(cc, o, d); });
@@ -222,3 +250,6 @@ extern "C" void hk_time_step(void* h) { ((CtxBase*)h)->time_step(); }
 extern "C" void hk_residual(void* h, int what) { ((CtxBase*)h)->residual(what); }
 extern "C" void hk_bc(void* h) { ((CtxBase*)h)->bc(); }
 extern "C" void hk_get(void* h, int what, double* out) { ((CtxBase*)h)->get(what, out); }
+extern "C" void hk_set_time_levels(void* h, const double* Un, const double* Un1) { ((CtxBase*)h)->set_time_levels(Un, Un1); }
+extern "C" void hk_set_inner_iteration(void* h, int64_t it) { ((CtxBase*)h)->intIter = it; }
+extern "C" void hk_dual_time(void* h) { ((CtxBase*)h)->dual_time(); }

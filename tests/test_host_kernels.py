@@ -4,7 +4,8 @@ checks the per-item arithmetic, this runs the kernels themselves: the structure-
 accumulation, the neighbour loops of the gradient and limiter kernels, the marker blocks of the boundary kernels.  One staged residual evaluation
 (RK stage 0) of every dumped iteration: primitives, transport, gradients, limiters, time step, the residual after the convective, viscous and
 source terms and after the boundary conditions.  Interior viscous edges go through the thread-per-edge kernel (on the device nine species use
-the two-lanes-per-edge kernel of the same arithmetic, a `-m gpu` test); TIME_STEPPING / dual-time cases are left to the GPU tier as well."""
+the two-lanes-per-edge kernel of the same arithmetic, a `-m gpu` test).  TIME_STEPPING and dual time stepping included (their global minimum is a
+plain loop here, a block reduction on the device)."""
 import ctypes as C
 import importlib
 import os
@@ -78,7 +79,8 @@ class HostKernels:
 
 NAMES = ["jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans", "channel_lam_walls", "channel_lam_muscl", "channel_lam_bj", "channel_euler",
          "channel_rans_gg", "channel_lam_edge", "channel_lam_clip", "channel_rans_ign", "channel_air3_lam", "channel_air3_rans", "channel_mix5_lam",
-         "channel_lam_inlet_total", "channel_rans_inlet_massflow", "channel_lam_supersonic", "channel_lam_visclim"]
+         "channel_lam_inlet_total", "channel_rans_inlet_massflow", "channel_lam_supersonic", "channel_lam_visclim",
+         "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed", "channel_lam_dualtime2", "channel_euler_dualtime1", "channel_rans_dualtime2"]
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -105,6 +107,9 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
             Uo = np.ascontiguousarray(case.stage(it, 0, "Uold"))
             hk.hk_set_state(s.h, _d(Uo), _d(T), _d(tb)); hk.hk_set_old(s.h)
         hk.hk_set_state(s.h, _d(U), _d(T), _d(tb))
+        if cf.get("dual_time", 0):
+            a = np.ascontiguousarray(case.stage(it, 0, "Un")); b = np.ascontiguousarray(case.stage(it, 0, "Un1"))
+            hk.hk_set_time_levels(s.h, _d(a), _d(b)); hk.hk_set_inner_iteration(s.h, C.c_int64(it % cf.get("dual_inner", 2)))
         hk.hk_preprocess(s.h, C.c_int64(it), 0)
         check(it, "pre_V", s.get(0, (s.nP, s.nPrim))); check(it, "pre_aux", s.get(1, (s.nP, 6)))
         if cf["viscous"]:
@@ -116,12 +121,16 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
         hk.hk_residual(s.h, 1); check(it, "res_conv", s.get(5, (s.nP, s.nVar)))
         hk.hk_residual(s.h, 2); check(it, "res_visc", s.get(5, (s.nP, s.nVar)))
         hk.hk_residual(s.h, 3); check(it, "res_src", s.get(5, (s.nP, s.nVar)))
+        if cf.get("dual_time", 0):
+            hk.hk_dual_time(s.h); check(it, "res_dual", s.get(5, (s.nP, s.nVar)))
         hk.hk_bc(s.h); check(it, "res_bc", s.get(5, (s.nP, s.nVar)))
     s.close()
     print(name, "stages compared bit for bit:", sorted(seen))
     assert {"pre_V", "pre_aux", "dt", "res_bc"} <= seen, seen
     if cf["viscous"]:
         assert "pre_grad" in seen
+    if cf.get("dual_time", 0):
+        assert "res_dual" in seen
 
 
 def test_kernels_on_the_host_are_clean_under_sanitizers():
