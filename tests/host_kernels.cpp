@@ -36,7 +36,8 @@ struct CtxBase {
   virtual void time_step() = 0;
   virtual void residual(int what) = 0;   // 1 conv, 2 visc, 3 source
   virtual void bc() = 0;
-  virtual void get(int what, double* out) = 0;   // 0 V, 1 aux6, 2 grad, 3 lim, 4 dt3, 5 R
+  virtual void get(int what, double* out) = 0;   // 0 V, 1 aux6, 2 grad, 3 lim, 4 dt3, 5 R, 6 U
+  virtual void update(double alpha) = 0;
   virtual void set_time_levels(const double* Un, const double* Un1) = 0;
   virtual void dual_time() = 0;
   long long intIter = 0;
@@ -222,6 +223,11 @@ struct Ctx : CtxBase {
     for (const MarkerDev& m : markers) if (is_inlet(m.kind) || is_super(m.kind) || m.kind == RX_BC_OUTLET || m.kind == RX_BC_EULER_WALL) bc_marker(m);
     for (const MarkerDev& m : markers) if (m.kind == RX_BC_ISOTHERMAL || m.kind == RX_BC_HEATFLUX) bc_marker(m);
   }
+  void update(double alpha) override {   // rx_update_explicit: the clipped update of every owned point; the block reductions of the norms are not formed here
+    const long long nb = (d.nPointDomain + 127) / 128;
+    std::vector<double> partial((size_t)std::max<long long>(nb, 1) * nVar);
+    launch(nb * 128, 128, [&] { k_update<NS, false>(d, alpha, partial.data(), nullptr, nullptr); });
+  }
   void get(int what, double* out) override {
     auto aos = [&](const std::vector<double>& soa, int nv) { for (long long p = 0; p < nP; ++p) for (int v = 0; v < nv; ++v) out[p * nv + v] = soa[v * nP + p]; };
     if (what == 0) aos(V, nPrim);
@@ -230,6 +236,7 @@ struct Ctx : CtxBase {
     else if (what == 3) aos(lim, 4);
     else if (what == 4) for (long long p = 0; p < nP; ++p) { out[3 * p] = dt[p]; out[3 * p + 1] = lamInv[p]; out[3 * p + 2] = lamVisc[p]; }
     else if (what == 5) aos(R, nVar);
+    else if (what == 6) aos(U, nVar);
   }
 };
 }  // namespace
@@ -253,3 +260,4 @@ extern "C" void hk_get(void* h, int what, double* out) { ((CtxBase*)h)->get(what
 extern "C" void hk_set_time_levels(void* h, const double* Un, const double* Un1) { ((CtxBase*)h)->set_time_levels(Un, Un1); }
 extern "C" void hk_set_inner_iteration(void* h, int64_t it) { ((CtxBase*)h)->intIter = it; }
 extern "C" void hk_dual_time(void* h) { ((CtxBase*)h)->dual_time(); }
+extern "C" void hk_update(void* h, double alpha) { ((CtxBase*)h)->update(alpha); }

@@ -1,9 +1,8 @@
 """The CUDA kernels of the residual path run on the HOST, one simulated thread after another (tests/host_kernels.cpp over tests/cuda_host_shim.h),
 in the launch order of rx_cuda.cu, against the reference's stage dumps — bit for bit, in the CPU test tier.  Where tests/test_host_emulation.py
 checks the per-item arithmetic, this runs the kernels themselves: the structure-of-arrays indexing, the incident-edge lists of the owner-computes
-accumulation, the neighbour loops of the gradient and limiter kernels, the marker blocks of the boundary kernels.  One staged residual evaluation
-(RK stage 0) of every dumped iteration: primitives, transport, gradients, limiters, time step, the residual after the convective, viscous and
-source terms and after the boundary conditions.  Interior viscous edges go through the thread-per-edge kernel (on the device nine species use
+accumulation, the neighbour loops of the gradient and limiter kernels, the marker blocks of the boundary kernels.  Every dumped iteration in full — all Runge-Kutta stages, each from the state the kernels themselves left: primitives, transport, gradients, limiters,
+time step, the residual after the convective, viscous and source terms and after the boundary conditions, the clipped update, the Output pass.  Interior viscous edges go through the thread-per-edge kernel (on the device nine species use
 the two-lanes-per-edge kernel of the same arithmetic, a `-m gpu` test).  TIME_STEPPING and dual time stepping included (their global minimum is a
 plain loop here, a block reduction on the device)."""
 import ctypes as C
@@ -92,15 +91,16 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
     its = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})
     seen = set()
 
-    def check(it, what, a):
-        key = "it%04d_rk0_%s" % (it, what)
+    def check(it, rk, what, a):
+        key = "it%04d_rk%d_%s" % (it, rk, what)
         if not case.has(key):
             return
         ref = case[key].reshape(a.shape)
-        rows = slice(0, nD) if what.startswith("res") or what == "dt" else slice(None)
+        rows = slice(0, nD) if what.startswith("res") or what in ("dt", "U1") else slice(None)
         assert np.array_equal(a[rows], ref[rows]), "%s %s: %d entries differ, worst %.3e" % (name, key, int((a[rows] != ref[rows]).sum()), float(np.abs(a[rows] - ref[rows]).max()))
         seen.add(what)
 
+    nrk = cf["nRK"] if cf["time_scheme"] == 1 else 1
     for it in its:
         U = np.ascontiguousarray(case.stage(it, 0, "U0")); T = np.ascontiguousarray(case.stage(it, 0, "prev_V")[:, 0]); tb = np.ascontiguousarray(case.stage(it, 0, "turb"))
         if case.has("it%04d_rk0_Uold" % it):   # Solution_Old at the start of the iteration: the non-physical fallback reads it
@@ -110,23 +110,29 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
         if cf.get("dual_time", 0):
             a = np.ascontiguousarray(case.stage(it, 0, "Un")); b = np.ascontiguousarray(case.stage(it, 0, "Un1"))
             hk.hk_set_time_levels(s.h, _d(a), _d(b)); hk.hk_set_inner_iteration(s.h, C.c_int64(it % cf.get("dual_inner", 2)))
-        hk.hk_preprocess(s.h, C.c_int64(it), 0)
-        check(it, "pre_V", s.get(0, (s.nP, s.nPrim))); check(it, "pre_aux", s.get(1, (s.nP, 6)))
-        if cf["viscous"]:
-            check(it, "pre_grad", s.get(2, (s.nP, s.nGrad, 2)))
-        if cf.get("limiter", 0):
-            check(it, "pre_lim", s.get(3, (s.nP, 4)))
-        hk.hk_set_old(s.h); hk.hk_time_step(s.h)
-        check(it, "dt", s.get(4, (s.nP, 3)))
-        hk.hk_residual(s.h, 1); check(it, "res_conv", s.get(5, (s.nP, s.nVar)))
-        hk.hk_residual(s.h, 2); check(it, "res_visc", s.get(5, (s.nP, s.nVar)))
-        hk.hk_residual(s.h, 3); check(it, "res_src", s.get(5, (s.nP, s.nVar)))
-        if cf.get("dual_time", 0):
-            hk.hk_dual_time(s.h); check(it, "res_dual", s.get(5, (s.nP, s.nVar)))
-        hk.hk_bc(s.h); check(it, "res_bc", s.get(5, (s.nP, s.nVar)))
+        for rk in range(nrk):   # the later stages start from the state the kernels themselves left
+            hk.hk_preprocess(s.h, C.c_int64(it), 0)
+            check(it, rk, "pre_V", s.get(0, (s.nP, s.nPrim))); check(it, rk, "pre_aux", s.get(1, (s.nP, 6)))
+            if cf["viscous"]:
+                check(it, rk, "pre_grad", s.get(2, (s.nP, s.nGrad, 2)))
+            if cf.get("limiter", 0):
+                check(it, rk, "pre_lim", s.get(3, (s.nP, 4)))
+            if rk == 0:
+                hk.hk_set_old(s.h); hk.hk_time_step(s.h)
+                check(it, rk, "dt", s.get(4, (s.nP, 3)))
+            hk.hk_residual(s.h, 1); check(it, rk, "res_conv", s.get(5, (s.nP, s.nVar)))
+            hk.hk_residual(s.h, 2); check(it, rk, "res_visc", s.get(5, (s.nP, s.nVar)))
+            hk.hk_residual(s.h, 3); check(it, rk, "res_src", s.get(5, (s.nP, s.nVar)))
+            if cf.get("dual_time", 0):
+                hk.hk_dual_time(s.h); check(it, rk, "res_dual", s.get(5, (s.nP, s.nVar)))
+            hk.hk_bc(s.h); check(it, rk, "res_bc", s.get(5, (s.nP, s.nVar)))
+            hk.hk_update(s.h, C.c_double(cf["rk_alpha"][rk] if nrk > 1 else 1.0))
+            check(it, rk, "U1", s.get(6, (s.nP, s.nVar)))
+        hk.hk_preprocess(s.h, C.c_int64(it), 1)   # the Output pass
+        check(it, 0, "out_V", s.get(0, (s.nP, s.nPrim))); check(it, 0, "out_aux", s.get(1, (s.nP, 6)))
     s.close()
     print(name, "stages compared bit for bit:", sorted(seen))
-    assert {"pre_V", "pre_aux", "dt", "res_bc"} <= seen, seen
+    assert {"pre_V", "pre_aux", "dt", "res_bc", "U1"} <= seen, seen
     if cf["viscous"]:
         assert "pre_grad" in seen
     if cf.get("dual_time", 0):
