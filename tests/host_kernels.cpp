@@ -4,7 +4,8 @@
 // residual evaluation of the path, laid out (structure of arrays, incident-edge lists, marker blocks) as rx_create lays it out.  TEST
 // INFRASTRUCTURE for tests/test_host_kernels.py: the kernels' source, not only their per-item arithmetic, is compared with the reference's dumps
 // where no GPU exists.  Not run here: the two-lanes-per-edge viscous kernel (warp shuffles; the thread-per-edge kernel of the same arithmetic
-// stands in, as it does on the device for five and three species), the update's block reductions, anything that needs the CUDA runtime.
+// stands in, as it does on the device for five and three species), the block reductions of the norms, the linear solve of the SST step (its sweeps synchronise inside a block), anything that needs the CUDA runtime.
+// The SST solver's residual assembly (k_turb_rows, k_turb_dual_time, k_turb_bc_io, k_turb_bc_wall) and Postprocessing (k_turb_blend) are run.
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
@@ -13,6 +14,8 @@
 #include "cuda_host_shim.h"
 #include "rx_cuda.h"
 #include "rx_kernels2.cuh"
+#include "rx_turb.cuh"
+#include "rx_turb_step.cuh"
 
 namespace rx { double smat[1 << 16]; }   // the dynamic shared memory of the boundary / thread-per-edge kernels: one thread-private matrix per lane
 
@@ -38,6 +41,10 @@ struct CtxBase {
   virtual void bc() = 0;
   virtual void get(int what, double* out) = 0;   // 0 V, 1 aux6, 2 grad, 3 lim, 4 dt3, 5 R, 6 U
   virtual void update(double alpha) = 0;
+  // SST solver: LinSysRes after Upwind + Viscous + Source (+ dual time) residual and the boundary conditions (tres); the Postprocessing fields (tpost)
+  virtual void turb_residual(const double* kw, const double* blend3, const double* dist, double kineInf, double omegaInf, const double* kwN, const double* kwN1,
+                             double* res2) = 0;
+  virtual void turb_post(const double* kw, const double* dist, double sigmaK, double* post12) = 0;
   virtual void set_time_levels(const double* Un, const double* Un1) = 0;
   virtual void dual_time() = 0;
   long long intIter = 0;
@@ -228,6 +235,56 @@ struct Ctx : CtxBase {
     std::vector<double> partial((size_t)std::max<long long>(nb, 1) * nVar);
     launch(nb * 128, 128, [&] { k_update<NS, false>(d, alpha, partial.data(), nullptr, nullptr); });
   }
+  std::vector<double> tp, tres, tdiag, toff, tx, told, tkN, tkN1;
+  void turb_load(const double* kw, const double* blend3, const double* dist) {
+    tp.resize((size_t)TP_N * nP, 0.0);
+    for (long long p = 0; p < nP; ++p) {
+      tp[TP_K * nP + p] = kw[2 * p]; tp[TP_W * nP + p] = kw[2 * p + 1]; tp[TP_DIST * nP + p] = dist[p];
+      if (blend3) { tp[TP_F1 * nP + p] = blend3[3 * p]; tp[TP_F2 * nP + p] = blend3[3 * p + 1]; tp[TP_CD * nP + p] = blend3[3 * p + 2]; }
+    }
+  }
+  void turb_gradient() {
+    double* t = tp.data();
+    if (o.leastSquares) launch(d.nPoint, 128, [&] { k_turb_gradient_ls(d, t); });
+    else {
+      launch(d.nPoint, 128, [&] { k_turb_gradient_gg_edges(d, t); });
+      for (const MarkerDev& m : markers) if (m.nVertex) launch(m.nVertex, 64, [&] { k_turb_gradient_gg_boundary(d, m, t); });
+      launch(d.nPoint, 128, [&] { k_turb_gradient_gg_finish(d, t); });
+    }
+  }
+  void turb_residual(const double* kw, const double* blend3, const double* dist, double kineInf, double omegaInf, const double* kwN, const double* kwN1,
+                     double* res2) override {   // rx_turb_iterate up to the assembled residual
+    turb_load(kw, blend3, dist);
+    TurbC tc;
+    tc.alfa_1 = tc.beta_1 / tc.beta_star - tc.sigma_om1 * 0.41 * 0.41 / std::sqrt(tc.beta_star);
+    tc.alfa_2 = tc.beta_2 / tc.beta_star - tc.sigma_om2 * 0.41 * 0.41 / std::sqrt(tc.beta_star);
+    tc.kineInf = kineInf; tc.omegaInf = omegaInf; tc.cflRed = 1.0; tc.relax = 1.0;
+    TurbW w;
+    w.nInc = (long long)incEdge.size();
+    tres.assign((size_t)2 * nP, 0.0); tdiag.assign((size_t)2 * nP, 0.0); toff.assign((size_t)2 * std::max<long long>(w.nInc, 1), 0.0);
+    tx.assign((size_t)2 * nP, 0.0); told.assign(tp.begin(), tp.begin() + 2 * nP);
+    w.res = tres.data(); w.diag = tdiag.data(); w.off = toff.data(); w.x = tx.data(); w.old = told.data();
+    turb_gradient();
+    double* t = tp.data();
+    launch(d.nPointDomain, 128, [&] { k_turb_rows(tc, d, t, w); });
+    if (o.dualTime) {
+      tkN.assign((size_t)2 * nP, 0.0); tkN1.assign((size_t)2 * nP, 0.0);
+      for (long long p = 0; p < nP; ++p) for (int v = 0; v < 2; ++v) { tkN[v * nP + p] = kwN[2 * p + v]; tkN1[v * nP + p] = kwN1[2 * p + v]; }
+      launch(d.nPointDomain, 128, [&] { k_turb_dual_time(d, t, w, o.dualTime, &dtND, Un.data(), Un1.data(), tkN.data(), tkN1.data()); });
+    }
+    for (const MarkerDev& m : markers)
+      if (m.nVertex && (is_inlet(m.kind) || m.kind == RX_BC_OUTLET)) launch(m.nVertex, 64, [&] { k_turb_bc_io(tc, d, m, t, w, is_inlet(m.kind) ? 1 : 0); });
+    for (const MarkerDev& m : markers)
+      if (m.nVertex && (m.kind == RX_BC_ISOTHERMAL || m.kind == RX_BC_HEATFLUX)) launch(m.nVertex, 64, [&] { k_turb_bc_wall(tc, d, m, t, w); });
+    for (long long p = 0; p < nP; ++p) { res2[2 * p] = tres[p]; res2[2 * p + 1] = tres[nP + p]; }
+  }
+  void turb_post(const double* kw, const double* dist, double sigmaK, double* post12) override {   // rx_turb_postprocess
+    turb_load(kw, nullptr, dist);
+    turb_gradient();
+    double* t = tp.data();
+    launch(d.nPoint, 128, [&] { k_turb_blend(d, t, sigmaK); });
+    for (long long p = 0; p < nP; ++p) for (int v = 0; v < TP_N; ++v) post12[p * TP_N + v] = tp[v * nP + p];
+  }
   void get(int what, double* out) override {
     auto aos = [&](const std::vector<double>& soa, int nv) { for (long long p = 0; p < nP; ++p) for (int v = 0; v < nv; ++v) out[p * nv + v] = soa[v * nP + p]; };
     if (what == 0) aos(V, nPrim);
@@ -261,3 +318,6 @@ extern "C" void hk_set_time_levels(void* h, const double* Un, const double* Un1)
 extern "C" void hk_set_inner_iteration(void* h, int64_t it) { ((CtxBase*)h)->intIter = it; }
 extern "C" void hk_dual_time(void* h) { ((CtxBase*)h)->dual_time(); }
 extern "C" void hk_update(void* h, double alpha) { ((CtxBase*)h)->update(alpha); }
+extern "C" void hk_turb_residual(void* h, const double* kw, const double* blend3, const double* dist, double kineInf, double omegaInf, const double* kwN,
+                                 const double* kwN1, double* res2) { ((CtxBase*)h)->turb_residual(kw, blend3, dist, kineInf, omegaInf, kwN, kwN1, res2); }
+extern "C" void hk_turb_post(void* h, const double* kw, const double* dist, double sigmaK, double* post12) { ((CtxBase*)h)->turb_post(kw, dist, sigmaK, post12); }

@@ -96,7 +96,7 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
         if not case.has(key):
             return
         ref = case[key].reshape(a.shape)
-        rows = slice(0, nD) if what.startswith("res") or what in ("dt", "U1") else slice(None)
+        rows = slice(0, nD) if what.startswith("res") or what in ("dt", "U1", "tres", "tpost") else slice(None)
         assert np.array_equal(a[rows], ref[rows]), "%s %s: %d entries differ, worst %.3e" % (name, key, int((a[rows] != ref[rows]).sum()), float(np.abs(a[rows] - ref[rows]).max()))
         seen.add(what)
 
@@ -130,6 +130,21 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
             check(it, rk, "U1", s.get(6, (s.nP, s.nVar)))
         hk.hk_preprocess(s.h, C.c_int64(it), 1)   # the Output pass
         check(it, 0, "out_V", s.get(0, (s.nP, s.nPrim))); check(it, 0, "out_aux", s.get(1, (s.nP, 6)))
+        if cf["rans"] and case.has("it%04d_rk0_tres" % it):
+            # the SST solver's step on the state the flow iteration left: its assembled residual (Upwind, Viscous, Source, dual-time term, boundary
+            # conditions), then its Postprocessing on the (k, omega) the reference's solve produced
+            tpost = case.stage(it, 0, "tpost")
+            kw = np.ascontiguousarray(tb[:, 1:3]); bl = np.ascontiguousarray(case.stage(it, 0, "tblend")); dist = np.ascontiguousarray(tpost[:, 2])
+            kn = np.ascontiguousarray(case.stage(it, 0, "tUn")) if cf.get("dual_time", 0) else None
+            kn1 = np.ascontiguousarray(case.stage(it, 0, "tUn1")) if cf.get("dual_time", 0) else None
+            res = np.empty((s.nP, 2))
+            hk.hk_turb_residual(s.h, _d(kw), _d(bl), _d(dist), C.c_double(cf["kine_inf"]), C.c_double(cf["omega_inf"]), _d(kn) if kn is not None else None,
+                                _d(kn1) if kn1 is not None else None, _d(res))
+            check(it, 0, "tres", res)
+            post = np.empty((s.nP, 12))
+            ksol = np.ascontiguousarray(case.stage(it, 0, "tsol"))
+            hk.hk_turb_post(s.h, _d(ksol), _d(dist), C.c_double(float(tpost[0, 11])), _d(post))
+            check(it, 0, "tpost", post)
     s.close()
     print(name, "stages compared bit for bit:", sorted(seen))
     assert {"pre_V", "pre_aux", "dt", "res_bc", "U1"} <= seen, seen
@@ -137,6 +152,8 @@ def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
         assert "pre_grad" in seen
     if cf.get("dual_time", 0):
         assert "res_dual" in seen
+    if cf["rans"]:
+        assert {"tres", "tpost"} <= seen, seen
 
 
 def test_kernels_on_the_host_are_clean_under_sanitizers():
