@@ -166,6 +166,7 @@ __device__ __forceinline__ void pair_colpiv_qr_solve(const PairLane& L, double* 
     double nb = nU[PM::off(k)];
     for (int j = k + 1; j < NS; ++j) { const double nj = nU[PM::off(j)]; if (nj > nb) { nb = nj; big = j; } }
     if (nonzero == NS && nb * nb < threshold_helper * (double)(NS - k)) nonzero = k;
+    __syncwarp();   // both lanes have read the norms (the scan above, and before the loop) before lane 0 swaps them below
     if (big != k) {
       double* ck = M.col(k); double* cb = M.col(big);
 #pragma unroll

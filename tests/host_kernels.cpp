@@ -16,8 +16,10 @@
 #include "rx_kernels2.cuh"
 #include "rx_turb.cuh"
 #include "rx_turb_step.cuh"
+#include "rx_visc_pair.cuh"   // compiled with -DRX_VP_NO_ASYNC_D: the 1/D prefetch through registers instead of cp.async (no PTX on the host)
+#include <thread>
 
-namespace rx { double smat[1 << 16]; }   // the dynamic shared memory of the boundary / thread-per-edge kernels: one thread-private matrix per lane
+namespace rx { double smat[1 << 16]; double vp_sm[1 << 16]; }   // the dynamic shared memory of the boundary / thread-per-edge kernels: one thread-private matrix per lane
 
 namespace {
 using namespace rx;
@@ -29,6 +31,22 @@ void launch(long long n, int bs, F kernel) {
     blockIdx.x = b;
     for (int t = 0; t < bs; ++t) { threadIdx.x = (unsigned)t; kernel(); }
   }
+}
+
+// the two-lanes-per-edge kernel: even lanes on this thread, odd lanes on a second one, pair after pair in the same order (cuda_host_shim.h)
+template <class F>
+void launch_pairs(long long nLanes, int bs, F kernel) {
+  const unsigned nb = (unsigned)((nLanes + bs - 1) / bs);
+  auto run = [&](int l) {
+    blockDim.x = (unsigned)bs; gridDim.x = nb;
+    for (unsigned b = 0; b < nb; ++b) {
+      blockIdx.x = b;
+      for (int t = l; t < bs; t += 2) { threadIdx.x = (unsigned)t; kernel(); emu::pair_barrier(); }
+    }
+  };
+  std::thread odd(run, 1);
+  run(0);
+  odd.join();
 }
 
 struct CtxBase {
@@ -48,6 +66,7 @@ struct CtxBase {
   virtual void set_time_levels(const double* Un, const double* Un1) = 0;
   virtual void dual_time() = 0;
   long long intIter = 0;
+  int usePair = 0;   // interior viscous edges of a nine-species context through k_edge_visc_pair instead of k_edge_visc_generic
   int nVar = 0, nPrim = 0, nGrad = 0;
   long long nP = 0;
 };
@@ -210,11 +229,21 @@ struct Ctx : CtxBase {
       else launch(d.nEdge, 128, [&] { k_edge_flux<NS>(cc, o, d); });
       launch(d.nPoint, 128, [&] { k_accumulate<NS, 1>(cc, o, d); });
     } else if (what == 2 && o.viscous) {
-      if (o.rans) launch(d.nEdge, EDGE_BS, [&] { k_edge_visc_generic<NS, true>(cc, o, d); });
+      if (usePair) launch_pair_kernel();
+      else if (o.rans) launch(d.nEdge, EDGE_BS, [&] { k_edge_visc_generic<NS, true>(cc, o, d); });
       else launch(d.nEdge, EDGE_BS, [&] { k_edge_visc_generic<NS, false>(cc, o, d); });
       launch(d.nPoint, 128, [&] { k_accumulate<NS, 2>(cc, o, d); });
     } else if (what == 3) {
       launch(d.nPointDomain, 128, [&] { k_source<NS>(cc, o, d); });
+    }
+  }
+  void launch_pair_kernel() {
+    if constexpr (NS == 9) {
+      if (o.viscLimiter) {
+        if (o.rans) launch_pairs(2 * d.nEdge, VP_BS, [&] { k_edge_visc_pair<9, true, true>(cc, o, d); });
+        else launch_pairs(2 * d.nEdge, VP_BS, [&] { k_edge_visc_pair<9, false, true>(cc, o, d); });
+      } else if (o.rans) launch_pairs(2 * d.nEdge, VP_BS, [&] { k_edge_visc_pair<9, true>(cc, o, d); });
+      else launch_pairs(2 * d.nEdge, VP_BS, [&] { k_edge_visc_pair<9, false>(cc, o, d); });
     }
   }
   void bc_marker(const MarkerDev& m) {
@@ -321,3 +350,5 @@ extern "C" void hk_update(void* h, double alpha) { ((CtxBase*)h)->update(alpha);
 extern "C" void hk_turb_residual(void* h, const double* kw, const double* blend3, const double* dist, double kineInf, double omegaInf, const double* kwN,
                                  const double* kwN1, double* res2) { ((CtxBase*)h)->turb_residual(kw, blend3, dist, kineInf, omegaInf, kwN, kwN1, res2); }
 extern "C" void hk_turb_post(void* h, const double* kw, const double* dist, double sigmaK, double* post12) { ((CtxBase*)h)->turb_post(kw, dist, sigmaK, post12); }
+extern "C" void hk_use_pair(void* h, int on) { ((CtxBase*)h)->usePair = on; }
+

@@ -28,7 +28,8 @@ def hk(tmp_path_factory):
     # RX_HK_SAN=1 (set by test_kernels_on_the_host_are_clean_under_sanitizers, which runs this file once more in a child process with the
     # sanitizer runtimes preloaded): every simulated thread under AddressSanitizer and UndefinedBehaviorSanitizer
     san = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"] if os.environ.get("RX_HK_SAN") == "1" else ["-O2"]
-    cc = subprocess.run(["g++", "-std=c++17"] + san + ["-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "tests"),
+    # -DRX_VP_NO_ASYNC_D: the pair kernel's 1/D prefetch through registers (the cp.async form is inline PTX)
+    cc = subprocess.run(["g++", "-std=c++17", "-pthread", "-DRX_VP_NO_ASYNC_D"] + san + ["-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "tests"),
                          "-I", os.path.join(ROOT, "include"), "-I", os.path.join(PKG, "csrc"), os.path.join(ROOT, "tests", "host_kernels.cpp"), "-o", so],
                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert cc.returncode == 0, cc.stdout[-3000:]
@@ -38,7 +39,7 @@ def hk(tmp_path_factory):
 
 
 class HostKernels:
-    def __init__(self, L, case):
+    def __init__(self, L, case, pair=False):
         pk = load_package()
         rs = importlib.import_module(pk.__name__ + ".rx_solver")
         self.L, self.case = L, case
@@ -65,6 +66,7 @@ class HostKernels:
         self.keep += [arr, ms, ch, o]
         self.h = C.c_void_p(L.hk_create(C.byref(ms), C.byref(ch), C.byref(o)))
         assert self.h
+        L.hk_use_pair(self.h, 1 if pair else 0)
         self.nP, self.nVar, self.nPrim, self.nGrad = case.nPoint, Ns + 4, Ns + 7, Ns + 4
 
     def close(self):
@@ -82,11 +84,30 @@ NAMES = ["jet_rans_perturbed", "channel_lam_rk", "channel_lam_gg", "channel_rans
          "channel_lam_unsteady", "channel_euler_unsteady", "channel_euler_unsteady_fixed", "channel_lam_dualtime2", "channel_euler_dualtime1", "channel_rans_dualtime2"]
 
 
+PAIR_NAMES = ["channel_lam_rk", "channel_lam_gg", "channel_lam_walls", "channel_lam_visclim", "channel_lam_edge", "channel_lam_clip", "channel_lam_muscl",
+              "channel_rans", "channel_rans_gg", "channel_rans_ign", "channel_rans_inlet_massflow", "channel_rans_dualtime2", "jet_rans_perturbed"]
+
+
+@pytest.mark.parametrize("name", PAIR_NAMES)
+def test_two_lanes_per_edge_viscous_kernel_on_the_host(hk, name):
+    """k_edge_visc_pair — the nine-species viscous kernel of the device, two lanes per edge — with its two lanes run as two host threads in lockstep
+    (shuffles and votes become exchanges between the two, tests/cuda_host_shim.h): the same stage dumps, bit for bit, through whole iterations.
+    Laminar and RANS fixtures (the SST closure's pivoted QR worked by the pair on one shared copy of the operator).  Two host threads do not
+    advance together the way the lanes of a warp do, so every hand-over between the lanes must go through a __syncwarp or a shuffle: the run is
+    race-free under ThreadSanitizer, which is how the one missing __syncwarp of the pair QR (before lane 0 swaps the column norms the other lane
+    has just scanned) was found."""
+    _run_case(hk, name, pair=True)
+
+
 @pytest.mark.parametrize("name", NAMES)
 def test_kernels_on_the_host_reproduce_the_reference_stage_dumps(hk, name):
+    _run_case(hk, name, pair=False)
+
+
+def _run_case(hk, name, pair):
     case = Case("%s/%s.npz" % (GOLDEN, name))
     cf = case.meta["cfg"]
-    s = HostKernels(hk, case)
+    s = HostKernels(hk, case, pair=pair)
     nD = case.nPointDomain
     its = sorted({int(k[2:6]) for k in case.arr if k.startswith("it")})
     seen = set()
