@@ -39,16 +39,19 @@ def hk(tmp_path_factory):
 
 
 class HostKernels:
-    def __init__(self, L, case, pair=False):
+    def __init__(self, L, case, pair=False, mesh=None, chem=None, opts=None):
+        """From a golden case, or (case = None) from a flat mesh dict, a mechanism dict and an options dict."""
         pk = load_package()
         rs = importlib.import_module(pk.__name__ + ".rx_solver")
         self.L, self.case = L, case
         self.keep = []
         k = lambda a, dt=np.float64: (self.keep.append(np.ascontiguousarray(a, dtype=dt)), self.keep[-1])[1]
         _i = lambda a: a.ctypes.data_as(C.POINTER(C.c_int64))
-        mesh = mesh_dict(case)
-        Ns = case.Ns
-        ch = rs._chem_struct(chem_arrays(case), self.keep)
+        mesh = mesh_dict(case) if case is not None else mesh
+        chem = chem_arrays(case) if case is not None else chem
+        Ns = int(chem["Ns"])
+        nPoint, nDom = int(mesh["nPoint"]), int(mesh["nPointDomain"])
+        ch = rs._chem_struct(chem, self.keep)
         mks = mesh["markers"]
         arr = (rs._Marker * max(len(mks), 1))()
         for q, m in enumerate(mks):
@@ -57,17 +60,17 @@ class HostKernels:
                                 float(m.get("Vmag", 0.0)), (C.c_double * 2)(*m.get("dir", [0.0, 0.0])), _d(k(m.get("Ys", np.zeros(Ns)))), float(m.get("P", 0.0)),
                                 float(m.get("Twall", 0.0)), float(m.get("heatFlux", 0.0)))
         en = k(mesh["edgeNodes"], np.int64)
-        ms = rs._Mesh(case.nPoint, case.nPointDomain, int(en.shape[0]), _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])), _d(k(mesh["volume"])),
+        ms = rs._Mesh(nPoint, nDom, int(en.shape[0]), _i(en), _d(k(mesh["edgeNormal"])), _d(k(mesh["coord"])), _d(k(mesh["volume"])),
                       _i(k(mesh["nbPtr"], np.int64)), _i(k(mesh["nbPoint"], np.int64)), len(mks), arr)
         od = dict(secondOrder=0, limiter=0, limCoeff=0.3, refElemLength=0.1, timeStepping=0, unstCfl=0.0, deltaUnstTime=0.0, dualTime=0, deltaUnstTimeND=0.0,
                   viscLimiter=0, device=0)
-        od.update(opts_dict(case))
+        od.update(opts_dict(case) if case is not None else opts)
         o = rs._Opts(**{f[0]: od[f[0]] for f in rs._Opts._fields_})
         self.keep += [arr, ms, ch, o]
         self.h = C.c_void_p(L.hk_create(C.byref(ms), C.byref(ch), C.byref(o)))
         assert self.h
         L.hk_use_pair(self.h, 1 if pair else 0)
-        self.nP, self.nVar, self.nPrim, self.nGrad = case.nPoint, Ns + 4, Ns + 7, Ns + 4
+        self.nP, self.nVar, self.nPrim, self.nGrad = nPoint, Ns + 4, Ns + 7, Ns + 4
 
     def close(self):
         self.L.hk_destroy(self.h)
@@ -175,6 +178,40 @@ def _run_case(hk, name, pair):
         assert "res_dual" in seen
     if cf["rans"]:
         assert {"tres", "tpost"} <= seen, seen
+
+
+@pytest.mark.parametrize("rans,pair", [(False, False), (False, True), (True, False), (True, True)])
+def test_kernels_on_the_host_equal_the_restatement_on_seeded_states(hk, rans, pair):
+    """Beyond the fixtures: three Runge-Kutta stages on a 23 x 13 channel from seeded shear-layer states with pure-fuel and pure-oxidiser regions,
+    trace species and temperatures from 500 to 1300 K (the bench's generator), five seeds — the kernels on the host against the CPU restatement
+    (pinned to the reference on the fixtures), every stage bit for bit."""
+    from rxcase import Oracle
+    pk = load_package()
+    chem = pk.load_mechanism()
+    mesh = pk.channel_mesh(23, 13)
+    opts = pk.default_opts(rans=rans, cfl=0.1)
+    alphas = [0.66667, 0.66667, 1.0]
+    for seed in (1, 2, 3, 4, 5):
+        U, T, tb = pk.synthetic_state(mesh, chem, seed=seed, rans=rans, Tpeak=500.0 + 60.0 * seed)
+        o = Oracle.from_mesh(mesh, chem, opts)
+        s = HostKernels(hk, None, pair=pair, mesh=mesh, chem=chem, opts=opts)
+        o.set_solution(U); o.set_temperature(T); o.set_turbulence(tb)
+        hk.hk_set_state(s.h, _d(np.ascontiguousarray(U)), _d(np.ascontiguousarray(T)), _d(np.ascontiguousarray(tb)))
+        for rk, a in enumerate(alphas):
+            o.preprocess(1, False); hk.hk_preprocess(s.h, C.c_int64(1), 0)
+            V, aux, g = o.primitive()
+            assert np.array_equal(s.get(0, V.shape), V) and np.array_equal(s.get(1, aux.shape), aux) and np.array_equal(s.get(2, g.shape), g), (seed, rk, "primitives")
+            if rk == 0:
+                o.set_old_solution(); o.time_step(); hk.hk_set_old(s.h); hk.hk_time_step(s.h)
+                assert np.array_equal(s.get(4, (s.nP, 3)), o.dt()), (seed, "dt")
+            for what, call in ((1, o.upwind_residual), (2, o.viscous_residual), (3, o.source_residual)):
+                call(); hk.hk_residual(s.h, what)
+                assert np.array_equal(s.get(5, (s.nP, s.nVar)), o.residual()), (seed, rk, "residual after stage %d" % what)
+            o.boundary_conditions(); hk.hk_bc(s.h)
+            assert np.array_equal(s.get(5, (s.nP, s.nVar)), o.residual()), (seed, rk, "boundary conditions")
+            o.explicit_update(a); hk.hk_update(s.h, C.c_double(a))
+            assert np.array_equal(s.get(6, (s.nP, s.nVar)), o.solution()), (seed, rk, "update")
+        s.close()
 
 
 def test_kernels_on_the_host_are_clean_under_sanitizers():
