@@ -11,6 +11,7 @@
 #include <cstring>
 #include <limits>
 #include <atomic>
+#include <thread>
 
 #define __global__
 #define __device__
@@ -42,7 +43,7 @@ inline void pair_barrier() {
   PairSync& s = ps();
   const int g = s.gen.load(std::memory_order_acquire);
   if (s.arrived.fetch_add(1, std::memory_order_acq_rel) == 1) { s.arrived.store(0, std::memory_order_relaxed); s.gen.store(g + 1, std::memory_order_release); }
-  else while (s.gen.load(std::memory_order_acquire) == g) {}
+  else { int spins = 0; while (s.gen.load(std::memory_order_acquire) == g) if (++spins > 2000) { std::this_thread::yield(); spins = 0; } }   // yields on a box with fewer cores than lanes
 }
 template <class T> inline T exchange(T v, int srcLane) {
   static_assert(sizeof(T) <= 8, "one word per lane");
