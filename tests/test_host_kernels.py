@@ -27,7 +27,8 @@ def hk(tmp_path_factory):
     so = str(tmp_path_factory.mktemp("host_kernels") / "libhost_kernels.so")
     # RX_HK_SAN=1 (set by test_kernels_on_the_host_are_clean_under_sanitizers, which runs this file once more in a child process with the
     # sanitizer runtimes preloaded): every simulated thread under AddressSanitizer and UndefinedBehaviorSanitizer
-    san = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"] if os.environ.get("RX_HK_SAN") == "1" else ["-O2"]
+    mode = os.environ.get("RX_HK_SAN")
+    san = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"] if mode == "1" else ["-O1", "-g", "-fsanitize=thread"] if mode == "tsan" else ["-O2"]
     # -DRX_VP_NO_ASYNC_D: the pair kernel's 1/D prefetch through registers (the cp.async form is inline PTX)
     cc = subprocess.run(["g++", "-std=c++17", "-pthread", "-DRX_VP_NO_ASYNC_D"] + san + ["-x", "c++", "-shared", "-fPIC", "-ffp-contract=off", "-I", os.path.join(ROOT, "tests"),
                          "-I", os.path.join(ROOT, "include"), "-I", os.path.join(PKG, "csrc"), os.path.join(ROOT, "tests", "host_kernels.cpp"), "-o", so],
@@ -218,7 +219,7 @@ def test_kernels_on_the_host_are_clean_under_sanitizers():
     """The same runs in a child process with tests/host_kernels.cpp built under AddressSanitizer and UndefinedBehaviorSanitizer: every access of
     every simulated thread — structure-of-arrays indexing, incident-edge and neighbour lists, marker blocks, the thread-private matrices in the
     stand-in for shared memory — stays inside its array, on all fixtures."""
-    if os.environ.get("RX_HK_SAN") == "1":
+    if os.environ.get("RX_HK_SAN"):
         pytest.skip("this is the child run")
     if shutil.which("g++") is None:
         pytest.skip("no g++")
@@ -230,3 +231,23 @@ def test_kernels_on_the_host_are_clean_under_sanitizers():
     run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider"], cwd=os.path.dirname(os.path.abspath(__file__)),
                          env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=2400)
     assert run.returncode == 0 and "AddressSanitizer" not in run.stdout and "runtime error" not in run.stdout and " passed" in run.stdout, run.stdout[-4000:]
+
+
+def test_two_lane_kernel_is_race_free_between_its_synchronisation_points():
+    """k_edge_visc_pair on the host under ThreadSanitizer (child process; one laminar, one RANS and one dual-time RANS fixture): the two lanes are two
+    threads that meet only at the kernel's shuffles, votes and __syncwarp calls, so any word one lane writes and the other reads without such a
+    meeting in between is reported — on the device the lanes of a warp advance together and would hide it."""
+    if os.environ.get("RX_HK_SAN"):
+        pytest.skip("this is the child run")
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    lib = subprocess.run(["g++", "-print-file-name=libtsan.so"], stdout=subprocess.PIPE, text=True).stdout.strip()
+    if not (os.path.isabs(lib) and os.path.exists(lib)):
+        pytest.skip("this g++ has no ThreadSanitizer runtime")
+    import sys
+    env = dict(os.environ, RX_HK_SAN="tsan", LD_PRELOAD=lib, TSAN_OPTIONS="halt_on_error=0 exitcode=0")
+    run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider", "-k",
+                          "two_lanes and (channel_lam_rk or channel_rans_dualtime2 or channel_rans])"],
+                         cwd=os.path.dirname(os.path.abspath(__file__)), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=2400)
+    assert run.returncode == 0 and " passed" in run.stdout, run.stdout[-4000:]
+    assert "ThreadSanitizer: data race" not in run.stdout, run.stdout[-6000:]
