@@ -230,6 +230,8 @@ def test_kernels_on_the_host_are_clean_under_sanitizers():
     env = dict(os.environ, RX_HK_SAN="1", LD_PRELOAD=" ".join(libs), ASAN_OPTIONS="detect_leaks=0:verify_asan_link_order=0")
     run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider"], cwd=os.path.dirname(os.path.abspath(__file__)),
                          env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=2400)
+    if "Shadow memory range interleaves" in run.stdout or "ReserveShadowMemoryRange failed" in run.stdout:
+        pytest.skip("the AddressSanitizer runtime cannot start in this process layout: " + run.stdout[-300:])
     assert run.returncode == 0 and "AddressSanitizer" not in run.stdout and "runtime error" not in run.stdout and " passed" in run.stdout, run.stdout[-4000:]
 
 
@@ -249,5 +251,7 @@ def test_two_lane_kernel_is_race_free_between_its_synchronisation_points():
     run = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider", "-k",
                           "two_lanes and (channel_lam_rk or channel_rans_dualtime2 or channel_rans])"],
                          cwd=os.path.dirname(os.path.abspath(__file__)), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=2400)
+    if "FATAL: ThreadSanitizer" in run.stdout or "unexpected memory mapping" in run.stdout:
+        pytest.skip("the ThreadSanitizer runtime cannot start in this process layout: " + run.stdout[-300:])
     assert run.returncode == 0 and " passed" in run.stdout, run.stdout[-4000:]
     assert "ThreadSanitizer: data race" not in run.stdout, run.stdout[-6000:]
